@@ -1,0 +1,303 @@
+"""ctypes binding of libswarm_sm100.so (C ABI in include/swarm_b200.h).
+
+The reference has no native layer (every FLOP goes through diffusers ->
+torch -> cuBLAS/cuDNN/SDPA, e.g. swarm/diffusion/diffusion_func.py:96).  Here the hot ops are our
+own sm_100a kernels; this module is the only place Python touches them.  On a machine with a GPU
+a missing library is a hard error -- there is no silent PyTorch fallback on the hot path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from pathlib import Path
+
+import torch
+
+from ..build_native import LIB_PATH, build
+
+_lock = threading.Lock()
+_lib = None
+
+ACT_NONE, ACT_SILU, ACT_GELU, ACT_GEGLU = 0, 1, 2, 3
+
+# count of kernel launches issued through this binding (bench.py reports it)
+launch_count = 0
+
+
+class IGemmParams(C.Structure):
+    _fields_ = [
+        ("a1", C.c_void_p), ("a2", C.c_void_p),
+        ("c1", C.c_int32), ("c2", C.c_int32),
+        ("n", C.c_int32), ("h", C.c_int32), ("w", C.c_int32),
+        ("kh", C.c_int32), ("kw", C.c_int32), ("pad", C.c_int32),
+        ("wgt", C.c_void_p),
+        ("cout", C.c_int32),
+        ("bias", C.c_void_p),
+        ("row_bias", C.c_void_p),
+        ("row_bias_ld", C.c_int32),
+        ("residual", C.c_void_p),
+        ("ldr", C.c_int32),
+        ("out", C.c_void_p),
+        ("ldc", C.c_int32),
+        ("act", C.c_int32),
+        ("out_scale", C.c_float),
+        ("bf16", C.c_int32),
+        ("tile_n", C.c_int32),
+        ("gn_stats", C.c_void_p),
+        ("gn_groups", C.c_int32),
+    ]
+
+
+class AttnParams(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p),
+        ("q_stride_b", C.c_int64), ("q_stride_s", C.c_int64), ("q_stride_h", C.c_int64),
+        ("k_stride_b", C.c_int64), ("k_stride_s", C.c_int64), ("k_stride_h", C.c_int64),
+        ("v_stride_b", C.c_int64), ("v_stride_s", C.c_int64), ("v_stride_h", C.c_int64),
+        ("out", C.c_void_p), ("o_stride_b", C.c_int64), ("o_stride_s", C.c_int64),
+        ("batch", C.c_int32), ("heads", C.c_int32), ("seq_q", C.c_int32), ("seq_kv", C.c_int32),
+        ("head_dim", C.c_int32),
+        ("scale", C.c_float),
+    ]
+
+
+class SchedParams(C.Structure):
+    _fields_ = [
+        ("eps", C.c_void_p),
+        ("n_cond", C.c_int32), ("rows", C.c_int32), ("c", C.c_int32), ("eps_ld", C.c_int32),
+        ("g_text", C.c_float), ("g_image", C.c_float),
+        ("x", C.c_void_p), ("x0_prev", C.c_void_p), ("noise", C.c_void_p),
+        ("x_model_in", C.c_void_p),
+        ("xin_ld", C.c_int32),
+        ("coef", C.c_void_p),
+        ("step_idx", C.c_void_p),
+    ]
+
+
+def available() -> bool:
+    return LIB_PATH.exists()
+
+
+def lib() -> C.CDLL:
+    """Loads (building first if the .so is absent) the native library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            path = LIB_PATH if LIB_PATH.exists() else build()
+            l = C.CDLL(str(path))
+            l.sw_last_error.restype = C.c_char_p
+            for name in (
+                "sw_igemm", "sw_flash_attn", "sw_groupnorm_nhwc", "sw_layernorm", "sw_upsample2x_nhwc",
+                "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
+                "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8",
+            ):
+                getattr(l, name).restype = C.c_int
+            l.sw_igemm.argtypes = [C.POINTER(IGemmParams), C.c_void_p]
+            l.sw_flash_attn.argtypes = [C.POINTER(AttnParams), C.c_void_p]
+            l.sw_groupnorm_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                            C.c_int, C.c_void_p, C.c_void_p]
+            l.sw_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                       C.c_float, C.c_void_p]
+            l.sw_upsample2x_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_void_p]
+            l.sw_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 11 + [C.c_void_p]
+            l.sw_nchw_to_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
+            l.sw_nhwc_to_nchw.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
+            l.sw_timestep_embedding.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                C.c_float, C.c_int, C.c_float, C.c_void_p]
+            l.sw_advance_counter.argtypes = [C.c_void_p, C.c_void_p]
+            l.sw_add.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+            l.sw_silu.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+            l.sw_sched_step.argtypes = [C.POINTER(SchedParams), C.c_void_p]
+            l.sw_image_to_u8.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+            _lib = l
+    return _lib
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().sw_last_error()
+        raise RuntimeError(f"{what} failed ({rc}): {msg.decode() if msg else '?'}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _count(n=1):
+    global launch_count
+    launch_count += n
+
+
+def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.dtype != torch.float16 or not t.is_cuda:
+        raise TypeError(f"{name}: expected a CUDA fp16 tensor, got {t.dtype} on {t.device}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: must be contiguous")
+    return t
+
+
+# --------------------------------------------------------------------------------------- ops
+def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
+          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0):
+    """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
+    [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
+    _f16(a1, "a1"); _f16(wgt, "wgt"); _f16(out, "out")
+    c1 = a1.shape[-1]
+    c2 = 0 if a2 is None else _f16(a2, "a2").shape[-1]
+    cout = wgt.shape[0]
+    assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
+    assert a1.numel() == n * h * w * c1
+    p = IGemmParams()
+    p.a1, p.a2 = _ptr(a1), _ptr(a2)
+    p.c1, p.c2 = c1, c2
+    p.n, p.h, p.w = n, h, w
+    p.kh, p.kw, p.pad = kh, kw, pad
+    p.wgt = _ptr(wgt)
+    p.cout = cout
+    p.bias = _ptr(bias)
+    p.row_bias = _ptr(row_bias)
+    p.row_bias_ld = 0 if row_bias is None else row_bias.shape[-1]
+    p.residual = _ptr(residual)
+    p.ldr = 0 if residual is None else residual.shape[-1]
+    p.out = _ptr(out)
+    p.ldc = out.shape[-1]
+    p.act = act
+    p.out_scale = out_scale
+    p.bf16 = 0
+    p.tile_n = tile_n
+    p.gn_stats = None
+    p.gn_groups = 0
+    _check(lib().sw_igemm(C.byref(p), _stream()), "sw_igemm")
+    _count()
+    return out
+
+
+def linear(x, wgt, out=None, **kw):
+    """x: [..., K] fp16 contiguous; wgt: [N, K]. Returns [..., N] (N/2 for GEGLU)."""
+    k = x.shape[-1]
+    m = x.numel() // k
+    ncols = wgt.shape[0] // 2 if kw.get("act") == ACT_GEGLU else wgt.shape[0]
+    if out is None:
+        out = torch.empty(*x.shape[:-1], ncols, dtype=torch.float16, device=x.device)
+    igemm(x, wgt, out, n=1, h=1, w=m, **kw)
+    return out
+
+
+def flash_attn(q, k, v, out, *, batch, heads, seq_q, seq_kv, head_dim, scale=None):
+    """q/k/v: fp16 tensors viewed as [batch, seq, heads, head_dim] (strides taken from the views);
+    out: [batch, seq_q, heads*head_dim]."""
+    for t, nm in ((q, "q"), (k, "k"), (v, "v")):
+        if t.dtype != torch.float16 or t.stride(-1) != 1 or t.dim() != 4:
+            raise ValueError(f"{nm}: need fp16 [b, s, h, d] view with contiguous d")
+    p = AttnParams()
+    p.q, p.k, p.v = q.data_ptr(), k.data_ptr(), v.data_ptr()
+    p.q_stride_b, p.q_stride_s, p.q_stride_h = q.stride(0), q.stride(1), q.stride(2)
+    p.k_stride_b, p.k_stride_s, p.k_stride_h = k.stride(0), k.stride(1), k.stride(2)
+    p.v_stride_b, p.v_stride_s, p.v_stride_h = v.stride(0), v.stride(1), v.stride(2)
+    p.out = out.data_ptr()
+    p.o_stride_b, p.o_stride_s = out.stride(0), out.stride(1)
+    p.batch, p.heads, p.seq_q, p.seq_kv, p.head_dim = batch, heads, seq_q, seq_kv, head_dim
+    p.scale = float(scale if scale is not None else head_dim ** -0.5)
+    _check(lib().sw_flash_attn(C.byref(p), _stream()), "sw_flash_attn")
+    _count()
+    return out
+
+
+def groupnorm(x, gamma, beta, out, *, n, hw, groups, eps, silu, stats, x2=None):
+    c1 = x.shape[-1]
+    c2 = 0 if x2 is None else x2.shape[-1]
+    _check(lib().sw_groupnorm_nhwc(_ptr(x), _ptr(x2), _ptr(out), _ptr(gamma), _ptr(beta), n, hw, c1, c2,
+                                   groups, eps, int(silu), _ptr(stats), _stream()), "sw_groupnorm_nhwc")
+    _count(3)
+    return out
+
+
+def layernorm(x, gamma, beta, out, eps=1e-5):
+    c = x.shape[-1]
+    _check(lib().sw_layernorm(_ptr(x), _ptr(out), _ptr(gamma), _ptr(beta), x.numel() // c, c, eps, _stream()),
+           "sw_layernorm")
+    _count()
+    return out
+
+
+def upsample2x(x, out, *, n, h, w):
+    _check(lib().sw_upsample2x_nhwc(_ptr(x), _ptr(out), n, h, w, x.shape[-1], _stream()), "sw_upsample2x_nhwc")
+    _count()
+    return out
+
+
+def im2col(x, out, *, n, h, w, kh, kw, stride, pad_top, pad_left, oh, ow):
+    _check(lib().sw_im2col_nhwc(_ptr(x), _ptr(out), n, h, w, x.shape[-1], kh, kw, stride, pad_top, pad_left,
+                                oh, ow, _stream()), "sw_im2col_nhwc")
+    _count()
+    return out
+
+
+def nchw_to_nhwc(x, out, c_pad):
+    n, c, h, w = x.shape
+    _check(lib().sw_nchw_to_nhwc(_ptr(x), _ptr(out), n, c, h, w, c_pad, int(x.dtype == torch.float32), _stream()),
+           "sw_nchw_to_nhwc")
+    _count()
+    return out
+
+
+def nhwc_to_nchw(x, out, c_pad):
+    n, c, h, w = out.shape
+    _check(lib().sw_nhwc_to_nchw(_ptr(x), _ptr(out), n, c, h, w, c_pad, int(out.dtype == torch.float32), _stream()),
+           "sw_nhwc_to_nchw")
+    _count()
+    return out
+
+
+def timestep_embedding(t_table, step_idx, out, *, n, dim, max_period=10000.0, flip_sin_to_cos=True,
+                       freq_shift=0.0):
+    _check(lib().sw_timestep_embedding(_ptr(t_table), _ptr(step_idx), _ptr(out), n, dim, max_period,
+                                       int(flip_sin_to_cos), freq_shift, _stream()), "sw_timestep_embedding")
+    _count()
+    return out
+
+
+def advance_counter(counter):
+    _check(lib().sw_advance_counter(_ptr(counter), _stream()), "sw_advance_counter")
+    _count()
+
+
+def add(a, b, out):
+    _check(lib().sw_add(_ptr(a), _ptr(b), _ptr(out), a.numel(), _stream()), "sw_add")
+    _count()
+    return out
+
+
+def silu(x, out):
+    _check(lib().sw_silu(_ptr(x), _ptr(out), x.numel(), _stream()), "sw_silu")
+    _count()
+    return out
+
+
+def sched_step(*, eps, n_cond, rows, c, eps_ld, g_text, g_image, x, x0_prev, noise, x_model_in, xin_ld,
+               coef, step_idx):
+    p = SchedParams()
+    p.eps = _ptr(eps)
+    p.n_cond, p.rows, p.c, p.eps_ld = n_cond, rows, c, eps_ld
+    p.g_text, p.g_image = g_text, g_image
+    p.x, p.x0_prev, p.noise = _ptr(x), _ptr(x0_prev), _ptr(noise)
+    p.x_model_in = _ptr(x_model_in)
+    p.xin_ld = xin_ld
+    p.coef = _ptr(coef)
+    p.step_idx = _ptr(step_idx)
+    _check(lib().sw_sched_step(C.byref(p), _stream()), "sw_sched_step")
+    _count()
+
+
+def image_to_u8(x_nhwc, out, pixels, c_pad):
+    _check(lib().sw_image_to_u8(_ptr(x_nhwc), _ptr(out), pixels, c_pad, _stream()), "sw_image_to_u8")
+    _count()
+    return out

@@ -1,0 +1,44 @@
+"""Weight re-packing from the diffusers/torch layouts into what the sm_100a kernels consume.
+
+Done once at model-load time (the reference re-reads checkpoints per job,
+swarm/diffusion/diffusion_func.py:41-46; here packed weights stay resident)."""
+from __future__ import annotations
+
+import torch
+
+
+def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int | None = None) -> torch.Tensor:
+    """[cout, cin, kh, kw] (torch conv layout) -> [cout_pad, kh*kw*cin_pad], tap-major then channel,
+    which is the K order sw_igemm walks (tap, 64-channel slab)."""
+    cout, cin, kh, kw = w.shape
+    cin_pad = cin if cin_pad is None else cin_pad
+    cout_pad = cout if cout_pad is None else cout_pad
+    out = torch.zeros(cout_pad, kh, kw, cin_pad, dtype=w.dtype, device=w.device)
+    out[:cout, :, :, :cin] = w.permute(0, 2, 3, 1)
+    return out.reshape(cout_pad, kh * kw * cin_pad).contiguous()
+
+
+def pad_vector(b: torch.Tensor | None, n_pad: int) -> torch.Tensor | None:
+    if b is None:
+        return None
+    if b.shape[0] == n_pad:
+        return b.contiguous()
+    out = torch.zeros(n_pad, dtype=b.dtype, device=b.device)
+    out[: b.shape[0]] = b
+    return out
+
+
+def interleave_geglu(w: torch.Tensor, b: torch.Tensor | None):
+    """GEGLU projection [2*inner, d] = [values; gates] -> blocks of 64 value rows followed by their
+    64 gate rows, so one 128-wide MMA tile holds both halves and the epilogue can fuse x*gelu(g)."""
+    two_inner = w.shape[0]
+    inner = two_inner // 2
+    assert inner % 64 == 0, "GEGLU inner dim must be a multiple of 64"
+    val, gate = w[:inner], w[inner:]
+    wi = torch.stack([val.reshape(inner // 64, 64, -1), gate.reshape(inner // 64, 64, -1)], dim=1)
+    wi = wi.reshape(two_inner, -1).contiguous()
+    bi = None
+    if b is not None:
+        bv, bg = b[:inner], b[inner:]
+        bi = torch.stack([bv.reshape(inner // 64, 64), bg.reshape(inner // 64, 64)], dim=1).reshape(two_inner).contiguous()
+    return wi, bi

@@ -1,0 +1,430 @@
+// Implicit-GEMM convolution / linear layer for sm_100a.
+//
+// One CTA computes a 128 x BN output tile: 128 output pixels (a BW x BH x BI box of the
+// channels-last activation) by BN output channels.  The K loop walks (filter tap, 64-channel
+// slab): for every step one TMA box load fetches the *shifted* activation window straight from
+// the NHWC tensor (out-of-bounds rows/cols are zero-filled by the TMA unit, which is the conv
+// padding) and one fetches the matching 64-wide weight slab.  tcgen05.mma accumulates in TMEM;
+// four epilogue warps drain TMEM with tcgen05.ld and apply bias / time-embedding row bias /
+// activation / GEGLU / residual before a vectorised fp16 store.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).
+#include "../include/swarm_b200.h"
+#include "common.cuh"
+#include "host_util.h"
+
+namespace {
+
+using namespace sw;
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kThreads = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
+
+struct IGemmArgs {
+    int c1, c2;
+    int n, h, w;
+    int kh, kw, pad;
+    int cout;
+    int bw, bh, bi;  // tile box: bw*bh*bi <= 128 pixels
+    int tiles_x, tiles_y;
+    int stages;
+    uint32_t idesc;
+    const __half* bias;
+    const __half* row_bias;
+    int row_bias_ld;
+    const __half* residual;
+    int ldr;
+    __half* out;
+    int ldc;
+    int act;
+    float out_scale;
+    int bf16;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads)
+    k_igemm(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+            const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    constexpr int B_STAGE_BYTES = BN * BK * 2;
+    constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B operands need 1024-byte aligned stage bases.
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int stages = p.stages;
+
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
+    uint64_t* empty = full + stages;
+    uint64_t* acc_full = empty + stages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+    // spatial tile -> origin pixel
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x;
+    t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int tn = t / p.tiles_y;
+    const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+    const int col0 = blockIdx.y * BN;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmA2);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < stages; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], 1);
+            }
+            mbar_init(acc_full, 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc<TMEM_COLS>(tmem_slot);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    const int nkb1 = (p.c1 + BK - 1) / BK;
+    const int nkb2 = (p.c2 + BK - 1) / BK;
+    const int per_tap = nkb1 + nkb2;
+    const int ctot = p.c1 + p.c2;
+    const int total = p.kh * p.kw * per_tap;
+    const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int it = 0; it < total; ++it) {
+                mbar_wait(&empty[s], ph ^ 1);
+                const int tap = it / per_tap;
+                const int j = it - tap * per_tap;
+                const int ky = tap / p.kw, kx = tap - ky * p.kw;
+                uint8_t* sa = smem + s * STAGE_BYTES;
+                uint8_t* sb = sa + A_STAGE_BYTES;
+                mbar_expect_tx(&full[s], a_bytes + B_STAGE_BYTES);
+                int kcol;
+                if (j < nkb1) {
+                    tma_load_4d(sa, &tmA1, &full[s], j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    kcol = tap * ctot + j * BK;
+                } else {
+                    const int j2 = j - nkb1;
+                    tma_load_4d(sa, &tmA2, &full[s], j2 * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    kcol = tap * ctot + p.c1 + j2 * BK;
+                }
+                tma_load_2d(sb, &tmB, &full[s], kcol, col0);
+                if (++s == stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            uint32_t acc = 0;
+            for (int it = 0; it < total; ++it) {
+                mbar_wait(&full[s], ph);
+                tc_fence_after();
+                const int j = it % per_tap;
+                const int cvalid = (j < nkb1) ? (p.c1 - j * BK) : (p.c2 - (j - nkb1) * BK);
+                const int ksteps = cvalid >= BK ? BK / 16 : (cvalid + 15) / 16;
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+                const uint32_t sb = sa + A_STAGE_BYTES;
+                const uint64_t adesc = umma_desc_sw128(sa, 16, 1024);
+                const uint64_t bdesc = umma_desc_sw128(sb, 16, 1024);
+                for (int k = 0; k < ksteps; ++k) {
+                    // +32 bytes per 16-element K step inside the 128-byte swizzle row
+                    umma_f16(tmem_acc, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), p.idesc, acc);
+                    acc = 1;
+                }
+                umma_commit(&empty[s]);
+                if (++s == stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+            umma_commit(acc_full);
+        }
+    } else {
+        // ---------------- epilogue: one thread per accumulator row
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const int xl = r % p.bw;
+        const int r2 = r / p.bw;
+        const int yl = r2 % p.bh;
+        const int nl = r2 / p.bh;
+        const int x = x0 + xl, y = y0 + yl, ni = n0 + nl;
+        const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
+        const size_t m = (size_t(ni) * p.h + y) * p.w + x;
+
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
+
+        if (p.act == SW_ACT_GEGLU) {
+            // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates
+            constexpr int HALF = BN / 2;
+            const int ocol0 = blockIdx.y * HALF;
+            const int ncols_out = p.cout / 2;
+#pragma unroll 1
+            for (int c = 0; c < HALF; c += 16) {
+                uint32_t v[16], g[16];
+                tmem_ld16(trow + c, v);
+                tmem_ld16(trow + HALF + c, g);
+                tmem_ld_wait();
+                if (row_ok && ocol0 + c < ncols_out) {
+                    uint32_t o[8];
+#pragma unroll
+                    for (int j = 0; j < 16; j += 2) {
+                        float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
+                        float g0 = __uint_as_float(g[j]), g1 = __uint_as_float(g[j + 1]);
+                        if (p.bias) {
+                            a0 += __half2float(p.bias[col0 + c + j]);
+                            a1 += __half2float(p.bias[col0 + c + j + 1]);
+                            g0 += __half2float(p.bias[col0 + HALF + c + j]);
+                            g1 += __half2float(p.bias[col0 + HALF + c + j + 1]);
+                        }
+                        o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
+                    }
+                    uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
+                    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                }
+            }
+        } else {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(trow + c, v);
+                tmem_ld_wait();
+                if (!row_ok) continue;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const int col = col0 + c + g8 * 8;
+                    if (col >= p.cout) break;
+                    float f[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]);
+                    if (p.bias) {
+                        const uint4 b = *reinterpret_cast<const uint4*>(p.bias + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    if (p.row_bias) {
+                        const uint4 b = *reinterpret_cast<const uint4*>(
+                            p.row_bias + size_t(ni) * p.row_bias_ld + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    if (p.act == SW_ACT_SILU) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
+                    } else if (p.act == SW_ACT_GELU) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                    }
+                    if (p.out_scale != 1.0f) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
+                    }
+                    if (p.residual) {
+                        const uint4 b =
+                            *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(p.out + m * p.ldc + col) =
+                        make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
+                                   pack_h2(f[6], f[7]));
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_acc);
+    }
+}
+
+// Choose the pixel box (bw x bh x bi, <= 128 pixels) that wastes the fewest MMA rows.
+void pick_box(int n, int h, int w, int* bw, int* bh, int* bi) {
+    double best = -1.0;
+    int b0 = 1, b1 = 1, b2 = 1;
+    for (int cw = 1; cw <= w && cw <= 128; ++cw) {
+        const int tiles_x = (w + cw - 1) / cw;
+        const int max_h = 128 / cw;
+        for (int ch = 1; ch <= h && ch <= max_h; ++ch) {
+            int ci = 1;
+            if (cw == w && ch == h) {
+                ci = 128 / (cw * ch);
+                if (ci > n) ci = n;
+                if (ci < 1) ci = 1;
+            }
+            const int tiles_y = (h + ch - 1) / ch;
+            const int tiles_n = (n + ci - 1) / ci;
+            const double useful = double(n) * h * w;
+            const double spent = double(tiles_x) * tiles_y * tiles_n * 128.0;
+            double score = useful / spent;
+            // prefer wide boxes (longer contiguous TMA rows) on ties
+            score += 1e-6 * cw;
+            if (score > best) {
+                best = score;
+                b0 = cw;
+                b1 = ch;
+                b2 = ci;
+            }
+        }
+    }
+    *bw = b0;
+    *bh = b1;
+    *bi = b2;
+}
+
+template <int BN>
+int launch(const sw_igemm_params* p, const IGemmArgs& a, const CUtensorMap& tA1,
+           const CUtensorMap& tA2, const CUtensorMap& tB, int grid_x, cudaStream_t st) {
+    constexpr int STAGE_BYTES = A_STAGE_BYTES + BN * BK * 2;
+    const int smem = a.stages * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static int configured_smem[64] = {0};
+    int dev = 0;
+    SW_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 64 && configured_smem[dev] < smem) {
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        200 * 1024));
+        configured_smem[dev] = 200 * 1024;
+    }
+    const int ncols = a.cout;
+    dim3 grid(grid_x, (ncols + BN - 1) / BN);
+    k_igemm<BN><<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
+    SW_CUDA_OK(cudaGetLastError());
+    (void)p;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
+    if (!p || !p->a1 || !p->wgt || !p->out) return swh::fail(-1, "sw_igemm: null argument");
+    if (p->c1 <= 0 || p->c1 % 8 || p->c2 % 8 || p->c2 < 0 || (p->c2 > 0 && !p->a2))
+        return swh::fail(-1, "sw_igemm: channel counts must be positive multiples of 8 (c1=%d c2=%d)",
+                         p->c1, p->c2);
+    if (p->cout <= 0 || p->cout % 8) return swh::fail(-1, "sw_igemm: cout=%d not a multiple of 8", p->cout);
+    if (p->n <= 0 || p->h <= 0 || p->w <= 0 || p->kh <= 0 || p->kw <= 0)
+        return swh::fail(-1, "sw_igemm: bad shape");
+    if (p->gn_stats) return swh::fail(-1, "sw_igemm: gn_stats epilogue not available in this build");
+    if (p->ldc % 8 || (p->residual && p->ldr % 8) || (p->row_bias && p->row_bias_ld % 8))
+        return swh::fail(-1, "sw_igemm: leading dimensions must be multiples of 8");
+
+    IGemmArgs a;
+    memset(&a, 0, sizeof(a));
+    a.c1 = p->c1;
+    a.c2 = p->c2;
+    a.n = p->n;
+    a.h = p->h;
+    a.w = p->w;
+    a.kh = p->kh;
+    a.kw = p->kw;
+    a.pad = p->pad;
+    a.cout = p->cout;
+    pick_box(p->n, p->h, p->w, &a.bw, &a.bh, &a.bi);
+    a.tiles_x = (p->w + a.bw - 1) / a.bw;
+    a.tiles_y = (p->h + a.bh - 1) / a.bh;
+    const int tiles_n = (p->n + a.bi - 1) / a.bi;
+    const int grid_x = a.tiles_x * a.tiles_y * tiles_n;
+    a.bias = static_cast<const __half*>(p->bias);
+    a.row_bias = static_cast<const __half*>(p->row_bias);
+    a.row_bias_ld = p->row_bias_ld;
+    a.residual = static_cast<const __half*>(p->residual);
+    a.ldr = p->ldr;
+    a.out = static_cast<__half*>(p->out);
+    a.ldc = p->ldc;
+    a.act = p->act;
+    a.out_scale = p->out_scale == 0.0f ? 1.0f : p->out_scale;
+    a.bf16 = p->bf16;
+
+    // Tile width: 128 unless that leaves most SMs idle or the layer is narrow.
+    int bn = p->tile_n;
+    if (bn == 0) {
+        bn = 128;
+        if (p->cout <= 64) bn = 64;
+        else if (p->act != SW_ACT_GEGLU) {
+            const long ctas128 = long(grid_x) * ((p->cout + 127) / 128);
+            if (ctas128 < 2L * swh::sm_count()) bn = 64;
+        }
+    }
+    if (p->act == SW_ACT_GEGLU) {
+        bn = 128;
+        if (p->cout % 128) return swh::fail(-1, "sw_igemm: GEGLU needs cout %% 128 == 0");
+    }
+    if (bn != 64 && bn != 128) return swh::fail(-1, "sw_igemm: tile_n must be 64 or 128");
+
+    const int ktotal = p->kh * p->kw * (p->c1 + p->c2);
+    const int kblocks = p->kh * p->kw * ((p->c1 + 63) / 64 + (p->c2 + 63) / 64);
+    int stages = bn == 128 ? 3 : 4;  // 96 KB either way: two CTAs per SM overlap epilogue and mainloop
+    if (kblocks < stages) stages = kblocks;
+    a.stages = stages;
+    a.idesc = sw::umma_idesc(128, bn, p->bf16 ? 1 : 0, 0, 0);
+
+    CUtensorMap tA1, tA2, tB;
+    {
+        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
+        const uint64_t str[3] = {uint64_t(p->c1) * 2, uint64_t(p->w) * p->c1 * 2,
+                                 uint64_t(p->h) * p->w * p->c1 * 2};
+        const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
+        int rc = swh::encode_tmap_f16(&tA1, p->a1, 4, dims, str, box);
+        if (rc) return rc;
+    }
+    if (p->c2 > 0) {
+        const uint64_t dims[4] = {uint64_t(p->c2), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
+        const uint64_t str[3] = {uint64_t(p->c2) * 2, uint64_t(p->w) * p->c2 * 2,
+                                 uint64_t(p->h) * p->w * p->c2 * 2};
+        const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
+        int rc = swh::encode_tmap_f16(&tA2, p->a2, 4, dims, str, box);
+        if (rc) return rc;
+    } else {
+        tA2 = tA1;
+    }
+    {
+        const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout)};
+        const uint64_t str[1] = {uint64_t(ktotal) * 2};
+        const uint32_t box[2] = {64, uint32_t(bn)};
+        int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
+        if (rc) return rc;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (bn == 128) return launch<128>(p, a, tA1, tA2, tB, grid_x, st);
+    return launch<64>(p, a, tA1, tA2, tB, grid_x, st);
+}

@@ -1,0 +1,261 @@
+// GroupNorm(+SiLU) and LayerNorm over channels-last fp16 activations (memory-bound; 16-byte
+// vector accesses, fp32 statistics).  The tensors of a diffusion UNet fit in the 126 MB L2, so
+// the statistics pass and the apply pass both stream from L2, not HBM.
+#include "../include/swarm_b200.h"
+#include "common.cuh"
+#include "host_util.h"
+
+namespace {
+
+using namespace sw;
+
+// ---- GroupNorm statistics: grid (chunks, n). Thread <-> fixed channel octet, strided rows.
+// The input may be the channel-concatenation of two tensors (UNet skip connections): octets below
+// c1 come from x1, the rest from x2.
+__global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1,
+                           float* __restrict__ stats, int hw, int c, int groups, int rows_per_cta,
+                           int rows_per_pass) {
+    extern __shared__ float sh[];  // [groups][2]
+    const int octs = c >> 3;
+    const int n = blockIdx.y;
+    const int r0 = blockIdx.x * rows_per_cta;
+    const int r1 = min(hw, r0 + rows_per_cta);
+    const int oct = threadIdx.x % octs;
+    const int rp = threadIdx.x / octs;
+    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) sh[i] = 0.0f;
+    __syncthreads();
+
+    float s[8], ss[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
+    if (rp < rows_per_pass) {
+        const bool first = oct * 8 < c1;
+        const int cs = first ? c1 : c - c1;
+        const __half* base =
+            (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
+        for (int r = r0 + rp; r < r1; r += rows_per_pass) {
+            const uint4 v = *reinterpret_cast<const uint4*>(base + size_t(r) * cs);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_h2(w[j]);
+                s[2 * j] += f.x;
+                ss[2 * j] += f.x * f.x;
+                s[2 * j + 1] += f.y;
+                ss[2 * j + 1] += f.y * f.y;
+            }
+        }
+        const int cg = c / groups;
+        int g_prev = (oct * 8) / cg;
+        float as = 0.0f, ass = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int g = (oct * 8 + i) / cg;
+            if (g != g_prev) {
+                atomicAdd(&sh[g_prev * 2], as);
+                atomicAdd(&sh[g_prev * 2 + 1], ass);
+                as = ass = 0.0f;
+                g_prev = g;
+            }
+            as += s[i];
+            ass += ss[i];
+        }
+        atomicAdd(&sh[g_prev * 2], as);
+        atomicAdd(&sh[g_prev * 2 + 1], ass);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x)
+        atomicAdd(&stats[size_t(n) * groups * 2 + i], sh[i]);
+}
+
+// ---- GroupNorm apply: y = silu?((x-mean)*rstd*gamma+beta)
+__global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1,
+                           __half* __restrict__ y,
+                           const __half* __restrict__ gamma, const __half* __restrict__ beta,
+                           const float* __restrict__ stats, int hw, int c, int groups, float eps,
+                           int silu, int rows_per_cta, int rows_per_pass) {
+    extern __shared__ float sh[];  // a[c], b[c]
+    float* sa = sh;
+    float* sb = sh + c;
+    const int n = blockIdx.y;
+    const int cg = c / groups;
+    const float inv_cnt = 1.0f / (float(hw) * float(cg));
+    for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {
+        const int g = ch / cg;
+        const float sum = stats[(size_t(n) * groups + g) * 2];
+        const float sq = stats[(size_t(n) * groups + g) * 2 + 1];
+        const float mean = sum * inv_cnt;
+        const float var = fmaxf(sq * inv_cnt - mean * mean, 0.0f);
+        const float rstd = rsqrtf(var + eps);
+        const float ga = gamma ? __half2float(gamma[ch]) : 1.0f;
+        const float be = beta ? __half2float(beta[ch]) : 0.0f;
+        sa[ch] = rstd * ga;
+        sb[ch] = be - mean * rstd * ga;
+    }
+    __syncthreads();
+    const int octs = c >> 3;
+    const int oct = threadIdx.x % octs;
+    const int rp = threadIdx.x / octs;
+    if (rp >= rows_per_pass) return;
+    const int r0 = blockIdx.x * rows_per_cta;
+    const int r1 = min(hw, r0 + rows_per_cta);
+    float a[8], b[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        a[i] = sa[oct * 8 + i];
+        b[i] = sb[oct * 8 + i];
+    }
+    const size_t base = (size_t(n) * hw) * c + oct * 8;
+    const bool first = oct * 8 < c1;
+    const int cs = first ? c1 : c - c1;
+    const __half* src = (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
+    for (int r = r0 + rp; r < r1; r += rows_per_pass) {
+        const uint4 v = *reinterpret_cast<const uint4*>(src + size_t(r) * cs);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_h2(w[j]);
+            float u0 = fmaf(f.x, a[2 * j], b[2 * j]);
+            float u1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
+            if (silu) {
+                u0 = silu_f(u0);
+                u1 = silu_f(u1);
+            }
+            o[j] = pack_h2(u0, u1);
+        }
+        *reinterpret_cast<uint4*>(y + base + size_t(r) * c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// ---- LayerNorm: one warp per row, row cached in registers (c <= 2048).
+template <int MAX_OCT>
+__global__ void k_layernorm(const __half* __restrict__ x, __half* __restrict__ y,
+                            const __half* __restrict__ gamma, const __half* __restrict__ beta,
+                            int rows, int c, float eps) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= rows) return;
+    const int octs = c >> 3;
+    const __half* xr = x + size_t(warp) * c;
+    float v[MAX_OCT][8];
+    float sum = 0.0f;
+#pragma unroll
+    for (int k = 0; k < MAX_OCT; ++k) {
+        const int o = lane + k * 32;
+        if (o < octs) {
+            const uint4 u = *reinterpret_cast<const uint4*>(xr + o * 8);
+            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_h2(w[j]);
+                v[k][2 * j] = f.x;
+                v[k][2 * j + 1] = f.y;
+                sum += f.x + f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum / float(c);
+    float var = 0.0f;
+#pragma unroll
+    for (int k = 0; k < MAX_OCT; ++k) {
+        if (lane + k * 32 < octs) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float d = v[k][j] - mean;
+                var += d * d;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
+    const float rstd = rsqrtf(var / float(c) + eps);
+    __half* yr = y + size_t(warp) * c;
+#pragma unroll
+    for (int k = 0; k < MAX_OCT; ++k) {
+        const int o = lane + k * 32;
+        if (o < octs) {
+            const uint4 g = *reinterpret_cast<const uint4*>(gamma + o * 8);
+            const uint4 b = *reinterpret_cast<const uint4*>(beta + o * 8);
+            const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+            const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+            uint32_t out[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 gf = unpack_h2(gw[j]);
+                const float2 bf = unpack_h2(bw[j]);
+                out[j] = pack_h2((v[k][2 * j] - mean) * rstd * gf.x + bf.x,
+                                 (v[k][2 * j + 1] - mean) * rstd * gf.y + bf.y);
+            }
+            *reinterpret_cast<uint4*>(yr + o * 8) = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+    }
+}
+
+}  // namespace
+
+// Shared by the public entry point; `stats` must already be usable device memory.
+int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                        int n, int hw, int c1, int c2, int groups, float eps, int silu, float* stats,
+                        cudaStream_t st) {
+    const int c = c1 + c2;
+    if (c1 <= 0 || c2 < 0 || c1 % 8 || (c2 > 0 && !x2))
+        return swh::fail(-1, "sw_groupnorm_nhwc: bad channel split c1=%d c2=%d", c1, c2);
+    if (c % 8 || groups <= 0 || c % groups)
+        return swh::fail(-1, "sw_groupnorm_nhwc: c=%d groups=%d unsupported", c, groups);
+    const int octs = c / 8;
+    if (octs > 1024) return swh::fail(-1, "sw_groupnorm_nhwc: c=%d too wide", c);
+    int rows_per_pass = 256 / octs;
+    if (rows_per_pass < 1) rows_per_pass = 1;
+    int threads = octs * rows_per_pass;
+    threads = (threads + 31) / 32 * 32;
+    // ~32 KB of activations per CTA
+    int rows_per_cta = (32768 / (c * 2)) / rows_per_pass * rows_per_pass;
+    if (rows_per_cta < rows_per_pass) rows_per_cta = rows_per_pass;
+    const int chunks = (hw + rows_per_cta - 1) / rows_per_cta;
+    SW_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * size_t(n) * groups * 2, st));
+    dim3 grid(chunks, n);
+    k_gn_stats<<<grid, threads, groups * 2 * sizeof(float), st>>>(
+        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, stats, hw, c, groups,
+        rows_per_cta, rows_per_pass);
+    SW_CUDA_OK(cudaGetLastError());
+    k_gn_apply<<<grid, threads, 2 * c * sizeof(float), st>>>(
+        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, static_cast<__half*>(y),
+        static_cast<const __half*>(gamma),
+        static_cast<const __half*>(beta), stats, hw, c, groups, eps, silu, rows_per_cta,
+        rows_per_pass);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma,
+                                 const void* beta, int n, int hw, int c1, int c2, int groups,
+                                 float eps, int silu, float* stats_scratch, void* stream) {
+    if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc: null argument");
+    return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu,
+                               stats_scratch, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows,
+                            int c, float eps, void* stream) {
+    if (!x || !y || !gamma || !beta) return swh::fail(-1, "sw_layernorm: null argument");
+    if (c % 8 || c > 2048) return swh::fail(-1, "sw_layernorm: c=%d unsupported", c);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int threads = 256;
+    const int blocks = (rows * 32 + threads - 1) / threads;
+    const int octs = c / 8;
+    const __half* xx = static_cast<const __half*>(x);
+    __half* yy = static_cast<__half*>(y);
+    const __half* g = static_cast<const __half*>(gamma);
+    const __half* b = static_cast<const __half*>(beta);
+    if (octs <= 64)
+        k_layernorm<2><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+    else if (octs <= 160)
+        k_layernorm<5><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+    else
+        k_layernorm<8><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,162 @@
+/* swarm_b200.h -- C ABI of libswarm_sm100.so (hand-written sm_100a kernels for the
+ * chiaswarm_b200 diffusion worker).
+ *
+ * Conventions
+ *  - every pointer is a device pointer unless its name ends in _host;
+ *  - activations are fp16, channels-last ("NHWC" == tokens [N*H*W, C]); accumulation is fp32;
+ *  - `stream` is a cudaStream_t passed as void*; all entry points are asynchronous on it;
+ *  - return value 0 == success; otherwise sw_last_error() describes the failure.
+ *
+ * The reference (Jsewill/chiaSWARM) has no native code at all: each entry point below names the
+ * library kernel family it replaces and the reference call
+ * site that triggers that family.
+ */
+#ifndef SWARM_B200_H_
+#define SWARM_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* sw_last_error(void);
+
+/* Epilogue activations for sw_igemm. */
+enum { SW_ACT_NONE = 0, SW_ACT_SILU = 1, SW_ACT_GELU = 2, SW_ACT_GEGLU = 3 };
+
+/* Implicit-GEMM convolution / linear layer on tcgen05 tensor cores (TMA-fed, TMEM accumulator).
+ * Replaces cuDNN conv2d (K4) and cuBLAS hgemm (K3) reached from the reference's
+ * `pipeline(**kwargs)` call (swarm/diffusion/diffusion_func.py:96).
+ *
+ *   out[n,y,x,:] = act( sum_{ky,kx,c} in[n, y+ky-pad, x+kx-pad, c] * wgt[:, (ky*kw+kx)*C + c]
+ *                       + bias + row_bias[n,:] ) * out_scale + residual[n,y,x,:]
+ *
+ * `in` is the channel-concatenation of a1 (c1 channels) and a2 (c2 channels, may be NULL): the
+ * UNet skip-concat is consumed as two K-slabs, never materialised.  A plain linear layer is the
+ * case n=h=1, w=M, kh=kw=1, pad=0.  Stride is always 1.
+ * With act == SW_ACT_GEGLU the weight rows must be pre-interleaved in blocks of 64 value rows
+ * followed by their 64 gate rows; `cout` counts weight rows and the output has cout/2 columns.
+ */
+typedef struct {
+    const void* a1;      /* fp16 [n,h,w,c1] */
+    const void* a2;      /* fp16 [n,h,w,c2] or NULL */
+    int32_t c1, c2;      /* channel counts, multiples of 8 */
+    int32_t n, h, w;
+    int32_t kh, kw, pad;
+    const void* wgt;     /* fp16 [cout, kh*kw*(c1+c2)], K contiguous */
+    int32_t cout;        /* multiple of 8 */
+    const void* bias;    /* fp16 [cout] or NULL */
+    const void* row_bias;/* fp16 [n, row_bias_ld] or NULL (per-image bias, e.g. time embedding) */
+    int32_t row_bias_ld;
+    const void* residual;/* fp16 [n*h*w, ldr] or NULL */
+    int32_t ldr;
+    void* out;           /* fp16 [n*h*w, ldc] */
+    int32_t ldc;
+    int32_t act;
+    float out_scale;     /* applied after the activation, before the residual add */
+    int32_t bf16;        /* 0: fp16 operands, 1: bf16 operands */
+    int32_t tile_n;      /* 0 = auto, else 64 or 128 */
+    float* gn_stats;     /* optional fp32 [n, gn_groups, 2]: += (sum, sumsq) of the stored output */
+    int32_t gn_groups;
+} sw_igemm_params;
+
+int sw_igemm(const sw_igemm_params* p, void* stream);
+
+/* Flash attention (non-causal, no mask) on tcgen05: S=QK^T and O+=PV accumulate in TMEM, online
+ * softmax in registers.  Replaces SDPA / xformers memory_efficient_attention (K1, K2), reference
+ * call sites swarm/diffusion/diffusion_func.py:86-87,96.
+ * q/k/v are fp16 with layout [batch, seq, heads, head_dim] expressed through element strides
+ * (head_dim contiguous); out is fp16 [batch, seq_q, heads*head_dim] with row stride ldo.
+ * head_dim must be a multiple of 8, at most 160.
+ */
+typedef struct {
+    const void* q; const void* k; const void* v;
+    int64_t q_stride_b, q_stride_s, q_stride_h; /* elements */
+    int64_t k_stride_b, k_stride_s, k_stride_h;
+    int64_t v_stride_b, v_stride_s, v_stride_h;
+    void* out; int64_t o_stride_b, o_stride_s;  /* elements; head h starts at column h*head_dim */
+    int32_t batch, heads, seq_q, seq_kv, head_dim;
+    float scale;                                 /* softmax scale, usually head_dim^-0.5 */
+} sw_attn_params;
+
+int sw_flash_attn(const sw_attn_params* p, void* stream);
+
+/* GroupNorm (+ optional SiLU) over channels-last fp16.  Replaces ATen GroupNorm + SiLU (K6, K8;
+ * reference call site swarm/diffusion/diffusion_func.py:96).
+ * The input is the channel-concatenation of x [n,hw,c1] and x2 [n,hw,c2] (x2 may be NULL with
+ * c2 = 0): the UNet skip-concat is normalised without being materialised.  y: [n,hw,c1+c2];
+ * gamma/beta fp16 [c1+c2].  A statistics kernel accumulates per-(image, group) sum and
+ * sum-of-squares into `stats_scratch` (fp32 [n, groups, 2], caller-owned, zeroed by the call
+ * itself), then an apply kernel normalises; both stream an L2-resident tensor once. */
+int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                      int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                      float* stats_scratch, void* stream);
+
+/* LayerNorm over the last dim of fp16 [rows, c] (K7). */
+int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows, int c,
+                 float eps, void* stream);
+
+/* Nearest-neighbour 2x upsample, channels-last fp16 (K8). */
+int sw_upsample2x_nhwc(const void* x, void* y, int n, int h, int w, int c, void* stream);
+
+/* im2col for strided / asymmetric-pad convolutions: out[n,oy,ox,(ky*kw+kx)*c + ch] (K4 helper). */
+int sw_im2col_nhwc(const void* x, void* out, int n, int h, int w, int c, int kh, int kw, int stride,
+                   int pad_top, int pad_left, int oh, int ow, void* stream);
+
+/* Layout converters between the public NCHW tensors and the internal channels-last fp16 ones.
+ * c_pad >= c: extra channels are written as zero (nchw->nhwc) / ignored (nhwc->nchw). */
+int sw_nchw_to_nhwc(const void* x, void* y, int n, int c, int h, int w, int c_pad, int src_fp32,
+                    void* stream);
+int sw_nhwc_to_nchw(const void* x, void* y, int n, int c, int h, int w, int c_pad, int dst_fp32,
+                    void* stream);
+
+/* Sinusoidal timestep embedding (flip_sin_to_cos=True, freq_shift=0): out fp16 [n, dim] (K8). */
+int sw_timestep_embedding(const float* t_table, const int32_t* step_idx, void* out, int n, int dim,
+                          float max_period, int flip_sin_to_cos, float freq_shift, void* stream);
+
+/* ++*counter on the device: lets one captured CUDA graph walk per-step tables on replay. */
+int sw_advance_counter(int32_t* counter, void* stream);
+
+/* y = a + b (fp16, n elements, multiple of 8) and friends (K8). */
+int sw_add(const void* a, const void* b, void* y, int64_t n, void* stream);
+int sw_silu(const void* x, void* y, int64_t n, void* stream);
+
+/* Fused classifier-free guidance + scheduler update (K9; replaces the diffusers scheduler.step
+ * python/elementwise chain reached from swarm/diffusion/diffusion_func.py:71-74,96).
+ * Every supported scheduler (DPM-Solver++ 2M, Euler, Euler-ancestral, DDIM) is linear in
+ * (x, x0, previous x0, noise), so the host precomputes per-step coefficients in fp64
+ * (ops/schedulers.py) and the kernel evaluates, per latent element,
+ *     eps    = CFG(eps_0 .. eps_{n_cond-1})
+ *     x0     = e0*x + e1*eps
+ *     x_new  = c0*x + c1*x0 + c2*x0_prev + c3*noise
+ *     x0_prev = x0;  x = x_new;  model_in[k] = fp16(x_new * s_in) for k < n_cond
+ * coef row = {e0, e1, c0, c1, c2, c3, s_in, 0}; row `*step_idx` of the table is used.
+ * n_cond == 2: eps = eps_0 + g_text*(eps_1 - eps_0)                 (order [uncond, cond])
+ * n_cond == 3: eps = eps_2 + g_text*(eps_0 - eps_1) + g_image*(eps_1 - eps_2)  (pix2pix order)
+ */
+typedef struct {
+    const void* eps;        /* fp16 [n_cond, rows, eps_ld] model output, channels-last */
+    int32_t n_cond;         /* 1, 2 or 3 */
+    int32_t rows;           /* batch*h*w latent pixels */
+    int32_t c;              /* latent channels (4) */
+    int32_t eps_ld;         /* padded channel stride of eps */
+    float g_text, g_image;
+    float* x;               /* fp32 [rows, c] latent, updated in place */
+    float* x0_prev;         /* fp32 [rows, c] multistep state, in/out */
+    const float* noise;     /* fp32 [steps, rows, c] ancestral noise table or NULL */
+    void* x_model_in;       /* fp16 [n_cond, rows, xin_ld]: columns [0,c) are rewritten */
+    int32_t xin_ld;
+    const float* coef;      /* fp32 [steps, 8] */
+    const int32_t* step_idx;/* device step counter (NULL = row 0) */
+} sw_sched_params;
+
+int sw_sched_step(const sw_sched_params* p, void* stream);
+
+/* VAE output head: clamp(x/2+0.5,0,1)*255 -> uint8 HWC, from channels-last fp16 (K10). */
+int sw_image_to_u8(const void* x_nhwc, uint8_t* out, int64_t pixels, int c_pad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWARM_B200_H_ */

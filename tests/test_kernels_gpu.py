@@ -1,0 +1,237 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 restatement of the same op
+(exact UNet shapes plus odd ones -- head_dim 40, S=45, partial tiles)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from chiaswarm_b200.ops import native
+
+    native.lib()
+    return native
+
+
+def _rel_err(got, ref):
+    ref = ref.float()
+    got = got.float()
+    return ((got - ref).abs().max() / ref.abs().max().clamp_min(1e-6)).item()
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (256, 128, 320), (4096, 320, 320), (8192, 1280, 320),
+                                   (154, 640, 768), (77, 320, 1024), (2, 1280, 320), (1000, 2560, 640)])
+def test_linear(nat, m, n, k):
+    torch.manual_seed(0)
+    x = torch.randn(m, k, device="cuda", dtype=torch.float16)
+    w = torch.randn(n, k, device="cuda", dtype=torch.float16) * (k ** -0.5)
+    b = torch.randn(n, device="cuda", dtype=torch.float16)
+    out = nat.linear(x, w, bias=b)
+    ref = x.float() @ w.float().t() + b.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("tile_n", [64, 128])
+def test_linear_tiles_and_epilogues(nat, tile_n):
+    torch.manual_seed(1)
+    m, n, k = 512, 640, 1280
+    x = torch.randn(m, k, device="cuda", dtype=torch.float16)
+    w = torch.randn(n, k, device="cuda", dtype=torch.float16) * (k ** -0.5)
+    b = torch.randn(n, device="cuda", dtype=torch.float16)
+    res = torch.randn(m, n, device="cuda", dtype=torch.float16)
+    out = nat.linear(x, w, bias=b, residual=res, act=nat.ACT_SILU, out_scale=0.5, tile_n=tile_n)
+    ref = F.silu(x.float() @ w.float().t() + b.float()) * 0.5 + res.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+def test_linear_geglu(nat):
+    from chiaswarm_b200.ops.packing import interleave_geglu
+
+    torch.manual_seed(2)
+    m, d = 300, 320
+    x = torch.randn(m, d, device="cuda", dtype=torch.float16)
+    w = torch.randn(8 * d, d, device="cuda", dtype=torch.float16) * (d ** -0.5)
+    b = torch.randn(8 * d, device="cuda", dtype=torch.float16)
+    wi, bi = interleave_geglu(w, b)
+    out = nat.linear(x, wi, bias=bi, act=nat.ACT_GEGLU)
+    h = x.float() @ w.float().t() + b.float()
+    val, gate = h.chunk(2, dim=-1)
+    ref = val * F.gelu(gate)
+    assert out.shape == (m, 4 * d)
+    assert _rel_err(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout", [(2, 64, 64, 320, 320), (2, 32, 32, 640, 640), (2, 16, 16, 1280, 1280),
+                                            (2, 8, 8, 1280, 1280), (1, 8, 8, 64, 64), (2, 64, 64, 8, 320),
+                                            (2, 64, 64, 320, 8), (1, 96, 96, 64, 128), (3, 40, 72, 64, 64),
+                                            (1, 5, 9, 32, 32)])
+def test_conv3x3(nat, n, h, w, cin, cout):
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    torch.manual_seed(3)
+    x = torch.randn(n, cin, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=torch.float16) * ((9 * cin) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    x_nhwc = x.permute(0, 2, 3, 1).contiguous()
+    out = torch.empty(n, h, w, cout, device="cuda", dtype=torch.float16)
+    nat.igemm(x_nhwc, pack_conv_weight(wt), out, n=n, h=h, w=w, kh=3, kw=3, pad=1, bias=b)
+    ref = F.conv2d(x.float(), wt.float(), b.float(), padding=1).permute(0, 2, 3, 1)
+    assert _rel_err(out, ref) < 4e-3
+
+
+def test_conv_dual_input_rowbias_residual(nat):
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    torch.manual_seed(4)
+    n, h, w, c1, c2, cout = 2, 32, 32, 640, 320, 640
+    x1 = torch.randn(n, c1, h, w, device="cuda", dtype=torch.float16)
+    x2 = torch.randn(n, c2, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, c1 + c2, 3, 3, device="cuda", dtype=torch.float16) * ((9 * (c1 + c2)) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    rb = torch.randn(n, cout, device="cuda", dtype=torch.float16)
+    res = torch.randn(n, h, w, cout, device="cuda", dtype=torch.float16)
+    out = torch.empty(n, h, w, cout, device="cuda", dtype=torch.float16)
+    nat.igemm(x1.permute(0, 2, 3, 1).contiguous(), pack_conv_weight(wt), out, n=n, h=h, w=w, kh=3, kw=3, pad=1,
+              a2=x2.permute(0, 2, 3, 1).contiguous(), bias=b, row_bias=rb, residual=res)
+    ref = F.conv2d(torch.cat([x1, x2], 1).float(), wt.float(), b.float(), padding=1)
+    ref = ref + rb.float()[:, :, None, None]
+    ref = ref.permute(0, 2, 3, 1) + res.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("b,heads,sq,skv,d", [(2, 8, 4096, 4096, 40), (2, 8, 1024, 1024, 80), (2, 8, 256, 256, 160),
+                                              (2, 8, 64, 64, 160), (2, 8, 4096, 77, 40), (2, 8, 256, 77, 160),
+                                              (1, 10, 1024, 1024, 64), (3, 5, 45, 45, 64), (2, 4, 300, 200, 64),
+                                              (1, 2, 130, 513, 40)])
+def test_flash_attn(nat, b, heads, sq, skv, d):
+    torch.manual_seed(5)
+    q = torch.randn(b, sq, heads, d, device="cuda", dtype=torch.float16)
+    k = torch.randn(b, skv, heads, d, device="cuda", dtype=torch.float16)
+    v = torch.randn(b, skv, heads, d, device="cuda", dtype=torch.float16)
+    out = torch.empty(b, sq, heads * d, device="cuda", dtype=torch.float16)
+    nat.flash_attn(q, k, v, out, batch=b, heads=heads, seq_q=sq, seq_kv=skv, head_dim=d)
+    qf, kf, vf = (t.float().permute(0, 2, 1, 3) for t in (q, k, v))
+    s = (qf @ kf.transpose(-1, -2)) * (d ** -0.5)
+    ref = (s.softmax(-1) @ vf).permute(0, 2, 1, 3).reshape(b, sq, heads * d)
+    assert _rel_err(out, ref) < 6e-3
+
+
+def test_flash_attn_fused_qkv_layout(nat):
+    """q/k/v as strided views of one [b*s, 3*h*d] projection output (how the UNet calls it)."""
+    torch.manual_seed(6)
+    b, s, heads, d = 2, 1024, 8, 80
+    qkv = torch.randn(b, s, 3, heads, d, device="cuda", dtype=torch.float16)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    out = torch.empty(b, s, heads * d, device="cuda", dtype=torch.float16)
+    nat.flash_attn(q, k, v, out, batch=b, heads=heads, seq_q=s, seq_kv=s, head_dim=d)
+    ref = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2),
+                                         v.float().transpose(1, 2)).transpose(1, 2).reshape(b, s, heads * d)
+    assert _rel_err(out, ref) < 6e-3
+
+
+def test_flash_attn_large_score_range(nat):
+    """Forces the lazy O-rescale path: the row max keeps growing across KV tiles."""
+    torch.manual_seed(7)
+    b, heads, s, d = 1, 2, 1024, 64
+    q = torch.randn(b, s, heads, d, device="cuda", dtype=torch.float16)
+    k = torch.randn(b, s, heads, d, device="cuda", dtype=torch.float16)
+    k = k * torch.linspace(0.2, 6.0, s, device="cuda", dtype=torch.float16)[None, :, None, None]
+    v = torch.randn(b, s, heads, d, device="cuda", dtype=torch.float16)
+    out = torch.empty(b, s, heads * d, device="cuda", dtype=torch.float16)
+    nat.flash_attn(q, k, v, out, batch=b, heads=heads, seq_q=s, seq_kv=s, head_dim=d)
+    ref = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2),
+                                         v.float().transpose(1, 2)).transpose(1, 2).reshape(b, s, heads * d)
+    assert _rel_err(out, ref) < 8e-3
+
+
+@pytest.mark.parametrize("n,hw,c1,c2,groups,silu", [(2, 4096, 320, 0, 32, True), (2, 1024, 1280, 640, 32, True),
+                                                    (2, 64, 1280, 1280, 32, False), (1, 45, 32, 0, 32, True),
+                                                    (2, 16384, 128, 0, 32, True), (3, 100, 64, 32, 8, False)])
+def test_groupnorm(nat, n, hw, c1, c2, groups, silu):
+    torch.manual_seed(8)
+    c = c1 + c2
+    x1 = torch.randn(n, hw, c1, device="cuda", dtype=torch.float16) * 2 + 0.5
+    x2 = torch.randn(n, hw, c2, device="cuda", dtype=torch.float16) if c2 else None
+    g = torch.randn(c, device="cuda", dtype=torch.float16)
+    b = torch.randn(c, device="cuda", dtype=torch.float16)
+    out = torch.empty(n, hw, c, device="cuda", dtype=torch.float16)
+    stats = torch.empty(n, groups, 2, device="cuda", dtype=torch.float32)
+    nat.groupnorm(x1, g, b, out, n=n, hw=hw, groups=groups, eps=1e-5, silu=silu, stats=stats, x2=x2)
+    xc = x1 if x2 is None else torch.cat([x1, x2], -1)
+    ref = F.group_norm(xc.float().permute(0, 2, 1), groups, g.float(), b.float(), 1e-5)
+    if silu:
+        ref = F.silu(ref)
+    ref = ref.permute(0, 2, 1)
+    assert (out.float() - ref).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("rows,c", [(8192, 320), (2048, 640), (512, 1280), (77, 768), (3, 2048)])
+def test_layernorm(nat, rows, c):
+    torch.manual_seed(9)
+    x = torch.randn(rows, c, device="cuda", dtype=torch.float16) * 3 + 1
+    g = torch.randn(c, device="cuda", dtype=torch.float16)
+    b = torch.randn(c, device="cuda", dtype=torch.float16)
+    out = torch.empty_like(x)
+    nat.layernorm(x, g, b, out, 1e-5)
+    ref = F.layer_norm(x.float(), (c,), g.float(), b.float(), 1e-5)
+    assert (out.float() - ref).abs().max().item() < 2e-2
+
+
+def test_upsample_im2col_layout(nat):
+    torch.manual_seed(10)
+    n, c, h, w = 2, 64, 12, 20
+    x = torch.randn(n, c, h, w, device="cuda", dtype=torch.float32)
+    nhwc = torch.empty(n, h, w, c, device="cuda", dtype=torch.float16)
+    nat.nchw_to_nhwc(x, nhwc, c)
+    assert torch.equal(nhwc, x.half().permute(0, 2, 3, 1))
+    up = torch.empty(n, 2 * h, 2 * w, c, device="cuda", dtype=torch.float16)
+    nat.upsample2x(nhwc, up, n=n, h=h, w=w)
+    ref_up = F.interpolate(x.half(), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1)
+    assert torch.equal(up, ref_up)
+    back = torch.empty(n, c, h, w, device="cuda", dtype=torch.float32)
+    nat.nhwc_to_nchw(nhwc, back, c)
+    assert torch.equal(back, x.half().float())
+    # stride-2 3x3 conv through im2col + GEMM
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    wt = torch.randn(32, c, 3, 3, device="cuda", dtype=torch.float16) * 0.05
+    oh, ow = h // 2, w // 2
+    cols = torch.empty(n, oh, ow, 9 * c, device="cuda", dtype=torch.float16)
+    nat.im2col(nhwc, cols, n=n, h=h, w=w, kh=3, kw=3, stride=2, pad_top=1, pad_left=1, oh=oh, ow=ow)
+    out = nat.linear(cols.view(-1, 9 * c), pack_conv_weight(wt))
+    ref = F.conv2d(x.half().float(), wt.float(), stride=2, padding=1).permute(0, 2, 3, 1).reshape(-1, 32)
+    assert _rel_err(out, ref) < 4e-3
+
+
+def test_timestep_embedding_and_sched(nat):
+    t = torch.tensor([999.0, 500.0], device="cuda")
+    step = torch.tensor([1], device="cuda", dtype=torch.int32)
+    out = torch.empty(2, 320, device="cuda", dtype=torch.float16)
+    nat.timestep_embedding(t, step, out, n=2, dim=320)
+    half = 160
+    freqs = torch.exp(-math.log(10000.0) * torch.arange(half, device="cuda").float() / half)
+    a = 500.0 * freqs
+    ref = torch.cat([a.cos(), a.sin()])
+    assert (out[0].float() - ref).abs().max().item() < 2e-3
+    assert torch.equal(out[0], out[1])
+
+    rows, c = 4096, 4
+    eps = torch.randn(2, rows, 8, device="cuda", dtype=torch.float16)
+    x = torch.randn(rows, c, device="cuda")
+    x0p = torch.randn(rows, c, device="cuda")
+    xin = torch.zeros(2, rows, 8, device="cuda", dtype=torch.float16)
+    coef = torch.tensor([[0.0] * 8, [1.1, -0.4, 0.9, 0.3, -0.05, 0.0, 0.7, 0.0]], device="cuda")
+    x_ref, x0p_ref = x.clone(), x0p.clone()
+    nat.sched_step(eps=eps, n_cond=2, rows=rows, c=c, eps_ld=8, g_text=7.5, g_image=0.0, x=x, x0_prev=x0p,
+                   noise=None, x_model_in=xin, xin_ld=8, coef=coef, step_idx=step)
+    e = eps[0, :, :4].float() + 7.5 * (eps[1, :, :4].float() - eps[0, :, :4].float())
+    x0 = 1.1 * x_ref - 0.4 * e
+    xn = 0.9 * x_ref + 0.3 * x0 - 0.05 * x0p_ref
+    assert (x - xn).abs().max().item() < 1e-4
+    assert (x0p - x0).abs().max().item() < 1e-4
+    assert (xin[1, :, :4].float() - xn * 0.7).abs().max().item() < 5e-3
+    assert xin[:, :, 4:].abs().max().item() == 0
