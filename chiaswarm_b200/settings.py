@@ -1,0 +1,96 @@
+"""Worker settings (reference: swarm/settings.py:7-73).
+
+Same file location (`$SDAAS_ROOT` or `~/.sdaas`/settings.json), same keys, same environment
+overrides (SDAAS_TOKEN / SDAAS_URI / SDAAS_WORKERNAME). New knobs for the B200 runtime are extra
+keys with safe defaults."""
+from __future__ import annotations
+
+import json
+import os
+from pathlib import Path
+from typing import Union
+
+_DEFAULTS = {
+    "log_level": "WARN",
+    "log_filename": "log/generator.log",
+    "sdaas_token": "",
+    "sdaas_uri": "http://localhost:9511",
+    "worker_name": "worker",
+    # --- B200 runtime knobs (not in the reference)
+    "parallel_mode": "dp",       # dp | patch | tp
+    "gang_size": 1,              # GPUs leased per job in patch/tp mode (1, 2, 4, 8)
+    "kernel_backend": "sm100",   # sm100 | torch (oracle / baseline path)
+    "model_root": "",            # directory holding diffusers-layout checkpoints (HF cache also searched)
+    "weight_cache_gb": 120,      # resident weight cache budget per GPU
+    "result_retries": 3,         # bounded retry for POST /api/results (reference drops on failure)
+}
+
+_ENV = {"sdaas_token": "SDAAS_TOKEN", "sdaas_uri": "SDAAS_URI", "worker_name": "SDAAS_WORKERNAME",
+        "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE",
+        "kernel_backend": "SDAAS_KERNEL_BACKEND", "model_root": "SDAAS_MODEL_ROOT"}
+
+
+class Settings:
+    huggingface_token: Union[bool, str] = True
+    log_level: str = _DEFAULTS["log_level"]
+    log_filename: str = _DEFAULTS["log_filename"]
+    sdaas_token: str = _DEFAULTS["sdaas_token"]
+    sdaas_uri: str = _DEFAULTS["sdaas_uri"]
+    worker_name: str = _DEFAULTS["worker_name"]
+    parallel_mode: str = _DEFAULTS["parallel_mode"]
+    gang_size: int = _DEFAULTS["gang_size"]
+    kernel_backend: str = _DEFAULTS["kernel_backend"]
+    model_root: str = _DEFAULTS["model_root"]
+    weight_cache_gb: int = _DEFAULTS["weight_cache_gb"]
+    result_retries: int = _DEFAULTS["result_retries"]
+
+
+def get_settings_dir() -> Path:
+    return Path(os.environ.get("SDAAS_ROOT") or "~/.sdaas/").expanduser()
+
+
+def resolve_path(path) -> Path:
+    """Path under the settings dir; creates the parent directory (reference behaviour)."""
+    full = get_settings_dir().joinpath(path)
+    full.parent.mkdir(parents=True, exist_ok=True)
+    return full
+
+
+def get_settings_full_path() -> Path:
+    return resolve_path("settings.json")
+
+
+def settings_exist() -> bool:
+    return get_settings_dir().joinpath("settings.json").is_file()
+
+
+def load_settings() -> Settings:
+    settings = Settings()
+    stored = {}
+    try:
+        with open(get_settings_full_path(), "r") as fh:
+            stored = json.load(fh)
+            if not isinstance(stored, dict):
+                raise json.JSONDecodeError("settings must be an object", "", 0)
+    except FileNotFoundError:
+        print("no settings file")
+    except json.JSONDecodeError:
+        print("invalid settings file")
+        stored = {}
+    for key, default in _DEFAULTS.items():
+        value = stored.get(key, default)
+        env = _ENV.get(key)
+        if env and os.getenv(env) is not None:
+            value = type(default)(os.getenv(env))
+        setattr(settings, key, value)
+    return settings
+
+
+def save_settings(settings: Settings) -> None:
+    with open(get_settings_full_path(), "w") as fh:
+        json.dump(dict(settings.__dict__), fh, indent=2)
+
+
+def save_file(data, filename) -> None:
+    with open(resolve_path(filename), "w") as fh:
+        json.dump(data, fh, indent=2)

@@ -1,0 +1,256 @@
+"""Hive client and scheduler (reference: swarm/worker.py:34-195).
+
+Same protocol and cadence: `GET {hive}/api/work` (10 s timeout; next poll after 1 s if jobs were
+returned, 11 s if idle, 121 s after an error; 400 means the hive considers this worker
+misbehaving), `POST {hive}/api/results` (60 s timeout), bearer token, `chiaSWARM.worker/<ver>`
+user agent.  Same back-pressure: a queue and a semaphore both sized to the number of execution
+lanes, and the poll itself holds a lane while it is in flight (Q11).
+
+What differs from the reference:
+  * settings are read when the worker starts, not at import;
+  * lanes are `Device` objects leased from the rank group, plus one CPU lane for pure-CPU
+    workflows (stitch) so they do not occupy a GPU (Q10);
+  * results that fail to POST are retried a bounded number of times instead of dropped (Q14);
+  * `Worker` is an object (testable against a fake hive) -- the module-level functions
+    `run_worker/startup/ask_for_work/device_worker/result_worker/submit_result` remain.
+"""
+from __future__ import annotations
+
+import asyncio
+import json
+import logging
+from datetime import datetime
+from typing import List, Optional
+
+import aiohttp
+
+from . import __version__
+from .generator import do_work
+from .gpu.device import Device
+from .log_setup import setup_logging
+from .settings import Settings, load_settings, resolve_path
+
+POLL_FOUND_S = 1
+POLL_IDLE_S = 11
+POLL_ERROR_S = 121
+WORK_TIMEOUT_S = 10
+RESULT_TIMEOUT_S = 60
+CPU_WORKFLOWS = ("stitch",)
+
+
+class Worker:
+    def __init__(self, settings: Optional[Settings] = None, devices: Optional[List[Device]] = None,
+                 cpu_lane: bool = True):
+        self.settings = settings or load_settings()
+        self.hive_uri = f"{self.settings.sdaas_uri.rstrip('/')}/api"
+        self.devices = devices
+        self.cpu_lane = cpu_lane
+        self.work_queue: asyncio.Queue
+        self.cpu_queue: asyncio.Queue
+        self.available_gpus: asyncio.Semaphore
+        self.result_queue: asyncio.Queue = asyncio.Queue()
+        self._tasks: list = []
+        self.polls = 0
+
+    # ------------------------------------------------------------------ lifecycle
+    def _headers(self):
+        return {
+            "Content-type": "application/json",
+            "Authorization": f"Bearer {self.settings.sdaas_token}",
+            "user-agent": f"chiaSWARM.worker/{__version__}",
+        }
+
+    async def startup(self):
+        import torch
+
+        if self.devices is None:
+            if not torch.cuda.is_available():
+                raise Exception("CUDA not present. Quitting.")
+            self.devices = [Device(i) for i in range(torch.cuda.device_count())]
+        from packaging import version
+
+        if version.parse(torch.__version__.split("+")[0]) < version.parse("2.0.0"):
+            raise Exception(f"Pytorch must be 2.0 or greater (found {torch.__version__}). Quitting.")
+        setup_logging(resolve_path(self.settings.log_filename), self.settings.log_level)
+        logging.info(f"Version {__version__}")
+        logging.debug(f"Torch version {torch.__version__}")
+        torch.set_float32_matmul_precision("high")
+        torch.backends.cudnn.benchmark = True
+        torch.backends.cuda.matmul.allow_tf32 = True
+
+        lanes = max(1, len(self.devices))
+        print(f"Found {len(self.devices)} GPUs")
+        self.work_queue = asyncio.Queue(maxsize=lanes)
+        self.cpu_queue = asyncio.Queue()
+        self.available_gpus = asyncio.Semaphore(lanes)
+
+    async def run(self, max_polls: Optional[int] = None, sleep=asyncio.sleep):
+        """The serve loop. `max_polls` bounds it for tests."""
+        await self.startup()
+        logging.info("worker")
+        for device in self.devices:
+            self._tasks.append(asyncio.create_task(self.device_worker(device)))
+            print(f"Started device {device.descriptor()}")
+        if self.cpu_lane:
+            self._tasks.append(asyncio.create_task(self.cpu_worker()))
+        self._tasks.append(asyncio.create_task(self.result_worker()))
+        try:
+            while max_polls is None or self.polls < max_polls:
+                while self.work_queue.full():
+                    await sleep(1)
+                delay = await self.ask_for_work()
+                await sleep(delay)
+        finally:
+            if max_polls is not None:
+                await self.drain()
+
+    async def drain(self):
+        await self.work_queue.join()
+        await self.cpu_queue.join()
+        await self.result_queue.join()
+        for t in self._tasks:
+            t.cancel()
+        await asyncio.gather(*self._tasks, return_exceptions=True)
+        self._tasks.clear()
+
+    # ------------------------------------------------------------------ hive I/O
+    async def ask_for_work(self) -> int:
+        await self.available_gpus.acquire()  # no polling while every lane is busy
+        self.polls += 1
+        print(f"{datetime.now()}: Asking for work from the hive at {self.hive_uri}...")
+        try:
+            timeout = aiohttp.ClientTimeout(total=WORK_TIMEOUT_S)
+            async with aiohttp.ClientSession(timeout=timeout) as session:
+                async with session.get(
+                    f"{self.hive_uri}/work",
+                    params={"worker_version": __version__, "worker_name": self.settings.worker_name},
+                    headers=self._headers(),
+                ) as response:
+                    if response.status == 200:
+                        body = await response.json()
+                        found = False
+                        for job in body["jobs"]:
+                            print(f"Got job {job['id']}")
+                            found = True
+                            if self.cpu_lane and job.get("workflow") in CPU_WORKFLOWS:
+                                await self.cpu_queue.put(job)
+                            else:
+                                await self.work_queue.put(job)
+                        return POLL_FOUND_S if found else POLL_IDLE_S
+                    if response.status == 400:
+                        body = await response.json()
+                        print(f"{self.hive_uri} says {body.pop('message', 'bad worker')}")
+                    else:
+                        print(f"{self.hive_uri} returned {response.status}")
+                    response.raise_for_status()
+        except Exception as e:
+            logging.exception(e)
+            print(e)
+            return POLL_ERROR_S
+        finally:
+            self.available_gpus.release()
+        return POLL_IDLE_S
+
+    async def submit_result(self, result) -> bool:
+        print("Result complete")
+        timeout = aiohttp.ClientTimeout(total=RESULT_TIMEOUT_S)
+        async with aiohttp.ClientSession(timeout=timeout) as session:
+            async with session.post(f"{self.hive_uri}/results", data=json.dumps(result),
+                                    headers=self._headers()) as response:
+                if response.status == 500:
+                    print(f"The hive returned an error: {response.reason}")
+                    return False
+                print(f"Result {await response.json()}")
+                return True
+
+    # ------------------------------------------------------------------ lanes
+    async def device_worker(self, device: Device):
+        while True:
+            job = await self.work_queue.get()
+            acquired = False
+            try:
+                await self.available_gpus.acquire()
+                acquired = True
+                result = await do_work(job, device)
+                await self.result_queue.put(result)
+            except asyncio.CancelledError:
+                raise
+            except Exception as e:
+                logging.exception(e)
+                print(f"device_worker {e}")
+            finally:
+                if acquired:
+                    self.available_gpus.release()
+                self.work_queue.task_done()
+
+    async def cpu_worker(self):
+        cpu = Device("cpu")
+        while True:
+            job = await self.cpu_queue.get()
+            try:
+                await self.result_queue.put(await do_work(job, cpu))
+            except asyncio.CancelledError:
+                raise
+            except Exception as e:
+                logging.exception(e)
+                print(f"cpu_worker {e}")
+            finally:
+                self.cpu_queue.task_done()
+
+    async def result_worker(self, backoff=asyncio.sleep):
+        while True:
+            result = await self.result_queue.get()
+            try:
+                attempts = max(1, int(getattr(self.settings, "result_retries", 1)))
+                for attempt in range(attempts):
+                    try:
+                        if await self.submit_result(result):
+                            break
+                    except asyncio.CancelledError:
+                        raise
+                    except Exception as e:
+                        logging.exception(e)
+                        print(f"result_worker {e}")
+                    if attempt + 1 < attempts:
+                        await backoff(min(2 ** attempt, 30))
+            finally:
+                self.result_queue.task_done()
+
+
+# ---------------------------------------------------------------- module-level surface
+_worker: Optional[Worker] = None
+
+
+def _get() -> Worker:
+    global _worker
+    if _worker is None:
+        _worker = Worker()
+    return _worker
+
+
+async def startup():
+    await _get().startup()
+
+
+async def ask_for_work():
+    return await _get().ask_for_work()
+
+
+async def device_worker(device: Device):
+    await _get().device_worker(device)
+
+
+async def result_worker():
+    await _get().result_worker()
+
+
+async def submit_result(result):
+    return await _get().submit_result(result)
+
+
+async def run_worker():
+    await _get().run()
+
+
+if __name__ == "__main__":
+    asyncio.run(run_worker())

@@ -162,7 +162,10 @@ __global__ void __launch_bounds__(kThreads)
                 }
                 mbar_wait(p_full, uint32_t(j & 1));  // softmax j has drained S and published P
                 tc_fence_after();
-                if (j + 1 < nkv) {
+                // With two K/V stages the next S tile is issued ahead of P.V so the softmax warps
+                // can start on it while P.V runs; with one stage K[j+1] only lands after P.V[j]
+                // released the buffer, so the order is reversed (head_dim 160: <= 2 KV tiles).
+                if (stages > 1 && j + 1 < nkv) {
                     mbar_wait(&k_full[s1], ph1);
                     tc_fence_after();
                     issue_qk(s1);
@@ -184,6 +187,12 @@ __global__ void __launch_bounds__(kThreads)
                 }
                 umma_commit(&kv_empty[s]);
                 umma_commit(pv_done);
+                if (stages == 1 && j + 1 < nkv) {
+                    mbar_wait(&k_full[s1], ph1);
+                    tc_fence_after();
+                    issue_qk(s1);
+                    umma_commit(s_full);
+                }
                 s = s1;
                 ph = ph1;
             }
@@ -341,7 +350,7 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
     a.nslab = (p->head_dim + 63) / 64;
     a.dpad = (p->head_dim + 15) / 16 * 16;
     const int nkv = (p->seq_kv + BKV - 1) / BKV;
-    a.kv_stages = (a.nslab == 1 && nkv > 1) ? 2 : 1;
+    a.kv_stages = (a.nslab <= 2 && nkv > 1) ? 2 : 1;
     a.tmem_cols = (O_COL0 + a.dpad <= 256) ? 256 : 512;
     a.scale_log2 = p->scale * 1.4426950408889634f;
     a.out = static_cast<__half*>(p->out);
