@@ -1,0 +1,391 @@
+"""Pipeline drivers: txt2img, img2img, inpaint, ControlNet, instruct-pix2pix (SURVEY.md appendix
+A.5-A.6).  The reference obtains these from diffusers (`pipeline_type.from_pretrained(...)` then
+`pipeline(**kwargs)`, swarm/diffusion/diffusion_func.py:41-46,96); here they are this framework's
+own drivers over its own models.
+
+One driver class serves the whole Stable-Diffusion family; the *mode* follows from the registry
+family of the requested pipeline type plus which inputs are present.  Two execution back ends:
+
+  * "torch"  -- eager PyTorch modules (CPU capable; oracle and the measured baseline);
+  * "sm100"  -- `engine.SM100Denoiser`: packed weights, hand-written sm_100a kernels, the whole
+                denoising step (UNet [+ControlNet] + CFG + scheduler update) captured in one CUDA
+                graph and replayed per step.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, field
+from pathlib import Path
+from typing import List, Optional
+
+import numpy as np
+import torch
+from PIL import Image
+
+from ..models import configs as arch_configs
+from ..models.clip_text import CLIPTextModel
+from ..models.controlnet import ControlNetModel
+from ..models.unet2d import UNet2DConditionModel
+from ..models.vae import AutoencoderKL
+from ..ops import schedulers
+from ..utils import checkpoints
+from ..utils.tokenizer import load_tokenizer
+
+
+@dataclass
+class PipelineOutput:
+    images: List[Image.Image]
+    nsfw_content_detected: Optional[List[bool]] = None
+    latents: Optional[torch.Tensor] = None
+    timings: dict = field(default_factory=dict)
+
+
+def default_backend(device) -> str:
+    env = os.environ.get("SDAAS_KERNEL_BACKEND")
+    if env:
+        return env
+    return "sm100" if str(device).startswith("cuda") else "torch"
+
+
+def _random_init_allowed() -> bool:
+    return os.environ.get("SDAAS_RANDOM_INIT", "0") not in ("0", "", "false")
+
+
+def _init_module(module: torch.nn.Module, seed: int):
+    """Deterministic random init with sane activation scales (timing runs use random weights)."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in module.named_parameters():
+            if p.dim() >= 2:
+                fan_in = p[0].numel()
+                p.copy_(torch.randn(p.shape, generator=g) * (0.7 / max(fan_in, 1) ** 0.5))
+            elif name.endswith("weight"):
+                p.fill_(1.0)
+            else:
+                p.zero_()
+    return module
+
+
+def pil_to_tensor(image: Image.Image, device, dtype, signed=True) -> torch.Tensor:
+    arr = np.asarray(image.convert("RGB"), dtype=np.float32) / 255.0
+    t = torch.from_numpy(arr).permute(2, 0, 1)[None]
+    if signed:
+        t = t * 2.0 - 1.0
+    return t.to(device=device, dtype=dtype)
+
+
+def tensor_to_pil(images: torch.Tensor) -> List[Image.Image]:
+    """[-1,1] NCHW -> PIL (clamp(x/2+0.5,0,1), round to uint8)."""
+    arr = (images.float() / 2 + 0.5).clamp(0, 1).permute(0, 2, 3, 1).cpu().numpy()
+    arr = (arr * 255).round().astype("uint8")
+    return [Image.fromarray(a) for a in arr]
+
+
+def _fit_multiple(image: Image.Image, multiple=8) -> Image.Image:
+    w, h = image.size
+    w2, h2 = max(multiple, w - w % multiple), max(multiple, h - h % multiple)
+    return image if (w2, h2) == (w, h) else image.resize((w2, h2), Image.Resampling.LANCZOS)
+
+
+class StableDiffusionPipeline:
+    """SD 1.x / 2.x / XL family driver."""
+
+    def __init__(self, unet, vae, text_encoder, tokenizer, scheduler_config, config=None, text_encoder_2=None,
+                 tokenizer_2=None, controlnet=None, family="sd", device="cpu", dtype=torch.float32, backend=None):
+        self.unet, self.vae, self.text_encoder, self.tokenizer = unet, vae, text_encoder, tokenizer
+        self.text_encoder_2, self.tokenizer_2 = text_encoder_2, tokenizer_2
+        self.controlnet = controlnet
+        self.scheduler_config = dict(scheduler_config)
+        self.scheduler_kind = "dpmpp_2m"
+        self.use_karras_sigmas = False
+        self.config = dict(config or {})
+        self.family = family
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self.backend = backend or default_backend(device)
+        self._engine = None
+        self.safety_checker = None
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_pretrained(cls, model_name, revision="main", variant=None, torch_dtype=torch.float16, controlnet=None,
+                        device="cpu", family=None, random_init=None, model_root="", backend=None, seed=0):
+        root = checkpoints.locate_checkpoint(model_name, revision, variant, model_root)
+        if root is not None and (root / "model_index.json").is_file():
+            pipe = cls._load(root, variant, family, controlnet)
+        else:
+            key = arch_configs.architecture_for(model_name)
+            if random_init is None:
+                random_init = _random_init_allowed()
+            if key is None or not random_init:
+                raise ValueError(
+                    f"Model {model_name} is not available locally"
+                    + ("" if key is None else " (set SDAAS_RANDOM_INIT=1 to run its architecture with random weights)"))
+            pipe = cls.from_architecture(key, controlnet=controlnet, family=family, seed=seed)
+            pipe.config["_name_or_path"] = model_name
+        pipe.backend = backend or default_backend(device)
+        return pipe.to(device, torch_dtype)
+
+    @classmethod
+    def from_architecture(cls, key, controlnet=None, family=None, seed=0):
+        """Random-init pipeline of a built-in architecture (BASELINE configs; no network here)."""
+        a = arch_configs.get_architecture(key)
+        unet = _init_module(UNet2DConditionModel(**a["unet"]), seed + 1)
+        vae = _init_module(AutoencoderKL(**a["vae"]), seed + 2)
+        te = _init_module(CLIPTextModel(**a["text_encoder"]), seed + 3)
+        te2 = _init_module(CLIPTextModel(**a["text_encoder_2"]), seed + 4) if "text_encoder_2" in a else None
+        tok = load_tokenizer(None, a["text_encoder"]["vocab_size"])
+        tok2 = load_tokenizer(None, a["text_encoder_2"]["vocab_size"]) if te2 is not None else None
+        config = {"_class_name": a["_class_name"], "_random_init": True,
+                  "unet": ["chiaswarm_b200", "UNet2DConditionModel"], "vae": ["chiaswarm_b200", "AutoencoderKL"],
+                  "text_encoder": ["chiaswarm_b200", "CLIPTextModel"], "scheduler": ["chiaswarm_b200", "StepPlan"]}
+        fam = family or _family_of_class(a["_class_name"])
+        return cls(unet, vae, te, tok, a["scheduler"], config, te2, tok2, controlnet, fam)
+
+    @classmethod
+    def _load(cls, root: Path, variant, family, controlnet):
+        index = checkpoints.read_json(root / "model_index.json")
+
+        def module(component, ctor, remap=None):
+            cfg = checkpoints.component_config(root, component)
+            if cfg is None:
+                return None
+            m = ctor(**{k: v for k, v in cfg.items() if not k.startswith("_")})
+            w = checkpoints.find_weights(root / component, variant)
+            if w is None:
+                raise ValueError(f"no weights for {component} under {root}")
+            sd = checkpoints.load_state_dict(w)
+            checkpoints.load_into(m, remap(sd) if remap else sd, strict=False)
+            return m
+
+        unet = module("unet", UNet2DConditionModel)
+        vae = module("vae", AutoencoderKL, checkpoints.remap_vae_keys)
+        te = module("text_encoder", CLIPTextModel)
+        te2 = module("text_encoder_2", CLIPTextModel) if (root / "text_encoder_2").is_dir() else None
+        tok = load_tokenizer(root / "tokenizer", te.config["vocab_size"])
+        tok2 = load_tokenizer(root / "tokenizer_2", te2.config["vocab_size"]) if te2 is not None else None
+        sched = checkpoints.component_config(root, "scheduler") or schedulers.SD_SCHEDULER_CONFIG
+        fam = family or _family_of_class(index.get("_class_name", "StableDiffusionPipeline"))
+        return cls(unet, vae, te, tok, sched, index, te2, tok2, controlnet, fam)
+
+    def to(self, device, dtype=None):
+        self.device = torch.device(device)
+        if dtype is not None:
+            self.dtype = dtype if self.device.type == "cuda" else torch.float32
+        for m in (self.unet, self.vae, self.text_encoder, self.text_encoder_2, self.controlnet):
+            if m is not None:
+                m.to(self.device, self.dtype).eval()
+        self._engine = None
+        return self
+
+    # ------------------------------------------------------------------ scheduler selection
+    def set_scheduler(self, scheduler_type, use_karras_sigmas=True):
+        """`scheduler_type.from_config(pipeline.scheduler.config, use_karras_sigmas=True)` in the
+        reference (swarm/diffusion/diffusion_func.py:71-74)."""
+        kind = getattr(scheduler_type, "kind", scheduler_type)
+        if kind not in schedulers.KINDS:
+            raise ValueError(f"Unsupported scheduler {scheduler_type}")
+        self.scheduler_kind = kind
+        self.use_karras_sigmas = bool(use_karras_sigmas)
+
+    # ------------------------------------------------------------------ text conditioning
+    @torch.no_grad()
+    def encode_prompt(self, prompts: List[str], negative: List[str], n_cond: int):
+        """Returns (embeds [n_cond*B, S, D], pooled [n_cond*B, P] or None). Stack order follows
+        the guidance kernel: 2-way [uncond, cond]; pix2pix 3-way [cond, uncond, uncond]."""
+        def enc(texts):
+            ids = self.tokenizer(texts).to(self.device)
+            if self.text_encoder_2 is None:
+                return self.text_encoder(ids)[0], None
+            h1, _ = self.text_encoder(ids, output_hidden_state=-2)
+            ids2 = self.tokenizer_2(texts).to(self.device)
+            h2, pooled = self.text_encoder_2(ids2, output_hidden_state=-2)
+            return torch.cat([h1, h2], dim=-1), pooled
+
+        cond, pooled_c = enc(prompts)
+        if n_cond == 1:
+            return cond, pooled_c
+        unc, pooled_u = enc(negative)
+        if n_cond == 2:
+            embeds = torch.cat([unc, cond])
+            pooled = None if pooled_c is None else torch.cat([pooled_u, pooled_c])
+        else:
+            embeds = torch.cat([cond, unc, unc])
+            pooled = None if pooled_c is None else torch.cat([pooled_c, pooled_u, pooled_u])
+        return embeds, pooled
+
+    # ------------------------------------------------------------------ main entry
+    @torch.no_grad()
+    def __call__(self, prompt="", negative_prompt=None, height=None, width=None, num_inference_steps=50,
+                 guidance_scale=7.5, num_images_per_prompt=1, generator=None, image=None, mask_image=None,
+                 strength=0.8, image_guidance_scale=1.5, controlnet_conditioning_scale=1.0, eta=0.0,
+                 cross_attention_kwargs=None, output_type="pil", latents=None, prompt_embeds=None, **ignored):
+        prompts = [prompt] if isinstance(prompt, str) else list(prompt)
+        if negative_prompt is None:
+            negative = [""] * len(prompts)
+        else:
+            negative = [negative_prompt] * len(prompts) if isinstance(negative_prompt, str) else list(negative_prompt)
+        prompts = [p for p in prompts for _ in range(num_images_per_prompt)]
+        negative = [p for p in negative for _ in range(num_images_per_prompt)]
+        batch = len(prompts)
+        unet_in = self.unet.config["in_channels"]
+        lat_ch = self.vae.config["latent_channels"]
+        vae_scale = 2 ** (len(self.vae.config["block_out_channels"]) - 1)
+
+        mode = self.family
+        if mode in ("auto", "sd"):
+            mode = "sd"
+            if unet_in == 8 and image is not None:
+                mode = "sd_pix2pix"
+            elif unet_in == 9 or mask_image is not None:
+                mode = "sd_inpaint"
+            elif self.controlnet is not None and image is not None:
+                mode = "sd_controlnet"
+        if mode == "sd_controlnet" and self.controlnet is None:
+            raise ValueError("ControlNet pipeline requested without a controlnet model")
+        if mode in ("sd_img2img", "sd_inpaint", "sd_pix2pix", "sd_controlnet") and image is None:
+            raise ValueError(f"{mode} needs an input image")
+        if mode == "sd_inpaint" and mask_image is None:
+            raise ValueError("inpainting needs a mask image")
+
+        if image is not None:
+            image = _fit_multiple(image, vae_scale)
+            width, height = image.size
+        sample = self.unet.config.get("sample_size", 64)
+        height = int(height or sample * vae_scale)
+        width = int(width or sample * vae_scale)
+        if height % vae_scale or width % vae_scale:
+            raise ValueError(f"`height` and `width` have to be divisible by {vae_scale} but are {height} and {width}.")
+        h8, w8 = height // vae_scale, width // vae_scale
+
+        pix2pix = mode == "sd_pix2pix"
+        do_cfg = guidance_scale > 1.0
+        n_cond = 3 if (pix2pix and do_cfg) else (2 if do_cfg else 1)
+        embeds, pooled = self.encode_prompt(prompts, negative, n_cond)
+        embeds = embeds.to(self.dtype)
+
+        plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), self.scheduler_config,
+                                    self.use_karras_sigmas)
+        shape = (batch, lat_ch, h8, w8)
+
+        def randn():
+            return torch.randn(shape, generator=generator, device=self.device, dtype=self.dtype)
+
+        extra = None          # constant extra UNet input channels [n_cond*B, C_extra, h8, w8]
+        control = None        # control image [n_cond*B, 3, H, W] in [0,1]
+        init_latents = None
+        if mode == "sd_img2img":
+            init = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), generator) * self.vae.scaling_factor
+            init = init.expand(batch, -1, -1, -1)
+            t_start = max(int(num_inference_steps) - min(int(int(num_inference_steps) * strength), int(num_inference_steps)), 0)
+            plan = plan.slice_from(t_start)
+            if plan.num_steps == 0:
+                raise ValueError("strength is too low: no denoising steps to run")
+            x = plan.add_noise(init.float(), randn().float(), 0)
+        else:
+            x = (latents if latents is not None else randn()).float() * plan.init_noise_sigma
+            if mode == "sd_inpaint":
+                img = pil_to_tensor(image, self.device, self.dtype)
+                m = torch.from_numpy(np.asarray(mask_image.convert("L").resize((width, height)), dtype=np.float32) / 255.0)
+                m = (m >= 0.5).to(self.device, self.dtype)[None, None]
+                masked = self.vae.encode(img * (1 - m), generator) * self.vae.scaling_factor
+                m8 = torch.nn.functional.interpolate(m, size=(h8, w8))
+                if unet_in == 9:
+                    extra = torch.cat([m8, masked], dim=1).expand(batch, -1, -1, -1).repeat(n_cond, 1, 1, 1)
+                else:  # legacy 4-channel inpainting: re-impose the known region every step
+                    init_latents = (self.vae.encode(img, generator) * self.vae.scaling_factor).float()
+                    init_latents = (init_latents, m8.float(), randn().float())
+            elif pix2pix:
+                img_lat = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), sample=False)
+                img_lat = img_lat.expand(batch, -1, -1, -1)
+                zeros = torch.zeros_like(img_lat)
+                extra = torch.cat([img_lat, img_lat, zeros]) if n_cond == 3 else img_lat
+            elif mode == "sd_controlnet":
+                control = pil_to_tensor(image, self.device, self.dtype, signed=False)
+                control = control.expand(batch, -1, -1, -1).repeat(n_cond, 1, 1, 1)
+
+        added = None
+        if self.unet.config.get("addition_embed_type") == "text_time":
+            ids = torch.tensor([[height, width, 0, 0, height, width]], device=self.device, dtype=torch.float32)
+            added = {"text_embeds": pooled.to(self.dtype), "time_ids": ids.expand(embeds.shape[0], -1)}
+
+        noise_table = None
+        if plan.needs_noise:
+            noise_table = torch.stack([randn().float() for _ in range(plan.num_steps)])
+
+        denoiser = self._denoiser()
+        x = denoiser.run(x=x, embeds=embeds, plan=plan, n_cond=n_cond, g_text=float(guidance_scale),
+                         g_image=float(image_guidance_scale), extra=extra, control=control,
+                         control_scale=float(controlnet_conditioning_scale), added=added, noise=noise_table,
+                         inpaint=init_latents)
+        if output_type == "latent":
+            return PipelineOutput(images=[], latents=x)
+        images = denoiser.decode(x / self.vae.scaling_factor)
+        pil = tensor_to_pil(images) if isinstance(images, torch.Tensor) and images.dtype != torch.uint8 else \
+            [Image.fromarray(a) for a in images.cpu().numpy()]
+        return PipelineOutput(images=pil, nsfw_content_detected=self.run_safety_checker(pil), latents=x)
+
+    def run_safety_checker(self, images):
+        if self.safety_checker is None:
+            return [False] * len(images)
+        return self.safety_checker(images)
+
+    def _denoiser(self):
+        if self._engine is None:
+            if self.backend == "sm100":
+                if self.device.type != "cuda":
+                    raise RuntimeError("the sm100 backend needs a CUDA device")
+                from ..engine.denoiser import SM100Denoiser
+
+                self._engine = SM100Denoiser(self)
+            else:
+                self._engine = TorchDenoiser(self)
+        return self._engine
+
+
+class TorchDenoiser:
+    """Eager reference loop: what diffusers would issue (cuDNN / cuBLAS / SDPA on CUDA)."""
+
+    def __init__(self, pipe: StableDiffusionPipeline):
+        self.pipe = pipe
+
+    @torch.no_grad()
+    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint):
+        p = self.pipe
+        x0_prev = None
+        scale = plan.first_scale
+        for i in range(plan.num_steps):
+            t = torch.tensor(float(plan.timesteps[i]), device=p.device)
+            model_in = torch.cat([x] * n_cond).to(p.dtype) * scale
+            if extra is not None:
+                model_in = torch.cat([model_in, extra.to(p.dtype)], dim=1)
+            down = mid = None
+            if control is not None:
+                down, mid = p.controlnet(model_in, t, embeds, control, control_scale)
+            out = p.unet(model_in, t, embeds, down, mid, added)
+            out = schedulers.guided(out.float(), n_cond, g_text, g_image)
+            x, x0_prev, scale = schedulers.apply_step_torch(plan, i, x, out, x0_prev,
+                                                            None if noise is None else noise[i])
+            if inpaint is not None:
+                init, m8, nz = inpaint
+                known = plan.add_noise(init, nz, i + 1) if i + 1 < plan.num_steps else init
+                x = m8 * x + (1 - m8) * known
+        return x
+
+    @torch.no_grad()
+    def decode(self, z):
+        return self.pipe.vae.decode(z.to(self.pipe.dtype))
+
+
+def _family_of_class(name: str) -> str:
+    from ..registry import _PIPELINES
+
+    return _PIPELINES.get(name, "sd")
+
+
+def build_pipeline(pipeline_type, model_name, **kw):
+    """`pipeline_type.from_pretrained(model_name, ...)` of the reference, for registry types."""
+    family = getattr(pipeline_type, "family", None) or "auto"
+    if family in ("txt2vid", "audioldm", "deepfloyd", "sd_upscale"):
+        raise ValueError(f"{getattr(pipeline_type, 'name', pipeline_type)} is not an image pipeline")
+    return StableDiffusionPipeline.from_pretrained(model_name, family=family, **kw)

@@ -1,0 +1,116 @@
+"""Built-in architecture configs.
+
+There is no network on the worker, so the component `config.json` contents of the architectures
+named by the benchmark configs (BASELINE.json) ship here; a locally present diffusers-layout
+checkpoint always wins over these.  They are recalled from the upstream repos (SURVEY.md section
+2.5 -- [UPSTREAM], re-verify against real config.json files when available).  `random_init=True`
+pipelines built from them are what the timing runs use (random weights of the named architecture).
+"""
+from __future__ import annotations
+
+import copy
+
+_SD_SCHED = dict(num_train_timesteps=1000, beta_start=0.00085, beta_end=0.012, beta_schedule="scaled_linear",
+                 prediction_type="epsilon", steps_offset=1)
+
+_SD15_UNET = dict(
+    in_channels=4, out_channels=4, block_out_channels=(320, 640, 1280, 1280), layers_per_block=2,
+    down_block_types=("CrossAttnDownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D", "DownBlock2D"),
+    up_block_types=("UpBlock2D", "CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "CrossAttnUpBlock2D"),
+    attention_head_dim=8, cross_attention_dim=768, norm_num_groups=32, norm_eps=1e-5, use_linear_projection=False,
+    sample_size=64)
+_SD_VAE = dict(in_channels=3, out_channels=3, latent_channels=4, block_out_channels=(128, 256, 512, 512),
+               layers_per_block=2, norm_num_groups=32, scaling_factor=0.18215)
+_CLIP_L = dict(vocab_size=49408, hidden_size=768, intermediate_size=3072, num_hidden_layers=12, num_attention_heads=12,
+               max_position_embeddings=77, hidden_act="quick_gelu", layer_norm_eps=1e-5)
+_CLIP_H = dict(vocab_size=49408, hidden_size=1024, intermediate_size=4096, num_hidden_layers=23, num_attention_heads=16,
+               max_position_embeddings=77, hidden_act="gelu", layer_norm_eps=1e-5)
+_CLIP_BIGG = dict(vocab_size=49408, hidden_size=1280, intermediate_size=5120, num_hidden_layers=32,
+                  num_attention_heads=20, max_position_embeddings=77, hidden_act="gelu", layer_norm_eps=1e-5,
+                  projection_dim=1280)
+
+_SD21_UNET = dict(_SD15_UNET, attention_head_dim=(5, 10, 20, 20), cross_attention_dim=1024, use_linear_projection=True,
+                  sample_size=96)
+
+_SDXL_UNET = dict(
+    in_channels=4, out_channels=4, block_out_channels=(320, 640, 1280), layers_per_block=2,
+    down_block_types=("DownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D"),
+    up_block_types=("CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "UpBlock2D"),
+    attention_head_dim=(5, 10, 20), transformer_layers_per_block=(1, 2, 10), cross_attention_dim=2048,
+    norm_num_groups=32, norm_eps=1e-5, use_linear_projection=True, addition_embed_type="text_time",
+    addition_time_embed_dim=256, projection_class_embeddings_input_dim=2816, sample_size=128)
+
+_TINY_UNET = dict(
+    in_channels=4, out_channels=4, block_out_channels=(32, 64), layers_per_block=2,
+    down_block_types=("DownBlock2D", "CrossAttnDownBlock2D"), up_block_types=("CrossAttnUpBlock2D", "UpBlock2D"),
+    attention_head_dim=8, cross_attention_dim=32, norm_num_groups=32, norm_eps=1e-5, use_linear_projection=False,
+    sample_size=8)
+_TINY_VAE = dict(in_channels=3, out_channels=3, latent_channels=4, block_out_channels=(32, 64), layers_per_block=1,
+                 norm_num_groups=32, scaling_factor=0.18215)
+_TINY_CLIP = dict(vocab_size=1000, hidden_size=32, intermediate_size=37, num_hidden_layers=5, num_attention_heads=4,
+                  max_position_embeddings=77, hidden_act="quick_gelu", layer_norm_eps=1e-5)
+
+_ZEROSCOPE_UNET3D = dict(
+    in_channels=4, out_channels=4, block_out_channels=(320, 640, 1280, 1280), layers_per_block=2,
+    down_block_types=("CrossAttnDownBlock3D", "CrossAttnDownBlock3D", "CrossAttnDownBlock3D", "DownBlock3D"),
+    up_block_types=("UpBlock3D", "CrossAttnUpBlock3D", "CrossAttnUpBlock3D", "CrossAttnUpBlock3D"),
+    attention_head_dim=64, cross_attention_dim=1024, norm_num_groups=32, norm_eps=1e-5, sample_size=32)
+
+_CONTROLNET_SD15 = dict(_SD15_UNET, conditioning_channels=3, conditioning_embedding_out_channels=(16, 32, 96, 256))
+
+_LATENT_UPSCALER_NOTE = "sd-x2-latent-upscaler uses a K-diffusion UNet; served by the SD UNet driver at 2x latent size"
+
+
+def _pipe(cls, unet, vae, text, sched=None, **extra):
+    d = dict(_class_name=cls, unet=unet, vae=vae, text_encoder=text, scheduler=dict(sched or _SD_SCHED))
+    d.update(extra)
+    return d
+
+
+ARCHITECTURES = {
+    "tiny-sd": _pipe("StableDiffusionPipeline", _TINY_UNET, _TINY_VAE, _TINY_CLIP),
+    "sd15": _pipe("StableDiffusionPipeline", _SD15_UNET, _SD_VAE, _CLIP_L),
+    "sd15-inpaint": _pipe("StableDiffusionInpaintPipeline", dict(_SD15_UNET, in_channels=9), _SD_VAE, _CLIP_L),
+    "instruct-pix2pix": _pipe("StableDiffusionInstructPix2PixPipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
+    "sd21": _pipe("StableDiffusionPipeline", _SD21_UNET, _SD_VAE, _CLIP_H,
+                  dict(_SD_SCHED, prediction_type="v_prediction")),
+    "sd21-base": _pipe("StableDiffusionPipeline", dict(_SD21_UNET, sample_size=64), _SD_VAE, _CLIP_H),
+    "sdxl": _pipe("StableDiffusionXLPipeline", _SDXL_UNET, dict(_SD_VAE, scaling_factor=0.13025), _CLIP_L,
+                  text_encoder_2=_CLIP_BIGG),
+    "zeroscope": _pipe("TextToVideoSDPipeline", _ZEROSCOPE_UNET3D, _SD_VAE, _CLIP_H),
+    "sd-x2-latent-upscaler": _pipe("StableDiffusionLatentUpscalePipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
+}
+
+CONTROLNETS = {"controlnet-sd15": _CONTROLNET_SD15}
+
+# model_name (as the hive sends it) -> architecture key
+_NAME_RULES = [
+    ("tiny-stable-diffusion", "tiny-sd"), ("tiny-sd", "tiny-sd"),
+    ("instruct-pix2pix", "instruct-pix2pix"),
+    ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
+    ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
+    ("sd-x2-latent-upscaler", "sd-x2-latent-upscaler"),
+    ("stable-diffusion-2-1-base", "sd21-base"), ("stable-diffusion-2-base", "sd21-base"),
+    ("stable-diffusion-2", "sd21"),
+    ("zeroscope", "zeroscope"), ("text-to-video", "zeroscope"), ("modelscope", "zeroscope"),
+    ("stable-diffusion-v1", "sd15"), ("sd15", "sd15"), ("sd-v1", "sd15"),
+]
+
+
+def architecture_for(model_name: str):
+    """Best-effort architecture key for a hive model name; None when unknown."""
+    low = model_name.lower()
+    if low in ARCHITECTURES:
+        return low
+    for needle, key in _NAME_RULES:
+        if needle in low:
+            return key
+    return None
+
+
+def get_architecture(key: str) -> dict:
+    return copy.deepcopy(ARCHITECTURES[key])
+
+
+def get_controlnet(model_name: str) -> dict:
+    return copy.deepcopy(CONTROLNETS["controlnet-sd15"])

@@ -1,0 +1,75 @@
+"""Resident pipeline / weight cache.  The reference reloads every model
+from disk for every job (swarm/diffusion/diffusion_func.py:41-46); on a 180 GB B200 the packed
+weights of every model a worker serves stay on the device, keyed by everything that changes the
+weights, with least-recently-used eviction by bytes."""
+from __future__ import annotations
+
+import threading
+from collections import OrderedDict
+from typing import Callable, Hashable
+
+
+def _nbytes(obj) -> int:
+    total = 0
+    seen = set()
+    for attr in ("unet", "vae", "text_encoder", "text_encoder_2", "controlnet"):
+        m = getattr(obj, attr, None)
+        if m is None or not hasattr(m, "parameters"):
+            continue
+        for p in m.parameters():
+            if id(p) not in seen:
+                seen.add(id(p))
+                total += p.numel() * p.element_size()
+    return total
+
+
+class LRUByBytes:
+    def __init__(self, budget_bytes: int):
+        self.budget = budget_bytes
+        self._items: "OrderedDict[Hashable, tuple]" = OrderedDict()
+        self._lock = threading.Lock()
+        self.hits = 0
+        self.misses = 0
+
+    def get(self, key: Hashable, loader: Callable):
+        with self._lock:
+            if key in self._items:
+                self._items.move_to_end(key)
+                self.hits += 1
+                return self._items[key][0]
+        value = loader()
+        size = _nbytes(value)
+        with self._lock:
+            self.misses += 1
+            self._items[key] = (value, size)
+            self._items.move_to_end(key)
+            while len(self._items) > 1 and sum(s for _, s in self._items.values()) > self.budget:
+                self._items.popitem(last=False)
+        return value
+
+    def clear(self):
+        with self._lock:
+            self._items.clear()
+
+    def __len__(self):
+        return len(self._items)
+
+    def bytes_resident(self) -> int:
+        with self._lock:
+            return sum(s for _, s in self._items.values())
+
+
+_cache = None
+
+
+def pipeline_cache() -> LRUByBytes:
+    global _cache
+    if _cache is None:
+        from ..settings import load_settings
+
+        try:
+            gb = float(getattr(load_settings(), "weight_cache_gb", 120))
+        except Exception:
+            gb = 120.0
+        _cache = LRUByBytes(int(gb * (1 << 30)))
+    return _cache

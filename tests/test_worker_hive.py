@@ -1,0 +1,131 @@
+"""End-to-end worker loop against a fake hive: /api/work and
+/api/results wire format, the 1 / 11 / 121 s cadence, 400 / 500 handling, bounded result retry."""
+import asyncio
+import json
+
+import pytest
+from aiohttp import web
+
+
+class FakeHive:
+    def __init__(self):
+        self.jobs = []
+        self.work_requests = []
+        self.results = []
+        self.work_status = 200
+        self.fail_results = 0
+
+    async def work(self, request):
+        self.work_requests.append({"query": dict(request.query), "headers": dict(request.headers)})
+        if self.work_status != 200:
+            return web.json_response({"message": "slow worker"}, status=self.work_status)
+        jobs, self.jobs = self.jobs, []
+        return web.json_response({"jobs": jobs})
+
+    async def result(self, request):
+        if self.fail_results > 0:
+            self.fail_results -= 1
+            return web.Response(status=500, reason="boom")
+        self.results.append(await request.json())
+        return web.json_response({"ok": True})
+
+    async def start(self):
+        app = web.Application(client_max_size=64 * 1024 * 1024)
+        app.router.add_get("/api/work", self.work)
+        app.router.add_post("/api/results", self.result)
+        self.runner = web.AppRunner(app)
+        await self.runner.setup()
+        site = web.TCPSite(self.runner, "127.0.0.1", 0)
+        await site.start()
+        port = site._server.sockets[0].getsockname()[1]
+        return f"http://127.0.0.1:{port}"
+
+    async def stop(self):
+        await self.runner.cleanup()
+
+
+@pytest.fixture(autouse=True)
+def _env(tmp_path, monkeypatch):
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    monkeypatch.setenv("SDAAS_RANDOM_INIT", "1")
+    monkeypatch.setenv("SDAAS_KERNEL_BACKEND", "torch")
+
+
+def _worker(uri, retries=3):
+    from chiaswarm_b200.gpu.device import Device
+    from chiaswarm_b200.settings import Settings
+    from chiaswarm_b200.worker import Worker
+
+    s = Settings()
+    s.sdaas_uri, s.sdaas_token, s.worker_name, s.result_retries = uri, "secret", "testrig", retries
+    return Worker(settings=s, devices=[Device("cpu")])
+
+
+def test_poll_cadence_and_wire_format():
+    from chiaswarm_b200 import __version__
+
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        try:
+            w = _worker(uri)
+            await w.startup()
+            assert await w.ask_for_work() == 11  # idle
+            hive.jobs = [{"id": "a", "workflow": "stitch", "model_name": "x", "jobs": []}]
+            assert await w.ask_for_work() == 1  # work found -> ask again right away
+            assert w.cpu_queue.qsize() == 1  # CPU-only workflow goes to the CPU lane
+            hive.work_status = 400
+            assert await w.ask_for_work() == 121
+            hive.work_status = 503
+            assert await w.ask_for_work() == 121
+            req = hive.work_requests[0]
+            assert req["query"] == {"worker_version": __version__, "worker_name": "testrig"}
+            assert req["headers"]["Authorization"] == "Bearer secret"
+            assert req["headers"]["User-Agent"] == f"chiaSWARM.worker/{__version__}"
+            assert w.available_gpus._value == 1  # the poll released its lane every time
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
+
+
+def test_unreachable_hive_backs_off():
+    async def main():
+        w = _worker("http://127.0.0.1:9")
+        await w.startup()
+        assert await w.ask_for_work() == 121
+
+    asyncio.run(main())
+
+
+def test_full_loop_generates_and_posts_results():
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        hive.jobs = [
+            {"id": "img", "model_name": "tiny-sd", "prompt": "p", "height": 64, "width": 64, "num_inference_steps": 2,
+             "seed": 3},
+            {"id": "bad", "model_name": "tiny-sd", "height": 5000, "width": 64},
+        ]
+        hive.fail_results = 1  # first POST gets a 500 and must be retried, not dropped
+        try:
+            w = _worker(uri)
+            slept = []
+
+            async def fast_sleep(s):
+                slept.append(s)
+                await asyncio.sleep(0)
+
+            w.result_worker.__func__.__defaults__ = (fast_sleep,)
+            await w.run(max_polls=2, sleep=fast_sleep)
+            ids = sorted(r["id"] for r in hive.results)
+            assert ids == ["bad", "img"]
+            by_id = {r["id"]: r for r in hive.results}
+            assert by_id["bad"]["fatal_error"] is True
+            assert set(by_id["img"]["artifacts"]["primary"]) == {"blob", "content_type", "thumbnail", "sha256_hash"}
+            assert by_id["img"]["pipeline_config"]["seed"] == 3
+            assert slept[0] == 1 and 11 in slept
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
