@@ -193,12 +193,17 @@ class StableDiffusionPipeline:
     def encode_prompt(self, prompts: List[str], negative: List[str], n_cond: int):
         """Returns (embeds [n_cond*B, S, D], pooled [n_cond*B, P] or None). Stack order follows
         the guidance kernel: 2-way [uncond, cond]; pix2pix 3-way [cond, uncond, uncond]."""
+        def to_dev(ids):
+            if self.device.type == "cuda":  # staged through pinned host memory
+                return ids.pin_memory().to(self.device, non_blocking=True)
+            return ids
+
         def enc(texts):
-            ids = self.tokenizer(texts).to(self.device)
+            ids = to_dev(self.tokenizer(texts))
             if self.text_encoder_2 is None:
                 return self.text_encoder(ids)[0], None
             h1, _ = self.text_encoder(ids, output_hidden_state=-2)
-            ids2 = self.tokenizer_2(texts).to(self.device)
+            ids2 = to_dev(self.tokenizer_2(texts))
             h2, pooled = self.text_encoder_2(ids2, output_hidden_state=-2)
             return torch.cat([h1, h2], dim=-1), pooled
 
@@ -321,6 +326,10 @@ class StableDiffusionPipeline:
         if output_type == "latent":
             return PipelineOutput(images=[], latents=x)
         images = denoiser.decode(x / self.vae.scaling_factor)
+        if output_type == "device":  # leave the decoded batch on the GPU (benchmarks, chained stages)
+            out = PipelineOutput(images=[], latents=x)
+            out.device_images = images
+            return out
         pil = tensor_to_pil(images) if isinstance(images, torch.Tensor) and images.dtype != torch.uint8 else \
             [Image.fromarray(a) for a in images.cpu().numpy()]
         return PipelineOutput(images=pil, nsfw_content_detected=self.run_safety_checker(pil), latents=x)

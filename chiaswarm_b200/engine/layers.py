@@ -1,0 +1,331 @@
+"""Plan recorder and packed layers for the sm_100a execution engine.
+
+The engine does not run nn.Modules.  It walks the module tree once (the modules are the
+checkpoint-compatible *specification*, models/*.py), re-packs every weight into the layout the
+kernels want, allocates every activation buffer up front and records a flat list of kernel
+launches -- a static plan.  Executing the plan issues only our own kernels (ops/native.py), so
+the whole thing can be captured into one CUDA graph and replayed per denoising step.
+
+Activations are channels-last fp16 everywhere: a feature map [N,H,W,C] *is* the token matrix
+[N*H*W, C], so convs, 1x1 projections and transformer blocks chain without a single permute.
+Replaces the eager diffusers module graph reached at swarm/diffusion/diffusion_func.py:96.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from ..ops import native as nat
+from ..ops.packing import interleave_geglu, pack_conv_weight, pad_vector
+
+
+def _r8(c: int) -> int:
+    return (c + 7) // 8 * 8
+
+
+@dataclass
+class FM:
+    """Channels-last feature map view of a flat fp16 buffer."""
+
+    t: torch.Tensor  # [n, h, w, c]
+    n: int
+    h: int
+    w: int
+    c: int
+
+    @property
+    def rows(self):
+        return self.n * self.h * self.w
+
+    def tokens(self):
+        return self.t.view(self.rows, self.c)
+
+
+class Recorder:
+    """Records kernel launches with concrete buffers; `run()` replays them in order."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.ops = []
+        self._free = {}
+        self.bytes_allocated = 0
+        self.gn_stats = torch.zeros(64 * 1024, dtype=torch.float32, device=self.device)
+
+    # ---- buffers (explicit liveness: release() makes a buffer reusable by later ops)
+    def buf(self, *shape, dtype=torch.float16):
+        numel = 1
+        for s in shape:
+            numel *= s
+        key = (numel, dtype)
+        lst = self._free.get(key)
+        if lst:
+            return lst.pop().view(*shape)
+        self.bytes_allocated += numel * torch.empty((), dtype=dtype).element_size()
+        return torch.empty(*shape, dtype=dtype, device=self.device)
+
+    def fm(self, n, h, w, c) -> FM:
+        return FM(self.buf(n, h, w, c), n, h, w, c)
+
+    def release(self, t):
+        if isinstance(t, FM):
+            t = t.t
+        self._free.setdefault((t.numel(), t.dtype), []).append(t.view(-1))
+
+    # ---- recording
+    def add(self, fn, *args, **kw):
+        self.ops.append((fn, args, kw))
+
+    def run(self):
+        for fn, args, kw in self.ops:
+            fn(*args, **kw)
+
+    def __len__(self):
+        return len(self.ops)
+
+
+# ------------------------------------------------------------------------------------------ layers
+class Conv:
+    """3x3 / 1x1 stride-1 conv (implicit GEMM) or stride-2 conv (im2col + GEMM)."""
+
+    def __init__(self, conv: torch.nn.Conv2d, cin_pad: Optional[int] = None, asym_pad: bool = False):
+        w = conv.weight.detach().to(torch.float16)
+        self.cout_real = w.shape[0]
+        self.cout = _r8(w.shape[0])
+        self.cin = cin_pad or _r8(w.shape[1])
+        self.k = w.shape[2]
+        self.stride = conv.stride[0]
+        self.pad = conv.padding[0] if not asym_pad else 0
+        self.asym = asym_pad
+        self.wgt = pack_conv_weight(w, self.cin, self.cout)
+        self.bias = None if conv.bias is None else pad_vector(conv.bias.detach().to(torch.float16), self.cout)
+
+    def __call__(self, rec: Recorder, x: FM, x2: Optional[FM] = None, row_bias=None, residual: Optional[FM] = None,
+                 act=nat.ACT_NONE, out_scale=1.0, out: Optional[FM] = None) -> FM:
+        if self.stride == 1:
+            o = out or rec.fm(x.n, x.h, x.w, self.cout)
+            rec.add(nat.igemm, x.t, self.wgt, o.t.view(-1, o.c), n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, pad=self.pad,
+                    a2=None if x2 is None else x2.t, bias=self.bias, row_bias=row_bias,
+                    residual=None if residual is None else residual.tokens(), act=act, out_scale=out_scale)
+            return o
+        assert x2 is None and self.stride == 2
+        if self.asym:  # VAE encoder: pad (0,1,0,1) then valid conv
+            oh, ow = (x.h + 1 - self.k) // 2 + 1, (x.w + 1 - self.k) // 2 + 1
+            pt = pl = 0
+        else:
+            oh, ow = (x.h + 2 * self.pad - self.k) // 2 + 1, (x.w + 2 * self.pad - self.k) // 2 + 1
+            pt = pl = self.pad
+        cols = rec.buf(x.n, oh, ow, self.k * self.k * x.c)
+        rec.add(nat.im2col, x.t, cols, n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, stride=2, pad_top=pt, pad_left=pl,
+                oh=oh, ow=ow)
+        o = out or rec.fm(x.n, oh, ow, self.cout)
+        rec.add(nat.igemm, cols.view(-1, cols.shape[-1]), self.wgt, o.t.view(-1, o.c), n=1, h=1, w=x.n * oh * ow,
+                bias=self.bias, row_bias=None, residual=None if residual is None else residual.tokens(), act=act,
+                out_scale=out_scale)
+        rec.release(cols)
+        return o
+
+
+class Linear:
+    def __init__(self, weight, bias=None, geglu=False):
+        w = weight.detach().to(torch.float16)
+        if w.dim() == 4:
+            w = w[:, :, 0, 0]
+        b = None if bias is None else bias.detach().to(torch.float16)
+        if w.shape[0] % 8 or w.shape[1] % 8:  # tiny projections (e.g. VAE post_quant 4->4): zero-pad
+            wp = torch.zeros(_r8(w.shape[0]), _r8(w.shape[1]), dtype=w.dtype, device=w.device)
+            wp[: w.shape[0], : w.shape[1]] = w
+            w, b = wp, pad_vector(b, wp.shape[0])
+        self.geglu = geglu
+        if geglu:
+            w, b = interleave_geglu(w, b)
+        self.nout = w.shape[0] // 2 if geglu else w.shape[0]
+        self.wgt = w.contiguous()
+        self.bias = None if b is None else b.contiguous()
+
+    def __call__(self, rec: Recorder, x: torch.Tensor, residual=None, act=nat.ACT_NONE, out=None, out_scale=1.0):
+        """x: [rows, K] -> [rows, nout]."""
+        rows = x.shape[0]
+        o = out if out is not None else rec.buf(rows, self.nout)
+        rec.add(nat.igemm, x, self.wgt, o, n=1, h=1, w=rows, bias=self.bias, residual=residual,
+                act=nat.ACT_GEGLU if self.geglu else act, out_scale=out_scale)
+        return o
+
+
+class GroupNorm:
+    def __init__(self, gn: torch.nn.GroupNorm):
+        self.groups, self.eps = gn.num_groups, gn.eps
+        self.gamma = gn.weight.detach().to(torch.float16).contiguous()
+        self.beta = gn.bias.detach().to(torch.float16).contiguous()
+
+    def __call__(self, rec: Recorder, x: FM, silu: bool, x2: Optional[FM] = None) -> FM:
+        c = x.c + (x2.c if x2 is not None else 0)
+        o = rec.fm(x.n, x.h, x.w, c)
+        assert x.n * self.groups * 2 <= rec.gn_stats.numel()
+        rec.add(nat.groupnorm, x.t, self.gamma, self.beta, o.t, n=x.n, hw=x.h * x.w, groups=self.groups, eps=self.eps,
+                silu=silu, stats=rec.gn_stats, x2=None if x2 is None else x2.t)
+        return o
+
+
+class LayerNorm:
+    def __init__(self, ln: torch.nn.LayerNorm):
+        self.eps = ln.eps
+        self.gamma = ln.weight.detach().to(torch.float16).contiguous()
+        self.beta = ln.bias.detach().to(torch.float16).contiguous()
+
+    def __call__(self, rec: Recorder, x: torch.Tensor) -> torch.Tensor:
+        o = rec.buf(*x.shape)
+        rec.add(nat.layernorm, x, self.gamma, self.beta, o, self.eps)
+        return o
+
+
+class Resnet:
+    """GN+SiLU -> conv3x3 (+time-embedding row bias) -> GN+SiLU -> conv3x3 (+shortcut residual).
+    A skip tensor (UNet up path) is consumed as a second input, never concatenated in memory."""
+
+    def __init__(self, m, temb_slice=None):
+        self.norm1, self.norm2 = GroupNorm(m.norm1), GroupNorm(m.norm2)
+        self.conv1, self.conv2 = Conv(m.conv1), Conv(m.conv2)
+        self.shortcut = None
+        if m.conv_shortcut is not None:
+            self.shortcut = Linear(m.conv_shortcut.weight, m.conv_shortcut.bias)
+        self.scale = 1.0 / m.output_scale_factor
+        self.temb_slice = temb_slice  # (offset, width) into the fused time-embedding projection
+
+    def __call__(self, rec: Recorder, x: FM, skip: Optional[FM] = None, temb_all=None) -> FM:
+        h = self.norm1(rec, x, True, skip)
+        rb = None
+        if self.temb_slice is not None and temb_all is not None:
+            off, width = self.temb_slice
+            rb = temb_all[:, off:off + width]
+        h2 = self.conv1(rec, h, row_bias=rb)
+        rec.release(h)
+        h3 = self.norm2(rec, h2, True)
+        rec.release(h2)
+        if self.shortcut is not None:
+            sc = rec.fm(x.n, x.h, x.w, self.conv2.cout)
+            rec.add(nat.igemm, x.t, self.shortcut.wgt, sc.tokens(), n=x.n, h=x.h, w=x.w, kh=1, kw=1, pad=0,
+                    a2=None if skip is None else skip.t, bias=self.shortcut.bias)
+            res = sc
+        else:
+            assert skip is None
+            res = x
+        out = self.conv2(rec, h3, residual=res, out_scale=self.scale)
+        # (x + h)/s == x/s + h/s: only scale != 1 needs the residual pre-scaled; SD uses s == 1.
+        assert self.scale == 1.0, "output_scale_factor != 1 is not used by the supported checkpoints"
+        rec.release(h3)
+        if self.shortcut is not None:
+            rec.release(sc)
+        return out
+
+
+class CrossKV:
+    """Per-job precomputed K/V of one cross-attention layer (text is step-invariant)."""
+
+    def __init__(self, attn):
+        wk = attn.to_k.weight.detach().to(torch.float16)
+        wv = attn.to_v.weight.detach().to(torch.float16)
+        self.lin = Linear(torch.cat([wk, wv], 0))
+        self.buffers = {}   # (n, s_text) -> [n, s_text, 2C]; captured graphs keep pointing at theirs
+        self.kv = None      # buffer of the job being prepared
+
+
+class TransformerBlock:
+    def __init__(self, m):
+        self.heads, self.dh = m.attn1.heads, m.attn1.dim_head
+        c = self.heads * self.dh
+        self.c = c
+        self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
+        a1, a2 = m.attn1, m.attn2
+        self.self_is_cross = m.only_cross_attention
+        if not self.self_is_cross:
+            self.qkv = Linear(torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], 0))
+        else:
+            self.q1 = Linear(a1.to_q.weight)
+            self.kv1 = CrossKV(a1)
+        self.o1 = Linear(a1.to_out[0].weight, a1.to_out[0].bias)
+        self.q2 = Linear(a2.to_q.weight)
+        self.kv2 = CrossKV(a2)
+        self.o2 = Linear(a2.to_out[0].weight, a2.to_out[0].bias)
+        self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True)
+        self.ff2 = Linear(m.ff.net[2].weight, m.ff.net[2].bias)
+
+    def cross_layers(self):
+        return [self.kv2] + ([self.kv1] if self.self_is_cross else [])
+
+    def _cross(self, rec, x_norm, kv: CrossKV, n, s, out_lin, residual):
+        q = (self.q1 if kv is getattr(self, "kv1", None) else self.q2)(rec, x_norm)
+        skv = kv.kv.shape[1]
+        kvv = kv.kv.view(n, skv, 2, self.heads, self.dh)
+        attn = rec.buf(n, s, self.c)
+        rec.add(nat.flash_attn, q.view(n, s, self.heads, self.dh), kvv[:, :, 0], kvv[:, :, 1], attn, batch=n,
+                heads=self.heads, seq_q=s, seq_kv=skv, head_dim=self.dh)
+        rec.release(q)
+        y = out_lin(rec, attn.view(n * s, self.c), residual=residual)
+        rec.release(attn)
+        return y
+
+    def __call__(self, rec: Recorder, y: torch.Tensor, n: int, s: int) -> torch.Tensor:
+        """y: [n*s, c] residual stream; returns the new stream (y is released)."""
+        x1 = self.ln1(rec, y)
+        if not self.self_is_cross:
+            qkv = self.qkv(rec, x1)
+            rec.release(x1)
+            v5 = qkv.view(n, s, 3, self.heads, self.dh)
+            attn = rec.buf(n, s, self.c)
+            rec.add(nat.flash_attn, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn, batch=n, heads=self.heads, seq_q=s,
+                    seq_kv=s, head_dim=self.dh)
+            rec.release(qkv)
+            y1 = self.o1(rec, attn.view(n * s, self.c), residual=y)
+            rec.release(attn)
+        else:
+            y1 = self._cross(rec, x1, self.kv1, n, s, self.o1, y)
+            rec.release(x1)
+        rec.release(y)
+        x2 = self.ln2(rec, y1)
+        y2 = self._cross(rec, x2, self.kv2, n, s, self.o2, y1)
+        rec.release(x2)
+        rec.release(y1)
+        x3 = self.ln3(rec, y2)
+        ff = self.ff1(rec, x3)
+        rec.release(x3)
+        y3 = self.ff2(rec, ff, residual=y2)
+        rec.release(ff)
+        rec.release(y2)
+        return y3
+
+
+class Transformer2D:
+    def __init__(self, m):
+        self.norm = GroupNorm(m.norm)
+        self.proj_in = Linear(m.proj_in.weight, m.proj_in.bias)
+        self.proj_out = Linear(m.proj_out.weight, m.proj_out.bias)
+        self.blocks = [TransformerBlock(b) for b in m.transformer_blocks]
+
+    def cross_layers(self):
+        return [kv for b in self.blocks for kv in b.cross_layers()]
+
+    def __call__(self, rec: Recorder, x: FM) -> FM:
+        g = self.norm(rec, x, False)
+        y = self.proj_in(rec, g.tokens())
+        rec.release(g)
+        s = x.h * x.w
+        for blk in self.blocks:
+            y = blk(rec, y, x.n, s)
+        out = rec.fm(x.n, x.h, x.w, x.c)
+        self.proj_out(rec, y, residual=x.tokens(), out=out.tokens())
+        rec.release(y)
+        return out
+
+
+class Upsample:
+    def __init__(self, m):
+        self.conv = Conv(m.conv)
+
+    def __call__(self, rec: Recorder, x: FM) -> FM:
+        up = rec.fm(x.n, 2 * x.h, 2 * x.w, x.c)
+        rec.add(nat.upsample2x, x.t, up.t, n=x.n, h=x.h, w=x.w)
+        o = self.conv(rec, up)
+        rec.release(up)
+        return o

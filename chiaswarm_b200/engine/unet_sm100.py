@@ -1,0 +1,267 @@
+"""sm_100a execution plans for UNet2DConditionModel / ControlNetModel / AutoencoderKL decoder.
+
+Each `build_*` walks the torch module (the specification) and records a static plan on a
+Recorder (engine/layers.py).  Per denoising step the UNet plan is:
+
+  timestep embedding (reads t_table[*step]) -> time MLP -> ONE fused GEMM for every resnet's
+  time_emb_proj -> conv_in -> down blocks -> mid -> up blocks (skip tensors consumed as second
+  GroupNorm / shortcut inputs, never concatenated) -> GN+SiLU -> conv_out
+
+followed (engine/denoiser.py) by the fused CFG + scheduler-update kernel.  Reference call site
+being replaced: `eps = unet(x_in, t, text, [residuals])` inside diffusers' denoising loop
+(swarm/diffusion/diffusion_func.py:96).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from ..ops import native as nat
+from .layers import FM, Conv, GroupNorm, Linear, Recorder, Resnet, Transformer2D, Upsample, _r8
+
+
+class UNetPlan:
+    def __init__(self, unet, device):
+        self.cfg = unet.config
+        self.device = torch.device(device)
+        self.in_ch = self.cfg["in_channels"]
+        self.in_pad = _r8(self.in_ch)
+        self.out_ch = self.cfg["out_channels"]
+        self.boc = list(self.cfg["block_out_channels"])
+        self.temb_in = self.boc[0]
+
+        # ---- time MLP + fused time_emb_proj of every resnet
+        te = unet.time_embedding
+        self.t1 = Linear(te.linear_1.weight, te.linear_1.bias)
+        self.t2 = Linear(te.linear_2.weight, te.linear_2.bias)
+        resnets = []
+        for blk in list(unet.down_blocks) + [unet.mid_block] + list(getattr(unet, "up_blocks", [])):
+            resnets.extend(blk.resnets)
+        off = 0
+        ws, bs = [], []
+        self._slices = {}
+        for r in resnets:
+            if r.time_emb_proj is not None:
+                width = r.time_emb_proj.weight.shape[0]
+                self._slices[id(r)] = (off, width)
+                ws.append(r.time_emb_proj.weight)
+                bs.append(r.time_emb_proj.bias)
+                off += width
+        self.temb_proj = Linear(torch.cat(ws, 0), torch.cat(bs, 0)) if ws else None
+
+        def res(m):
+            return Resnet(m, self._slices.get(id(m)))
+
+        self.conv_in = Conv(unet.conv_in, cin_pad=self.in_pad)
+        self.down = []
+        for blk in unet.down_blocks:
+            self.down.append(dict(
+                resnets=[res(r) for r in blk.resnets],
+                attns=[Transformer2D(a) for a in blk.attentions] if blk.attentions is not None else None,
+                down=Conv(blk.downsamplers[0].conv) if blk.downsamplers is not None else None))
+        mb = unet.mid_block
+        self.mid = dict(resnets=[res(r) for r in mb.resnets],
+                        attns=[Transformer2D(a) for a in mb.attentions] if mb.attentions is not None else None)
+        self.up = []
+        if hasattr(unet, "up_blocks"):
+            for blk in unet.up_blocks:
+                self.up.append(dict(
+                    resnets=[res(r) for r in blk.resnets],
+                    attns=[Transformer2D(a) for a in blk.attentions] if blk.attentions is not None else None,
+                    up=Upsample(blk.upsamplers[0]) if blk.upsamplers is not None else None))
+            self.norm_out = GroupNorm(unet.conv_norm_out)
+            self.conv_out = Conv(unet.conv_out)
+
+    # ------------------------------------------------------------------ cross-attention K/V
+    def cross_layers(self):
+        out = []
+        for blk in self.down + [self.mid] + self.up:
+            for a in (blk["attns"] or []):
+                out.extend(a.cross_layers())
+        return out
+
+    def set_context(self, embeds: torch.Tensor):
+        """embeds [n, s_text, d] fp16: computes every cross-attention layer's K/V once per job
+        (they do not depend on the timestep)."""
+        n, s, d = embeds.shape
+        flat = embeds.reshape(n * s, d).contiguous()
+        for kv in self.cross_layers():
+            buf = kv.buffers.get((n, s))
+            if buf is None:
+                buf = kv.buffers[(n, s)] = torch.empty(n, s, kv.lin.nout, dtype=torch.float16, device=embeds.device)
+            kv.kv = buf
+            nat.igemm(flat, kv.lin.wgt, buf.view(n * s, -1), n=1, h=1, w=n * s)
+
+    # ------------------------------------------------------------------ plan
+    def record_time_embedding(self, rec: Recorder, n: int, t_table, step_idx, aug_emb=None):
+        """Returns the fused per-resnet time projections [n, sum(cout)]."""
+        sin = rec.buf(n, self.temb_in)
+        rec.add(nat.timestep_embedding, t_table, step_idx, sin, n=n, dim=self.temb_in,
+                flip_sin_to_cos=self.cfg.get("flip_sin_to_cos", True), freq_shift=float(self.cfg.get("freq_shift", 0)))
+        h = self.t1(rec, sin, act=nat.ACT_SILU)
+        # emb = linear_2(h) [+ added-condition embedding]; every consumer applies SiLU first
+        if aug_emb is None:
+            act_emb = self.t2(rec, h, act=nat.ACT_SILU)
+        else:
+            emb = self.t2(rec, h, residual=aug_emb)
+            act_emb = rec.buf(*emb.shape)
+            rec.add(nat.silu, emb, act_emb)
+        if self.temb_proj is None:
+            return None
+        return self.temb_proj(rec, act_emb)
+
+    def record_encoder(self, rec: Recorder, x_in: FM, temb_all, cond_feat: Optional[FM] = None):
+        """conv_in + down blocks + mid. Returns (mid output, skip list)."""
+        x = self.conv_in(rec, x_in, residual=cond_feat)
+        skips = [x]
+        for blk in self.down:
+            for i, r in enumerate(blk["resnets"]):
+                x = r(rec, x, None, temb_all)
+                if blk["attns"] is not None:
+                    x2 = blk["attns"][i](rec, x)
+                    rec.release(x)
+                    x = x2
+                skips.append(x)
+            if blk["down"] is not None:
+                x = blk["down"](rec, x)
+                skips.append(x)
+        x = self.mid["resnets"][0](rec, x, None, temb_all)
+        if self.mid["attns"] is not None:
+            x2 = self.mid["attns"][0](rec, x)
+            rec.release(x)
+            x = x2
+        x2 = self.mid["resnets"][1](rec, x, None, temb_all)
+        rec.release(x)
+        return x2, skips
+
+    def record_decoder(self, rec: Recorder, x: FM, skips: List[FM], temb_all) -> FM:
+        skips = list(skips)
+        for blk in self.up:
+            for i, r in enumerate(blk["resnets"]):
+                skip = skips.pop()
+                x2 = r(rec, x, skip, temb_all)
+                rec.release(x)
+                rec.release(skip)
+                x = x2
+                if blk["attns"] is not None:
+                    x2 = blk["attns"][i](rec, x)
+                    rec.release(x)
+                    x = x2
+            if blk["up"] is not None:
+                x2 = blk["up"](rec, x)
+                rec.release(x)
+                x = x2
+        g = self.norm_out(rec, x, True)
+        rec.release(x)
+        out = self.conv_out(rec, g)
+        rec.release(g)
+        return out
+
+
+class ControlNetPlan(UNetPlan):
+    """Encoder copy + conditioning embedder + zero convs.  The zero-conv outputs are not stored
+    separately: each zero conv writes `unet_skip + scale * zero_conv(feature)` straight over the
+    UNet's skip tensor (the residual add is its epilogue)."""
+
+    def __init__(self, cn, device):
+        super().__init__(cn, device)
+        ce = cn.controlnet_cond_embedding
+        self.cond_in_pad = _r8(ce.conv_in.weight.shape[1])
+        self.cond_convs = [Conv(ce.conv_in, cin_pad=self.cond_in_pad)] + [Conv(b) for b in ce.blocks] + [Conv(ce.conv_out)]
+        self.zero = [Linear(c.weight, c.bias) for c in cn.controlnet_down_blocks]
+        self.zero_mid = Linear(cn.controlnet_mid_block.weight, cn.controlnet_mid_block.bias)
+
+    def record_cond_embedding(self, rec: Recorder, cond: FM) -> FM:
+        """Step-invariant: run once per job, outside the per-step graph."""
+        x = cond
+        for i, c in enumerate(self.cond_convs):
+            last = i == len(self.cond_convs) - 1
+            x = c(rec, x, act=nat.ACT_NONE if last else nat.ACT_SILU)
+        return x
+
+    def record_residual_adds(self, rec: Recorder, feats: List[FM], mid: FM, unet_skips: List[FM], unet_mid: FM,
+                             scale: float):
+        for z, f, s in zip(self.zero, feats, unet_skips):
+            rec.add(nat.igemm, f.tokens(), z.wgt, s.tokens(), n=1, h=1, w=f.rows, bias=z.bias, residual=s.tokens(),
+                    out_scale=scale)
+        rec.add(nat.igemm, mid.tokens(), self.zero_mid.wgt, unet_mid.tokens(), n=1, h=1, w=mid.rows,
+                bias=self.zero_mid.bias, residual=unet_mid.tokens(), out_scale=scale)
+
+
+class VaeDecoderPlan:
+    """AutoencoderKL.decode on sm_100a kernels, ending in a uint8 HWC image (row W8)."""
+
+    def __init__(self, vae, device):
+        self.vae_cfg = vae.config
+        self.lat = vae.config["latent_channels"]
+        self.lat_pad = _r8(self.lat)
+        dec = vae.decoder
+        self.post_quant = Linear(vae.post_quant_conv.weight, vae.post_quant_conv.bias)
+        self.conv_in = Conv(dec.conv_in, cin_pad=self.lat_pad)
+        self.mid_res = [Resnet(r) for r in dec.mid_block.resnets]
+        at = dec.mid_block.attentions[0]
+        self.attn_norm = GroupNorm(at.group_norm)
+        self.attn_qkv = Linear(torch.cat([at.to_q.weight, at.to_k.weight, at.to_v.weight], 0),
+                               torch.cat([at.to_q.bias, at.to_k.bias, at.to_v.bias], 0))
+        self.attn_out = Linear(at.to_out[0].weight, at.to_out[0].bias)
+        self.attn_c = at.to_q.weight.shape[0]
+        self.ups = []
+        for blk in dec.up_blocks:
+            self.ups.append(dict(resnets=[Resnet(r) for r in blk.resnets],
+                                 up=Upsample(blk.upsamplers[0]) if blk.upsamplers is not None else None))
+        self.norm_out = GroupNorm(dec.conv_norm_out)
+        self.conv_out = Conv(dec.conv_out)
+
+    def _attention(self, rec: Recorder, x: FM) -> FM:
+        c = self.attn_c
+        s = x.h * x.w
+        g = self.attn_norm(rec, x, False)
+        qkv = self.attn_qkv(rec, g.tokens())  # [n*s, 3c]
+        rec.release(g)
+        out = rec.fm(x.n, x.h, x.w, c)
+        o_tok = out.tokens()
+        attn = rec.buf(x.n * s, c)
+        scores = rec.buf(s, s)
+        vt = rec.buf(c, s)
+        for b in range(x.n):
+            blk = qkv[b * s:(b + 1) * s]
+            # q, k are column blocks of the fused projection (strided operands); V^T via the
+            # channels-last -> planar transpose kernel
+            rec.add(nat.igemm, blk[:, :c], blk[:, c:2 * c], scores, n=1, h=1, w=s, out_scale=c ** -0.5)
+            rec.add(nat.softmax_rows, scores, scores, 1.0)
+            rec.add(nat.nhwc_to_nchw, blk[:, 2 * c:], vt.view(1, c, 1, s), 3 * c)
+            rec.add(nat.igemm, scores, vt, attn[b * s:(b + 1) * s], n=1, h=1, w=s)
+        self.attn_out(rec, attn, residual=x.tokens(), out=o_tok)
+        for t in (attn, scores, vt, qkv):
+            rec.release(t)
+        return out
+
+    def record(self, rec: Recorder, z: FM):
+        """z: latents / scaling_factor (+ post-quant bias), channels-last, padded to 8 channels.
+        Returns (image FM [n, H, W, 8], of which 3 channels are real)."""
+        zq = rec.fm(z.n, z.h, z.w, self.lat_pad)
+        self.post_quant(rec, z.tokens(), out=zq.tokens())
+        x = self.conv_in(rec, zq)
+        rec.release(zq)
+        x2 = self.mid_res[0](rec, x)
+        rec.release(x)
+        x = self._attention(rec, x2)
+        rec.release(x2)
+        x2 = self.mid_res[1](rec, x)
+        rec.release(x)
+        x = x2
+        for blk in self.ups:
+            for r in blk["resnets"]:
+                x2 = r(rec, x)
+                rec.release(x)
+                x = x2
+            if blk["up"] is not None:
+                x2 = blk["up"](rec, x)
+                rec.release(x)
+                x = x2
+        g = self.norm_out(rec, x, True)
+        rec.release(x)
+        img = self.conv_out(rec, g)
+        rec.release(g)
+        return img

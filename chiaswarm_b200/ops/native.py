@@ -45,6 +45,8 @@ class IGemmParams(C.Structure):
         ("tile_n", C.c_int32),
         ("gn_stats", C.c_void_p),
         ("gn_groups", C.c_int32),
+        ("a_ld", C.c_int32),
+        ("w_ld", C.c_int32),
     ]
 
 
@@ -91,7 +93,7 @@ def lib() -> C.CDLL:
             for name in (
                 "sw_igemm", "sw_flash_attn", "sw_groupnorm_nhwc", "sw_layernorm", "sw_upsample2x_nhwc",
                 "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
-                "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8",
+                "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8", "sw_softmax_rows",
             ):
                 getattr(l, name).restype = C.c_int
             l.sw_igemm.argtypes = [C.POINTER(IGemmParams), C.c_void_p]
@@ -101,6 +103,7 @@ def lib() -> C.CDLL:
                                             C.c_int, C.c_void_p, C.c_void_p]
             l.sw_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                        C.c_float, C.c_void_p]
+            l.sw_softmax_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p]
             l.sw_upsample2x_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                              C.c_void_p]
             l.sw_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 11 + [C.c_void_p]
@@ -149,12 +152,19 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
           residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
-    _f16(a1, "a1"); _f16(wgt, "wgt"); _f16(out, "out")
+    for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
+        if t.dtype != torch.float16 or not t.is_cuda or t.stride(-1) != 1:
+            raise TypeError(f"{nm}: expected a CUDA fp16 tensor with contiguous last dim")
     c1 = a1.shape[-1]
     c2 = 0 if a2 is None else _f16(a2, "a2").shape[-1]
     cout = wgt.shape[0]
     assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
     assert a1.numel() == n * h * w * c1
+    # strided 2-D views (a column block of a wider matrix) are passed through leading dimensions
+    a_ld = 0 if a1.is_contiguous() else a1.stride(-2)
+    w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
+    if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
+        raise ValueError("strided a1 is only supported for plain GEMMs")
     p = IGemmParams()
     p.a1, p.a2 = _ptr(a1), _ptr(a2)
     p.c1, p.c2 = c1, c2
@@ -164,17 +174,19 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.cout = cout
     p.bias = _ptr(bias)
     p.row_bias = _ptr(row_bias)
-    p.row_bias_ld = 0 if row_bias is None else row_bias.shape[-1]
+    p.row_bias_ld = 0 if row_bias is None else row_bias.stride(-2)
     p.residual = _ptr(residual)
-    p.ldr = 0 if residual is None else residual.shape[-1]
+    p.ldr = 0 if residual is None else residual.stride(-2)
     p.out = _ptr(out)
-    p.ldc = out.shape[-1]
+    p.ldc = out.stride(-2) if out.dim() > 1 else out.shape[-1]
     p.act = act
     p.out_scale = out_scale
     p.bf16 = 0
     p.tile_n = tile_n
     p.gn_stats = None
     p.gn_groups = 0
+    p.a_ld = a_ld
+    p.w_ld = w_ld
     _check(lib().sw_igemm(C.byref(p), _stream()), "sw_igemm")
     _count()
     return out
@@ -224,6 +236,13 @@ def layernorm(x, gamma, beta, out, eps=1e-5):
     c = x.shape[-1]
     _check(lib().sw_layernorm(_ptr(x), _ptr(out), _ptr(gamma), _ptr(beta), x.numel() // c, c, eps, _stream()),
            "sw_layernorm")
+    _count()
+    return out
+
+
+def softmax_rows(x, out, scale=1.0):
+    cols = x.shape[-1]
+    _check(lib().sw_softmax_rows(_ptr(x), _ptr(out), x.numel() // cols, cols, scale, _stream()), "sw_softmax_rows")
     _count()
     return out
 

@@ -345,6 +345,9 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     if (p->n <= 0 || p->h <= 0 || p->w <= 0 || p->kh <= 0 || p->kw <= 0)
         return swh::fail(-1, "sw_igemm: bad shape");
     if (p->gn_stats) return swh::fail(-1, "sw_igemm: gn_stats epilogue not available in this build");
+    if (p->bf16) return swh::fail(-1, "sw_igemm: bf16 operands not enabled in this build (fp16 only)");
+    if ((p->a_ld && (p->a_ld % 8 || p->a_ld < p->c1)) || (p->w_ld % 8))
+        return swh::fail(-1, "sw_igemm: a_ld/w_ld must be multiples of 8 (a_ld >= c1)");
     if (p->ldc % 8 || (p->residual && p->ldr % 8) || (p->row_bias && p->row_bias_ld % 8))
         return swh::fail(-1, "sw_igemm: leading dimensions must be multiples of 8");
 
@@ -400,9 +403,9 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
 
     CUtensorMap tA1, tA2, tB;
     {
+        const uint64_t lda = p->a_ld > 0 ? uint64_t(p->a_ld) : uint64_t(p->c1);
         const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
-        const uint64_t str[3] = {uint64_t(p->c1) * 2, uint64_t(p->w) * p->c1 * 2,
-                                 uint64_t(p->h) * p->w * p->c1 * 2};
+        const uint64_t str[3] = {lda * 2, uint64_t(p->w) * lda * 2, uint64_t(p->h) * p->w * lda * 2};
         const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
         int rc = swh::encode_tmap_f16(&tA1, p->a1, 4, dims, str, box);
         if (rc) return rc;
@@ -419,7 +422,7 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     }
     {
         const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout)};
-        const uint64_t str[1] = {uint64_t(ktotal) * 2};
+        const uint64_t str[1] = {(p->w_ld > 0 ? uint64_t(p->w_ld) : uint64_t(ktotal)) * 2};
         const uint32_t box[2] = {64, uint32_t(bn)};
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
         if (rc) return rc;

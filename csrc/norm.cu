@@ -194,6 +194,61 @@ __global__ void k_layernorm(const __half* __restrict__ x, __half* __restrict__ y
     }
 }
 
+// ---- row softmax (VAE mid-block attention: one head of dim 512, scores materialised by a GEMM)
+__global__ void k_softmax_rows(const __half* __restrict__ x, __half* __restrict__ y, int cols,
+                               float scale) {
+    __shared__ float red[32];
+    const __half* xr = x + size_t(blockIdx.x) * cols;
+    __half* yr = y + size_t(blockIdx.x) * cols;
+    const int octs = cols >> 3;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    float mx = -INFINITY;
+    for (int o = threadIdx.x; o < octs; o += blockDim.x) {
+        const uint4 u = *reinterpret_cast<const uint4*>(xr + o * 8);
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_h2(w[j]);
+            mx = fmaxf(mx, fmaxf(f.x, f.y));
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) red[wid] = mx;
+    __syncthreads();
+    mx = red[0];
+    for (int i = 1; i < nw; ++i) mx = fmaxf(mx, red[i]);
+    __syncthreads();
+    float sum = 0.0f;
+    for (int o = threadIdx.x; o < octs; o += blockDim.x) {
+        const uint4 u = *reinterpret_cast<const uint4*>(xr + o * 8);
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_h2(w[j]);
+            sum += __expf((f.x - mx) * scale) + __expf((f.y - mx) * scale);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) red[wid] = sum;
+    __syncthreads();
+    sum = 0.0f;
+    for (int i = 0; i < nw; ++i) sum += red[i];
+    const float inv = 1.0f / sum;
+    for (int o = threadIdx.x; o < octs; o += blockDim.x) {
+        const uint4 u = *reinterpret_cast<const uint4*>(xr + o * 8);
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+        uint32_t out[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_h2(w[j]);
+            out[j] = pack_h2(__expf((f.x - mx) * scale) * inv, __expf((f.y - mx) * scale) * inv);
+        }
+        *reinterpret_cast<uint4*>(yr + o * 8) = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+}
+
 }  // namespace
 
 // Shared by the public entry point; `stats` must already be usable device memory.
@@ -256,6 +311,15 @@ extern "C" int sw_layernorm(const void* x, void* y, const void* gamma, const voi
         k_layernorm<5><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
     else
         k_layernorm<8><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_softmax_rows(const void* x, void* y, int rows, int cols, float scale, void* stream) {
+    if (!x || !y) return swh::fail(-1, "sw_softmax_rows: null argument");
+    if (cols % 8) return swh::fail(-1, "sw_softmax_rows: cols=%d not a multiple of 8", cols);
+    k_softmax_rows<<<rows, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __half*>(x), static_cast<__half*>(y), cols, scale);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -59,6 +59,8 @@ typedef struct {
     int32_t tile_n;      /* 0 = auto, else 64 or 128 */
     float* gn_stats;     /* optional fp32 [n, gn_groups, 2]: += (sum, sumsq) of the stored output */
     int32_t gn_groups;
+    int32_t a_ld;        /* elements between consecutive pixels of a1 (0 = c1): strided-view operand */
+    int32_t w_ld;        /* elements between consecutive weight rows (0 = kh*kw*(c1+c2)) */
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);
@@ -96,6 +98,10 @@ int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma,
 /* LayerNorm over the last dim of fp16 [rows, c] (K7). */
 int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows, int c,
                  float eps, void* stream);
+
+/* Row softmax of fp16 [rows, cols]: y = softmax(x * scale) (K10: the VAE mid-block attention has
+ * one 512-wide head, so its scores are materialised by sw_igemm and normalised here). */
+int sw_softmax_rows(const void* x, void* y, int rows, int cols, float scale, void* stream);
 
 /* Nearest-neighbour 2x upsample, channels-last fp16 (K8). */
 int sw_upsample2x_nhwc(const void* x, void* y, int n, int h, int w, int c, void* stream);

@@ -1,0 +1,104 @@
+"""Scheduler coefficient tables against independent fp64 restatements of the formulas
+(SURVEY.md appendix A.1-A.4)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from chiaswarm_b200.ops import schedulers as S
+
+
+def _run_table(plan, x, eps_fn, noise=None):
+    x = torch.tensor(x, dtype=torch.float64)
+    x0_prev = None
+    for i in range(plan.num_steps):
+        out = torch.tensor(eps_fn(x.numpy(), i), dtype=torch.float64)
+        e0, e1, c0, c1, c2, c3, s_in, _ = (float(v) for v in plan.coef[i].astype(np.float64))
+        x0 = e0 * x + e1 * out
+        xn = c0 * x + c1 * x0
+        if c2:
+            xn = xn + c2 * x0_prev
+        if c3:
+            xn = xn + c3 * torch.tensor(noise[i])
+        x, x0_prev = xn, x0
+    return x.numpy()
+
+
+@pytest.mark.parametrize("steps", [2, 10, 30, 50])
+@pytest.mark.parametrize("pred", ["epsilon", "v_prediction"])
+def test_dpmpp_2m_table_matches_formulas(steps, pred):
+    plan = S.make_plan("dpmpp_2m", steps, {"prediction_type": pred}, use_karras_sigmas=True)
+    assert plan.coef.shape == (steps, 8) and np.isfinite(plan.coef).all()
+    assert plan.sigmas[-1] == 0 and np.all(np.diff(plan.sigmas) < 0)
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(16)
+    w = rng.standard_normal(16)
+    eps_fn = lambda xx, i: 0.3 * xx + 0.1 * w * math.cos(i)
+    got = _run_table(plan, x, eps_fn)
+    ref = S.reference_dpmpp_2m(plan, x, eps_fn)
+    assert np.allclose(got, ref, rtol=2e-4, atol=2e-4)
+
+
+def test_karras_sigmas_and_timesteps():
+    plan = S.make_plan("dpmpp_2m", 50, None, True)
+    acp = plan.alphas_cumprod
+    smax, smin = math.sqrt((1 - acp[-1]) / acp[-1]), math.sqrt((1 - acp[0]) / acp[0])
+    assert plan.sigmas[0] == pytest.approx(smax) and plan.sigmas[-2] == pytest.approx(smin)
+    rho = 7.0
+    i = 17
+    expect = (smax ** (1 / rho) + i / 49 * (smin ** (1 / rho) - smax ** (1 / rho))) ** rho
+    assert plan.sigmas[i] == pytest.approx(expect)
+    assert plan.timesteps[0] == 999 and plan.timesteps[-1] <= 1 and np.all(np.diff(plan.timesteps) <= 0)
+
+
+def test_euler_and_ancestral_rows():
+    plan = S.make_plan("euler", 8, None, True)
+    s, sn = plan.sigmas[3], plan.sigmas[4]
+    x, eps = 0.7, -0.2
+    x0 = x - s * eps
+    d = (x - x0) / s
+    e0, e1, c0, c1, *_ = plan.coef[3]
+    got = c0 * x + c1 * (e0 * x + e1 * eps)
+    assert got == pytest.approx(x + d * (sn - s), rel=1e-5)
+    assert plan.init_noise_sigma == pytest.approx(plan.sigmas[0])
+    assert plan.first_scale == pytest.approx(1 / math.sqrt(plan.sigmas[0] ** 2 + 1))
+    assert plan.coef[3][6] == pytest.approx(1 / math.sqrt(sn * sn + 1), rel=1e-6)
+
+    pa = S.make_plan("euler_a", 8, None, True)
+    assert pa.needs_noise
+    up = math.sqrt(sn ** 2 * (s ** 2 - sn ** 2) / s ** 2)
+    down = math.sqrt(sn ** 2 - up ** 2)
+    e0, e1, c0, c1, c2, c3, *_ = pa.coef[3]
+    nz = 0.4
+    got = c0 * x + c1 * (e0 * x + e1 * eps) + c3 * nz
+    assert got == pytest.approx(x + d * (down - s) + up * nz, rel=1e-5)
+    assert pa.coef[-1][5] == 0  # last step lands on sigma 0: no noise
+
+
+def test_ddim_rows_and_guidance():
+    plan = S.make_plan("ddim", 10, None, False)
+    acp = plan.alphas_cumprod
+    t = int(plan.timesteps[2])
+    prev = t - 100
+    x, eps = 0.3, 0.9
+    x0 = (x - math.sqrt(1 - acp[t]) * eps) / math.sqrt(acp[t])
+    expect = math.sqrt(acp[prev]) * x0 + math.sqrt(1 - acp[prev]) * eps
+    e0, e1, c0, c1, *_ = plan.coef[2].astype(np.float64)
+    assert c0 * x + c1 * (e0 * x + e1 * eps) == pytest.approx(expect, rel=1e-5)
+
+    out = torch.tensor([[1.0], [3.0]])
+    assert S.guided(out, 2, 7.5).item() == pytest.approx(1 + 7.5 * 2)
+    out3 = torch.tensor([[5.0], [2.0], [1.0]])  # [text+img, img, uncond]
+    assert S.guided(out3, 3, 7.5, 1.5).item() == pytest.approx(1 + 7.5 * (5 - 2) + 1.5 * (2 - 1))
+
+
+def test_img2img_slice_restarts_first_order():
+    plan = S.make_plan("dpmpp_2m", 20, None, True)
+    sl = plan.slice_from(8)
+    assert sl.num_steps == 12 and sl.coef[0][4] == 0 and plan.coef[8][4] != 0
+    x0 = torch.ones(4)
+    nz = torch.full((4,), 2.0)
+    s = plan.sigmas[8]
+    a = 1 / math.sqrt(s * s + 1)
+    assert torch.allclose(sl.add_noise(x0, nz, 0), a * x0 + s * a * nz)
