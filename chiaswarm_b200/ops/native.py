@@ -101,6 +101,8 @@ def lib() -> C.CDLL:
             l.sw_groupnorm_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                             C.c_int, C.c_void_p, C.c_void_p]
+            l.sw_groupnorm_scratch_floats.restype = C.c_int64
+            l.sw_groupnorm_scratch_floats.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
             l.sw_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                        C.c_float, C.c_void_p]
             l.sw_softmax_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p]
@@ -223,12 +225,19 @@ def flash_attn(q, k, v, out, *, batch, heads, seq_q, seq_kv, head_dim, scale=Non
     return out
 
 
+def groupnorm_scratch_floats(n, hw, c, groups) -> int:
+    return int(lib().sw_groupnorm_scratch_floats(n, hw, c, groups))
+
+
 def groupnorm(x, gamma, beta, out, *, n, hw, groups, eps, silu, stats, x2=None):
     c1 = x.shape[-1]
     c2 = 0 if x2 is None else x2.shape[-1]
+    need = groupnorm_scratch_floats(n, hw, c1 + c2, groups)
+    if stats.numel() < need:
+        raise ValueError(f"groupnorm scratch too small: {stats.numel()} < {need} floats")
     _check(lib().sw_groupnorm_nhwc(_ptr(x), _ptr(x2), _ptr(out), _ptr(gamma), _ptr(beta), n, hw, c1, c2,
                                    groups, eps, int(silu), _ptr(stats), _stream()), "sw_groupnorm_nhwc")
-    _count(3)
+    _count(2)
     return out
 
 

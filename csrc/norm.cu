@@ -9,26 +9,32 @@ namespace {
 
 using namespace sw;
 
-// ---- GroupNorm statistics: grid (chunks, n). Thread <-> fixed channel octet, strided rows.
+// ---- GroupNorm statistics, deterministic: grid (chunks, n).  Thread <-> fixed channel octet,
+// strided rows.  No floating-point atomics anywhere: per-thread sums go to shared memory, are
+// combined in a fixed order into per-(chunk, group) partials, and the last CTA of each image
+// (ticket counter) folds the partials -- again in a fixed order -- into final[n][group][2].
 // The input may be the channel-concatenation of two tensors (UNet skip connections): octets below
 // c1 come from x1, the rest from x2.
+// scratch layout (floats): final[n*groups*2] | tickets[n] (as uint) | partial[n][chunks][groups][2]
 __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1,
-                           float* __restrict__ stats, int hw, int c, int groups, int rows_per_cta,
+                           float* __restrict__ scratch, int hw, int c, int groups, int rows_per_cta,
                            int rows_per_pass) {
-    extern __shared__ float sh[];  // [groups][2]
+    extern __shared__ float sh[];  // [rows_per_pass][c][2] then [c][2]
+    __shared__ bool is_last;
     const int octs = c >> 3;
-    const int n = blockIdx.y;
+    const int n = blockIdx.y, nimg = gridDim.y, chunks = gridDim.x;
     const int r0 = blockIdx.x * rows_per_cta;
     const int r1 = min(hw, r0 + rows_per_cta);
     const int oct = threadIdx.x % octs;
     const int rp = threadIdx.x / octs;
-    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) sh[i] = 0.0f;
-    __syncthreads();
+    float* fin = scratch;
+    unsigned int* tickets = reinterpret_cast<unsigned int*>(scratch + size_t(nimg) * groups * 2);
+    float* partial = scratch + size_t(nimg) * groups * 2 + nimg;
 
-    float s[8], ss[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
     if (rp < rows_per_pass) {
+        float s[8], ss[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
         const bool first = oct * 8 < c1;
         const int cs = first ? c1 : c - c1;
         const __half* base =
@@ -45,27 +51,67 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
                 ss[2 * j + 1] += f.y * f.y;
             }
         }
-        const int cg = c / groups;
-        int g_prev = (oct * 8) / cg;
-        float as = 0.0f, ass = 0.0f;
+        float* dst = sh + (size_t(rp) * c + oct * 8) * 2;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const int g = (oct * 8 + i) / cg;
-            if (g != g_prev) {
-                atomicAdd(&sh[g_prev * 2], as);
-                atomicAdd(&sh[g_prev * 2 + 1], ass);
-                as = ass = 0.0f;
-                g_prev = g;
-            }
-            as += s[i];
-            ass += ss[i];
+            dst[2 * i] = s[i];
+            dst[2 * i + 1] = ss[i];
         }
-        atomicAdd(&sh[g_prev * 2], as);
-        atomicAdd(&sh[g_prev * 2 + 1], ass);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < groups * 2; i += blockDim.x)
-        atomicAdd(&stats[size_t(n) * groups * 2 + i], sh[i]);
+    // per-channel totals over the row passes (fixed order)
+    float* chs = sh + size_t(rows_per_pass) * c * 2;
+    for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {
+        float a = 0.0f, b = 0.0f;
+        for (int k = 0; k < rows_per_pass; ++k) {
+            a += sh[(size_t(k) * c + ch) * 2];
+            b += sh[(size_t(k) * c + ch) * 2 + 1];
+        }
+        chs[2 * ch] = a;
+        chs[2 * ch + 1] = b;
+    }
+    __syncthreads();
+    const int cg = c / groups;
+    float* my_partial = partial + (size_t(n) * chunks + blockIdx.x) * groups * 2;
+    for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+        float a = 0.0f, b = 0.0f;
+        for (int k = 0; k < cg; ++k) {
+            a += chs[2 * (g * cg + k)];
+            b += chs[2 * (g * cg + k) + 1];
+        }
+        my_partial[2 * g] = a;
+        my_partial[2 * g + 1] = b;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(&tickets[n], 1u);
+        is_last = (t == unsigned(chunks) - 1u);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // last CTA of this image: fold the partials, one warp per group, lanes over chunks,
+    // then a fixed shuffle tree.
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const float* pimg = partial + size_t(n) * chunks * groups * 2;
+    for (int g = wid; g < groups; g += nw) {
+        float a = 0.0f, b = 0.0f;
+        for (int k = lane; k < chunks; k += 32) {
+            a += __ldcg(pimg + (size_t(k) * groups + g) * 2);
+            b += __ldcg(pimg + (size_t(k) * groups + g) * 2 + 1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if (lane == 0) {
+            fin[(size_t(n) * groups + g) * 2] = a;
+            fin[(size_t(n) * groups + g) * 2 + 1] = b;
+        }
+    }
+    if (threadIdx.x == 0) tickets[n] = 0u;  // leave the scratch ready for the next call
 }
 
 // ---- GroupNorm apply: y = silu?((x-mean)*rstd*gamma+beta)
@@ -251,36 +297,56 @@ __global__ void k_softmax_rows(const __half* __restrict__ x, __half* __restrict_
 
 }  // namespace
 
-// Shared by the public entry point; `stats` must already be usable device memory.
+// Launch geometry shared by the statistics and apply kernels.
+struct GnGeom {
+    int rows_per_pass, threads, rows_per_cta, chunks;
+};
+static GnGeom gn_geom(int hw, int c) {
+    GnGeom g;
+    const int octs = c / 8;
+    g.rows_per_pass = 256 / octs;
+    if (g.rows_per_pass < 1) g.rows_per_pass = 1;
+    g.threads = (octs * g.rows_per_pass + 31) / 32 * 32;
+    // ~32 KB of activations per CTA, but never more than 256 CTAs per image
+    int rpc = (32768 / (c * 2)) / g.rows_per_pass * g.rows_per_pass;
+    if (rpc < g.rows_per_pass) rpc = g.rows_per_pass;
+    const int min_rpc = ((hw + 255) / 256 + g.rows_per_pass - 1) / g.rows_per_pass * g.rows_per_pass;
+    if (rpc < min_rpc) rpc = min_rpc;
+    g.rows_per_cta = rpc;
+    g.chunks = (hw + rpc - 1) / rpc;
+    return g;
+}
+
+extern "C" int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups) {
+    if (c <= 0 || c % 8 || hw <= 0 || n <= 0 || groups <= 0) return -1;
+    const GnGeom g = gn_geom(hw, c);
+    return int64_t(n) * groups * 2 + n + int64_t(n) * g.chunks * groups * 2;
+}
+
+// Shared by the public entry points; `scratch` must already be usable device memory of at least
+// sw_groupnorm_scratch_floats() floats.
 int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
-                        int n, int hw, int c1, int c2, int groups, float eps, int silu, float* stats,
-                        cudaStream_t st) {
+                        int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                        float* scratch, cudaStream_t st) {
     const int c = c1 + c2;
     if (c1 <= 0 || c2 < 0 || c1 % 8 || (c2 > 0 && !x2))
         return swh::fail(-1, "sw_groupnorm_nhwc: bad channel split c1=%d c2=%d", c1, c2);
     if (c % 8 || groups <= 0 || c % groups)
         return swh::fail(-1, "sw_groupnorm_nhwc: c=%d groups=%d unsupported", c, groups);
-    const int octs = c / 8;
-    if (octs > 1024) return swh::fail(-1, "sw_groupnorm_nhwc: c=%d too wide", c);
-    int rows_per_pass = 256 / octs;
-    if (rows_per_pass < 1) rows_per_pass = 1;
-    int threads = octs * rows_per_pass;
-    threads = (threads + 31) / 32 * 32;
-    // ~32 KB of activations per CTA
-    int rows_per_cta = (32768 / (c * 2)) / rows_per_pass * rows_per_pass;
-    if (rows_per_cta < rows_per_pass) rows_per_cta = rows_per_pass;
-    const int chunks = (hw + rows_per_cta - 1) / rows_per_cta;
-    SW_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(float) * size_t(n) * groups * 2, st));
-    dim3 grid(chunks, n);
-    k_gn_stats<<<grid, threads, groups * 2 * sizeof(float), st>>>(
-        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, stats, hw, c, groups,
-        rows_per_cta, rows_per_pass);
+    if (c / 8 > 1024) return swh::fail(-1, "sw_groupnorm_nhwc: c=%d too wide", c);
+    const GnGeom g = gn_geom(hw, c);
+    // only the ticket counters have to start at zero
+    SW_CUDA_OK(cudaMemsetAsync(scratch + size_t(n) * groups * 2, 0, sizeof(float) * size_t(n), st));
+    dim3 grid(g.chunks, n);
+    const size_t smem_stats = (size_t(g.rows_per_pass) * c * 2 + size_t(c) * 2) * sizeof(float);
+    k_gn_stats<<<grid, g.threads, smem_stats, st>>>(
+        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, scratch, hw, c, groups,
+        g.rows_per_cta, g.rows_per_pass);
     SW_CUDA_OK(cudaGetLastError());
-    k_gn_apply<<<grid, threads, 2 * c * sizeof(float), st>>>(
+    k_gn_apply<<<grid, g.threads, 2 * c * sizeof(float), st>>>(
         static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, static_cast<__half*>(y),
-        static_cast<const __half*>(gamma),
-        static_cast<const __half*>(beta), stats, hw, c, groups, eps, silu, rows_per_cta,
-        rows_per_pass);
+        static_cast<const __half*>(gamma), static_cast<const __half*>(beta), scratch, hw, c, groups,
+        eps, silu, g.rows_per_cta, g.rows_per_pass);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }

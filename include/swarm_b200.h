@@ -88,9 +88,12 @@ int sw_flash_attn(const sw_attn_params* p, void* stream);
  * reference call site swarm/diffusion/diffusion_func.py:96).
  * The input is the channel-concatenation of x [n,hw,c1] and x2 [n,hw,c2] (x2 may be NULL with
  * c2 = 0): the UNet skip-concat is normalised without being materialised.  y: [n,hw,c1+c2];
- * gamma/beta fp16 [c1+c2].  A statistics kernel accumulates per-(image, group) sum and
- * sum-of-squares into `stats_scratch` (fp32 [n, groups, 2], caller-owned, zeroed by the call
- * itself), then an apply kernel normalises; both stream an L2-resident tensor once. */
+ * gamma/beta fp16 [c1+c2].  A statistics kernel writes per-CTA partial sums to `stats_scratch`
+ * and the last CTA of each image folds them in a fixed order (bit-reproducible: no floating-point
+ * atomics); an apply kernel normalises.  Both stream an L2-resident tensor once.
+ * `stats_scratch` is caller-owned fp32 memory of sw_groupnorm_scratch_floats(n,hw,c,groups)
+ * floats; its contents need no initialisation. */
+int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups);
 int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                       int n, int hw, int c1, int c2, int groups, float eps, int silu,
                       float* stats_scratch, void* stream);
