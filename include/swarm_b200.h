@@ -98,6 +98,29 @@ int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma,
                       int n, int hw, int c1, int c2, int groups, float eps, int silu,
                       float* stats_scratch, void* stream);
 
+/* Same operation as sw_groupnorm_nhwc for callers that cannot allocate device memory (this entry
+ * point has no counterpart in the reference, which has no native code).  Who needs it: a host
+ * process that committed all of its device memory to its own arena at start-up and has nothing
+ * left to carve a scratch buffer from, or a caller on a latency-critical path that may not call
+ * cudaMalloc/cudaFree because they can stall the whole device.  The statistics scratch is a
+ * fixed array of SW_GN_STATIC_MAX_FLOATS floats (1 MiB) compiled into the library; every GPU
+ * that loads the library keeps its copy until the process exits.  The call itself performs no
+ * allocation of any kind.
+ *  - Limit: sw_groupnorm_scratch_floats(n, hw, c1+c2, groups) must not exceed
+ *    SW_GN_STATIC_MAX_FLOATS, otherwise the call fails with a message saying so (for 32 groups
+ *    that is up to 15 images per call at any resolution).
+ *  - The first call on each device looks up the array's device address (a one-time, per-device
+ *    set-up done with that device current); make that first call before starting any stream
+ *    capture on the thread.
+ *  - All calls on a device share the one array, which still holds the previous call's values;
+ *    the call clears the few counters that must start at zero itself.  Two calls whose kernels
+ *    can overlap on the GPU (different streams without an ordering between them) race on it:
+ *    keep them on one stream or order them with events. */
+#define SW_GN_STATIC_MAX_FLOATS (256 * 1024)
+int sw_groupnorm_nhwc_static(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                             int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                             void* stream);
+
 /* LayerNorm over the last dim of fp16 [rows, c] (K7). */
 int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows, int c,
                  float eps, void* stream);
