@@ -52,6 +52,8 @@ class Recorder:
         self._free = {}
         self.bytes_allocated = 0
         self.gn_stats = torch.zeros(1 << 20, dtype=torch.float32, device=self.device)  # GroupNorm scratch
+        # split-K scratch (tickets + fp32 partial tiles), zeroed once; shared by every GEMM of the plan
+        self.splitk = torch.zeros((64 << 20) + 16384, dtype=torch.uint8, device=self.device)
 
     # ---- buffers (explicit liveness: release() makes a buffer reusable by later ops)
     def buf(self, *shape, dtype=torch.float16):
@@ -107,7 +109,8 @@ class Conv:
             o = out or rec.fm(x.n, x.h, x.w, self.cout)
             rec.add(nat.igemm, x.t, self.wgt, o.t.view(-1, o.c), n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, pad=self.pad,
                     a2=None if x2 is None else x2.t, bias=self.bias, row_bias=row_bias,
-                    residual=None if residual is None else residual.tokens(), act=act, out_scale=out_scale)
+                    residual=None if residual is None else residual.tokens(), act=act, out_scale=out_scale,
+                    splitk_scratch=rec.splitk)
             return o
         assert x2 is None and self.stride == 2
         if self.asym:  # VAE encoder: pad (0,1,0,1) then valid conv
@@ -122,7 +125,7 @@ class Conv:
         o = out or rec.fm(x.n, oh, ow, self.cout)
         rec.add(nat.igemm, cols.view(-1, cols.shape[-1]), self.wgt, o.t.view(-1, o.c), n=1, h=1, w=x.n * oh * ow,
                 bias=self.bias, row_bias=None, residual=None if residual is None else residual.tokens(), act=act,
-                out_scale=out_scale)
+                out_scale=out_scale, splitk_scratch=rec.splitk)
         rec.release(cols)
         return o
 
@@ -149,7 +152,7 @@ class Linear:
         rows = x.shape[0]
         o = out if out is not None else rec.buf(rows, self.nout)
         rec.add(nat.igemm, x, self.wgt, o, n=1, h=1, w=rows, bias=self.bias, residual=residual,
-                act=nat.ACT_GEGLU if self.geglu else act, out_scale=out_scale)
+                act=nat.ACT_GEGLU if self.geglu else act, out_scale=out_scale, splitk_scratch=rec.splitk)
         return o
 
 
@@ -205,7 +208,7 @@ class Resnet:
         if self.shortcut is not None:
             sc = rec.fm(x.n, x.h, x.w, self.conv2.cout)
             rec.add(nat.igemm, x.t, self.shortcut.wgt, sc.tokens(), n=x.n, h=x.h, w=x.w, kh=1, kw=1, pad=0,
-                    a2=None if skip is None else skip.t, bias=self.shortcut.bias)
+                    a2=None if skip is None else skip.t, bias=self.shortcut.bias, splitk_scratch=rec.splitk)
             res = sc
         else:
             assert skip is None

@@ -47,6 +47,8 @@ class IGemmParams(C.Structure):
         ("gn_groups", C.c_int32),
         ("a_ld", C.c_int32),
         ("w_ld", C.c_int32),
+        ("splitk_scratch", C.c_void_p),
+        ("splitk_scratch_bytes", C.c_int64),
     ]
 
 
@@ -151,7 +153,7 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 
 # --------------------------------------------------------------------------------------- ops
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
-          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0):
+          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -189,6 +191,9 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.gn_groups = 0
     p.a_ld = a_ld
     p.w_ld = w_ld
+    if splitk_scratch is not None:
+        p.splitk_scratch = splitk_scratch.data_ptr()
+        p.splitk_scratch_bytes = splitk_scratch.numel() * splitk_scratch.element_size()
     _check(lib().sw_igemm(C.byref(p), _stream()), "sw_igemm")
     _count()
     return out

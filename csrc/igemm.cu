@@ -42,15 +42,33 @@ struct IGemmArgs {
     int act;
     float out_scale;
     int bf16;
+    int bn;             // N tile (multiple of 32, <= 256)
+    int tmem_cols;      // power of two >= bn
+    int splits;         // split-K factor (grid.z)
+    int kb_per_split;   // k-blocks per split
+    unsigned int* tickets;  // [tiles] arrival counters (split-K), self-resetting
+    float* partials;        // [tile][split][bn/32][128][32] fp32
 };
 
-template <int BN>
+__device__ __forceinline__ void tmem_alloc_rt(uint32_t* slot, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(slot)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_rt(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+                 : "memory");
+}
+
 __global__ void __launch_bounds__(kThreads)
     k_igemm(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
             const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
-    constexpr int B_STAGE_BYTES = BN * BK * 2;
-    constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+    const int BN = p.bn;
+    const int B_STAGE_BYTES = BN * BK * 2;
+    const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    __shared__ int s_is_last;
 
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B operands need 1024-byte aligned stage bases.
@@ -90,7 +108,7 @@ __global__ void __launch_bounds__(kThreads)
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc<TMEM_COLS>(tmem_slot);
+        tmem_alloc_rt(tmem_slot, uint32_t(p.tmem_cols));
     }
     tc_fence_before();
     __syncthreads();
@@ -101,14 +119,16 @@ __global__ void __launch_bounds__(kThreads)
     const int nkb2 = (p.c2 + BK - 1) / BK;
     const int per_tap = nkb1 + nkb2;
     const int ctot = p.c1 + p.c2;
-    const int total = p.kh * p.kw * per_tap;
+    const int total_all = p.kh * p.kw * per_tap;
+    const int it_begin = blockIdx.z * p.kb_per_split;
+    const int it_end = min(total_all, it_begin + p.kb_per_split);
     const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
 
     if (warp == 0) {
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0;
-            for (int it = 0; it < total; ++it) {
+            for (int it = it_begin; it < it_end; ++it) {
                 mbar_wait(&empty[s], ph ^ 1);
                 const int tap = it / per_tap;
                 const int j = it - tap * per_tap;
@@ -137,7 +157,7 @@ __global__ void __launch_bounds__(kThreads)
             int s = 0;
             uint32_t ph = 0;
             uint32_t acc = 0;
-            for (int it = 0; it < total; ++it) {
+            for (int it = it_begin; it < it_end; ++it) {
                 mbar_wait(&full[s], ph);
                 tc_fence_after();
                 const int j = it % per_tap;
@@ -176,9 +196,72 @@ __global__ void __launch_bounds__(kThreads)
         tc_fence_after();
         const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
 
-        if (p.act == SW_ACT_GEGLU) {
+        // ---- split-K: every split parks its fp32 tile in scratch; the split that arrives last
+        // (ticket counter) sums all of them in split order -- a fixed order, so the result does
+        // not depend on which CTA happened to finish last -- and runs the epilogue.
+        const float* my_partials = nullptr;
+        if (p.splits > 1) {
+            const int tile_id = blockIdx.x * gridDim.y + blockIdx.y;
+            const int nchunk = BN / 32;
+            float* tile_base = p.partials + size_t(tile_id) * p.splits * nchunk * 4096;
+            float* mine = tile_base + size_t(blockIdx.z) * nchunk * 4096 + r * 32;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(trow + c, v);
+                tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(mine + (c / 32) * 4096);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) {
+                const unsigned int t = atomicAdd(&p.tickets[tile_id], 1u);
+                const int last = (t == unsigned(p.splits) - 1u);
+                if (last) p.tickets[tile_id] = 0u;  // ready for the next launch
+                s_is_last = last;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (s_is_last) {
+                __threadfence();
+                my_partials = tile_base + r * 32;
+            }
+        }
+        const bool do_epilogue = (p.splits == 1) || (my_partials != nullptr);
+        auto load_chunk = [&](int c, uint32_t (&v)[32]) {
+            if (my_partials == nullptr) {
+                tmem_ld32(trow + c, v);
+                tmem_ld_wait();
+            } else {
+                const int nchunk = BN / 32;
+                float acc[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
+                for (int z = 0; z < p.splits; ++z) {
+                    const float4* src = reinterpret_cast<const float4*>(
+                        my_partials + (size_t(z) * nchunk + c / 32) * 4096);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 f = __ldcg(src + j);
+                        acc[4 * j] += f.x;
+                        acc[4 * j + 1] += f.y;
+                        acc[4 * j + 2] += f.z;
+                        acc[4 * j + 3] += f.w;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
+            }
+        };
+
+        if (!do_epilogue) {
+            // another split owns the epilogue of this tile
+        } else if (p.act == SW_ACT_GEGLU) {
             // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates
-            constexpr int HALF = BN / 2;
+            const int HALF = BN / 2;
             const int ocol0 = blockIdx.y * HALF;
             const int ncols_out = p.cout / 2;
 #pragma unroll 1
@@ -210,8 +293,7 @@ __global__ void __launch_bounds__(kThreads)
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t v[32];
-                tmem_ld32(trow + c, v);
-                tmem_ld_wait();
+                load_chunk(c, v);
                 if (!row_ok) continue;
 #pragma unroll
                 for (int g8 = 0; g8 < 4; ++g8) {
@@ -275,7 +357,7 @@ __global__ void __launch_bounds__(kThreads)
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<TMEM_COLS>(tmem_acc);
+        tmem_dealloc_rt(tmem_acc, uint32_t(p.tmem_cols));
     }
 }
 
@@ -313,26 +395,24 @@ void pick_box(int n, int h, int w, int* bw, int* bh, int* bi) {
     *bi = b2;
 }
 
-template <int BN>
-int launch(const sw_igemm_params* p, const IGemmArgs& a, const CUtensorMap& tA1,
-           const CUtensorMap& tA2, const CUtensorMap& tB, int grid_x, cudaStream_t st) {
-    constexpr int STAGE_BYTES = A_STAGE_BYTES + BN * BK * 2;
-    const int smem = a.stages * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
-    static int configured_smem[64] = {0};
+int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB,
+           int grid_x, cudaStream_t st) {
+    const int stage_bytes = A_STAGE_BYTES + a.bn * BK * 2;
+    const int smem = a.stages * stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
+    static bool configured[64] = {false};
     int dev = 0;
     SW_CUDA_OK(cudaGetDevice(&dev));
-    if (dev < 64 && configured_smem[dev] < smem) {
-        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        200 * 1024));
-        configured_smem[dev] = 200 * 1024;
+    if (dev < 64 && !configured[dev]) {
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        configured[dev] = true;
     }
-    const int ncols = a.cout;
-    dim3 grid(grid_x, (ncols + BN - 1) / BN);
-    k_igemm<BN><<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
+    dim3 grid(grid_x, (a.cout + a.bn - 1) / a.bn, a.splits);
+    k_igemm<<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
     SW_CUDA_OK(cudaGetLastError());
-    (void)p;
     return 0;
 }
+
+constexpr int kMaxSplitTiles = 4096;
 
 }  // namespace
 
@@ -378,28 +458,60 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     a.out_scale = p->out_scale == 0.0f ? 1.0f : p->out_scale;
     a.bf16 = p->bf16;
 
-    // Tile width: 128 unless that leaves most SMs idle or the layer is narrow.
+    const int ktotal = p->kh * p->kw * (p->c1 + p->c2);
+    const int kblocks = p->kh * p->kw * ((p->c1 + 63) / 64 + (p->c2 + 63) / 64);
+    const int sms = swh::sm_count();
+
+    // ---- N tile.  The kernel is bound by L2 -> SM operand traffic, so wide tiles win: the
+    // activation tile (re-read once per filter tap) is amortised over more output channels.
+    // Layers with few pixel tiles are weight-streaming bound instead and want many CTAs.
     int bn = p->tile_n;
-    if (bn == 0) {
-        bn = 128;
-        if (p->cout <= 64) bn = 64;
-        else if (p->act != SW_ACT_GEGLU) {
-            const long ctas128 = long(grid_x) * ((p->cout + 127) / 128);
-            if (ctas128 < 2L * swh::sm_count()) bn = 64;
-        }
-    }
     if (p->act == SW_ACT_GEGLU) {
         bn = 128;
         if (p->cout % 128) return swh::fail(-1, "sw_igemm: GEGLU needs cout %% 128 == 0");
+    } else if (bn == 0) {
+        if (grid_x <= 4) {
+            bn = p->cout <= 32 ? 32 : 64;
+        } else {
+            const int ntiles = (p->cout + 255) / 256;
+            bn = ((p->cout + ntiles - 1) / ntiles + 31) / 32 * 32;
+        }
     }
-    if (bn != 64 && bn != 128) return swh::fail(-1, "sw_igemm: tile_n must be 64 or 128");
+    if (bn < 32 || bn > 256 || bn % 32) return swh::fail(-1, "sw_igemm: tile_n=%d must be a multiple of 32 in [32,256]", bn);
+    const int tiles_ncol = (p->cout + bn - 1) / bn;
+    a.bn = bn;
+    a.tmem_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
 
-    const int ktotal = p->kh * p->kw * (p->c1 + p->c2);
-    const int kblocks = p->kh * p->kw * ((p->c1 + 63) / 64 + (p->c2 + 63) / 64);
-    int stages = bn == 128 ? 3 : 4;  // 96 KB either way: two CTAs per SM overlap epilogue and mainloop
+    // ---- pipeline depth: two CTAs per SM (epilogue of one overlaps the main loop of the other)
+    // when three stages fit in ~110 KB, else one CTA with a deeper ring.
+    const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+    int stages = (3 * stage_bytes <= 110 * 1024) ? 3 : 4;
+    if (stage_bytes <= 24 * 1024) stages = 4;
     if (kblocks < stages) stages = kblocks;
     a.stages = stages;
-    a.idesc = sw::umma_idesc(128, bn, p->bf16 ? 1 : 0, 0, 0);
+    a.idesc = sw::umma_idesc(128, bn, 0, 0, 0);
+
+    // ---- split-K: when the tile grid cannot fill the GPU and K is long, several CTAs share a
+    // tile's K range (deterministic reduction in the epilogue of the last arrival).
+    a.splits = 1;
+    a.kb_per_split = kblocks;
+    const long ctas = long(grid_x) * tiles_ncol;
+    if (p->splitk_scratch && p->act != SW_ACT_GEGLU && ctas < sms && kblocks >= 16 && ctas <= kMaxSplitTiles) {
+        int want = int((2L * sms + ctas - 1) / ctas);
+        int max_by_k = kblocks / 8;
+        int splits = want < max_by_k ? want : max_by_k;
+        if (splits > 32) splits = 32;
+        const long long per_tile = (long long)(bn / 32) * 4096 * sizeof(float);
+        const long long avail = p->splitk_scratch_bytes - (long long)kMaxSplitTiles * 4;
+        while (splits > 1 && per_tile * splits * ctas > avail) --splits;
+        if (splits > 1) {
+            a.kb_per_split = (kblocks + splits - 1) / splits;
+            a.splits = (kblocks + a.kb_per_split - 1) / a.kb_per_split;
+            a.tickets = static_cast<unsigned int*>(p->splitk_scratch);
+            a.partials = reinterpret_cast<float*>(static_cast<char*>(p->splitk_scratch) + kMaxSplitTiles * 4);
+            if (a.kb_per_split < a.stages) a.stages = a.kb_per_split;
+        }
+    }
 
     CUtensorMap tA1, tA2, tB;
     {
@@ -427,7 +539,5 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
         if (rc) return rc;
     }
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (bn == 128) return launch<128>(p, a, tA1, tA2, tB, grid_x, st);
-    return launch<64>(p, a, tA1, tA2, tB, grid_x, st);
+    return launch(a, tA1, tA2, tB, grid_x, static_cast<cudaStream_t>(stream));
 }

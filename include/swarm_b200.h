@@ -56,11 +56,15 @@ typedef struct {
     int32_t act;
     float out_scale;     /* applied after the activation, before the residual add */
     int32_t bf16;        /* 0: fp16 operands, 1: bf16 operands */
-    int32_t tile_n;      /* 0 = auto, else 64 or 128 */
+    int32_t tile_n;      /* 0 = auto, else a multiple of 32 in [32, 256] */
     float* gn_stats;     /* optional fp32 [n, gn_groups, 2]: += (sum, sumsq) of the stored output */
     int32_t gn_groups;
     int32_t a_ld;        /* elements between consecutive pixels of a1 (0 = c1): strided-view operand */
     int32_t w_ld;        /* elements between consecutive weight rows (0 = kh*kw*(c1+c2)) */
+    void* splitk_scratch;/* optional: enables split-K for layers with few output tiles.  Caller-owned,
+                            zero-filled once before first use (the kernel leaves it reusable);
+                            calls sharing one scratch must be stream-ordered. */
+    int64_t splitk_scratch_bytes;
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);

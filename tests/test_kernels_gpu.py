@@ -35,7 +35,7 @@ def test_linear(nat, m, n, k):
     assert _rel_err(out, ref) < 4e-3
 
 
-@pytest.mark.parametrize("tile_n", [64, 128])
+@pytest.mark.parametrize("tile_n", [32, 64, 128, 160, 224, 256])
 def test_linear_tiles_and_epilogues(nat, tile_n):
     torch.manual_seed(1)
     m, n, k = 512, 640, 1280
@@ -45,6 +45,38 @@ def test_linear_tiles_and_epilogues(nat, tile_n):
     res = torch.randn(m, n, device="cuda", dtype=torch.float16)
     out = nat.linear(x, w, bias=b, residual=res, act=nat.ACT_SILU, out_scale=0.5, tile_n=tile_n)
     ref = F.silu(x.float() @ w.float().t() + b.float()) * 0.5 + res.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 1280, 11520), (512, 640, 5760), (77, 320, 4096), (2048, 96, 2304)])
+def test_linear_split_k(nat, m, n, k):
+    """Few output tiles + long K: several CTAs share a tile's K range; fixed-order reduction."""
+    torch.manual_seed(12)
+    x = torch.randn(m, k, device="cuda", dtype=torch.float16)
+    w = torch.randn(n, k, device="cuda", dtype=torch.float16) * (k ** -0.5)
+    b = torch.randn(n, device="cuda", dtype=torch.float16)
+    res = torch.randn(m, n, device="cuda", dtype=torch.float16)
+    scratch = torch.zeros((64 << 20) + 16384, device="cuda", dtype=torch.uint8)
+    out = nat.linear(x, w, bias=b, residual=res, splitk_scratch=scratch)
+    ref = x.float() @ w.float().t() + b.float() + res.float()
+    assert _rel_err(out, ref) < 4e-3
+    out2 = nat.linear(x, w, bias=b, residual=res, splitk_scratch=scratch)  # scratch is left reusable
+    assert torch.equal(out, out2)
+
+
+def test_conv_split_k(nat):
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    torch.manual_seed(13)
+    n, h, w, cin, cout = 2, 8, 8, 1280, 1280
+    x = torch.randn(n, cin, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=torch.float16) * ((9 * cin) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    scratch = torch.zeros((64 << 20) + 16384, device="cuda", dtype=torch.uint8)
+    out = torch.empty(n, h, w, cout, device="cuda", dtype=torch.float16)
+    nat.igemm(x.permute(0, 2, 3, 1).contiguous(), pack_conv_weight(wt), out, n=n, h=h, w=w, kh=3, kw=3, pad=1, bias=b,
+              splitk_scratch=scratch)
+    ref = F.conv2d(x.float(), wt.float(), b.float(), padding=1).permute(0, 2, 3, 1)
     assert _rel_err(out, ref) < 4e-3
 
 
