@@ -14,6 +14,8 @@
 #include "common.cuh"
 #include "host_util.h"
 
+#include <stdlib.h>
+
 namespace {
 
 using namespace sw;
@@ -136,16 +138,16 @@ __global__ void __launch_bounds__(kThreads)
                 uint8_t* sa = smem + s * STAGE_BYTES;
                 uint8_t* sb = sa + A_STAGE_BYTES;
                 mbar_expect_tx(&full[s], a_bytes + B_STAGE_BYTES);
-                int kcol;
                 if (j < nkb1) {
                     tma_load_4d(sa, &tmA1, &full[s], j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
-                    kcol = tap * ctot + j * BK;
                 } else {
                     const int j2 = j - nkb1;
                     tma_load_4d(sa, &tmA2, &full[s], j2 * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
-                    kcol = tap * ctot + p.c1 + j2 * BK;
                 }
-                tma_load_2d(sb, &tmB, &full[s], kcol, col0);
+                {
+                    const int kcol = tap * ctot + (j < nkb1 ? j * BK : p.c1 + (j - nkb1) * BK);
+                    tma_load_2d(sb, &tmB, &full[s], kcol, col0);
+                }
                 if (++s == stages) {
                     s = 0;
                     ph ^= 1;
@@ -180,7 +182,7 @@ __global__ void __launch_bounds__(kThreads)
             }
             umma_commit(acc_full);
         }
-    } else {
+    } else if (warp >= 2 && warp <= 5) {
         // ---------------- epilogue: one thread per accumulator row
         const int q = warp & 3;
         const int r = q * 32 + lane;
@@ -192,7 +194,8 @@ __global__ void __launch_bounds__(kThreads)
         const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
         const size_t m = (size_t(ni) * p.h + y) * p.w + x;
 
-        mbar_wait(acc_full, 0);
+        if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
+        __syncwarp();
         tc_fence_after();
         const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
 
@@ -361,6 +364,372 @@ __global__ void __launch_bounds__(kThreads)
     }
 }
 
+// ---------------------------------------------------------------- CTA-pair (cta_group::2) helpers
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc2_rt(uint32_t* slot, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(slot)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2_rt(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+                 : "memory");
+}
+// The mbarrier operand always names the even (leader) CTA of the pair: bit 24 of a
+// shared::cluster address selects the CTA within the pair.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0,
+                                                int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0,
+                                                int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2),
+        "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void umma2_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Arrive on the same barrier offset in both CTAs of the pair once the MMAs issued so far are done.
+__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
+    const uint16_t mask = 0x3;
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
+            "r"(smem_u32(bar)),
+        "h"(mask)
+        : "memory");
+}
+
+// Same tile program as k_igemm, executed by a pair of CTAs (cluster of 2) as one 256 x BN tile:
+// each CTA stages its own 128 pixels of A and half of the weight tile, the leader issues
+// tcgen05.mma.cta_group::2 (M = 256) which reads both halves of B, so every SM reads only half of
+// the B operand from its shared memory -- the shared-memory port, not the tensor pipe, is what
+// limits the single-CTA kernel.  Accumulators land in both CTAs' TMEM; each CTA runs its own
+// epilogue.
+__global__ void __launch_bounds__(kThreads)
+    k_igemm2(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+            const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    const int BN = p.bn;
+    const int B_STAGE_BYTES = (BN / 2) * BK * 2;  // each CTA of the pair stages half of the weight tile
+    const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    __shared__ int s_is_last;
+
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B operands need 1024-byte aligned stage bases.
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int stages = p.stages;
+    uint32_t cta_rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    const bool leader = cta_rank == 0;
+
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
+    uint64_t* empty = full + stages;
+    uint64_t* acc_full = empty + stages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+    // spatial tile -> origin pixel
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x;
+    t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int tn = t / p.tiles_y;
+    const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+    const int col0 = blockIdx.y * BN;
+    const int bcol0 = col0 + int(cta_rank) * (BN / 2);  // this CTA's half of the weight tile
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmA2);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < stages; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], 1);
+            }
+            mbar_init(acc_full, 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc2_rt(tmem_slot, uint32_t(p.tmem_cols));
+    }
+    tc_fence_before();
+    cluster_sync_all();  // peer barriers must exist before any remote arrive / complete_tx
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    const int nkb1 = (p.c1 + BK - 1) / BK;
+    const int nkb2 = (p.c2 + BK - 1) / BK;
+    const int per_tap = nkb1 + nkb2;
+    const int ctot = p.c1 + p.c2;
+    const int total_all = p.kh * p.kw * per_tap;
+    const int it_begin = blockIdx.z * p.kb_per_split;
+    const int it_end = min(total_all, it_begin + p.kb_per_split);
+    const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int it = it_begin; it < it_end; ++it) {
+                mbar_wait(&empty[s], ph ^ 1);
+                const int tap = it / per_tap;
+                const int j = it - tap * per_tap;
+                const int ky = tap / p.kw, kx = tap - ky * p.kw;
+                uint8_t* sa = smem + s * STAGE_BYTES;
+                uint8_t* sb = sa + A_STAGE_BYTES;
+                // both CTAs' loads complete on the leader's barrier; only the leader arms it
+                if (leader) mbar_expect_tx(&full[s], 2u * (a_bytes + uint32_t(B_STAGE_BYTES)));
+                if (j < nkb1) {
+                    tma_load_4d_2sm(sa, &tmA1, &full[s], j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                } else {
+                    const int j2 = j - nkb1;
+                    tma_load_4d_2sm(sa, &tmA2, &full[s], j2 * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                }
+                {
+                    const int kcol = tap * ctot + (j < nkb1 ? j * BK : p.c1 + (j - nkb1) * BK);
+                    tma_load_2d_2sm(sb, &tmB, &full[s], kcol, bcol0);
+                }
+                if (++s == stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            int s = 0;
+            uint32_t ph = 0;
+            uint32_t acc = 0;
+            for (int it = it_begin; it < it_end; ++it) {
+                mbar_wait(&full[s], ph);
+                tc_fence_after();
+                const int j = it % per_tap;
+                const int cvalid = (j < nkb1) ? (p.c1 - j * BK) : (p.c2 - (j - nkb1) * BK);
+                const int ksteps = cvalid >= BK ? BK / 16 : (cvalid + 15) / 16;
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+                const uint32_t sb = sa + A_STAGE_BYTES;
+                const uint64_t adesc = umma_desc_sw128(sa, 16, 1024);
+                const uint64_t bdesc = umma_desc_sw128(sb, 16, 1024);
+                for (int k = 0; k < ksteps; ++k) {
+                    // +32 bytes per 16-element K step inside the 128-byte swizzle row
+                    umma2_f16(tmem_acc, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), p.idesc, acc);
+                    acc = 1;
+                }
+                umma2_commit_mc(&empty[s]);
+                if (++s == stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+            umma2_commit_mc(acc_full);
+        }
+    } else if (warp >= 2 && warp <= 5) {
+        // ---------------- epilogue: one thread per accumulator row
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const int xl = r % p.bw;
+        const int r2 = r / p.bw;
+        const int yl = r2 % p.bh;
+        const int nl = r2 / p.bh;
+        const int x = x0 + xl, y = y0 + yl, ni = n0 + nl;
+        const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
+        const size_t m = (size_t(ni) * p.h + y) * p.w + x;
+
+        if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
+        __syncwarp();
+        tc_fence_after();
+        const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
+
+        // ---- split-K: every split parks its fp32 tile in scratch; the split that arrives last
+        // (ticket counter) sums all of them in split order -- a fixed order, so the result does
+        // not depend on which CTA happened to finish last -- and runs the epilogue.
+        const float* my_partials = nullptr;
+        if (p.splits > 1) {
+            const int tile_id = blockIdx.x * gridDim.y + blockIdx.y;
+            const int nchunk = BN / 32;
+            float* tile_base = p.partials + size_t(tile_id) * p.splits * nchunk * 4096;
+            float* mine = tile_base + size_t(blockIdx.z) * nchunk * 4096 + r * 32;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(trow + c, v);
+                tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(mine + (c / 32) * 4096);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) {
+                const unsigned int t = atomicAdd(&p.tickets[tile_id], 1u);
+                const int last = (t == unsigned(p.splits) - 1u);
+                if (last) p.tickets[tile_id] = 0u;  // ready for the next launch
+                s_is_last = last;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (s_is_last) {
+                __threadfence();
+                my_partials = tile_base + r * 32;
+            }
+        }
+        const bool do_epilogue = (p.splits == 1) || (my_partials != nullptr);
+        auto load_chunk = [&](int c, uint32_t (&v)[32]) {
+            if (my_partials == nullptr) {
+                tmem_ld32(trow + c, v);
+                tmem_ld_wait();
+            } else {
+                const int nchunk = BN / 32;
+                float acc[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
+                for (int z = 0; z < p.splits; ++z) {
+                    const float4* src = reinterpret_cast<const float4*>(
+                        my_partials + (size_t(z) * nchunk + c / 32) * 4096);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 f = __ldcg(src + j);
+                        acc[4 * j] += f.x;
+                        acc[4 * j + 1] += f.y;
+                        acc[4 * j + 2] += f.z;
+                        acc[4 * j + 3] += f.w;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
+            }
+        };
+
+        if (!do_epilogue) {
+            // another split owns the epilogue of this tile
+        } else if (p.act == SW_ACT_GEGLU) {
+            // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates
+            const int HALF = BN / 2;
+            const int ocol0 = blockIdx.y * HALF;
+            const int ncols_out = p.cout / 2;
+#pragma unroll 1
+            for (int c = 0; c < HALF; c += 16) {
+                uint32_t v[16], g[16];
+                tmem_ld16(trow + c, v);
+                tmem_ld16(trow + HALF + c, g);
+                tmem_ld_wait();
+                if (row_ok && ocol0 + c < ncols_out) {
+                    uint32_t o[8];
+#pragma unroll
+                    for (int j = 0; j < 16; j += 2) {
+                        float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
+                        float g0 = __uint_as_float(g[j]), g1 = __uint_as_float(g[j + 1]);
+                        if (p.bias) {
+                            a0 += __half2float(p.bias[col0 + c + j]);
+                            a1 += __half2float(p.bias[col0 + c + j + 1]);
+                            g0 += __half2float(p.bias[col0 + HALF + c + j]);
+                            g1 += __half2float(p.bias[col0 + HALF + c + j + 1]);
+                        }
+                        o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
+                    }
+                    uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
+                    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                }
+            }
+        } else {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                load_chunk(c, v);
+                if (!row_ok) continue;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const int col = col0 + c + g8 * 8;
+                    if (col >= p.cout) break;
+                    float f[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]);
+                    if (p.bias) {
+                        const uint4 b = *reinterpret_cast<const uint4*>(p.bias + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    if (p.row_bias) {
+                        const uint4 b = *reinterpret_cast<const uint4*>(
+                            p.row_bias + size_t(ni) * p.row_bias_ld + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    if (p.act == SW_ACT_SILU) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
+                    } else if (p.act == SW_ACT_GELU) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                    }
+                    if (p.out_scale != 1.0f) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
+                    }
+                    if (p.residual) {
+                        const uint4 b =
+                            *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
+                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 t2 = unpack_h2(bw[j]);
+                            f[2 * j] += t2.x;
+                            f[2 * j + 1] += t2.y;
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(p.out + m * p.ldc + col) =
+                        make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
+                                   pack_h2(f[6], f[7]));
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();  // both epilogues have drained TMEM
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc2_rt(tmem_acc, uint32_t(p.tmem_cols));
+    }
+}
+
 // Choose the pixel box (bw x bh x bi, <= 128 pixels) that wastes the fewest MMA rows.
 void pick_box(int n, int h, int w, int* bw, int* bh, int* bi) {
     double best = -1.0;
@@ -396,19 +765,39 @@ void pick_box(int n, int h, int w, int* bw, int* bh, int* bi) {
 }
 
 int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB,
-           int grid_x, cudaStream_t st) {
-    const int stage_bytes = A_STAGE_BYTES + a.bn * BK * 2;
+           int grid_x, bool pair, cudaStream_t st) {
+    const int b_rows = pair ? a.bn / 2 : a.bn;
+    const int stage_bytes = A_STAGE_BYTES + b_rows * BK * 2;
     const int smem = a.stages * stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
     static bool configured[64] = {false};
     int dev = 0;
     SW_CUDA_OK(cudaGetDevice(&dev));
     if (dev < 64 && !configured[dev]) {
-        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         configured[dev] = true;
     }
-    dim3 grid(grid_x, (a.cout + a.bn - 1) / a.bn, a.splits);
-    k_igemm<<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
-    SW_CUDA_OK(cudaGetLastError());
+    const int ntile = (a.cout + a.bn - 1) / a.bn;
+    if (!pair) {
+        dim3 grid(grid_x, ntile, a.splits);
+        k_igemm<<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
+        SW_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((grid_x + 1) / 2 * 2, ntile, a.splits);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = size_t(smem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SW_CUDA_OK(cudaLaunchKernelEx(&cfg, k_igemm2, tA1, tA2, tB, a));
     return 0;
 }
 
@@ -482,23 +871,44 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     a.bn = bn;
     a.tmem_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
 
+    // ---- CTA pairs: with >= 2 pixel tiles per weight tile the layer runs as 256 x BN tiles on
+    // tcgen05 cta_group::2 (halves every SM's shared-memory reads of the weight operand).
+    bool pair = grid_x >= 8 && bn >= 64;
+    if (p->cta_pair == 1) pair = false;
+    if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64;
+
     // ---- pipeline depth: two CTAs per SM (epilogue of one overlaps the main loop of the other)
     // when three stages fit in ~110 KB, else one CTA with a deeper ring.
-    const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+    const int stage_bytes = A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
     int stages = (3 * stage_bytes <= 110 * 1024) ? 3 : 4;
     if (stage_bytes <= 24 * 1024) stages = 4;
+    {
+        static int forced = -1;  // tuning hook: SW_IGEMM_STAGES overrides the ring depth
+        if (forced < 0) {
+            const char* e = getenv("SW_IGEMM_STAGES");
+            forced = e ? atoi(e) : 0;
+        }
+        if (forced > 0) {
+            stages = forced;
+            while (stages > 2 && stages * stage_bytes > 220 * 1024) --stages;
+        }
+    }
     if (kblocks < stages) stages = kblocks;
     a.stages = stages;
-    a.idesc = sw::umma_idesc(128, bn, 0, 0, 0);
+    a.idesc = sw::umma_idesc(pair ? 256 : 128, bn, 0, 0, 0);
 
-    // ---- split-K: when the tile grid cannot fill the GPU and K is long, several CTAs share a
-    // tile's K range (deterministic reduction in the epilogue of the last arrival).
+    // ---- split-K.  A CTA ingests operands from L2 at a bounded rate (~40 B/clk/SM measured), so a
+    // layer finishes when its busiest SM has pulled its share: with fewer CTAs than SMs, several
+    // CTAs share each tile's K range (deterministic reduction by the last arrival).
     a.splits = 1;
     a.kb_per_split = kblocks;
-    const long ctas = long(grid_x) * tiles_ncol;
-    if (p->splitk_scratch && p->act != SW_ACT_GEGLU && ctas < sms && kblocks >= 16 && ctas <= kMaxSplitTiles) {
-        int want = int((2L * sms + ctas - 1) / ctas);
-        int max_by_k = kblocks / 8;
+    const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
+    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
+    if (p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
+        ctas <= kMaxSplitTiles) {
+        const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
+        int want = int(slots / ctas);
+        int max_by_k = kblocks / min_kb;
         int splits = want < max_by_k ? want : max_by_k;
         if (splits > 32) splits = 32;
         const long long per_tile = (long long)(bn / 32) * 4096 * sizeof(float);
@@ -535,9 +945,9 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     {
         const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout)};
         const uint64_t str[1] = {(p->w_ld > 0 ? uint64_t(p->w_ld) : uint64_t(ktotal)) * 2};
-        const uint32_t box[2] = {64, uint32_t(bn)};
+        const uint32_t box[2] = {64, uint32_t(pair ? bn / 2 : bn)};
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
         if (rc) return rc;
     }
-    return launch(a, tA1, tA2, tB, grid_x, static_cast<cudaStream_t>(stream));
+    return launch(a, tA1, tA2, tB, grid_x, pair, static_cast<cudaStream_t>(stream));
 }

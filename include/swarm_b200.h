@@ -65,6 +65,8 @@ typedef struct {
                             zero-filled once before first use (the kernel leaves it reusable);
                             calls sharing one scratch must be stream-ordered. */
     int64_t splitk_scratch_bytes;
+    int32_t splitk_min_kb; /* 0 = default (16): fewest 64-wide K blocks a split may get */
+    int32_t cta_pair;    /* 0 = auto, 1 = single-CTA tiles (128 x N), 2 = CTA-pair tiles (256 x N, cta_group::2) */
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);

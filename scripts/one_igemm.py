@@ -1,0 +1,14 @@
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from chiaswarm_b200.ops import native as nat
+from chiaswarm_b200.ops.packing import pack_conv_weight
+n, h, w, cin, cout, k, tile = (int(a) for a in sys.argv[1:8])
+x = torch.randn(n, h, w, cin, device="cuda", dtype=torch.float16)
+wp = pack_conv_weight(torch.randn(cout, cin, k, k, device="cuda", dtype=torch.float16) * 0.02)
+b = torch.randn(cout, device="cuda", dtype=torch.float16)
+out = torch.empty(n, h, w, cout, device="cuda", dtype=torch.float16)
+for _ in range(4):
+    nat.igemm(x, wp, out, n=n, h=h, w=w, kh=k, kw=k, pad=k // 2, bias=b, tile_n=tile)
+torch.cuda.synchronize()
+print("ok")

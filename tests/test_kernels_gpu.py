@@ -115,6 +115,42 @@ def test_conv3x3(nat, n, h, w, cin, cout):
     assert _rel_err(out, ref) < 4e-3
 
 
+@pytest.mark.parametrize("n,h,w,cin,cout,tile_n", [(2, 64, 64, 320, 320, 0), (2, 32, 32, 640, 640, 256), (2, 16, 16, 128, 192, 64),
+                                                   (1, 96, 96, 64, 128, 128), (3, 40, 72, 64, 320, 160), (1, 24, 24, 64, 64, 64)])
+def test_conv3x3_cta_pair(nat, n, h, w, cin, cout, tile_n):
+    """256 x N tiles on tcgen05 cta_group::2 (cluster of two CTAs), incl. an odd tile count."""
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    torch.manual_seed(14)
+    x = torch.randn(n, cin, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=torch.float16) * ((9 * cin) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    res = torch.randn(n, h, w, cout, device="cuda", dtype=torch.float16)
+    out = torch.empty(n, h, w, cout, device="cuda", dtype=torch.float16)
+    nat.igemm(x.permute(0, 2, 3, 1).contiguous(), pack_conv_weight(wt), out, n=n, h=h, w=w, kh=3, kw=3, pad=1, bias=b,
+              residual=res, tile_n=tile_n, cta_pair=2)
+    ref = F.conv2d(x.float(), wt.float(), b.float(), padding=1).permute(0, 2, 3, 1) + res.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+def test_linear_cta_pair_and_geglu(nat):
+    from chiaswarm_b200.ops.packing import interleave_geglu
+
+    torch.manual_seed(15)
+    m, d = 1300, 640
+    x = torch.randn(m, d, device="cuda", dtype=torch.float16)
+    w = torch.randn(1920, d, device="cuda", dtype=torch.float16) * (d ** -0.5)
+    out = nat.linear(x, w, cta_pair=2)
+    assert _rel_err(out, x.float() @ w.float().t()) < 4e-3
+    wg = torch.randn(8 * d, d, device="cuda", dtype=torch.float16) * (d ** -0.5)
+    bg = torch.randn(8 * d, device="cuda", dtype=torch.float16)
+    wi, bi = interleave_geglu(wg, bg)
+    out = nat.linear(x, wi, bias=bi, act=nat.ACT_GEGLU, cta_pair=2)
+    h = x.float() @ wg.float().t() + bg.float()
+    val, gate = h.chunk(2, dim=-1)
+    assert _rel_err(out, val * F.gelu(gate)) < 4e-3
+
+
 def test_conv_dual_input_rowbias_residual(nat):
     from chiaswarm_b200.ops.packing import pack_conv_weight
 
