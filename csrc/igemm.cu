@@ -52,23 +52,136 @@ struct IGemmArgs {
     float* partials;        // [tile][split][bn/32][128][32] fp32
 };
 
-__device__ __forceinline__ void tmem_alloc_rt(uint32_t* slot, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(slot)),
-                 "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+// ---------------------------------------------------------------- raw-address PTX helpers
+// The producer and MMA roles are single threads: every instruction they execute sits on the
+// critical path of a K block (a lone thread retires a dependent instruction every ~5-30 cycles;
+// a runtime division alone costs more than a whole MMA).  So their loops carry incremental
+// counters and precomputed 32-bit shared addresses / descriptor halves -- no div/mod, no
+// generic->shared conversions, no descriptor assembly inside the loop.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // bit 24 of a shared::cluster address: CTA in the pair
+
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    for (uint32_t i = 0; !ok; ++i) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (i > SW_SPIN_LIMIT) __trap();
+    }
 }
-__device__ __forceinline__ void tmem_dealloc_rt(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
-                 : "memory");
+__device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+template <bool PAIR>
+__device__ __forceinline__ void tma4(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+    if (PAIR)
+        asm volatile(
+            "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+            : "memory");
+    else
+        asm volatile(
+            "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+            : "memory");
+}
+template <bool PAIR>
+__device__ __forceinline__ void tma2(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+    if (PAIR)
+        asm volatile(
+            "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1)
+            : "memory");
+    else
+        asm volatile(
+            "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
+            : "memory");
+}
+template <bool PAIR>
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
+                                        uint32_t idesc, uint32_t accumulate) {
+    if (PAIR)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+            "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+            "setp.ne.b32 p, %5, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}" ::"r"(tmem_d),
+            "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+            "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+            "setp.ne.b32 p, %5, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}" ::"r"(tmem_d),
+            "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+            : "memory");
+}
+// Arrive on `bar` (same offset in both CTAs for a pair) once all MMAs issued so far are done.
+template <bool PAIR>
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+    if (PAIR) {
+        const uint16_t mask = 0x3;
+        asm volatile(
+            "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
+                "r"(bar),
+            "h"(mask)
+            : "memory");
+    } else {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                     : "memory");
+    }
+}
+template <bool PAIR>
+__device__ __forceinline__ void tmem_alloc_any(uint32_t* slot, uint32_t cols) {
+    if (PAIR) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)),
+                     "r"(cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)),
+                     "r"(cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+}
+template <bool PAIR>
+__device__ __forceinline__ void tmem_dealloc_any(uint32_t taddr, uint32_t cols) {
+    if (PAIR)
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    else
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+template <bool PAIR>
+__device__ __forceinline__ void cta_or_cluster_sync() {
+    if (PAIR) {
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    } else {
+        __syncthreads();
+    }
 }
 
-__global__ void __launch_bounds__(kThreads)
-    k_igemm(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-            const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+// PAIR == false: one CTA computes a 128 x BN tile (tcgen05 cta_group::1).
+// PAIR == true : a cluster of two CTAs computes a 256 x BN tile (cta_group::2): each CTA stages its
+// own 128 pixels of A and half of the weight tile, the leader issues the M = 256 MMAs which read
+// both halves of B, so every SM pulls only half of the weight operand; accumulators land in both
+// CTAs' TMEM and each CTA runs its own epilogue.
+template <bool PAIR>
+__device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtensorMap& tmA2,
+                                           const CUtensorMap& tmB, const IGemmArgs& p) {
     const int BN = p.bn;
-    const int B_STAGE_BYTES = BN * BK * 2;
+    const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     __shared__ int s_is_last;
 
@@ -80,369 +193,8 @@ __global__ void __launch_bounds__(kThreads)
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int stages = p.stages;
-
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
-    uint64_t* empty = full + stages;
-    uint64_t* acc_full = empty + stages;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
-
-    // spatial tile -> origin pixel
-    int t = blockIdx.x;
-    const int tx = t % p.tiles_x;
-    t /= p.tiles_x;
-    const int ty = t % p.tiles_y;
-    const int tn = t / p.tiles_y;
-    const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
-    const int col0 = blockIdx.y * BN;
-
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tmA1);
-        tma_prefetch_desc(&tmA2);
-        tma_prefetch_desc(&tmB);
-    }
-    if (warp == 1) {
-        if (lane == 0) {
-            for (int s = 0; s < stages; ++s) {
-                mbar_init(&full[s], 1);
-                mbar_init(&empty[s], 1);
-            }
-            mbar_init(acc_full, 1);
-            fence_mbar_init();
-        }
-        __syncwarp();
-        tmem_alloc_rt(tmem_slot, uint32_t(p.tmem_cols));
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_acc = *tmem_slot;
-
-    const int nkb1 = (p.c1 + BK - 1) / BK;
-    const int nkb2 = (p.c2 + BK - 1) / BK;
-    const int per_tap = nkb1 + nkb2;
-    const int ctot = p.c1 + p.c2;
-    const int total_all = p.kh * p.kw * per_tap;
-    const int it_begin = blockIdx.z * p.kb_per_split;
-    const int it_end = min(total_all, it_begin + p.kb_per_split);
-    const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
-
-    if (warp == 0) {
-        if (lane == 0) {
-            int s = 0;
-            uint32_t ph = 0;
-            for (int it = it_begin; it < it_end; ++it) {
-                mbar_wait(&empty[s], ph ^ 1);
-                const int tap = it / per_tap;
-                const int j = it - tap * per_tap;
-                const int ky = tap / p.kw, kx = tap - ky * p.kw;
-                uint8_t* sa = smem + s * STAGE_BYTES;
-                uint8_t* sb = sa + A_STAGE_BYTES;
-                mbar_expect_tx(&full[s], a_bytes + B_STAGE_BYTES);
-                if (j < nkb1) {
-                    tma_load_4d(sa, &tmA1, &full[s], j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
-                } else {
-                    const int j2 = j - nkb1;
-                    tma_load_4d(sa, &tmA2, &full[s], j2 * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
-                }
-                {
-                    const int kcol = tap * ctot + (j < nkb1 ? j * BK : p.c1 + (j - nkb1) * BK);
-                    tma_load_2d(sb, &tmB, &full[s], kcol, col0);
-                }
-                if (++s == stages) {
-                    s = 0;
-                    ph ^= 1;
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            int s = 0;
-            uint32_t ph = 0;
-            uint32_t acc = 0;
-            for (int it = it_begin; it < it_end; ++it) {
-                mbar_wait(&full[s], ph);
-                tc_fence_after();
-                const int j = it % per_tap;
-                const int cvalid = (j < nkb1) ? (p.c1 - j * BK) : (p.c2 - (j - nkb1) * BK);
-                const int ksteps = cvalid >= BK ? BK / 16 : (cvalid + 15) / 16;
-                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
-                const uint32_t sb = sa + A_STAGE_BYTES;
-                const uint64_t adesc = umma_desc_sw128(sa, 16, 1024);
-                const uint64_t bdesc = umma_desc_sw128(sb, 16, 1024);
-                for (int k = 0; k < ksteps; ++k) {
-                    // +32 bytes per 16-element K step inside the 128-byte swizzle row
-                    umma_f16(tmem_acc, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), p.idesc, acc);
-                    acc = 1;
-                }
-                umma_commit(&empty[s]);
-                if (++s == stages) {
-                    s = 0;
-                    ph ^= 1;
-                }
-            }
-            umma_commit(acc_full);
-        }
-    } else if (warp >= 2 && warp <= 5) {
-        // ---------------- epilogue: one thread per accumulator row
-        const int q = warp & 3;
-        const int r = q * 32 + lane;
-        const int xl = r % p.bw;
-        const int r2 = r / p.bw;
-        const int yl = r2 % p.bh;
-        const int nl = r2 / p.bh;
-        const int x = x0 + xl, y = y0 + yl, ni = n0 + nl;
-        const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
-        const size_t m = (size_t(ni) * p.h + y) * p.w + x;
-
-        if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
-        __syncwarp();
-        tc_fence_after();
-        const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
-
-        // ---- split-K: every split parks its fp32 tile in scratch; the split that arrives last
-        // (ticket counter) sums all of them in split order -- a fixed order, so the result does
-        // not depend on which CTA happened to finish last -- and runs the epilogue.
-        const float* my_partials = nullptr;
-        if (p.splits > 1) {
-            const int tile_id = blockIdx.x * gridDim.y + blockIdx.y;
-            const int nchunk = BN / 32;
-            float* tile_base = p.partials + size_t(tile_id) * p.splits * nchunk * 4096;
-            float* mine = tile_base + size_t(blockIdx.z) * nchunk * 4096 + r * 32;
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                tmem_ld32(trow + c, v);
-                tmem_ld_wait();
-                float4* dst = reinterpret_cast<float4*>(mine + (c / 32) * 4096);
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-            }
-            __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (threadIdx.x == 64) {
-                const unsigned int t = atomicAdd(&p.tickets[tile_id], 1u);
-                const int last = (t == unsigned(p.splits) - 1u);
-                if (last) p.tickets[tile_id] = 0u;  // ready for the next launch
-                s_is_last = last;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (s_is_last) {
-                __threadfence();
-                my_partials = tile_base + r * 32;
-            }
-        }
-        const bool do_epilogue = (p.splits == 1) || (my_partials != nullptr);
-        auto load_chunk = [&](int c, uint32_t (&v)[32]) {
-            if (my_partials == nullptr) {
-                tmem_ld32(trow + c, v);
-                tmem_ld_wait();
-            } else {
-                const int nchunk = BN / 32;
-                float acc[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
-                for (int z = 0; z < p.splits; ++z) {
-                    const float4* src = reinterpret_cast<const float4*>(
-                        my_partials + (size_t(z) * nchunk + c / 32) * 4096);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 f = __ldcg(src + j);
-                        acc[4 * j] += f.x;
-                        acc[4 * j + 1] += f.y;
-                        acc[4 * j + 2] += f.z;
-                        acc[4 * j + 3] += f.w;
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
-            }
-        };
-
-        if (!do_epilogue) {
-            // another split owns the epilogue of this tile
-        } else if (p.act == SW_ACT_GEGLU) {
-            // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates
-            const int HALF = BN / 2;
-            const int ocol0 = blockIdx.y * HALF;
-            const int ncols_out = p.cout / 2;
-#pragma unroll 1
-            for (int c = 0; c < HALF; c += 16) {
-                uint32_t v[16], g[16];
-                tmem_ld16(trow + c, v);
-                tmem_ld16(trow + HALF + c, g);
-                tmem_ld_wait();
-                if (row_ok && ocol0 + c < ncols_out) {
-                    uint32_t o[8];
-#pragma unroll
-                    for (int j = 0; j < 16; j += 2) {
-                        float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
-                        float g0 = __uint_as_float(g[j]), g1 = __uint_as_float(g[j + 1]);
-                        if (p.bias) {
-                            a0 += __half2float(p.bias[col0 + c + j]);
-                            a1 += __half2float(p.bias[col0 + c + j + 1]);
-                            g0 += __half2float(p.bias[col0 + HALF + c + j]);
-                            g1 += __half2float(p.bias[col0 + HALF + c + j + 1]);
-                        }
-                        o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
-                    }
-                    uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
-                    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-                    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-                }
-            }
-        } else {
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                load_chunk(c, v);
-                if (!row_ok) continue;
-#pragma unroll
-                for (int g8 = 0; g8 < 4; ++g8) {
-                    const int col = col0 + c + g8 * 8;
-                    if (col >= p.cout) break;
-                    float f[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]);
-                    if (p.bias) {
-                        const uint4 b = *reinterpret_cast<const uint4*>(p.bias + col);
-                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float2 t2 = unpack_h2(bw[j]);
-                            f[2 * j] += t2.x;
-                            f[2 * j + 1] += t2.y;
-                        }
-                    }
-                    if (p.row_bias) {
-                        const uint4 b = *reinterpret_cast<const uint4*>(
-                            p.row_bias + size_t(ni) * p.row_bias_ld + col);
-                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float2 t2 = unpack_h2(bw[j]);
-                            f[2 * j] += t2.x;
-                            f[2 * j + 1] += t2.y;
-                        }
-                    }
-                    if (p.act == SW_ACT_SILU) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
-                    } else if (p.act == SW_ACT_GELU) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
-                    }
-                    if (p.out_scale != 1.0f) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
-                    }
-                    if (p.residual) {
-                        const uint4 b =
-                            *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
-                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float2 t2 = unpack_h2(bw[j]);
-                            f[2 * j] += t2.x;
-                            f[2 * j + 1] += t2.y;
-                        }
-                    }
-                    *reinterpret_cast<uint4*>(p.out + m * p.ldc + col) =
-                        make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
-                                   pack_h2(f[6], f[7]));
-                }
-            }
-        }
-    }
-
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc_rt(tmem_acc, uint32_t(p.tmem_cols));
-    }
-}
-
-// ---------------------------------------------------------------- CTA-pair (cta_group::2) helpers
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_alloc2_rt(uint32_t* slot, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(slot)),
-                 "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc2_rt(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
-                 : "memory");
-}
-// The mbarrier operand always names the even (leader) CTA of the pair: bit 24 of a
-// shared::cluster address selects the CTA within the pair.
-constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
-__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0,
-                                                int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_4d_2sm(void* dst, const CUtensorMap* m, uint64_t* bar, int c0,
-                                                int c1, int c2, int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2),
-        "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void umma2_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// Arrive on the same barrier offset in both CTAs of the pair once the MMAs issued so far are done.
-__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
-    const uint16_t mask = 0x3;
-    asm volatile(
-        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::
-            "r"(smem_u32(bar)),
-        "h"(mask)
-        : "memory");
-}
-
-// Same tile program as k_igemm, executed by a pair of CTAs (cluster of 2) as one 256 x BN tile:
-// each CTA stages its own 128 pixels of A and half of the weight tile, the leader issues
-// tcgen05.mma.cta_group::2 (M = 256) which reads both halves of B, so every SM reads only half of
-// the B operand from its shared memory -- the shared-memory port, not the tensor pipe, is what
-// limits the single-CTA kernel.  Accumulators land in both CTAs' TMEM; each CTA runs its own
-// epilogue.
-__global__ void __launch_bounds__(kThreads)
-    k_igemm2(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-            const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
-    const int BN = p.bn;
-    const int B_STAGE_BYTES = (BN / 2) * BK * 2;  // each CTA of the pair stages half of the weight tile
-    const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    __shared__ int s_is_last;
-
-    extern __shared__ uint8_t smem_raw[];
-    // SWIZZLE_128B operands need 1024-byte aligned stage bases.
-    const uint32_t raw_addr = smem_u32(smem_raw);
-    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const int stages = p.stages;
-    uint32_t cta_rank;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    uint32_t cta_rank = 0;
+    if (PAIR) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
     const bool leader = cta_rank == 0;
 
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * STAGE_BYTES);
@@ -458,7 +210,7 @@ __global__ void __launch_bounds__(kThreads)
     const int tn = t / p.tiles_y;
     const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
     const int col0 = blockIdx.y * BN;
-    const int bcol0 = col0 + int(cta_rank) * (BN / 2);  // this CTA's half of the weight tile
+    const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA1);
@@ -475,10 +227,10 @@ __global__ void __launch_bounds__(kThreads)
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc2_rt(tmem_slot, uint32_t(p.tmem_cols));
+        tmem_alloc_any<PAIR>(tmem_slot, uint32_t(p.tmem_cols));
     }
     tc_fence_before();
-    cluster_sync_all();  // peer barriers must exist before any remote arrive / complete_tx
+    cta_or_cluster_sync<PAIR>();  // (pair: peer barriers must exist before any remote arrive)
     tc_fence_after();
     const uint32_t tmem_acc = *tmem_slot;
 
@@ -490,65 +242,100 @@ __global__ void __launch_bounds__(kThreads)
     const int it_begin = blockIdx.z * p.kb_per_split;
     const int it_end = min(total_all, it_begin + p.kb_per_split);
     const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
+    const uint32_t smem0 = smem_u32(smem);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
 
     if (warp == 0) {
         if (lane == 0) {
+            // ---------------- TMA producer (lean loop, see note above)
+            int tap = it_begin / per_tap;
+            int j = it_begin - tap * per_tap;
+            int ky = tap / p.kw, kx = tap - ky * p.kw;
+            int tapbase = tap * ctot;
+            const uint32_t tx_bytes = (PAIR ? 2u : 1u) * (a_bytes + uint32_t(B_STAGE_BYTES));
+            uint32_t sa = smem0, fb = full0, eb = empty0;
             int s = 0;
-            uint32_t ph = 0;
+            uint32_t ph = 1;
             for (int it = it_begin; it < it_end; ++it) {
-                mbar_wait(&empty[s], ph ^ 1);
-                const int tap = it / per_tap;
-                const int j = it - tap * per_tap;
-                const int ky = tap / p.kw, kx = tap - ky * p.kw;
-                uint8_t* sa = smem + s * STAGE_BYTES;
-                uint8_t* sb = sa + A_STAGE_BYTES;
+                bar_wait(eb, ph);
                 // both CTAs' loads complete on the leader's barrier; only the leader arms it
-                if (leader) mbar_expect_tx(&full[s], 2u * (a_bytes + uint32_t(B_STAGE_BYTES)));
+                if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
+                int kcol;
                 if (j < nkb1) {
-                    tma_load_4d_2sm(sa, &tmA1, &full[s], j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    kcol = tapbase + j * BK;
                 } else {
-                    const int j2 = j - nkb1;
-                    tma_load_4d_2sm(sa, &tmA2, &full[s], j2 * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    kcol = tapbase + p.c1 + (j - nkb1) * BK;
                 }
-                {
-                    const int kcol = tap * ctot + (j < nkb1 ? j * BK : p.c1 + (j - nkb1) * BK);
-                    tma_load_2d_2sm(sb, &tmB, &full[s], kcol, bcol0);
+                tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, kcol, bcol0);
+                if (++j == per_tap) {
+                    j = 0;
+                    tapbase += ctot;
+                    if (++kx == p.kw) {
+                        kx = 0;
+                        ++ky;
+                    }
                 }
                 if (++s == stages) {
                     s = 0;
                     ph ^= 1;
+                    sa = smem0;
+                    fb = full0;
+                    eb = empty0;
+                } else {
+                    sa += STAGE_BYTES;
+                    fb += 8;
+                    eb += 8;
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
+        if (lane == 0 && (!PAIR || leader)) {
+            // ---------------- MMA issuer (lean loop)
+            // descriptor = {lo: addr>>4 | LBO(16 B)>>4 << 16, hi: SBO(1024 B)>>4 | version 1 | SWIZZLE_128B}
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((smem0 & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_off = uint32_t(A_STAGE_BYTES) >> 4;
+            const uint32_t stage_step = uint32_t(STAGE_BYTES) >> 4;
+            // K steps (of 16) in the last slab of each input; all other slabs have 4
+            const int ks1 = (p.c1 - (nkb1 - 1) * BK + 15) / 16;
+            const int ks2 = nkb2 ? (p.c2 - (nkb2 - 1) * BK + 15) / 16 : 4;
+            const int last1 = nkb1 - 1, last2 = per_tap - 1;
+            int j = it_begin % per_tap;
+            uint32_t a_lo = a_lo0, fb = full0, eb = empty0;
             int s = 0;
-            uint32_t ph = 0;
-            uint32_t acc = 0;
+            uint32_t ph = 0, acc = 0;
+            const uint32_t idesc = p.idesc;
             for (int it = it_begin; it < it_end; ++it) {
-                mbar_wait(&full[s], ph);
+                bar_wait(fb, ph);
                 tc_fence_after();
-                const int j = it % per_tap;
-                const int cvalid = (j < nkb1) ? (p.c1 - j * BK) : (p.c2 - (j - nkb1) * BK);
-                const int ksteps = cvalid >= BK ? BK / 16 : (cvalid + 15) / 16;
-                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
-                const uint32_t sb = sa + A_STAGE_BYTES;
-                const uint64_t adesc = umma_desc_sw128(sa, 16, 1024);
-                const uint64_t bdesc = umma_desc_sw128(sb, 16, 1024);
-                for (int k = 0; k < ksteps; ++k) {
-                    // +32 bytes per 16-element K step inside the 128-byte swizzle row
-                    umma2_f16(tmem_acc, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), p.idesc, acc);
-                    acc = 1;
-                }
-                umma2_commit_mc(&empty[s]);
+                int ksteps = 4;
+                if (j == last1) ksteps = ks1 < 4 ? ks1 : 4;
+                if (nkb2 && j == last2) ksteps = ks2 < 4 ? ks2 : 4;
+                // +32 bytes (2 descriptor units) per 16-element K step inside the 128-byte swizzle row
+                mma_f16<PAIR>(tmem_acc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
+                if (ksteps > 1) mma_f16<PAIR>(tmem_acc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
+                if (ksteps > 2) mma_f16<PAIR>(tmem_acc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
+                if (ksteps > 3) mma_f16<PAIR>(tmem_acc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                acc = 1u;
+                mma_commit<PAIR>(eb);
+                if (++j == per_tap) j = 0;
                 if (++s == stages) {
                     s = 0;
                     ph ^= 1;
+                    a_lo = a_lo0;
+                    fb = full0;
+                    eb = empty0;
+                } else {
+                    a_lo += stage_step;
+                    fb += 8;
+                    eb += 8;
                 }
             }
-            umma2_commit_mc(acc_full);
+            mma_commit<PAIR>(smem_u32(acc_full));
         }
-    } else if (warp >= 2 && warp <= 5) {
+    } else {
         // ---------------- epilogue: one thread per accumulator row
         const int q = warp & 3;
         const int r = q * 32 + lane;
@@ -723,11 +510,23 @@ __global__ void __launch_bounds__(kThreads)
     }
 
     tc_fence_before();
-    cluster_sync_all();  // both epilogues have drained TMEM
+    cta_or_cluster_sync<PAIR>();  // (pair: both epilogues have drained TMEM)
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc2_rt(tmem_acc, uint32_t(p.tmem_cols));
+        tmem_dealloc_any<PAIR>(tmem_acc, uint32_t(p.tmem_cols));
     }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    k_igemm(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+            const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    igemm_body<false>(tmA1, tmA2, tmB, p);
+}
+
+__global__ void __launch_bounds__(kThreads)
+    k_igemm2(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+             const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    igemm_body<true>(tmA1, tmA2, tmB, p);
 }
 
 // Choose the pixel box (bw x bh x bi, <= 128 pixels) that wastes the fewest MMA rows.
@@ -873,7 +672,7 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
 
     // ---- CTA pairs: with >= 2 pixel tiles per weight tile the layer runs as 256 x BN tiles on
     // tcgen05 cta_group::2 (halves every SM's shared-memory reads of the weight operand).
-    bool pair = grid_x >= 8 && bn >= 64;
+    bool pair = grid_x >= 32 && bn >= 192;  // measured: pays off for wide tiles with many pixel tiles
     if (p->cta_pair == 1) pair = false;
     if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64;
 
@@ -903,7 +702,7 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     a.splits = 1;
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
-    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
+    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 32;
     if (p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;

@@ -26,16 +26,17 @@ __device__ __forceinline__ void csync() {
 }
 
 template <bool PAIR>
-__global__ void __launch_bounds__(128) probe(int n, int iters, int kadv, long long* out) {
+__global__ void __launch_bounds__(128) probe(int n, int iters, int kadv, long long* out, int commit_every) {
     extern __shared__ uint8_t raw[];
     const uint32_t ra = smem_u32(raw);
     uint8_t* smem = raw + (((ra + 1023u) & ~1023u) - ra);
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 16384 + 32768);
-    uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+    uint64_t* bar2 = bar + 1;
+    uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 2);
     uint32_t rank = 0;
     if (PAIR) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     for (int i = threadIdx.x; i < (16384 + 32768) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
-    if (threadIdx.x == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+    if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_init(bar2, 1); fence_mbar_init(); }
     fence_proxy_async_smem();
     if (threadIdx.x < 32) { if (PAIR) alloc2(slot, 256); else alloc1(slot, 256); }
     tc_fence_before();
@@ -52,6 +53,10 @@ __global__ void __launch_bounds__(128) probe(int n, int iters, int kadv, long lo
             const uint64_t off = kadv ? uint64_t((i & 3) * 2) : 0;
             if (PAIR) mma2(tm, ad + off, bd + off, idesc, i > 0);
             else umma_f16(tm, ad + off, bd + off, idesc, i > 0);
+            if (commit_every && (i % commit_every) == commit_every - 1) {
+                if (PAIR) commit2(bar2); else umma_commit(bar2);
+                if (commit_every < 0) {}
+            }
         }
         if (PAIR) commit2(bar); else umma_commit(bar);
         mbar_wait(bar, 0);
@@ -75,14 +80,15 @@ int main() {
     cudaFuncSetAttribute(probe<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaFuncSetAttribute(probe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const int iters = 512;
-    for (int grid : {1, 148}) {
-        for (int kadv : {0, 1}) {
+    for (int grid : {148}) {
+        for (int ce : {2, 8, 16, 64}) {
+        for (int kadv : {1}) {
             for (int n : {32, 64, 128, 256}) {
                 for (int pair = 0; pair < 2; ++pair) {
                     if (pair && grid == 1) continue;
                     cudaMemset(out, 0, 1024 * sizeof(long long));
                     if (!pair) {
-                        probe<false><<<grid, 128, smem>>>(n, iters, kadv, out);
+                        probe<false><<<grid, 128, smem>>>(n, iters, kadv, out, ce);
                     } else {
                         cudaLaunchConfig_t cfg = {};
                         cfg.gridDim = dim3(grid, 1, 1);
@@ -92,17 +98,18 @@ int main() {
                         at[0].id = cudaLaunchAttributeClusterDimension;
                         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
                         cfg.attrs = at; cfg.numAttrs = 1;
-                        cudaLaunchKernelEx(&cfg, probe<true>, n, iters, kadv, out);
+                        cudaLaunchKernelEx(&cfg, probe<true>, n, iters, kadv, out, ce);
                     }
                     cudaError_t e = cudaDeviceSynchronize();
                     long long h[2];
                     cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
                     const double cyc = double(h[0]) / iters;
                     const double macs = (pair ? 256.0 : 128.0) * n * 16;
-                    printf("grid=%3d kadv=%d N=%3d %s: %7.1f cycles/MMA  -> %6.0f MAC/clk/SM  (%s)\n", grid, kadv, n,
+                    printf("commit_every=%d grid=%3d kadv=%d N=%3d %s: %7.1f cycles/MMA  -> %6.0f MAC/clk/SM  (%s)\n", ce, grid, kadv, n,
                            pair ? "M=256 2CTA" : "M=128 1CTA", cyc, macs / cyc / (pair ? 2 : 1), cudaGetErrorString(e));
                 }
             }
+        }
         }
     }
     return 0;
