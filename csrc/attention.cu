@@ -13,6 +13,8 @@
 #include "common.cuh"
 #include "host_util.h"
 
+#include <stdlib.h>
+
 namespace {
 
 using namespace sw;
@@ -26,6 +28,7 @@ constexpr int O_COL0 = 128;
 struct AttnArgs {
     int batch, heads, seq_q, seq_kv, head_dim;
     int nslab, dpad, kv_stages, tmem_cols;
+    int k_stages, v_stages;  // v2 kernel: independent K and V rings
     float scale_log2;
     __half* out;
     long long o_stride_b, o_stride_s;
@@ -133,23 +136,32 @@ __global__ void __launch_bounds__(kThreads)
         }
     } else if (warp == 1) {
         if (lane == 0) {
+            // Lean issue loop: this single thread is on the critical path of every KV tile, so all
+            // descriptor halves are precomputed and the K loops are unrolled with predicates.
             const int kq = (p.head_dim + 15) / 16;
             const uint32_t tS = tmem_base;
             const uint32_t tO = tmem_base + O_COL0;
-            auto issue_qk = [&](int s) {
-                const uint32_t qa = smem_u32(sQ);
-                const uint32_t ka = smem_u32(sK + s * tile_bytes);
-                for (int kk = 0; kk < kq; ++kk) {
-                    const uint32_t off = uint32_t(kk >> 2) * SLAB_BYTES;
-                    const uint64_t ad = umma_desc_sw128(qa + off, 16, 1024) + uint64_t((kk & 3) * 2);
-                    const uint64_t bd = umma_desc_sw128(ka + off, 16, 1024) + uint64_t((kk & 3) * 2);
-                    umma_f16(tS, ad, bd, p.idesc_qk, kk > 0 ? 1u : 0u);
+            const uint32_t q_lo = desc_lo(smem_u32(sQ), 16);
+            const uint32_t k_lo0 = desc_lo(smem_u32(sK), 16);
+            const uint32_t p_lo = desc_lo(smem_u32(sP), 16);
+            // V is MN-major: 16 kv rows (K) per step = 2048 bytes; slabs of 64 dims are SLAB_BYTES
+            // apart (LBO), 8-row groups 1024 bytes apart (SBO).
+            const uint32_t v_lo0 = desc_lo(smem_u32(sV), SLAB_BYTES);
+            const uint32_t stage_step = uint32_t(tile_bytes) >> 4;
+            const uint32_t idesc_qk = p.idesc_qk, idesc_pv = p.idesc_pv;
+            auto issue_qk = [&](uint32_t k_lo) {
+#pragma unroll
+                for (int kk = 0; kk < 10; ++kk) {
+                    if (kk < kq) {
+                        const uint32_t off = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
+                        umma_f16_lohi(tS, q_lo + off, k_lo + off, kDescHiSw128, idesc_qk, kk > 0 ? 1u : 0u);
+                    }
                 }
             };
             mbar_wait(q_full, 0);
             mbar_wait(&k_full[0], 0);
             tc_fence_after();
-            issue_qk(0);
+            issue_qk(k_lo0);
             umma_commit(s_full);
             int s = 0;
             uint32_t ph = 0;
@@ -168,29 +180,29 @@ __global__ void __launch_bounds__(kThreads)
                 if (stages > 1 && j + 1 < nkv) {
                     mbar_wait(&k_full[s1], ph1);
                     tc_fence_after();
-                    issue_qk(s1);
+                    issue_qk(k_lo0 + uint32_t(s1) * stage_step);
                     umma_commit(s_full);
                 }
                 mbar_wait(&v_full[s], ph);
                 tc_fence_after();
                 const int kv_valid = min(BKV, p.seq_kv - j * BKV);
-                const int kp = (kv_valid + 15) / 16;
-                const uint32_t pa = smem_u32(sP);
-                const uint32_t va = smem_u32(sV + s * tile_bytes);
-                for (int kk = 0; kk < kp; ++kk) {
-                    const uint64_t ad = umma_desc_sw128(pa + uint32_t(kk >> 2) * SLAB_BYTES, 16, 1024) +
-                                        uint64_t((kk & 3) * 2);
-                    // V is MN-major: 16 kv rows (K) per step = 2048 bytes; slabs of 64 dims are
-                    // SLAB_BYTES apart (LBO), 8-row groups 1024 bytes apart (SBO).
-                    const uint64_t bd = umma_desc_sw128(va + uint32_t(kk) * 2048, SLAB_BYTES, 1024);
-                    umma_f16(tO, ad, bd, p.idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                const int kp = (kv_valid + 15) >> 4;
+                const uint32_t v_lo = v_lo0 + uint32_t(s) * stage_step;
+                const uint32_t acc0 = j > 0 ? 1u : 0u;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    if (kk < kp) {
+                        const uint32_t poff = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
+                        umma_f16_lohi(tO, p_lo + poff, v_lo + uint32_t(kk) * (2048 >> 4), kDescHiSw128, idesc_pv,
+                                      kk > 0 ? 1u : acc0);
+                    }
                 }
                 umma_commit(&kv_empty[s]);
                 umma_commit(pv_done);
                 if (stages == 1 && j + 1 < nkv) {
                     mbar_wait(&k_full[s1], ph1);
                     tc_fence_after();
-                    issue_qk(s1);
+                    issue_qk(k_lo0 + uint32_t(s1) * stage_step);
                     umma_commit(s_full);
                 }
                 s = s1;
@@ -211,7 +223,8 @@ __global__ void __launch_bounds__(kThreads)
         float l = 0.0f;
         for (int j = 0; j < nkv; ++j) {
             const int kv_valid = min(BKV, p.seq_kv - j * BKV);
-            mbar_wait(s_full, uint32_t(j & 1));
+            if (lane == 0) mbar_wait(s_full, uint32_t(j & 1));
+            __syncwarp();
             tc_fence_after();
             // pass 1: row max of the raw scores
             float mx = -INFINITY;
@@ -227,7 +240,8 @@ __global__ void __launch_bounds__(kThreads)
             }
             const float m_new = fmaxf(m_ref, mx * p.scale_log2);
             if (j > 0) {
-                mbar_wait(pv_done, uint32_t((j - 1) & 1));  // O is stable, P tile is free again
+                if (lane == 0) mbar_wait(pv_done, uint32_t((j - 1) & 1));  // O is stable, P tile is free again
+                __syncwarp();
                 tc_fence_after();
                 const bool need = m_new > m_ref + 8.0f;
                 if (__any_sync(0xffffffffu, need)) {
@@ -286,7 +300,8 @@ __global__ void __launch_bounds__(kThreads)
             tc_fence_before();
             mbar_arrive(p_full);
         }
-        mbar_wait(pv_done, uint32_t((nkv - 1) & 1));
+        if (lane == 0) mbar_wait(pv_done, uint32_t((nkv - 1) & 1));
+        __syncwarp();
         tc_fence_after();
         const float inv_l = 1.0f / l;
         const int qi = q0 + r;
@@ -318,6 +333,349 @@ __global__ void __launch_bounds__(kThreads)
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc_rt(tmem_base, uint32_t(p.tmem_cols));
+    }
+}
+
+
+// =================================================================================================
+// v2: two query tiles per CTA, ping-pong (head_dim <= 128).
+//
+// The v1 kernel above serialises, per KV tile, MMA -> softmax -> MMA inside one CTA and relies on a
+// second resident CTA for overlap; measured 4.5x slower than it should be at S = 4096.  Here one
+// CTA owns 256 query rows as two 128-row tiles with their own S/O accumulators in TMEM
+// (S0 S1 O0 O1 = 4 x 128 columns) and their own softmax warpgroup, so while warpgroup 0 turns S0
+// into P0 the tensor core is busy with tile 1's GEMMs and vice versa.  The softmax is single-pass:
+// P = exp2(S*scale - m_ref) is computed against the running reference max of earlier tiles while
+// the tile max is tracked on the side; only if some row exceeds the reference by more than 2^8
+// (rare after the first tiles) is O rescaled and the tile recomputed.
+// Warps: 0 TMA, 1 MMA issuer + TMEM owner, 2-5 softmax of tile 0, 6-9 softmax of tile 1.
+constexpr int kThreads2 = 320;
+
+__global__ void __launch_bounds__(kThreads2, 1)
+    k_flash_attn2(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const AttnArgs p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nslab = p.nslab;
+    const int kst = p.k_stages, vst = p.v_stages;
+    const int tile_bytes = nslab * SLAB_BYTES;
+
+    uint8_t* sQ = smem;                        // [2][tile_bytes]
+    uint8_t* sK = sQ + 2 * tile_bytes;         // [kst][tile_bytes]
+    uint8_t* sV = sK + kst * tile_bytes;       // [vst][tile_bytes]
+    uint8_t* sP = sV + vst * tile_bytes;       // [2][2 * SLAB_BYTES]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 4 * SLAB_BYTES);
+    uint64_t* q_full = bars;        // 1
+    uint64_t* s_full = bars + 1;    // 2
+    uint64_t* p_full = bars + 3;    // 2 (128 arrivals each)
+    uint64_t* pv_done = bars + 5;   // 2
+    uint64_t* k_full = bars + 7;    // kst
+    uint64_t* k_empty = k_full + kst;
+    uint64_t* v_full = k_empty + kst;
+    uint64_t* v_empty = v_full + vst;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(v_empty + vst);
+
+    const int q0 = blockIdx.x * (2 * BQ);
+    const int head = blockIdx.y;
+    const int b = blockIdx.z;
+    const int nkv = (p.seq_kv + BKV - 1) / BKV;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            mbar_init(q_full, 1);
+            for (int t = 0; t < 2; ++t) {
+                mbar_init(&s_full[t], 1);
+                mbar_init(&p_full[t], 128);
+                mbar_init(&pv_done[t], 1);
+            }
+            for (int s = 0; s < kst; ++s) {
+                mbar_init(&k_full[s], 1);
+                mbar_init(&k_empty[s], 1);
+            }
+            for (int s = 0; s < vst; ++s) {
+                mbar_init(&v_full[s], 1);
+                mbar_init(&v_empty[s], 1);
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc_rt(tmem_slot, 512u);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---------------- TMA producer
+            mbar_expect_tx(q_full, uint32_t(2 * tile_bytes));
+            for (int t = 0; t < 2; ++t)
+                for (int sl = 0; sl < nslab; ++sl)
+                    tma_load_4d(sQ + t * tile_bytes + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0 + t * BQ, b);
+            int sk = 0, sv = 0;
+            uint32_t phk = 1, phv = 1;
+            for (int j = 0; j < nkv; ++j) {
+                mbar_wait(&k_empty[sk], phk);
+                mbar_expect_tx(&k_full[sk], uint32_t(tile_bytes));
+                for (int sl = 0; sl < nslab; ++sl)
+                    tma_load_4d(sK + sk * tile_bytes + sl * SLAB_BYTES, &tmK, &k_full[sk], sl * 64, head, j * BKV, b);
+                if (++sk == kst) {
+                    sk = 0;
+                    phk ^= 1;
+                }
+                mbar_wait(&v_empty[sv], phv);
+                mbar_expect_tx(&v_full[sv], uint32_t(tile_bytes));
+                for (int sl = 0; sl < nslab; ++sl)
+                    tma_load_4d(sV + sv * tile_bytes + sl * SLAB_BYTES, &tmV, &v_full[sv], sl * 64, head, j * BKV, b);
+                if (++sv == vst) {
+                    sv = 0;
+                    phv ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---------------- MMA issuer (lean: precomputed descriptor halves, unrolled K loops)
+            const int kq = (p.head_dim + 15) / 16;
+            const uint32_t q_lo0 = desc_lo(smem_u32(sQ), 16);
+            const uint32_t k_lo0 = desc_lo(smem_u32(sK), 16);
+            const uint32_t p_lo0 = desc_lo(smem_u32(sP), 16);
+            const uint32_t v_lo0 = desc_lo(smem_u32(sV), SLAB_BYTES);  // MN-major: LBO = slab stride
+            const uint32_t tile_step = uint32_t(tile_bytes) >> 4;
+            const uint32_t p_step = uint32_t(2 * SLAB_BYTES) >> 4;
+            const uint32_t idesc_qk = p.idesc_qk, idesc_pv = p.idesc_pv;
+            auto issue_qk = [&](int t, uint32_t k_lo) {
+                const uint32_t q_lo = q_lo0 + uint32_t(t) * tile_step;
+                const uint32_t tS = tmem_base + uint32_t(t) * 128u;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    if (kk < kq) {
+                        const uint32_t off = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
+                        umma_f16_lohi(tS, q_lo + off, k_lo + off, kDescHiSw128, idesc_qk, kk > 0 ? 1u : 0u);
+                    }
+                }
+            };
+            auto issue_pv = [&](int t, uint32_t v_lo, int kp, uint32_t acc0) {
+                const uint32_t p_lo = p_lo0 + uint32_t(t) * p_step;
+                const uint32_t tO = tmem_base + 256u + uint32_t(t) * 128u;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    if (kk < kp) {
+                        const uint32_t poff = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
+                        umma_f16_lohi(tO, p_lo + poff, v_lo + uint32_t(kk) * (2048 >> 4), kDescHiSw128, idesc_pv,
+                                      kk > 0 ? 1u : acc0);
+                    }
+                }
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after();
+            issue_qk(0, k_lo0);
+            umma_commit(&s_full[0]);
+            issue_qk(1, k_lo0);
+            umma_commit(&s_full[1]);
+            if (nkv == 1 || kst > 1) {
+                // K[0] is free once both S tiles are computed (only matters for the ring bookkeeping)
+            }
+            umma_commit(&k_empty[0]);
+            int sk = (kst > 1) ? 1 : 0;           // ring slot of K[j+1]
+            uint32_t phk = (kst > 1) ? 0u : 1u;   // its full-barrier parity
+            int sv = 0;
+            uint32_t phv = 0;
+            for (int j = 0; j < nkv; ++j) {
+                const bool more = j + 1 < nkv;
+                const int kv_valid = min(BKV, p.seq_kv - j * BKV);
+                const int kp = (kv_valid + 15) >> 4;
+                const uint32_t acc0 = j > 0 ? 1u : 0u;
+                const uint32_t k_lo = k_lo0 + uint32_t(sk) * tile_step;
+                const uint32_t v_lo = v_lo0 + uint32_t(sv) * tile_step;
+                // ---- tile 0: its softmax has drained S0 and published P0
+                mbar_wait(&p_full[0], uint32_t(j & 1));
+                tc_fence_after();
+                if (more) {
+                    mbar_wait(&k_full[sk], phk);
+                    tc_fence_after();
+                    issue_qk(0, k_lo);
+                    umma_commit(&s_full[0]);
+                }
+                mbar_wait(&v_full[sv], phv);
+                tc_fence_after();
+                issue_pv(0, v_lo, kp, acc0);
+                umma_commit(&pv_done[0]);
+                // ---- tile 1
+                mbar_wait(&p_full[1], uint32_t(j & 1));
+                tc_fence_after();
+                if (more) {
+                    issue_qk(1, k_lo);
+                    umma_commit(&s_full[1]);
+                    umma_commit(&k_empty[sk]);
+                    if (++sk == kst) {
+                        sk = 0;
+                        phk ^= 1;
+                    }
+                }
+                issue_pv(1, v_lo, kp, acc0);
+                umma_commit(&v_empty[sv]);
+                umma_commit(&pv_done[1]);
+                if (++sv == vst) {
+                    sv = 0;
+                    phv ^= 1;
+                }
+            }
+        }
+    } else {
+        // ---------------- softmax warpgroups: thread <-> query row of tile t
+        const int t = (warp - 2) >> 2;
+        const int q = warp & 3;  // TMEM lane quadrant this warp may touch
+        const int r = q * 32 + lane;
+        const uint32_t lane_off = uint32_t(q * 32) << 16;
+        const uint32_t tS = tmem_base + lane_off + uint32_t(t) * 128u;
+        const uint32_t tO = tmem_base + lane_off + 256u + uint32_t(t) * 128u;
+        uint8_t* prow = sP + t * (2 * SLAB_BYTES) + (r >> 3) * 1024 + (r & 7) * 128;
+        const int rsw = r & 7;
+        const float scale = p.scale_log2;
+
+        float m_ref = -INFINITY;
+        float l = 0.0f;
+        for (int j = 0; j < nkv; ++j) {
+            const int kv_valid = min(BKV, p.seq_kv - j * BKV);
+            if (lane == 0) mbar_wait(&s_full[t], uint32_t(j & 1));
+            __syncwarp();
+            tc_fence_after();
+            if (j == 0) {
+                // first tile: the reference max is this tile's row max
+                float mx = -INFINITY;
+#pragma unroll 1
+                for (int c = 0; c < BKV; c += 32) {
+                    if (c >= kv_valid) break;  // warp-uniform
+                    uint32_t v[32];
+                    tmem_ld32(tS + c, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c + i < kv_valid) mx = fmaxf(mx, __uint_as_float(v[i]));
+                }
+                m_ref = mx * scale;
+            } else {
+                if (lane == 0) mbar_wait(&pv_done[t], uint32_t((j - 1) & 1));  // O stable, P tile free
+                __syncwarp();
+                tc_fence_after();
+            }
+            // P = exp2(S*scale - m_ref) -> fp16 -> swizzled smem; returns row sum, tracks max exponent
+            float xmax = -INFINITY;
+            auto emit_p = [&]() -> float {
+                float lsum = 0.0f;
+                xmax = -INFINITY;
+#pragma unroll 1
+                for (int c = 0; c < BKV; c += 32) {
+                    uint32_t pk[16];
+                    if (c < kv_valid) {
+                        uint32_t v[32];
+                        tmem_ld32(tS + c, v);
+                        tmem_ld_wait();
+                        if (c + 32 <= kv_valid) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 2) {
+                                const float x0 = fmaf(__uint_as_float(v[i]), scale, -m_ref);
+                                const float x1 = fmaf(__uint_as_float(v[i + 1]), scale, -m_ref);
+                                xmax = fmaxf(xmax, fmaxf(x0, x1));
+                                const float e0 = ex2(x0), e1 = ex2(x1);
+                                lsum += e0 + e1;
+                                pk[i >> 1] = pack_h2(e0, e1);
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 2) {
+                                const bool ok0 = c + i < kv_valid, ok1 = c + i + 1 < kv_valid;
+                                const float x0 = ok0 ? fmaf(__uint_as_float(v[i]), scale, -m_ref) : -INFINITY;
+                                const float x1 = ok1 ? fmaf(__uint_as_float(v[i + 1]), scale, -m_ref) : -INFINITY;
+                                xmax = fmaxf(xmax, fmaxf(x0, x1));
+                                const float e0 = ok0 ? ex2(x0) : 0.0f, e1 = ok1 ? ex2(x1) : 0.0f;
+                                lsum += e0 + e1;
+                                pk[i >> 1] = pack_h2(e0, e1);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) pk[i] = 0u;
+                    }
+                    uint8_t* slab = prow + (c >> 6) * SLAB_BYTES;
+                    const int cc0 = (c & 63) >> 3;
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        *reinterpret_cast<uint4*>(slab + (((cc0 + g) ^ rsw) << 4)) =
+                            make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+                }
+                return lsum;
+            };
+            float lsum = emit_p();
+            if (j > 0) {
+                const bool need = xmax > 8.0f;  // this row outgrew the reference: rescale and redo
+                if (__any_sync(0xffffffffu, need)) {
+                    const float alpha = need ? ex2(-xmax) : 1.0f;
+                    if (need) m_ref += xmax;
+#pragma unroll 1
+                    for (int c = 0; c < p.dpad; c += 16) {
+                        uint32_t o[16];
+                        tmem_ld16(tO + c, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st16(tO + c, o);
+                    }
+                    tmem_st_wait();
+                    l *= alpha;
+                    lsum = emit_p();
+                }
+            }
+            l += lsum;
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(&p_full[t]);
+        }
+        if (lane == 0) mbar_wait(&pv_done[t], uint32_t((nkv - 1) & 1));
+        __syncwarp();
+        tc_fence_after();
+        const float inv_l = 1.0f / l;
+        const int qi = q0 + t * BQ + r;
+        __half* orow = p.out + (long long)b * p.o_stride_b + (long long)qi * p.o_stride_s +
+                       (long long)head * p.head_dim;
+#pragma unroll 1
+        for (int c = 0; c < p.dpad; c += 16) {
+            uint32_t o[16];
+            tmem_ld16(tO + c, o);
+            tmem_ld_wait();
+            if (qi < p.seq_q) {
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    if (c + g * 8 < p.head_dim) {
+                        const int i = g * 8;
+                        *reinterpret_cast<uint4*>(orow + c + i) = make_uint4(
+                            pack_h2(__uint_as_float(o[i]) * inv_l, __uint_as_float(o[i + 1]) * inv_l),
+                            pack_h2(__uint_as_float(o[i + 2]) * inv_l, __uint_as_float(o[i + 3]) * inv_l),
+                            pack_h2(__uint_as_float(o[i + 4]) * inv_l, __uint_as_float(o[i + 5]) * inv_l),
+                            pack_h2(__uint_as_float(o[i + 6]) * inv_l, __uint_as_float(o[i + 7]) * inv_l));
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_rt(tmem_base, 512u);
     }
 }
 
@@ -370,16 +728,30 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
                       p->v_stride_s, p->v_stride_h);
     if (rc) return rc;
 
-    const int tile_bytes = a.nslab * SLAB_BYTES;
-    const int smem = tile_bytes * (1 + 2 * a.kv_stages) + 2 * SLAB_BYTES + 1024 + 256;
     static bool configured[64] = {false};
     int dev = 0;
     SW_CUDA_OK(cudaGetDevice(&dev));
     if (dev < 64 && !configured[dev]) {
-        SW_CUDA_OK(cudaFuncSetAttribute(k_flash_attn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        227 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_flash_attn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_flash_attn2, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         configured[dev] = true;
     }
+    const int tile_bytes = a.nslab * SLAB_BYTES;
+    static int force_v1 = -1;
+    if (force_v1 < 0) force_v1 = getenv("SW_ATTN_V1") ? 1 : 0;
+    if (!force_v1 && a.nslab <= 2 && p->seq_q > BQ) {
+        // two query tiles per CTA, ping-pong softmax warpgroups
+        a.k_stages = nkv > 1 ? 2 : 1;
+        a.v_stages = (a.nslab == 1 && nkv > 1) ? 2 : 1;
+        const int smem2 = tile_bytes * (2 + a.k_stages + a.v_stages) + 4 * SLAB_BYTES + 1024 + 256;
+        if (smem2 <= 227 * 1024) {
+            dim3 grid2((p->seq_q + 2 * BQ - 1) / (2 * BQ), p->heads, p->batch);
+            k_flash_attn2<<<grid2, kThreads2, smem2, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, a);
+            SW_CUDA_OK(cudaGetLastError());
+            return 0;
+        }
+    }
+    const int smem = tile_bytes * (1 + 2 * a.kv_stages) + 2 * SLAB_BYTES + 1024 + 256;
     if (smem > 227 * 1024) return swh::fail(-1, "sw_flash_attn: shared memory budget exceeded (%d)", smem);
     dim3 grid((p->seq_q + BQ - 1) / BQ, p->heads, p->batch);
     k_flash_attn<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, a);
