@@ -80,6 +80,20 @@ class SchedParams(C.Structure):
     ]
 
 
+class Peers(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("epoch", C.c_int32),
+                ("peer", C.c_void_p * 8), ("flags", C.c_void_p * 8)]
+
+
+def make_peers(world, rank, epoch, peer_ptrs, flag_ptrs) -> Peers:
+    p = Peers()
+    p.world, p.rank, p.epoch = world, rank, epoch
+    for d in range(world):
+        p.peer[d] = peer_ptrs[d] if peer_ptrs is not None else None
+        p.flags[d] = flag_ptrs[d]
+    return p
+
+
 def available() -> bool:
     return LIB_PATH.exists()
 
@@ -98,10 +112,23 @@ def lib() -> C.CDLL:
                 "sw_igemm", "sw_flash_attn", "sw_groupnorm_nhwc", "sw_layernorm", "sw_upsample2x_nhwc",
                 "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
                 "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8", "sw_softmax_rows",
+                "sw_igemm_ag", "sw_igemm_rs", "sw_rs_reduce", "sw_peer_signal", "sw_peer_wait",
+                "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist",
             ):
                 getattr(l, name).restype = C.c_int
             l.sw_igemm.argtypes = [C.POINTER(IGemmParams), C.c_void_p]
             l.sw_flash_attn.argtypes = [C.POINTER(AttnParams), C.c_void_p]
+            l.sw_igemm_ag.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p]
+            l.sw_igemm_rs.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p, C.c_void_p]
+            l.sw_rs_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, C.POINTER(Peers), C.c_void_p]
+            l.sw_peer_signal.argtypes = [C.POINTER(Peers), C.c_void_p]
+            l.sw_peer_wait.argtypes = [C.POINTER(Peers), C.c_void_p]
+            l.sw_flash_attn_gather.argtypes = [C.POINTER(AttnParams), C.POINTER(Peers), C.POINTER(C.c_void_p), C.c_int,
+                                               C.c_void_p]
+            l.sw_groupnorm_nhwc_dist.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
+                                                 C.c_void_p, C.POINTER(Peers), C.c_void_p]
             l.sw_groupnorm_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                             C.c_int, C.c_void_p, C.c_void_p]
@@ -337,4 +364,86 @@ def sched_step(*, eps, n_cond, rows, c, eps_ld, g_text, g_image, x, x0_prev, noi
 def image_to_u8(x_nhwc, out, pixels, c_pad):
     _check(lib().sw_image_to_u8(_ptr(x_nhwc), _ptr(out), pixels, c_pad, _stream()), "sw_image_to_u8")
     _count()
+    return out
+
+
+# --------------------------------------------------------------------------- fused collectives
+def _gemm_params(wgt, out_ptr, ldc, m_total, k, bias=None, residual=None, act=ACT_NONE):
+    p = IGemmParams()
+    p.a1 = None
+    p.c1, p.c2 = k, 0
+    p.n, p.h, p.w = 1, 1, m_total
+    p.kh, p.kw, p.pad = 1, 1, 0
+    p.wgt = wgt.data_ptr()
+    p.cout = wgt.shape[0]
+    p.bias = _ptr(bias)
+    p.residual = _ptr(residual)
+    p.ldr = 0 if residual is None else residual.stride(-2)
+    p.out = out_ptr
+    p.ldc = ldc
+    p.act = act
+    p.out_scale = 1.0
+    return p
+
+
+def igemm_ag(wgt, out, peers: Peers, *, m_local, k, bias=None, residual=None, act=ACT_NONE):
+    """out[world*m_local, N] = concat_d(X_d) @ wgt^T, A tiles loaded from the owning ranks."""
+    p = _gemm_params(wgt, out.data_ptr(), out.stride(-2), m_local * peers.world, k, bias, residual, act)
+    _check(lib().sw_igemm_ag(C.byref(p), C.byref(peers), m_local, _stream()), "sw_igemm_ag")
+    _count()
+    return out
+
+
+def igemm_rs(x, wgt, peers: Peers, ticket, *, m_local, ldc):
+    """Partial GEMM over this rank's K shard, rows pushed to their owners' staging slots."""
+    p = _gemm_params(wgt, None, ldc, m_local * peers.world, x.shape[-1])
+    p.a1 = x.data_ptr()
+    _check(lib().sw_igemm_rs(C.byref(p), C.byref(peers), m_local, ticket.data_ptr(), _stream()), "sw_igemm_rs")
+    _count()
+
+
+def rs_reduce(staging, out, peers: Peers, *, m_local, ncols, bias=None, residual=None):
+    _check(lib().sw_rs_reduce(staging.data_ptr(), out.data_ptr(), _ptr(bias), _ptr(residual), m_local, ncols,
+                              staging.stride(-2), out.stride(-2), 0 if residual is None else residual.stride(-2),
+                              C.byref(peers), _stream()), "sw_rs_reduce")
+    _count()
+    return out
+
+
+def peer_signal(peers: Peers):
+    _check(lib().sw_peer_signal(C.byref(peers), _stream()), "sw_peer_signal")
+    _count()
+
+
+def peer_wait(peers: Peers):
+    _check(lib().sw_peer_wait(C.byref(peers), _stream()), "sw_peer_wait")
+    _count()
+
+
+def flash_attn_gather(q, k_local, v_local, out, kpeers: Peers, v_ptrs, *, batch, heads, seq_q, s_local, head_dim,
+                      scale=None):
+    """q: [b, sq, h, d] view; k_local/v_local: this rank's [b, s_local, h, d] views (strides are
+    taken from them; every rank uses the same layout)."""
+    p = AttnParams()
+    p.q = q.data_ptr()
+    p.q_stride_b, p.q_stride_s, p.q_stride_h = q.stride(0), q.stride(1), q.stride(2)
+    p.k_stride_b, p.k_stride_s, p.k_stride_h = k_local.stride(0), k_local.stride(1), k_local.stride(2)
+    p.v_stride_b, p.v_stride_s, p.v_stride_h = v_local.stride(0), v_local.stride(1), v_local.stride(2)
+    p.out = out.data_ptr()
+    p.o_stride_b, p.o_stride_s = out.stride(0), out.stride(1)
+    p.batch, p.heads, p.seq_q, p.seq_kv, p.head_dim = batch, heads, seq_q, s_local * kpeers.world, head_dim
+    p.scale = float(scale if scale is not None else head_dim ** -0.5)
+    arr = (C.c_void_p * 8)(*[v_ptrs[d] if d < kpeers.world else None for d in range(8)])
+    _check(lib().sw_flash_attn_gather(C.byref(p), C.byref(kpeers), arr, s_local, _stream()), "sw_flash_attn_gather")
+    _count()
+    return out
+
+
+def groupnorm_dist(x, gamma, beta, out, peers: Peers, *, n, hw, groups, eps, silu, stats, x2=None):
+    c1 = x.shape[-1]
+    c2 = 0 if x2 is None else x2.shape[-1]
+    _check(lib().sw_groupnorm_nhwc_dist(_ptr(x), _ptr(x2), _ptr(out), _ptr(gamma), _ptr(beta), n, hw, c1, c2, groups,
+                                        eps, int(silu), _ptr(stats), C.byref(peers), _stream()),
+           "sw_groupnorm_nhwc_dist")
+    _count(2)
     return out

@@ -29,6 +29,9 @@ struct AttnArgs {
     int batch, heads, seq_q, seq_kv, head_dim;
     int nslab, dpad, kv_stages, tmem_cols;
     int k_stages, v_stages;  // v2 kernel: independent K and V rings
+    // cross-GPU K/V gather (sequence parallel): K/V rows [src*s_local, (src+1)*s_local) live on rank src
+    int world, rank, epoch, s_local;
+    const int* flags_local;  // this rank's int32[world] epoch flags
     float scale_log2;
     __half* out;
     long long o_stride_b, o_stride_s;
@@ -351,9 +354,25 @@ __global__ void __launch_bounds__(kThreads)
 // Warps: 0 TMA, 1 MMA issuer + TMEM owner, 2-5 softmax of tile 0, 6-9 softmax of tile 1.
 constexpr int kThreads2 = 320;
 
-__global__ void __launch_bounds__(kThreads2, 1)
-    k_flash_attn2(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                  const __grid_constant__ CUtensorMap tmV, const AttnArgs p) {
+struct KvMaps {
+    CUtensorMap k[8];
+    CUtensorMap v[8];
+};
+
+__device__ __forceinline__ void attn_wait_flag_ge(const int* p, int v) {
+    int cur;
+    for (unsigned i = 0;; ++i) {
+        asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(cur) : "l"(p) : "memory");
+        if (cur >= v) break;
+        if (i > (1u << 27)) __trap();
+        __nanosleep(64);
+    }
+}
+
+// tmKs / tmVs: one tensor map (local attention) or one per rank (K/V gathered in-kernel: the tile
+// loop starts at this rank's own rows and walks the peers' shards through their NVLink mappings).
+__device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtensorMap* tmKs,
+                                           const CUtensorMap* tmVs, const AttnArgs& p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -386,8 +405,8 @@ __global__ void __launch_bounds__(kThreads2, 1)
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
-        tma_prefetch_desc(&tmK);
-        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(tmKs);
+        tma_prefetch_desc(tmVs);
     }
     if (warp == 1) {
         if (lane == 0) {
@@ -424,11 +443,25 @@ __global__ void __launch_bounds__(kThreads2, 1)
                     tma_load_4d(sQ + t * tile_bytes + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0 + t * BQ, b);
             int sk = 0, sv = 0;
             uint32_t phk = 1, phv = 1;
+            const int per_rank = p.world > 1 ? p.s_local / BKV : nkv;
+            int jj = p.world > 1 ? p.rank * per_rank : 0;  // local shard first
+            int last_src = p.world > 1 ? p.rank : 0;
             for (int j = 0; j < nkv; ++j) {
+                int src = 0, row = jj * BKV;
+                if (p.world > 1) {
+                    src = jj / per_rank;
+                    row = (jj - src * per_rank) * BKV;
+                    if (src != last_src) {  // first touch of a peer's shard: wait until it is published
+                        attn_wait_flag_ge(p.flags_local + src, p.epoch);
+                        last_src = src;
+                    }
+                }
+                const CUtensorMap* mk = tmKs + src;
+                const CUtensorMap* mv = tmVs + src;
                 mbar_wait(&k_empty[sk], phk);
                 mbar_expect_tx(&k_full[sk], uint32_t(tile_bytes));
                 for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sK + sk * tile_bytes + sl * SLAB_BYTES, &tmK, &k_full[sk], sl * 64, head, j * BKV, b);
+                    tma_load_4d(sK + sk * tile_bytes + sl * SLAB_BYTES, mk, &k_full[sk], sl * 64, head, row, b);
                 if (++sk == kst) {
                     sk = 0;
                     phk ^= 1;
@@ -436,11 +469,12 @@ __global__ void __launch_bounds__(kThreads2, 1)
                 mbar_wait(&v_empty[sv], phv);
                 mbar_expect_tx(&v_full[sv], uint32_t(tile_bytes));
                 for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sV + sv * tile_bytes + sl * SLAB_BYTES, &tmV, &v_full[sv], sl * 64, head, j * BKV, b);
+                    tma_load_4d(sV + sv * tile_bytes + sl * SLAB_BYTES, mv, &v_full[sv], sl * 64, head, row, b);
                 if (++sv == vst) {
                     sv = 0;
                     phv ^= 1;
                 }
+                if (++jj == nkv) jj = 0;
             }
         }
     } else if (warp == 1) {
@@ -679,6 +713,18 @@ __global__ void __launch_bounds__(kThreads2, 1)
     }
 }
 
+__global__ void __launch_bounds__(kThreads2, 1)
+    k_flash_attn2(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const AttnArgs p) {
+    attn2_body(tmQ, &tmK, &tmV, p);
+}
+
+__global__ void __launch_bounds__(kThreads2, 1)
+    k_flash_attn2_gather(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ KvMaps kv,
+                         const AttnArgs p) {
+    attn2_body(tmQ, kv.k, kv.v, p);
+}
+
 int make_qkv_map(CUtensorMap* m, const void* base, int d, int heads, int seq, int batch,
                  long long sb, long long ss, long long sh) {
     const uint64_t dims[4] = {uint64_t(d), uint64_t(heads), uint64_t(seq), uint64_t(batch)};
@@ -755,6 +801,70 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
     if (smem > 227 * 1024) return swh::fail(-1, "sw_flash_attn: shared memory budget exceeded (%d)", smem);
     dim3 grid((p->seq_q + BQ - 1) / BQ, p->heads, p->batch);
     k_flash_attn<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, a);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpeers, const void* const* v_ptrs,
+                                    int s_local, void* stream) {
+    if (!p || !p->q || !p->out || !kpeers || !v_ptrs) return swh::fail(-1, "sw_flash_attn_gather: null argument");
+    const int world = kpeers->world;
+    if (world < 1 || world > 8) return swh::fail(-1, "sw_flash_attn_gather: world=%d", world);
+    if (p->head_dim <= 0 || p->head_dim % 8 || p->head_dim > 128)
+        return swh::fail(-1, "sw_flash_attn_gather: head_dim=%d unsupported (multiple of 8, <= 128)", p->head_dim);
+    if (s_local <= 0 || s_local % BKV || p->seq_kv != s_local * world)
+        return swh::fail(-1, "sw_flash_attn_gather: s_local must be a multiple of 128 and seq_kv == world*s_local");
+    AttnArgs a;
+    memset(&a, 0, sizeof(a));
+    a.batch = p->batch;
+    a.heads = p->heads;
+    a.seq_q = p->seq_q;
+    a.seq_kv = p->seq_kv;
+    a.head_dim = p->head_dim;
+    a.nslab = (p->head_dim + 63) / 64;
+    a.dpad = (p->head_dim + 15) / 16 * 16;
+    a.scale_log2 = p->scale * 1.4426950408889634f;
+    a.out = static_cast<__half*>(p->out);
+    a.o_stride_b = p->o_stride_b;
+    a.o_stride_s = p->o_stride_s;
+    a.idesc_qk = sw::umma_idesc(128, 128, 0, 0, 0);
+    a.idesc_pv = sw::umma_idesc(128, a.dpad, 0, 0, 1);
+    a.world = world;
+    a.rank = kpeers->rank;
+    a.epoch = kpeers->epoch;
+    a.s_local = s_local;
+    a.flags_local = kpeers->flags[kpeers->rank];
+    const int nkv = p->seq_kv / BKV;
+    a.k_stages = nkv > 1 ? 2 : 1;
+    a.v_stages = (a.nslab == 1 && nkv > 1) ? 2 : 1;
+
+    CUtensorMap tq;
+    KvMaps kv;
+    int rc = make_qkv_map(&tq, p->q, p->head_dim, p->heads, p->seq_q, p->batch, p->q_stride_b, p->q_stride_s,
+                          p->q_stride_h);
+    if (rc) return rc;
+    for (int d = 0; d < 8; ++d) {
+        const int s = d < world ? d : 0;
+        rc = make_qkv_map(&kv.k[d], kpeers->peer[s], p->head_dim, p->heads, s_local, p->batch, p->k_stride_b,
+                          p->k_stride_s, p->k_stride_h);
+        if (rc) return rc;
+        rc = make_qkv_map(&kv.v[d], v_ptrs[s], p->head_dim, p->heads, s_local, p->batch, p->v_stride_b,
+                          p->v_stride_s, p->v_stride_h);
+        if (rc) return rc;
+    }
+    static bool configured[64] = {false};
+    int dev = 0;
+    SW_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 64 && !configured[dev]) {
+        SW_CUDA_OK(cudaFuncSetAttribute(k_flash_attn2_gather, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        227 * 1024));
+        configured[dev] = true;
+    }
+    const int tile_bytes = a.nslab * SLAB_BYTES;
+    const int smem2 = tile_bytes * (2 + a.k_stages + a.v_stages) + 4 * SLAB_BYTES + 1024 + 256;
+    if (smem2 > 227 * 1024) return swh::fail(-1, "sw_flash_attn_gather: shared memory budget exceeded");
+    dim3 grid2((p->seq_q + 2 * BQ - 1) / (2 * BQ), p->heads, p->batch);
+    k_flash_attn2_gather<<<grid2, kThreads2, smem2, static_cast<cudaStream_t>(stream)>>>(tq, kv, a);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -15,7 +15,7 @@
 // defined in norm.cu: statistics + apply kernels on a caller-chosen scratch pointer
 int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                         int n, int hw, int c1, int c2, int groups, float eps, int silu,
-                        float* scratch, cudaStream_t st);
+                        float* scratch, cudaStream_t st, const sw_peers* peers);
 
 namespace {
 
@@ -68,5 +68,5 @@ extern "C" int sw_groupnorm_nhwc_static(const void* x, const void* x2, void* y, 
     // The buffer still holds the previous call's numbers.  Only the per-image ticket counters
     // have to start at zero, and the launch below clears exactly those on `stream` first.
     return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, scratch,
-                               static_cast<cudaStream_t>(stream));
+                               static_cast<cudaStream_t>(stream), nullptr);
 }

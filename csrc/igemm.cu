@@ -50,7 +50,31 @@ struct IGemmArgs {
     int kb_per_split;   // k-blocks per split
     unsigned int* tickets;  // [tiles] arrival counters (split-K), self-resetting
     float* partials;        // [tile][split][bn/32][128][32] fp32
+    // ---- fused collectives (plain GEMMs only; see sw_igemm_ag / sw_igemm_rs)
+    int mode;               // 0 local, 1 all-gather fused into the A loads, 2 reduce-scatter push epilogue
+    int world, rank, epoch;
+    int m_local;            // rows of the activation shard each rank owns
+    __half* rs_out[8];      // mode 2: rank d's staging buffer [world][m_local][ldc]
+    int* flags[8];          // rank d's int32[world] epoch flags
+    unsigned int* rs_ticket;
 };
+
+struct AgMaps {
+    CUtensorMap m[8];       // mode 1: tensor map of every rank's activation shard (peer mappings)
+};
+
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
+    int cur;
+    for (unsigned i = 0;; ++i) {
+        asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(cur) : "l"(p) : "memory");
+        if (cur >= v) break;
+        if (i > (1u << 27)) __trap();
+        __nanosleep(64);
+    }
+}
 
 // ---------------------------------------------------------------- raw-address PTX helpers
 // The producer and MMA roles are single threads: every instruction they execute sits on the
@@ -204,6 +228,12 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
 
     // spatial tile -> origin pixel
     int t = blockIdx.x;
+    if (p.mode != 0) {
+        // fused collectives: rotate the tile order by rank so that (all-gather) local rows are
+        // consumed first and (reduce-scatter) the ranks push to different owners at any moment
+        const int per_rank = p.m_local / BM;
+        t = (t + (p.rank + (p.mode == 2 ? 1 : 0)) * per_rank) % int(gridDim.x);
+    }
     const int tx = t % p.tiles_x;
     t /= p.tiles_x;
     const int ty = t % p.tiles_y;
@@ -211,6 +241,16 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
     const int col0 = blockIdx.y * BN;
     const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
+    // mode 1 (all-gather fused): this tile's rows live on rank `ag_src`; they are fetched straight
+    // from that rank's memory by TMA over NVLink, local rows first (tile order is rotated by rank).
+    const CUtensorMap* pA1 = &tmA1;
+    int ax0 = x0;
+    int ag_src = -1;
+    if (p.mode == 1) {
+        ag_src = x0 / p.m_local;
+        ax0 = x0 - ag_src * p.m_local;
+        pA1 = &tmA1 + ag_src;  // tmA1 is element 0 of an AgMaps array
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA1);
@@ -256,13 +296,14 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             uint32_t sa = smem0, fb = full0, eb = empty0;
             int s = 0;
             uint32_t ph = 1;
+            if (p.mode == 1 && ag_src != p.rank) wait_flag_ge(p.flags[p.rank] + ag_src, p.epoch);
             for (int it = it_begin; it < it_end; ++it) {
                 bar_wait(eb, ph);
                 // both CTAs' loads complete on the leader's barrier; only the leader arms it
                 if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                 int kcol;
                 if (j < nkb1) {
-                    tma4<PAIR>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad, y0 + ky - p.pad, n0);
                     kcol = tapbase + j * BK;
                 } else {
                     tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
@@ -501,7 +542,14 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                             f[2 * j + 1] += t2.y;
                         }
                     }
-                    *reinterpret_cast<uint4*>(p.out + m * p.ldc + col) =
+                    __half* dst = p.out + m * p.ldc + col;
+                    if (p.mode == 2) {
+                        // reduce-scatter push: the partial row goes to its owner's staging slot [rank]
+                        const int d = int(m) / p.m_local;
+                        const size_t lr = size_t(p.rank) * p.m_local + (m - size_t(d) * p.m_local);
+                        dst = p.rs_out[d] + lr * p.ldc + col;
+                    }
+                    *reinterpret_cast<uint4*>(dst) =
                         make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
                                    pack_h2(f[6], f[7]));
                 }
@@ -509,6 +557,20 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         }
     }
 
+    if (p.mode == 2) {
+        // every CTA publishes its pushes system-wide; the CTA that finishes last raises this
+        // rank's epoch flag on every peer (their reduce kernels poll it)
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int total = gridDim.x * gridDim.y;
+            if (atomicAdd(p.rs_ticket, 1u) == total - 1u) {
+                *p.rs_ticket = 0u;
+                __threadfence_system();
+                for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + p.rank, p.epoch);
+            }
+        }
+    }
     tc_fence_before();
     cta_or_cluster_sync<PAIR>();  // (pair: both epilogues have drained TMEM)
     if (warp == 1) {
@@ -521,6 +583,11 @@ __global__ void __launch_bounds__(kThreads)
     k_igemm(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
             const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
     igemm_body<false>(tmA1, tmA2, tmB, p);
+}
+
+__global__ void __launch_bounds__(kThreads)
+    k_igemm_ag(const __grid_constant__ AgMaps maps, const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    igemm_body<false>(maps.m[0], maps.m[0], tmB, p);
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -604,8 +671,19 @@ constexpr int kMaxSplitTiles = 4096;
 
 }  // namespace
 
-extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
-    if (!p || !p->a1 || !p->wgt || !p->out) return swh::fail(-1, "sw_igemm: null argument");
+static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode, int m_local,
+                      unsigned int* ticket, void* stream) {
+    if (!p || !p->wgt || (mode != 1 && !p->a1) || (mode != 2 && !p->out))
+        return swh::fail(-1, "sw_igemm: null argument");
+    if (mode != 0) {
+        if (!peers || peers->world < 1 || peers->world > 8) return swh::fail(-1, "sw_igemm: bad peer description");
+        if (p->kh != 1 || p->kw != 1 || p->n != 1 || p->h != 1 || p->c2 != 0 || p->act == SW_ACT_GEGLU)
+            return swh::fail(-1, "sw_igemm: fused collectives are defined for plain GEMMs");
+        if (m_local <= 0 || m_local % 128 || p->w != m_local * peers->world)
+            return swh::fail(-1, "sw_igemm: m_local=%d must be a multiple of 128 and w == world*m_local", m_local);
+        if (mode == 2 && (p->bias || p->row_bias || p->residual || p->act != SW_ACT_NONE || !ticket))
+            return swh::fail(-1, "sw_igemm_rs: the push epilogue carries raw partial sums only");
+    }
     if (p->c1 <= 0 || p->c1 % 8 || p->c2 % 8 || p->c2 < 0 || (p->c2 > 0 && !p->a2))
         return swh::fail(-1, "sw_igemm: channel counts must be positive multiples of 8 (c1=%d c2=%d)",
                          p->c1, p->c2);
@@ -645,6 +723,19 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     a.act = p->act;
     a.out_scale = p->out_scale == 0.0f ? 1.0f : p->out_scale;
     a.bf16 = p->bf16;
+    a.mode = mode;
+    if (mode != 0) {
+        a.world = peers->world;
+        a.rank = peers->rank;
+        a.epoch = peers->epoch;
+        a.m_local = m_local;
+        a.rs_ticket = ticket;
+        for (int d = 0; d < peers->world; ++d) {
+            a.flags[d] = peers->flags[d];
+            if (mode == 2) a.rs_out[d] = static_cast<__half*>(peers->peer[d]);
+        }
+        if (mode == 2) a.out = a.rs_out[peers->rank];
+    }
 
     const int ktotal = p->kh * p->kw * (p->c1 + p->c2);
     const int kblocks = p->kh * p->kw * ((p->c1 + 63) / 64 + (p->c2 + 63) / 64);
@@ -672,9 +763,9 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
 
     // ---- CTA pairs: with >= 2 pixel tiles per weight tile the layer runs as 256 x BN tiles on
     // tcgen05 cta_group::2 (halves every SM's shared-memory reads of the weight operand).
-    bool pair = grid_x >= 32 && bn >= 192;  // measured: pays off for wide tiles with many pixel tiles
+    bool pair = grid_x >= 32 && bn >= 192 && mode == 0;  // measured: pays off for wide tiles with many pixel tiles
     if (p->cta_pair == 1) pair = false;
-    if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64;
+    if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64 && mode == 0;
 
     // ---- pipeline depth: two CTAs per SM (epilogue of one overlaps the main loop of the other)
     // when three stages fit in ~110 KB, else one CTA with a deeper ring.
@@ -703,7 +794,7 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
     const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 32;
-    if (p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
+    if (mode == 0 && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
         int want = int(slots / ctas);
@@ -723,7 +814,19 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
     }
 
     CUtensorMap tA1, tA2, tB;
-    {
+    AgMaps ag;
+    if (mode == 1) {
+        for (int d = 0; d < peers->world; ++d) {
+            const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(m_local), 1, 1};
+            const uint64_t lda = p->a_ld > 0 ? uint64_t(p->a_ld) : uint64_t(p->c1);
+            const uint64_t str[3] = {lda * 2, uint64_t(m_local) * lda * 2, uint64_t(m_local) * lda * 2};
+            const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
+            int rc = swh::encode_tmap_f16(&ag.m[d], peers->peer[d], 4, dims, str, box);
+            if (rc) return rc;
+        }
+        for (int d = peers->world; d < 8; ++d) ag.m[d] = ag.m[0];
+        tA1 = ag.m[0];
+    } else {
         const uint64_t lda = p->a_ld > 0 ? uint64_t(p->a_ld) : uint64_t(p->c1);
         const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
         const uint64_t str[3] = {lda * 2, uint64_t(p->w) * lda * 2, uint64_t(p->h) * p->w * lda * 2};
@@ -748,5 +851,33 @@ extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
         if (rc) return rc;
     }
+    if (mode == 1) {
+        const int stage_bytes2 = A_STAGE_BYTES + a.bn * BK * 2;
+        const int smem = a.stages * stage_bytes2 + 1024 + 256;
+        static bool configured[64] = {false};
+        int dev = 0;
+        SW_CUDA_OK(cudaGetDevice(&dev));
+        if (dev < 64 && !configured[dev]) {
+            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+            configured[dev] = true;
+        }
+        dim3 grid(grid_x, (a.cout + a.bn - 1) / a.bn, 1);
+        k_igemm_ag<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(ag, tB, a);
+        SW_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
     return launch(a, tA1, tA2, tB, grid_x, pair, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {
+    return igemm_impl(p, nullptr, 0, 0, nullptr, stream);
+}
+
+extern "C" int sw_igemm_ag(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* stream) {
+    return igemm_impl(p, peers, 1, m_local, nullptr, stream);
+}
+
+extern "C" int sw_igemm_rs(const sw_igemm_params* p, const sw_peers* peers, int m_local,
+                           unsigned int* ticket, void* stream) {
+    return igemm_impl(p, peers, 2, m_local, ticket, stream);
 }

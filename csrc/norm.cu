@@ -9,6 +9,33 @@ namespace {
 
 using namespace sw;
 
+// Cross-GPU extension of GroupNorm (sequence / patch parallel: every rank holds H/world rows of
+// the feature map, the statistics are global).  The all-reduce of the per-(image, group) sums is
+// done by the GroupNorm kernels themselves over NVLink peer mappings: the statistics kernel's
+// finishing CTA stores its sums into every peer's slot and raises an epoch flag with
+// st.release.sys; the apply kernel polls the flags with ld.acquire.sys and adds the slots in rank
+// order (deterministic).  world == 1 disables all of it.
+struct GnDist {
+    int world, rank, epoch;
+    float* peer_stats[8];  // rank d: float [2 (epoch parity)][world][n][groups][2]
+    int* peer_flags[8];    // rank d: int [world], slot [src] written by rank src
+};
+
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
+    for (unsigned i = 0; ld_acquire_sys(p) < v; ++i) {
+        if (i > (1u << 27)) __trap();  // a lost peer must not hang the box
+        __nanosleep(64);
+    }
+}
+
 // ---- GroupNorm statistics, deterministic: grid (chunks, n).  Thread <-> fixed channel octet,
 // strided rows.  No floating-point atomics anywhere: per-thread sums go to shared memory, are
 // combined in a fixed order into per-(chunk, group) partials, and the last CTA of each image
@@ -18,7 +45,7 @@ using namespace sw;
 // scratch layout (floats): final[n*groups*2] | tickets[n] (as uint) | partial[n][chunks][groups][2]
 __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1,
                            float* __restrict__ scratch, int hw, int c, int groups, int rows_per_cta,
-                           int rows_per_pass) {
+                           int rows_per_pass, const GnDist dist) {
     extern __shared__ float sh[];  // [rows_per_pass][c][2] then [c][2]
     __shared__ bool is_last;
     const int octs = c >> 3;
@@ -29,7 +56,7 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
     const int rp = threadIdx.x / octs;
     float* fin = scratch;
     unsigned int* tickets = reinterpret_cast<unsigned int*>(scratch + size_t(nimg) * groups * 2);
-    float* partial = scratch + size_t(nimg) * groups * 2 + nimg;
+    float* partial = scratch + size_t(nimg) * groups * 2 + nimg + 1;
 
     if (rp < rows_per_pass) {
         float s[8], ss[8];
@@ -109,9 +136,29 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
         if (lane == 0) {
             fin[(size_t(n) * groups + g) * 2] = a;
             fin[(size_t(n) * groups + g) * 2 + 1] = b;
+            if (dist.world > 1) {
+                // push this rank's sums into every peer's slot [parity][rank][n][g]
+                const size_t slot = ((size_t(dist.epoch & 1) * dist.world + dist.rank) * nimg + n) * groups + g;
+                for (int d = 0; d < dist.world; ++d) {
+                    dist.peer_stats[d][slot * 2] = a;
+                    dist.peer_stats[d][slot * 2 + 1] = b;
+                }
+            }
         }
     }
     if (threadIdx.x == 0) tickets[n] = 0u;  // leave the scratch ready for the next call
+    if (dist.world > 1) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // the image that finishes last raises this rank's flag on every peer
+            const unsigned int t = atomicAdd(&tickets[nimg], 1u);
+            if (t == unsigned(nimg) - 1u) {
+                tickets[nimg] = 0u;
+                for (int d = 0; d < dist.world; ++d) st_release_sys(dist.peer_flags[d] + dist.rank, dist.epoch);
+            }
+        }
+    }
 }
 
 // ---- GroupNorm apply: y = silu?((x-mean)*rstd*gamma+beta)
@@ -119,17 +166,32 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
                            __half* __restrict__ y,
                            const __half* __restrict__ gamma, const __half* __restrict__ beta,
                            const float* __restrict__ stats, int hw, int c, int groups, float eps,
-                           int silu, int rows_per_cta, int rows_per_pass) {
+                           int silu, int rows_per_cta, int rows_per_pass, const GnDist dist) {
     extern __shared__ float sh[];  // a[c], b[c]
     float* sa = sh;
     float* sb = sh + c;
     const int n = blockIdx.y;
     const int cg = c / groups;
-    const float inv_cnt = 1.0f / (float(hw) * float(cg));
+    const float inv_cnt = 1.0f / (float(hw) * float(cg) * float(dist.world > 1 ? dist.world : 1));
+    if (dist.world > 1) {
+        if (threadIdx.x < dist.world) wait_flag_ge(dist.peer_flags[dist.rank] + threadIdx.x, dist.epoch);
+        __syncthreads();
+    }
     for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {
         const int g = ch / cg;
-        const float sum = stats[(size_t(n) * groups + g) * 2];
-        const float sq = stats[(size_t(n) * groups + g) * 2 + 1];
+        float sum, sq;
+        if (dist.world > 1) {
+            sum = sq = 0.0f;
+            const float* mine = dist.peer_stats[dist.rank];
+            for (int src = 0; src < dist.world; ++src) {  // fixed rank order: same bits on every rank
+                const size_t slot = ((size_t(dist.epoch & 1) * dist.world + src) * gridDim.y + n) * groups + g;
+                sum += __ldcg(mine + slot * 2);
+                sq += __ldcg(mine + slot * 2 + 1);
+            }
+        } else {
+            sum = stats[(size_t(n) * groups + g) * 2];
+            sq = stats[(size_t(n) * groups + g) * 2 + 1];
+        }
         const float mean = sum * inv_cnt;
         const float var = fmaxf(sq * inv_cnt - mean * mean, 0.0f);
         const float rstd = rsqrtf(var + eps);
@@ -320,15 +382,32 @@ static GnGeom gn_geom(int hw, int c) {
 extern "C" int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups) {
     if (c <= 0 || c % 8 || hw <= 0 || n <= 0 || groups <= 0) return -1;
     const GnGeom g = gn_geom(hw, c);
-    return int64_t(n) * groups * 2 + n + int64_t(n) * g.chunks * groups * 2;
+    return int64_t(n) * groups * 2 + n + 1 + int64_t(n) * g.chunks * groups * 2;
 }
+
+int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                        int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                        float* scratch, cudaStream_t st, const sw_peers* peers);
 
 // Shared by the public entry points; `scratch` must already be usable device memory of at least
 // sw_groupnorm_scratch_floats() floats.
 int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                         int n, int hw, int c1, int c2, int groups, float eps, int silu,
-                        float* scratch, cudaStream_t st) {
+                        float* scratch, cudaStream_t st, const sw_peers* peers) {
     const int c = c1 + c2;
+    GnDist dist;
+    memset(&dist, 0, sizeof(dist));
+    dist.world = 1;
+    if (peers && peers->world > 1) {
+        if (peers->world > 8) return swh::fail(-1, "sw_groupnorm_nhwc_dist: world > 8");
+        dist.world = peers->world;
+        dist.rank = peers->rank;
+        dist.epoch = peers->epoch;
+        for (int d = 0; d < peers->world; ++d) {
+            dist.peer_stats[d] = static_cast<float*>(peers->peer[d]);
+            dist.peer_flags[d] = peers->flags[d];
+        }
+    }
     if (c1 <= 0 || c2 < 0 || c1 % 8 || (c2 > 0 && !x2))
         return swh::fail(-1, "sw_groupnorm_nhwc: bad channel split c1=%d c2=%d", c1, c2);
     if (c % 8 || groups <= 0 || c % groups)
@@ -336,17 +415,17 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
     if (c / 8 > 1024) return swh::fail(-1, "sw_groupnorm_nhwc: c=%d too wide", c);
     const GnGeom g = gn_geom(hw, c);
     // only the ticket counters have to start at zero
-    SW_CUDA_OK(cudaMemsetAsync(scratch + size_t(n) * groups * 2, 0, sizeof(float) * size_t(n), st));
+    SW_CUDA_OK(cudaMemsetAsync(scratch + size_t(n) * groups * 2, 0, sizeof(float) * size_t(n + 1), st));
     dim3 grid(g.chunks, n);
     const size_t smem_stats = (size_t(g.rows_per_pass) * c * 2 + size_t(c) * 2) * sizeof(float);
     k_gn_stats<<<grid, g.threads, smem_stats, st>>>(
         static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, scratch, hw, c, groups,
-        g.rows_per_cta, g.rows_per_pass);
+        g.rows_per_cta, g.rows_per_pass, dist);
     SW_CUDA_OK(cudaGetLastError());
     k_gn_apply<<<grid, g.threads, 2 * c * sizeof(float), st>>>(
         static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, static_cast<__half*>(y),
         static_cast<const __half*>(gamma), static_cast<const __half*>(beta), scratch, hw, c, groups,
-        eps, silu, g.rows_per_cta, g.rows_per_pass);
+        eps, silu, g.rows_per_cta, g.rows_per_pass, dist);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -356,7 +435,16 @@ extern "C" int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const v
                                  float eps, int silu, float* stats_scratch, void* stream) {
     if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc: null argument");
     return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu,
-                               stats_scratch, static_cast<cudaStream_t>(stream));
+                               stats_scratch, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+extern "C" int sw_groupnorm_nhwc_dist(const void* x, const void* x2, void* y, const void* gamma,
+                                      const void* beta, int n, int hw, int c1, int c2, int groups,
+                                      float eps, int silu, float* stats_scratch, const sw_peers* peers,
+                                      void* stream) {
+    if (!x || !y || !stats_scratch || !peers) return swh::fail(-1, "sw_groupnorm_nhwc_dist: null argument");
+    return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu,
+                               stats_scratch, static_cast<cudaStream_t>(stream), peers);
 }
 
 extern "C" int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows,

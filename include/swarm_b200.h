@@ -22,6 +22,17 @@ extern "C" {
 
 const char* sw_last_error(void);
 
+/* Peer description for the fused compute+collective entry points (one process per GPU, buffers
+ * in symmetric memory mapped on every rank; see chiaswarm_b200/parallel/runtime.py).
+ * peer[d]  : rank d's copy of the buffer the operation communicates through
+ * flags[d] : rank d's int32[world] epoch flags; slot [src] is written by rank src
+ * epoch    : strictly increasing per use of a flag set. */
+typedef struct {
+    int32_t world, rank, epoch;
+    void* peer[8];
+    int32_t* flags[8];
+} sw_peers;
+
 /* Epilogue activations for sw_igemm. */
 enum { SW_ACT_NONE = 0, SW_ACT_SILU = 1, SW_ACT_GELU = 2, SW_ACT_GEGLU = 3 };
 
@@ -71,6 +82,29 @@ typedef struct {
 
 int sw_igemm(const sw_igemm_params* p, void* stream);
 
+/* All-gather fused into the GEMM (collective call site 2): the activation is
+ * row-sharded, rank d holds X_d [m_local, c1] at peers->peer[d]; the kernel computes
+ * out[world*m_local, cout] = concat_d(X_d) . wgt^T by TMA-loading every A tile straight from the
+ * rank that owns it (NVLink peer mapping) -- no gathered copy exists.  The loader of a remote
+ * tile first waits for that rank's epoch flag (raised by sw_peer_signal or a producer kernel).
+ * p->a1 is ignored; p->w must equal world*m_local; m_local % 128 == 0. */
+int sw_igemm_ag(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* stream);
+
+/* GEMM fused with reduce-scatter (collective call site 3): every rank multiplies
+ * its K-shard, partial = A_r . W_r^T for all world*m_local rows, and the epilogue pushes each
+ * partial row over NVLink into the staging slot [rank] of the rank that owns that row
+ * (peers->peer[d]: fp16 [world][m_local][ldc] on rank d).  The CTA that finishes last raises this
+ * rank's epoch flag on every peer.  sw_rs_reduce (owner side) waits for all flags and adds the
+ * world slots in rank order (+ bias, + residual).  `ticket` is a zeroed uint32 in local memory. */
+int sw_igemm_rs(const sw_igemm_params* p, const sw_peers* peers, int m_local, uint32_t* ticket, void* stream);
+int sw_rs_reduce(const void* staging_local, void* out, const void* bias, const void* residual, int m_local,
+                 int ncols, int ld_stage, int ldo, int ldr, const sw_peers* peers, void* stream);
+
+/* Epoch-flag signal / wait between the ranks of a gang (st.release.sys / ld.acquire.sys on peer
+ * mappings; bounded spin).  Used to publish a tensor to the peers and as the NCCL-free barrier. */
+int sw_peer_signal(const sw_peers* peers, void* stream);
+int sw_peer_wait(const sw_peers* peers, void* stream);
+
 /* Flash attention (non-causal, no mask) on tcgen05: S=QK^T and O+=PV accumulate in TMEM, online
  * softmax in registers.  Replaces SDPA / xformers memory_efficient_attention (K1, K2), reference
  * call sites swarm/diffusion/diffusion_func.py:86-87,96.
@@ -90,6 +124,15 @@ typedef struct {
 
 int sw_flash_attn(const sw_attn_params* p, void* stream);
 
+/* Self-attention with the cross-patch K/V all-gather fused in (collective call
+ * site 1): queries are this rank's rows, K/V are row-sharded over `world` ranks (s_local rows each,
+ * same strides everywhere).  The KV loop starts on the local shard and then TMA-loads the peers'
+ * tiles through their NVLink mappings -- K/V are never gathered into one buffer.
+ * kpeers->peer[d] = rank d's K base, v_ptrs[d] = rank d's V base; p->k / p->v are ignored;
+ * p->seq_kv == world * s_local, s_local % 128 == 0, head_dim <= 128. */
+int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpeers, const void* const* v_ptrs,
+                         int s_local, void* stream);
+
 /* GroupNorm (+ optional SiLU) over channels-last fp16.  Replaces ATen GroupNorm + SiLU (K6, K8;
  * reference call site swarm/diffusion/diffusion_func.py:96).
  * The input is the channel-concatenation of x [n,hw,c1] and x2 [n,hw,c2] (x2 may be NULL with
@@ -103,6 +146,15 @@ int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups);
 int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                       int n, int hw, int c1, int c2, int groups, float eps, int silu,
                       float* stats_scratch, void* stream);
+
+/* GroupNorm over a feature map whose rows are sharded across `peers->world` GPUs (patch /
+ * sequence parallel): the statistics all-reduce (SURVEY.md collective call site 4) is done by the
+ * GroupNorm kernels themselves with peer stores + epoch flags over NVLink, no NCCL call.
+ * hw is the LOCAL number of pixels; every rank must hold the same hw.
+ * peers->peer[d]: fp32 [2][world][n][groups][2] on rank d. */
+int sw_groupnorm_nhwc_dist(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                           int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                           float* stats_scratch, const sw_peers* peers, void* stream);
 
 /* Same operation as sw_groupnorm_nhwc for callers that cannot allocate device memory (this entry
  * point has no counterpart in the reference, which has no native code).  Who needs it: a host
