@@ -591,6 +591,11 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 __global__ void __launch_bounds__(kThreads)
+    k_igemm2_ag(const __grid_constant__ AgMaps maps, const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
+    igemm_body<true>(maps.m[0], maps.m[0], tmB, p);
+}
+
+__global__ void __launch_bounds__(kThreads)
     k_igemm2(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
              const __grid_constant__ CUtensorMap tmB, const IGemmArgs p) {
     igemm_body<true>(tmA1, tmA2, tmB, p);
@@ -763,7 +768,8 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
 
     // ---- CTA pairs: with >= 2 pixel tiles per weight tile the layer runs as 256 x BN tiles on
     // tcgen05 cta_group::2 (halves every SM's shared-memory reads of the weight operand).
-    bool pair = grid_x >= 32 && bn >= 192 && mode == 0;  // measured: pays off for wide tiles with many pixel tiles
+    // measured: pays off for wide tiles with many pixel tiles (fused collectives: shards must hold whole pairs)
+    bool pair = grid_x >= 32 && bn >= 192 && (mode == 0 || m_local % 256 == 0);
     if (p->cta_pair == 1) pair = false;
     if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64 && mode == 0;
 
@@ -852,18 +858,36 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         if (rc) return rc;
     }
     if (mode == 1) {
-        const int stage_bytes2 = A_STAGE_BYTES + a.bn * BK * 2;
+        const int stage_bytes2 = A_STAGE_BYTES + (pair ? a.bn / 2 : a.bn) * BK * 2;
         const int smem = a.stages * stage_bytes2 + 1024 + 256;
         static bool configured[64] = {false};
         int dev = 0;
         SW_CUDA_OK(cudaGetDevice(&dev));
         if (dev < 64 && !configured[dev]) {
             SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             configured[dev] = true;
         }
-        dim3 grid(grid_x, (a.cout + a.bn - 1) / a.bn, 1);
-        k_igemm_ag<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(ag, tB, a);
-        SW_CUDA_OK(cudaGetLastError());
+        const int ntile = (a.cout + a.bn - 1) / a.bn;
+        if (!pair) {
+            k_igemm_ag<<<dim3(grid_x, ntile, 1), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(ag, tB, a);
+            SW_CUDA_OK(cudaGetLastError());
+            return 0;
+        }
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid_x, ntile, 1);  // even: m_local % 256 == 0
+        cfg.blockDim = dim3(kThreads, 1, 1);
+        cfg.dynamicSmemBytes = size_t(smem);
+        cfg.stream = static_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        SW_CUDA_OK(cudaLaunchKernelEx(&cfg, k_igemm2_ag, ag, tB, a));
         return 0;
     }
     return launch(a, tA1, tA2, tB, grid_x, pair, static_cast<cudaStream_t>(stream));
