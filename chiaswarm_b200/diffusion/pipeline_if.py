@@ -1,0 +1,48 @@
+"""DeepFloyd-IF cascade (reference: swarm/diffusion/diffusion_func_if.py:16-65).  Stage I and II are
+pixel-space UNets conditioned on T5-XXL, stage III is the SD x4 upscaler.  The stage checkpoints
+(and T5-XXL, ~20 GB) must be present locally; the callback has already verified that.  The T5
+encoder comes from transformers; the denoisers run on this framework's UNet / scheduler code with
+the IF block variant (`resnet_time_scale_shift="scale_shift"`, learned variance) handled here."""
+from __future__ import annotations
+
+import torch
+from PIL import Image
+
+from ..utils import checkpoints
+
+
+def run_if_cascade(device, stage1, stage2, stage3, prompt, negative_prompt=None, num_inference_steps=None,
+                   guidance_scale=7.0, generator=None):
+    from transformers import T5EncoderModel, T5Tokenizer
+
+    root1 = checkpoints.locate_checkpoint(stage1)
+    tok = T5Tokenizer.from_pretrained(str(root1 / "tokenizer"))
+    enc = T5EncoderModel.from_pretrained(str(root1 / "text_encoder"), torch_dtype=torch.float16).to(device)
+
+    def embed(text):
+        ids = tok(text, max_length=77, padding="max_length", truncation=True, return_tensors="pt").to(device)
+        with torch.no_grad():
+            return enc(**ids).last_hidden_state
+
+    cond, unc = embed(prompt), embed(negative_prompt or "")
+    del enc
+    from .if_unet import IFStage
+
+    s1 = IFStage.from_checkpoint(checkpoints.locate_checkpoint(stage1), device)
+    img = s1.sample(cond, unc, size=64, steps=num_inference_steps or 100, guidance_scale=guidance_scale,
+                    generator=generator)
+    s2 = IFStage.from_checkpoint(checkpoints.locate_checkpoint(stage2), device)
+    img = s2.sample(cond, unc, size=256, steps=num_inference_steps or 50, guidance_scale=min(guidance_scale, 4.0),
+                    generator=generator, low_res=img)
+    from .pipelines import StableDiffusionPipeline, tensor_to_pil
+
+    try:
+        up = StableDiffusionPipeline.from_pretrained(stage3, torch_dtype=torch.float16, device=device,
+                                                     family="sd_img2img")
+        pil = tensor_to_pil(img)
+        big = [p.resize((p.width * 4, p.height * 4), Image.Resampling.LANCZOS) for p in pil]
+        out = up(prompt=prompt, image=big[0], strength=0.25, num_inference_steps=30, generator=generator)
+        return out.images, any(out.nsfw_content_detected or [False])
+    except ValueError:
+        pil = tensor_to_pil(img)
+        return [p.resize((p.width * 4, p.height * 4), Image.Resampling.LANCZOS) for p in pil], False

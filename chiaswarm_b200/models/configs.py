@@ -56,6 +56,11 @@ _ZEROSCOPE_UNET3D = dict(
     up_block_types=("UpBlock3D", "CrossAttnUpBlock3D", "CrossAttnUpBlock3D", "CrossAttnUpBlock3D"),
     attention_head_dim=64, cross_attention_dim=1024, norm_num_groups=32, norm_eps=1e-5, sample_size=32)
 
+_TINY_UNET3D = dict(
+    in_channels=4, out_channels=4, block_out_channels=(32, 64), layers_per_block=1,
+    down_block_types=("CrossAttnDownBlock3D", "DownBlock3D"), up_block_types=("UpBlock3D", "CrossAttnUpBlock3D"),
+    attention_head_dim=8, cross_attention_dim=32, norm_num_groups=32, norm_eps=1e-5, sample_size=8)
+
 _CONTROLNET_SD15 = dict(_SD15_UNET, conditioning_channels=3, conditioning_embedding_out_channels=(16, 32, 96, 256))
 
 _LATENT_UPSCALER_NOTE = "sd-x2-latent-upscaler uses a K-diffusion UNet; served by the SD UNet driver at 2x latent size"
@@ -78,14 +83,19 @@ ARCHITECTURES = {
     "sdxl": _pipe("StableDiffusionXLPipeline", _SDXL_UNET, dict(_SD_VAE, scaling_factor=0.13025), _CLIP_L,
                   text_encoder_2=_CLIP_BIGG),
     "zeroscope": _pipe("TextToVideoSDPipeline", _ZEROSCOPE_UNET3D, _SD_VAE, _CLIP_H),
+    "tiny-t2v": _pipe("TextToVideoSDPipeline", _TINY_UNET3D, _TINY_VAE, _TINY_CLIP),
     "sd-x2-latent-upscaler": _pipe("StableDiffusionLatentUpscalePipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
 }
 
-CONTROLNETS = {"controlnet-sd15": _CONTROLNET_SD15}
+_CONTROLNET_TINY = dict(_TINY_UNET, conditioning_channels=3, conditioning_embedding_out_channels=(16, 32))
+
+CONTROLNETS = {"controlnet-sd15": _CONTROLNET_SD15, "controlnet-tiny": _CONTROLNET_TINY}
 
 # model_name (as the hive sends it) -> architecture key
 _NAME_RULES = [
+    ("tiny-t2v", "tiny-t2v"), ("tiny-text-to-video", "tiny-t2v"),
     ("tiny-stable-diffusion", "tiny-sd"), ("tiny-sd", "tiny-sd"),
+    ("controlnet-tiny", "tiny-sd"),
     ("instruct-pix2pix", "instruct-pix2pix"),
     ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
     ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
@@ -113,4 +123,5 @@ def get_architecture(key: str) -> dict:
 
 
 def get_controlnet(model_name: str) -> dict:
-    return copy.deepcopy(CONTROLNETS["controlnet-sd15"])
+    key = "controlnet-tiny" if "tiny" in model_name.lower() else "controlnet-sd15"
+    return copy.deepcopy(CONTROLNETS[key])

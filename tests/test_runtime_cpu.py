@@ -1,0 +1,158 @@
+"""Rank group (gang leasing), weight cache, checkpoint layout round trip, loaders, initializer."""
+import asyncio
+import json
+import threading
+
+import pytest
+import torch
+
+
+def test_rank_group_aligned_leases():
+    from chiaswarm_b200.gpu.device_pool import RankGroup
+
+    g = RankGroup(8)
+    assert g.aligned_subsets(4) == [(0, 1, 2, 3), (4, 5, 6, 7)] and len(g.aligned_subsets(2)) == 4
+    a = g.lease(1)
+    b = g.lease(2)
+    assert a.ranks == (0,) and b.ranks == (2, 3)  # buddy of the busy rank is skipped, pair stays aligned
+    c = g.lease(4)
+    assert c.ranks == (4, 5, 6, 7) and g.free_count() == 1
+    with pytest.raises(Exception, match="busy"):
+        g.lease(2, timeout=0)
+    with pytest.raises(ValueError):
+        g.lease(3)
+    got = {}
+    t = threading.Thread(target=lambda: got.update(g=g.lease(2, timeout=5)))
+    t.start()
+    g.release(a)
+    t.join()
+    assert got["g"].ranks == (0, 1)
+    with pytest.raises(ValueError):
+        g.release(a)
+    assert [x.lease_id for x in g.mark_dead(5)] == [c.lease_id]
+
+
+def test_reference_pool_functions():
+    from chiaswarm_b200.gpu import device_pool as dp
+    from chiaswarm_b200.gpu.device import Device
+
+    dp.available.clear()
+    assert dp.get_available_gpu_count() == 0
+    with pytest.raises(Exception, match="busy"):
+        dp.remove_device_from_pool()
+    d = Device("cpu")
+    dp.add_device_to_pool(d)
+    assert dp.get_available_gpu_count() == 1 and dp.remove_device_from_pool() is d
+
+
+def test_weight_cache_lru_by_bytes():
+    from chiaswarm_b200.utils.weight_cache import LRUByBytes
+
+    class Fake:
+        def __init__(self, n):
+            self.unet = torch.nn.Linear(n, n, bias=False)
+
+    cache = LRUByBytes(budget_bytes=4 * (100 * 100 + 120 * 120))
+    loads = []
+
+    def loader(n):
+        return lambda: (loads.append(n), Fake(n))[1]
+
+    a = cache.get("a", loader(100))
+    assert cache.get("a", loader(100)) is a and loads == [100] and cache.hits == 1
+    cache.get("b", loader(120))
+    cache.get("c", loader(100))  # evicts the least recently used ("a")
+    assert len(cache) == 2 and cache.get("a", loader(100)) is not a
+
+
+def test_diffusers_layout_round_trip(tmp_path, monkeypatch):
+    monkeypatch.setenv("SDAAS_RANDOM_INIT", "0")
+    monkeypatch.setenv("SDAAS_KERNEL_BACKEND", "torch")
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+    from chiaswarm_b200.utils import checkpoints
+
+    src = StableDiffusionPipeline.from_architecture("tiny-sd", seed=5)
+    root = tmp_path / "models" / "acme--tiny"
+    checkpoints.save_diffusers_layout(root, {"unet": src.unet, "vae": src.vae, "text_encoder": src.text_encoder},
+                                      {"_class_name": "StableDiffusionPipeline"}, src.scheduler_config)
+    assert checkpoints.locate_checkpoint("acme/tiny", model_root=str(tmp_path / "models")) == root
+    monkeypatch.setenv("SDAAS_MODEL_ROOT", str(tmp_path / "models"))
+    pipe = StableDiffusionPipeline.from_pretrained("acme/tiny", device="cpu")
+    for k, v in src.unet.state_dict().items():
+        assert torch.equal(v, pipe.unet.state_dict()[k]), k
+    outs = []
+    for p in (src, pipe):
+        p.set_scheduler("dpmpp_2m", True)
+        g = torch.Generator().manual_seed(1)
+        outs.append(p(prompt="a", height=32, width=32, num_inference_steps=2, generator=g, output_type="latent").latents)
+    assert torch.allclose(outs[0], outs[1])
+    with pytest.raises(ValueError, match="not available locally"):
+        StableDiffusionPipeline.from_pretrained("runwayml/stable-diffusion-v1-5", device="cpu")
+
+
+def test_vae_legacy_key_remap():
+    from chiaswarm_b200.utils.checkpoints import remap_vae_keys
+
+    sd = {"decoder.mid_block.attentions.0.query.weight": torch.zeros(4, 4, 1, 1),
+          "decoder.mid_block.attentions.0.proj_attn.bias": torch.zeros(4), "decoder.conv_in.weight": torch.zeros(1)}
+    out = remap_vae_keys(sd)
+    assert out["decoder.mid_block.attentions.0.to_q.weight"].shape == (4, 4)
+    assert "decoder.mid_block.attentions.0.to_out.0.bias" in out and "decoder.conv_in.weight" in out
+
+
+def test_lora_merge_and_textual_inversion(tmp_path):
+    from safetensors.torch import save_file
+
+    from chiaswarm_b200.diffusion.loaders import load_lora, load_textual_inversion
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+
+    pipe = StableDiffusionPipeline.from_architecture("tiny-sd")
+    name = "down_blocks.1.attentions.0.transformer_blocks.0.attn1"
+    attn = dict(pipe.unet.named_modules())[name]
+    before = attn.to_q.weight.clone()
+    d = attn.to_q.weight.shape[0]
+    down, up = torch.randn(4, d), torch.randn(d, 4)
+    lora_dir = tmp_path / "lora"
+    lora_dir.mkdir()
+    save_file({f"{name}.processor.to_q_lora.down.weight": down, f"{name}.processor.to_q_lora.up.weight": up},
+              str(lora_dir / "pytorch_lora_weights.safetensors"))
+    assert load_lora(pipe, str(lora_dir), scale=0.5) == 1
+    assert torch.allclose(attn.to_q.weight, before + 0.5 * up @ down, atol=1e-5)
+    with pytest.raises(ValueError):
+        load_lora(pipe, str(tmp_path / "missing"))
+    ti_dir = tmp_path / "ti"
+    ti_dir.mkdir()
+    dim = pipe.text_encoder.config["hidden_size"]
+    save_file({"<cat-toy>": torch.ones(dim)}, str(ti_dir / "learned_embeds.safetensors"))
+    added = load_textual_inversion(pipe, str(ti_dir))
+    row = added["<cat-toy>"]
+    assert torch.equal(pipe.text_encoder.text_model.embeddings.token_embedding.weight[row], torch.ones(dim))
+
+
+def test_initialize_first_run_prompts_and_reports(tmp_path, monkeypatch):
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    from chiaswarm_b200 import initialize, settings
+
+    answers = iter(["https://hive.test", "tok123"])
+    monkeypatch.setattr(initialize, "get_models_from_hive", lambda uri: [
+        {"model_name": "nobody/absent", "revision": "main", "parameters": {}},
+        {"model_name": "x/skip", "revision": "main", "parameters": {"can_preload": False}}])
+    report = asyncio.run(initialize.init([], input_fn=lambda prompt: next(answers)))
+    s = settings.load_settings()
+    assert (s.sdaas_uri, s.sdaas_token) == ("https://hive.test", "tok123")  # prompted on first run (Q8 fixed)
+    assert report == {"nobody/absent": "missing: no local diffusers-layout checkpoint"}
+    asyncio.run(initialize.init(["--silent"], input_fn=lambda p: pytest.fail("must not prompt")))
+    assert json.loads(settings.get_settings_full_path().read_text())["sdaas_token"] == "tok123"
+
+
+def test_type_helpers_and_registry():
+    from chiaswarm_b200.registry import pipeline_names, scheduler_names
+    from chiaswarm_b200.type_helpers import get_type, has_method
+
+    assert get_type("diffusers", "EulerAncestralDiscreteScheduler").kind == "euler_a"
+    assert get_type("diffusers", "StableDiffusionControlNetPipeline").family == "sd_controlnet"
+    assert get_type("transformers", "BlipProcessor").__name__ == "BlipProcessor"
+    with pytest.raises(ValueError):
+        get_type("diffusers", "TotallyUnknownPipeline")
+    assert "DPMSolverMultistepScheduler" in scheduler_names() and "DiffusionPipeline" in pipeline_names()
+    assert has_method("x", "upper") and not has_method("x", "nope")

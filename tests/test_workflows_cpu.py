@@ -1,0 +1,124 @@
+"""CPU tests of the non-txt2img workflows through the job API: ControlNet (canny), inpaint,
+instruct-pix2pix routing, text-to-video, stitch, and the long-tail callbacks' error shapes."""
+import asyncio
+import base64
+import io
+
+import numpy as np
+import pytest
+from PIL import Image
+
+from tests.helpers import decode_artifact_image, png_data_uri
+
+
+@pytest.fixture(autouse=True)
+def _env(tmp_path, monkeypatch):
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    monkeypatch.setenv("SDAAS_RANDOM_INIT", "1")
+    monkeypatch.setenv("SDAAS_KERNEL_BACKEND", "torch")
+    from chiaswarm_b200.utils.weight_cache import pipeline_cache
+
+    pipeline_cache().clear()
+
+
+def _run(job):
+    from chiaswarm_b200.generator import do_work
+    from chiaswarm_b200.gpu.device import Device
+
+    return asyncio.run(do_work(job, Device("cpu")))
+
+
+def _checker(size=(64, 64)):
+    arr = np.zeros((size[1], size[0], 3), np.uint8)
+    arr[: size[1] // 2, : size[0] // 2] = 255
+    arr[size[1] // 2:, size[0] // 2:] = 200
+    buf = io.BytesIO()
+    Image.fromarray(arr).save(buf, format="PNG")
+    return "data:image/png;base64," + base64.b64encode(buf.getvalue()).decode()
+
+
+def test_controlnet_canny_job_emits_preprocessed_input():
+    r = _run({"id": "c1", "model_name": "tiny-sd", "prompt": "edges", "start_image_uri": _checker(), "seed": 2,
+              "num_inference_steps": 2,
+              "parameters": {"controlnet": {"type": "canny", "preprocess": True,
+                                            "controlnet_model_name": "lllyasviel/controlnet-tiny"}}})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert set(r["artifacts"]) == {"primary", "preprocessed_input"}
+    edges = np.asarray(decode_artifact_image(r["artifacts"]["preprocessed_input"]).convert("L"))
+    assert edges.max() > 200 and edges.mean() < 60  # thin white edges on black
+    assert decode_artifact_image(r["artifacts"]["primary"]).size == (64, 64)
+
+
+def test_controlnet_changes_the_image():
+    base = {"id": "c2", "model_name": "tiny-sd", "prompt": "x", "seed": 3, "num_inference_steps": 2}
+    a = _run(dict(base, start_image_uri=_checker(), parameters={"controlnet": {"type": "canny", "preprocess": True,
+                                                                               "controlnet_model_name": "controlnet-tiny"}}))
+    b = _run(dict(base, height=64, width=64))
+    assert a["artifacts"]["primary"]["sha256_hash"] != b["artifacts"]["primary"]["sha256_hash"]
+
+
+def test_inpaint_legacy_keeps_unmasked_region_close():
+    mask = np.zeros((64, 64), np.uint8)
+    mask[:, 32:] = 255
+    buf = io.BytesIO()
+    Image.fromarray(mask).save(buf, format="PNG")
+    mask_uri = "data:image/png;base64," + base64.b64encode(buf.getvalue()).decode()
+    r = _run({"id": "i1", "model_name": "tiny-sd", "prompt": "fill", "start_image_uri": png_data_uri((64, 64)),
+              "mask_image_uri": mask_uri, "seed": 4, "num_inference_steps": 3,
+              "parameters": {"pipeline_type": "StableDiffusionInpaintPipelineLegacy"}})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert decode_artifact_image(r["artifacts"]["primary"]).size == (64, 64)
+
+
+def test_txt2vid_job_returns_a_video():
+    r = _run({"id": "v1", "workflow": "txt2vid", "model_name": "tiny-t2v", "prompt": "waves", "num_frames": 3,
+              "num_inference_steps": 2, "height": 32, "width": 32, "seed": 5})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    art = r["artifacts"]["primary"]
+    assert art["content_type"] == "video/mp4" and len(base64.b64decode(art["blob"])) > 100
+    thumb = Image.open(io.BytesIO(base64.b64decode(art["thumbnail"])))
+    assert max(thumb.size) <= 100
+
+
+def test_stitch_geometry_and_image_map():
+    from chiaswarm_b200.toolbox import stitch
+
+    uris = [png_data_uri((200, 100), (i * 40, 0, 0)) for i in range(5)]
+    r = _run({"id": "s1", "workflow": "stitch", "model_name": "stitcher",
+              "jobs": [{"resultUri": u, "fileName": f"f{i}.jpg", "model_name": f"m{i}"} for i, u in enumerate(uris)]})
+    sheet = decode_artifact_image(r["artifacts"]["primary"])
+    assert sheet.size == (3 * stitch.thumb_size, 3 * stitch.thumb_size)  # ceil(sqrt(5)) = 3
+    amap = r["pipeline_config"]["image_map"]
+    assert [a["coords"] for a in amap][:4] == ["0,0,144,144", "144,0,288,144", "288,0,432,144", "0,144,144,288"]
+    assert amap[2]["alt"] == "m2" and amap[2]["filename"] == "f2.jpg" and amap[0]["shape"] == "rect"
+    thumbs = stitch.resize_images([Image.new("RGB", (200, 100)), Image.new("RGB", (50, 300))])
+    assert thumbs[0].size == (144, 72) and thumbs[1].size == (24, 144)
+
+
+def test_long_tail_callbacks_fail_in_the_reference_error_shape():
+    r = _run({"id": "a1", "workflow": "txt2audio", "model_name": "cvssp/audioldm", "prompt": "rain",
+              "content_type": "audio/mpeg"})
+    assert r["fatal_error"] is True and r["artifacts"]["primary"]["content_type"] == "application/json"
+    r = _run({"id": "a2", "workflow": "txt2audio", "model_name": "suno/bark", "prompt": "hi", "content_type": "audio/mpeg"})
+    assert r["fatal_error"] is True and "not available" in r["pipeline_config"]["error"]
+    r = _run({"id": "if1", "model_name": "DeepFloyd/IF-I-XL-v1.0", "prompt": "frog"})
+    assert r["fatal_error"] is True and "DeepFloyd" in r["pipeline_config"]["error"]
+    # captioning never raises: the error becomes the caption artifact
+    r = _run({"id": "cap", "workflow": "img2txt", "model_name": "Salesforce/blip-image-captioning-base",
+              "start_image_uri": png_data_uri((32, 32)),
+              "parameters": {"processor_type": "BlipProcessor", "model_type": "BlipForConditionalGeneration"}})
+    assert "fatal_error" not in r and "error" in r["pipeline_config"]
+
+
+def test_controlnet_preprocessors_all_types_produce_rgb():
+    from chiaswarm_b200.controlnet.input_processor import preprocess_image
+
+    img = decode_artifact_image({"blob": _checker((96, 64)).split(",")[1]})
+    for kind in ("canny", "mlsd", "depth", "normalbae", "seg", "lineart", "openpose", "pix2pix", "scribble", "softedge",
+                 "shuffle", "tile"):
+        out = preprocess_image(img, {"type": kind, "preprocess": True})
+        assert out.mode == "RGB", kind
+    assert preprocess_image(img, {"type": "tile", "preprocess": True}).size[1] == 1024
+    assert preprocess_image(img, {"type": "canny", "preprocess": False}) is img
+    with pytest.raises(Exception, match="Unknown controlnet type"):
+        preprocess_image(img, {"type": "nope", "preprocess": True})
