@@ -59,3 +59,35 @@ def test_graph_replay_is_deterministic():
         g = torch.Generator(device="cuda:0").manual_seed(5)
         res.append(eng(prompt="x", height=64, width=64, num_inference_steps=4, generator=g, output_type="latent").latents)
     assert torch.equal(res[0], res[1])
+
+
+def test_controlnet_and_img2img_engine_match_torch():
+    from PIL import Image
+
+    from chiaswarm_b200.diffusion.pipelines import _init_module
+    from chiaswarm_b200.models import configs
+    from chiaswarm_b200.models.controlnet import ControlNetModel
+
+    cn = _init_module(ControlNetModel(**configs.get_controlnet("controlnet-tiny")), 9)
+    ref, eng = _pipes("tiny-sd", controlnet=cn, family="sd_controlnet")
+    img = Image.radial_gradient("L").resize((64, 64)).convert("RGB")
+    _compare(ref, eng, 3, 3e-2, image=img)
+    ref2, eng2 = _pipes("tiny-sd", family="sd_img2img")
+    _compare(ref2, eng2, 4, 3e-2, image=img, strength=0.6)
+
+
+def test_sdxl_shaped_engine_matches_torch():
+    """text_time added embedding, linear projections, transformer depth > 1, two text encoders."""
+    import chiaswarm_b200.models.configs as C
+
+    C.ARCHITECTURES["tiny-xl"] = C._pipe(
+        "StableDiffusionXLPipeline",
+        dict(in_channels=4, out_channels=4, block_out_channels=(64, 128), layers_per_block=1,
+             down_block_types=("DownBlock2D", "CrossAttnDownBlock2D"), up_block_types=("CrossAttnUpBlock2D", "UpBlock2D"),
+             attention_head_dim=(2, 4), transformer_layers_per_block=(1, 2), cross_attention_dim=96, norm_num_groups=32,
+             norm_eps=1e-5, use_linear_projection=True, addition_embed_type="text_time", addition_time_embed_dim=32,
+             projection_class_embeddings_input_dim=64 + 6 * 32, sample_size=16),
+        C._TINY_VAE, dict(C._TINY_CLIP, hidden_size=32),
+        text_encoder_2=dict(C._TINY_CLIP, hidden_size=64, num_attention_heads=4, projection_dim=64))
+    ref, eng = _pipes("tiny-xl")
+    _compare(ref, eng, 3, 4e-2, height=64, width=64)
