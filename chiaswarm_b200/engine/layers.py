@@ -86,6 +86,25 @@ class Recorder:
     def __len__(self):
         return len(self.ops)
 
+    def profile(self, iters: int = 5):
+        """Per-op device time (CUDA events, op by op, warm): list of (label, microseconds)."""
+        out = []
+        for fn, args, kw in self.ops:
+            shapes = [tuple(a.shape) for a in args if isinstance(a, torch.Tensor)][:3]
+            extra = {k: kw[k] for k in ("n", "h", "w", "kh", "act", "heads", "seq_q", "seq_kv", "head_dim", "hw", "groups")
+                     if k in kw}
+            label = f"{getattr(fn, '__name__', 'op')} {shapes} {extra}"
+            fn(*args, **kw)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn(*args, **kw)
+            e1.record()
+            torch.cuda.synchronize()
+            out.append((label, e0.elapsed_time(e1) / iters * 1e3))
+        return out
+
 
 # ------------------------------------------------------------------------------------------ layers
 class Conv:

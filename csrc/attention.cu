@@ -113,6 +113,8 @@ __global__ void __launch_bounds__(kThreads)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -433,6 +435,8 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -605,10 +609,50 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 __syncwarp();
                 tc_fence_after();
             }
-            // P = exp2(S*scale - m_ref) -> fp16 -> swizzled smem; returns row sum, tracks max exponent
+            // P = exp2(S*scale - m_ref) -> fp16 -> swizzled smem; returns the row sum and tracks the
+            // largest P (as packed halves: P > 2^8 <=> the row outgrew the reference by more than 8).
             float xmax = -INFINITY;
+            auto chunk_full = [&](const uint32_t (&v)[32], int c, float& lsum, __half2& pmax) {
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    const float e0 = ex2(fmaf(__uint_as_float(v[i]), scale, -m_ref));
+                    const float e1 = ex2(fmaf(__uint_as_float(v[i + 1]), scale, -m_ref));
+                    lsum += e0 + e1;
+                    const __half2 h = __floats2half2_rn(e0, e1);
+                    pmax = __hmax2(pmax, h);
+                    pk[i >> 1] = *reinterpret_cast<const uint32_t*>(&h);
+                }
+                uint8_t* slab = prow + (c >> 6) * SLAB_BYTES;
+                const int cc0 = (c & 63) >> 3;
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    *reinterpret_cast<uint4*>(slab + (((cc0 + g) ^ rsw) << 4)) =
+                        make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+            };
             auto emit_p = [&]() -> float {
                 float lsum = 0.0f;
+                if (kv_valid == BKV) {
+                    // full tile: TMEM loads software-pipelined against the exponentials
+                    __half2 pmax = __floats2half2_rn(0.0f, 0.0f);
+                    uint32_t va[32], vb[32];
+                    tmem_ld32(tS, va);
+                    tmem_ld_wait_dep(va);
+                    tmem_ld32(tS + 32, vb);
+                    chunk_full(va, 0, lsum, pmax);
+                    tmem_ld_wait_dep(vb);
+                    tmem_ld32(tS + 64, va);
+                    chunk_full(vb, 32, lsum, pmax);
+                    tmem_ld_wait_dep(va);
+                    tmem_ld32(tS + 96, vb);
+                    chunk_full(va, 64, lsum, pmax);
+                    tmem_ld_wait_dep(vb);
+                    chunk_full(vb, 96, lsum, pmax);
+                    const float pm = fmaxf(__low2float(pmax), __high2float(pmax));
+                    xmax = pm > 256.0f ? log2f(fminf(pm, 60000.0f)) : 0.0f;  // only > 8 matters
+                    if (pm > 60000.0f) xmax = 17.0f;                          // overflowed: force a rescale
+                    return lsum;
+                }
                 xmax = -INFINITY;
 #pragma unroll 1
                 for (int c = 0; c < BKV; c += 32) {
@@ -617,27 +661,15 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                         uint32_t v[32];
                         tmem_ld32(tS + c, v);
                         tmem_ld_wait();
-                        if (c + 32 <= kv_valid) {
 #pragma unroll
-                            for (int i = 0; i < 32; i += 2) {
-                                const float x0 = fmaf(__uint_as_float(v[i]), scale, -m_ref);
-                                const float x1 = fmaf(__uint_as_float(v[i + 1]), scale, -m_ref);
-                                xmax = fmaxf(xmax, fmaxf(x0, x1));
-                                const float e0 = ex2(x0), e1 = ex2(x1);
-                                lsum += e0 + e1;
-                                pk[i >> 1] = pack_h2(e0, e1);
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; i += 2) {
-                                const bool ok0 = c + i < kv_valid, ok1 = c + i + 1 < kv_valid;
-                                const float x0 = ok0 ? fmaf(__uint_as_float(v[i]), scale, -m_ref) : -INFINITY;
-                                const float x1 = ok1 ? fmaf(__uint_as_float(v[i + 1]), scale, -m_ref) : -INFINITY;
-                                xmax = fmaxf(xmax, fmaxf(x0, x1));
-                                const float e0 = ok0 ? ex2(x0) : 0.0f, e1 = ok1 ? ex2(x1) : 0.0f;
-                                lsum += e0 + e1;
-                                pk[i >> 1] = pack_h2(e0, e1);
-                            }
+                        for (int i = 0; i < 32; i += 2) {
+                            const bool ok0 = c + i < kv_valid, ok1 = c + i + 1 < kv_valid;
+                            const float x0 = ok0 ? fmaf(__uint_as_float(v[i]), scale, -m_ref) : -INFINITY;
+                            const float x1 = ok1 ? fmaf(__uint_as_float(v[i + 1]), scale, -m_ref) : -INFINITY;
+                            xmax = fmaxf(xmax, fmaxf(x0, x1));
+                            const float e0 = ok0 ? ex2(x0) : 0.0f, e1 = ok1 ? ex2(x1) : 0.0f;
+                            lsum += e0 + e1;
+                            pk[i >> 1] = pack_h2(e0, e1);
                         }
                     } else {
 #pragma unroll
@@ -654,8 +686,9 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             };
             float lsum = emit_p();
             if (j > 0) {
-                const bool need = xmax > 8.0f;  // this row outgrew the reference: rescale and redo
-                if (__any_sync(0xffffffffu, need)) {
+                for (int fix = 0; fix < 8; ++fix) {
+                    const bool need = xmax > 8.0f;  // this row outgrew the reference: rescale and redo
+                    if (!__any_sync(0xffffffffu, need)) break;
                     const float alpha = need ? ex2(-xmax) : 1.0f;
                     if (need) m_ref += xmax;
 #pragma unroll 1
@@ -792,16 +825,16 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
         const int smem2 = tile_bytes * (2 + a.k_stages + a.v_stages) + 4 * SLAB_BYTES + 1024 + 256;
         if (smem2 <= 227 * 1024) {
             dim3 grid2((p->seq_q + 2 * BQ - 1) / (2 * BQ), p->heads, p->batch);
-            k_flash_attn2<<<grid2, kThreads2, smem2, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, a);
-            SW_CUDA_OK(cudaGetLastError());
+            SW_CUDA_OK(swh::launch_pdl(k_flash_attn2, grid2, dim3(kThreads2), size_t(smem2),
+                                       static_cast<cudaStream_t>(stream), 1, tq, tk, tv, a));
             return 0;
         }
     }
     const int smem = tile_bytes * (1 + 2 * a.kv_stages) + 2 * SLAB_BYTES + 1024 + 256;
     if (smem > 227 * 1024) return swh::fail(-1, "sw_flash_attn: shared memory budget exceeded (%d)", smem);
     dim3 grid((p->seq_q + BQ - 1) / BQ, p->heads, p->batch);
-    k_flash_attn<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, a);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_flash_attn, grid, dim3(kThreads), size_t(smem), static_cast<cudaStream_t>(stream), 1,
+                               tq, tk, tv, a));
     return 0;
 }
 

@@ -17,6 +17,8 @@ inline int blocks_for(long long work, int threads) {
 
 __global__ void k_upsample2x(const uint4* __restrict__ x, uint4* __restrict__ y, int n, int h, int w,
                              int octs) {
+    pdl_trigger();
+    pdl_wait();
     const long long total = (long long)n * (2 * h) * (2 * w) * octs;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -33,6 +35,8 @@ __global__ void k_upsample2x(const uint4* __restrict__ x, uint4* __restrict__ y,
 __global__ void k_im2col(const uint4* __restrict__ x, uint4* __restrict__ out, int n, int h, int w,
                          int octs, int kh, int kw, int stride, int pad_top, int pad_left, int oh,
                          int ow) {
+    pdl_trigger();
+    pdl_wait();
     const long long total = (long long)n * oh * ow * kh * kw * octs;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -88,6 +92,8 @@ __global__ void k_nhwc_to_nchw(const __half* __restrict__ x, T* __restrict__ y, 
 __global__ void k_timestep_embedding(const float* __restrict__ t_table,
                                      const int* __restrict__ step_idx, __half* __restrict__ out,
                                      int n, int dim, float max_period, int flip, float freq_shift) {
+    pdl_trigger();
+    pdl_wait();
     const int half = dim / 2;
     const float t = t_table[step_idx ? *step_idx : 0];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n * half; i += gridDim.x * blockDim.x) {
@@ -107,10 +113,14 @@ __global__ void k_timestep_embedding(const float* __restrict__ t_table,
     }
 }
 
-__global__ void k_advance(int* c) { *c += 1; }
+__global__ void k_advance(int* c) {
+    pdl_trigger();
+    pdl_wait(); *c += 1; }
 
 __global__ void k_add(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ y,
                       long long n8) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
          i += (long long)gridDim.x * blockDim.x) {
         const uint4 u = a[i], v = b[i];
@@ -126,6 +136,8 @@ __global__ void k_add(const uint4* __restrict__ a, const uint4* __restrict__ b, 
 }
 
 __global__ void k_silu(const uint4* __restrict__ a, uint4* __restrict__ y, long long n8) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
          i += (long long)gridDim.x * blockDim.x) {
         const uint4 u = a[i];
@@ -141,6 +153,8 @@ __global__ void k_silu(const uint4* __restrict__ a, uint4* __restrict__ y, long 
 }
 
 __global__ void k_sched_step(const sw_sched_params p) {
+    pdl_trigger();
+    pdl_wait();
     const int step = p.step_idx ? *p.step_idx : 0;
     const float* cf = p.coef + (size_t)step * 8;
     const float e0 = cf[0], e1 = cf[1], c0 = cf[2], c1 = cf[3], c2 = cf[4], c3 = cf[5], s_in = cf[6];
@@ -198,9 +212,8 @@ __global__ void k_image_to_u8(const __half* __restrict__ x, uint8_t* __restrict_
 extern "C" int sw_upsample2x_nhwc(const void* x, void* y, int n, int h, int w, int c, void* stream) {
     if (c % 8) return swh::fail(-1, "sw_upsample2x_nhwc: c=%d not a multiple of 8", c);
     const long long total = (long long)n * 4 * h * w * (c / 8);
-    k_upsample2x<<<blocks_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(x), static_cast<uint4*>(y), n, h, w, c / 8);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_upsample2x, dim3(blocks_for(total, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                               1, static_cast<const uint4*>(x), static_cast<uint4*>(y), n, h, w, c / 8));
     return 0;
 }
 
@@ -208,10 +221,9 @@ extern "C" int sw_im2col_nhwc(const void* x, void* out, int n, int h, int w, int
                               int stride, int pad_top, int pad_left, int oh, int ow, void* stream) {
     if (c % 8) return swh::fail(-1, "sw_im2col_nhwc: c=%d not a multiple of 8", c);
     const long long total = (long long)n * oh * ow * kh * kw * (c / 8);
-    k_im2col<<<blocks_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(x), static_cast<uint4*>(out), n, h, w, c / 8, kh, kw, stride,
-        pad_top, pad_left, oh, ow);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_im2col, dim3(blocks_for(total, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 1,
+                               static_cast<const uint4*>(x), static_cast<uint4*>(out), n, h, w, c / 8, kh, kw, stride,
+                               pad_top, pad_left, oh, ow));
     return 0;
 }
 
@@ -247,33 +259,30 @@ extern "C" int sw_timestep_embedding(const float* t_table, const int32_t* step_i
                                      int dim, float max_period, int flip_sin_to_cos,
                                      float freq_shift, void* stream) {
     if (dim % 2) return swh::fail(-1, "sw_timestep_embedding: odd dim");
-    k_timestep_embedding<<<blocks_for((long long)n * dim / 2, 128), 128, 0,
-                           static_cast<cudaStream_t>(stream)>>>(
-        t_table, step_idx, static_cast<__half*>(out), n, dim, max_period, flip_sin_to_cos,
-        freq_shift);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_timestep_embedding, dim3(blocks_for((long long)n * dim / 2, 128)), dim3(128), 0,
+                               static_cast<cudaStream_t>(stream), 1, t_table, static_cast<const int*>(step_idx),
+                               static_cast<__half*>(out), n, dim, max_period, flip_sin_to_cos, freq_shift));
     return 0;
 }
 
 extern "C" int sw_advance_counter(int32_t* counter, void* stream) {
-    k_advance<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(counter);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_advance, dim3(1), dim3(1), 0, static_cast<cudaStream_t>(stream), 1,
+                               static_cast<int*>(counter)));
     return 0;
 }
 
 extern "C" int sw_add(const void* a, const void* b, void* y, int64_t n, void* stream) {
     if (n % 8) return swh::fail(-1, "sw_add: n not a multiple of 8");
-    k_add<<<blocks_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(y), n / 8);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_add, dim3(blocks_for(n / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 1,
+                               static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(y),
+                               (long long)(n / 8)));
     return 0;
 }
 
 extern "C" int sw_silu(const void* x, void* y, int64_t n, void* stream) {
     if (n % 8) return swh::fail(-1, "sw_silu: n not a multiple of 8");
-    k_silu<<<blocks_for(n / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const uint4*>(x), static_cast<uint4*>(y), n / 8);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_silu, dim3(blocks_for(n / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), 1,
+                               static_cast<const uint4*>(x), static_cast<uint4*>(y), (long long)(n / 8)));
     return 0;
 }
 
@@ -282,8 +291,8 @@ extern "C" int sw_sched_step(const sw_sched_params* p, void* stream) {
         return swh::fail(-1, "sw_sched_step: null argument");
     if (p->n_cond < 1 || p->n_cond > 3) return swh::fail(-1, "sw_sched_step: n_cond=%d", p->n_cond);
     const long long total = (long long)p->rows * p->c;
-    k_sched_step<<<blocks_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(*p);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_sched_step, dim3(blocks_for(total, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                               1, *p));
     return 0;
 }
 

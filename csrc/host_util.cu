@@ -1,6 +1,7 @@
 #include "host_util.h"
 
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -85,6 +86,15 @@ int sm_count() {
         n[dev] = v;
     }
     return n[dev];
+}
+
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("SW_PDL");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
 }
 
 }  // namespace swh

@@ -273,6 +273,8 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     cta_or_cluster_sync<PAIR>();  // (pair: peer barriers must exist before any remote arrive)
     tc_fence_after();
     const uint32_t tmem_acc = *tmem_slot;
+    pdl_trigger();  // the next kernel may start its prologue
+    pdl_wait();     // our inputs (and the buffers we overwrite) belong to the previous kernel until here
 
     const int nkb1 = (p.c1 + BK - 1) / BK;
     const int nkb2 = (p.c2 + BK - 1) / BK;
@@ -650,25 +652,12 @@ int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, c
     }
     const int ntile = (a.cout + a.bn - 1) / a.bn;
     if (!pair) {
-        dim3 grid(grid_x, ntile, a.splits);
-        k_igemm<<<grid, kThreads, smem, st>>>(tA1, tA2, tB, a);
-        SW_CUDA_OK(cudaGetLastError());
+        SW_CUDA_OK(swh::launch_pdl(k_igemm, dim3(grid_x, ntile, a.splits), dim3(kThreads), size_t(smem), st, 1, tA1,
+                                   tA2, tB, a));
         return 0;
     }
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((grid_x + 1) / 2 * 2, ntile, a.splits);
-    cfg.blockDim = dim3(kThreads, 1, 1);
-    cfg.dynamicSmemBytes = size_t(smem);
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    SW_CUDA_OK(cudaLaunchKernelEx(&cfg, k_igemm2, tA1, tA2, tB, a));
+    SW_CUDA_OK(swh::launch_pdl(k_igemm2, dim3((grid_x + 1) / 2 * 2, ntile, a.splits), dim3(kThreads), size_t(smem),
+                               st, 2, tA1, tA2, tB, a));
     return 0;
 }
 
@@ -778,12 +767,16 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     const int stage_bytes = A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
     int stages = (3 * stage_bytes <= 110 * 1024) ? 3 : 4;
     if (stage_bytes <= 24 * 1024) stages = 4;
+    // one or two pixel tiles: pure weight streaming, latency-bound -> deepest ring that fits (one CTA per SM)
+    if (grid_x <= 2 && !pair) stages = stage_bytes <= 24 * 1024 ? 8 : (200 * 1024) / stage_bytes;
     {
-        static int forced = -1;  // tuning hook: SW_IGEMM_STAGES overrides the ring depth
-        if (forced < 0) {
+        static int env_forced = -1;  // tuning hook: SW_IGEMM_STAGES overrides the ring depth
+        if (env_forced < 0) {
             const char* e = getenv("SW_IGEMM_STAGES");
-            forced = e ? atoi(e) : 0;
+            env_forced = e ? atoi(e) : 0;
         }
+        int forced = env_forced;
+        if (p->stages > 0) forced = p->stages;
         if (forced > 0) {
             stages = forced;
             while (stages > 2 && stages * stage_bytes > 220 * 1024) --stages;

@@ -46,6 +46,8 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
 __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1,
                            float* __restrict__ scratch, int hw, int c, int groups, int rows_per_cta,
                            int rows_per_pass, const GnDist dist) {
+    pdl_trigger();
+    pdl_wait();
     extern __shared__ float sh[];  // [rows_per_pass][c][2] then [c][2]
     __shared__ bool is_last;
     const int octs = c >> 3;
@@ -66,7 +68,27 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
         const int cs = first ? c1 : c - c1;
         const __half* base =
             (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
-        for (int r = r0 + rp; r < r1; r += rows_per_pass) {
+        // four independent 16-byte loads in flight per thread (the loop is latency-, not bandwidth-bound)
+        int r = r0 + rp;
+        for (; r + 3 * rows_per_pass < r1; r += 4 * rows_per_pass) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                v[u] = *reinterpret_cast<const uint4*>(base + size_t(r + u * rows_per_pass) * cs);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 f = unpack_h2(w[j]);
+                    s[2 * j] += f.x;
+                    ss[2 * j] += f.x * f.x;
+                    s[2 * j + 1] += f.y;
+                    ss[2 * j + 1] += f.y * f.y;
+                }
+            }
+        }
+        for (; r < r1; r += rows_per_pass) {
             const uint4 v = *reinterpret_cast<const uint4*>(base + size_t(r) * cs);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -167,6 +189,8 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
                            const __half* __restrict__ gamma, const __half* __restrict__ beta,
                            const float* __restrict__ stats, int hw, int c, int groups, float eps,
                            int silu, int rows_per_cta, int rows_per_pass, const GnDist dist) {
+    pdl_trigger();
+    pdl_wait();
     extern __shared__ float sh[];  // a[c], b[c]
     float* sa = sh;
     float* sb = sh + c;
@@ -217,8 +241,7 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
     const bool first = oct * 8 < c1;
     const int cs = first ? c1 : c - c1;
     const __half* src = (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
-    for (int r = r0 + rp; r < r1; r += rows_per_pass) {
-        const uint4 v = *reinterpret_cast<const uint4*>(src + size_t(r) * cs);
+    auto apply_row = [&](const uint4& v, int r) {
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
         uint32_t o[4];
 #pragma unroll
@@ -233,7 +256,16 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
             o[j] = pack_h2(u0, u1);
         }
         *reinterpret_cast<uint4*>(y + base + size_t(r) * c) = make_uint4(o[0], o[1], o[2], o[3]);
+    };
+    int r = r0 + rp;
+    for (; r + 3 * rows_per_pass < r1; r += 4 * rows_per_pass) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(src + size_t(r + u * rows_per_pass) * cs);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) apply_row(v[u], r + u * rows_per_pass);
     }
+    for (; r < r1; r += rows_per_pass) apply_row(*reinterpret_cast<const uint4*>(src + size_t(r) * cs), r);
 }
 
 // ---- LayerNorm: one warp per row, row cached in registers (c <= 2048).
@@ -241,6 +273,8 @@ template <int MAX_OCT>
 __global__ void k_layernorm(const __half* __restrict__ x, __half* __restrict__ y,
                             const __half* __restrict__ gamma, const __half* __restrict__ beta,
                             int rows, int c, float eps) {
+    pdl_trigger();
+    pdl_wait();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (warp >= rows) return;
@@ -418,15 +452,14 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
     SW_CUDA_OK(cudaMemsetAsync(scratch + size_t(n) * groups * 2, 0, sizeof(float) * size_t(n + 1), st));
     dim3 grid(g.chunks, n);
     const size_t smem_stats = (size_t(g.rows_per_pass) * c * 2 + size_t(c) * 2) * sizeof(float);
-    k_gn_stats<<<grid, g.threads, smem_stats, st>>>(
-        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, scratch, hw, c, groups,
-        g.rows_per_cta, g.rows_per_pass, dist);
-    SW_CUDA_OK(cudaGetLastError());
-    k_gn_apply<<<grid, g.threads, 2 * c * sizeof(float), st>>>(
-        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1, static_cast<__half*>(y),
-        static_cast<const __half*>(gamma), static_cast<const __half*>(beta), scratch, hw, c, groups,
-        eps, silu, g.rows_per_cta, g.rows_per_pass, dist);
-    SW_CUDA_OK(cudaGetLastError());
+    SW_CUDA_OK(swh::launch_pdl(k_gn_stats, grid, dim3(g.threads), smem_stats, st, 1, static_cast<const __half*>(x),
+                               static_cast<const __half*>(x2), c1, scratch, hw, c, groups, g.rows_per_cta,
+                               g.rows_per_pass, dist));
+    SW_CUDA_OK(swh::launch_pdl(k_gn_apply, grid, dim3(g.threads), size_t(2 * c * sizeof(float)), st, 1,
+                               static_cast<const __half*>(x), static_cast<const __half*>(x2), c1,
+                               static_cast<__half*>(y), static_cast<const __half*>(gamma),
+                               static_cast<const __half*>(beta), static_cast<const float*>(scratch), hw, c, groups,
+                               eps, silu, g.rows_per_cta, g.rows_per_pass, dist));
     return 0;
 }
 
@@ -460,11 +493,11 @@ extern "C" int sw_layernorm(const void* x, void* y, const void* gamma, const voi
     const __half* g = static_cast<const __half*>(gamma);
     const __half* b = static_cast<const __half*>(beta);
     if (octs <= 64)
-        k_layernorm<2><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+        SW_CUDA_OK(swh::launch_pdl(k_layernorm<2>, dim3(blocks), dim3(threads), 0, st, 1, xx, yy, g, b, rows, c, eps));
     else if (octs <= 160)
-        k_layernorm<5><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+        SW_CUDA_OK(swh::launch_pdl(k_layernorm<5>, dim3(blocks), dim3(threads), 0, st, 1, xx, yy, g, b, rows, c, eps));
     else
-        k_layernorm<8><<<blocks, threads, 0, st>>>(xx, yy, g, b, rows, c, eps);
+        SW_CUDA_OK(swh::launch_pdl(k_layernorm<8>, dim3(blocks), dim3(threads), 0, st, 1, xx, yy, g, b, rows, c, eps));
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }
