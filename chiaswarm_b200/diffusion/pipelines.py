@@ -30,6 +30,7 @@ from ..models.vae import AutoencoderKL
 from ..ops import schedulers
 from ..utils import checkpoints
 from ..utils.tokenizer import load_tokenizer
+from ..utils.tracing import StageTimer
 
 
 @dataclass
@@ -266,7 +267,9 @@ class StableDiffusionPipeline:
         pix2pix = mode == "sd_pix2pix"
         do_cfg = guidance_scale > 1.0
         n_cond = 3 if (pix2pix and do_cfg) else (2 if do_cfg else 1)
-        embeds, pooled = self.encode_prompt(prompts, negative, n_cond)
+        timer = StageTimer(enabled=os.environ.get("SDAAS_TRACE", "0") not in ("0", ""))
+        with timer.stage("encode_prompt"):
+            embeds, pooled = self.encode_prompt(prompts, negative, n_cond)
         embeds = embeds.to(self.dtype)
 
         plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), self.scheduler_config,
@@ -319,20 +322,23 @@ class StableDiffusionPipeline:
             noise_table = torch.stack([randn().float() for _ in range(plan.num_steps)])
 
         denoiser = self._denoiser()
-        x = denoiser.run(x=x, embeds=embeds, plan=plan, n_cond=n_cond, g_text=float(guidance_scale),
-                         g_image=float(image_guidance_scale), extra=extra, control=control,
-                         control_scale=float(controlnet_conditioning_scale), added=added, noise=noise_table,
-                         inpaint=init_latents)
+        with timer.stage("denoise"):
+            x = denoiser.run(x=x, embeds=embeds, plan=plan, n_cond=n_cond, g_text=float(guidance_scale),
+                             g_image=float(image_guidance_scale), extra=extra, control=control,
+                             control_scale=float(controlnet_conditioning_scale), added=added, noise=noise_table,
+                             inpaint=init_latents)
         if output_type == "latent":
-            return PipelineOutput(images=[], latents=x)
-        images = denoiser.decode(x / self.vae.scaling_factor)
+            return PipelineOutput(images=[], latents=x, timings=timer.result() if timer.enabled else {})
+        with timer.stage("vae_decode"):
+            images = denoiser.decode(x / self.vae.scaling_factor)
         if output_type == "device":  # leave the decoded batch on the GPU (benchmarks, chained stages)
-            out = PipelineOutput(images=[], latents=x)
+            out = PipelineOutput(images=[], latents=x, timings=timer.result() if timer.enabled else {})
             out.device_images = images
             return out
         pil = tensor_to_pil(images) if isinstance(images, torch.Tensor) and images.dtype != torch.uint8 else \
             [Image.fromarray(a) for a in images.cpu().numpy()]
-        return PipelineOutput(images=pil, nsfw_content_detected=self.run_safety_checker(pil), latents=x)
+        return PipelineOutput(images=pil, nsfw_content_detected=self.run_safety_checker(pil), latents=x,
+                              timings=timer.result() if timer.enabled else {})
 
     def run_safety_checker(self, images):
         if self.safety_checker is None:

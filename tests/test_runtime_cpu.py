@@ -156,3 +156,37 @@ def test_type_helpers_and_registry():
         get_type("diffusers", "TotallyUnknownPipeline")
     assert "DPMSolverMultistepScheduler" in scheduler_names() and "DiffusionPipeline" in pipeline_names()
     assert has_method("x", "upper") and not has_method("x", "nope")
+
+
+def _crashy_child(gpu, suffix):
+    import sys
+
+    sys.exit(3 if gpu == 1 else 0)
+
+
+def test_launcher_supervisor_restarts_dead_children():
+    from chiaswarm_b200.parallel.launcher import Supervisor
+
+    sup = Supervisor([0, 1], restart_backoff_s=0.2, target=_crashy_child)
+    for g in sup.gpus:
+        sup._start(g)
+    for p in sup.procs.values():
+        p.join(30)
+    assert sup.poll_once() == 2 and sup.restarts == {0: 1, 1: 1}
+    sup.stop()
+
+
+def test_stage_timer_and_watchdog():
+    import time
+
+    from chiaswarm_b200.utils.tracing import StageTimer, Watchdog
+
+    t = StageTimer()
+    with t.stage("a"):
+        time.sleep(0.01)
+    assert t.result()["a_wall"] >= 9
+    with pytest.raises(TimeoutError):
+        with Watchdog(0.05, "slow"):
+            time.sleep(0.2)
+    with Watchdog(5):
+        pass
