@@ -112,7 +112,12 @@ class SM100Denoiser:
         self.device = pipe.device
         nat.lib()  # a missing native library on a GPU box is an error, never a silent fallback
         self.lat_c = pipe.vae.config["latent_channels"]
-        self.unet_plan = UNetPlan(pipe.unet, self.device)
+        if hasattr(pipe.unet, "transformer_in"):  # UNet3DConditionModel: frames ride in the batch dimension
+            from .unet3d_sm100 import UNet3DPlan
+
+            self.unet_plan = UNet3DPlan(pipe.unet, self.device)
+        else:
+            self.unet_plan = UNetPlan(pipe.unet, self.device)
         self.control_plan = ControlNetPlan(pipe.controlnet, self.device) if pipe.controlnet is not None else None
         self.vae_plan = None
         self._graphs: Dict[tuple, _StepGraph] = {}
@@ -121,7 +126,9 @@ class SM100Denoiser:
 
     # ------------------------------------------------------------------ denoise
     @torch.no_grad()
-    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint):
+    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint,
+            num_frames: int = 1):
+        """`num_frames` > 1 (UNet3D): `x` is [clips*frames, c, h, w] and `embeds` holds one row per frame."""
         if inpaint is not None:
             # legacy 4-channel inpainting re-imposes the known region between steps (host-side blend)
             from ..diffusion.pipelines import TorchDenoiser
@@ -134,9 +141,13 @@ class SM100Denoiser:
             raise ValueError(f"at most {MAX_STEPS} denoising steps are supported")
         extra_ch = 0 if extra is None else extra.shape[1]
         key = (batch, h, w, n_cond, extra_ch, control is not None, noise is not None, added is not None,
-               g_text, g_image, control_scale)
+               g_text, g_image, control_scale, num_frames)
         sg = self._graphs.get(key)
         up = self.unet_plan
+        if num_frames > 1 or hasattr(up, "num_frames"):
+            if not hasattr(up, "num_frames") or batch % num_frames:
+                raise ValueError("num_frames needs a UNet3D plan and a batch that is a multiple of it")
+            up.num_frames = num_frames
         up.set_context(embeds.to(torch.float16))
         if self.control_plan is not None and control is not None:
             self.control_plan.set_context(embeds.to(torch.float16))

@@ -50,6 +50,7 @@ class IGemmParams(C.Structure):
         ("splitk_scratch", C.c_void_p),
         ("splitk_scratch_bytes", C.c_int64),
         ("splitk_min_kb", C.c_int32),
+        ("pad_w1", C.c_int32),
         ("stages", C.c_int32),
         ("cta_pair", C.c_int32),
     ]
@@ -183,7 +184,7 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 
 # --------------------------------------------------------------------------------------- ops
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
-          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0):
+          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -224,6 +225,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.cta_pair = cta_pair
     p.splitk_min_kb = splitk_min_kb
     p.stages = stages
+    p.pad_w1 = 0 if pad_w is None else pad_w + 1
     if splitk_scratch is not None:
         p.splitk_scratch = splitk_scratch.data_ptr()
         p.splitk_scratch_bytes = splitk_scratch.numel() * splitk_scratch.element_size()

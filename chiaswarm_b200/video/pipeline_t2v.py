@@ -37,6 +37,8 @@ class TextToVideoPipeline:
         self.device, self.dtype = torch.device("cpu"), torch.float32
         self.backend = "torch"
         self._vae_engine = None
+        self._engine = None
+        self.controlnet = None
 
     @classmethod
     def from_pretrained(cls, model_name, revision="main", variant=None, torch_dtype=torch.float16, device="cpu",
@@ -85,6 +87,7 @@ class TextToVideoPipeline:
             m.to(self.device, self.dtype).eval()
         self.backend = default_backend(self.device)
         self._vae_engine = None
+        self._engine = None
         return self
 
     def set_scheduler(self, scheduler_type, use_karras_sigmas=True):
@@ -96,15 +99,29 @@ class TextToVideoPipeline:
     def _decode(self, z):
         """z: (N, 4, h, w) -> uint8 (N, H, W, 3)."""
         if self.backend == "sm100" and self.device.type == "cuda":
-            if self._vae_engine is None:
-                from ..engine.denoiser import SM100Denoiser
-
-                self._vae_engine = SM100Denoiser.__new__(SM100Denoiser)
-                self._vae_engine.pipe, self._vae_engine.device = self, self.device
-                self._vae_engine.vae_plan, self._vae_engine._vae_graphs = None, {}
-            return self._vae_engine.decode(z)
+            return self._sm100().decode(z)
         img = self.vae.decode(z.to(self.dtype)).float()
         return ((img / 2 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8).permute(0, 2, 3, 1)
+
+    def _sm100(self):
+        if self._engine is None:
+            from ..engine.denoiser import SM100Denoiser
+
+            self._engine = SM100Denoiser(self)
+        return self._engine
+
+    def _denoise_sm100(self, x, embeds, plan, n_cond, guidance_scale, generator):
+        """Whole denoising loop on the engine: frames ride in the batch dimension of the captured plan."""
+        nf = x.shape[2]
+        frames = x[0].permute(1, 0, 2, 3).contiguous()                     # (F, 4, h, w)
+        per_frame = embeds.repeat_interleave(nf, dim=0)                    # cond-major, one row per frame
+        noise = None
+        if plan.needs_noise:
+            noise = torch.randn((plan.num_steps,) + tuple(frames.shape), generator=generator, device=self.device,
+                                dtype=self.dtype)
+        out = self._sm100().run(frames, per_frame, plan, n_cond, float(guidance_scale), 0.0, None, None, 1.0, None,
+                                noise, None, num_frames=nf)
+        return out.permute(1, 0, 2, 3).unsqueeze(0)
 
     @torch.no_grad()
     def __call__(self, prompt="", negative_prompt=None, height=None, width=None, num_frames=16,
@@ -129,7 +146,10 @@ class TextToVideoPipeline:
         x = torch.randn(shape, generator=generator, device=self.device, dtype=self.dtype).float() * plan.init_noise_sigma
         x0_prev, scale = None, plan.first_scale
         n_cond = 2 if do_cfg else 1
-        for i in range(plan.num_steps):
+        engine = self.backend == "sm100" and self.device.type == "cuda"
+        if engine:
+            x = self._denoise_sm100(x, embeds, plan, n_cond, guidance_scale, generator)
+        for i in range(0 if engine else plan.num_steps):
             t = torch.tensor(float(plan.timesteps[i]), device=self.device)
             model_in = torch.cat([x] * n_cond).to(self.dtype) * scale
             out = self.unet(model_in, t, embeds)
@@ -142,6 +162,6 @@ class TextToVideoPipeline:
             return VideoOutput(frames=[], latents=x)
         z = (x[0].permute(1, 0, 2, 3) / self.vae.scaling_factor).contiguous()  # (F, 4, h, w)
         frames = []
-        for chunk in z.split(8):
+        for chunk in z.split(8 if not engine else 24):
             frames.extend(list(self._decode(chunk).cpu().numpy()))
         return VideoOutput(frames=frames, latents=x)

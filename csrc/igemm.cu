@@ -28,7 +28,7 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 struct IGemmArgs {
     int c1, c2;
     int n, h, w;
-    int kh, kw, pad;
+    int kh, kw, pad, pad_w;
     int cout;
     int bw, bh, bi;  // tile box: bw*bh*bi <= 128 pixels
     int tiles_x, tiles_y;
@@ -305,10 +305,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                 int kcol;
                 if (j < nkb1) {
-                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad, n0);
                     kcol = tapbase + j * BK;
                 } else {
-                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
                     kcol = tapbase + p.c1 + (j - nkb1) * BK;
                 }
                 tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, kcol, bcol0);
@@ -701,6 +701,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.kh = p->kh;
     a.kw = p->kw;
     a.pad = p->pad;
+    a.pad_w = p->pad_w1 > 0 ? p->pad_w1 - 1 : p->pad;
     a.cout = p->cout;
     pick_box(p->n, p->h, p->w, &a.bw, &a.bh, &a.bi);
     a.tiles_x = (p->w + a.bw - 1) / a.bw;

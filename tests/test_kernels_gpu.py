@@ -306,3 +306,34 @@ def test_timestep_embedding_and_sched(nat):
     assert (x0p - x0).abs().max().item() < 1e-4
     assert (xin[1, :, :4].float() - xn * 0.7).abs().max().item() < 5e-3
     assert xin[:, :, 4:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("b,f,hw,c", [(2, 8, 64, 64), (1, 24, 180, 320), (2, 5, 45, 128)])
+def test_temporal_conv_3x1(nat, b, f, hw, c):
+    """Conv3d (3,1,1) over frames == 3x1 implicit GEMM on the [b, f, hw, c] view (vertical pad 1, horizontal pad 0)."""
+    torch.manual_seed(7)
+    x = torch.randn(b, f, hw, c, device="cuda", dtype=torch.float16)
+    w3 = torch.randn(c, c, 3, 1, 1, device="cuda", dtype=torch.float16) * (3 * c) ** -0.5
+    bias = torch.randn(c, device="cuda", dtype=torch.float16)
+    res = torch.randn(b * f * hw, c, device="cuda", dtype=torch.float16)
+    wk = w3[:, :, :, 0, 0].permute(0, 2, 1).reshape(c, 3 * c).contiguous()
+    out = torch.empty(b * f * hw, c, device="cuda", dtype=torch.float16)
+    nat.igemm(x, wk, out, n=b, h=f, w=hw, kh=3, kw=1, pad=1, pad_w=0, bias=bias, residual=res)
+    ref = F.conv3d(x.float().permute(0, 3, 1, 2).unsqueeze(-1), w3.float(), bias.float(), padding=(1, 0, 0))
+    ref = ref.squeeze(-1).permute(0, 2, 3, 1).reshape(b * f * hw, c) + res.float()
+    assert _rel_err(out, ref) < 4e-3
+
+
+@pytest.mark.parametrize("f,hw,heads,d", [(8, 64, 4, 8), (24, 180, 5, 64), (16, 45, 20, 64)])
+def test_flash_attn_over_frames(nat, f, hw, heads, d):
+    """Temporal attention: batch = pixel, sequence = frame, straight from the strides of a fused QKV buffer."""
+    torch.manual_seed(8)
+    c = heads * d
+    qkv = torch.randn(f, hw, 3, heads, d, device="cuda", dtype=torch.float16)
+    out = torch.zeros(f, hw, c, device="cuda", dtype=torch.float16)
+    v = qkv.permute(1, 0, 2, 3, 4)
+    nat.flash_attn(v[:, :, 0], v[:, :, 1], v[:, :, 2], out.permute(1, 0, 2), batch=hw, heads=heads, seq_q=f, seq_kv=f,
+                   head_dim=d)
+    q, k, vv = (v[:, :, i].float().permute(0, 2, 1, 3) for i in range(3))  # [hw, heads, f, d]
+    ref = F.scaled_dot_product_attention(q, k, vv).permute(2, 0, 1, 3).reshape(f, hw, c)
+    assert _rel_err(out, ref) < 5e-3
