@@ -345,6 +345,12 @@ class StableDiffusionPipeline:
             return [False] * len(images)
         return self.safety_checker(images)
 
+    def enable_patch_parallel(self, gang):
+        """Single-image jobs run patch-parallel over `gang` (engine/patch_engine.py); every rank of the
+        gang must then issue the same pipeline calls with the same seeds."""
+        self.patch_gang = gang if gang is not None and gang.world > 1 else None
+        self._engine = None
+
     def _denoiser(self):
         if self._engine is None:
             if self.backend == "sm100":
@@ -352,7 +358,12 @@ class StableDiffusionPipeline:
                     raise RuntimeError("the sm100 backend needs a CUDA device")
                 from ..engine.denoiser import SM100Denoiser
 
-                self._engine = SM100Denoiser(self)
+                if getattr(self, "patch_gang", None) is not None:
+                    from ..engine.patch_engine import PatchDenoiser
+
+                    self._engine = PatchDenoiser(self, self.patch_gang)
+                else:
+                    self._engine = SM100Denoiser(self)
             else:
                 self._engine = TorchDenoiser(self)
         return self._engine

@@ -34,6 +34,11 @@ class FM:
     h: int
     w: int
     c: int
+    # patch-parallel plans (engine/patch_engine.py): `sym` is the peer-visible [h+2, w, c] buffer whose
+    # interior `t` views (rows 0 and h+1 are the halo rows the neighbours fill); `window` = (rows of the
+    # full image `t` actually holds, first row of this rank's strip) for inputs every rank keeps whole
+    sym: object = None
+    window: Optional[tuple] = None
 
     @property
     def rows(self):
@@ -45,6 +50,8 @@ class FM:
 
 class Recorder:
     """Records kernel launches with concrete buffers; `run()` replays them in order."""
+
+    patch = None  # PatchContext when the plan runs patch-parallel (engine/patch_engine.py)
 
     def __init__(self, device):
         self.device = torch.device(device)
@@ -124,14 +131,30 @@ class Conv:
 
     def __call__(self, rec: Recorder, x: FM, x2: Optional[FM] = None, row_bias=None, residual: Optional[FM] = None,
                  act=nat.ACT_NONE, out_scale=1.0, out: Optional[FM] = None) -> FM:
+        a, halo = x.t, {}
+        if rec.patch is not None and self.k == 3:  # rows above / below this strip live on the neighbours
+            assert x2 is None and self.pad == 1 and not self.asym
+            a, halo = rec.patch.conv_input(rec, x)
         if self.stride == 1:
             o = out or rec.fm(x.n, x.h, x.w, self.cout)
-            rec.add(nat.igemm, x.t, self.wgt, o.t.view(-1, o.c), n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, pad=self.pad,
+            rec.add(nat.igemm, a, self.wgt, o.t.view(-1, o.c), n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, pad=self.pad,
                     a2=None if x2 is None else x2.t, bias=self.bias, row_bias=row_bias,
                     residual=None if residual is None else residual.tokens(), act=act, out_scale=out_scale,
-                    splitk_scratch=rec.splitk)
+                    splitk_scratch=rec.splitk, **halo)
             return o
         assert x2 is None and self.stride == 2
+        if halo:  # stride 2 over the halo-padded strip: the top halo row is the padding row
+            assert halo["a_y_off"] == 1 and x.h % 2 == 0
+            oh, ow = x.h // 2, (x.w + 2 * self.pad - self.k) // 2 + 1
+            cols = rec.buf(x.n, oh, ow, self.k * self.k * x.c)
+            rec.add(nat.im2col, a, cols, n=x.n, h=x.h + 2, w=x.w, kh=self.k, kw=self.k, stride=2, pad_top=0,
+                    pad_left=self.pad, oh=oh, ow=ow)
+            o = out or rec.fm(x.n, oh, ow, self.cout)
+            rec.add(nat.igemm, cols.view(-1, cols.shape[-1]), self.wgt, o.t.view(-1, o.c), n=1, h=1, w=x.n * oh * ow,
+                    bias=self.bias, residual=None if residual is None else residual.tokens(), act=act,
+                    out_scale=out_scale, splitk_scratch=rec.splitk)
+            rec.release(cols)
+            return o
         if self.asym:  # VAE encoder: pad (0,1,0,1) then valid conv
             oh, ow = (x.h + 1 - self.k) // 2 + 1, (x.w + 1 - self.k) // 2 + 1
             pt = pl = 0
@@ -184,6 +207,11 @@ class GroupNorm:
     def __call__(self, rec: Recorder, x: FM, silu: bool, x2: Optional[FM] = None) -> FM:
         c = x.c + (x2.c if x2 is not None else 0)
         o = rec.fm(x.n, x.h, x.w, c)
+        if rec.patch is not None and rec.patch.P > 1:  # statistics span the whole image: in-kernel all-reduce
+            rec.add(nat.groupnorm_dist, x.t, self.gamma, self.beta, o.t, rec.patch.gn_peers(self.groups), n=x.n,
+                    hw=x.h * x.w, groups=self.groups, eps=self.eps, silu=silu, stats=rec.gn_stats,
+                    x2=None if x2 is None else x2.t)
+            return o
         rec.add(nat.groupnorm, x.t, self.gamma, self.beta, o.t, n=x.n, hw=x.h * x.w, groups=self.groups, eps=self.eps,
                 silu=silu, stats=rec.gn_stats, x2=None if x2 is None else x2.t)
         return o
@@ -290,7 +318,36 @@ class TransformerBlock:
     def __call__(self, rec: Recorder, y: torch.Tensor, n: int, s: int) -> torch.Tensor:
         """y: [n*s, c] residual stream; returns the new stream (y is released)."""
         x1 = self.ln1(rec, y)
-        if not self.self_is_cross:
+        if not self.self_is_cross and rec.patch is not None and rec.patch.P > 1:
+            # sequence-parallel self-attention: K/V of the other strips are read from their owners inside the
+            # kernel (TMA over the NVLink mappings), never gathered
+            attn = rec.buf(n, s, self.c)
+            if s % 128 == 0 and self.dh <= 128:
+                qs = rec.patch.sym_buf(n * s, 3 * self.c)
+                self.qkv(rec, x1, out=qs.local)
+                v5 = qs.local.view(n, s, 3, self.heads, self.dh)
+                kpeers, v_ptrs = rec.patch.kv_peers(qs, self.c)
+                rec.add(nat.peer_signal, kpeers)
+                rec.add(nat.flash_attn_gather, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn, kpeers, v_ptrs, batch=n,
+                        heads=self.heads, seq_q=s, s_local=s, head_dim=self.dh)
+            else:
+                # strips too short for whole K/V tiles (deep levels): the K/V projection writes this strip's
+                # rows of a full-sequence buffer and one push exchange completes it on every peer
+                pp, P = rec.patch.p, rec.patch.P
+                kvf = rec.patch.sym_buf(n * s * P, 2 * self.c)
+                q = rec.buf(n * s, self.c)
+                rec.add(nat.igemm, x1, self.qkv.wgt[:self.c], q, n=1, h=1, w=n * s, splitk_scratch=rec.splitk)
+                mine = kvf.local[pp * s:(pp + 1) * s]
+                rec.add(nat.igemm, x1, self.qkv.wgt[self.c:], mine, n=1, h=1, w=n * s, splitk_scratch=rec.splitk)
+                rec.patch.group_exchange(rec, mine, kvf, pp * s * 2 * self.c * 2)
+                kv5 = kvf.local.view(n, s * P, 2, self.heads, self.dh)
+                rec.add(nat.flash_attn, q.view(n, s, self.heads, self.dh), kv5[:, :, 0], kv5[:, :, 1], attn, batch=n,
+                        heads=self.heads, seq_q=s, seq_kv=s * P, head_dim=self.dh)
+                rec.release(q)
+            rec.release(x1)
+            y1 = self.o1(rec, attn.view(n * s, self.c), residual=y)
+            rec.release(attn)
+        elif not self.self_is_cross:
             qkv = self.qkv(rec, x1)
             rec.release(x1)
             v5 = qkv.view(n, s, 3, self.heads, self.dh)

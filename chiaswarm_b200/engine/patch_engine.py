@@ -1,0 +1,253 @@
+"""Patch-parallel denoiser: ONE image's UNet spread over 2 / 4 / 8 B200s (BASELINE config 3, SURVEY.md
+section 2.3 "patch / sequence parallel", kernel rows W9 / W10).  The reference runs a job on a single
+GPU (swarm/worker.py:41-43); this is the latency mode that replaces it for large single images.
+
+Layout of the gang (world = G x P):
+  * G = n_cond classifier-free-guidance branches run on disjoint GPU groups (branch g on ranks
+    [g*P, (g+1)*P)); the branches only meet in the per-step epsilon exchange;
+  * inside a group the latent is cut into P horizontal strips, rank p owns rows [p*H/P, (p+1)*H/P) of
+    every feature map, so each rank always holds a batch of exactly one strip.
+
+Every rank records the same static plan as the single-GPU engine (engine/unet_sm100.py) -- the layers
+consult `rec.patch` at the four places where a strip needs its peers, and all of that traffic is issued
+from inside kernels over the symmetric-memory arena (parallel/runtime.py), never through NCCL:
+
+  conv 3x3     feature maps live in [h+2, w, c] buffers; `sw_peer_exchange` pushes the boundary rows into
+               the neighbours' halo rows, the implicit-GEMM kernel then reads rows -1 / h through TMA
+               (a_h_total / a_y_off); image borders keep their zero halo = the conv's zero padding
+  GroupNorm    `sw_groupnorm_nhwc_dist`: partial sums pushed to every peer, folded in rank order
+  self-attn    `sw_flash_attn_gather`: K/V tiles of the other strips TMA-loaded from their owners
+  epsilon      conv_out writes this strip's slice of eps[n_cond, H, W, c]; one exchange makes it whole on
+               every rank, and every rank runs the (tiny) fused CFG + scheduler kernel redundantly
+
+Epochs: each channel (halo / GroupNorm / K-V / epsilon) owns a flag row; sync point i of a channel uses
+epoch i + tick * K, K = sync points per step and `tick` a device counter bumped once per step, so the
+captured CUDA graph replays with monotonically increasing epochs.  Peer-visible buffers are never
+recycled inside a step; the epsilon exchange is the step barrier that makes their reuse safe.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from ..ops import native as nat
+from ..parallel.runtime import Gang, SymmetricArena, SymTensor
+from .denoiser import MAX_STEPS, SM100Denoiser, _StepGraph
+from .layers import FM, Recorder, _r8
+
+
+class _Channel:
+    def __init__(self, flags: SymTensor):
+        self.flags = flags
+        self.structs: List[nat.Peers] = []
+
+
+class PatchContext:
+    def __init__(self, gang: Gang, n_cond: int, arena_bytes: int):
+        if gang.world % n_cond:
+            raise ValueError(f"{gang.world} ranks cannot be split into {n_cond} guidance groups")
+        self.gang = gang
+        self.world, self.rank = gang.world, gang.rank
+        self.G = n_cond
+        self.P = gang.world // n_cond
+        self.g, self.p = gang.rank // self.P, gang.rank % self.P
+        self.arena = SymmetricArena(gang, arena_bytes)
+        self.tick = torch.zeros(1, dtype=torch.int32, device=gang.device)
+        self._channels: Dict[str, _Channel] = {}
+        self._gn_stats: Optional[SymTensor] = None
+        self._gn_groups = 0
+
+    # ---- addressing
+    def global_rank(self, d: int) -> int:
+        return self.g * self.P + d
+
+    def _channel(self, name: str) -> _Channel:
+        ch = self._channels.get(name)
+        if ch is None:
+            ch = self._channels[name] = _Channel(self.arena.alloc_flags(8))
+        return ch
+
+    def _peers(self, name: str, peer_ptrs, scope_world: bool = False) -> nat.Peers:
+        """Next sync point of channel `name`: group scope (P strips) or the whole gang."""
+        ch = self._channel(name)
+        n = self.world if scope_world else self.P
+        me = self.rank if scope_world else self.p
+        ranks = list(range(self.world)) if scope_world else [self.global_rank(d) for d in range(self.P)]
+        flag_ptrs = [ch.flags.peer_ptr(r) for r in ranks]
+        ps = nat.make_peers(n, me, len(ch.structs) + 1, peer_ptrs, flag_ptrs, epoch_base=self.tick, epoch_mul=0)
+        ch.structs.append(ps)
+        return ps
+
+    def finalize(self):
+        """All sync points are known: epochs advance by the per-step count of their channel."""
+        for ch in self._channels.values():
+            for ps in ch.structs:
+                ps.epoch_mul = len(ch.structs)
+
+    # ---- buffers
+    def sym_buf(self, rows: int, c: int) -> SymTensor:
+        return self.arena.alloc(rows, c)
+
+    def owns(self, t: torch.Tensor) -> bool:
+        base = self.arena.buffer.data_ptr()
+        return base <= t.data_ptr() < base + self.arena.nbytes
+
+    # ---- the four communication points
+    def conv_input(self, rec: Recorder, x: FM):
+        if x.window is not None:
+            total, first = x.window
+            return x.t, dict(a_h_total=total, a_y_off=first)
+        if x.sym is None or x.n != 1:
+            raise ValueError("patch-parallel 3x3 convs need a halo-padded single-strip input")
+        st, h = x.sym, x.h
+        if self.P > 1:
+            row = x.w * x.c * 2
+            xfers = []
+            if self.p > 0:  # my first row -> bottom halo of the strip above
+                xfers.append((self.p - 1, st.local[1], st.peer_ptr(self.global_rank(self.p - 1)) + (h + 1) * row))
+            if self.p < self.P - 1:  # my last row -> top halo of the strip below
+                xfers.append((self.p + 1, st.local[h], st.peer_ptr(self.global_rank(self.p + 1))))
+            rec.add(nat.peer_exchange, self._peers("halo", None), xfers)
+        return st.local.view(1, h + 2, x.w, x.c), dict(a_h_total=h + 2, a_y_off=1)
+
+    def gn_peers(self, groups: int) -> nat.Peers:
+        if self._gn_stats is None:
+            self._gn_groups = groups
+            self._gn_stats = self.arena.alloc(2 * self.P * groups * 2, dtype=torch.float32)
+        if groups != self._gn_groups:
+            raise ValueError("patch-parallel GroupNorm expects one group count per model")
+        return self._peers("gn", [self._gn_stats.peer_ptr(self.global_rank(d)) for d in range(self.P)])
+
+    def kv_peers(self, qkv: SymTensor, c: int):
+        ranks = [self.global_rank(d) for d in range(self.P)]
+        kp = self._peers("kv", [qkv.peer_ptr(r) + 2 * c for r in ranks])
+        return kp, [qkv.peer_ptr(r) + 4 * c for r in ranks]
+
+    def group_exchange(self, rec: Recorder, local: torch.Tensor, sym: SymTensor, offset: int):
+        """All-gather inside the strip group: `local` lands at `offset` of `sym` on the other P-1 strips."""
+        ps = self._peers("kvpush", None)
+        xfers = [(d, local, sym.peer_ptr(self.global_rank(d)) + offset) for d in range(self.P) if d != self.p]
+        rec.add(nat.peer_exchange, ps, xfers)
+
+    def all_exchange(self, rec: Recorder, local: Optional[torch.Tensor], sym: Optional[SymTensor], offset: int):
+        """Every rank sends `local` (or nothing: a pure barrier) to the same offset of `sym` on all others."""
+        ps = self._peers("eps", None, scope_world=True)
+        xfers = []
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            xfers.append((r, None, 0) if local is None else (r, local, sym.peer_ptr(r) + offset))
+        rec.add(nat.peer_exchange, ps, xfers)
+
+
+class PatchRecorder(Recorder):
+    def __init__(self, device, ctx: PatchContext):
+        super().__init__(device)
+        self.patch = ctx
+
+    def fm(self, n, h, w, c) -> FM:
+        if n != 1:
+            raise ValueError("patch-parallel plans hold one strip per rank")
+        st = self.patch.arena.alloc(h + 2, w, c)
+        return FM(st.local[1:h + 1].view(1, h, w, c), 1, h, w, c, sym=st)
+
+    def release(self, t):
+        if isinstance(t, FM):
+            if t.sym is not None or t.window is not None:
+                return
+            t = t.t
+        if self.patch.owns(t):
+            return  # peers may still be reading it: peer-visible memory is only reused across steps
+        super().release(t)
+
+
+class _PatchStepGraph(_StepGraph):
+    def __init__(self, eng: "PatchDenoiser", h, w, n_cond, extra_ch, has_noise, aug, arena_bytes):
+        super().__init__(eng, 1, h, w, n_cond, extra_ch, False, has_noise, aug)
+        self.ctx = PatchContext(eng.gang, n_cond, arena_bytes)
+        if aug:
+            self.aug_full = self.aug_emb                      # [n_cond, D]: _load_job fills all branches
+            self.aug_emb = self.aug_full[self.ctx.g:self.ctx.g + 1]
+
+    def build(self, max_noise_steps: int):
+        eng, up, ctx = self.eng, self.eng.unet_plan, self.ctx
+        H, W = self.h, self.w
+        levels = len(up.boc)
+        if H % ctx.P or (H // ctx.P) % (1 << (levels - 1)):
+            raise ValueError(f"latent height {H} does not split into {ctx.P} strips at every UNet level")
+        hl = H // ctx.P
+        if self.has_noise:
+            self.noise = torch.zeros(max_noise_steps, self.rows, self.lat_c, dtype=torch.float32, device=eng.device)
+        rec = PatchRecorder(eng.device, ctx)
+        x_in = FM(self.model_in[ctx.g], 1, hl, W, up.in_pad, window=(H, ctx.p * hl))
+        temb = up.record_time_embedding(rec, 1, self.t_table, self.step, self.aug_emb)
+        mid, skips = up.record_encoder(rec, x_in, temb)
+        cpad = _r8(up.out_ch)
+        self.eps_all = ctx.arena.alloc(self.n_cond, H, W, cpad)
+        mine = self.eps_all.local[ctx.g, ctx.p * hl:(ctx.p + 1) * hl]
+        up.record_decoder(rec, mid, skips, temb, out=FM(mine.view(1, hl, W, cpad), 1, hl, W, cpad))
+        if ctx.world > 1:
+            # barrier first: nobody overwrites a peer's eps while that peer still runs the previous
+            # step's scheduler kernel on it; then the all-gather push
+            ctx.all_exchange(rec, None, None, 0)
+            off = ((ctx.g * H + ctx.p * hl) * W * cpad) * 2
+            ctx.all_exchange(rec, mine, self.eps_all, off)
+        rec.add(self._sched, FM(self.eps_all.local, self.n_cond, H, W, cpad))
+        rec.add(nat.advance_counter, self.step)
+        rec.add(nat.advance_counter, ctx.tick)
+        ctx.finalize()
+        self.rec = rec
+        return self
+
+
+class PatchDenoiser(SM100Denoiser):
+    """SM100Denoiser whose single-image jobs run patch-parallel over `gang`; every rank of the gang
+    must make the same calls with the same seeds (SPMD).  Other jobs fall back to the local engine."""
+
+    def __init__(self, pipe, gang: Gang, arena_bytes: int = 6 << 30):
+        super().__init__(pipe)
+        self.gang = gang
+        self.arena_bytes = arena_bytes
+
+    def supports(self, x, n_cond, control, inpaint) -> bool:
+        return (self.gang.world > 1 and x.shape[0] == 1 and control is None and inpaint is None
+                and self.gang.world % n_cond == 0)
+
+    @torch.no_grad()
+    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint,
+            num_frames: int = 1):
+        if not self.supports(x, n_cond, control, inpaint) or num_frames != 1:
+            return super().run(x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise,
+                               inpaint, num_frames)
+        batch, c, h, w = x.shape
+        steps = plan.num_steps
+        if steps > MAX_STEPS:
+            raise ValueError(f"at most {MAX_STEPS} denoising steps are supported")
+        extra_ch = 0 if extra is None else extra.shape[1]
+        key = ("patch", h, w, n_cond, extra_ch, noise is not None, added is not None, g_text, g_image)
+        sg = self._graphs.get(key)
+        if sg is None:
+            sg = _PatchStepGraph(self, h, w, n_cond, extra_ch, noise is not None, added is not None, self.arena_bytes)
+        g = sg.ctx.g
+        self.unet_plan.set_context(embeds[g:g + 1].to(torch.float16))
+        if key not in self._graphs:
+            sg.g_text, sg.g_image = g_text, g_image
+            sg.build(steps if noise is not None else 0)
+            self._load_patch_job(sg, x, plan, extra, added, noise)
+            sg.capture()
+            self._graphs[key] = sg
+        self._load_patch_job(sg, x, plan, extra, added, noise)
+        for _ in range(steps):
+            sg.replay()
+        self.last_launches = sg.launches_per_step * steps
+        return sg.x.view(batch, h, w, c).permute(0, 3, 1, 2).contiguous()
+
+    def _load_patch_job(self, sg: _PatchStepGraph, x, plan, extra, added, noise):
+        local_aug = sg.aug_emb
+        if added is not None:
+            sg.aug_emb = sg.aug_full
+        try:
+            self._load_job(sg, x, plan, extra, None, added, noise)
+        finally:
+            sg.aug_emb = local_aug

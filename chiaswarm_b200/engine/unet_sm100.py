@@ -135,7 +135,7 @@ class UNetPlan:
         rec.release(x)
         return x2, skips
 
-    def record_decoder(self, rec: Recorder, x: FM, skips: List[FM], temb_all) -> FM:
+    def record_decoder(self, rec: Recorder, x: FM, skips: List[FM], temb_all, out: Optional[FM] = None) -> FM:
         skips = list(skips)
         for blk in self.up:
             for i, r in enumerate(blk["resnets"]):
@@ -154,7 +154,7 @@ class UNetPlan:
                 x = x2
         g = self.norm_out(rec, x, True)
         rec.release(x)
-        out = self.conv_out(rec, g)
+        out = self.conv_out(rec, g, out=out)
         rec.release(g)
         return out
 

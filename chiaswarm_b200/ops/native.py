@@ -53,6 +53,8 @@ class IGemmParams(C.Structure):
         ("pad_w1", C.c_int32),
         ("stages", C.c_int32),
         ("cta_pair", C.c_int32),
+        ("a_h_total", C.c_int32),
+        ("a_y_off", C.c_int32),
     ]
 
 
@@ -84,12 +86,20 @@ class SchedParams(C.Structure):
 
 class Peers(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("epoch", C.c_int32),
-                ("peer", C.c_void_p * 8), ("flags", C.c_void_p * 8)]
+                ("peer", C.c_void_p * 8), ("flags", C.c_void_p * 8),
+                ("epoch_base", C.c_void_p), ("epoch_mul", C.c_int32)]
 
 
-def make_peers(world, rank, epoch, peer_ptrs, flag_ptrs) -> Peers:
+class Xfer(C.Structure):
+    _fields_ = [("dst", C.c_int32), ("src", C.c_void_p), ("dst_ptr", C.c_void_p), ("nbytes", C.c_int64)]
+
+
+def make_peers(world, rank, epoch, peer_ptrs, flag_ptrs, epoch_base=None, epoch_mul=0) -> Peers:
+    """`epoch_base` (int32 device tensor) + `epoch_mul`: effective epoch = epoch + *epoch_base * epoch_mul."""
     p = Peers()
     p.world, p.rank, p.epoch = world, rank, epoch
+    p.epoch_base = None if epoch_base is None else epoch_base.data_ptr()
+    p.epoch_mul = epoch_mul
     for d in range(world):
         p.peer[d] = peer_ptrs[d] if peer_ptrs is not None else None
         p.flags[d] = flag_ptrs[d]
@@ -115,7 +125,7 @@ def lib() -> C.CDLL:
                 "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
                 "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8", "sw_softmax_rows",
                 "sw_igemm_ag", "sw_igemm_rs", "sw_rs_reduce", "sw_peer_signal", "sw_peer_wait",
-                "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist",
+                "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist", "sw_peer_exchange",
             ):
                 getattr(l, name).restype = C.c_int
             l.sw_igemm.argtypes = [C.POINTER(IGemmParams), C.c_void_p]
@@ -126,6 +136,7 @@ def lib() -> C.CDLL:
                                        C.c_int, C.c_int, C.POINTER(Peers), C.c_void_p]
             l.sw_peer_signal.argtypes = [C.POINTER(Peers), C.c_void_p]
             l.sw_peer_wait.argtypes = [C.POINTER(Peers), C.c_void_p]
+            l.sw_peer_exchange.argtypes = [C.POINTER(Peers), C.POINTER(Xfer), C.c_int, C.c_void_p]
             l.sw_flash_attn_gather.argtypes = [C.POINTER(AttnParams), C.POINTER(Peers), C.POINTER(C.c_void_p), C.c_int,
                                                C.c_void_p]
             l.sw_groupnorm_nhwc_dist.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -184,7 +195,8 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 
 # --------------------------------------------------------------------------------------- ops
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
-          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None):
+          residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None,
+          a_h_total=0, a_y_off=0):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -194,7 +206,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     c2 = 0 if a2 is None else _f16(a2, "a2").shape[-1]
     cout = wgt.shape[0]
     assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
-    assert a1.numel() == n * h * w * c1
+    assert a1.numel() == n * (a_h_total or h) * w * c1
     # strided 2-D views (a column block of a wider matrix) are passed through leading dimensions
     a_ld = 0 if a1.is_contiguous() else a1.stride(-2)
     w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
@@ -226,6 +238,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.splitk_min_kb = splitk_min_kb
     p.stages = stages
     p.pad_w1 = 0 if pad_w is None else pad_w + 1
+    p.a_h_total, p.a_y_off = a_h_total, a_y_off
     if splitk_scratch is not None:
         p.splitk_scratch = splitk_scratch.data_ptr()
         p.splitk_scratch_bytes = splitk_scratch.numel() * splitk_scratch.element_size()
@@ -421,6 +434,24 @@ def peer_signal(peers: Peers):
 
 def peer_wait(peers: Peers):
     _check(lib().sw_peer_wait(C.byref(peers), _stream()), "sw_peer_wait")
+    _count()
+
+
+def peer_exchange(peers: Peers, transfers):
+    """transfers: [(dst index, local source tensor (contiguous), destination address on that rank)]."""
+    if not transfers:
+        return
+    arr = (Xfer * len(transfers))()
+    for i, (dst, src, dst_ptr) in enumerate(transfers):
+        arr[i].dst = dst
+        if src is None:  # flag-only transfer: pairwise barrier
+            arr[i].src, arr[i].dst_ptr, arr[i].nbytes = None, None, 0
+            continue
+        if not src.is_contiguous():
+            raise ValueError("peer_exchange: source must be contiguous")
+        arr[i].src, arr[i].dst_ptr = src.data_ptr(), dst_ptr
+        arr[i].nbytes = src.numel() * src.element_size()
+    _check(lib().sw_peer_exchange(C.byref(peers), arr, len(transfers), _stream()), "sw_peer_exchange")
     _count()
 
 

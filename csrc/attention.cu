@@ -32,6 +32,8 @@ struct AttnArgs {
     // cross-GPU K/V gather (sequence parallel): K/V rows [src*s_local, (src+1)*s_local) live on rank src
     int world, rank, epoch, s_local;
     const int* flags_local;  // this rank's int32[world] epoch flags
+    const int* epoch_base;   // optional device counter: epoch += *epoch_base * epoch_mul (graph replays)
+    int epoch_mul;
     float scale_log2;
     __half* out;
     long long o_stride_b, o_stride_s;
@@ -450,13 +452,14 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             const int per_rank = p.world > 1 ? p.s_local / BKV : nkv;
             int jj = p.world > 1 ? p.rank * per_rank : 0;  // local shard first
             int last_src = p.world > 1 ? p.rank : 0;
+            const int epoch = p.epoch + (p.epoch_base ? __ldcg(p.epoch_base) * p.epoch_mul : 0);
             for (int j = 0; j < nkv; ++j) {
                 int src = 0, row = jj * BKV;
                 if (p.world > 1) {
                     src = jj / per_rank;
                     row = (jj - src * per_rank) * BKV;
                     if (src != last_src) {  // first touch of a peer's shard: wait until it is published
-                        attn_wait_flag_ge(p.flags_local + src, p.epoch);
+                        attn_wait_flag_ge(p.flags_local + src, epoch);
                         last_src = src;
                     }
                 }
@@ -865,6 +868,8 @@ extern "C" int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpe
     a.world = world;
     a.rank = kpeers->rank;
     a.epoch = kpeers->epoch;
+    a.epoch_base = kpeers->epoch_base;
+    a.epoch_mul = kpeers->epoch_mul;
     a.s_local = s_local;
     a.flags_local = kpeers->flags[kpeers->rank];
     const int nkv = p->seq_kv / BKV;

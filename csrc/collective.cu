@@ -27,17 +27,51 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
 struct PeerFlags {
     int world, rank, epoch;
     int* flags[8];
+    const int* epoch_base;  // optional device counter: epoch += *epoch_base * epoch_mul
+    int epoch_mul;
 };
+
+__device__ __forceinline__ int resolve_epoch(const PeerFlags& f) {
+    return f.epoch + (f.epoch_base ? __ldcg(f.epoch_base) * f.epoch_mul : 0);
+}
 
 // Everything this rank wrote before (on this stream) becomes visible to the peers, then its flag
 // slot on every peer is raised to `epoch`.
 __global__ void k_peer_signal(const PeerFlags f) {
     __threadfence_system();
-    if (threadIdx.x < f.world) st_release_sys(f.flags[threadIdx.x] + f.rank, f.epoch);
+    if (threadIdx.x < f.world) st_release_sys(f.flags[threadIdx.x] + f.rank, resolve_epoch(f));
 }
 
 __global__ void k_peer_wait(const PeerFlags f) {
-    if (threadIdx.x < f.world) wait_flag_ge(f.flags[f.rank] + threadIdx.x, f.epoch);
+    if (threadIdx.x < f.world) wait_flag_ge(f.flags[f.rank] + threadIdx.x, resolve_epoch(f));
+}
+
+// Pairwise exchange (halo rows between neighbouring patches, the per-step epsilon all-gather): one
+// CTA per transfer copies `nbytes` from local memory into the destination rank's buffer over its
+// NVLink mapping (16-byte stores), publishes them (fence + release flag on the destination), then
+// waits for the flag the destination raises after ITS transfer to this rank has landed.  Every
+// rank runs the same kernel at the same point of its stream, so the waits cannot cycle.
+struct Xfers {
+    int count;
+    int dst[8];
+    const uint4* src[8];
+    uint4* dst_ptr[8];
+    long long n16[8];
+};
+
+__global__ void __launch_bounds__(1024) k_peer_exchange(const PeerFlags f, const Xfers x) {
+    const int t = blockIdx.x;
+    if (t >= x.count) return;
+    const uint4* __restrict__ src = x.src[t];
+    uint4* __restrict__ dst = x.dst_ptr[t];
+    for (long long i = threadIdx.x; i < x.n16[t]; i += blockDim.x) dst[i] = src[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int epoch = resolve_epoch(f);
+        st_release_sys(f.flags[x.dst[t]] + f.rank, epoch);
+        wait_flag_ge(f.flags[f.rank] + x.dst[t], epoch);
+    }
 }
 
 // out[r, :] = sum_src staging[src][r][:] (+ bias) (+ residual[r, :]), fp32 accumulation in rank order.
@@ -45,7 +79,7 @@ __global__ void k_rs_reduce(const __half* __restrict__ staging, __half* __restri
                             const __half* __restrict__ bias, const __half* __restrict__ residual, int m_local,
                             int ncols, int ld_stage, int ldo, int ldr, const PeerFlags f) {
     __shared__ int ready;
-    if (threadIdx.x < f.world) wait_flag_ge(f.flags[f.rank] + threadIdx.x, f.epoch);
+    if (threadIdx.x < f.world) wait_flag_ge(f.flags[f.rank] + threadIdx.x, resolve_epoch(f));
     __syncthreads();
     (void)ready;
     const int octs = ncols >> 3;
@@ -100,6 +134,8 @@ int fill(PeerFlags* f, const sw_peers* p) {
     f->world = p->world;
     f->rank = p->rank;
     f->epoch = p->epoch;
+    f->epoch_base = p->epoch_base;
+    f->epoch_mul = p->epoch_mul;
     for (int d = 0; d < p->world; ++d) f->flags[d] = p->flags[d];
     return 0;
 }
@@ -118,6 +154,33 @@ extern "C" int sw_peer_wait(const sw_peers* peers, void* stream) {
     PeerFlags f;
     if (int rc = fill(&f, peers)) return rc;
     k_peer_wait<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(f);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_peer_exchange(const sw_peers* peers, const sw_xfer* xfers, int count, void* stream) {
+    PeerFlags f;
+    if (int rc = fill(&f, peers)) return rc;
+    if (count < 0 || count > 8 || (count > 0 && !xfers)) return swh::fail(-1, "sw_peer_exchange: 0..8 transfers");
+    if (count == 0) return 0;
+    Xfers x;
+    memset(&x, 0, sizeof(x));
+    x.count = count;
+    for (int i = 0; i < count; ++i) {
+        const sw_xfer& t = xfers[i];
+        const bool empty = t.nbytes == 0;  // flag-only: a pairwise barrier
+        if (t.dst < 0 || t.dst >= peers->world || t.dst == peers->rank || t.nbytes < 0 || t.nbytes % 16 ||
+            (!empty && (!t.src || !t.dst_ptr ||
+                        (reinterpret_cast<uintptr_t>(t.src) | reinterpret_cast<uintptr_t>(t.dst_ptr)) % 16)))
+            return swh::fail(-1, "sw_peer_exchange: transfer %d is malformed (16-byte granularity, dst != rank)", i);
+        for (int j = 0; j < i; ++j)
+            if (xfers[j].dst == t.dst) return swh::fail(-1, "sw_peer_exchange: one transfer per destination");
+        x.dst[i] = t.dst;
+        x.src[i] = static_cast<const uint4*>(t.src);
+        x.dst_ptr[i] = static_cast<uint4*>(t.dst_ptr);
+        x.n16[i] = t.nbytes / 16;
+    }
+    k_peer_exchange<<<count, 1024, 0, static_cast<cudaStream_t>(stream)>>>(f, x);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }

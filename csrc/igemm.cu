@@ -28,7 +28,7 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 struct IGemmArgs {
     int c1, c2;
     int n, h, w;
-    int kh, kw, pad, pad_w;
+    int kh, kw, pad, pad_w, pad_y1;
     int cout;
     int bw, bh, bi;  // tile box: bw*bh*bi <= 128 pixels
     int tiles_x, tiles_y;
@@ -305,7 +305,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                 int kcol;
                 if (j < nkb1) {
-                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
                     kcol = tapbase + j * BK;
                 } else {
                     tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
@@ -684,6 +684,9 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     if (p->cout <= 0 || p->cout % 8) return swh::fail(-1, "sw_igemm: cout=%d not a multiple of 8", p->cout);
     if (p->n <= 0 || p->h <= 0 || p->w <= 0 || p->kh <= 0 || p->kw <= 0)
         return swh::fail(-1, "sw_igemm: bad shape");
+    if (p->a_h_total < 0 || (p->a_h_total > 0 && (mode != 0 || p->a_y_off < 0 || p->a_y_off + p->h > p->a_h_total)))
+        return swh::fail(-1, "sw_igemm: a_h_total=%d / a_y_off=%d do not contain the %d output rows", p->a_h_total,
+                         p->a_y_off, p->h);
     if (p->gn_stats) return swh::fail(-1, "sw_igemm: gn_stats epilogue not available in this build");
     if (p->bf16) return swh::fail(-1, "sw_igemm: bf16 operands not enabled in this build (fp16 only)");
     if ((p->a_ld && (p->a_ld % 8 || p->a_ld < p->c1)) || (p->w_ld % 8))
@@ -702,6 +705,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.kw = p->kw;
     a.pad = p->pad;
     a.pad_w = p->pad_w1 > 0 ? p->pad_w1 - 1 : p->pad;
+    a.pad_y1 = p->pad - p->a_y_off;  // a1 may be a taller tensor (halo rows / a window of a full image)
     a.cout = p->cout;
     pick_box(p->n, p->h, p->w, &a.bw, &a.bh, &a.bi);
     a.tiles_x = (p->w + a.bw - 1) / a.bw;
@@ -828,8 +832,9 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         tA1 = ag.m[0];
     } else {
         const uint64_t lda = p->a_ld > 0 ? uint64_t(p->a_ld) : uint64_t(p->c1);
-        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
-        const uint64_t str[3] = {lda * 2, uint64_t(p->w) * lda * 2, uint64_t(p->h) * p->w * lda * 2};
+        const uint64_t ah = p->a_h_total > 0 ? uint64_t(p->a_h_total) : uint64_t(p->h);
+        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), ah, uint64_t(p->n)};
+        const uint64_t str[3] = {lda * 2, uint64_t(p->w) * lda * 2, ah * p->w * lda * 2};
         const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
         int rc = swh::encode_tmap_f16(&tA1, p->a1, 4, dims, str, box);
         if (rc) return rc;

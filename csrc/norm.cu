@@ -19,6 +19,8 @@ struct GnDist {
     int world, rank, epoch;
     float* peer_stats[8];  // rank d: float [2 (epoch parity)][world][n][groups][2]
     int* peer_flags[8];    // rank d: int [world], slot [src] written by rank src
+    const int* epoch_base;  // optional device counter: epoch += *epoch_base * epoch_mul (graph replays)
+    int epoch_mul;
 };
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
@@ -34,6 +36,10 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
         if (i > (1u << 27)) __trap();  // a lost peer must not hang the box
         __nanosleep(64);
     }
+}
+
+__device__ __forceinline__ int gn_epoch(const GnDist& d) {
+    return d.epoch + (d.epoch_base ? __ldcg(d.epoch_base) * d.epoch_mul : 0);
 }
 
 // ---- GroupNorm statistics, deterministic: grid (chunks, n).  Thread <-> fixed channel octet,
@@ -160,7 +166,7 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
             fin[(size_t(n) * groups + g) * 2 + 1] = b;
             if (dist.world > 1) {
                 // push this rank's sums into every peer's slot [parity][rank][n][g]
-                const size_t slot = ((size_t(dist.epoch & 1) * dist.world + dist.rank) * nimg + n) * groups + g;
+                const size_t slot = ((size_t(gn_epoch(dist) & 1) * dist.world + dist.rank) * nimg + n) * groups + g;
                 for (int d = 0; d < dist.world; ++d) {
                     dist.peer_stats[d][slot * 2] = a;
                     dist.peer_stats[d][slot * 2 + 1] = b;
@@ -177,7 +183,8 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
             const unsigned int t = atomicAdd(&tickets[nimg], 1u);
             if (t == unsigned(nimg) - 1u) {
                 tickets[nimg] = 0u;
-                for (int d = 0; d < dist.world; ++d) st_release_sys(dist.peer_flags[d] + dist.rank, dist.epoch);
+                const int epoch = gn_epoch(dist);
+                for (int d = 0; d < dist.world; ++d) st_release_sys(dist.peer_flags[d] + dist.rank, epoch);
             }
         }
     }
@@ -197,8 +204,9 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
     const int n = blockIdx.y;
     const int cg = c / groups;
     const float inv_cnt = 1.0f / (float(hw) * float(cg) * float(dist.world > 1 ? dist.world : 1));
+    const int epoch = dist.world > 1 ? gn_epoch(dist) : 0;
     if (dist.world > 1) {
-        if (threadIdx.x < dist.world) wait_flag_ge(dist.peer_flags[dist.rank] + threadIdx.x, dist.epoch);
+        if (threadIdx.x < dist.world) wait_flag_ge(dist.peer_flags[dist.rank] + threadIdx.x, epoch);
         __syncthreads();
     }
     for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {
@@ -208,7 +216,7 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
             sum = sq = 0.0f;
             const float* mine = dist.peer_stats[dist.rank];
             for (int src = 0; src < dist.world; ++src) {  // fixed rank order: same bits on every rank
-                const size_t slot = ((size_t(dist.epoch & 1) * dist.world + src) * gridDim.y + n) * groups + g;
+                const size_t slot = ((size_t(epoch & 1) * dist.world + src) * gridDim.y + n) * groups + g;
                 sum += __ldcg(mine + slot * 2);
                 sq += __ldcg(mine + slot * 2 + 1);
             }
@@ -437,6 +445,8 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
         dist.world = peers->world;
         dist.rank = peers->rank;
         dist.epoch = peers->epoch;
+        dist.epoch_base = peers->epoch_base;
+        dist.epoch_mul = peers->epoch_mul;
         for (int d = 0; d < peers->world; ++d) {
             dist.peer_stats[d] = static_cast<float*>(peers->peer[d]);
             dist.peer_flags[d] = peers->flags[d];

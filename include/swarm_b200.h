@@ -31,6 +31,11 @@ typedef struct {
     int32_t world, rank, epoch;
     void* peer[8];
     int32_t* flags[8];
+    /* Optional device-resident epoch offset: the effective epoch is epoch + *epoch_base * epoch_mul.
+     * A captured CUDA graph bakes `epoch` in; the counter (advanced once per replay) keeps the
+     * flags monotonic across replays.  NULL = use `epoch` as is. */
+    const int32_t* epoch_base;
+    int32_t epoch_mul;
 } sw_peers;
 
 /* Epilogue activations for sw_igemm. */
@@ -80,6 +85,12 @@ typedef struct {
     int32_t pad_w1;      /* 0 = horizontal padding equals `pad`; else horizontal padding + 1 (temporal (3,1,1) convs) */
     int32_t stages;      /* 0 = auto, else operand ring depth (clamped to what fits in shared memory) */
     int32_t cta_pair;    /* 0 = auto, 1 = single-CTA tiles (128 x N), 2 = CTA-pair tiles (256 x N, cta_group::2) */
+    /* a1 taller than the output: a1 is [n, a_h_total, w, c1] and output row y reads input rows
+     * y + a_y_off + ky - pad (rows outside [0, a_h_total) are zero).  Patch-parallel convs read a
+     * buffer with one halo row above and below (a_h_total = h + 2, a_y_off = 1) or a window of the
+     * full image.  0 = a1 has exactly h rows. */
+    int32_t a_h_total;
+    int32_t a_y_off;
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);
@@ -106,6 +117,21 @@ int sw_rs_reduce(const void* staging_local, void* out, const void* bias, const v
  * mappings; bounded spin).  Used to publish a tensor to the peers and as the NCCL-free barrier. */
 int sw_peer_signal(const sw_peers* peers, void* stream);
 int sw_peer_wait(const sw_peers* peers, void* stream);
+
+/* Pairwise push exchange over NVLink peer mappings: for each transfer, `nbytes` (multiple of 16)
+ * go from local `src` to `dst_ptr` (an address inside rank `dst`'s mapping); the destination's
+ * flag slot [rank] is then raised to the epoch and the kernel waits for the flag rank `dst` raises
+ * after its own transfer to this rank.  Every rank of the exchange must issue the mirror call.
+ * Used for conv halo rows between neighbouring patches and for the per-step
+ * epsilon all-gather of the patch-parallel denoiser; the reference has no counterpart (single GPU
+ * per job, swarm/worker.py:41-43).  At most 8 transfers, one per destination. */
+typedef struct {
+    int32_t dst;        /* index into peers->flags */
+    const void* src;    /* local */
+    void* dst_ptr;      /* peer-mapped */
+    int64_t nbytes;
+} sw_xfer;
+int sw_peer_exchange(const sw_peers* peers, const sw_xfer* xfers, int count, void* stream);
 
 /* Flash attention (non-causal, no mask) on tcgen05: S=QK^T and O+=PV accumulate in TMEM, online
  * softmax in registers.  Replaces SDPA / xformers memory_efficient_attention (K1, K2), reference
