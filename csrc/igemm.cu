@@ -208,6 +208,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     __shared__ int s_is_last;
+    __shared__ __align__(16) float s_bias[256];
 
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B operands need 1024-byte aligned stage bases.
@@ -390,6 +391,21 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
         const size_t m = (size_t(ni) * p.h + y) * p.w + x;
 
+        // per-column addends of this tile (bias, plus the time-embedding row bias when the whole tile
+        // lies in one image) go to shared memory while the main loop runs: the per-chunk epilogue then
+        // has no global-load latency on its critical path
+        const bool fold_rb = p.row_bias != nullptr && p.bi == 1;
+        for (int i = threadIdx.x - 64; i < BN; i += 128) {
+            const int col = col0 + i;
+            float b = 0.0f;
+            if (col < p.cout) {
+                if (p.bias) b = __half2float(p.bias[col]);
+                if (fold_rb && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
+            }
+            s_bias[i] = b;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+
         if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
         __syncwarp();
         tc_fence_after();
@@ -459,59 +475,86 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         if (!do_epilogue) {
             // another split owns the epilogue of this tile
         } else if (p.act == SW_ACT_GEGLU) {
-            // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates
+            // columns [0,BN/2) of the tile are values, [BN/2,BN) their gates; the TMEM loads of chunk
+            // c+16 are in flight while chunk c is converted and stored
             const int HALF = BN / 2;
             const int ocol0 = blockIdx.y * HALF;
             const int ncols_out = p.cout / 2;
-#pragma unroll 1
-            for (int c = 0; c < HALF; c += 16) {
-                uint32_t v[16], g[16];
-                tmem_ld16(trow + c, v);
-                tmem_ld16(trow + HALF + c, g);
-                tmem_ld_wait();
-                if (row_ok && ocol0 + c < ncols_out) {
-                    uint32_t o[8];
+            auto emit = [&](int c, const uint32_t (&v)[16], const uint32_t (&g)[16]) {
+                if (!(row_ok && ocol0 + c < ncols_out)) return;
+                uint32_t o[8];
 #pragma unroll
-                    for (int j = 0; j < 16; j += 2) {
-                        float a0 = __uint_as_float(v[j]), a1 = __uint_as_float(v[j + 1]);
-                        float g0 = __uint_as_float(g[j]), g1 = __uint_as_float(g[j + 1]);
-                        if (p.bias) {
-                            a0 += __half2float(p.bias[col0 + c + j]);
-                            a1 += __half2float(p.bias[col0 + c + j + 1]);
-                            g0 += __half2float(p.bias[col0 + HALF + c + j]);
-                            g1 += __half2float(p.bias[col0 + HALF + c + j + 1]);
-                        }
-                        o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
+                for (int j = 0; j < 16; j += 2) {
+                    const float a0 = __uint_as_float(v[j]) + s_bias[c + j];
+                    const float a1 = __uint_as_float(v[j + 1]) + s_bias[c + j + 1];
+                    const float g0 = __uint_as_float(g[j]) + s_bias[HALF + c + j];
+                    const float g1 = __uint_as_float(g[j + 1]) + s_bias[HALF + c + j + 1];
+                    o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
+                }
+                uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
+                dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+            };
+            uint32_t v0[16], g0[16], v1[16], g1[16];
+            tmem_ld16(trow, v0);
+            tmem_ld16(trow + HALF, g0);
+#pragma unroll 1
+            for (int c = 0; c < HALF; c += 32) {
+                tmem_ld_wait();
+                const bool more1 = c + 16 < HALF;
+                if (more1) {
+                    tmem_ld16(trow + c + 16, v1);
+                    tmem_ld16(trow + HALF + c + 16, g1);
+                }
+                emit(c, v0, g0);
+                if (more1) {
+                    tmem_ld_wait();
+                    if (c + 32 < HALF) {
+                        tmem_ld16(trow + c + 32, v0);
+                        tmem_ld16(trow + HALF + c + 32, g0);
                     }
-                    uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
-                    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-                    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                    emit(c + 16, v1, g1);
                 }
             }
         } else {
-#pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                load_chunk(c, v);
-                if (!row_ok) continue;
+            // one 32-column chunk: addends from shared memory, residual already in registers
+            // the common case (bias / folded row bias / residual only) gets a short straight-line body:
+            // these kernels live for microseconds, so the instructions actually fetched matter
+            const bool plain = p.act == SW_ACT_NONE && p.out_scale == 1.0f && p.mode != 2 && (!p.row_bias || fold_rb);
+            const bool has_res = p.residual != nullptr;
+            __half* const out_row = p.out + m * p.ldc + col0;
+            auto emit = [&](int c, const uint32_t (&v)[32], const uint4 (&rs)[4]) {
+                if (!row_ok) return;
+                if (plain) {
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        if (col0 + c + g8 * 8 < p.cout) {
+                            const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c + g8 * 8]);
+                            const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c + g8 * 8 + 4]);
+                            float f0 = __uint_as_float(v[g8 * 8 + 0]) + b0.x, f1 = __uint_as_float(v[g8 * 8 + 1]) + b0.y;
+                            float f2 = __uint_as_float(v[g8 * 8 + 2]) + b0.z, f3 = __uint_as_float(v[g8 * 8 + 3]) + b0.w;
+                            float f4 = __uint_as_float(v[g8 * 8 + 4]) + b1.x, f5 = __uint_as_float(v[g8 * 8 + 5]) + b1.y;
+                            float f6 = __uint_as_float(v[g8 * 8 + 6]) + b1.z, f7 = __uint_as_float(v[g8 * 8 + 7]) + b1.w;
+                            if (has_res) {
+                                const float2 r0 = unpack_h2(rs[g8].x), r1 = unpack_h2(rs[g8].y);
+                                const float2 r2 = unpack_h2(rs[g8].z), r3 = unpack_h2(rs[g8].w);
+                                f0 += r0.x, f1 += r0.y, f2 += r1.x, f3 += r1.y;
+                                f4 += r2.x, f5 += r2.y, f6 += r3.x, f7 += r3.y;
+                            }
+                            *reinterpret_cast<uint4*>(out_row + c + g8 * 8) =
+                                make_uint4(pack_h2(f0, f1), pack_h2(f2, f3), pack_h2(f4, f5), pack_h2(f6, f7));
+                        }
+                    }
+                    return;
+                }
 #pragma unroll
                 for (int g8 = 0; g8 < 4; ++g8) {
                     const int col = col0 + c + g8 * 8;
                     if (col >= p.cout) break;
                     float f[8];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]);
-                    if (p.bias) {
-                        const uint4 b = *reinterpret_cast<const uint4*>(p.bias + col);
-                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float2 t2 = unpack_h2(bw[j]);
-                            f[2 * j] += t2.x;
-                            f[2 * j + 1] += t2.y;
-                        }
-                    }
-                    if (p.row_bias) {
+                    for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g8 * 8 + j]) + s_bias[c + g8 * 8 + j];
+                    if (p.row_bias && !fold_rb) {  // tile spans several images (tiny feature maps)
                         const uint4 b = *reinterpret_cast<const uint4*>(
                             p.row_bias + size_t(ni) * p.row_bias_ld + col);
                         const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
@@ -534,9 +577,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                         for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
                     }
                     if (p.residual) {
-                        const uint4 b =
-                            *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
-                        const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+                        const uint32_t bw[4] = {rs[g8].x, rs[g8].y, rs[g8].z, rs[g8].w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             const float2 t2 = unpack_h2(bw[j]);
@@ -554,6 +595,47 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     *reinterpret_cast<uint4*>(dst) =
                         make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
                                    pack_h2(f[6], f[7]));
+                }
+            };
+            // residual of chunk c (read before this thread writes those columns: in-place adds are fine)
+            auto fetch = [&](int c, uint4 (&rs)[4]) {
+                if (!p.residual || !row_ok) return;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const int col = col0 + c + g8 * 8;
+                    if (col < p.cout) rs[g8] = *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
+                }
+            };
+            if (my_partials != nullptr) {
+                // split-K owner: chunks come from the parked partial tiles
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    uint32_t v[32];
+                    uint4 rs[4];
+                    fetch(c, rs);
+                    load_chunk(c, v);
+                    emit(c, v, rs);
+                }
+            } else {
+                // TMEM chunk c+32 and its residual are in flight while chunk c is converted and stored
+                uint32_t vn[32];
+                uint4 rn[4];
+                tmem_ld32(trow, vn);
+                fetch(0, rn);
+#pragma unroll 1
+                for (int c = 0; c < BN; c += 32) {
+                    uint32_t v[32];
+                    uint4 rs[4];
+                    tmem_ld_wait_dep(vn);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = vn[j];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) rs[j] = rn[j];
+                    if (c + 32 < BN) {
+                        tmem_ld32(trow + c + 32, vn);
+                        fetch(c + 32, rn);
+                    }
+                    emit(c, v, rs);
                 }
             }
         }
@@ -646,8 +728,8 @@ int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, c
     int dev = 0;
     SW_CUDA_OK(cudaGetDevice(&dev));
     if (dev < 64 && !configured[dev]) {
-        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         configured[dev] = true;
     }
     const int ntile = (a.cout + a.bn - 1) / a.bn;
@@ -863,8 +945,8 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         int dev = 0;
         SW_CUDA_OK(cudaGetDevice(&dev));
         if (dev < 64 && !configured[dev]) {
-            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+            SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
             configured[dev] = true;
         }
         const int ntile = (a.cout + a.bn - 1) / a.bn;
