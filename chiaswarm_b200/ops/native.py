@@ -125,7 +125,7 @@ def lib() -> C.CDLL:
                 "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
                 "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8", "sw_softmax_rows",
                 "sw_igemm_ag", "sw_igemm_rs", "sw_rs_reduce", "sw_peer_signal", "sw_peer_wait",
-                "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist", "sw_peer_exchange",
+                "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist", "sw_peer_exchange", "sw_groupnorm_nhwc_zeroed",
             ):
                 getattr(l, name).restype = C.c_int
             l.sw_igemm.argtypes = [C.POINTER(IGemmParams), C.c_void_p]
@@ -145,6 +145,9 @@ def lib() -> C.CDLL:
             l.sw_groupnorm_nhwc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                             C.c_int, C.c_void_p, C.c_void_p]
+            l.sw_groupnorm_nhwc_zeroed.argtypes = l.sw_groupnorm_nhwc.argtypes
+            l.sw_groupnorm_kernel_count.restype = C.c_int
+            l.sw_groupnorm_kernel_count.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
             l.sw_groupnorm_scratch_floats.restype = C.c_int64
             l.sw_groupnorm_scratch_floats.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
             l.sw_layernorm.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
@@ -282,15 +285,17 @@ def groupnorm_scratch_floats(n, hw, c, groups) -> int:
     return int(lib().sw_groupnorm_scratch_floats(n, hw, c, groups))
 
 
-def groupnorm(x, gamma, beta, out, *, n, hw, groups, eps, silu, stats, x2=None):
+def groupnorm(x, gamma, beta, out, *, n, hw, groups, eps, silu, stats, x2=None, scratch_zeroed=False):
+    """`scratch_zeroed`: the caller zeroed `stats` once at allocation (skips the per-call memset node)."""
     c1 = x.shape[-1]
     c2 = 0 if x2 is None else x2.shape[-1]
     need = groupnorm_scratch_floats(n, hw, c1 + c2, groups)
     if stats.numel() < need:
         raise ValueError(f"groupnorm scratch too small: {stats.numel()} < {need} floats")
-    _check(lib().sw_groupnorm_nhwc(_ptr(x), _ptr(x2), _ptr(out), _ptr(gamma), _ptr(beta), n, hw, c1, c2,
-                                   groups, eps, int(silu), _ptr(stats), _stream()), "sw_groupnorm_nhwc")
-    _count(2)
+    fn = lib().sw_groupnorm_nhwc_zeroed if scratch_zeroed else lib().sw_groupnorm_nhwc
+    _check(fn(_ptr(x), _ptr(x2), _ptr(out), _ptr(gamma), _ptr(beta), n, hw, c1, c2, groups, eps, int(silu),
+              _ptr(stats), _stream()), "sw_groupnorm_nhwc")
+    _count(lib().sw_groupnorm_kernel_count(n, hw, c1 + c2, groups))
     return out
 
 

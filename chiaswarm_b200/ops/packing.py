@@ -28,17 +28,19 @@ def pad_vector(b: torch.Tensor | None, n_pad: int) -> torch.Tensor | None:
     return out
 
 
-def interleave_geglu(w: torch.Tensor, b: torch.Tensor | None):
-    """GEGLU projection [2*inner, d] = [values; gates] -> blocks of 64 value rows followed by their
-    64 gate rows, so one 128-wide MMA tile holds both halves and the epilogue can fuse x*gelu(g)."""
+def interleave_geglu(w: torch.Tensor, b: torch.Tensor | None, half: int = 64):
+    """GEGLU projection [2*inner, d] = [values; gates] -> blocks of `half` value rows followed by their
+    `half` gate rows, so one 2*half-wide MMA tile holds both halves and the epilogue can fuse x*gelu(g).
+    half = 64 pairs with tile_n = 128, half = 128 with tile_n = 256."""
     two_inner = w.shape[0]
     inner = two_inner // 2
-    assert inner % 64 == 0, "GEGLU inner dim must be a multiple of 64"
+    assert half in (64, 128) and inner % half == 0, "GEGLU inner dim must be a multiple of the tile half"
     val, gate = w[:inner], w[inner:]
-    wi = torch.stack([val.reshape(inner // 64, 64, -1), gate.reshape(inner // 64, 64, -1)], dim=1)
+    wi = torch.stack([val.reshape(inner // half, half, -1), gate.reshape(inner // half, half, -1)], dim=1)
     wi = wi.reshape(two_inner, -1).contiguous()
     bi = None
     if b is not None:
         bv, bg = b[:inner], b[inner:]
-        bi = torch.stack([bv.reshape(inner // 64, 64), bg.reshape(inner // 64, 64)], dim=1).reshape(two_inner).contiguous()
+        bi = torch.stack([bv.reshape(inner // half, half), bg.reshape(inner // half, half)], dim=1)
+        bi = bi.reshape(two_inner).contiguous()
     return wi, bi

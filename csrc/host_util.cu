@@ -41,6 +41,11 @@ static EncodeTiledFn get_encode() {
 
 int encode_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box) {
+    return encode_tmap_f16_ex(out, base, rank, dims, strides_bytes, box, true);
+}
+
+int encode_tmap_f16_ex(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                       const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return fail(-2, "cuTensorMapEncodeTiled entry point unavailable");
     cuuint64_t gd[5];
@@ -61,7 +66,7 @@ int encode_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t
                         (unsigned long long)gs[i]);
     CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, (cuuint32_t)rank,
                      const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         return fail(-4,

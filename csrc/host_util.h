@@ -23,6 +23,9 @@ int fail(int code, const char* fmt, ...);
 // strides_bytes[i] is the byte stride of dim i+1. Returns 0 on success.
 int encode_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box);
+// Same, with an explicit swizzle choice (false = CU_TENSOR_MAP_SWIZZLE_NONE: rows of the box are dense).
+int encode_tmap_f16_ex(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128);
 
 int sm_count();
 

@@ -5,6 +5,10 @@
 #include "common.cuh"
 #include "host_util.h"
 
+#include <cooperative_groups.h>
+
+#include <stdlib.h>
+
 namespace {
 
 using namespace sw;
@@ -276,6 +280,157 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
     for (; r < r1; r += rows_per_pass) apply_row(*reinterpret_cast<const uint4*>(src + size_t(r) * cs), r);
 }
 
+// ---- Fused GroupNorm: ONE launch, the tensor is read from global memory once.
+// One thread-block cluster per image: each CTA parks its rows in shared memory while it accumulates the
+// statistics, pushes its per-group partial sums into every CTA of the cluster through distributed shared
+// memory, and after one hardware cluster barrier folds the partials in rank order (deterministic) and
+// normalises its rows straight out of shared memory.  No global scratch, no atomics, no second read.
+// The host takes this path whenever an image fits in the cluster's shared memory (clusters of up to
+// 16 CTAs): every GroupNorm of the SD / SDXL UNets except the widest skip-concats at full resolution.
+__global__ void __launch_bounds__(1024)
+    k_gn_fused(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1, __half* __restrict__ y,
+               const __half* __restrict__ gamma, const __half* __restrict__ beta, int hw, int c, int groups, float eps,
+               int silu, int rows_per_cta, int rows_per_pass) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    pdl_trigger();
+    pdl_wait();
+    extern __shared__ __align__(16) uint8_t gsm[];
+    __shared__ float s_all[16 * 64 * 2];  // [rank][group][2], written by every CTA of the cluster
+    __shared__ float s_mean[64], s_rstd[64];
+    const int octs = c >> 3;
+    const int n = blockIdx.y;
+    const int csize = int(cluster.num_blocks());
+    const int crank = int(cluster.block_rank());
+    const int r0 = crank * rows_per_cta;
+    const int r1 = min(hw, r0 + rows_per_cta);
+    const int oct = threadIdx.x % octs;
+    const int rp = threadIdx.x / octs;
+    uint4* slab = reinterpret_cast<uint4*>(gsm);
+    float* sh = reinterpret_cast<float*>(slab + size_t(rows_per_cta) * octs);  // [rows_per_pass][c][2]
+    float* chs = sh + size_t(rows_per_pass) * c * 2;                            // [c][2]
+
+    const bool active = rp < rows_per_pass;
+    const bool first = oct * 8 < c1;
+    const int cs = first ? c1 : c - c1;
+    const __half* src = (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
+    // affine parameters of this thread's 8 channels: in flight while the rows stream in
+    uint4 gv = make_uint4(0x3C003C00u, 0x3C003C00u, 0x3C003C00u, 0x3C003C00u), bv = make_uint4(0, 0, 0, 0);
+    if (active) {
+        if (gamma) gv = *reinterpret_cast<const uint4*>(gamma + oct * 8);
+        if (beta) bv = *reinterpret_cast<const uint4*>(beta + oct * 8);
+    }
+    if (active) {
+        float s[8], ss[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
+        auto acc = [&](const uint4& v) {
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_h2(w[j]);
+                s[2 * j] += f.x;
+                ss[2 * j] += f.x * f.x;
+                s[2 * j + 1] += f.y;
+                ss[2 * j + 1] += f.y * f.y;
+            }
+        };
+        int r = r0 + rp;
+        for (; r + 7 * rows_per_pass < r1; r += 8 * rows_per_pass) {
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const uint4*>(src + size_t(r + u * rows_per_pass) * cs);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                slab[size_t(r + u * rows_per_pass - r0) * octs + oct] = v[u];
+                acc(v[u]);
+            }
+        }
+        for (; r < r1; r += rows_per_pass) {
+            const uint4 v = *reinterpret_cast<const uint4*>(src + size_t(r) * cs);
+            slab[size_t(r - r0) * octs + oct] = v;
+            acc(v);
+        }
+        float* dst = sh + (size_t(rp) * c + oct * 8) * 2;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            dst[2 * i] = s[i];
+            dst[2 * i + 1] = ss[i];
+        }
+    }
+    __syncthreads();
+    for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {  // per-channel totals over the row passes (fixed order)
+        float a = 0.0f, b = 0.0f;
+        for (int k = 0; k < rows_per_pass; ++k) {
+            a += sh[(size_t(k) * c + ch) * 2];
+            b += sh[(size_t(k) * c + ch) * 2 + 1];
+        }
+        chs[2 * ch] = a;
+        chs[2 * ch + 1] = b;
+    }
+    __syncthreads();
+    const int cg_ = c / groups;
+    // (group, destination rank) pairs: this CTA's partial of group g lands in slot [crank][g] of rank d
+    for (int i = threadIdx.x; i < groups * csize; i += blockDim.x) {
+        const int g = i % groups, d = i / groups;
+        float a = 0.0f, b = 0.0f;
+        for (int k = 0; k < cg_; ++k) {
+            a += chs[2 * (g * cg_ + k)];
+            b += chs[2 * (g * cg_ + k) + 1];
+        }
+        float* remote = cluster.map_shared_rank(s_all, d);
+        remote[(crank * 64 + g) * 2] = a;
+        remote[(crank * 64 + g) * 2 + 1] = b;
+    }
+    cluster.sync();  // release / acquire: every partial of the image is now in this CTA's s_all
+    if (threadIdx.x < groups) {
+        const int g = threadIdx.x;
+        float a = 0.0f, b = 0.0f;
+        for (int k = 0; k < csize; ++k) {  // rank order: the same bits in every CTA and on every launch
+            a += s_all[(k * 64 + g) * 2];
+            b += s_all[(k * 64 + g) * 2 + 1];
+        }
+        const float inv_cnt = 1.0f / (float(hw) * float(cg_));
+        const float mean = a * inv_cnt;
+        const float var = fmaxf(b * inv_cnt - mean * mean, 0.0f);
+        s_mean[g] = mean;
+        s_rstd[g] = rsqrtf(var + eps);
+    }
+    __syncthreads();
+    if (!active) return;
+    float a[8], b[8];
+    {
+        const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 gf = unpack_h2(gw[j]), bf = unpack_h2(bw[j]);
+            const int g0 = (oct * 8 + 2 * j) / cg_, g1 = (oct * 8 + 2 * j + 1) / cg_;
+            a[2 * j] = s_rstd[g0] * gf.x;
+            b[2 * j] = bf.x - s_mean[g0] * a[2 * j];
+            a[2 * j + 1] = s_rstd[g1] * gf.y;
+            b[2 * j + 1] = bf.y - s_mean[g1] * a[2 * j + 1];
+        }
+    }
+    __half* out = y + (size_t(n) * hw) * c + oct * 8;
+    for (int r = r0 + rp; r < r1; r += rows_per_pass) {
+        const uint4 v = slab[size_t(r - r0) * octs + oct];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_h2(w[j]);
+            float u0 = fmaf(f.x, a[2 * j], b[2 * j]);
+            float u1 = fmaf(f.y, a[2 * j + 1], b[2 * j + 1]);
+            if (silu) {
+                u0 = silu_f(u0);
+                u1 = silu_f(u1);
+            }
+            o[j] = pack_h2(u0, u1);
+        }
+        *reinterpret_cast<uint4*>(out + size_t(r) * c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 // ---- LayerNorm: one warp per row, row cached in registers (c <= 2048).
 template <int MAX_OCT>
 __global__ void k_layernorm(const __half* __restrict__ x, __half* __restrict__ y,
@@ -421,9 +576,51 @@ static GnGeom gn_geom(int hw, int c) {
     return g;
 }
 
+// Geometry of the fused single-launch path; cluster == 0 when the tensor does not qualify.
+struct GnFusedGeom {
+    int rows_per_pass, threads, rows_per_cta, cluster, chunks;
+    size_t smem;
+};
+static GnFusedGeom gn_fused_geom(int n, int hw, int c, int groups) {
+    GnFusedGeom g;
+    memset(&g, 0, sizeof(g));
+    static int enabled = -1;  // SW_GN_FUSED=0 keeps the two-kernel path (A/B runs)
+    if (enabled < 0) {
+        const char* e = getenv("SW_GN_FUSED");
+        enabled = e ? atoi(e) : 1;
+    }
+    const int octs = c / 8;
+    if (!enabled || groups > 64 || octs > 1024 || n > 65535) return g;
+    g.rows_per_pass = 512 / octs;
+    if (g.rows_per_pass < 1) g.rows_per_pass = 1;
+    g.threads = (octs * g.rows_per_pass + 31) / 32 * 32;
+    // largest cluster (<= 16 CTAs) that still gives every CTA a full pass of rows; more CTAs per image
+    // = more SMs pulling the tensor in (one SM ingests ~40 B/clk)
+    for (int cl = 16; cl >= 1; cl >>= 1) {
+        int rpc = (hw + cl - 1) / cl;
+        rpc = (rpc + g.rows_per_pass - 1) / g.rows_per_pass * g.rows_per_pass;
+        if (cl > 1 && rpc * (cl - 1) >= hw) continue;  // trailing CTAs would own no rows
+        const size_t smem = size_t(rpc) * c * 2 + (size_t(g.rows_per_pass) * c * 2 + size_t(c) * 2) * sizeof(float);
+        if (smem > 216 * 1024) break;  // smaller clusters only need more
+        g.rows_per_cta = rpc;
+        g.cluster = cl;
+        g.chunks = cl;
+        g.smem = smem;
+        break;
+    }
+    return g;
+}
+
+extern "C" int sw_groupnorm_kernel_count(int n, int hw, int c, int groups) {
+    if (c <= 0 || c % 8 || hw <= 0 || n <= 0 || groups <= 0) return -1;
+    return gn_fused_geom(n, hw, c, groups).cluster > 0 ? 1 : 2;
+}
+
 extern "C" int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups) {
     if (c <= 0 || c % 8 || hw <= 0 || n <= 0 || groups <= 0) return -1;
     const GnGeom g = gn_geom(hw, c);
+    const GnFusedGeom f = gn_fused_geom(n, hw, c, groups);
+    (void)f;  // the single-launch path needs no scratch
     return int64_t(n) * groups * 2 + n + 1 + int64_t(n) * g.chunks * groups * 2;
 }
 
@@ -433,9 +630,9 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
 
 // Shared by the public entry points; `scratch` must already be usable device memory of at least
 // sw_groupnorm_scratch_floats() floats.
-int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
-                        int n, int hw, int c1, int c2, int groups, float eps, int silu,
-                        float* scratch, cudaStream_t st, const sw_peers* peers) {
+static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                     int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                     float* scratch, cudaStream_t st, const sw_peers* peers, bool scratch_zeroed) {
     const int c = c1 + c2;
     GnDist dist;
     memset(&dist, 0, sizeof(dist));
@@ -457,6 +654,26 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
     if (c % 8 || groups <= 0 || c % groups)
         return swh::fail(-1, "sw_groupnorm_nhwc: c=%d groups=%d unsupported", c, groups);
     if (c / 8 > 1024) return swh::fail(-1, "sw_groupnorm_nhwc: c=%d too wide", c);
+    if (dist.world == 1) {
+        const GnFusedGeom f = gn_fused_geom(n, hw, c, groups);
+        if (f.cluster > 0) {
+            static bool configured[64] = {false};
+            int dev = 0;
+            SW_CUDA_OK(cudaGetDevice(&dev));
+            if (dev < 64 && !configured[dev]) {
+                SW_CUDA_OK(cudaFuncSetAttribute(k_gn_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
+                SW_CUDA_OK(cudaFuncSetAttribute(k_gn_fused, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+                configured[dev] = true;
+            }
+            (void)scratch_zeroed;
+            SW_CUDA_OK(swh::launch_pdl(k_gn_fused, dim3(f.cluster, n), dim3(f.threads), f.smem, st, f.cluster,
+                                       static_cast<const __half*>(x), static_cast<const __half*>(x2), c1,
+                                       static_cast<__half*>(y), static_cast<const __half*>(gamma),
+                                       static_cast<const __half*>(beta), hw, c, groups, eps, silu, f.rows_per_cta,
+                                       f.rows_per_pass));
+            return 0;
+        }
+    }
     const GnGeom g = gn_geom(hw, c);
     // only the ticket counters have to start at zero
     SW_CUDA_OK(cudaMemsetAsync(scratch + size_t(n) * groups * 2, 0, sizeof(float) * size_t(n + 1), st));
@@ -473,12 +690,26 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
     return 0;
 }
 
+int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                        int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                        float* scratch, cudaStream_t st, const sw_peers* peers) {
+    return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, scratch, st, peers, false);
+}
+
 extern "C" int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma,
                                  const void* beta, int n, int hw, int c1, int c2, int groups,
                                  float eps, int silu, float* stats_scratch, void* stream) {
     if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc: null argument");
-    return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu,
-                               stats_scratch, static_cast<cudaStream_t>(stream), nullptr);
+    return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, stats_scratch,
+                     static_cast<cudaStream_t>(stream), nullptr, false);
+}
+
+extern "C" int sw_groupnorm_nhwc_zeroed(const void* x, const void* x2, void* y, const void* gamma,
+                                        const void* beta, int n, int hw, int c1, int c2, int groups,
+                                        float eps, int silu, float* stats_scratch, void* stream) {
+    if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc_zeroed: null argument");
+    return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, stats_scratch,
+                     static_cast<cudaStream_t>(stream), nullptr, true);
 }
 
 extern "C" int sw_groupnorm_nhwc_dist(const void* x, const void* x2, void* y, const void* gamma,

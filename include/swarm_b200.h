@@ -171,9 +171,19 @@ int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpeers, const 
  * `stats_scratch` is caller-owned fp32 memory of sw_groupnorm_scratch_floats(n,hw,c,groups)
  * floats; its contents need no initialisation. */
 int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups);
+/* Kernels sw_groupnorm_nhwc launches for this shape: 1 (single-launch path) or 2 (statistics + apply). */
+int sw_groupnorm_kernel_count(int n, int hw, int c, int groups);
 int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                       int n, int hw, int c1, int c2, int groups, float eps, int silu,
                       float* stats_scratch, void* stream);
+/* Same operation for callers that zero `stats_scratch` ONCE when they allocate it (the engine's
+ * plan recorder): tensors that fit in the SMs' shared memory (every GroupNorm of the UNets) then run
+ * as a single launch -- rows parked in shared memory, grid-wide barrier on two scratch words that
+ * the kernel returns to zero, deterministic fold, apply from shared memory -- with no memset node.
+ * sw_groupnorm_nhwc takes the same single-launch path but clears those words first. */
+int sw_groupnorm_nhwc_zeroed(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
+                             int n, int hw, int c1, int c2, int groups, float eps, int silu,
+                             float* stats_scratch, void* stream);
 
 /* GroupNorm over a feature map whose rows are sharded across `peers->world` GPUs (patch /
  * sequence parallel): the statistics all-reduce (SURVEY.md collective call site 4) is done by the

@@ -68,7 +68,7 @@ for (m, n, k, geglu) in shapes:
     t_ref = graph_time([(lambda i=i: F.linear(xs[i], ws[i], bs[i])) for i in range(POOL)])
     row = []
     for t, pr, mk, st in cfgs:
-        if geglu and t not in (0, 128):
+        if geglu and t not in (0, 128, 256):
             row.append(float("nan"))
             continue
         if t > max(64, (n + 31) // 32 * 32):

@@ -35,8 +35,18 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
     torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == DeviceType.CUDA and not e.name.startswith(("Memset", "Memcpy"))]
 evs.sort(key=lambda e: e.time_range.start)
-KERNELS = {"groupnorm": 2, "groupnorm_dist": 2}
-need = sum(KERNELS.get(getattr(fn, "__name__", ""), 1) for fn, _, _ in rec.ops)
+from chiaswarm_b200.ops import native as _nat
+
+
+def nkernels(fn, args, kw):
+    name = getattr(fn, "__name__", "")
+    if name == "groupnorm":  # single-launch cluster kernel or statistics + apply, by shape
+        c = args[0].shape[-1] + (kw["x2"].shape[-1] if kw.get("x2") is not None else 0)
+        return _nat.lib().sw_groupnorm_kernel_count(kw["n"], kw["hw"], c, kw["groups"])
+    return 2 if name == "groupnorm_dist" else 1
+
+
+need = sum(nkernels(*op) for op in rec.ops)
 print(f"plan: {len(rec.ops)} ops, {need} kernels expected, {len(evs)} kernel records")
 if need != len(evs):
     names = defaultdict(int)
@@ -66,7 +76,7 @@ kinds = defaultdict(lambda: [0.0, 0.0])
 i = 0
 total = 0.0
 for fn, args, kw in rec.ops:
-    k = KERNELS.get(getattr(fn, "__name__", ""), 1)
+    k = nkernels(fn, args, kw)
     t = sum(e.time_range.elapsed_us() for e in evs[i:i + k])
     i += k
     f = flops(fn, args, kw)

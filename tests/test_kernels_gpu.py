@@ -80,7 +80,8 @@ def test_conv_split_k(nat):
     assert _rel_err(out, ref) < 4e-3
 
 
-def test_linear_geglu(nat):
+@pytest.mark.parametrize("half", [64, 128])
+def test_linear_geglu(nat, half):
     from chiaswarm_b200.ops.packing import interleave_geglu
 
     torch.manual_seed(2)
@@ -88,8 +89,8 @@ def test_linear_geglu(nat):
     x = torch.randn(m, d, device="cuda", dtype=torch.float16)
     w = torch.randn(8 * d, d, device="cuda", dtype=torch.float16) * (d ** -0.5)
     b = torch.randn(8 * d, device="cuda", dtype=torch.float16)
-    wi, bi = interleave_geglu(w, b)
-    out = nat.linear(x, wi, bias=bi, act=nat.ACT_GEGLU)
+    wi, bi = interleave_geglu(w, b, half)
+    out = nat.linear(x, wi, bias=bi, act=nat.ACT_GEGLU, tile_n=2 * half)
     h = x.float() @ w.float().t() + b.float()
     val, gate = h.chunk(2, dim=-1)
     ref = val * F.gelu(gate)
@@ -232,6 +233,11 @@ def test_groupnorm(nat, n, hw, c1, c2, groups, silu):
     out2 = torch.empty_like(out)
     nat.groupnorm(x1, g, b, out2, n=n, hw=hw, groups=groups, eps=1e-5, silu=silu, stats=stats, x2=x2)
     assert torch.equal(out, out2)  # fixed-order reduction: bit-reproducible, scratch reusable
+    zeroed = torch.zeros_like(stats)  # engine contract: scratch zeroed once, no per-call memset node
+    for _ in range(2):
+        out3 = torch.empty_like(out)
+        nat.groupnorm(x1, g, b, out3, n=n, hw=hw, groups=groups, eps=1e-5, silu=silu, stats=zeroed, x2=x2, scratch_zeroed=True)
+        assert torch.equal(out, out3)
     xc = x1 if x2 is None else torch.cat([x1, x2], -1)
     ref = F.group_norm(xc.float().permute(0, 2, 1), groups, g.float(), b.float(), 1e-5)
     if silu:
