@@ -22,6 +22,8 @@ ap.add_argument("--guidance", type=float, default=1.0)
 ap.add_argument("--runs", type=int, default=0, help="timed full-pipeline runs (0 = numerics only)")
 ap.add_argument("--tol", type=float, default=3e-2)
 ap.add_argument("--skip-single", action="store_true")
+ap.add_argument("--nccl-baseline", action="store_true",
+                help="also time one UNet forward of the NCCL-only patch-parallel path (parallel/patch.py, eager torch)")
 args = ap.parse_args()
 
 from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
@@ -75,6 +77,41 @@ if ref is not None:
     ok = ok and res["rel_err_vs_single"] < args.tol
 if args.runs:
     res["patch_ms"] = timed(args.runs)
+    # one denoising step of the captured plan, all ranks in lockstep
+    torch.cuda.synchronize()
+    gang.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        sg.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    res["patch_step_ms"] = gang.all_reduce_max(e0.elapsed_time(e1) / 10)
+if args.nccl_baseline:
+    from chiaswarm_b200.parallel.patch import PatchParallelUNet
+
+    n_cond = 2 if args.guidance > 1.0 else 1
+    lat = args.size // 8
+    x = torch.randn(n_cond, 4, lat, lat, device=dev, dtype=torch.float16)
+    ctx_dim = pipe.unet.config["cross_attention_dim"]
+    ctx = torch.randn(n_cond, 77, ctx_dim, device=dev, dtype=torch.float16)
+    added = None
+    if pipe.unet.config.get("addition_embed_type") == "text_time":
+        added = {"text_embeds": torch.randn(n_cond, 1280, device=dev, dtype=torch.float16),
+                 "time_ids": torch.tensor([[args.size, args.size, 0, 0, args.size, args.size]] * n_cond, device=dev,
+                                          dtype=torch.float32)}
+    ppu = PatchParallelUNet(pipe.unet, gang)
+    for _ in range(2):
+        ppu(x, 500.0, ctx, added)
+    torch.cuda.synchronize()
+    gang.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        ppu(x, 500.0, ctx, added)
+    e1.record()
+    torch.cuda.synchronize()
+    res["nccl_patch_step_ms"] = gang.all_reduce_max(e0.elapsed_time(e1) / 5)
 ok = gang.all_reduce_max(0.0 if ok else 1.0) == 0.0
 if gang.rank == 0:
     print(json.dumps(res))
