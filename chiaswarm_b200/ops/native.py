@@ -14,6 +14,7 @@ from pathlib import Path
 import torch
 
 from ..build_native import LIB_PATH, build
+from . import tuning
 
 _lock = threading.Lock()
 _lib = None
@@ -215,6 +216,10 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
     if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
         raise ValueError("strided a1 is only supported for plain GEMMs")
+    if tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0:
+        tuned = tuning.lookup(n, h, w, kh, kw, c1, c2, cout, act, residual is not None)
+        if tuned is not None:
+            tile_n, cta_pair, splitk_min_kb = tuned
     p = IGemmParams()
     p.a1, p.a2 = _ptr(a1), _ptr(a2)
     p.c1, p.c2 = c1, c2

@@ -49,7 +49,8 @@ struct IGemmArgs {
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
     int splits;         // split-K factor (grid.z)
     int kb_per_split;   // k-blocks per split
-    unsigned int* tickets;  // [tiles] arrival counters (split-K), self-resetting
+    unsigned int* tickets;  // [tiles] arrival counters (split-K)
+    unsigned int* done;     // [tiles] departure counters: the last split to leave zeroes both
     float* partials;        // [tile][split][bn/32][128][32] fp32
     // ---- fused collectives (plain GEMMs only; see sw_igemm_ag / sw_igemm_rs)
     int mode;               // 0 local, 1 all-gather fused into the A loads, 2 reduce-scatter push epilogue
@@ -209,7 +210,6 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const int BN = p.bn;
     const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    __shared__ int s_is_last;
     __shared__ __align__(16) float s_bias[256];
 
     extern __shared__ uint8_t smem_raw[];
@@ -423,20 +423,25 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         tc_fence_after();
         const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
 
-        // ---- split-K: every split parks its fp32 tile in scratch; the split that arrives last
-        // (ticket counter) sums all of them in split order -- a fixed order, so the result does
-        // not depend on which CTA happened to finish last -- and runs the epilogue.
-        const float* my_partials = nullptr;
+        // ---- split-K: every split parks its fp32 tile in scratch, then ALL splits of the tile (they are
+        // co-resident: the host sizes the grid to one wave) wait for each other and each reduces its own
+        // band of rows -- sums in split order, so the result is bit-reproducible -- and runs the epilogue
+        // for that band.  The reduction is spread over every participating SM instead of serialising
+        // on the CTA that happened to arrive last (that version lost to no split at all beyond 4 splits).
         if (p.splits > 1) {
             const int tile_id = blockIdx.x * gridDim.y + blockIdx.y;
             const int nchunk = BN / 32;
             float* tile_base = p.partials + size_t(tile_id) * p.splits * nchunk * 4096;
             float* mine = tile_base + size_t(blockIdx.z) * nchunk * 4096 + r * 32;
+            uint32_t vn[32];
+            tmem_ld32(trow, vn);
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t v[32];
-                tmem_ld32(trow + c, v);
-                tmem_ld_wait();
+                tmem_ld_wait_dep(vn);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = vn[j];
+                if (c + 32 < BN) tmem_ld32(trow + c + 32, vn);
                 float4* dst = reinterpret_cast<float4*>(mine + (c / 32) * 4096);
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
@@ -446,44 +451,73 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             __threadfence();
             asm volatile("bar.sync 1, 128;" ::: "memory");
             if (threadIdx.x == 64) {
-                const unsigned int t = atomicAdd(&p.tickets[tile_id], 1u);
-                const int last = (t == unsigned(p.splits) - 1u);
-                if (last) p.tickets[tile_id] = 0u;  // ready for the next launch
-                s_is_last = last;
+                atomicAdd(&p.tickets[tile_id], 1u);
+                const volatile unsigned int* t = p.tickets + tile_id;
+                for (unsigned int i = 0; *t < unsigned(p.splits); ++i) {
+                    if (i > (1u << 26)) __trap();  // a split that never became resident must not hang the box
+                    __nanosleep(20);
+                }
+                __threadfence();
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (s_is_last) {
-                __threadfence();
-                my_partials = tile_base + r * 32;
+            // my band of rows; items = (row, 8-column group), consecutive threads -> consecutive columns
+            const int band = (128 + p.splits - 1) / p.splits;
+            const int row_begin = int(blockIdx.z) * band;
+            const int row_end = min(128, row_begin + band);
+            const int g8s = BN >> 3;
+            const int items = max(0, row_end - row_begin) * g8s;
+            for (int i = threadIdx.x - 64; i < items; i += 128) {
+                const int rr = row_begin + i / g8s;
+                const int c8 = (i - (i / g8s) * g8s) << 3;
+                const int col = col0 + c8;
+                const int xl2 = rr % p.bw, t2 = rr / p.bw;
+                const int yl2 = t2 % p.bh, nl2 = t2 / p.bh;
+                const int xx = x0 + xl2, yy = y0 + yl2, nn = n0 + nl2;
+                if (!(nl2 < p.bi && xx < p.w && yy < p.h && nn < p.n) || col >= p.cout) continue;
+                const size_t mm = (size_t(nn) * p.h + yy) * p.w + xx;
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = 0.0f;
+                const float* src = tile_base + size_t(c8 >> 5) * 4096 + rr * 32 + (c8 & 31);
+                for (int z = 0; z < p.splits; ++z) {
+                    const float4 a0 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * nchunk * 4096));
+                    const float4 a1 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * nchunk * 4096) + 1);
+                    f[0] += a0.x, f[1] += a0.y, f[2] += a0.z, f[3] += a0.w;
+                    f[4] += a1.x, f[5] += a1.y, f[6] += a1.z, f[7] += a1.w;
+                }
+                auto add_h8 = [&](const __half* ptr) {
+                    const uint4 b = *reinterpret_cast<const uint4*>(ptr);
+                    const float2 b0 = unpack_h2(b.x), b1 = unpack_h2(b.y), b2 = unpack_h2(b.z), b3 = unpack_h2(b.w);
+                    f[0] += b0.x, f[1] += b0.y, f[2] += b1.x, f[3] += b1.y;
+                    f[4] += b2.x, f[5] += b2.y, f[6] += b3.x, f[7] += b3.y;
+                };
+                if (p.bias) add_h8(p.bias + col);
+                if (p.row_bias) add_h8(p.row_bias + size_t(nn) * p.row_bias_ld + col);
+                if (p.act == SW_ACT_SILU) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
+                } else if (p.act == SW_ACT_GELU) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                }
+                if (p.out_scale != 1.0f) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
+                }
+                if (p.residual) add_h8(p.residual + mm * p.ldr + col);
+                *reinterpret_cast<uint4*>(p.out + mm * p.ldc + col) =
+                    make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]), pack_h2(f[6], f[7]));
+            }
+            // departure: the last split to finish its band re-arms both counters for the next launch
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) {
+                if (atomicAdd(&p.done[tile_id], 1u) == unsigned(p.splits) - 1u) {
+                    p.tickets[tile_id] = 0u;
+                    p.done[tile_id] = 0u;
+                }
             }
         }
-        const bool do_epilogue = (p.splits == 1) || (my_partials != nullptr);
-        auto load_chunk = [&](int c, uint32_t (&v)[32]) {
-            if (my_partials == nullptr) {
-                tmem_ld32(trow + c, v);
-                tmem_ld_wait();
-            } else {
-                const int nchunk = BN / 32;
-                float acc[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
-                for (int z = 0; z < p.splits; ++z) {
-                    const float4* src = reinterpret_cast<const float4*>(
-                        my_partials + (size_t(z) * nchunk + c / 32) * 4096);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 f = __ldcg(src + j);
-                        acc[4 * j] += f.x;
-                        acc[4 * j + 1] += f.y;
-                        acc[4 * j + 2] += f.z;
-                        acc[4 * j + 3] += f.w;
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(acc[j]);
-            }
-        };
-
+        const bool do_epilogue = p.splits == 1;
         if (!do_epilogue) {
             // another split owns the epilogue of this tile
         } else if (p.tma_epi) {
@@ -766,17 +800,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     if (col < p.cout) rs[g8] = *reinterpret_cast<const uint4*>(p.residual + m * p.ldr + col);
                 }
             };
-            if (my_partials != nullptr) {
-                // split-K owner: chunks come from the parked partial tiles
-#pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
-                    uint32_t v[32];
-                    uint4 rs[4];
-                    fetch(c, rs);
-                    load_chunk(c, v);
-                    emit(c, v, rs);
-                }
-            } else {
+            {
                 // TMEM chunk c+32 and its residual are in flight while chunk c is converted and stored
                 uint32_t vn[32];
                 uint4 rn[4];
@@ -1006,11 +1030,20 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         bn = p->tile_n == 256 ? 256 : 128;
         if (p->cout % bn) return swh::fail(-1, "sw_igemm: GEGLU needs cout %% tile_n == 0");
     } else if (bn == 0) {
-        if (grid_x <= 4) {
-            bn = p->cout <= 32 ? 32 : 64;
-        } else {
+        // graph-timed sweeps (scripts/bench_gemm_graph.py, bench_stream.py): 128 columns is within a few
+        // percent of the best everywhere except (a) layers big enough to fill the chip several times over
+        // with 128-wide tiles, which want the widest tile (least operand re-fetch per flop), and (b) grids
+        // so small that even split-K cannot spread them, which want many narrow tiles
+        const long ctas128 = long(grid_x) * ((p->cout + 127) / 128);
+        if (2 * ctas128 >= 5L * sms) {
             const int ntiles = (p->cout + 255) / 256;
             bn = ((p->cout + ntiles - 1) / ntiles + 31) / 32 * 32;
+        } else if (p->cout <= 64) {
+            bn = p->cout <= 32 ? 32 : 64;
+        } else if (2 * ctas128 <= sms && kblocks < 16) {
+            bn = 64;
+        } else {
+            bn = p->cout < 128 ? (p->cout + 31) / 32 * 32 : 128;
         }
     }
     if (bn < 32 || bn > 256 || bn % 32) return swh::fail(-1, "sw_igemm: tile_n=%d must be a multiple of 32 in [32,256]", bn);
@@ -1055,7 +1088,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.splits = 1;
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
-    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 32;
+    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 8;
     if (mode == 0 && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
@@ -1064,13 +1097,14 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         int splits = want < max_by_k ? want : max_by_k;
         if (splits > 32) splits = 32;
         const long long per_tile = (long long)(bn / 32) * 4096 * sizeof(float);
-        const long long avail = p->splitk_scratch_bytes - (long long)kMaxSplitTiles * 4;
+        const long long avail = p->splitk_scratch_bytes - (long long)kMaxSplitTiles * 8;
         while (splits > 1 && per_tile * splits * ctas > avail) --splits;
         if (splits > 1) {
             a.kb_per_split = (kblocks + splits - 1) / splits;
             a.splits = (kblocks + a.kb_per_split - 1) / a.kb_per_split;
             a.tickets = static_cast<unsigned int*>(p->splitk_scratch);
-            a.partials = reinterpret_cast<float*>(static_cast<char*>(p->splitk_scratch) + kMaxSplitTiles * 4);
+            a.done = a.tickets + kMaxSplitTiles;
+            a.partials = reinterpret_cast<float*>(static_cast<char*>(p->splitk_scratch) + kMaxSplitTiles * 8);
             if (a.kb_per_split < a.stages) a.stages = a.kb_per_split;
         }
     }

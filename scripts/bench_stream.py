@@ -33,8 +33,8 @@ def graph_time(fns):
     return e0.elapsed_time(e1) / (5 * REPS) * 1e3
 
 
-cfgs = [(0, 0, -1), (64, 1, 4), (64, 1, 8), (64, 1, 16), (128, 1, 4), (128, 1, 8), (256, 1, 4), (256, 1, 8), (256, 2, 8),
-        (64, 1, 0), (256, 1, 0)]
+cfgs = [(0, 0, -1), (64, 1, 4), (64, 1, 8), (128, 1, 2), (128, 1, 4), (128, 1, 8), (256, 1, 2), (256, 1, 4), (256, 1, 8),
+        (256, 2, 4), (256, 2, 8), (128, 2, 4), (64, 1, 0), (256, 1, 0)]
 print("M,N,K pool | cublas | " + " ".join(f"{t}{'p' if pr == 2 else ''}/s{mk}" for t, pr, mk in cfgs))
 for (m, n, k) in [(128, 1280, 11520), (512, 1280, 11520), (128, 1280, 23040), (512, 1280, 5120), (2048, 640, 5760)]:
     for pool in (1, 6):

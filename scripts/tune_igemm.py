@@ -1,0 +1,128 @@
+"""Builds `chiaswarm_b200/ops/igemm_tuning.json`: for every distinct implicit-GEMM shape in the step plans
+of the supported pipelines, time the kernel's tile width / CTA-pair / split-K choices (CUDA graph of 8
+launches of the real plan op, device-timed, best of 3 replays) and keep the fastest.
+  python scripts/tune_igemm.py [--out gpurun_out/igemm_tuning.json]
+Run on the target GPU; copy the result over chiaswarm_b200/ops/igemm_tuning.json."""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ["SDAAS_RANDOM_INIT"] = "1"
+os.environ["SW_IGEMM_TUNING"] = "0"  # measure against the built-in heuristics, not a previous table
+import torch
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--out", default="gpurun_out/igemm_tuning.json")
+ap.add_argument("--quick", action="store_true")
+args = ap.parse_args()
+
+from chiaswarm_b200.ops import native as nat
+from chiaswarm_b200.ops import tuning
+
+dev = "cuda:0"
+REPS = 8
+
+
+def graph_time(fn):
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(REPS):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    best = 1e9
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) / REPS * 1e3)
+    return best
+
+
+def plans():
+    """(name, recorder) for every pipeline shape we serve by default."""
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline, _init_module
+
+    def sd(arch, size, guidance, batch=1, controlnet=False):
+        cn = None
+        if controlnet:
+            from chiaswarm_b200.models import configs
+            from chiaswarm_b200.models.controlnet import ControlNetModel
+
+            cn = _init_module(ControlNetModel(**configs.get_controlnet("sd15")), 9)
+        pipe = StableDiffusionPipeline.from_architecture(arch, controlnet=cn, family="sd_controlnet" if cn else None)
+        pipe.backend = "sm100"
+        pipe.to(dev, torch.float16)
+        pipe.set_scheduler("dpmpp_2m", True)
+        kw = dict(prompt="t", height=size, width=size, num_inference_steps=1, guidance_scale=guidance,
+                  num_images_per_prompt=batch, generator=torch.Generator(device=dev).manual_seed(0), output_type="device")
+        if cn is not None:
+            from PIL import Image
+
+            kw["image"] = Image.new("RGB", (size, size), (128, 128, 128))
+        pipe(**kw)
+        eng = pipe._denoiser()
+        recs = [sg.rec for sg in eng._graphs.values()] + [e[2] for e in eng._vae_graphs.values()]
+        return recs, pipe
+
+    yield "sd15-512-cfg", sd("sd15", 512, 7.5)
+    if args.quick:
+        return
+    yield "sd15-512-nocfg", sd("sd15", 512, 1.0)
+    yield "sd15-768-cn-b8", sd("sd15", 768, 7.5, batch=8, controlnet=True)
+    yield "sdxl-1024-cfg", sd("sdxl", 1024, 7.5)
+    yield "sdxl-1024-nocfg", sd("sdxl", 1024, 1.0)
+    yield "sd21-768-cfg", sd("sd21", 768, 7.5)
+
+
+CANDS = [(0, 0, 0), (64, 1, 0), (128, 1, 0), (256, 1, 0), (128, 2, 0), (256, 2, 0),
+         (64, 1, 8), (128, 1, 8), (256, 1, 8), (128, 2, 8), (256, 2, 8)]
+configs, report = {}, []
+for name, (recs, keep) in plans():
+    seen = 0
+    for rec in recs:
+        for fn, a, kw in rec.ops:
+            if getattr(fn, "__name__", "") != "igemm" or kw.get("tile_n") or kw.get("pad_w") is not None:
+                continue
+            a1, wgt = a[0], a[1]
+            c1 = a1.shape[-1]
+            c2 = 0 if kw.get("a2") is None else kw["a2"].shape[-1]
+            act = kw.get("act", 0)
+            key = tuning.key_of(kw["n"], kw["h"], kw["w"], kw.get("kh", 1), kw.get("kw", 1), c1, c2, wgt.shape[0], act,
+                                kw.get("residual") is not None)
+            if key in configs:
+                continue
+            seen += 1
+            times = []
+            for t, pr, mk in CANDS:
+                if act == nat.ACT_GEGLU and t not in (0, 128):
+                    continue
+                if t > max(64, (wgt.shape[0] + 31) // 32 * 32):
+                    continue
+                k2 = dict(kw, tile_n=t, cta_pair=pr, splitk_min_kb=mk)
+                try:
+                    times.append((graph_time(lambda: fn(*a, **k2)), (t, pr, mk)))
+                except Exception:
+                    pass
+            times.sort()
+            base = [x for x, c in times if c == (0, 0, 0)]
+            configs[key] = times[0][1]
+            report.append((name, key, times[0][1], times[0][0], base[0] if base else float("nan")))
+    print(f"{name}: {seen} new shapes", flush=True)
+    del recs, keep
+    torch.cuda.empty_cache()
+gain = sum(b - t for _, _, _, t, b in report if b == b)
+print(f"{len(configs)} shapes; sum over distinct shapes: heuristic {sum(b for *_, b in report if b == b):.0f} us -> tuned "
+      f"{sum(t for *_, t, _ in report):.0f} us (-{gain:.0f} us)")
+for name, key, cfg, t, b in sorted(report, key=lambda r: r[3] - r[4])[:40]:
+    print(f"  {name:18s} {key:44s} -> {cfg}  {b:7.1f} -> {t:7.1f} us")
+os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
+with open(args.out, "w") as f:
+    json.dump({"device": torch.cuda.get_device_name(0), "configs": {k: list(v) for k, v in configs.items()}}, f, indent=0)
+print("wrote", args.out)
