@@ -396,7 +396,8 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
     uint64_t* s_full = bars + 1;    // 2
     uint64_t* p_full = bars + 3;    // 2 (128 arrivals each)
     uint64_t* pv_done = bars + 5;   // 2
-    uint64_t* k_full = bars + 7;    // kst
+    uint64_t* s_free = bars + 7;    // 2 (128 arrivals each): S has been copied to registers
+    uint64_t* k_full = bars + 9;    // kst
     uint64_t* k_empty = k_full + kst;
     uint64_t* v_full = k_empty + kst;
     uint64_t* v_empty = v_full + vst;
@@ -419,6 +420,7 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 mbar_init(&s_full[t], 1);
                 mbar_init(&p_full[t], 128);
                 mbar_init(&pv_done[t], 1);
+                mbar_init(&s_free[t], 128);
             }
             for (int s = 0; s < kst; ++s) {
                 mbar_init(&k_full[s], 1);
@@ -518,16 +520,18 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                     }
                 }
             };
+            // The two Q tiles run half a period apart: a tile's S = Q K^T is issued when the OTHER tile has
+            // just copied its scores to registers, so one tile drains TMEM (tcgen05.ld, ~64 B/clk) while
+            // the other sits in the exponentials (MUFU) instead of both fighting for the same unit.
             mbar_wait(q_full, 0);
             mbar_wait(&k_full[0], 0);
             tc_fence_after();
             issue_qk(0, k_lo0);
             umma_commit(&s_full[0]);
+            mbar_wait(&s_free[0], 0);  // tile 0 holds S0(0) in registers
+            tc_fence_after();
             issue_qk(1, k_lo0);
             umma_commit(&s_full[1]);
-            if (nkv == 1 || kst > 1) {
-                // K[0] is free once both S tiles are computed (only matters for the ring bookkeeping)
-            }
             umma_commit(&k_empty[0]);
             int sk = (kst > 1) ? 1 : 0;           // ring slot of K[j+1]
             uint32_t phk = (kst > 1) ? 0u : 1u;   // its full-barrier parity
@@ -540,23 +544,21 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 const uint32_t acc0 = j > 0 ? 1u : 0u;
                 const uint32_t k_lo = k_lo0 + uint32_t(sk) * tile_step;
                 const uint32_t v_lo = v_lo0 + uint32_t(sv) * tile_step;
-                // ---- tile 0: its softmax has drained S0 and published P0
-                mbar_wait(&p_full[0], uint32_t(j & 1));
-                tc_fence_after();
-                if (more) {
+                if (more) {  // tile 1 has copied S1(j): tile 0 may start on S0(j+1)
+                    mbar_wait(&s_free[1], uint32_t(j & 1));
                     mbar_wait(&k_full[sk], phk);
                     tc_fence_after();
                     issue_qk(0, k_lo);
                     umma_commit(&s_full[0]);
                 }
+                mbar_wait(&p_full[0], uint32_t(j & 1));
                 mbar_wait(&v_full[sv], phv);
                 tc_fence_after();
                 issue_pv(0, v_lo, kp, acc0);
                 umma_commit(&pv_done[0]);
-                // ---- tile 1
-                mbar_wait(&p_full[1], uint32_t(j & 1));
-                tc_fence_after();
-                if (more) {
+                if (more) {  // tile 0 has copied S0(j+1): tile 1 may start on S1(j+1)
+                    mbar_wait(&s_free[0], uint32_t((j + 1) & 1));
+                    tc_fence_after();
                     issue_qk(1, k_lo);
                     umma_commit(&s_full[1]);
                     umma_commit(&k_empty[sk]);
@@ -565,6 +567,8 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                         phk ^= 1;
                     }
                 }
+                mbar_wait(&p_full[1], uint32_t(j & 1));
+                tc_fence_after();
                 issue_pv(1, v_lo, kp, acc0);
                 umma_commit(&v_empty[sv]);
                 umma_commit(&pv_done[1]);
@@ -593,107 +597,48 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             if (lane == 0) mbar_wait(&s_full[t], uint32_t(j & 1));
             __syncwarp();
             tc_fence_after();
-            if (j == 0) {
-                // first tile: the reference max is this tile's row max
-                float mx = -INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < BKV; c += 32) {
-                    if (c >= kv_valid) break;  // warp-uniform
-                    uint32_t v[32];
-                    tmem_ld32(tS + c, v);
-                    tmem_ld_wait();
+            // The whole score row moves to registers in one go and the TMEM tile is handed back at once:
+            // the MMA warp computes the next S = Q K^T while this row is still in the exponentials.
+            uint32_t s0[32], s1[32], s2[32], s3[32];
+            tmem_ld32(tS, s0);
+            tmem_ld32(tS + 32, s1);
+            tmem_ld32(tS + 64, s2);
+            tmem_ld32(tS + 96, s3);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s_free[t]);
+            // exact running maximum (online softmax); the reference only moves when the row outgrows
+            // it by more than 2^8, so most tiles skip the O rescale
+            // (four independent running maxima / sums per thread: with two softmax warps per scheduler a
+            // 128-long dependent FMNMX or FADD chain is pure exposed latency)
+            float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+            auto row_max = [&](const uint32_t (&v)[32], int c) {
+                if (kv_valid == BKV) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mxa[i & 3] = fmaxf(mxa[i & 3], __uint_as_float(v[i]));
+                } else {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
-                        if (c + i < kv_valid) mx = fmaxf(mx, __uint_as_float(v[i]));
+                        if (c + i < kv_valid) mxa[i & 3] = fmaxf(mxa[i & 3], __uint_as_float(v[i]));
                 }
-                m_ref = mx * scale;
+            };
+            row_max(s0, 0);
+            row_max(s1, 32);
+            row_max(s2, 64);
+            row_max(s3, 96);
+            const float mx = fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3]));
+            const float m_new = mx * scale;
+            bool need = false;
+            if (j == 0) {
+                m_ref = m_new;
             } else {
+                need = m_new > m_ref + 8.0f;
                 if (lane == 0) mbar_wait(&pv_done[t], uint32_t((j - 1) & 1));  // O stable, P tile free
                 __syncwarp();
                 tc_fence_after();
-            }
-            // P = exp2(S*scale - m_ref) -> fp16 -> swizzled smem; returns the row sum and tracks the
-            // largest P (as packed halves: P > 2^8 <=> the row outgrew the reference by more than 8).
-            float xmax = -INFINITY;
-            auto chunk_full = [&](const uint32_t (&v)[32], int c, float& lsum, __half2& pmax) {
-                uint32_t pk[16];
-#pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    const float e0 = ex2(fmaf(__uint_as_float(v[i]), scale, -m_ref));
-                    const float e1 = ex2(fmaf(__uint_as_float(v[i + 1]), scale, -m_ref));
-                    lsum += e0 + e1;
-                    const __half2 h = __floats2half2_rn(e0, e1);
-                    pmax = __hmax2(pmax, h);
-                    pk[i >> 1] = *reinterpret_cast<const uint32_t*>(&h);
-                }
-                uint8_t* slab = prow + (c >> 6) * SLAB_BYTES;
-                const int cc0 = (c & 63) >> 3;
-#pragma unroll
-                for (int g = 0; g < 4; ++g)
-                    *reinterpret_cast<uint4*>(slab + (((cc0 + g) ^ rsw) << 4)) =
-                        make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
-            };
-            auto emit_p = [&]() -> float {
-                float lsum = 0.0f;
-                if (kv_valid == BKV) {
-                    // full tile: TMEM loads software-pipelined against the exponentials
-                    __half2 pmax = __floats2half2_rn(0.0f, 0.0f);
-                    uint32_t va[32], vb[32];
-                    tmem_ld32(tS, va);
-                    tmem_ld_wait_dep(va);
-                    tmem_ld32(tS + 32, vb);
-                    chunk_full(va, 0, lsum, pmax);
-                    tmem_ld_wait_dep(vb);
-                    tmem_ld32(tS + 64, va);
-                    chunk_full(vb, 32, lsum, pmax);
-                    tmem_ld_wait_dep(va);
-                    tmem_ld32(tS + 96, vb);
-                    chunk_full(va, 64, lsum, pmax);
-                    tmem_ld_wait_dep(vb);
-                    chunk_full(vb, 96, lsum, pmax);
-                    const float pm = fmaxf(__low2float(pmax), __high2float(pmax));
-                    xmax = pm > 256.0f ? log2f(fminf(pm, 60000.0f)) : 0.0f;  // only > 8 matters
-                    if (pm > 60000.0f) xmax = 17.0f;                          // overflowed: force a rescale
-                    return lsum;
-                }
-                xmax = -INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < BKV; c += 32) {
-                    uint32_t pk[16];
-                    if (c < kv_valid) {
-                        uint32_t v[32];
-                        tmem_ld32(tS + c, v);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int i = 0; i < 32; i += 2) {
-                            const bool ok0 = c + i < kv_valid, ok1 = c + i + 1 < kv_valid;
-                            const float x0 = ok0 ? fmaf(__uint_as_float(v[i]), scale, -m_ref) : -INFINITY;
-                            const float x1 = ok1 ? fmaf(__uint_as_float(v[i + 1]), scale, -m_ref) : -INFINITY;
-                            xmax = fmaxf(xmax, fmaxf(x0, x1));
-                            const float e0 = ok0 ? ex2(x0) : 0.0f, e1 = ok1 ? ex2(x1) : 0.0f;
-                            lsum += e0 + e1;
-                            pk[i >> 1] = pack_h2(e0, e1);
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) pk[i] = 0u;
-                    }
-                    uint8_t* slab = prow + (c >> 6) * SLAB_BYTES;
-                    const int cc0 = (c & 63) >> 3;
-#pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        *reinterpret_cast<uint4*>(slab + (((cc0 + g) ^ rsw) << 4)) =
-                            make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
-                }
-                return lsum;
-            };
-            float lsum = emit_p();
-            if (j > 0) {
-                for (int fix = 0; fix < 8; ++fix) {
-                    const bool need = xmax > 8.0f;  // this row outgrew the reference: rescale and redo
-                    if (!__any_sync(0xffffffffu, need)) break;
-                    const float alpha = need ? ex2(-xmax) : 1.0f;
-                    if (need) m_ref += xmax;
+                if (__any_sync(0xffffffffu, need)) {
+                    const float alpha = need ? ex2(m_ref - m_new) : 1.0f;
+                    if (need) m_ref = m_new;
 #pragma unroll 1
                     for (int c = 0; c < p.dpad; c += 16) {
                         uint32_t o[16];
@@ -705,10 +650,41 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                     }
                     tmem_st_wait();
                     l *= alpha;
-                    lsum = emit_p();
                 }
             }
-            l += lsum;
+            // P = exp2(S*scale - m_ref) -> fp16 -> swizzled smem
+            float ls[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            auto chunk = [&](const uint32_t (&v)[32], int c) {
+                uint32_t pk[16];
+                if (kv_valid == BKV) {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        const float e0 = ex2(fmaf(__uint_as_float(v[i]), scale, -m_ref));
+                        const float e1 = ex2(fmaf(__uint_as_float(v[i + 1]), scale, -m_ref));
+                        ls[(i >> 1) & 3] += e0 + e1;
+                        pk[i >> 1] = pack_h2(e0, e1);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 2) {
+                        const float e0 = c + i < kv_valid ? ex2(fmaf(__uint_as_float(v[i]), scale, -m_ref)) : 0.0f;
+                        const float e1 = c + i + 1 < kv_valid ? ex2(fmaf(__uint_as_float(v[i + 1]), scale, -m_ref)) : 0.0f;
+                        ls[(i >> 1) & 3] += e0 + e1;
+                        pk[i >> 1] = pack_h2(e0, e1);
+                    }
+                }
+                uint8_t* slab = prow + (c >> 6) * SLAB_BYTES;
+                const int cc0 = (c & 63) >> 3;
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    *reinterpret_cast<uint4*>(slab + (((cc0 + g) ^ rsw) << 4)) =
+                        make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+            };
+            chunk(s0, 0);
+            chunk(s1, 32);
+            chunk(s2, 64);
+            chunk(s3, 96);
+            l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(&p_full[t]);
