@@ -1088,7 +1088,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.splits = 1;
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
-    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 8;
+    const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
     if (mode == 0 && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;

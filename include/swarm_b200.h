@@ -81,7 +81,7 @@ typedef struct {
                             zero-filled once before first use (the kernel leaves it reusable);
                             calls sharing one scratch must be stream-ordered. */
     int64_t splitk_scratch_bytes;
-    int32_t splitk_min_kb; /* 0 = default (8): fewest 64-wide K blocks a split may get */
+    int32_t splitk_min_kb; /* 0 = default (16): fewest 64-wide K blocks a split may get */
     int32_t pad_w1;      /* 0 = horizontal padding equals `pad`; else horizontal padding + 1 (temporal (3,1,1) convs) */
     int32_t stages;      /* 0 = auto, else operand ring depth (clamped to what fits in shared memory) */
     int32_t cta_pair;    /* 0 = auto, 1 = single-CTA tiles (128 x N), 2 = CTA-pair tiles (256 x N, cta_group::2) */

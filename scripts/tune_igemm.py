@@ -25,13 +25,14 @@ dev = "cuda:0"
 REPS = 8
 
 
-def graph_time(fn):
-    fn()
-    torch.cuda.synchronize()
+_flush = torch.empty(192 << 20, dtype=torch.uint8, device=dev)
+
+
+def _replay_time(build):
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for _ in range(REPS):
-            fn()
+            build()
     g.replay()
     torch.cuda.synchronize()
     best = 1e9
@@ -43,6 +44,22 @@ def graph_time(fn):
         torch.cuda.synchronize()
         best = min(best, e0.elapsed_time(e1) / REPS * 1e3)
     return best
+
+
+def graph_time(fn, acts=()):
+    """us per launch in the state the op sees inside a step: weights cold (L2 flushed before every
+    launch), activations warm (touched after the flush, as if the previous layer had just written them).
+    The flush + touch cost is measured separately and subtracted."""
+    fn()
+    torch.cuda.synchronize()
+
+    def prep():
+        _flush.zero_()
+        for a in acts:
+            a.mul_(1)
+
+    base = _replay_time(prep)
+    return _replay_time(lambda: (prep(), fn())) - base
 
 
 def plans():
@@ -81,8 +98,9 @@ def plans():
     yield "sd21-768-cfg", sd("sd21", 768, 7.5)
 
 
-CANDS = [(0, 0, 0), (64, 1, 0), (128, 1, 0), (256, 1, 0), (128, 2, 0), (256, 2, 0),
-         (64, 1, 8), (128, 1, 8), (256, 1, 8), (128, 2, 8), (256, 2, 8)]
+# (tile_n, cta_pair, splitk_min_kb): 64 k-blocks per split = effectively no split-K for the UNet shapes
+CANDS = [(0, 0, 0), (64, 1, 64), (128, 1, 64), (256, 1, 64), (128, 2, 64), (256, 2, 64),
+         (64, 1, 8), (128, 1, 8), (256, 1, 8), (128, 2, 8), (256, 2, 8), (64, 1, 16), (128, 1, 16), (256, 1, 16)]
 configs, report = {}, []
 for name, (recs, keep) in plans():
     seen = 0
@@ -107,7 +125,8 @@ for name, (recs, keep) in plans():
                     continue
                 k2 = dict(kw, tile_n=t, cta_pair=pr, splitk_min_kb=mk)
                 try:
-                    times.append((graph_time(lambda: fn(*a, **k2)), (t, pr, mk)))
+                    acts = [x for x in (a1, kw.get("a2"), kw.get("residual")) if x is not None]
+                    times.append((graph_time(lambda: fn(*a, **k2), acts), (t, pr, mk)))
                 except Exception:
                     pass
             times.sort()
