@@ -16,6 +16,8 @@ import torch
 ap = argparse.ArgumentParser()
 ap.add_argument("--out", default="gpurun_out/igemm_tuning.json")
 ap.add_argument("--quick", action="store_true")
+ap.add_argument("--only", default="", help="comma-separated plan names to (re)tune")
+ap.add_argument("--merge", default="", help="existing table to extend (its entries are kept unless re-measured)")
 args = ap.parse_args()
 
 from chiaswarm_b200.ops import native as nat
@@ -88,25 +90,43 @@ def plans():
         recs = [sg.rec for sg in eng._graphs.values()] + [e[2] for e in eng._vae_graphs.values()]
         return recs, pipe
 
-    yield "sd15-512-cfg", sd("sd15", 512, 7.5)
-    if args.quick:
-        return
-    yield "sd15-512-nocfg", sd("sd15", 512, 1.0)
-    yield "sd15-768-cn-b8", sd("sd15", 768, 7.5, batch=8, controlnet=True)
-    yield "sdxl-1024-cfg", sd("sdxl", 1024, 7.5)
-    yield "sdxl-1024-nocfg", sd("sdxl", 1024, 1.0)
-    yield "sd21-768-cfg", sd("sd21", 768, 7.5)
+    def t2v():
+        from chiaswarm_b200.video.pipeline_t2v import TextToVideoPipeline
+
+        pipe = TextToVideoPipeline.from_architecture("zeroscope").to(dev, torch.float16)
+        pipe.backend = "sm100"
+        pipe.set_scheduler("dpmpp_2m", True)
+        pipe(prompt="t", height=320, width=576, num_frames=24, num_inference_steps=1,
+             generator=torch.Generator(device=dev).manual_seed(0))
+        eng = pipe._sm100()
+        return [sg.rec for sg in eng._graphs.values()] + [e[2] for e in eng._vae_graphs.values()], pipe
+
+    only = [x for x in args.only.split(",") if x]
+    todo = [("sd15-512-cfg", lambda: sd("sd15", 512, 7.5))]
+    if not args.quick:
+        todo += [("sd15-512-nocfg", lambda: sd("sd15", 512, 1.0)),
+                 ("sd15-768-cn-b8", lambda: sd("sd15", 768, 7.5, batch=8, controlnet=True)),
+                 ("sdxl-1024-cfg", lambda: sd("sdxl", 1024, 7.5)),
+                 ("sdxl-1024-nocfg", lambda: sd("sdxl", 1024, 1.0)),
+                 ("sd21-768-cfg", lambda: sd("sd21", 768, 7.5)),
+                 ("zeroscope-576x320x24", t2v)]
+    for name, make in todo:
+        if not only or name in only:
+            yield name, make()
 
 
 # (tile_n, cta_pair, splitk_min_kb): 64 k-blocks per split = effectively no split-K for the UNet shapes
 CANDS = [(0, 0, 0), (64, 1, 64), (128, 1, 64), (256, 1, 64), (128, 2, 64), (256, 2, 64),
          (64, 1, 8), (128, 1, 8), (256, 1, 8), (128, 2, 8), (256, 2, 8), (64, 1, 16), (128, 1, 16), (256, 1, 16)]
 configs, report = {}, []
+kept = {}
+if args.merge and os.path.isfile(args.merge):
+    kept = {k: tuple(v) for k, v in json.load(open(args.merge)).get("configs", {}).items()}
 for name, (recs, keep) in plans():
     seen = 0
     for rec in recs:
         for fn, a, kw in rec.ops:
-            if getattr(fn, "__name__", "") != "igemm" or kw.get("tile_n") or kw.get("pad_w") is not None:
+            if getattr(fn, "__name__", "") != "igemm" or kw.get("tile_n"):
                 continue
             a1, wgt = a[0], a[1]
             c1 = a1.shape[-1]
@@ -143,5 +163,6 @@ for name, key, cfg, t, b in sorted(report, key=lambda r: r[3] - r[4])[:40]:
     print(f"  {name:18s} {key:44s} -> {cfg}  {b:7.1f} -> {t:7.1f} us")
 os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
 with open(args.out, "w") as f:
-    json.dump({"device": torch.cuda.get_device_name(0), "configs": {k: list(v) for k, v in configs.items()}}, f, indent=0)
+    kept.update(configs)
+    json.dump({"device": torch.cuda.get_device_name(0), "configs": {k: list(v) for k, v in kept.items()}}, f, indent=0)
 print("wrote", args.out)
