@@ -38,6 +38,9 @@ struct AttnArgs {
     __half* out;
     long long o_stride_b, o_stride_s;
     uint32_t idesc_qk, idesc_pv;
+    // v1, short sequences (temporal attention: seq = frames): `pack` batch entries share one 128-row
+    // tile (TMA box {64, 1, seq, pack}); the softmax masks everything outside a row's own entry
+    int pack;
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -85,10 +88,14 @@ __global__ void __launch_bounds__(kThreads)
     uint64_t* kv_empty = v_full + stages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(kv_empty + stages);
 
+    const int pack = p.pack;  // > 1: blockIdx.z walks groups of `pack` batch entries
     const int q0 = blockIdx.x * BQ;
     const int head = blockIdx.y;
-    const int b = blockIdx.z;
+    const int b = blockIdx.z * pack;
     const int nkv = (p.seq_kv + BKV - 1) / BKV;
+    // bytes one TMA box delivers per 64-wide slab (a packed box has pack * seq rows, not 128)
+    const uint32_t q_tx = uint32_t(nslab) * uint32_t(pack > 1 ? pack * p.seq_q : BQ) * 128u;
+    const uint32_t kv_tx = uint32_t(nslab) * uint32_t(pack > 1 ? pack * p.seq_kv : BKV) * 128u;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -111,6 +118,13 @@ __global__ void __launch_bounds__(kThreads)
         __syncwarp();
         tmem_alloc_rt(tmem_slot, uint32_t(p.tmem_cols));
     }
+    if (pack > 1) {
+        // rows past pack * seq of the operand tiles are never written by TMA: clear them once so the
+        // P.V product cannot pick up stale NaNs (P is zero there, but 0 * NaN is not)
+        for (int i = threadIdx.x; i < (1 + 2 * stages) * tile_bytes / 16; i += blockDim.x)
+            reinterpret_cast<uint4*>(sQ)[i] = make_uint4(0, 0, 0, 0);
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -120,18 +134,18 @@ __global__ void __launch_bounds__(kThreads)
 
     if (warp == 0) {
         if (lane == 0) {
-            mbar_expect_tx(q_full, uint32_t(tile_bytes));
+            mbar_expect_tx(q_full, q_tx);
             for (int sl = 0; sl < nslab; ++sl)
                 tma_load_4d(sQ + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0, b);
             int s = 0;
             uint32_t ph = 0;
             for (int j = 0; j < nkv; ++j) {
                 mbar_wait(&kv_empty[s], ph ^ 1);
-                mbar_expect_tx(&k_full[s], uint32_t(tile_bytes));
+                mbar_expect_tx(&k_full[s], kv_tx);
                 for (int sl = 0; sl < nslab; ++sl)
                     tma_load_4d(sK + s * tile_bytes + sl * SLAB_BYTES, &tmK, &k_full[s], sl * 64,
                                 head, j * BKV, b);
-                mbar_expect_tx(&v_full[s], uint32_t(tile_bytes));
+                mbar_expect_tx(&v_full[s], kv_tx);
                 for (int sl = 0; sl < nslab; ++sl)
                     tma_load_4d(sV + s * tile_bytes + sl * SLAB_BYTES, &tmV, &v_full[s], sl * 64,
                                 head, j * BKV, b);
@@ -192,7 +206,7 @@ __global__ void __launch_bounds__(kThreads)
                 }
                 mbar_wait(&v_full[s], ph);
                 tc_fence_after();
-                const int kv_valid = min(BKV, p.seq_kv - j * BKV);
+                const int kv_valid = pack > 1 ? pack * p.seq_kv : min(BKV, p.seq_kv - j * BKV);
                 const int kp = (kv_valid + 15) >> 4;
                 const uint32_t v_lo = v_lo0 + uint32_t(s) * stage_step;
                 const uint32_t acc0 = j > 0 ? 1u : 0u;
@@ -226,10 +240,14 @@ __global__ void __launch_bounds__(kThreads)
         uint8_t* prow = sP + (r >> 3) * 1024 + (r & 7) * 128;
         const int rsw = r & 7;
 
+        // columns of S this row may attend to: the whole tile, or (packed) its own batch entry's block
+        const int grp = pack > 1 ? r / p.seq_q : 0;
+        const int col_lo = pack > 1 ? grp * p.seq_kv : 0;
         float m_ref = -INFINITY;
         float l = 0.0f;
         for (int j = 0; j < nkv; ++j) {
-            const int kv_valid = min(BKV, p.seq_kv - j * BKV);
+            const int kv_valid = pack > 1 ? pack * p.seq_kv : min(BKV, p.seq_kv - j * BKV);
+            const int col_hi = pack > 1 ? col_lo + p.seq_kv : kv_valid;
             if (lane == 0) mbar_wait(s_full, uint32_t(j & 1));
             __syncwarp();
             tc_fence_after();
@@ -243,7 +261,7 @@ __global__ void __launch_bounds__(kThreads)
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
-                    if (c + i < kv_valid) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    if (c + i >= col_lo && c + i < col_hi) mx = fmaxf(mx, __uint_as_float(v[i]));
             }
             const float m_new = fmaxf(m_ref, mx * p.scale_log2);
             if (j > 0) {
@@ -281,10 +299,10 @@ __global__ void __launch_bounds__(kThreads)
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
-                        float e0 = (c + i < kv_valid)
+                        float e0 = (c + i >= col_lo && c + i < col_hi)
                                        ? ex2(fmaf(__uint_as_float(v[i]), p.scale_log2, -m_ref))
                                        : 0.0f;
-                        float e1 = (c + i + 1 < kv_valid)
+                        float e1 = (c + i + 1 >= col_lo && c + i + 1 < col_hi)
                                        ? ex2(fmaf(__uint_as_float(v[i + 1]), p.scale_log2, -m_ref))
                                        : 0.0f;
                         lsum += e0 + e1;
@@ -311,8 +329,12 @@ __global__ void __launch_bounds__(kThreads)
         __syncwarp();
         tc_fence_after();
         const float inv_l = 1.0f / l;
-        const int qi = q0 + r;
-        __half* orow = p.out + (long long)b * p.o_stride_b + (long long)qi * p.o_stride_s +
+        int qi = q0 + r, bo = b;
+        if (pack > 1) {  // row r = (batch entry grp, position r - grp * seq)
+            qi = (grp < pack && b + grp < p.batch) ? r - grp * p.seq_q : p.seq_q;  // seq_q = "do not store"
+            bo = b + grp;
+        }
+        __half* orow = p.out + (long long)bo * p.o_stride_b + (long long)qi * p.o_stride_s +
                        (long long)head * p.head_dim;
 #pragma unroll 1
         for (int c = 0; c < p.dpad; c += 16) {
@@ -738,10 +760,10 @@ __global__ void __launch_bounds__(kThreads2, 1)
 }
 
 int make_qkv_map(CUtensorMap* m, const void* base, int d, int heads, int seq, int batch,
-                 long long sb, long long ss, long long sh) {
+                 long long sb, long long ss, long long sh, int pack = 1) {
     const uint64_t dims[4] = {uint64_t(d), uint64_t(heads), uint64_t(seq), uint64_t(batch)};
     const uint64_t str[3] = {uint64_t(sh) * 2, uint64_t(ss) * 2, uint64_t(sb) * 2};
-    const uint32_t box[4] = {64, 1, 128, 1};
+    const uint32_t box[4] = {64, 1, pack > 1 ? uint32_t(seq) : 128u, uint32_t(pack)};
     return swh::encode_tmap_f16(m, base, 4, dims, str, box);
 }
 
@@ -775,15 +797,28 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
     a.idesc_qk = sw::umma_idesc(128, 128, 0, 0, 0);
     a.idesc_pv = sw::umma_idesc(128, a.dpad, 0, 0, 1);
 
+    // short self-attention sequences (temporal attention over frames): several batch entries per tile
+    a.pack = 1;
+    if (p->seq_q == p->seq_kv && p->seq_q <= 64 && p->batch > 1) {
+        a.pack = 128 / p->seq_q;
+        if (a.pack > p->batch) a.pack = p->batch;
+        if (a.pack > 128) a.pack = 128;
+        static int no_pack = -1;  // SW_ATTN_PACK=0: one batch entry per tile (A/B runs)
+        if (no_pack < 0) {
+            const char* e = getenv("SW_ATTN_PACK");
+            no_pack = (e && atoi(e) == 0) ? 1 : 0;
+        }
+        if (no_pack) a.pack = 1;
+    }
     CUtensorMap tq, tk, tv;
     int rc = make_qkv_map(&tq, p->q, p->head_dim, p->heads, p->seq_q, p->batch, p->q_stride_b,
-                          p->q_stride_s, p->q_stride_h);
+                          p->q_stride_s, p->q_stride_h, a.pack);
     if (rc) return rc;
     rc = make_qkv_map(&tk, p->k, p->head_dim, p->heads, p->seq_kv, p->batch, p->k_stride_b,
-                      p->k_stride_s, p->k_stride_h);
+                      p->k_stride_s, p->k_stride_h, a.pack);
     if (rc) return rc;
     rc = make_qkv_map(&tv, p->v, p->head_dim, p->heads, p->seq_kv, p->batch, p->v_stride_b,
-                      p->v_stride_s, p->v_stride_h);
+                      p->v_stride_s, p->v_stride_h, a.pack);
     if (rc) return rc;
 
     static bool configured[64] = {false};
@@ -811,7 +846,7 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
     }
     const int smem = tile_bytes * (1 + 2 * a.kv_stages) + 2 * SLAB_BYTES + 1024 + 256;
     if (smem > 227 * 1024) return swh::fail(-1, "sw_flash_attn: shared memory budget exceeded (%d)", smem);
-    dim3 grid((p->seq_q + BQ - 1) / BQ, p->heads, p->batch);
+    dim3 grid((p->seq_q + BQ - 1) / BQ, p->heads, (p->batch + a.pack - 1) / a.pack);
     SW_CUDA_OK(swh::launch_pdl(k_flash_attn, grid, dim3(kThreads), size_t(smem), static_cast<cudaStream_t>(stream), 1,
                                tq, tk, tv, a));
     return 0;

@@ -330,7 +330,7 @@ def test_temporal_conv_3x1(nat, b, f, hw, c):
     assert _rel_err(out, ref) < 4e-3
 
 
-@pytest.mark.parametrize("f,hw,heads,d", [(8, 64, 4, 8), (24, 180, 5, 64), (16, 45, 20, 64)])
+@pytest.mark.parametrize("f,hw,heads,d", [(8, 64, 4, 8), (24, 180, 5, 64), (16, 45, 20, 64), (24, 2883, 5, 64), (5, 7, 2, 40)])
 def test_flash_attn_over_frames(nat, f, hw, heads, d):
     """Temporal attention: batch = pixel, sequence = frame, straight from the strides of a fused QKV buffer."""
     torch.manual_seed(8)
