@@ -54,7 +54,11 @@ cfgs = [  # (tile_n, cta_pair, splitk_min_kb (0 = no split-K), stages)
     (128, 1, 4, 0), (256, 1, 4, 0), (128, 1, 8, 0), (256, 1, 8, 0), (256, 2, 8, 0),
 ]
 flt = sys.argv[1] if len(sys.argv) > 1 else ""
-hdr = " ".join(f"{('auto' if t == 0 else str(t)) + ('p' if pr == 2 else '') + ('' if mk <= 0 else '/s' + str(mk)):>8s}" for t, pr, mk, _ in cfgs)
+if os.environ.get("GEGLU_SWEEP"):
+    shapes = [sh for sh in shapes if sh[3]]
+    cfgs = [(0, 0, -1, 0), (128, 1, 0, 2), (128, 1, 0, 3), (128, 1, 0, 4), (256, 1, 0, 2), (256, 1, 0, 3), (256, 2, 0, 2),
+            (256, 2, 0, 3), (128, 2, 0, 2), (128, 2, 0, 3)]
+hdr = " ".join(f"{('auto' if t == 0 else str(t)) + ('p' if pr == 2 else '') + ('' if mk <= 0 else '/s' + str(mk)) + ('' if not st else '@' + str(st)):>8s}" for t, pr, mk, st in cfgs)
 print(f"{'M,N,K':22s} {'GF':>6s} {'cublas':>7s} {hdr}")
 for (m, n, k, geglu) in shapes:
     if flt and flt not in f"{m},{n},{k}":
