@@ -56,6 +56,7 @@ class IGemmParams(C.Structure):
         ("cta_pair", C.c_int32),
         ("a_h_total", C.c_int32),
         ("a_y_off", C.c_int32),
+        ("persist", C.c_int32),
     ]
 
 
@@ -200,7 +201,7 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 # --------------------------------------------------------------------------------------- ops
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
           residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None,
-          a_h_total=0, a_y_off=0):
+          a_h_total=0, a_y_off=0, persist=0):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -216,10 +217,10 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
     if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
         raise ValueError("strided a1 is only supported for plain GEMMs")
-    if tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0:
+    if tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0 and persist == 0:
         tuned = tuning.lookup(n, h, w, kh, kw, c1, c2, cout, act, residual is not None)
         if tuned is not None:
-            tile_n, cta_pair, splitk_min_kb = tuned
+            tile_n, cta_pair, splitk_min_kb, persist = tuned
     p = IGemmParams()
     p.a1, p.a2 = _ptr(a1), _ptr(a2)
     p.c1, p.c2 = c1, c2
@@ -247,6 +248,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.stages = stages
     p.pad_w1 = 0 if pad_w is None else pad_w + 1
     p.a_h_total, p.a_y_off = a_h_total, a_y_off
+    p.persist = persist
     if splitk_scratch is not None:
         p.splitk_scratch = splitk_scratch.data_ptr()
         p.splitk_scratch_bytes = splitk_scratch.numel() * splitk_scratch.element_size()

@@ -46,6 +46,7 @@ struct IGemmArgs {
     int bf16;
     int bn;             // N tile (multiple of 32, <= 256)
     int tmem_cols;      // power of two >= bn
+    int ptiles, total_tiles;  // persistent kernel: pixel tiles, pixel tiles x column tiles
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
     int splits;         // split-K factor (grid.z)
     int kb_per_split;   // k-blocks per split
@@ -877,6 +878,477 @@ __global__ void __launch_bounds__(kThreads)
     igemm_body<true>(tmA1, tmA2, tmB, tmOut, tmRes, tmOut32, p);
 }
 
+// =================================================================================================
+// Persistent variant (mode 0, single-CTA tiles, no split-K): each CTA walks tiles
+// blockIdx.x, blockIdx.x + gridDim.x, ... with TWO accumulators in TMEM.  The kernel above pays its
+// prologue (barrier init, TMEM allocation, first TMA round trip) and its epilogue once per tile with
+// nothing to hide them behind except a second resident CTA; graph-timed sweeps put it 2-3x behind
+// cuBLAS on the short-K transformer GEMMs for exactly that reason.  Here the producer warp runs ahead
+// into the next tile's operands while the epilogue warps drain the previous accumulator, and the MMA
+// warp switches accumulators per tile:
+//   warp 0   TMA producer      ring of `stages` operand slots, continuous across tiles
+//   warp 1   MMA issuer        waits acc_empty[b], accumulates tile i into TMEM buffer b = i & 1,
+//                              commits acc_full[b]
+//   warps 2-5 epilogue         wait acc_full[b], drain, arrive acc_empty[b] as soon as the last
+//                              tcgen05.ld has landed, then finish the math / stores
+// Output goes through 64-column swizzled staging boxes + TMA stores (dedicated shared memory: the ring
+// is busy with the next tile), or straight from registers for GEGLU.
+__global__ void __launch_bounds__(kThreads)
+    k_igemm_p(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+              const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+              const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut32,
+              const IGemmArgs p) {
+    const int BN = p.bn;
+    const int B_STAGE_BYTES = BN * BK * 2;
+    const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    __shared__ __align__(16) float s_bias[2][256];
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int stages = p.stages;
+    const int ring_bytes = stages * STAGE_BYTES;
+    const int stage_area = p.tma_epi ? 65536 : 0;  // out[2] + res[2] boxes of 16 KB
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + ring_bytes + stage_area);
+    uint64_t* empty = full + stages;
+    uint64_t* acc_full = empty + stages;   // [2]
+    uint64_t* acc_empty = acc_full + 2;    // [2], 128 arrivals
+    uint64_t* res_full = acc_empty + 2;    // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmA2);
+        tma_prefetch_desc(&tmB);
+        if (p.tma_epi) {
+            tma_prefetch_desc(&tmOut);
+            tma_prefetch_desc(&tmRes);
+            tma_prefetch_desc(&tmOut32);
+        }
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < stages; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], 1);
+            }
+            for (int b = 0; b < 2; ++b) {
+                mbar_init(&acc_full[b], 1);
+                mbar_init(&acc_empty[b], 128);
+                mbar_init(&res_full[b], 1);
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc_any<false>(tmem_slot, uint32_t(2 * p.tmem_cols));
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();
+    pdl_wait();
+
+    const int nkb1 = (p.c1 + BK - 1) / BK;
+    const int nkb2 = (p.c2 + BK - 1) / BK;
+    const int per_tap = nkb1 + nkb2;
+    const int ctot = p.c1 + p.c2;
+    const int total_kb = p.kh * p.kw * per_tap;
+    const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
+    const uint32_t smem0 = smem_u32(smem);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    const int ptiles = p.ptiles;          // pixel tiles (fastest-varying: concurrent CTAs share a weight tile)
+    const int total_tiles = p.total_tiles;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---------------- TMA producer
+            const uint32_t tx_bytes = a_bytes + uint32_t(B_STAGE_BYTES);
+            uint32_t sa = smem0, fb = full0, eb = empty0;
+            int s = 0;
+            uint32_t ph = 1;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int nt = tile / ptiles;
+                int t = tile - nt * ptiles;
+                const int tx = t % p.tiles_x;
+                t /= p.tiles_x;
+                const int ty = t % p.tiles_y;
+                const int tn = t / p.tiles_y;
+                const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+                const int bcol0 = nt * BN;
+                int j = 0, ky = 0, kx = 0, tapbase = 0;
+                for (int it = 0; it < total_kb; ++it) {
+                    bar_wait(eb, ph);
+                    bar_expect_tx(fb, tx_bytes);
+                    int kcol;
+                    if (j < nkb1) {
+                        tma4<false>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                        kcol = tapbase + j * BK;
+                    } else {
+                        tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                        kcol = tapbase + p.c1 + (j - nkb1) * BK;
+                    }
+                    tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, kcol, bcol0);
+                    if (++j == per_tap) {
+                        j = 0;
+                        tapbase += ctot;
+                        if (++kx == p.kw) {
+                            kx = 0;
+                            ++ky;
+                        }
+                    }
+                    if (++s == stages) {
+                        s = 0;
+                        ph ^= 1;
+                        sa = smem0;
+                        fb = full0;
+                        eb = empty0;
+                    } else {
+                        sa += STAGE_BYTES;
+                        fb += 8;
+                        eb += 8;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---------------- MMA issuer
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((smem0 & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_off = uint32_t(A_STAGE_BYTES) >> 4;
+            const uint32_t stage_step = uint32_t(STAGE_BYTES) >> 4;
+            const int ks1 = (p.c1 - (nkb1 - 1) * BK + 15) / 16;
+            const int ks2 = nkb2 ? (p.c2 - (nkb2 - 1) * BK + 15) / 16 : 4;
+            const int last1 = nkb1 - 1, last2 = per_tap - 1;
+            uint32_t a_lo = a_lo0, fb = full0, eb = empty0;
+            int s = 0;
+            uint32_t ph = 0;
+            const uint32_t idesc = p.idesc;
+            const uint32_t accf0 = smem_u32(acc_full), acce0 = smem_u32(acc_empty);
+            int i = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++i) {
+                const uint32_t ab = uint32_t(i) & 1u;
+                const uint32_t tacc = tmem_base + ab * uint32_t(p.tmem_cols);
+                bar_wait(acce0 + 8 * ab, ((uint32_t(i) >> 1) & 1u) ^ 1u);  // epilogue has drained this buffer
+                tc_fence_after();
+                int j = 0;
+                uint32_t acc = 0;
+                for (int it = 0; it < total_kb; ++it) {
+                    bar_wait(fb, ph);
+                    tc_fence_after();
+                    int ksteps = 4;
+                    if (j == last1) ksteps = ks1 < 4 ? ks1 : 4;
+                    if (nkb2 && j == last2) ksteps = ks2 < 4 ? ks2 : 4;
+                    mma_f16<false>(tacc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
+                    if (ksteps > 1) mma_f16<false>(tacc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
+                    if (ksteps > 2) mma_f16<false>(tacc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
+                    if (ksteps > 3) mma_f16<false>(tacc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                    acc = 1u;
+                    mma_commit<false>(eb);
+                    if (++j == per_tap) j = 0;
+                    if (++s == stages) {
+                        s = 0;
+                        ph ^= 1;
+                        a_lo = a_lo0;
+                        fb = full0;
+                        eb = empty0;
+                    } else {
+                        a_lo += stage_step;
+                        fb += 8;
+                        eb += 8;
+                    }
+                }
+                mma_commit<false>(accf0 + 8 * ab);
+            }
+        }
+    } else {
+        // ---------------- epilogue: one thread per accumulator row
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const int xl = r % p.bw;
+        const int r2 = r / p.bw;
+        const int yl = r2 % p.bh;
+        const int nl = r2 / p.bh;
+        const uint32_t lane_off = uint32_t(q * 32) << 16;
+        const bool lead = threadIdx.x == 64;
+        const bool geglu = p.act == SW_ACT_GEGLU;
+        const bool has_res = p.residual != nullptr;
+        const uint32_t out_stage = smem0 + uint32_t(ring_bytes);
+        const uint32_t res_stage = out_stage + 32768u;
+        const uint32_t rfull0 = smem_u32(res_full);
+        const uint32_t accf0 = smem_u32(acc_full);
+        const uint32_t row_off = uint32_t(r) * 128u, swz = uint32_t(r) & 7u;
+        uint32_t rph[2] = {0u, 0u};  // parity of the next completion of each residual box
+        int osl = 0;                 // output slabs staged so far (box = osl & 1), across tiles
+        int i = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++i) {
+            const int nt = tile / ptiles;
+            int t = tile - nt * ptiles;
+            const int tx = t % p.tiles_x;
+            t /= p.tiles_x;
+            const int ty = t % p.tiles_y;
+            const int tn = t / p.tiles_y;
+            const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+            const int col0 = nt * BN;
+            const int x = x0 + xl, y = y0 + yl, ni = n0 + nl;
+            const bool row_ok = (nl < p.bi) && x < p.w && y < p.h && ni < p.n;
+            const size_t m = (size_t(ni) * p.h + y) * p.w + x;
+            const uint32_t ab = uint32_t(i) & 1u;
+            float* sb = s_bias[ab];
+            const bool fold_rb = p.row_bias != nullptr && p.bi == 1;
+            for (int k = threadIdx.x - 64; k < BN; k += 128) {
+                const int col = col0 + k;
+                float b = 0.0f;
+                if (col < p.cout) {
+                    if (p.bias) b = __half2float(p.bias[col]);
+                    if (fold_rb && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
+                }
+                sb[k] = b;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const uint32_t trow = tmem_base + ab * uint32_t(p.tmem_cols) + lane_off;
+            const uint32_t acce = smem_u32(&acc_empty[ab]);
+
+            if (geglu) {
+                // values in accumulator columns [0, BN/2), gates in [BN/2, BN); direct 16-byte stores
+                const int HALF = BN / 2;
+                const int ocol0 = nt * HALF;
+                const int ncols_out = p.cout / 2;
+                if (lane == 0) bar_wait(accf0 + 8 * ab, (uint32_t(i) >> 1) & 1u);
+                __syncwarp();
+                tc_fence_after();
+                uint32_t vn[16], gn[16];
+                tmem_ld16(trow, vn);
+                tmem_ld16(trow + HALF, gn);
+#pragma unroll 1
+                for (int c = 0; c < HALF; c += 16) {
+                    uint32_t v[16], g[16];
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = vn[j], g[j] = gn[j];
+                    if (c + 16 < HALF) {
+                        tmem_ld16(trow + c + 16, vn);
+                        tmem_ld16(trow + HALF + c + 16, gn);
+                    } else {  // the accumulator is in registers: hand it back to the MMA warp
+                        tc_fence_before();
+                        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acce) : "memory");
+                    }
+                    if (row_ok && ocol0 + c < ncols_out) {
+                        uint32_t o[8];
+#pragma unroll
+                        for (int j = 0; j < 16; j += 2) {
+                            const float a0 = __uint_as_float(v[j]) + sb[c + j];
+                            const float a1 = __uint_as_float(v[j + 1]) + sb[c + j + 1];
+                            const float g0 = __uint_as_float(g[j]) + sb[HALF + c + j];
+                            const float g1 = __uint_as_float(g[j + 1]) + sb[HALF + c + j + 1];
+                            o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
+                        }
+                        uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
+                        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                    }
+                }
+                continue;
+            }
+
+            if (!p.tma_epi) {
+                // ---- register -> global epilogue (two persistent CTAs per SM, no staging boxes): TMEM
+                // chunk c+32 and its residual are in flight while chunk c is converted and stored
+                int nv = p.cout - col0;
+                if (nv > BN) nv = BN;
+                const int ce = (nv + 31) & ~31;
+                const bool pl = p.act == SW_ACT_NONE && p.out_scale == 1.0f && (!p.row_bias || fold_rb);
+                __half* const out_row = p.out + m * p.ldc + col0;
+                const __half* const res_row = has_res ? p.residual + m * p.ldr + col0 : nullptr;
+                auto fetch = [&](int c, uint4 (&rs)[4]) {
+                    if (!has_res || !row_ok) return;
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8)
+                        if (col0 + c + g8 * 8 < p.cout) rs[g8] = *reinterpret_cast<const uint4*>(res_row + c + g8 * 8);
+                };
+                if (lane == 0) bar_wait(accf0 + 8 * ab, (uint32_t(i) >> 1) & 1u);
+                __syncwarp();
+                tc_fence_after();
+                uint32_t vn[32];
+                uint4 rn[4];
+                tmem_ld32(trow, vn);
+                fetch(0, rn);
+#pragma unroll 1
+                for (int c = 0; c < ce; c += 32) {
+                    uint32_t v[32];
+                    uint4 rs[4];
+                    tmem_ld_wait_dep(vn);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = vn[j];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) rs[j] = rn[j];
+                    if (c + 32 < ce) {
+                        tmem_ld32(trow + c + 32, vn);
+                        fetch(c + 32, rn);
+                    } else {
+                        tc_fence_before();
+                        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acce) : "memory");
+                    }
+                    if (!row_ok) continue;
+#pragma unroll
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        const int c8 = c + g8 * 8;
+                        if (col0 + c8 >= p.cout) break;
+                        const float4 b0 = *reinterpret_cast<const float4*>(&sb[c8]);
+                        const float4 b1 = *reinterpret_cast<const float4*>(&sb[c8 + 4]);
+                        float f[8] = {__uint_as_float(v[g8 * 8 + 0]) + b0.x, __uint_as_float(v[g8 * 8 + 1]) + b0.y,
+                                      __uint_as_float(v[g8 * 8 + 2]) + b0.z, __uint_as_float(v[g8 * 8 + 3]) + b0.w,
+                                      __uint_as_float(v[g8 * 8 + 4]) + b1.x, __uint_as_float(v[g8 * 8 + 5]) + b1.y,
+                                      __uint_as_float(v[g8 * 8 + 6]) + b1.z, __uint_as_float(v[g8 * 8 + 7]) + b1.w};
+                        if (!pl) {
+                            if (p.row_bias && !fold_rb) {
+                                const uint4 b = *reinterpret_cast<const uint4*>(p.row_bias + size_t(ni) * p.row_bias_ld +
+                                                                                col0 + c8);
+                                const float2 t0 = unpack_h2(b.x), t1 = unpack_h2(b.y), t2 = unpack_h2(b.z),
+                                             t3 = unpack_h2(b.w);
+                                f[0] += t0.x, f[1] += t0.y, f[2] += t1.x, f[3] += t1.y;
+                                f[4] += t2.x, f[5] += t2.y, f[6] += t3.x, f[7] += t3.y;
+                            }
+                            if (p.act == SW_ACT_SILU) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
+                            } else if (p.act == SW_ACT_GELU) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                            }
+                            if (p.out_scale != 1.0f) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
+                            }
+                        }
+                        if (has_res) {
+                            const float2 r0 = unpack_h2(rs[g8].x), r1 = unpack_h2(rs[g8].y), r2 = unpack_h2(rs[g8].z),
+                                         r3 = unpack_h2(rs[g8].w);
+                            f[0] += r0.x, f[1] += r0.y, f[2] += r1.x, f[3] += r1.y;
+                            f[4] += r2.x, f[5] += r2.y, f[6] += r3.x, f[7] += r3.y;
+                        }
+                        *reinterpret_cast<uint4*>(out_row + c8) =
+                            make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]), pack_h2(f[6], f[7]));
+                    }
+                }
+                continue;
+            }
+
+            // ---- 64-column slabs staged in swizzled shared memory, written by TMA stores
+            int nvalid = p.cout - col0;
+            if (nvalid > BN) nvalid = BN;
+            const int cend = (nvalid + 31) & ~31;
+            const int nslab = (nvalid + 63) >> 6;
+            const bool tail32 = (cend & 63) == 32;
+            const bool plain = p.act == SW_ACT_NONE && p.out_scale == 1.0f && (!p.row_bias || fold_rb);
+            if (has_res && lead) {
+                for (int sl = 0; sl < 2 && sl < nslab; ++sl) {
+                    bar_expect_tx(rfull0 + 8 * sl, a_bytes);
+                    tma4<false>(res_stage + sl * 16384, &tmRes, rfull0 + 8 * sl, col0 + sl * 64, x0, y0, n0);
+                }
+            }
+            if (lane == 0) bar_wait(accf0 + 8 * ab, (uint32_t(i) >> 1) & 1u);
+            __syncwarp();
+            tc_fence_after();
+            uint32_t vn[32];
+            tmem_ld32(trow, vn);
+#pragma unroll 1
+            for (int c = 0; c < cend; c += 32) {
+                const int sl = c >> 6;
+                const uint32_t obox = out_stage + uint32_t(osl & 1) * 16384u;
+                const uint32_t rbox = res_stage + uint32_t(sl & 1) * 16384u;
+                if ((c & 63) == 0) {
+                    if (osl >= 2) {  // the store issued two slabs ago must have finished reading this box
+                        if (lead) bulk_wait_read<1>();
+                        asm volatile("bar.sync 1, 128;" ::: "memory");
+                    }
+                    if (has_res) {
+                        bar_wait(rfull0 + 8 * (sl & 1), rph[sl & 1]);
+                        rph[sl & 1] ^= 1u;
+                    }
+                }
+                uint32_t v[32];
+                tmem_ld_wait_dep(vn);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = vn[j];
+                if (c + 32 < cend) {
+                    tmem_ld32(trow + c + 32, vn);
+                } else {  // whole accumulator read: the MMA warp may start the tile after next in it
+                    tc_fence_before();
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acce) : "memory");
+                }
+                const bool tail_slab = tail32 && sl == nslab - 1;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const int c8 = c + g8 * 8;
+                    const float4 b0 = *reinterpret_cast<const float4*>(&sb[c8]);
+                    const float4 b1 = *reinterpret_cast<const float4*>(&sb[c8 + 4]);
+                    float f[8] = {__uint_as_float(v[g8 * 8 + 0]) + b0.x, __uint_as_float(v[g8 * 8 + 1]) + b0.y,
+                                  __uint_as_float(v[g8 * 8 + 2]) + b0.z, __uint_as_float(v[g8 * 8 + 3]) + b0.w,
+                                  __uint_as_float(v[g8 * 8 + 4]) + b1.x, __uint_as_float(v[g8 * 8 + 5]) + b1.y,
+                                  __uint_as_float(v[g8 * 8 + 6]) + b1.z, __uint_as_float(v[g8 * 8 + 7]) + b1.w};
+                    if (!plain) {
+                        if (p.row_bias && !fold_rb && row_ok) {
+                            const uint4 b =
+                                *reinterpret_cast<const uint4*>(p.row_bias + size_t(ni) * p.row_bias_ld + col0 + c8);
+                            const float2 t0 = unpack_h2(b.x), t1 = unpack_h2(b.y), t2 = unpack_h2(b.z), t3 = unpack_h2(b.w);
+                            f[0] += t0.x, f[1] += t0.y, f[2] += t1.x, f[3] += t1.y;
+                            f[4] += t2.x, f[5] += t2.y, f[6] += t3.x, f[7] += t3.y;
+                        }
+                        if (p.act == SW_ACT_SILU) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[j] = silu_f(f[j]);
+                        } else if (p.act == SW_ACT_GELU) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                        }
+                        if (p.out_scale != 1.0f) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) f[j] *= p.out_scale;
+                        }
+                    }
+                    const uint32_t off = row_off + (((uint32_t(c8 >> 3) & 7u) ^ swz) << 4);
+                    if (has_res) {
+                        const uint4 rv = lds128(rbox + off);
+                        const float2 r0 = unpack_h2(rv.x), r1 = unpack_h2(rv.y), r2 = unpack_h2(rv.z),
+                                     r3 = unpack_h2(rv.w);
+                        f[0] += r0.x, f[1] += r0.y, f[2] += r1.x, f[3] += r1.y;
+                        f[4] += r2.x, f[5] += r2.y, f[6] += r3.x, f[7] += r3.y;
+                    }
+                    const uint32_t dst = tail_slab ? obox + uint32_t(r) * 64u + ((uint32_t(c8 >> 3) & 3u) << 4) : obox + off;
+                    sts128(dst, make_uint4(pack_h2(f[0], f[1]), pack_h2(f[2], f[3]), pack_h2(f[4], f[5]),
+                                           pack_h2(f[6], f[7])));
+                }
+                if ((c & 63) == 32 || c + 32 >= cend) {
+                    fence_proxy_async_smem();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (lead) {
+                        tma_store_4d(tail_slab ? &tmOut32 : &tmOut, obox, col0 + sl * 64, x0, y0, n0);
+                        bulk_commit();
+                        if (has_res && sl + 2 < nslab) {
+                            bar_expect_tx(rfull0 + 8 * (sl & 1), a_bytes);
+                            tma4<false>(rbox, &tmRes, rfull0 + 8 * (sl & 1), col0 + (sl + 2) * 64, x0, y0, n0);
+                        }
+                    }
+                    ++osl;
+                }
+            }
+        }
+        if (lead) bulk_wait_read<0>();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_any<false>(tmem_base, uint32_t(2 * p.tmem_cols));
+    }
+}
+
 // Choose the pixel box (bw x bh x bi, <= 128 pixels) that wastes the fewest MMA rows.
 void pick_box(int n, int h, int w, int* bw, int* bh, int* bi) {
     double best = -1.0;
@@ -1180,6 +1652,47 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         }
     } else {
         tOut = tRes = tOut32 = tB;
+    }
+    // ---- persistent kernel (see k_igemm_p): worth it once a CTA would get more than one tile
+    if (mode == 0 && !pair && a.splits == 1) {
+        static int env_persist = -1;  // SW_IGEMM_PERSIST: 0 never, 1 auto (default), 2 whenever possible
+        if (env_persist < 0) {
+            const char* e = getenv("SW_IGEMM_PERSIST");
+            env_persist = e ? atoi(e) : 1;
+        }
+        const long total = long(grid_x) * tiles_ncol;
+        int want = p->persist ? p->persist : (env_persist == 0 ? 1 : env_persist == 2 ? 2 : 0);
+        // measured: the GELU-gated epilogue is the one heavy enough to win from the overlap by default
+        // (25-30 %); other shapes are within +-10 % either way and are left to the tuning table
+        bool persist = want == 2 || (want == 0 && p->act == SW_ACT_GEGLU && total > 2L * sms);
+        if (persist && total < (1L << 30)) {
+            // tiles up to 128 columns wide: register -> global epilogue, which leaves room for two CTAs
+            // (= eight epilogue warps, two MMA issuers) per SM; wider tiles stage through TMA stores
+            if (bn <= 128) a.tma_epi = 0;
+            const int stage_area = a.tma_epi ? 65536 : 0;
+            // GEGLU (no staging boxes, epilogue-heavy): two persistent CTAs per SM = eight epilogue warps
+            const int occ = (!a.tma_epi && 2 * a.tmem_cols * 2 <= 512 && 2 * (3 * stage_bytes + 4096) <= 227 * 1024) ? 2 : 1;
+            int st = ((occ == 2 ? 112 : 225) * 1024 - 1280 - stage_area) / stage_bytes;
+            if (st > 8) st = 8;
+            if (st > kblocks * 2) st = kblocks * 2;
+            if (st >= 2) {
+                a.stages = st;
+                a.ptiles = grid_x;
+                a.total_tiles = int(total);
+                const int smem = st * stage_bytes + stage_area + 1024 + 256;
+                static bool configured[64] = {false};
+                int dev = 0;
+                SW_CUDA_OK(cudaGetDevice(&dev));
+                if (dev < 64 && !configured[dev]) {
+                    SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_p, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+                    configured[dev] = true;
+                }
+                const int grid = total < long(occ) * sms ? int(total) : occ * sms;
+                SW_CUDA_OK(swh::launch_pdl(k_igemm_p, dim3(grid), dim3(kThreads), size_t(smem),
+                                           static_cast<cudaStream_t>(stream), 1, tA1, tA2, tB, tOut, tRes, tOut32, a));
+                return 0;
+            }
+        }
     }
     if (mode == 1) {
         const int smem = smem_bytes(a, pair);

@@ -91,6 +91,7 @@ typedef struct {
      * full image.  0 = a1 has exactly h rows. */
     int32_t a_h_total;
     int32_t a_y_off;
+    int32_t persist;     /* 0 = auto, 1 = one tile per CTA, 2 = persistent CTAs with double-buffered accumulators when possible */
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);
