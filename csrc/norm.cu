@@ -290,7 +290,7 @@ __global__ void k_gn_apply(const __half* __restrict__ x1, const __half* __restri
 __global__ void __launch_bounds__(1024)
     k_gn_fused(const __half* __restrict__ x1, const __half* __restrict__ x2, int c1, __half* __restrict__ y,
                const __half* __restrict__ gamma, const __half* __restrict__ beta, int hw, int c, int groups, float eps,
-               int silu, int rows_per_cta, int rows_per_pass) {
+               int silu, int rows_per_cta, int rows_per_pass, int c_total) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     pdl_trigger();
@@ -310,15 +310,18 @@ __global__ void __launch_bounds__(1024)
     float* sh = reinterpret_cast<float*>(slab + size_t(rows_per_cta) * octs);  // [rows_per_pass][c][2]
     float* chs = sh + size_t(rows_per_pass) * c * 2;                            // [c][2]
 
+    // blockIdx.z selects a slice of whole groups (`c` channels, `groups` groups of the c_total-wide tensor):
+    // groups are independent, so slices only multiply the number of SMs pulling the tensor in
+    const int ch0 = int(blockIdx.z) * c + oct * 8;  // first of this thread's 8 channels, in the full tensor
     const bool active = rp < rows_per_pass;
-    const bool first = oct * 8 < c1;
-    const int cs = first ? c1 : c - c1;
-    const __half* src = (first ? x1 + oct * 8 : x2 + (oct * 8 - c1)) + (size_t(n) * hw) * cs;
+    const bool first = ch0 < c1;
+    const int cs = first ? c1 : c_total - c1;
+    const __half* src = (first ? x1 + ch0 : x2 + (ch0 - c1)) + (size_t(n) * hw) * cs;
     // affine parameters of this thread's 8 channels: in flight while the rows stream in
     uint4 gv = make_uint4(0x3C003C00u, 0x3C003C00u, 0x3C003C00u, 0x3C003C00u), bv = make_uint4(0, 0, 0, 0);
     if (active) {
-        if (gamma) gv = *reinterpret_cast<const uint4*>(gamma + oct * 8);
-        if (beta) bv = *reinterpret_cast<const uint4*>(beta + oct * 8);
+        if (gamma) gv = *reinterpret_cast<const uint4*>(gamma + ch0);
+        if (beta) bv = *reinterpret_cast<const uint4*>(beta + ch0);
     }
     if (active) {
         float s[8], ss[8];
@@ -411,7 +414,7 @@ __global__ void __launch_bounds__(1024)
             b[2 * j + 1] = bf.y - s_mean[g1] * a[2 * j + 1];
         }
     }
-    __half* out = y + (size_t(n) * hw) * c + oct * 8;
+    __half* out = y + (size_t(n) * hw) * c_total + ch0;
     for (int r = r0 + rp; r < r1; r += rows_per_pass) {
         const uint4 v = slab[size_t(r - r0) * octs + oct];
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -427,7 +430,7 @@ __global__ void __launch_bounds__(1024)
             }
             o[j] = pack_h2(u0, u1);
         }
-        *reinterpret_cast<uint4*>(out + size_t(r) * c) = make_uint4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<uint4*>(out + size_t(r) * c_total) = make_uint4(o[0], o[1], o[2], o[3]);
     }
 }
 
@@ -578,7 +581,7 @@ static GnGeom gn_geom(int hw, int c) {
 
 // Geometry of the fused single-launch path; cluster == 0 when the tensor does not qualify.
 struct GnFusedGeom {
-    int rows_per_pass, threads, rows_per_cta, cluster, chunks;
+    int rows_per_pass, threads, rows_per_cta, cluster, chunks, slices;
     size_t smem;
 };
 static GnFusedGeom gn_fused_geom(int n, int hw, int c, int groups) {
@@ -589,24 +592,34 @@ static GnFusedGeom gn_fused_geom(int n, int hw, int c, int groups) {
         const char* e = getenv("SW_GN_FUSED");
         enabled = e ? atoi(e) : 1;
     }
-    const int octs = c / 8;
-    if (!enabled || groups > 64 || octs > 1024 || n > 65535) return g;
-    g.rows_per_pass = 512 / octs;
-    if (g.rows_per_pass < 1) g.rows_per_pass = 1;
-    g.threads = (octs * g.rows_per_pass + 31) / 32 * 32;
-    // largest cluster (<= 16 CTAs) that still gives every CTA a full pass of rows; more CTAs per image
-    // = more SMs pulling the tensor in (one SM ingests ~40 B/clk)
-    for (int cl = 16; cl >= 1; cl >>= 1) {
-        int rpc = (hw + cl - 1) / cl;
-        rpc = (rpc + g.rows_per_pass - 1) / g.rows_per_pass * g.rows_per_pass;
-        if (cl > 1 && rpc * (cl - 1) >= hw) continue;  // trailing CTAs would own no rows
-        const size_t smem = size_t(rpc) * c * 2 + (size_t(g.rows_per_pass) * c * 2 + size_t(c) * 2) * sizeof(float);
-        if (smem > 216 * 1024) break;  // smaller clusters only need more
-        g.rows_per_cta = rpc;
-        g.cluster = cl;
-        g.chunks = cl;
-        g.smem = smem;
-        break;
+    if (!enabled || groups > 64 || c / 8 > 1024 || n > 65535) return g;
+    const int sms = swh::sm_count();
+    const int cgw = c / groups;
+    // try the finest channel slicing first: slices of whole groups whose width is a multiple of 8
+    for (int sl = 8; sl >= 1; sl >>= 1) {
+        if (groups % sl || ((groups / sl) * cgw) % 8) continue;
+        const int cs = c / sl, octs = cs / 8;
+        int rpp = 512 / octs;
+        if (rpp < 1) rpp = 1;
+        if (rpp > hw) rpp = hw;
+        // largest cluster (<= 16 CTAs) that still gives every CTA a full pass of rows; more CTAs per image
+        // = more SMs pulling the tensor in (one SM ingests ~40 B/clk)
+        for (int cl = 16; cl >= 1; cl >>= 1) {
+            int rpc = (hw + cl - 1) / cl;
+            rpc = (rpc + rpp - 1) / rpp * rpp;
+            if (cl > 1 && rpc * (cl - 1) >= hw) continue;  // trailing CTAs would own no rows
+            const size_t smem = size_t(rpc) * cs * 2 + (size_t(rpp) * cs * 2 + size_t(cs) * 2) * sizeof(float);
+            if (smem > 216 * 1024) break;  // smaller clusters only need more
+            if (sl > 1 && long(n) * cl * sl > 2L * sms) break;  // enough CTAs already: use coarser slices
+            g.rows_per_pass = rpp;
+            g.threads = (octs * rpp + 31) / 32 * 32;
+            g.rows_per_cta = rpc;
+            g.cluster = cl;
+            g.chunks = cl;
+            g.slices = sl;
+            g.smem = smem;
+            return g;
+        }
     }
     return g;
 }
@@ -666,11 +679,11 @@ static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, 
                 configured[dev] = true;
             }
             (void)scratch_zeroed;
-            SW_CUDA_OK(swh::launch_pdl(k_gn_fused, dim3(f.cluster, n), dim3(f.threads), f.smem, st, f.cluster,
+            SW_CUDA_OK(swh::launch_pdl(k_gn_fused, dim3(f.cluster, n, f.slices), dim3(f.threads), f.smem, st, f.cluster,
                                        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1,
                                        static_cast<__half*>(y), static_cast<const __half*>(gamma),
-                                       static_cast<const __half*>(beta), hw, c, groups, eps, silu, f.rows_per_cta,
-                                       f.rows_per_pass));
+                                       static_cast<const __half*>(beta), hw, c / f.slices, groups / f.slices, eps, silu,
+                                       f.rows_per_cta, f.rows_per_pass, c));
             return 0;
         }
     }
