@@ -17,6 +17,8 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--out", default="gpurun_out/igemm_tuning.json")
 ap.add_argument("--quick", action="store_true")
 ap.add_argument("--only", default="", help="comma-separated plan names to (re)tune")
+ap.add_argument("--strips", default="", help="also tune the 1/P-row strips of the single-image plans (patch-parallel "
+                "ranks run exactly these shapes), e.g. 2,4")
 ap.add_argument("--merge", default="", help="existing table to extend (its entries are kept unless re-measured)")
 args = ap.parse_args()
 
@@ -124,12 +126,47 @@ configs, report = {}, []
 kept = {}
 if args.merge and os.path.isfile(args.merge):
     kept = {k: tuple(v) for k, v in json.load(open(args.merge)).get("configs", {}).items()}
+def strip_of(a, kw, P):
+    """The same op on the first 1/P of the rows (what a patch-parallel rank with P strips computes)."""
+    if kw["n"] != 1:
+        return None
+    a1, wgt, out = a[0], a[1], a[2]
+    if kw["h"] > 1:
+        if kw["h"] % P:
+            return None
+        h, w = kw["h"] // P, kw["w"]
+        rows = h * w
+        k2 = dict(kw, h=h)
+        a1s = a1.reshape(kw["h"], w, -1)[:h].reshape(1, h, w, -1)
+        if kw.get("a2") is not None:
+            k2["a2"] = kw["a2"].reshape(kw["h"], w, -1)[:h].reshape(1, h, w, -1)
+    else:
+        if kw["w"] % P or (kw["w"] // P) < 8:
+            return None
+        rows = kw["w"] // P
+        k2 = dict(kw, w=rows)
+        a1s = a1.reshape(kw["w"], -1)[:rows]
+    if kw.get("residual") is not None:
+        k2["residual"] = kw["residual"].reshape(-1, kw["residual"].shape[-1])[:rows]
+    return (a1s, wgt, out.reshape(-1, out.shape[-1])[:rows]) + tuple(a[3:]), k2
+
+
+strips = [int(x) for x in args.strips.split(",") if x]
 for name, (recs, keep) in plans():
     seen = 0
+    ops = []
     for rec in recs:
         for fn, a, kw in rec.ops:
             if getattr(fn, "__name__", "") != "igemm" or kw.get("tile_n"):
                 continue
+            ops.append((fn, a, kw))
+            if "nocfg" in name:
+                for P in strips:
+                    so = strip_of(a, kw, P)
+                    if so is not None:
+                        ops.append((fn, so[0], so[1]))
+    for rec in [None]:
+        for fn, a, kw in ops:
             a1, wgt = a[0], a[1]
             c1 = a1.shape[-1]
             c2 = 0 if kw.get("a2") is None else kw["a2"].shape[-1]
