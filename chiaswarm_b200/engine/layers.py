@@ -15,10 +15,13 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import List, Optional
 
+import os
+
 import torch
 
 from ..ops import native as nat
-from ..ops.packing import interleave_geglu, pack_conv_weight, pad_vector
+from ..ops import tuning
+from ..ops.packing import fold_layernorm, interleave_geglu, pack_conv_weight, pad_vector
 
 
 def _r8(c: int) -> int:
@@ -172,13 +175,38 @@ class Conv:
         return o
 
 
+STATS_TILE = 128  # column tile of GEMMs that emit row statistics (fixes the number of partial slots)
+
+
+def fuse_layernorm() -> bool:
+    """SW_LN_FUSE=1 folds the transformer LayerNorms into the GEMMs around them (48 fewer launches per SD1.5
+    step, 210 per SDXL step).  Measured a wash (SD1.5 3.67 vs 3.68 img/s, SDXL 723 vs 717 ms, 4-GPU patch
+    14.9 vs 14.7 ms/step): the GEMMs that carry the statistics give up CTA pairs / split-K and each pays 1-2 us
+    for the extra loads, which is what the 4.5 us LayerNorm kernels cost.  Off by default; kept, tested."""
+    return os.environ.get("SW_LN_FUSE", "0") not in ("0", "")
+
+
+class RowStats:
+    """Per-row (sum, sum of squares) partials a producer GEMM left for the GEMM that consumes LayerNorm(y)."""
+
+    def __init__(self, buf: torch.Tensor, tiles: int, width: int):
+        self.buf, self.tiles, self.width = buf, tiles, width
+
+
 class Linear:
-    def __init__(self, weight, bias=None, geglu=False):
+    def __init__(self, weight, bias=None, geglu=False, ln: Optional[torch.nn.LayerNorm] = None):
+        """`ln`: fold this LayerNorm (applied to the input) into the weights; calls then need `stats`."""
         w = weight.detach().to(torch.float16)
         if w.dim() == 4:
             w = w[:, :, 0, 0]
         b = None if bias is None else bias.detach().to(torch.float16)
+        self.col_sums = None
+        self.ln_eps = 0.0
+        if ln is not None:
+            w, b, cs = fold_layernorm(w, b, ln.weight, ln.bias)
+            self.col_sums, self.ln_eps = cs, float(ln.eps)
         if w.shape[0] % 8 or w.shape[1] % 8:  # tiny projections (e.g. VAE post_quant 4->4): zero-pad
+            assert ln is None
             wp = torch.zeros(_r8(w.shape[0]), _r8(w.shape[1]), dtype=w.dtype, device=w.device)
             wp[: w.shape[0], : w.shape[1]] = w
             w, b = wp, pad_vector(b, wp.shape[0])
@@ -189,19 +217,59 @@ class Linear:
             # other's main loop; 256-wide tiles (half = 128) measured 30-40 % slower on the UNet shapes
             half = 64
             self.tile_n = 2 * half
+            if self.col_sums is not None:  # the column sums ride through the same row interleave
+                _, cs16 = interleave_geglu(w, self.col_sums, half)
+                self.col_sums = cs16.float().contiguous() if cs16.dtype != torch.float32 else cs16
             w, b = interleave_geglu(w, b, half)
         self.nout = w.shape[0] // 2 if geglu else w.shape[0]
         self.wgt = w.contiguous()
         self.bias = None if b is None else b.contiguous()
 
-    def __call__(self, rec: Recorder, x: torch.Tensor, residual=None, act=nat.ACT_NONE, out=None, out_scale=1.0):
-        """x: [rows, K] -> [rows, nout]."""
+    def _ln_kw(self, stats: Optional[RowStats], lo=None, hi=None):
+        if self.col_sums is None:
+            assert stats is None
+            return {}
+        assert stats is not None, "this projection has a LayerNorm folded in: it needs the producer's row statistics"
+        cs = self.col_sums if lo is None else self.col_sums[lo:hi]
+        return dict(row_stats_in=stats.buf, stats_tiles=stats.tiles, ln_width=stats.width, ln_eps=self.ln_eps, col_sums=cs)
+
+    def __call__(self, rec: Recorder, x: torch.Tensor, residual=None, act=nat.ACT_NONE, out=None, out_scale=1.0,
+                 stats: Optional[RowStats] = None, emit_stats: bool = False):
+        """x: [rows, K] -> [rows, nout].  `stats`: row statistics of x (folded LayerNorm).  `emit_stats`: also
+        return RowStats of the output for a downstream folded LayerNorm -> (out, RowStats)."""
         rows = x.shape[0]
         o = out if out is not None else rec.buf(rows, self.nout)
+        kw = self._ln_kw(stats)
+        tile_n = self.tile_n
+        st = None
+        act_code = nat.ACT_GEGLU if self.geglu else act
+        if emit_stats or stats is not None:
+            # GEMMs with LayerNorm plumbing bypass the binding's table lookup (pairs and split-K do not carry it):
+            # take the measured tile width / persistence of the same shape when it is a single-CTA configuration
+            cfg = tuning.lookup(1, 1, rows, 1, 1, x.shape[-1], 0, self.wgt.shape[0], act_code, residual is not None)
+            if cfg is not None and cfg[1] != 2 and cfg[0] in (64, 128, 256) and not self.geglu:
+                tile_n = cfg[0]
+            if cfg is not None and stats is not None and not emit_stats:
+                kw["persist"] = cfg[3]
+        if emit_stats:
+            assert not self.geglu
+            tile = tile_n if tile_n in (64, 128, 256) else STATS_TILE
+            tiles = (self.nout + tile - 1) // tile
+            st = RowStats(rec.buf(tiles, rows, 2, dtype=torch.float32), tiles, self.nout)
+            kw["row_stats_out"] = st.buf
+            tile_n = tile
         rec.add(nat.igemm, x, self.wgt, o, n=1, h=1, w=rows, bias=self.bias, residual=residual,
-                act=nat.ACT_GEGLU if self.geglu else act, out_scale=out_scale, splitk_scratch=rec.splitk,
-                tile_n=self.tile_n)
-        return o
+                act=act_code, out_scale=out_scale, splitk_scratch=rec.splitk,
+                tile_n=tile_n, **kw)
+        return (o, st) if emit_stats else o
+
+    def call_rows(self, rec: Recorder, x: torch.Tensor, lo: int, hi: int, out: torch.Tensor,
+                  stats: Optional[RowStats] = None):
+        """Only output columns [lo, hi) (a row block of the weight), e.g. Q or K/V of a fused QKV projection."""
+        rec.add(nat.igemm, x, self.wgt[lo:hi], out, n=1, h=1, w=x.shape[0],
+                bias=None if self.bias is None else self.bias[lo:hi], splitk_scratch=rec.splitk,
+                **self._ln_kw(stats, lo, hi))
+        return out
 
 
 class GroupNorm:
@@ -287,50 +355,58 @@ class CrossKV:
 
 
 class TransformerBlock:
+    """Self-attention, cross-attention, GEGLU feed-forward on the residual stream y [n*s, c].
+
+    With `fuse_layernorm()` the three LayerNorms never run as kernels: each is folded into the projection that
+    consumes it (ops/packing.fold_layernorm), and the GEMM that produces the residual stream (proj_in, the
+    attention output projections, ff2) emits the row statistics in its epilogue."""
+
     def __init__(self, m):
         self.heads, self.dh = m.attn1.heads, m.attn1.dim_head
         c = self.heads * self.dh
         self.c = c
-        self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
         a1, a2 = m.attn1, m.attn2
         self.self_is_cross = m.only_cross_attention
+        self.fused = fuse_layernorm() and not self.self_is_cross
+        f = self.fused
+        if not f:
+            self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
         if not self.self_is_cross:
-            self.qkv = Linear(torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], 0))
+            self.qkv = Linear(torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], 0), ln=m.norm1 if f else None)
         else:
             self.q1 = Linear(a1.to_q.weight)
             self.kv1 = CrossKV(a1)
         self.o1 = Linear(a1.to_out[0].weight, a1.to_out[0].bias)
-        self.q2 = Linear(a2.to_q.weight)
+        self.q2 = Linear(a2.to_q.weight, ln=m.norm2 if f else None)
         self.kv2 = CrossKV(a2)
         self.o2 = Linear(a2.to_out[0].weight, a2.to_out[0].bias)
-        self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True)
+        self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True, ln=m.norm3 if f else None)
         self.ff2 = Linear(m.ff.net[2].weight, m.ff.net[2].bias)
 
     def cross_layers(self):
         return [self.kv2] + ([self.kv1] if self.self_is_cross else [])
 
-    def _cross(self, rec, x_norm, kv: CrossKV, n, s, out_lin, residual):
-        q = (self.q1 if kv is getattr(self, "kv1", None) else self.q2)(rec, x_norm)
+    def _cross(self, rec, q, kv: CrossKV, n, s, out_lin, residual, emit):
+        """q: projected queries [n*s, c] (released here); returns out_lin(attention) (+ RowStats if emit)."""
         skv = kv.kv.shape[1]
         kvv = kv.kv.view(n, skv, 2, self.heads, self.dh)
         attn = rec.buf(n, s, self.c)
         rec.add(nat.flash_attn, q.view(n, s, self.heads, self.dh), kvv[:, :, 0], kvv[:, :, 1], attn, batch=n,
                 heads=self.heads, seq_q=s, seq_kv=skv, head_dim=self.dh)
         rec.release(q)
-        y = out_lin(rec, attn.view(n * s, self.c), residual=residual)
+        y = out_lin(rec, attn.view(n * s, self.c), residual=residual, emit_stats=emit)
         rec.release(attn)
         return y
 
-    def __call__(self, rec: Recorder, y: torch.Tensor, n: int, s: int) -> torch.Tensor:
-        """y: [n*s, c] residual stream; returns the new stream (y is released)."""
-        x1 = self.ln1(rec, y)
-        if not self.self_is_cross and rec.patch is not None and rec.patch.P > 1:
+    def _self_attention(self, rec, x, st, n, s):
+        """x: input of the fused QKV projection (LayerNorm output, or the raw stream + its statistics)."""
+        attn = rec.buf(n, s, self.c)
+        if rec.patch is not None and rec.patch.P > 1:
             # sequence-parallel self-attention: K/V of the other strips are read from their owners inside the
             # kernel (TMA over the NVLink mappings), never gathered
-            attn = rec.buf(n, s, self.c)
             if s % 128 == 0 and self.dh <= 128:
                 qs = rec.patch.sym_buf(n * s, 3 * self.c)
-                self.qkv(rec, x1, out=qs.local)
+                self.qkv(rec, x, out=qs.local, stats=st)
                 v5 = qs.local.view(n, s, 3, self.heads, self.dh)
                 kpeers, v_ptrs = rec.patch.kv_peers(qs, self.c)
                 rec.add(nat.peer_signal, kpeers)
@@ -342,33 +418,52 @@ class TransformerBlock:
                 pp, P = rec.patch.p, rec.patch.P
                 kvf = rec.patch.sym_buf(n * s * P, 2 * self.c)
                 q = rec.buf(n * s, self.c)
-                rec.add(nat.igemm, x1, self.qkv.wgt[:self.c], q, n=1, h=1, w=n * s, splitk_scratch=rec.splitk)
+                self.qkv.call_rows(rec, x, 0, self.c, q, stats=st)
                 mine = kvf.local[pp * s:(pp + 1) * s]
-                rec.add(nat.igemm, x1, self.qkv.wgt[self.c:], mine, n=1, h=1, w=n * s, splitk_scratch=rec.splitk)
+                self.qkv.call_rows(rec, x, self.c, 3 * self.c, mine, stats=st)
                 rec.patch.group_exchange(rec, mine, kvf, pp * s * 2 * self.c * 2)
                 kv5 = kvf.local.view(n, s * P, 2, self.heads, self.dh)
                 rec.add(nat.flash_attn, q.view(n, s, self.heads, self.dh), kv5[:, :, 0], kv5[:, :, 1], attn, batch=n,
                         heads=self.heads, seq_q=s, seq_kv=s * P, head_dim=self.dh)
                 rec.release(q)
-            rec.release(x1)
-            y1 = self.o1(rec, attn.view(n * s, self.c), residual=y)
-            rec.release(attn)
-        elif not self.self_is_cross:
-            qkv = self.qkv(rec, x1)
-            rec.release(x1)
+        else:
+            qkv = self.qkv(rec, x, stats=st)
             v5 = qkv.view(n, s, 3, self.heads, self.dh)
-            attn = rec.buf(n, s, self.c)
             rec.add(nat.flash_attn, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn, batch=n, heads=self.heads, seq_q=s,
                     seq_kv=s, head_dim=self.dh)
             rec.release(qkv)
+        return attn
+    def __call__(self, rec: Recorder, y: torch.Tensor, n: int, s: int, st=None, emit: bool = False):
+        """y: [n*s, c] residual stream (released here).  Fused mode: `st` = RowStats of y, and with `emit` the
+        new stream comes back as (y3, RowStats) for the next block.  Returns the new stream."""
+        if self.fused:
+            attn = self._self_attention(rec, y, st, n, s)
+            rec.release(st.buf)
+            y1, st1 = self.o1(rec, attn.view(n * s, self.c), residual=y, emit_stats=True)
+            rec.release(attn)
+            rec.release(y)
+            q = self.q2(rec, y1, stats=st1)
+            rec.release(st1.buf)
+            y2, st2 = self._cross(rec, q, self.kv2, n, s, self.o2, y1, True)
+            rec.release(y1)
+            ff = self.ff1(rec, y2, stats=st2)
+            rec.release(st2.buf)
+            y3 = self.ff2(rec, ff, residual=y2, emit_stats=emit)
+            rec.release(ff)
+            rec.release(y2)
+            return y3
+        x1 = self.ln1(rec, y)
+        if not self.self_is_cross:
+            attn = self._self_attention(rec, x1, None, n, s)
+            rec.release(x1)
             y1 = self.o1(rec, attn.view(n * s, self.c), residual=y)
             rec.release(attn)
         else:
-            y1 = self._cross(rec, x1, self.kv1, n, s, self.o1, y)
+            y1 = self._cross(rec, self.q1(rec, x1), self.kv1, n, s, self.o1, y, False)
             rec.release(x1)
         rec.release(y)
         x2 = self.ln2(rec, y1)
-        y2 = self._cross(rec, x2, self.kv2, n, s, self.o2, y1)
+        y2 = self._cross(rec, self.q2(rec, x2), self.kv2, n, s, self.o2, y1, False)
         rec.release(x2)
         rec.release(y1)
         x3 = self.ln3(rec, y2)
@@ -392,11 +487,20 @@ class Transformer2D:
 
     def __call__(self, rec: Recorder, x: FM) -> FM:
         g = self.norm(rec, x, False)
-        y = self.proj_in(rec, g.tokens())
+        st = None
+        if self.blocks[0].fused:
+            y, st = self.proj_in(rec, g.tokens(), emit_stats=True)
+        else:
+            y = self.proj_in(rec, g.tokens())
         rec.release(g)
         s = x.h * x.w
-        for blk in self.blocks:
-            y = blk(rec, y, x.n, s)
+        for i, blk in enumerate(self.blocks):
+            nxt = i + 1 < len(self.blocks) and self.blocks[i + 1].fused
+            if blk.fused:
+                r = blk(rec, y, x.n, s, st, emit=nxt)
+                y, st = r if nxt else (r, None)
+            else:
+                y = blk(rec, y, x.n, s)
         out = rec.fm(x.n, x.h, x.w, x.c)
         self.proj_out(rec, y, residual=x.tokens(), out=out.tokens())
         rec.release(y)

@@ -44,3 +44,17 @@ def interleave_geglu(w: torch.Tensor, b: torch.Tensor | None, half: int = 64):
         bi = torch.stack([bv.reshape(inner // half, half), bg.reshape(inner // half, half)], dim=1)
         bi = bi.reshape(two_inner).contiguous()
     return wi, bi
+
+
+def fold_layernorm(w: torch.Tensor, b: torch.Tensor | None, gamma: torch.Tensor, beta: torch.Tensor):
+    """LayerNorm(x) @ w.T + b  ==  rstd * (x @ w2.T - mean * col_sums) + b2  with
+    w2 = w * gamma (per input column), b2 = w @ beta + b, col_sums = w2.sum(1): the affine part of the
+    LayerNorm moves into the weights, the statistics into the GEMM epilogue (sw_igemm row_stats_in).
+    Returns (w2 fp16, b2 fp16, col_sums fp32); col_sums is taken from the ROUNDED w2 so that the epilogue
+    subtracts exactly what the tensor core accumulated."""
+    w32, g32, be32 = w.detach().float(), gamma.detach().float(), beta.detach().float()
+    w2 = (w32 * g32[None, :]).to(torch.float16)
+    b2 = w32 @ be32
+    if b is not None:
+        b2 = b2 + b.detach().float()
+    return w2.contiguous(), b2.to(torch.float16).contiguous(), w2.float().sum(1).contiguous()

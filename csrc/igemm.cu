@@ -46,6 +46,15 @@ struct IGemmArgs {
     int bf16;
     int bn;             // N tile (multiple of 32, <= 256)
     int tmem_cols;      // power of two >= bn
+    // LayerNorm folded into the GEMM (weights pre-multiplied by gamma, bias' = W.beta + b on the host side):
+    //   out = rstd_r * (acc - mean_r * col_sums[c]) + bias'[c]
+    // with (mean, rstd) of each activation row rebuilt from per-column-tile partial sums that the GEMM
+    // producing the activation wrote in its own epilogue (row_stats_out), in tile order = deterministic.
+    float* row_stats_out;        // producer: [column tiles][rows][2] (sum, sum of squares) of the stored output
+    const float* row_stats_in;   // consumer: the producer's buffer
+    const float* col_sums;       // consumer: fp32 [cout], sum over K of the folded weight row
+    int stats_tiles, ln_width;   // consumer: partial slots per row, elements per normalised row
+    float ln_eps;
     int ptiles, total_tiles;  // persistent kernel: pixel tiles, pixel tiles x column tiles
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
     int splits;         // split-K factor (grid.z)
@@ -212,6 +221,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     __shared__ __align__(16) float s_bias[256];
+    __shared__ __align__(16) float s_cs[256];
 
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B operands need 1024-byte aligned stage bases.
@@ -416,8 +426,23 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 if (fold_rb && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
             }
             s_bias[i] = b;
+            s_cs[i] = (p.col_sums && col < p.cout) ? p.col_sums[col] : 0.0f;
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
+        float ln_mean = 0.0f, ln_rstd = 1.0f;
+        if (p.row_stats_in && row_ok) {
+            const size_t rows_total = size_t(p.n) * p.h * p.w;
+            float su = 0.0f, sq = 0.0f;
+            for (int ti = 0; ti < p.stats_tiles; ++ti) {
+                const float2 pr = *reinterpret_cast<const float2*>(p.row_stats_in + (size_t(ti) * rows_total + m) * 2);
+                su += pr.x;
+                sq += pr.y;
+            }
+            const float inv_w = 1.0f / float(p.ln_width);
+            ln_mean = su * inv_w;
+            ln_rstd = rsqrtf(fmaxf(sq * inv_w - ln_mean * ln_mean, 0.0f) + p.ln_eps);
+        }
+        float st_sum = 0.0f, st_sq = 0.0f;  // producer side: this row's sums over the tile's columns
 
         if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
         __syncwarp();
@@ -608,6 +633,13 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     f[0] += r0.x, f[1] += r0.y, f[2] += r1.x, f[3] += r1.y;
                     f[4] += r2.x, f[5] += r2.y, f[6] += r3.x, f[7] += r3.y;
                 }
+                if (p.row_stats_out) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        st_sum += f[j];
+                        st_sq = fmaf(f[j], f[j], st_sq);
+                    }
+                }
                 uint32_t dst = smem0 + off;
                 if (tail32 && (c8 >> 6) == nslab - 1)
                     dst = smem0 + (uint32_t(c8 >> 6) & 1u) * 16384u + uint32_t(r) * 64u + ((uint32_t(c8 >> 3) & 3u) << 4);
@@ -659,14 +691,26 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     for (int g8 = 0; g8 < 4; ++g8) {
                         const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c + g8 * 8]);
                         const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c + g8 * 8 + 4]);
-                        float f[8] = {__uint_as_float(v[g8 * 8 + 0]) + b0.x, __uint_as_float(v[g8 * 8 + 1]) + b0.y,
-                                      __uint_as_float(v[g8 * 8 + 2]) + b0.z, __uint_as_float(v[g8 * 8 + 3]) + b0.w,
-                                      __uint_as_float(v[g8 * 8 + 4]) + b1.x, __uint_as_float(v[g8 * 8 + 5]) + b1.y,
-                                      __uint_as_float(v[g8 * 8 + 6]) + b1.z, __uint_as_float(v[g8 * 8 + 7]) + b1.w};
+                        const float4 k0 = *reinterpret_cast<const float4*>(&s_cs[c + g8 * 8]);
+                        const float4 k1 = *reinterpret_cast<const float4*>(&s_cs[c + g8 * 8 + 4]);
+                        // (mean = 0, rstd = 1, col sums = 0 when no LayerNorm is folded in: plain acc + bias)
+                        float f[8] = {fmaf(ln_rstd, fmaf(-ln_mean, k0.x, __uint_as_float(v[g8 * 8 + 0])), b0.x),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k0.y, __uint_as_float(v[g8 * 8 + 1])), b0.y),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k0.z, __uint_as_float(v[g8 * 8 + 2])), b0.z),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k0.w, __uint_as_float(v[g8 * 8 + 3])), b0.w),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k1.x, __uint_as_float(v[g8 * 8 + 4])), b1.x),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k1.y, __uint_as_float(v[g8 * 8 + 5])), b1.y),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k1.z, __uint_as_float(v[g8 * 8 + 6])), b1.z),
+                                      fmaf(ln_rstd, fmaf(-ln_mean, k1.w, __uint_as_float(v[g8 * 8 + 7])), b1.w)};
                         put8(c + g8 * 8, f);
                     }
                     if ((c & 63) == 32 || c + 32 >= cend) slab_end(c >> 6);
                 }
+            }
+            if (p.row_stats_out && row_ok) {
+                const size_t rows_total = size_t(p.n) * p.h * p.w;
+                *reinterpret_cast<float2*>(p.row_stats_out + (size_t(blockIdx.y) * rows_total + m) * 2) =
+                    make_float2(st_sum, st_sq);
             }
             if (lead) bulk_wait_read<0>();
         } else if (p.act == SW_ACT_GEGLU) {
@@ -680,10 +724,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 uint32_t o[8];
 #pragma unroll
                 for (int j = 0; j < 16; j += 2) {
-                    const float a0 = __uint_as_float(v[j]) + s_bias[c + j];
-                    const float a1 = __uint_as_float(v[j + 1]) + s_bias[c + j + 1];
-                    const float g0 = __uint_as_float(g[j]) + s_bias[HALF + c + j];
-                    const float g1 = __uint_as_float(g[j + 1]) + s_bias[HALF + c + j + 1];
+                    const float a0 = fmaf(ln_rstd, fmaf(-ln_mean, s_cs[c + j], __uint_as_float(v[j])), s_bias[c + j]);
+                    const float a1 = fmaf(ln_rstd, fmaf(-ln_mean, s_cs[c + j + 1], __uint_as_float(v[j + 1])), s_bias[c + j + 1]);
+                    const float g0 = fmaf(ln_rstd, fmaf(-ln_mean, s_cs[HALF + c + j], __uint_as_float(g[j])), s_bias[HALF + c + j]);
+                    const float g1 = fmaf(ln_rstd, fmaf(-ln_mean, s_cs[HALF + c + j + 1], __uint_as_float(g[j + 1])),
+                                          s_bias[HALF + c + j + 1]);
                     o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
                 }
                 uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
@@ -902,6 +947,7 @@ __global__ void __launch_bounds__(kThreads)
     const int B_STAGE_BYTES = BN * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     __shared__ __align__(16) float s_bias[2][256];
+    __shared__ __align__(16) float s_csp[2][256];
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
@@ -1099,6 +1145,7 @@ __global__ void __launch_bounds__(kThreads)
             const size_t m = (size_t(ni) * p.h + y) * p.w + x;
             const uint32_t ab = uint32_t(i) & 1u;
             float* sb = s_bias[ab];
+            float* scs = s_csp[ab];
             const bool fold_rb = p.row_bias != nullptr && p.bi == 1;
             for (int k = threadIdx.x - 64; k < BN; k += 128) {
                 const int col = col0 + k;
@@ -1108,8 +1155,22 @@ __global__ void __launch_bounds__(kThreads)
                     if (fold_rb && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
                 }
                 sb[k] = b;
+                scs[k] = (p.col_sums && col < p.cout) ? p.col_sums[col] : 0.0f;
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
+            float ln_mean = 0.0f, ln_rstd = 1.0f;
+            if (p.row_stats_in && row_ok) {
+                const size_t rows_total = size_t(p.n) * p.h * p.w;
+                float su = 0.0f, sq = 0.0f;
+                for (int ti = 0; ti < p.stats_tiles; ++ti) {
+                    const float2 pr = *reinterpret_cast<const float2*>(p.row_stats_in + (size_t(ti) * rows_total + m) * 2);
+                    su += pr.x;
+                    sq += pr.y;
+                }
+                const float inv_w = 1.0f / float(p.ln_width);
+                ln_mean = su * inv_w;
+                ln_rstd = rsqrtf(fmaxf(sq * inv_w - ln_mean * ln_mean, 0.0f) + p.ln_eps);
+            }
             const uint32_t trow = tmem_base + ab * uint32_t(p.tmem_cols) + lane_off;
             const uint32_t acce = smem_u32(&acc_empty[ab]);
 
@@ -1141,10 +1202,11 @@ __global__ void __launch_bounds__(kThreads)
                         uint32_t o[8];
 #pragma unroll
                         for (int j = 0; j < 16; j += 2) {
-                            const float a0 = __uint_as_float(v[j]) + sb[c + j];
-                            const float a1 = __uint_as_float(v[j + 1]) + sb[c + j + 1];
-                            const float g0 = __uint_as_float(g[j]) + sb[HALF + c + j];
-                            const float g1 = __uint_as_float(g[j + 1]) + sb[HALF + c + j + 1];
+                            const float a0 = fmaf(ln_rstd, fmaf(-ln_mean, scs[c + j], __uint_as_float(v[j])), sb[c + j]);
+                            const float a1 = fmaf(ln_rstd, fmaf(-ln_mean, scs[c + j + 1], __uint_as_float(v[j + 1])), sb[c + j + 1]);
+                            const float g0 = fmaf(ln_rstd, fmaf(-ln_mean, scs[HALF + c + j], __uint_as_float(g[j])), sb[HALF + c + j]);
+                            const float g1 = fmaf(ln_rstd, fmaf(-ln_mean, scs[HALF + c + j + 1], __uint_as_float(g[j + 1])),
+                                                  sb[HALF + c + j + 1]);
                             o[j / 2] = pack_h2(a0 * gelu_f(g0), a1 * gelu_f(g1));
                         }
                         uint4* dst = reinterpret_cast<uint4*>(p.out + m * p.ldc + ocol0 + c);
@@ -1440,6 +1502,14 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     if (p->a_h_total < 0 || (p->a_h_total > 0 && (mode != 0 || p->a_y_off < 0 || p->a_y_off + p->h > p->a_h_total)))
         return swh::fail(-1, "sw_igemm: a_h_total=%d / a_y_off=%d do not contain the %d output rows", p->a_h_total,
                          p->a_y_off, p->h);
+    const bool ln_fused = p->row_stats_out != nullptr || p->row_stats_in != nullptr;
+    if (ln_fused) {
+        if (mode != 0) return swh::fail(-1, "sw_igemm: folded LayerNorm is defined for local GEMMs");
+        if (p->row_stats_out && p->act == SW_ACT_GEGLU)
+            return swh::fail(-1, "sw_igemm: row statistics cannot be emitted from a GEGLU epilogue");
+        if (p->row_stats_in && (!p->col_sums || p->stats_tiles <= 0 || p->ln_width <= 0))
+            return swh::fail(-1, "sw_igemm: row_stats_in needs col_sums, stats_tiles and ln_width");
+    }
     if (p->gn_stats) return swh::fail(-1, "sw_igemm: gn_stats epilogue not available in this build");
     if (p->bf16) return swh::fail(-1, "sw_igemm: bf16 operands not enabled in this build (fp16 only)");
     if ((p->a_ld && (p->a_ld % 8 || p->a_ld < p->c1)) || (p->w_ld % 8))
@@ -1458,6 +1528,12 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.kw = p->kw;
     a.pad = p->pad;
     a.pad_w = p->pad_w1 > 0 ? p->pad_w1 - 1 : p->pad;
+    a.row_stats_out = p->row_stats_out;
+    a.row_stats_in = p->row_stats_in;
+    a.col_sums = p->col_sums;
+    a.stats_tiles = p->stats_tiles;
+    a.ln_width = p->ln_width;
+    a.ln_eps = p->ln_eps;
     a.pad_y1 = p->pad - p->a_y_off;  // a1 may be a taller tensor (halo rows / a window of a full image)
     a.cout = p->cout;
     pick_box(p->n, p->h, p->w, &a.bw, &a.bh, &a.bi);
@@ -1529,6 +1605,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     bool pair = grid_x >= 32 && bn >= 192 && (mode == 0 || m_local % 256 == 0);
     if (p->cta_pair == 1) pair = false;
     if (p->cta_pair == 2) pair = grid_x >= 2 && bn >= 64 && mode == 0;
+    if (ln_fused) pair = false;  // folded LayerNorm lives in the single-CTA epilogues only
 
     // ---- pipeline depth: two CTAs per SM (epilogue of one overlaps the main loop of the other)
     // when three stages fit in ~110 KB, else one CTA with a deeper ring.
@@ -1561,7 +1638,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
     const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
-    if (mode == 0 && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
+    if (mode == 0 && !ln_fused && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
         int want = int(slots / ctas);
@@ -1631,7 +1708,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             const char* e = getenv("SW_IGEMM_TMA_EPI");
             env_epi = e ? atoi(e) : 1;
         }
-        if (!env_epi) a.tma_epi = 0;
+        if (!env_epi && !ln_fused) a.tma_epi = 0;
     }
     if (a.tma_epi) {
         const uint64_t nc = p->act == SW_ACT_GEGLU ? uint64_t(p->cout / 2) : uint64_t(p->cout);
@@ -1654,7 +1731,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         tOut = tRes = tOut32 = tB;
     }
     // ---- persistent kernel (see k_igemm_p): worth it once a CTA would get more than one tile
-    if (mode == 0 && !pair && a.splits == 1) {
+    if (mode == 0 && !pair && a.splits == 1 && (!ln_fused || (p->act == SW_ACT_GEGLU && !p->row_stats_out))) {
         static int env_persist = -1;  // SW_IGEMM_PERSIST: 0 never, 1 auto (default), 2 whenever possible
         if (env_persist < 0) {
             const char* e = getenv("SW_IGEMM_PERSIST");
@@ -1672,7 +1749,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             const int stage_area = a.tma_epi ? 65536 : 0;
             // GEGLU (no staging boxes, epilogue-heavy): two persistent CTAs per SM = eight epilogue warps
             const int occ = (!a.tma_epi && 2 * a.tmem_cols * 2 <= 512 && 2 * (3 * stage_bytes + 4096) <= 227 * 1024) ? 2 : 1;
-            int st = ((occ == 2 ? 112 : 225) * 1024 - 1280 - stage_area) / stage_bytes;
+            int st = ((occ == 2 ? 110 : 222) * 1024 - 1280 - stage_area) / stage_bytes;
             if (st > 8) st = 8;
             if (st > kblocks * 2) st = kblocks * 2;
             if (st >= 2) {
@@ -1684,7 +1761,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
                 int dev = 0;
                 SW_CUDA_OK(cudaGetDevice(&dev));
                 if (dev < 64 && !configured[dev]) {
-                    SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_p, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+                    SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_p, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024));
                     configured[dev] = true;
                 }
                 const int grid = total < long(occ) * sms ? int(total) : occ * sms;

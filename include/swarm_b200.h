@@ -91,6 +91,18 @@ typedef struct {
      * full image.  0 = a1 has exactly h rows. */
     int32_t a_h_total;
     int32_t a_y_off;
+    /* LayerNorm folded into the GEMM that consumes it.  The consumer runs on the RAW activation with
+     * weights pre-multiplied by gamma (bias' = W.beta + b, col_sums[c] = sum_k W'[c,k], host side) and
+     * its epilogue computes rstd_r * (acc - mean_r * col_sums[c]) + bias'[c]; (mean, rstd) of row r come
+     * from `stats_tiles` partial (sum, sum of squares) pairs that the GEMM PRODUCING the activation wrote
+     * to row_stats_out = float [its column tiles][rows][2] in its own epilogue (pass tile_n so the tile
+     * count is known).  Replaces the LayerNorm launch and the normalised copy of the activation. */
+    float* row_stats_out;
+    const float* row_stats_in;
+    const float* col_sums;
+    int32_t stats_tiles;
+    int32_t ln_width;
+    float ln_eps;
     int32_t persist;     /* 0 = auto, 1 = one tile per CTA, 2 = persistent CTAs with double-buffered accumulators when possible */
 } sw_igemm_params;
 

@@ -124,3 +124,12 @@ def test_unet3d_engine_matches_torch(overrides, frames, size):
     assert torch.isfinite(outs[3]).all() and outs[3].shape == outs[2].shape
     vid = eng(prompt="a video", num_frames=frames, height=size, width=size, num_inference_steps=2)
     assert len(vid.frames) == frames and vid.frames[0].shape == (size, size, 3) and vid.frames[0].dtype.name == "uint8"
+
+
+def test_layernorm_fusion_matches_torch(monkeypatch):
+    """SW_LN_FUSE=1: LayerNorms folded into the consuming projections, statistics from the producing GEMMs."""
+    monkeypatch.setenv("SW_LN_FUSE", "1")
+    ref, eng = _pipes("sd15")
+    _compare(ref, eng, 2, 5e-2, height=256, width=256)
+    rec = next(iter(eng._denoiser()._graphs.values())).rec
+    assert not any(getattr(fn, "__name__", "") == "layernorm" for fn, _, _ in rec.ops)

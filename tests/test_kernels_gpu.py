@@ -343,3 +343,44 @@ def test_flash_attn_over_frames(nat, f, hw, heads, d):
     q, k, vv = (v[:, :, i].float().permute(0, 2, 1, 3) for i in range(3))  # [hw, heads, f, d]
     ref = F.scaled_dot_product_attention(q, k, vv).permute(2, 0, 1, 3).reshape(f, hw, c)
     assert _rel_err(out, ref) < 5e-3
+
+
+@pytest.mark.parametrize("rows,c,nout,geglu", [(512, 1280, 3840, False), (2048, 640, 640, False), (8192, 320, 2560, True),
+                                               (300, 320, 960, False), (1024, 1280, 10240, True)])
+def test_layernorm_folded_into_gemm(nat, rows, c, nout, geglu):
+    """y = x0 @ Wp^T + r (producer, emits row statistics); out = LayerNorm(y) @ W^T + b (consumer, LayerNorm folded
+    into the weights + epilogue) against the unfused fp32 computation."""
+    from chiaswarm_b200.ops.packing import fold_layernorm, interleave_geglu
+
+    torch.manual_seed(12)
+    x0 = torch.randn(rows, c, device="cuda", dtype=torch.float16)
+    wp = torch.randn(c, c, device="cuda", dtype=torch.float16) * c ** -0.5
+    bp = torch.randn(c, device="cuda", dtype=torch.float16)
+    res = torch.randn(rows, c, device="cuda", dtype=torch.float16) * 2 + 0.3
+    gamma = torch.randn(c, device="cuda", dtype=torch.float16) * 0.5 + 1
+    beta = torch.randn(c, device="cuda", dtype=torch.float16) * 0.2
+    w = torch.randn(nout, c, device="cuda", dtype=torch.float16) * c ** -0.5
+    b = torch.randn(nout, device="cuda", dtype=torch.float16)
+    tiles = (c + 127) // 128
+    stats = torch.zeros(tiles, rows, 2, device="cuda", dtype=torch.float32)
+    y = torch.empty(rows, c, device="cuda", dtype=torch.float16)
+    nat.igemm(x0, wp, y, n=1, h=1, w=rows, bias=bp, residual=res, tile_n=128, row_stats_out=stats)
+    y_ref = x0.float() @ wp.float().t() + bp.float() + res.float()
+    assert _rel_err(y, y_ref) < 4e-3
+    s_ref = torch.stack([y_ref.sum(1), (y_ref * y_ref).sum(1)], 1)
+    assert _rel_err(stats.sum(0), s_ref) < 2e-3
+    w2, b2, cs = fold_layernorm(w, b, gamma, beta)
+    act = nat.ACT_NONE
+    if geglu:
+        _, cs = interleave_geglu(w2, cs)
+        w2, b2 = interleave_geglu(w2, b2)
+        act = nat.ACT_GEGLU
+    out = torch.empty(rows, nout // 2 if geglu else nout, device="cuda", dtype=torch.float16)
+    nat.igemm(y, w2, out, n=1, h=1, w=rows, bias=b2, act=act, tile_n=128 if geglu else 0, row_stats_in=stats,
+              stats_tiles=tiles, ln_width=c, ln_eps=1e-5, col_sums=cs.float().contiguous())
+    ln = F.layer_norm(y.float(), (c,), gamma.float(), beta.float(), 1e-5)
+    ref = ln @ w.float().t() + b.float()
+    if geglu:
+        val, gate = ref.chunk(2, dim=-1)
+        ref = val * F.gelu(gate)
+    assert _rel_err(out, ref) < 8e-3
