@@ -62,6 +62,7 @@ class IGemmParams(C.Structure):
         ("stats_tiles", C.c_int32),
         ("ln_width", C.c_int32),
         ("ln_eps", C.c_float),
+        ("cluster_k", C.c_int32),
         ("persist", C.c_int32),
     ]
 
@@ -208,7 +209,7 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
           residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None,
           a_h_total=0, a_y_off=0, persist=0, row_stats_out=None, row_stats_in=None, col_sums=None, stats_tiles=0,
-          ln_width=0, ln_eps=0.0):
+          ln_width=0, ln_eps=0.0, cluster_k=0):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -224,11 +225,11 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
     if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
         raise ValueError("strided a1 is only supported for plain GEMMs")
-    if (tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0 and persist == 0
+    if (tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0 and persist == 0 and cluster_k == 0
             and row_stats_out is None and row_stats_in is None):
         tuned = tuning.lookup(n, h, w, kh, kw, c1, c2, cout, act, residual is not None)
         if tuned is not None:
-            tile_n, cta_pair, splitk_min_kb, persist = tuned
+            tile_n, cta_pair, splitk_min_kb, persist, cluster_k = tuned
     p = IGemmParams()
     p.a1, p.a2 = _ptr(a1), _ptr(a2)
     p.c1, p.c2 = c1, c2
@@ -257,6 +258,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.pad_w1 = 0 if pad_w is None else pad_w + 1
     p.a_h_total, p.a_y_off = a_h_total, a_y_off
     p.persist = persist
+    p.cluster_k = cluster_k
     p.row_stats_out, p.row_stats_in, p.col_sums = _ptr(row_stats_out), _ptr(row_stats_in), _ptr(col_sums)
     p.stats_tiles, p.ln_width, p.ln_eps = stats_tiles, ln_width, ln_eps
     if splitk_scratch is not None:

@@ -14,27 +14,27 @@ from pathlib import Path
 from typing import Dict, Optional, Tuple
 
 _PATH = Path(__file__).with_name("igemm_tuning.json")
-_table: Optional[Dict[str, Tuple[int, int, int, int]]] = None
+_table: Optional[Dict[str, Tuple[int, ...]]] = None
 
 
 def key_of(n, h, w, kh, kw, c1, c2, cout, act, residual) -> str:
     return f"{n},{h},{w},{kh},{kw},{c1},{c2},{cout},{act},{int(bool(residual))}"
 
 
-def table() -> Dict[str, Tuple[int, int, int, int]]:
+def table() -> Dict[str, Tuple[int, ...]]:
     global _table
     if _table is None:
         _table = {}
         if os.environ.get("SW_IGEMM_TUNING", "1") not in ("0", "") and _PATH.is_file():
             try:
                 raw = json.loads(_PATH.read_text())
-                _table = {k: (int(v[0]), int(v[1]), int(v[2]), int(v[3]) if len(v) > 3 else 0)
+                _table = {k: (int(v[0]), int(v[1]), int(v[2]), int(v[3]) if len(v) > 3 else 0, int(v[4]) if len(v) > 4 else 0)
                           for k, v in raw.get("configs", {}).items()}
             except (ValueError, OSError, TypeError, IndexError):
                 _table = {}
     return _table
 
 
-def lookup(n, h, w, kh, kw, c1, c2, cout, act, residual) -> Optional[Tuple[int, int, int, int]]:
-    """(tile_n, cta_pair, splitk_min_kb, persist) or None."""
+def lookup(n, h, w, kh, kw, c1, c2, cout, act, residual) -> Optional[Tuple[int, ...]]:
+    """(tile_n, cta_pair, splitk_min_kb, persist, cluster_k) or None."""
     return table().get(key_of(n, h, w, kh, kw, c1, c2, cout, act, residual))

@@ -57,6 +57,7 @@ struct IGemmArgs {
     float ln_eps;
     int ptiles, total_tiles;  // persistent kernel: pixel tiles, pixel tiles x column tiles
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
+    int cluster_k;      // splits == 2 and the two splits of a tile form a cluster: partials meet in DSMEM
     int splits;         // split-K factor (grid.z)
     int kb_per_split;   // k-blocks per split
     unsigned int* tickets;  // [tiles] arrival counters (split-K)
@@ -197,6 +198,10 @@ __device__ __forceinline__ void tmem_dealloc_any(uint32_t taddr, uint32_t cols) 
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
     else
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 template <bool PAIR>
 __device__ __forceinline__ void cta_or_cluster_sync() {
@@ -357,6 +362,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 }
             }
         }
+        if (!PAIR && p.cluster_k) cluster_sync_all();  // (whole cluster: see the epilogue)
     } else if (warp == 1) {
         if (lane == 0 && (!PAIR || leader)) {
             // ---------------- MMA issuer (lean loop)
@@ -402,6 +408,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             }
             mma_commit<PAIR>(smem_u32(acc_full));
         }
+        if (!PAIR && p.cluster_k) cluster_sync_all();
     } else {
         // ---------------- epilogue: one thread per accumulator row
         const int q = warp & 3;
@@ -454,7 +461,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         // band of rows -- sums in split order, so the result is bit-reproducible -- and runs the epilogue
         // for that band.  The reduction is spread over every participating SM instead of serialising
         // on the CTA that happened to arrive last (that version lost to no split at all beyond 4 splits).
-        if (p.splits > 1) {
+        if (p.splits > 1 && !p.cluster_k) {
             const int tile_id = blockIdx.x * gridDim.y + blockIdx.y;
             const int nchunk = BN / 32;
             float* tile_base = p.partials + size_t(tile_id) * p.splits * nchunk * 4096;
@@ -543,7 +550,37 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 }
             }
         }
-        const bool do_epilogue = p.splits == 1;
+        // ---- split-K over a cluster of two CTAs (small GEMMs: every CTA otherwise streams the whole
+        // 128 x K activation slab at ~40 B/clk): each CTA accumulates half of K, ships the OTHER CTA's half
+        // of the columns through distributed shared memory, and after one cluster barrier finishes its own
+        // half.  No global round trip, no spinning; a + b is the same in both orders, so still deterministic.
+        int kc_begin = 0, kc_end = BN;
+        const float* kstage = nullptr;
+        if (!PAIR && p.cluster_k) {
+            const uint32_t zr = blockIdx.z;  // == rank in the (1,1,2) cluster
+            const int half = BN >> 1;
+            float* stage = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full) + 256);
+            uint32_t remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(stage)), "r"(zr ^ 1u));
+            const int pc0 = int(zr ^ 1u) * half;
+#pragma unroll 1
+            for (int k = 0; k < half; k += 32) {
+                uint32_t v[32];
+                tmem_ld32(trow + pc0 + k, v);
+                tmem_ld_wait();
+                const uint32_t dst = remote + uint32_t(((k >> 5) * 128 + r) * 128);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16 * j), "r"(v[4 * j]),
+                                 "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3])
+                                 : "memory");
+            }
+            cluster_sync_all();
+            kc_begin = int(zr) * half;
+            kc_end = kc_begin + half;
+            kstage = stage;
+        }
+        const bool do_epilogue = p.splits == 1 || p.cluster_k;
         if (!do_epilogue) {
             // another split owns the epilogue of this tile
         } else if (p.tma_epi) {
@@ -850,10 +887,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                 // TMEM chunk c+32 and its residual are in flight while chunk c is converted and stored
                 uint32_t vn[32];
                 uint4 rn[4];
-                tmem_ld32(trow, vn);
-                fetch(0, rn);
+                tmem_ld32(trow + kc_begin, vn);
+                fetch(kc_begin, rn);
 #pragma unroll 1
-                for (int c = 0; c < BN; c += 32) {
+                for (int c = kc_begin; c < kc_end; c += 32) {
                     uint32_t v[32];
                     uint4 rs[4];
                     tmem_ld_wait_dep(vn);
@@ -861,9 +898,20 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     for (int j = 0; j < 32; ++j) v[j] = vn[j];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) rs[j] = rn[j];
-                    if (c + 32 < BN) {
+                    if (c + 32 < kc_end) {
                         tmem_ld32(trow + c + 32, vn);
                         fetch(c + 32, rn);
+                    }
+                    if (kstage != nullptr) {  // the other half of K, delivered by the cluster peer
+                        const float4* ps = reinterpret_cast<const float4*>(kstage + (((c - kc_begin) >> 5) * 128 + r) * 32);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 a = ps[j];
+                            v[4 * j] = __float_as_uint(__uint_as_float(v[4 * j]) + a.x);
+                            v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + a.y);
+                            v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + a.z);
+                            v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + a.w);
+                        }
                     }
                     emit(c, v, rs);
                 }
@@ -1450,7 +1498,7 @@ int smem_bytes(const IGemmArgs& a, bool pair) {
     const int stage_bytes = A_STAGE_BYTES + (pair ? a.bn / 2 : a.bn) * BK * 2;
     int ring = a.stages * stage_bytes;
     if (a.tma_epi && ring < 65536) ring = 65536;
-    return ring + 1024 + 256;
+    return ring + 1024 + 256 + (a.cluster_k ? 128 * (a.bn / 2) * 4 : 0);
 }
 
 int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, const CUtensorMap& tB,
@@ -1467,6 +1515,11 @@ int launch(const IGemmArgs& a, const CUtensorMap& tA1, const CUtensorMap& tA2, c
     }
     const int ntile = (a.cout + a.bn - 1) / a.bn;
     if (!pair) {
+        if (a.cluster_k) {
+            SW_CUDA_OK(swh::launch_pdl_z(k_igemm, dim3(grid_x, ntile, 2), dim3(kThreads), size_t(smem), st, 2, tA1, tA2,
+                                         tB, tOut, tRes, tOut32, a));
+            return 0;
+        }
         SW_CUDA_OK(swh::launch_pdl(k_igemm, dim3(grid_x, ntile, a.splits), dim3(kThreads), size_t(smem), st, 1, tA1,
                                    tA2, tB, tOut, tRes, tOut32, a));
         return 0;
@@ -1637,8 +1690,27 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     a.splits = 1;
     a.kb_per_split = kblocks;
     const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
+    // ---- split-K over a cluster of two (DSMEM exchange, see the epilogue): small GEMMs whose tiles do not fill
+    // the chip, so that every SM streams half of its activation slab
+    {
+        static int env_ck = -1;  // SW_IGEMM_CLUSTERK: 0 never, 1 when requested (default), 2 whenever eligible
+        if (env_ck < 0) {
+            const char* e = getenv("SW_IGEMM_CLUSTERK");
+            env_ck = e ? atoi(e) : 1;
+        }
+        const bool eligible = mode == 0 && !pair && !ln_fused && p->act != SW_ACT_GEGLU && bn % 64 == 0 && kblocks >= 4 &&
+                              2 * ctas <= 2L * sms;
+        const bool want = env_ck == 2 || (env_ck == 1 && p->cluster_k == 2);
+        if (eligible && want && p->cluster_k != 1) {
+            a.cluster_k = 1;
+            a.splits = 2;
+            a.kb_per_split = (kblocks + 1) / 2;
+            if (a.kb_per_split < a.stages) a.stages = a.kb_per_split;
+            while (a.stages > 2 && a.stages * stage_bytes + 128 * (bn / 2) * 4 > 220 * 1024) --a.stages;
+        }
+    }
     const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
-    if (mode == 0 && !ln_fused && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
+    if (mode == 0 && !a.cluster_k && !ln_fused && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
         int want = int(slots / ctas);
@@ -1701,7 +1773,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     CUtensorMap tOut, tRes, tOut32;
     // (GEGLU tiles produce a single 64-column slab: nothing to overlap the store's round trip with, the
     // direct register -> global path measured 30-50 % faster there)
-    a.tma_epi = (mode != 2 && a.splits == 1 && p->act != SW_ACT_GEGLU) ? 1 : 0;
+    a.tma_epi = (mode != 2 && a.splits == 1 && !a.cluster_k && p->act != SW_ACT_GEGLU) ? 1 : 0;
     {
         static int env_epi = -1;  // SW_IGEMM_TMA_EPI=0 keeps the register -> global store epilogue (A/B runs)
         if (env_epi < 0) {

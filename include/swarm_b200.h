@@ -103,6 +103,7 @@ typedef struct {
     int32_t stats_tiles;
     int32_t ln_width;
     float ln_eps;
+    int32_t cluster_k;   /* 0 / 1 = off, 2 = split K over a cluster of two CTAs (partials meet in distributed shared memory) when eligible */
     int32_t persist;     /* 0 = auto, 1 = one tile per CTA, 2 = persistent CTAs with double-buffered accumulators when possible */
 } sw_igemm_params;
 

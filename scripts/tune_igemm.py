@@ -119,9 +119,11 @@ def plans():
 
 # (tile_n, cta_pair, splitk_min_kb): 64 k-blocks per split = effectively no split-K for the UNet shapes
 # 4th field: 0 = kernel's default, 1 = one tile per CTA, 2 = persistent CTAs (double-buffered accumulators)
-CANDS = [(0, 0, 0, 0), (64, 1, 64, 1), (128, 1, 64, 1), (256, 1, 64, 1), (128, 2, 64, 1), (256, 2, 64, 1),
-         (64, 1, 8, 1), (128, 1, 8, 1), (256, 1, 8, 1), (128, 2, 8, 1), (256, 2, 8, 1), (64, 1, 16, 1), (128, 1, 16, 1),
-         (256, 1, 16, 1), (64, 1, 64, 2), (128, 1, 64, 2), (256, 1, 64, 2)]
+# 5th field: 2 = split K over a cluster of two CTAs (DSMEM exchange) when the launcher finds it eligible
+CANDS = [(0, 0, 0, 0, 0), (64, 1, 64, 1, 0), (128, 1, 64, 1, 0), (256, 1, 64, 1, 0), (128, 2, 64, 1, 0), (256, 2, 64, 1, 0),
+         (64, 1, 8, 1, 0), (128, 1, 8, 1, 0), (256, 1, 8, 1, 0), (128, 2, 8, 1, 0), (256, 2, 8, 1, 0), (64, 1, 16, 1, 0),
+         (128, 1, 16, 1, 0), (256, 1, 16, 1, 0), (64, 1, 64, 2, 0), (128, 1, 64, 2, 0), (256, 1, 64, 2, 0),
+         (64, 1, 64, 1, 2), (128, 1, 64, 1, 2), (256, 1, 64, 1, 2)]
 configs, report = {}, []
 kept = {}
 if args.merge and os.path.isfile(args.merge):
@@ -177,19 +179,19 @@ for name, (recs, keep) in plans():
                 continue
             seen += 1
             times = []
-            for t, pr, mk, ps in CANDS:
+            for t, pr, mk, ps, ck in CANDS:
                 if act == nat.ACT_GEGLU and t not in (0, 128):
                     continue
                 if t > max(64, (wgt.shape[0] + 31) // 32 * 32):
                     continue
-                k2 = dict(kw, tile_n=t, cta_pair=pr, splitk_min_kb=mk, persist=ps)
+                k2 = dict(kw, tile_n=t, cta_pair=pr, splitk_min_kb=mk, persist=ps, cluster_k=ck)
                 try:
                     acts = [x for x in (a1, kw.get("a2"), kw.get("residual")) if x is not None]
-                    times.append((graph_time(lambda: fn(*a, **k2), acts), (t, pr, mk, ps)))
+                    times.append((graph_time(lambda: fn(*a, **k2), acts), (t, pr, mk, ps, ck)))
                 except Exception:
                     pass
             times.sort()
-            base = [x for x, c in times if c == (0, 0, 0, 0)]
+            base = [x for x, c in times if c == (0, 0, 0, 0, 0)]
             configs[key] = times[0][1]
             report.append((name, key, times[0][1], times[0][0], base[0] if base else float("nan")))
     print(f"{name}: {seen} new shapes", flush=True)
