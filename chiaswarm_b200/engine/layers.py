@@ -178,12 +178,18 @@ class Conv:
 STATS_TILE = 128  # column tile of GEMMs that emit row statistics (fixes the number of partial slots)
 
 
-def fuse_layernorm() -> bool:
-    """SW_LN_FUSE=1 folds the transformer LayerNorms into the GEMMs around them (48 fewer launches per SD1.5
-    step, 210 per SDXL step).  Measured a wash (SD1.5 3.67 vs 3.68 img/s, SDXL 723 vs 717 ms, 4-GPU patch
-    14.9 vs 14.7 ms/step): the GEMMs that carry the statistics give up CTA pairs / split-K and each pays 1-2 us
-    for the extra loads, which is what the 4.5 us LayerNorm kernels cost.  Off by default; kept, tested."""
-    return os.environ.get("SW_LN_FUSE", "0") not in ("0", "")
+def fuse_layernorm(width: int = 0) -> bool:
+    """Fold a transformer block's LayerNorms into the GEMMs around them (ops/packing.fold_layernorm)?
+    SW_LN_FUSE = 0 never, 1 always, unset = blocks up to 640 channels.  Measured: all blocks fused gives SD1.5
+    3.67 vs 3.62 img/s but SDXL 728 vs 722 ms (its sixty 1280-wide blocks lose: the GEMMs that carry the
+    statistics give up CTA pairs / split-K and pay 1-2 us for the extra loads, about what a 4.5 us LayerNorm
+    kernel costs); the 4-GPU patch-parallel step does not care (14.9 vs 14.7 ms with 210 fewer launches)."""
+    mode = os.environ.get("SW_LN_FUSE", "auto")
+    if mode in ("0", ""):
+        return False
+    if mode == "1":
+        return True
+    return 0 < width <= 640
 
 
 class RowStats:
@@ -367,7 +373,7 @@ class TransformerBlock:
         self.c = c
         a1, a2 = m.attn1, m.attn2
         self.self_is_cross = m.only_cross_attention
-        self.fused = fuse_layernorm() and not self.self_is_cross
+        self.fused = fuse_layernorm(c) and not self.self_is_cross
         f = self.fused
         if not f:
             self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
