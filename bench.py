@@ -34,16 +34,21 @@ METRIC = "images/sec/box SD1.5 512x512 50-step txt2img"
 
 
 def reference_unavailable():
-    why = ("reference is not installable: /root/reference has no setup.py/pyproject.toml, and it imports diffusers, "
-           "accelerate and xformers, none of which are on the image or in /opt/wheelhouse")
+    """Why the unmodified reference cannot be benchmarked here (one line), or None if it can."""
+    why = ("reference is not installable: /root/reference has no setup.py/pyproject.toml (pip: not installable), and "
+           "swarm/worker.py imports diffusers, accelerate and xformers, none of which are on the image or in /opt/wheelhouse")
+    ref = os.path.join(ROOT, "baseline", "_ref", "swarm", "worker.py")
+    if not os.path.isfile(ref):  # (this repo's own `swarm` alias package must not be mistaken for it)
+        return why + "; baseline/_ref is empty"
     try:
-        sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))
-        import swarm.worker  # noqa: F401
+        import importlib.util
 
-        why = None
-    except Exception as e:  # expected
-        why = f"{why} ({type(e).__name__}: {e})"
-    return why
+        spec = importlib.util.spec_from_file_location("_reference_swarm_worker", ref)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return "reference imported but no driver for it exists in this bench (it needs diffusers pipelines and hub checkpoints)"
+    except Exception as e:  # expected: ModuleNotFoundError: diffusers
+        return f"{why} ({type(e).__name__}: {e})"
 
 
 class ClockSampler:
