@@ -373,21 +373,29 @@ class TransformerBlock:
         self.c = c
         a1, a2 = m.attn1, m.attn2
         self.self_is_cross = m.only_cross_attention
-        self.fused = fuse_layernorm(c) and not self.self_is_cross
-        f = self.fused
-        if not f:
-            self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
+        self.can_fuse = fuse_layernorm(c) and not self.self_is_cross
+        self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
         if not self.self_is_cross:
-            self.qkv = Linear(torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], 0), ln=m.norm1 if f else None)
+            wqkv = torch.cat([a1.to_q.weight, a1.to_k.weight, a1.to_v.weight], 0)
+            self.qkv = Linear(wqkv)
+            if self.can_fuse:  # second set of the three consuming projections with their LayerNorm folded in
+                self.qkv_f = Linear(wqkv, ln=m.norm1)
+                self.q2_f = Linear(a2.to_q.weight, ln=m.norm2)
+                self.ff1_f = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True, ln=m.norm3)
         else:
             self.q1 = Linear(a1.to_q.weight)
             self.kv1 = CrossKV(a1)
         self.o1 = Linear(a1.to_out[0].weight, a1.to_out[0].bias)
-        self.q2 = Linear(a2.to_q.weight, ln=m.norm2 if f else None)
+        self.q2 = Linear(a2.to_q.weight)
         self.kv2 = CrossKV(a2)
         self.o2 = Linear(a2.to_out[0].weight, a2.to_out[0].bias)
-        self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True, ln=m.norm3 if f else None)
+        self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True)
         self.ff2 = Linear(m.ff.net[2].weight, m.ff.net[2].bias)
+
+    def use_fused(self, rows: int) -> bool:
+        """Fold the LayerNorms for this call?  Big token counts keep the separate kernel: their GEMMs want CTA
+        pairs, which the statistics plumbing rules out (ControlNet 768x768 batch 8 and text-to-video lost 3 %)."""
+        return self.can_fuse and (rows <= 16384 or os.environ.get("SW_LN_FUSE") == "1")
 
     def cross_layers(self):
         return [self.kv2] + ([self.kv1] if self.self_is_cross else [])
@@ -404,15 +412,16 @@ class TransformerBlock:
         rec.release(attn)
         return y
 
-    def _self_attention(self, rec, x, st, n, s):
+    def _self_attention(self, rec, x, st, n, s, qkv_lin=None):
         """x: input of the fused QKV projection (LayerNorm output, or the raw stream + its statistics)."""
         attn = rec.buf(n, s, self.c)
+        lin = qkv_lin or self.qkv
         if rec.patch is not None and rec.patch.P > 1:
             # sequence-parallel self-attention: K/V of the other strips are read from their owners inside the
             # kernel (TMA over the NVLink mappings), never gathered
             if s % 128 == 0 and self.dh <= 128:
                 qs = rec.patch.sym_buf(n * s, 3 * self.c)
-                self.qkv(rec, x, out=qs.local, stats=st)
+                lin(rec, x, out=qs.local, stats=st)
                 v5 = qs.local.view(n, s, 3, self.heads, self.dh)
                 kpeers, v_ptrs = rec.patch.kv_peers(qs, self.c)
                 rec.add(nat.peer_signal, kpeers)
@@ -424,16 +433,16 @@ class TransformerBlock:
                 pp, P = rec.patch.p, rec.patch.P
                 kvf = rec.patch.sym_buf(n * s * P, 2 * self.c)
                 q = rec.buf(n * s, self.c)
-                self.qkv.call_rows(rec, x, 0, self.c, q, stats=st)
+                lin.call_rows(rec, x, 0, self.c, q, stats=st)
                 mine = kvf.local[pp * s:(pp + 1) * s]
-                self.qkv.call_rows(rec, x, self.c, 3 * self.c, mine, stats=st)
+                lin.call_rows(rec, x, self.c, 3 * self.c, mine, stats=st)
                 rec.patch.group_exchange(rec, mine, kvf, pp * s * 2 * self.c * 2)
                 kv5 = kvf.local.view(n, s * P, 2, self.heads, self.dh)
                 rec.add(nat.flash_attn, q.view(n, s, self.heads, self.dh), kv5[:, :, 0], kv5[:, :, 1], attn, batch=n,
                         heads=self.heads, seq_q=s, seq_kv=s * P, head_dim=self.dh)
                 rec.release(q)
         else:
-            qkv = self.qkv(rec, x, stats=st)
+            qkv = lin(rec, x, stats=st)
             v5 = qkv.view(n, s, 3, self.heads, self.dh)
             rec.add(nat.flash_attn, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn, batch=n, heads=self.heads, seq_q=s,
                     seq_kv=s, head_dim=self.dh)
@@ -442,17 +451,17 @@ class TransformerBlock:
     def __call__(self, rec: Recorder, y: torch.Tensor, n: int, s: int, st=None, emit: bool = False):
         """y: [n*s, c] residual stream (released here).  Fused mode: `st` = RowStats of y, and with `emit` the
         new stream comes back as (y3, RowStats) for the next block.  Returns the new stream."""
-        if self.fused:
-            attn = self._self_attention(rec, y, st, n, s)
+        if st is not None:  # fused: y comes with its row statistics
+            attn = self._self_attention(rec, y, st, n, s, self.qkv_f)
             rec.release(st.buf)
             y1, st1 = self.o1(rec, attn.view(n * s, self.c), residual=y, emit_stats=True)
             rec.release(attn)
             rec.release(y)
-            q = self.q2(rec, y1, stats=st1)
+            q = self.q2_f(rec, y1, stats=st1)
             rec.release(st1.buf)
             y2, st2 = self._cross(rec, q, self.kv2, n, s, self.o2, y1, True)
             rec.release(y1)
-            ff = self.ff1(rec, y2, stats=st2)
+            ff = self.ff1_f(rec, y2, stats=st2)
             rec.release(st2.buf)
             y3 = self.ff2(rec, ff, residual=y2, emit_stats=emit)
             rec.release(ff)
@@ -494,15 +503,16 @@ class Transformer2D:
     def __call__(self, rec: Recorder, x: FM) -> FM:
         g = self.norm(rec, x, False)
         st = None
-        if self.blocks[0].fused:
+        s = x.h * x.w
+        fused = all(b.use_fused(x.n * s) for b in self.blocks)
+        if fused:
             y, st = self.proj_in(rec, g.tokens(), emit_stats=True)
         else:
             y = self.proj_in(rec, g.tokens())
         rec.release(g)
-        s = x.h * x.w
         for i, blk in enumerate(self.blocks):
-            nxt = i + 1 < len(self.blocks) and self.blocks[i + 1].fused
-            if blk.fused:
+            if fused:
+                nxt = i + 1 < len(self.blocks)
                 r = blk(rec, y, x.n, s, st, emit=nxt)
                 y, st = r if nxt else (r, None)
             else:
