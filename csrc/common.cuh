@@ -247,19 +247,40 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 }
 
 // ---------------------------------------------------------------- small math helpers
-__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
-// exact-GELU 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.26 (|error| < 1.5e-7,
-// far below fp16 resolution): branch-free, two MUFU ops -- libdevice erff costs ~3x the instructions,
-// which matters in epilogues that run once per CTA
+// x * sigmoid(x) with ONE MUFU op (the reciprocal): 2^t is split t = n + f (round to nearest), a cubic gives
+// 2^f (relative error 1e-4, below the fp16 rounding of the result) and n goes straight into the exponent.
+// GroupNorm+SiLU runs this on every feature-map element and B200 retires only 8 MUFU results per clock per SM.
+__device__ __forceinline__ float silu_f(float x) {
+    float t = fminf(fmaxf(x * -1.4426950408889634f, -126.0f), 126.0f);
+    const float r = t + 12582912.0f;  // 1.5 * 2^23: the integer part lands in the low mantissa bits
+    const float f = t - (r - 12582912.0f);
+    float p = fmaf(f, 0.0550093f, 0.24221097f);
+    p = fmaf(p, f, 0.69328285f);
+    p = fmaf(p, f, 1.0f);
+    const float e = __int_as_float(__float_as_int(p) + (__float_as_int(r) << 23));  // e^-x
+    float inv;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f + e));
+    return x * inv;
+}
+// exact-GELU 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.28,
+//   erf(z) = 1 - (1 + a1 z + ... + a6 z^6)^-16   (|error| < 3e-7, far below fp16 resolution):
+// branch-free, ONE MUFU op (the reciprocal) -- libdevice erff costs ~3x the instructions and 7.1.26 needs an
+// exponential as well; ncu showed the XU pipe half busy in the GELU-gated GEMM epilogues.
 __device__ __forceinline__ float gelu_f(float x) {
     const float z = fabsf(x) * 0.70710678118654752f;
-    const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-    float poly = fmaf(1.061405429f, t, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
-    const float erf_abs = 1.0f - poly * t * __expf(-z * z);
-    return 0.5f * x * (1.0f + copysignf(erf_abs, x));
+    float p = fmaf(0.0000430638f, z, 0.0002765672f);
+    p = fmaf(p, z, 0.0001520143f);
+    p = fmaf(p, z, 0.0092705272f);
+    p = fmaf(p, z, 0.0422820123f);
+    p = fmaf(p, z, 0.0705230784f);
+    p = fmaf(p, z, 1.0f);
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(p));
+    t *= t;
+    t *= t;
+    t *= t;
+    t *= t;
+    return 0.5f * x * (1.0f + copysignf(1.0f - t, x));
 }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
     __half2 h = __floats2half2_rn(a, b);
