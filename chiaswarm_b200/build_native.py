@@ -90,5 +90,33 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+def build_trace() -> Path:
+    """Probe build: the same sources with -DSW_TRACE (per-CTA phase stamps in the GEMM kernels, read back with
+    sw_trace_dump) as `_lib/libswarm_sm100_trace.so`.  Load it with SW_NATIVE_LIB=<path> (scripts/trace_igemm.py)."""
+    nvcc = _nvcc()
+    out = LIB_DIR / "libswarm_sm100_trace.so"
+    obj_dir = LIB_DIR / "obj_trace"
+    obj_dir.mkdir(parents=True, exist_ok=True)
+    procs = []
+    for src in sources():
+        obj = obj_dir / (src.stem + ".o")
+        cmd = [nvcc, *NVCC_FLAGS, "-DSW_TRACE", "-I", str(ROOT / "include"), "-c", str(src), "-o", str(obj)]
+        procs.append((obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for obj, p in procs:
+        log, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(log)
+            raise RuntimeError("nvcc failed (trace build)")
+    r = subprocess.run([nvcc, "-shared", "-o", str(out), *[str(o) for o, _ in procs], "-lcudart"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("link failed (trace build)")
+    return out
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--trace" in sys.argv:
+        print(build_trace())
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -126,7 +126,9 @@ def lib() -> C.CDLL:
         return _lib
     with _lock:
         if _lib is None:
-            path = LIB_PATH if LIB_PATH.exists() else build()
+            import os
+
+            path = os.environ.get("SW_NATIVE_LIB") or (LIB_PATH if LIB_PATH.exists() else build())
             l = C.CDLL(str(path))
             l.sw_last_error.restype = C.c_char_p
             for name in (

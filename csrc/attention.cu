@@ -68,7 +68,9 @@ __global__ void __launch_bounds__(kThreads)
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-    const int warp = threadIdx.x >> 5;
+    // (through a shuffle so that ptxas knows the role branches and everything inside them are warp-uniform:
+    // the TMA / MMA loops then run on the uniform datapath instead of R2UR.BROADCAST waterfalls)
+    const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
     const int nslab = p.nslab;
     const int stages = p.kv_stages;
@@ -128,27 +130,32 @@ __global__ void __launch_bounds__(kThreads)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     pdl_trigger();
     pdl_wait();
 
     if (warp == 0) {
-        if (lane == 0) {
-            mbar_expect_tx(q_full, q_tx);
-            for (int sl = 0; sl < nslab; ++sl)
-                tma_load_4d(sQ + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0, b);
+        {
+            // whole warp walks the loop, one elected lane issues
+            if (elect_one()) {
+                mbar_expect_tx(q_full, q_tx);
+                for (int sl = 0; sl < nslab; ++sl)
+                    tma_load_4d(sQ + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0, b);
+            }
             int s = 0;
             uint32_t ph = 0;
             for (int j = 0; j < nkv; ++j) {
                 mbar_wait(&kv_empty[s], ph ^ 1);
-                mbar_expect_tx(&k_full[s], kv_tx);
-                for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sK + s * tile_bytes + sl * SLAB_BYTES, &tmK, &k_full[s], sl * 64,
-                                head, j * BKV, b);
-                mbar_expect_tx(&v_full[s], kv_tx);
-                for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sV + s * tile_bytes + sl * SLAB_BYTES, &tmV, &v_full[s], sl * 64,
-                                head, j * BKV, b);
+                if (elect_one()) {
+                    mbar_expect_tx(&k_full[s], kv_tx);
+                    for (int sl = 0; sl < nslab; ++sl)
+                        tma_load_4d(sK + s * tile_bytes + sl * SLAB_BYTES, &tmK, &k_full[s], sl * 64,
+                                    head, j * BKV, b);
+                    mbar_expect_tx(&v_full[s], kv_tx);
+                    for (int sl = 0; sl < nslab; ++sl)
+                        tma_load_4d(sV + s * tile_bytes + sl * SLAB_BYTES, &tmV, &v_full[s], sl * 64,
+                                    head, j * BKV, b);
+                }
                 if (++s == stages) {
                     s = 0;
                     ph ^= 1;
@@ -156,9 +163,10 @@ __global__ void __launch_bounds__(kThreads)
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // Lean issue loop: this single thread is on the critical path of every KV tile, so all
-            // descriptor halves are precomputed and the K loops are unrolled with predicates.
+        {
+            // Lean issue loop (whole warp, one elected lane -- always the same one -- issues): it is on the
+            // critical path of every KV tile, so all descriptor halves are precomputed and the K loops are
+            // unrolled with predicates.
             const int kq = (p.head_dim + 15) / 16;
             const uint32_t tS = tmem_base;
             const uint32_t tO = tmem_base + O_COL0;
@@ -182,8 +190,10 @@ __global__ void __launch_bounds__(kThreads)
             mbar_wait(q_full, 0);
             mbar_wait(&k_full[0], 0);
             tc_fence_after();
-            issue_qk(k_lo0);
-            umma_commit(s_full);
+            if (elect_one()) {
+                issue_qk(k_lo0);
+                umma_commit(s_full);
+            }
             int s = 0;
             uint32_t ph = 0;
             for (int j = 0; j < nkv; ++j) {
@@ -201,8 +211,10 @@ __global__ void __launch_bounds__(kThreads)
                 if (stages > 1 && j + 1 < nkv) {
                     mbar_wait(&k_full[s1], ph1);
                     tc_fence_after();
-                    issue_qk(k_lo0 + uint32_t(s1) * stage_step);
-                    umma_commit(s_full);
+                    if (elect_one()) {
+                        issue_qk(k_lo0 + uint32_t(s1) * stage_step);
+                        umma_commit(s_full);
+                    }
                 }
                 mbar_wait(&v_full[s], ph);
                 tc_fence_after();
@@ -210,21 +222,25 @@ __global__ void __launch_bounds__(kThreads)
                 const int kp = (kv_valid + 15) >> 4;
                 const uint32_t v_lo = v_lo0 + uint32_t(s) * stage_step;
                 const uint32_t acc0 = j > 0 ? 1u : 0u;
+                if (elect_one()) {
 #pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {
-                    if (kk < kp) {
-                        const uint32_t poff = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
-                        umma_f16_lohi(tO, p_lo + poff, v_lo + uint32_t(kk) * (2048 >> 4), kDescHiSw128, idesc_pv,
-                                      kk > 0 ? 1u : acc0);
+                    for (int kk = 0; kk < 8; ++kk) {
+                        if (kk < kp) {
+                            const uint32_t poff = uint32_t(kk >> 2) * (SLAB_BYTES >> 4) + uint32_t(kk & 3) * 2;
+                            umma_f16_lohi(tO, p_lo + poff, v_lo + uint32_t(kk) * (2048 >> 4), kDescHiSw128, idesc_pv,
+                                          kk > 0 ? 1u : acc0);
+                        }
                     }
+                    umma_commit(&kv_empty[s]);
+                    umma_commit(pv_done);
                 }
-                umma_commit(&kv_empty[s]);
-                umma_commit(pv_done);
                 if (stages == 1 && j + 1 < nkv) {
                     mbar_wait(&k_full[s1], ph1);
                     tc_fence_after();
-                    issue_qk(k_lo0 + uint32_t(s1) * stage_step);
-                    umma_commit(s_full);
+                    if (elect_one()) {
+                        issue_qk(k_lo0 + uint32_t(s1) * stage_step);
+                        umma_commit(s_full);
+                    }
                 }
                 s = s1;
                 ph = ph1;
@@ -403,7 +419,9 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-    const int warp = threadIdx.x >> 5;
+    // (through a shuffle so that ptxas knows the role branches and everything inside them are warp-uniform:
+    // the TMA / MMA loops then run on the uniform datapath instead of R2UR.BROADCAST waterfalls)
+    const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
     const int nslab = p.nslab;
     const int kst = p.k_stages, vst = p.v_stages;
@@ -460,23 +478,25 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     pdl_trigger();
     pdl_wait();
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ---------------- TMA producer
-            mbar_expect_tx(q_full, uint32_t(2 * tile_bytes));
-            for (int t = 0; t < 2; ++t)
-                for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sQ + t * tile_bytes + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0 + t * BQ, b);
+        {
+            // ---------------- TMA producer (whole warp walks the loop, one elected lane issues)
+            if (elect_one()) {
+                mbar_expect_tx(q_full, uint32_t(2 * tile_bytes));
+                for (int t = 0; t < 2; ++t)
+                    for (int sl = 0; sl < nslab; ++sl)
+                        tma_load_4d(sQ + t * tile_bytes + sl * SLAB_BYTES, &tmQ, q_full, sl * 64, head, q0 + t * BQ, b);
+            }
             int sk = 0, sv = 0;
             uint32_t phk = 1, phv = 1;
             const int per_rank = p.world > 1 ? p.s_local / BKV : nkv;
             int jj = p.world > 1 ? p.rank * per_rank : 0;  // local shard first
             int last_src = p.world > 1 ? p.rank : 0;
-            const int epoch = p.epoch + (p.epoch_base ? __ldcg(p.epoch_base) * p.epoch_mul : 0);
+            const int epoch = p.epoch + (p.epoch_base ? __shfl_sync(0xffffffffu, __ldcg(p.epoch_base), 0) * p.epoch_mul : 0);
             for (int j = 0; j < nkv; ++j) {
                 int src = 0, row = jj * BKV;
                 if (p.world > 1) {
@@ -490,17 +510,21 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 const CUtensorMap* mk = tmKs + src;
                 const CUtensorMap* mv = tmVs + src;
                 mbar_wait(&k_empty[sk], phk);
-                mbar_expect_tx(&k_full[sk], uint32_t(tile_bytes));
-                for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sK + sk * tile_bytes + sl * SLAB_BYTES, mk, &k_full[sk], sl * 64, head, row, b);
+                if (elect_one()) {
+                    mbar_expect_tx(&k_full[sk], uint32_t(tile_bytes));
+                    for (int sl = 0; sl < nslab; ++sl)
+                        tma_load_4d(sK + sk * tile_bytes + sl * SLAB_BYTES, mk, &k_full[sk], sl * 64, head, row, b);
+                }
                 if (++sk == kst) {
                     sk = 0;
                     phk ^= 1;
                 }
                 mbar_wait(&v_empty[sv], phv);
-                mbar_expect_tx(&v_full[sv], uint32_t(tile_bytes));
-                for (int sl = 0; sl < nslab; ++sl)
-                    tma_load_4d(sV + sv * tile_bytes + sl * SLAB_BYTES, mv, &v_full[sv], sl * 64, head, row, b);
+                if (elect_one()) {
+                    mbar_expect_tx(&v_full[sv], uint32_t(tile_bytes));
+                    for (int sl = 0; sl < nslab; ++sl)
+                        tma_load_4d(sV + sv * tile_bytes + sl * SLAB_BYTES, mv, &v_full[sv], sl * 64, head, row, b);
+                }
                 if (++sv == vst) {
                     sv = 0;
                     phv ^= 1;
@@ -509,8 +533,9 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ---------------- MMA issuer (lean: precomputed descriptor halves, unrolled K loops)
+        {
+            // ---------------- MMA issuer (lean: precomputed descriptor halves, unrolled K loops; whole warp walks
+            // the loop and one elected lane -- always the same one -- issues the MMAs and their commits)
             const int kq = (p.head_dim + 15) / 16;
             const uint32_t q_lo0 = desc_lo(smem_u32(sQ), 16);
             const uint32_t k_lo0 = desc_lo(smem_u32(sK), 16);
@@ -548,13 +573,17 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             mbar_wait(q_full, 0);
             mbar_wait(&k_full[0], 0);
             tc_fence_after();
-            issue_qk(0, k_lo0);
-            umma_commit(&s_full[0]);
+            if (elect_one()) {
+                issue_qk(0, k_lo0);
+                umma_commit(&s_full[0]);
+            }
             mbar_wait(&s_free[0], 0);  // tile 0 holds S0(0) in registers
             tc_fence_after();
-            issue_qk(1, k_lo0);
-            umma_commit(&s_full[1]);
-            umma_commit(&k_empty[0]);
+            if (elect_one()) {
+                issue_qk(1, k_lo0);
+                umma_commit(&s_full[1]);
+                umma_commit(&k_empty[0]);
+            }
             int sk = (kst > 1) ? 1 : 0;           // ring slot of K[j+1]
             uint32_t phk = (kst > 1) ? 0u : 1u;   // its full-barrier parity
             int sv = 0;
@@ -570,20 +599,26 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                     mbar_wait(&s_free[1], uint32_t(j & 1));
                     mbar_wait(&k_full[sk], phk);
                     tc_fence_after();
-                    issue_qk(0, k_lo);
-                    umma_commit(&s_full[0]);
+                    if (elect_one()) {
+                        issue_qk(0, k_lo);
+                        umma_commit(&s_full[0]);
+                    }
                 }
                 mbar_wait(&p_full[0], uint32_t(j & 1));
                 mbar_wait(&v_full[sv], phv);
                 tc_fence_after();
-                issue_pv(0, v_lo, kp, acc0);
-                umma_commit(&pv_done[0]);
+                if (elect_one()) {
+                    issue_pv(0, v_lo, kp, acc0);
+                    umma_commit(&pv_done[0]);
+                }
                 if (more) {  // tile 0 has copied S0(j+1): tile 1 may start on S1(j+1)
                     mbar_wait(&s_free[0], uint32_t((j + 1) & 1));
                     tc_fence_after();
-                    issue_qk(1, k_lo);
-                    umma_commit(&s_full[1]);
-                    umma_commit(&k_empty[sk]);
+                    if (elect_one()) {
+                        issue_qk(1, k_lo);
+                        umma_commit(&s_full[1]);
+                        umma_commit(&k_empty[sk]);
+                    }
                     if (++sk == kst) {
                         sk = 0;
                         phk ^= 1;
@@ -591,9 +626,11 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 }
                 mbar_wait(&p_full[1], uint32_t(j & 1));
                 tc_fence_after();
-                issue_pv(1, v_lo, kp, acc0);
-                umma_commit(&v_empty[sv]);
-                umma_commit(&pv_done[1]);
+                if (elect_one()) {
+                    issue_pv(1, v_lo, kp, acc0);
+                    umma_commit(&v_empty[sv]);
+                    umma_commit(&pv_done[1]);
+                }
                 if (++sv == vst) {
                     sv = 0;
                     phv ^= 1;

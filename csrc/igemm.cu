@@ -57,6 +57,7 @@ struct IGemmArgs {
     float ln_eps;
     int ptiles, total_tiles;  // persistent kernel: pixel tiles, pixel tiles x column tiles
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
+    int epi_alias;      // lean kernel: the epilogue boxes overlay the drained operand ring (else dedicated)
     int cluster_k;      // splits == 2 and the two splits of a tile form a cluster: partials meet in DSMEM
     int splits;         // split-K factor (grid.z)
     int kb_per_split;   // k-blocks per split
@@ -88,6 +89,36 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
         __nanosleep(64);
     }
 }
+
+// ---------------------------------------------------------------- phase trace (probe builds only)
+// -DSW_TRACE: every CTA stamps clock64 at its phase boundaries into a device array that the probe
+// script reads back (sw_trace_dump); the shipped library is built without it.
+#ifdef SW_TRACE
+constexpr int kTraceSlots = 16;
+constexpr int kTraceCtas = 8192;
+__device__ unsigned long long g_sw_trace[kTraceCtas * kTraceSlots];
+__device__ __forceinline__ void trace_stamp(int slot) {
+    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (cta < unsigned(kTraceCtas)) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+        g_sw_trace[cta * kTraceSlots + slot] = t;
+    }
+}
+__device__ __forceinline__ void trace_stamp_global(int slot) {
+    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (cta < unsigned(kTraceCtas)) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_sw_trace[cta * kTraceSlots + slot] = t;
+    }
+}
+#define TR(slot) trace_stamp(slot)
+#define TRG(slot) trace_stamp_global(slot)
+#else
+#define TR(slot) ((void)0)
+#define TRG(slot) ((void)0)
+#endif
 
 // ---------------------------------------------------------------- raw-address PTX helpers
 // The producer and MMA roles are single threads: every instruction they execute sits on the
@@ -233,11 +264,19 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-    const int warp = threadIdx.x >> 5;
+    // (warp index through a shuffle: ptxas then knows it is warp-uniform, see the note on the role loops)
+    const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
     const int stages = p.stages;
+    if (threadIdx.x == 0) {
+        TR(0);
+        TRG(11);
+    }
     uint32_t cta_rank = 0;
-    if (PAIR) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    if (PAIR) {
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+        cta_rank = __shfl_sync(0xffffffffu, cta_rank, 0);
+    }
     const bool leader = cta_rank == 0;
 
     // (the TMA-store epilogue stages 4 x 16 KB boxes over the drained ring: keep the barriers clear of them)
@@ -301,9 +340,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     tc_fence_before();
     cta_or_cluster_sync<PAIR>();  // (pair: peer barriers must exist before any remote arrive)
     tc_fence_after();
-    const uint32_t tmem_acc = *tmem_slot;
+    const uint32_t tmem_acc = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    if (threadIdx.x == 0) TR(1);
     pdl_trigger();  // the next kernel may start its prologue
     pdl_wait();     // our inputs (and the buffers we overwrite) belong to the previous kernel until here
+    if (threadIdx.x == 0) TR(2);
 
     const int nkb1 = (p.c1 + BK - 1) / BK;
     const int nkb2 = (p.c2 + BK - 1) / BK;
@@ -317,8 +358,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ---------------- TMA producer (lean loop, see note above)
+        {
+            // ---------------- TMA producer (lean loop, see note above).  The whole warp walks the loop with
+            // warp-uniform values and ONE elected lane issues: with the loop under `lane == 0` ptxas treated every
+            // operand as divergent and wrapped each UTMALDG in an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall
+            // (a k-block cost ~565 clocks of issue whatever the tile size: scripts/trace_igemm.py).
             int tap = it_begin / per_tap;
             int j = it_begin - tap * per_tap;
             int ky = tap / p.kw, kx = tap - ky * p.kw;
@@ -328,19 +372,20 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             int s = 0;
             uint32_t ph = 1;
             if (p.mode == 1 && ag_src != p.rank) wait_flag_ge(p.flags[p.rank] + ag_src, p.epoch);
+            if (lane == 0) TR(3);
             for (int it = it_begin; it < it_end; ++it) {
                 bar_wait(eb, ph);
-                // both CTAs' loads complete on the leader's barrier; only the leader arms it
-                if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
-                int kcol;
-                if (j < nkb1) {
-                    tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                    kcol = tapbase + j * BK;
-                } else {
-                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
-                    kcol = tapbase + p.c1 + (j - nkb1) * BK;
+                if (elect_one()) {
+                    // both CTAs' loads complete on the leader's barrier; only the leader arms it
+                    if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
+                    if (j < nkb1) {
+                        tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                        tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                    } else {
+                        tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                        tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                    }
                 }
-                tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, kcol, bcol0);
                 if (++j == per_tap) {
                     j = 0;
                     tapbase += ctot;
@@ -361,11 +406,13 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     eb += 8;
                 }
             }
+            if (lane == 0) TR(4);
         }
         if (!PAIR && p.cluster_k) cluster_sync_all();  // (whole cluster: see the epilogue)
     } else if (warp == 1) {
-        if (lane == 0 && (!PAIR || leader)) {
-            // ---------------- MMA issuer (lean loop)
+        if (!PAIR || leader) {
+            // ---------------- MMA issuer (lean loop; whole warp walks it, one elected lane issues -- the same lane
+            // every time, so the commits track the MMAs)
             // descriptor = {lo: addr>>4 | LBO(16 B)>>4 << 16, hi: SBO(1024 B)>>4 | version 1 | SWIZZLE_128B}
             const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
             const uint32_t a_lo0 = ((smem0 & 0x3FFFFu) >> 4) | (1u << 16);
@@ -383,16 +430,21 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             for (int it = it_begin; it < it_end; ++it) {
                 bar_wait(fb, ph);
                 tc_fence_after();
+#ifdef SW_TRACE
+                if (it == it_begin && lane == 0) TR(5);
+#endif
                 int ksteps = 4;
                 if (j == last1) ksteps = ks1 < 4 ? ks1 : 4;
                 if (nkb2 && j == last2) ksteps = ks2 < 4 ? ks2 : 4;
-                // +32 bytes (2 descriptor units) per 16-element K step inside the 128-byte swizzle row
-                mma_f16<PAIR>(tmem_acc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
-                if (ksteps > 1) mma_f16<PAIR>(tmem_acc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
-                if (ksteps > 2) mma_f16<PAIR>(tmem_acc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
-                if (ksteps > 3) mma_f16<PAIR>(tmem_acc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                if (elect_one()) {
+                    // +32 bytes (2 descriptor units) per 16-element K step inside the 128-byte swizzle row
+                    mma_f16<PAIR>(tmem_acc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
+                    if (ksteps > 1) mma_f16<PAIR>(tmem_acc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
+                    if (ksteps > 2) mma_f16<PAIR>(tmem_acc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
+                    if (ksteps > 3) mma_f16<PAIR>(tmem_acc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                    mma_commit<PAIR>(eb);
+                }
                 acc = 1u;
-                mma_commit<PAIR>(eb);
                 if (++j == per_tap) j = 0;
                 if (++s == stages) {
                     s = 0;
@@ -406,7 +458,8 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     eb += 8;
                 }
             }
-            mma_commit<PAIR>(smem_u32(acc_full));
+            if (elect_one()) mma_commit<PAIR>(smem_u32(acc_full));
+            if (lane == 0) TR(6);
         }
         if (!PAIR && p.cluster_k) cluster_sync_all();
     } else {
@@ -451,9 +504,11 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         }
         float st_sum = 0.0f, st_sq = 0.0f;  // producer side: this row's sums over the tile's columns
 
+        if (threadIdx.x == 64) TR(7);
         if (lane == 0) mbar_wait(acc_full, 0);  // one poller per warp: 128 spinning threads steal issue slots
         __syncwarp();
         tc_fence_after();
+        if (threadIdx.x == 64) TR(8);
         const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
 
         // ---- split-K: every split parks its fp32 tile in scratch, then ALL splits of the tile (they are
@@ -919,6 +974,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         }
     }
 
+    if (threadIdx.x == 64) TR(9);
     if (p.mode == 2) {
         // every CTA publishes its pushes system-wide; the CTA that finishes last raises this
         // rank's epoch flag on every peer (their reduce kernels poll it)
@@ -939,6 +995,23 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
         tc_fence_after();
         tmem_dealloc_any<PAIR>(tmem_acc, uint32_t(p.tmem_cols));
     }
+#ifdef SW_TRACE
+    if (threadIdx.x == 0) {
+        TR(10);
+        TRG(12);
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (cta < unsigned(kTraceCtas)) {
+            g_sw_trace[cta * kTraceSlots + 13] = smid;
+            g_sw_trace[cta * kTraceSlots + 14] = (unsigned long long)p.bn | ((unsigned long long)p.stages << 16) |
+                                                 ((unsigned long long)p.splits << 24) | ((unsigned long long)(PAIR ? 1 : 0) << 32) |
+                                                 ((unsigned long long)p.cluster_k << 33) | ((unsigned long long)p.tma_epi << 34);
+            g_sw_trace[cta * kTraceSlots + 15] = (unsigned long long)gridDim.x | ((unsigned long long)gridDim.y << 20) |
+                                                 ((unsigned long long)gridDim.z << 40);
+        }
+    }
+#endif
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -972,6 +1045,335 @@ __global__ void __launch_bounds__(kThreads)
 }
 
 // =================================================================================================
+// Lean variant: the same tile / ring / TMEM design for the one epilogue that almost every layer of a UNet step
+// uses -- bias (+ the per-image time-embedding bias when the tile lies in one image) (+ residual), fp16 out
+// through swizzled staging boxes and TMA stores -- and nothing else.  scripts/trace_igemm.py (per-CTA clock
+// stamps) showed where a small GEMM spends its life in the general kernel above: ~1500 clocks of set-up, ~600
+// from the dependency wait to the first TMA (integer divisions), ~1000 of first-load latency, a main loop paced
+// by the issuing threads, and an epilogue of ~5600-6900 clocks for a 128x128 tile -- half of the kernel --
+// because one warp per scheduler walks ~1400 SASS instructions per 32 columns of a 127 KB kernel image whose
+// every line is an instruction-cache miss in a kernel that lives for microseconds.  Here all run-time epilogue
+// choices are template parameters or gone, everything that does not touch global memory is computed before the
+// dependency wait, and (when the grid is a single wave anyway) the residual tile gets its own staging boxes so
+// its TMA loads are issued before the main loop instead of after it.
+template <bool PAIR, bool HAS_RES>
+__device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const CUtensorMap& tmA2,
+                                                const CUtensorMap& tmB, const CUtensorMap& tmOut,
+                                                const CUtensorMap& tmRes, const CUtensorMap& tmOut32,
+                                                const IGemmArgs& p) {
+    const int BN = p.bn;
+    const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
+    const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    __shared__ __align__(16) float s_bias[256];
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0);
+    const int lane = threadIdx.x & 31;
+    const int stages = p.stages;
+    if (threadIdx.x == 0) {
+        TR(0);
+        TRG(11);
+    }
+    uint32_t cta_rank = 0;
+    if (PAIR) {
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+        cta_rank = __shfl_sync(0xffffffffu, cta_rank, 0);
+    }
+    const bool leader = cta_rank == 0;
+
+    // shared memory: operand ring | epilogue boxes (out[2], res[2]; they alias the drained ring when
+    // p.epi_alias) | barriers
+    const int ring_only = stages * STAGE_BYTES;
+    const int ring_bytes = p.epi_alias ? (ring_only < 65536 ? 65536 : ring_only) : ring_only;
+    const int box_off = p.epi_alias ? 0 : ring_bytes;
+    const int bars_off = p.epi_alias ? ring_bytes : ring_bytes + (HAS_RES ? 65536 : 32768);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + bars_off);
+    uint64_t* empty = full + stages;
+    uint64_t* acc_full = empty + stages;
+    uint64_t* res_full = acc_full + 1;  // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA1);
+        tma_prefetch_desc(&tmA2);
+        tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmOut);
+        if (HAS_RES) tma_prefetch_desc(&tmRes);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < stages; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], 1);
+            }
+            mbar_init(acc_full, 1);
+            mbar_init(&res_full[0], 1);
+            mbar_init(&res_full[1], 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc_any<PAIR>(tmem_slot, uint32_t(p.tmem_cols));
+    }
+
+    // ---- everything that needs no global memory comes before the dependency wait
+    int t = blockIdx.x;
+    const int tx = t % p.tiles_x;
+    t /= p.tiles_x;
+    const int ty = t % p.tiles_y;
+    const int tn = t / p.tiles_y;
+    const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+    const int col0 = blockIdx.y * BN;
+    const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
+    const int nkb1 = (p.c1 + BK - 1) / BK;
+    const int nkb2 = (p.c2 + BK - 1) / BK;
+    const int per_tap = nkb1 + nkb2;
+    const int ctot = p.c1 + p.c2;
+    const int total_kb = p.kh * p.kw * per_tap;
+    const uint32_t a_bytes = uint32_t(p.bw * p.bh * p.bi) * (BK * 2);
+    const uint32_t smem0 = smem_u32(smem);
+    const uint32_t full0 = smem_u32(full), empty0 = smem_u32(empty);
+    const uint32_t out_stage = smem0 + uint32_t(box_off);
+    const uint32_t res_stage = out_stage + 32768u;
+    const uint32_t rfull0 = smem_u32(res_full);
+    int nvalid = p.cout - col0;
+    if (nvalid > BN) nvalid = BN;
+    const int cend = (nvalid + 31) & ~31;
+    const int nslab = (nvalid + 63) >> 6;
+
+    tc_fence_before();
+    cta_or_cluster_sync<PAIR>();
+    tc_fence_after();
+    const uint32_t tmem_acc = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    if (threadIdx.x == 0) TR(1);
+    pdl_trigger();
+    pdl_wait();
+    if (threadIdx.x == 0) TR(2);
+
+    if (warp == 0) {
+        // ---------------- TMA producer: the whole warp walks the loop, one elected lane issues
+        int j = 0, ky = 0, kx = 0, tapbase = 0;
+        const uint32_t tx_bytes = (PAIR ? 2u : 1u) * (a_bytes + uint32_t(B_STAGE_BYTES));
+        uint32_t sa = smem0, fb = full0, eb = empty0;
+        int s = 0;
+        uint32_t ph = 1;
+        if (lane == 0) TR(3);
+        for (int it = 0; it < total_kb; ++it) {
+            bar_wait(eb, ph);
+            if (elect_one()) {
+                if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
+                if (j < nkb1) {
+                    tma4<PAIR>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                    tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                } else {
+                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                    tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                }
+            }
+            if (++j == per_tap) {
+                j = 0;
+                tapbase += ctot;
+                if (++kx == p.kw) {
+                    kx = 0;
+                    ++ky;
+                }
+            }
+            if (++s == stages) {
+                s = 0;
+                ph ^= 1;
+                sa = smem0;
+                fb = full0;
+                eb = empty0;
+            } else {
+                sa += STAGE_BYTES;
+                fb += 8;
+                eb += 8;
+            }
+        }
+        if (lane == 0) TR(4);
+    } else if (warp == 1) {
+        if (!PAIR || leader) {
+            // ---------------- MMA issuer (whole warp walks the loop; the same elected lane issues MMAs and commits)
+            const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((smem0 & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_off = uint32_t(A_STAGE_BYTES) >> 4;
+            const uint32_t stage_step = uint32_t(STAGE_BYTES) >> 4;
+            const int ks1 = (p.c1 - (nkb1 - 1) * BK + 15) / 16;
+            const int ks2 = nkb2 ? (p.c2 - (nkb2 - 1) * BK + 15) / 16 : 4;
+            const int last1 = nkb1 - 1, last2 = per_tap - 1;
+            int j = 0;
+            uint32_t a_lo = a_lo0, fb = full0, eb = empty0;
+            int s = 0;
+            uint32_t ph = 0, acc = 0;
+            const uint32_t idesc = p.idesc;
+            for (int it = 0; it < total_kb; ++it) {
+                bar_wait(fb, ph);
+                tc_fence_after();
+#ifdef SW_TRACE
+                if (it == 0 && lane == 0) TR(5);
+#endif
+                int ksteps = 4;
+                if (j == last1) ksteps = ks1 < 4 ? ks1 : 4;
+                if (nkb2 && j == last2) ksteps = ks2 < 4 ? ks2 : 4;
+                if (elect_one()) {
+                    mma_f16<PAIR>(tmem_acc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
+                    if (ksteps > 1) mma_f16<PAIR>(tmem_acc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
+                    if (ksteps > 2) mma_f16<PAIR>(tmem_acc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
+                    if (ksteps > 3) mma_f16<PAIR>(tmem_acc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                    mma_commit<PAIR>(eb);
+                }
+                acc = 1u;
+                if (++j == per_tap) j = 0;
+                if (++s == stages) {
+                    s = 0;
+                    ph ^= 1;
+                    a_lo = a_lo0;
+                    fb = full0;
+                    eb = empty0;
+                } else {
+                    a_lo += stage_step;
+                    fb += 8;
+                    eb += 8;
+                }
+            }
+            if (elect_one()) mma_commit<PAIR>(smem_u32(acc_full));
+            if (lane == 0) TR(6);
+        }
+    } else {
+        // ---------------- epilogue: one thread per accumulator row
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const bool lead = threadIdx.x == 64;
+        const bool tail32 = (cend & 63) == 32;  // last slab is 32 columns wide: staged unswizzled, own tensor map
+        // the residual boxes do not alias the ring: fetch the first two slabs while the main loop runs
+        if (HAS_RES && !p.epi_alias && lead) {
+            for (int sl = 0; sl < 2 && sl < nslab; ++sl) {
+                bar_expect_tx(rfull0 + 8 * sl, a_bytes);
+                tma4<false>(res_stage + sl * 16384, &tmRes, rfull0 + 8 * sl, col0 + sl * 64, x0, y0, n0);
+            }
+        }
+        // per-column addends (bias, plus the time-embedding row bias: the host only picks this kernel when a
+        // tile lies within one image) go to shared memory while the main loop runs
+        for (int i = threadIdx.x - 64; i < BN; i += 128) {
+            const int col = col0 + i;
+            float b = 0.0f;
+            if (col < p.cout) {
+                if (p.bias) b = __half2float(p.bias[col]);
+                if (p.row_bias && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
+            }
+            s_bias[i] = b;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) TR(7);
+        if (lane == 0) mbar_wait(acc_full, 0);
+        __syncwarp();
+        tc_fence_after();
+        if (threadIdx.x == 64) TR(8);
+        if (HAS_RES && p.epi_alias && lead) {  // the boxes overlay the ring: every MMA has retired by now
+            for (int sl = 0; sl < 2 && sl < nslab; ++sl) {
+                bar_expect_tx(rfull0 + 8 * sl, a_bytes);
+                tma4<false>(res_stage + sl * 16384, &tmRes, rfull0 + 8 * sl, col0 + sl * 64, x0, y0, n0);
+            }
+        }
+        const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
+        const uint32_t row_off = uint32_t(r) * 128u, swz = uint32_t(r) & 7u;
+        uint32_t vn[32];
+        tmem_ld32(trow, vn);
+#pragma unroll 1
+        for (int c = 0; c < cend; c += 32) {
+            const int sl = c >> 6;
+            const uint32_t box = uint32_t(sl & 1) * 16384u;
+            if ((c & 63) == 0) {
+                if (sl >= 2) {  // the store issued two slabs ago must have finished reading this box
+                    if (lead) bulk_wait_read<1>();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+                if (HAS_RES) bar_wait(rfull0 + 8 * (sl & 1), uint32_t(sl >> 1) & 1u);
+            }
+            uint32_t v[32];
+            tmem_ld_wait_dep(vn);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = vn[j];
+            if (c + 32 < cend) tmem_ld32(trow + c + 32, vn);
+            const bool tail_slab = tail32 && sl == nslab - 1;
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+                const int c8 = c + g8 * 8;
+                const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c8]);
+                const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c8 + 4]);
+                float f0 = __uint_as_float(v[g8 * 8 + 0]) + b0.x, f1 = __uint_as_float(v[g8 * 8 + 1]) + b0.y;
+                float f2 = __uint_as_float(v[g8 * 8 + 2]) + b0.z, f3 = __uint_as_float(v[g8 * 8 + 3]) + b0.w;
+                float f4 = __uint_as_float(v[g8 * 8 + 4]) + b1.x, f5 = __uint_as_float(v[g8 * 8 + 5]) + b1.y;
+                float f6 = __uint_as_float(v[g8 * 8 + 6]) + b1.z, f7 = __uint_as_float(v[g8 * 8 + 7]) + b1.w;
+                const uint32_t off = box + row_off + (((uint32_t(c8 >> 3) & 7u) ^ swz) << 4);
+                if (HAS_RES) {
+                    const uint4 rv = lds128(res_stage + off);
+                    const float2 r0 = unpack_h2(rv.x), r1 = unpack_h2(rv.y), r2 = unpack_h2(rv.z), r3 = unpack_h2(rv.w);
+                    f0 += r0.x, f1 += r0.y, f2 += r1.x, f3 += r1.y;
+                    f4 += r2.x, f5 += r2.y, f6 += r3.x, f7 += r3.y;
+                }
+                const uint32_t dst = tail_slab ? out_stage + box + uint32_t(r) * 64u + ((uint32_t(c8 >> 3) & 3u) << 4)
+                                               : out_stage + off;
+                sts128(dst, make_uint4(pack_h2(f0, f1), pack_h2(f2, f3), pack_h2(f4, f5), pack_h2(f6, f7)));
+            }
+            if ((c & 63) == 32 || c + 32 >= cend) {
+                fence_proxy_async_smem();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (lead) {
+                    tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + sl * 64, x0, y0, n0);
+                    bulk_commit();
+                    if (HAS_RES && sl + 2 < nslab) {
+                        bar_expect_tx(rfull0 + 8 * (sl & 1), a_bytes);
+                        tma4<false>(res_stage + box, &tmRes, rfull0 + 8 * (sl & 1), col0 + (sl + 2) * 64, x0, y0, n0);
+                    }
+                }
+            }
+        }
+        if (lead) bulk_wait_read<0>();
+    }
+    if (threadIdx.x == 64) TR(9);
+    tc_fence_before();
+    cta_or_cluster_sync<PAIR>();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_any<PAIR>(tmem_acc, uint32_t(p.tmem_cols));
+    }
+#ifdef SW_TRACE
+    if (threadIdx.x == 0) {
+        TR(10);
+        TRG(12);
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        if (cta < unsigned(kTraceCtas)) {
+            g_sw_trace[cta * kTraceSlots + 13] = smid;
+            g_sw_trace[cta * kTraceSlots + 14] = (unsigned long long)p.bn | ((unsigned long long)p.stages << 16) | (1ull << 24) |
+                                                 ((unsigned long long)(PAIR ? 1 : 0) << 32) | (1ull << 34) | (1ull << 36) |
+                                                 ((unsigned long long)p.epi_alias << 37);
+            g_sw_trace[cta * kTraceSlots + 15] = (unsigned long long)gridDim.x | ((unsigned long long)gridDim.y << 20) |
+                                                 ((unsigned long long)gridDim.z << 40);
+        }
+    }
+#endif
+}
+
+#define SW_LEAN_KERNEL(NAME, PAIR, RES)                                                                            \
+    __global__ void __launch_bounds__(kThreads)                                                                    \
+        NAME(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,                   \
+             const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,                   \
+             const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut32,               \
+             const IGemmArgs p) {                                                                                  \
+        igemm_lean_body<PAIR, RES>(tmA1, tmA2, tmB, tmOut, tmRes, tmOut32, p);                                     \
+    }
+SW_LEAN_KERNEL(k_igemm_lean, false, false)
+SW_LEAN_KERNEL(k_igemm_lean_r, false, true)
+SW_LEAN_KERNEL(k_igemm2_lean, true, false)
+SW_LEAN_KERNEL(k_igemm2_lean_r, true, true)
+#undef SW_LEAN_KERNEL
+
+// =================================================================================================
 // Persistent variant (mode 0, single-CTA tiles, no split-K): each CTA walks tiles
 // blockIdx.x, blockIdx.x + gridDim.x, ... with TWO accumulators in TMEM.  The kernel above pays its
 // prologue (barrier init, TMEM allocation, first TMA round trip) and its epilogue once per tile with
@@ -1001,9 +1403,13 @@ __global__ void __launch_bounds__(kThreads)
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
     const int stages = p.stages;
+    if (threadIdx.x == 0) {
+        TR(0);
+        TRG(11);
+    }
     const int ring_bytes = stages * STAGE_BYTES;
     const int stage_area = p.tma_epi ? 65536 : 0;  // out[2] + res[2] boxes of 16 KB
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + ring_bytes + stage_area);
@@ -1042,9 +1448,11 @@ __global__ void __launch_bounds__(kThreads)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    if (threadIdx.x == 0) TR(1);
     pdl_trigger();
     pdl_wait();
+    if (threadIdx.x == 0) TR(2);
 
     const int nkb1 = (p.c1 + BK - 1) / BK;
     const int nkb2 = (p.c2 + BK - 1) / BK;
@@ -1058,12 +1466,13 @@ __global__ void __launch_bounds__(kThreads)
     const int total_tiles = p.total_tiles;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ---------------- TMA producer
+        {
+            // ---------------- TMA producer (whole warp walks the loop, one elected lane issues)
             const uint32_t tx_bytes = a_bytes + uint32_t(B_STAGE_BYTES);
             uint32_t sa = smem0, fb = full0, eb = empty0;
             int s = 0;
             uint32_t ph = 1;
+            if (lane == 0) TR(3);
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const int nt = tile / ptiles;
                 int t = tile - nt * ptiles;
@@ -1076,16 +1485,16 @@ __global__ void __launch_bounds__(kThreads)
                 int j = 0, ky = 0, kx = 0, tapbase = 0;
                 for (int it = 0; it < total_kb; ++it) {
                     bar_wait(eb, ph);
-                    bar_expect_tx(fb, tx_bytes);
-                    int kcol;
-                    if (j < nkb1) {
-                        tma4<false>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                        kcol = tapbase + j * BK;
-                    } else {
-                        tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
-                        kcol = tapbase + p.c1 + (j - nkb1) * BK;
+                    if (elect_one()) {
+                        bar_expect_tx(fb, tx_bytes);
+                        if (j < nkb1) {
+                            tma4<false>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                            tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                        } else {
+                            tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                            tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                        }
                     }
-                    tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, kcol, bcol0);
                     if (++j == per_tap) {
                         j = 0;
                         tapbase += ctot;
@@ -1107,10 +1516,11 @@ __global__ void __launch_bounds__(kThreads)
                     }
                 }
             }
+            if (lane == 0) TR(4);
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ---------------- MMA issuer
+        {
+            // ---------------- MMA issuer (whole warp, one elected lane issues)
             const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
             const uint32_t a_lo0 = ((smem0 & 0x3FFFFu) >> 4) | (1u << 16);
             const uint32_t b_off = uint32_t(A_STAGE_BYTES) >> 4;
@@ -1134,15 +1544,20 @@ __global__ void __launch_bounds__(kThreads)
                 for (int it = 0; it < total_kb; ++it) {
                     bar_wait(fb, ph);
                     tc_fence_after();
+#ifdef SW_TRACE
+                    if (it == 0 && i == 0 && lane == 0) TR(5);
+#endif
                     int ksteps = 4;
                     if (j == last1) ksteps = ks1 < 4 ? ks1 : 4;
                     if (nkb2 && j == last2) ksteps = ks2 < 4 ? ks2 : 4;
-                    mma_f16<false>(tacc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
-                    if (ksteps > 1) mma_f16<false>(tacc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
-                    if (ksteps > 2) mma_f16<false>(tacc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
-                    if (ksteps > 3) mma_f16<false>(tacc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                    if (elect_one()) {
+                        mma_f16<false>(tacc, a_lo, a_lo + b_off, desc_hi, idesc, acc);
+                        if (ksteps > 1) mma_f16<false>(tacc, a_lo + 2, a_lo + b_off + 2, desc_hi, idesc, 1u);
+                        if (ksteps > 2) mma_f16<false>(tacc, a_lo + 4, a_lo + b_off + 4, desc_hi, idesc, 1u);
+                        if (ksteps > 3) mma_f16<false>(tacc, a_lo + 6, a_lo + b_off + 6, desc_hi, idesc, 1u);
+                        mma_commit<false>(eb);
+                    }
                     acc = 1u;
-                    mma_commit<false>(eb);
                     if (++j == per_tap) j = 0;
                     if (++s == stages) {
                         s = 0;
@@ -1156,8 +1571,9 @@ __global__ void __launch_bounds__(kThreads)
                         eb += 8;
                     }
                 }
-                mma_commit<false>(accf0 + 8 * ab);
+                if (elect_one()) mma_commit<false>(accf0 + 8 * ab);
             }
+            if (lane == 0) TR(6);
         }
     } else {
         // ---------------- epilogue: one thread per accumulator row
@@ -1449,6 +1865,7 @@ __global__ void __launch_bounds__(kThreads)
             }
         }
         if (lead) bulk_wait_read<0>();
+        if (lead) TR(9);
     }
 
     tc_fence_before();
@@ -1457,6 +1874,20 @@ __global__ void __launch_bounds__(kThreads)
         tc_fence_after();
         tmem_dealloc_any<false>(tmem_base, uint32_t(2 * p.tmem_cols));
     }
+#ifdef SW_TRACE
+    if (threadIdx.x == 0) {
+        TR(10);
+        TRG(12);
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        if (blockIdx.x < unsigned(kTraceCtas)) {
+            g_sw_trace[blockIdx.x * kTraceSlots + 13] = smid;
+            g_sw_trace[blockIdx.x * kTraceSlots + 14] = (unsigned long long)p.bn | ((unsigned long long)p.stages << 16) |
+                                                        (1ull << 24) | (1ull << 35) | ((unsigned long long)p.tma_epi << 34);
+            g_sw_trace[blockIdx.x * kTraceSlots + 15] = (unsigned long long)gridDim.x | (1ull << 20) | (1ull << 40);
+        }
+    }
+#endif
 }
 
 // Choose the pixel box (bw x bh x bi, <= 128 pixels) that wastes the fewest MMA rows.
@@ -1802,6 +2233,56 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     } else {
         tOut = tRes = tOut32 = tB;
     }
+    // ---- lean kernel (see igemm_lean_body): plain bias / row bias / residual epilogue, no split, no folded
+    // LayerNorm -- most layers of a step
+    {
+        static int env_lean = -1;  // SW_IGEMM_LEAN=0 keeps the general kernel (A/B runs)
+        if (env_lean < 0) {
+            const char* e = getenv("SW_IGEMM_LEAN");
+            env_lean = e ? atoi(e) : 1;
+        }
+        const bool lean_ok = mode == 0 && a.splits == 1 && !a.cluster_k && a.tma_epi && p->act == SW_ACT_NONE &&
+                             a.out_scale == 1.0f && (!p->row_bias || a.bi == 1) && !ln_fused && p->persist != 2;
+        if (env_lean && lean_ok) {
+            const int boxes = p->residual ? 65536 : 32768;
+            // a grid of at most one CTA per SM gains nothing from a second resident CTA: give the epilogue its own
+            // staging boxes (residual prefetched under the main loop) and the ring every remaining byte
+            a.epi_alias = ctas > long(sms) ? 1 : 0;
+            int st = a.stages;
+            if (!a.epi_alias) {
+                st = (225 * 1024 - 1024 - 512 - boxes) / stage_bytes;
+                if (st > 8) st = 8;
+                if (p->stages > 0 && p->stages < st) st = p->stages;
+                if (st > kblocks) st = kblocks;
+                if (st < 1) st = 1;
+            }
+            a.stages = st;
+            const int ring = a.epi_alias ? (st * stage_bytes < 65536 ? 65536 : st * stage_bytes) : st * stage_bytes + boxes;
+            const int smem = ring + 1024 + 512;
+            static bool configured[64] = {false};
+            int dev = 0;
+            SW_CUDA_OK(cudaGetDevice(&dev));
+            if (dev < 64 && !configured[dev]) {
+                SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_lean, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_lean_r, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2_lean, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                SW_CUDA_OK(cudaFuncSetAttribute(k_igemm2_lean_r, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+                configured[dev] = true;
+            }
+            const int ntile = (a.cout + a.bn - 1) / a.bn;
+            cudaStream_t st_ = static_cast<cudaStream_t>(stream);
+            if (!pair) {
+                auto kern = p->residual ? k_igemm_lean_r : k_igemm_lean;
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3(grid_x, ntile, 1), dim3(kThreads), size_t(smem), st_, 1, tA1, tA2, tB,
+                                           tOut, tRes, tOut32, a));
+            } else {
+                auto kern = p->residual ? k_igemm2_lean_r : k_igemm2_lean;
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3((grid_x + 1) / 2 * 2, ntile, 1), dim3(kThreads), size_t(smem), st_, 2,
+                                           tA1, tA2, tB, tOut, tRes, tOut32, a));
+            }
+            return 0;
+        }
+    }
     // ---- persistent kernel (see k_igemm_p): worth it once a CTA would get more than one tile
     if (mode == 0 && !pair && a.splits == 1 && (!ln_fused || (p->act == SW_ACT_GEGLU && !p->row_stats_out))) {
         static int env_persist = -1;  // SW_IGEMM_PERSIST: 0 never, 1 auto (default), 2 whenever possible
@@ -1890,4 +2371,18 @@ extern "C" int sw_igemm_ag(const sw_igemm_params* p, const sw_peers* peers, int 
 extern "C" int sw_igemm_rs(const sw_igemm_params* p, const sw_peers* peers, int m_local,
                            unsigned int* ticket, void* stream) {
     return igemm_impl(p, peers, 2, m_local, ticket, stream);
+}
+
+// Probe builds (-DSW_TRACE) only: copies the per-CTA phase stamps of the last launches to the host.
+extern "C" int sw_trace_dump(unsigned long long* host, int ctas) {
+#ifdef SW_TRACE
+    if (!host || ctas <= 0 || ctas > kTraceCtas) return swh::fail(-1, "sw_trace_dump: bad arguments");
+    SW_CUDA_OK(cudaDeviceSynchronize());
+    SW_CUDA_OK(cudaMemcpyFromSymbol(host, g_sw_trace, size_t(ctas) * kTraceSlots * sizeof(unsigned long long)));
+    return 0;
+#else
+    (void)host;
+    (void)ctas;
+    return swh::fail(-1, "sw_trace_dump: library built without SW_TRACE");
+#endif
 }

@@ -645,7 +645,7 @@ int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamm
 // sw_groupnorm_scratch_floats() floats.
 static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                      int n, int hw, int c1, int c2, int groups, float eps, int silu,
-                     float* scratch, cudaStream_t st, const sw_peers* peers, bool scratch_zeroed) {
+                     float* scratch, cudaStream_t st, const sw_peers* peers) {
     const int c = c1 + c2;
     GnDist dist;
     memset(&dist, 0, sizeof(dist));
@@ -678,7 +678,6 @@ static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, 
                 SW_CUDA_OK(cudaFuncSetAttribute(k_gn_fused, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
                 configured[dev] = true;
             }
-            (void)scratch_zeroed;
             SW_CUDA_OK(swh::launch_pdl(k_gn_fused, dim3(f.cluster, n, f.slices), dim3(f.threads), f.smem, st, f.cluster,
                                        static_cast<const __half*>(x), static_cast<const __half*>(x2), c1,
                                        static_cast<__half*>(y), static_cast<const __half*>(gamma),
@@ -706,7 +705,7 @@ static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, 
 int sw_groupnorm_launch(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                         int n, int hw, int c1, int c2, int groups, float eps, int silu,
                         float* scratch, cudaStream_t st, const sw_peers* peers) {
-    return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, scratch, st, peers, false);
+    return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, scratch, st, peers);
 }
 
 extern "C" int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma,
@@ -714,7 +713,7 @@ extern "C" int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const v
                                  float eps, int silu, float* stats_scratch, void* stream) {
     if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc: null argument");
     return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, stats_scratch,
-                     static_cast<cudaStream_t>(stream), nullptr, false);
+                     static_cast<cudaStream_t>(stream), nullptr);
 }
 
 extern "C" int sw_groupnorm_nhwc_zeroed(const void* x, const void* x2, void* y, const void* gamma,
@@ -722,7 +721,7 @@ extern "C" int sw_groupnorm_nhwc_zeroed(const void* x, const void* x2, void* y, 
                                         float eps, int silu, float* stats_scratch, void* stream) {
     if (!x || !y || !stats_scratch) return swh::fail(-1, "sw_groupnorm_nhwc_zeroed: null argument");
     return gn_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu, stats_scratch,
-                     static_cast<cudaStream_t>(stream), nullptr, true);
+                     static_cast<cudaStream_t>(stream), nullptr);
 }
 
 extern "C" int sw_groupnorm_nhwc_dist(const void* x, const void* x2, void* y, const void* gamma,

@@ -179,9 +179,15 @@ int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpeers, const 
  * reference call site swarm/diffusion/diffusion_func.py:96).
  * The input is the channel-concatenation of x [n,hw,c1] and x2 [n,hw,c2] (x2 may be NULL with
  * c2 = 0): the UNet skip-concat is normalised without being materialised.  y: [n,hw,c1+c2];
- * gamma/beta fp16 [c1+c2].  A statistics kernel writes per-CTA partial sums to `stats_scratch`
- * and the last CTA of each image folds them in a fixed order (bit-reproducible: no floating-point
- * atomics); an apply kernel normalises.  Both stream an L2-resident tensor once.
+ * gamma/beta fp16 [c1+c2].  Two paths, chosen per shape (sw_groupnorm_kernel_count tells which):
+ *  1 launch : an image (or a slice of whole groups of it) fits the shared memory of a cluster of
+ *             <= 16 CTAs: rows are parked in shared memory, partial sums meet through distributed
+ *             shared memory behind one cluster barrier, the apply pass reads shared memory.  This
+ *             path touches no scratch at all.
+ *  2 launches: a statistics kernel writes per-CTA partial sums to `stats_scratch` and the last CTA
+ *             of each image (ticket counter in the scratch, cleared by a memset node on `stream`
+ *             before the launch) folds them in a fixed order; an apply kernel normalises.
+ * Both are bit-reproducible (no floating-point atomics).
  * `stats_scratch` is caller-owned fp32 memory of sw_groupnorm_scratch_floats(n,hw,c,groups)
  * floats; its contents need no initialisation. */
 int64_t sw_groupnorm_scratch_floats(int n, int hw, int c, int groups);
@@ -190,11 +196,8 @@ int sw_groupnorm_kernel_count(int n, int hw, int c, int groups);
 int sw_groupnorm_nhwc(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                       int n, int hw, int c1, int c2, int groups, float eps, int silu,
                       float* stats_scratch, void* stream);
-/* Same operation for callers that zero `stats_scratch` ONCE when they allocate it (the engine's
- * plan recorder): tensors that fit in the SMs' shared memory (every GroupNorm of the UNets) then run
- * as a single launch -- rows parked in shared memory, grid-wide barrier on two scratch words that
- * the kernel returns to zero, deterministic fold, apply from shared memory -- with no memset node.
- * sw_groupnorm_nhwc takes the same single-launch path but clears those words first. */
+/* Alias of sw_groupnorm_nhwc kept for callers of the first release (its scratch-pre-zeroed fast
+ * path was replaced by the scratch-free cluster kernel described above). */
 int sw_groupnorm_nhwc_zeroed(const void* x, const void* x2, void* y, const void* gamma, const void* beta,
                              int n, int hw, int c1, int c2, int groups, float eps, int silu,
                              float* stats_scratch, void* stream);

@@ -4,9 +4,13 @@ latency-critical path where cudaMalloc/cudaFree are forbidden because they can s
 
 The entry point is driven through the C ABI with ctypes, exactly as such a caller would, and its
 output is compared with the regular entry point (caller-provided scratch) on two back-to-back
-calls: the second call runs on the scratch contents the first one left behind, which is the
-situation the built-in buffer is always in.  The file name sorts last on purpose, so a failure
-here cannot hide results of the other GPU tests in a stop-at-first-failure run.
+calls.  The shapes cover both launch paths: small feature maps run the single-launch cluster
+kernel (which needs no scratch at all), while a 256x256 map and a 128-group norm fall to the
+statistics + apply kernels -- those are the calls that really read and write the built-in array,
+and their second call runs on the numbers and ticket counters the first one left behind, which
+is the situation that buffer is always in.  For them the result is also checked against
+torch.nn.functional.group_norm evaluated in fp32.  The file name sorts last on purpose, so a
+failure here cannot hide results of the other GPU tests in a stop-at-first-failure run.
 """
 import ctypes as C
 
@@ -33,11 +37,16 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
-@pytest.mark.parametrize("n,hw,c1,c2,groups,silu", [(2, 4096, 320, 0, 32, True), (2, 256, 1280, 640, 32, False)])
-def test_static_scratch_groupnorm_matches_regular_entry_point(n, hw, c1, c2, groups, silu):
+@pytest.mark.parametrize("n,hw,c1,c2,groups,silu,kernels", [
+    (2, 4096, 320, 0, 32, True, 1), (2, 256, 1280, 640, 32, False, 1),
+    # two-kernel path = the calls that use the built-in scratch array
+    (1, 65536, 256, 0, 32, True, 2), (2, 4096, 512, 512, 128, False, 2)])
+def test_static_scratch_groupnorm_matches_regular_entry_point(n, hw, c1, c2, groups, silu, kernels):
     native, lib, fn = _lib()
     torch.manual_seed(21)
     c = c1 + c2
+    assert lib.sw_groupnorm_kernel_count(n, hw, c, groups) == kernels
+    assert native.groupnorm_scratch_floats(n, hw, c, groups) <= MAX_FLOATS
     gamma = torch.randn(c, device="cuda", dtype=torch.float16)
     beta = torch.randn(c, device="cuda", dtype=torch.float16)
     stream = torch.cuda.current_stream().cuda_stream
@@ -53,6 +62,13 @@ def test_static_scratch_groupnorm_matches_regular_entry_point(n, hw, c1, c2, gro
         torch.cuda.synchronize()
         assert torch.isfinite(got.float()).all()
         assert (got.float() - want.float()).abs().max().item() < 2e-2
+        if kernels == 2:
+            xin = (x1 if x2 is None else torch.cat([x1, x2], dim=-1)).float()
+            ref = torch.nn.functional.group_norm(xin.transpose(1, 2), groups, gamma.float(), beta.float(), 1e-5)
+            if silu:
+                ref = torch.nn.functional.silu(ref)
+            err = (got.float() - ref.transpose(1, 2)).abs().max().item()
+            assert err < 3e-2, err
 
 
 def test_static_scratch_groupnorm_rejects_oversized_problems():
