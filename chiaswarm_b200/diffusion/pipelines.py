@@ -167,7 +167,19 @@ class StableDiffusionPipeline:
         tok2 = load_tokenizer(root / "tokenizer_2", te2.config["vocab_size"]) if te2 is not None else None
         sched = checkpoints.component_config(root, "scheduler") or schedulers.SD_SCHEDULER_CONFIG
         fam = family or _family_of_class(index.get("_class_name", "StableDiffusionPipeline"))
-        return cls(unet, vae, te, tok, sched, index, te2, tok2, controlnet, fam)
+        pipe = cls(unet, vae, te, tok, sched, index, te2, tok2, controlnet, fam)
+        # safety checker (K12): loaded whenever model_index.json lists one and its folder is present
+        entry = index.get("safety_checker")
+        if isinstance(entry, (list, tuple)) and entry and entry[-1] and (root / "safety_checker").is_dir():
+            from .safety_checker import ClipImageProcessor, SafetyChecker, StableDiffusionSafetyChecker
+
+            checker = module("safety_checker", StableDiffusionSafetyChecker)
+            pre = checkpoints.read_json(root / "feature_extractor" / "preprocessor_config.json") \
+                if (root / "feature_extractor" / "preprocessor_config.json").is_file() else {}
+            pipe.safety_checker = SafetyChecker(checker, ClipImageProcessor(**{k: v for k, v in pre.items()
+                                                                               if k in ("size", "crop_size", "image_mean",
+                                                                                        "image_std")}))
+        return pipe
 
     def to(self, device, dtype=None):
         self.device = torch.device(device)
@@ -176,6 +188,8 @@ class StableDiffusionPipeline:
         for m in (self.unet, self.vae, self.text_encoder, self.text_encoder_2, self.controlnet):
             if m is not None:
                 m.to(self.device, self.dtype).eval()
+        if self.safety_checker is not None and hasattr(self.safety_checker, "to"):
+            self.safety_checker.to(self.device, self.dtype)
         self._engine = None
         return self
 
@@ -337,13 +351,23 @@ class StableDiffusionPipeline:
             return out
         pil = tensor_to_pil(images) if isinstance(images, torch.Tensor) and images.dtype != torch.uint8 else \
             [Image.fromarray(a) for a in images.cpu().numpy()]
-        return PipelineOutput(images=pil, nsfw_content_detected=self.run_safety_checker(pil), latents=x,
+        with timer.stage("safety_checker"):
+            pil, flags = self.run_safety_checker(pil)
+        return PipelineOutput(images=pil, nsfw_content_detected=flags, latents=x,
                               timings=timer.result() if timer.enabled else {})
 
     def run_safety_checker(self, images):
+        """(images with flagged ones blacked out, per-image flags).  Without a checker (checkpoints that ship
+        none, random-init benchmark weights) nothing is flagged and `config["nsfw_unchecked"]` says so on the
+        wire instead of a silent `nsfw: false`."""
         if self.safety_checker is None:
-            return [False] * len(images)
-        return self.safety_checker(images)
+            self.config["nsfw_unchecked"] = True
+            return images, [False] * len(images)
+        self.config.pop("nsfw_unchecked", None)
+        if hasattr(self.safety_checker, "check"):
+            return self.safety_checker.check(images)
+        flags = [bool(f) for f in self.safety_checker(images)]
+        return [Image.new("RGB", im.size, (0, 0, 0)) if f else im for im, f in zip(images, flags)], flags
 
     def enable_patch_parallel(self, gang):
         """Single-image jobs run patch-parallel over `gang` (engine/patch_engine.py); every rank of the

@@ -48,12 +48,9 @@ class _StepGraph:
         self.step = torch.zeros(1, dtype=torch.int32, device=dev)
         self.noise = torch.zeros(0, device=dev)
         self.has_noise = has_noise
-        self.guidance = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.guidance = torch.zeros(2, dtype=torch.float32, device=dev)  # (g_text, g_image), filled per job
         self.aug_emb = torch.zeros(n, up.boc[0] * 4, dtype=torch.float16, device=dev) if aug else None
         self.control_feat: Optional[FM] = None
-        self.g_text = 7.5
-        self.g_image = 1.5
-        self.control_scale = 1.0
         self.rec: Optional[Recorder] = None
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.has_control = has_control
@@ -75,7 +72,7 @@ class _StepGraph:
             cn_mid, cn_feats = cp.record_encoder(rec, x_in, ctemb, cond_feat=self.control_feat)
         mid, skips = up.record_encoder(rec, x_in, temb)
         if self.has_control:
-            eng.control_plan.record_residual_adds(rec, cn_feats, cn_mid, skips, mid, self.control_scale)
+            eng.control_plan.record_residual_adds(rec, cn_feats, cn_mid, skips, mid)
         eps = up.record_decoder(rec, mid, skips, temb)
         rec.add(self._sched, eps)
         rec.add(nat.advance_counter, self.step)
@@ -84,7 +81,7 @@ class _StepGraph:
 
     def _sched(self, eps: FM):
         nat.sched_step(eps=eps.t, n_cond=self.n_cond, rows=self.rows, c=self.lat_c, eps_ld=eps.c,
-                       g_text=self.g_text, g_image=self.g_image, x=self.x, x0_prev=self.x0_prev,
+                       g_text=0.0, g_image=0.0, guidance=self.guidance, x=self.x, x0_prev=self.x0_prev,
                        noise=self.noise if self.has_noise else None, x_model_in=self.model_in,
                        xin_ld=self.model_in.shape[-1], coef=self.coef, step_idx=self.step)
 
@@ -120,7 +117,8 @@ class SM100Denoiser:
             self.unet_plan = UNetPlan(pipe.unet, self.device)
         self.control_plan = ControlNetPlan(pipe.controlnet, self.device) if pipe.controlnet is not None else None
         self.vae_plan = None
-        self._graphs: Dict[tuple, _StepGraph] = {}
+        self._graphs: Dict[tuple, _StepGraph] = {}  # insertion order = LRU order
+        self.max_graphs = 8
         self._vae_graphs: Dict[tuple, tuple] = {}
         self.last_launches = 0
 
@@ -140,9 +138,12 @@ class SM100Denoiser:
         if steps > MAX_STEPS:
             raise ValueError(f"at most {MAX_STEPS} denoising steps are supported")
         extra_ch = 0 if extra is None else extra.shape[1]
-        key = (batch, h, w, n_cond, extra_ch, control is not None, noise is not None, added is not None,
-               g_text, g_image, control_scale, num_frames)
-        sg = self._graphs.get(key)
+        # shapes only: guidance lives in a device slot and the ControlNet scale in the zero-conv weights, both
+        # refreshed per job, so a new guidance value never re-records or re-captures a plan
+        key = (batch, h, w, n_cond, extra_ch, control is not None, noise is not None, added is not None, num_frames)
+        sg = self._graphs.pop(key, None)
+        if sg is not None:
+            self._graphs[key] = sg  # most recently used goes last
         up = self.unet_plan
         if num_frames > 1 or hasattr(up, "num_frames"):
             if not hasattr(up, "num_frames") or batch % num_frames:
@@ -154,22 +155,31 @@ class SM100Denoiser:
         if sg is None:
             sg = _StepGraph(self, batch, h, w, n_cond, extra_ch, control is not None, noise is not None,
                             added is not None)
-            sg.g_text, sg.g_image, sg.control_scale = g_text, g_image, control_scale
             sg.build(steps if noise is not None else 0)
-            self._load_job(sg, x, plan, extra, control, added, noise)
+            self._load_job(sg, x, plan, extra, control, added, noise, g_text, g_image, control_scale)
             sg.capture()
             self._graphs[key] = sg
-            if len(self._graphs) > 8:
-                self._graphs.pop(next(iter(self._graphs)))
-        self._load_job(sg, x, plan, extra, control, added, noise)
+            if len(self._graphs) > self.max_graphs:
+                self._evict(next(iter(self._graphs)))  # least recently used
+        self._load_job(sg, x, plan, extra, control, added, noise, g_text, g_image, control_scale)
         for _ in range(steps):
             sg.replay()
         self.last_launches = sg.launches_per_step * steps
         return sg.x.view(batch, h, w, c).permute(0, 3, 1, 2).contiguous()
 
-    def _load_job(self, sg: _StepGraph, x, plan, extra, control, added, noise):
+    def _evict(self, key):
+        sg = self._graphs.pop(key, None)
+        if sg is not None:
+            sg.graph = None
+            sg.rec = None
+
+    def _load_job(self, sg: _StepGraph, x, plan, extra, control, added, noise, g_text=7.5, g_image=1.5,
+                  control_scale=1.0):
         batch, c, h, w = x.shape
         steps = plan.num_steps
+        sg.guidance.copy_(torch.tensor([float(g_text), float(g_image)], dtype=torch.float32))
+        if self.control_plan is not None and control is not None:
+            self.control_plan.set_scale(float(control_scale))
         x_nhwc = x.float().permute(0, 2, 3, 1).reshape(sg.rows, c)
         sg.x.copy_(x_nhwc)
         sg.x0_prev.zero_()

@@ -44,7 +44,9 @@ class _Channel:
 
 
 class PatchContext:
-    def __init__(self, gang: Gang, n_cond: int, arena_bytes: int):
+    def __init__(self, gang: Gang, n_cond: int, arena):
+        """`arena`: a SymmetricArena or one recyclable ArenaSlice of the gang's arena (PatchDenoiser hands every
+        cached plan its own slice, so the peer-visible memory of an evicted plan is reused)."""
         if gang.world % n_cond:
             raise ValueError(f"{gang.world} ranks cannot be split into {n_cond} guidance groups")
         self.gang = gang
@@ -52,7 +54,7 @@ class PatchContext:
         self.G = n_cond
         self.P = gang.world // n_cond
         self.g, self.p = gang.rank // self.P, gang.rank % self.P
-        self.arena = SymmetricArena(gang, arena_bytes)
+        self.arena = SymmetricArena(gang, arena) if isinstance(arena, int) else arena
         self.tick = torch.zeros(1, dtype=torch.int32, device=gang.device)
         self._channels: Dict[str, _Channel] = {}
         self._gn_stats: Optional[SymTensor] = None
@@ -90,8 +92,7 @@ class PatchContext:
         return self.arena.alloc(rows, c)
 
     def owns(self, t: torch.Tensor) -> bool:
-        base = self.arena.buffer.data_ptr()
-        return base <= t.data_ptr() < base + self.arena.nbytes
+        return self.arena.contains(t)
 
     # ---- the four communication points
     def conv_input(self, rec: Recorder, x: FM):
@@ -163,9 +164,10 @@ class PatchRecorder(Recorder):
 
 
 class _PatchStepGraph(_StepGraph):
-    def __init__(self, eng: "PatchDenoiser", h, w, n_cond, extra_ch, has_noise, aug, arena_bytes):
+    def __init__(self, eng: "PatchDenoiser", h, w, n_cond, extra_ch, has_noise, aug, arena):
         super().__init__(eng, 1, h, w, n_cond, extra_ch, False, has_noise, aug)
-        self.ctx = PatchContext(eng.gang, n_cond, arena_bytes)
+        self.arena_slice = arena
+        self.ctx = PatchContext(eng.gang, n_cond, arena)
         if aug:
             self.aug_full = self.aug_emb                      # [n_cond, D]: _load_job fills all branches
             self.aug_emb = self.aug_full[self.ctx.g:self.ctx.g + 1]
@@ -205,10 +207,33 @@ class PatchDenoiser(SM100Denoiser):
     """SM100Denoiser whose single-image jobs run patch-parallel over `gang`; every rank of the gang
     must make the same calls with the same seeds (SPMD).  Other jobs fall back to the local engine."""
 
-    def __init__(self, pipe, gang: Gang, arena_bytes: int = 6 << 30):
+    def __init__(self, pipe, gang: Gang, arena_bytes: int = 6 << 30, max_patch_graphs: int = 2):
         super().__init__(pipe)
         self.gang = gang
         self.arena_bytes = arena_bytes
+        # ONE symmetric arena per gang, cut into recyclable slices (one per cached patch plan, least recently used
+        # evicted): a stream of jobs with new shapes can neither exhaust HBM nor pay a rendezvous per plan
+        self.max_patch_graphs = max_patch_graphs
+        self._slices = None
+
+    def _take_slice(self):
+        if self._slices is None:
+            self._slices = SymmetricArena(self.gang, self.arena_bytes).slices(self.max_patch_graphs)
+        free = [s for s in self._slices if not s.in_use]
+        if not free:
+            victim = next(k for k in self._graphs if isinstance(k, tuple) and k and k[0] == "patch")
+            self._evict(victim)
+            free = [s for s in self._slices if not s.in_use]
+        sl = free[0]
+        sl.reset()
+        sl.in_use = True
+        return sl
+
+    def _evict(self, key):
+        sg = self._graphs.get(key)
+        if sg is not None and getattr(sg, "arena_slice", None) is not None:
+            sg.arena_slice.in_use = False
+        super()._evict(key)
 
     def supports(self, x, n_cond, control, inpaint) -> bool:
         return (self.gang.world > 1 and x.shape[0] == 1 and control is None and inpaint is None
@@ -225,29 +250,30 @@ class PatchDenoiser(SM100Denoiser):
         if steps > MAX_STEPS:
             raise ValueError(f"at most {MAX_STEPS} denoising steps are supported")
         extra_ch = 0 if extra is None else extra.shape[1]
-        key = ("patch", h, w, n_cond, extra_ch, noise is not None, added is not None, g_text, g_image)
-        sg = self._graphs.get(key)
-        if sg is None:
-            sg = _PatchStepGraph(self, h, w, n_cond, extra_ch, noise is not None, added is not None, self.arena_bytes)
+        # shapes only (guidance is a device slot, see SM100Denoiser.run)
+        key = ("patch", h, w, n_cond, extra_ch, noise is not None, added is not None)
+        sg = self._graphs.pop(key, None)
+        fresh = sg is None
+        if fresh:
+            sg = _PatchStepGraph(self, h, w, n_cond, extra_ch, noise is not None, added is not None, self._take_slice())
+        self._graphs[key] = sg  # most recently used goes last
         g = sg.ctx.g
         self.unet_plan.set_context(embeds[g:g + 1].to(torch.float16))
-        if key not in self._graphs:
-            sg.g_text, sg.g_image = g_text, g_image
+        if fresh:
             sg.build(steps if noise is not None else 0)
-            self._load_patch_job(sg, x, plan, extra, added, noise)
+            self._load_patch_job(sg, x, plan, extra, added, noise, g_text, g_image)
             sg.capture()
-            self._graphs[key] = sg
-        self._load_patch_job(sg, x, plan, extra, added, noise)
+        self._load_patch_job(sg, x, plan, extra, added, noise, g_text, g_image)
         for _ in range(steps):
             sg.replay()
         self.last_launches = sg.launches_per_step * steps
         return sg.x.view(batch, h, w, c).permute(0, 3, 1, 2).contiguous()
 
-    def _load_patch_job(self, sg: _PatchStepGraph, x, plan, extra, added, noise):
+    def _load_patch_job(self, sg: _PatchStepGraph, x, plan, extra, added, noise, g_text=7.5, g_image=1.5):
         local_aug = sg.aug_emb
         if added is not None:
             sg.aug_emb = sg.aug_full
         try:
-            self._load_job(sg, x, plan, extra, None, added, noise)
+            self._load_job(sg, x, plan, extra, None, added, noise, g_text, g_image)
         finally:
             sg.aug_emb = local_aug

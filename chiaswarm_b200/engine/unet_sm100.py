@@ -171,6 +171,21 @@ class ControlNetPlan(UNetPlan):
         self.cond_convs = [Conv(ce.conv_in, cin_pad=self.cond_in_pad)] + [Conv(b) for b in ce.blocks] + [Conv(ce.conv_out)]
         self.zero = [Linear(c.weight, c.bias) for c in cn.controlnet_down_blocks]
         self.zero_mid = Linear(cn.controlnet_mid_block.weight, cn.controlnet_mid_block.bias)
+        # controlnet_conditioning_scale is folded into the zero convs (skip + s*(W f + b) = skip + (sW) f + sb):
+        # the unscaled parameters are kept and the buffers the recorded plans point at are rewritten in place when
+        # a job asks for another scale, so captured graphs are independent of it
+        self._zero_unscaled = [(z, z.wgt.clone(), None if z.bias is None else z.bias.clone())
+                               for z in self.zero + [self.zero_mid]]
+        self._scale = 1.0
+
+    def set_scale(self, scale: float):
+        if scale == self._scale:
+            return
+        for z, w0, b0 in self._zero_unscaled:
+            z.wgt.copy_(w0 * scale)
+            if b0 is not None:
+                z.bias.copy_(b0 * scale)
+        self._scale = scale
 
     def record_cond_embedding(self, rec: Recorder, cond: FM) -> FM:
         """Step-invariant: run once per job, outside the per-step graph."""
@@ -180,13 +195,11 @@ class ControlNetPlan(UNetPlan):
             x = c(rec, x, act=nat.ACT_NONE if last else nat.ACT_SILU)
         return x
 
-    def record_residual_adds(self, rec: Recorder, feats: List[FM], mid: FM, unet_skips: List[FM], unet_mid: FM,
-                             scale: float):
+    def record_residual_adds(self, rec: Recorder, feats: List[FM], mid: FM, unet_skips: List[FM], unet_mid: FM):
         for z, f, s in zip(self.zero, feats, unet_skips):
-            rec.add(nat.igemm, f.tokens(), z.wgt, s.tokens(), n=1, h=1, w=f.rows, bias=z.bias, residual=s.tokens(),
-                    out_scale=scale)
+            rec.add(nat.igemm, f.tokens(), z.wgt, s.tokens(), n=1, h=1, w=f.rows, bias=z.bias, residual=s.tokens())
         rec.add(nat.igemm, mid.tokens(), self.zero_mid.wgt, unet_mid.tokens(), n=1, h=1, w=mid.rows,
-                bias=self.zero_mid.bias, residual=unet_mid.tokens(), out_scale=scale)
+                bias=self.zero_mid.bias, residual=unet_mid.tokens())
 
 
 class VaeDecoderPlan:

@@ -64,6 +64,7 @@ class IGemmParams(C.Structure):
         ("ln_eps", C.c_float),
         ("cluster_k", C.c_int32),
         ("persist", C.c_int32),
+        ("w_kmajor", C.c_int32),
     ]
 
 
@@ -90,6 +91,7 @@ class SchedParams(C.Structure):
         ("xin_ld", C.c_int32),
         ("coef", C.c_void_p),
         ("step_idx", C.c_void_p),
+        ("guidance", C.c_void_p),
     ]
 
 
@@ -219,12 +221,18 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
             raise TypeError(f"{nm}: expected a CUDA fp16 tensor with contiguous last dim")
     c1 = a1.shape[-1]
     c2 = 0 if a2 is None else _f16(a2, "a2").shape[-1]
-    cout = wgt.shape[0]
-    assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
+    kmajor = wgt.dim() == 3  # k-block-major packing [k-blocks, cout, 64] (ops/packing.pack_kmajor)
+    if kmajor:
+        cout = wgt.shape[1]
+        assert wgt.is_contiguous() and wgt.shape[2] == 64
+        assert wgt.shape[0] == kh * kw * ((c1 + 63) // 64 + (c2 + 63) // 64), (wgt.shape, kh, kw, c1, c2)
+    else:
+        cout = wgt.shape[0]
+        assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
     assert a1.numel() == n * (a_h_total or h) * w * c1
     # strided 2-D views (a column block of a wider matrix) are passed through leading dimensions
     a_ld = 0 if a1.is_contiguous() else a1.stride(-2)
-    w_ld = 0 if wgt.is_contiguous() else wgt.stride(0)
+    w_ld = 0 if (kmajor or wgt.is_contiguous()) else wgt.stride(0)
     if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
         raise ValueError("strided a1 is only supported for plain GEMMs")
     if (tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0 and persist == 0 and cluster_k == 0
@@ -261,6 +269,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.a_h_total, p.a_y_off = a_h_total, a_y_off
     p.persist = persist
     p.cluster_k = cluster_k
+    p.w_kmajor = 1 if kmajor else 0
     p.row_stats_out, p.row_stats_in, p.col_sums = _ptr(row_stats_out), _ptr(row_stats_in), _ptr(col_sums)
     p.stats_tiles, p.ln_width, p.ln_eps = stats_tiles, ln_width, ln_eps
     if splitk_scratch is not None:
@@ -275,7 +284,8 @@ def linear(x, wgt, out=None, **kw):
     """x: [..., K] fp16 contiguous; wgt: [N, K]. Returns [..., N] (N/2 for GEGLU)."""
     k = x.shape[-1]
     m = x.numel() // k
-    ncols = wgt.shape[0] // 2 if kw.get("act") == ACT_GEGLU else wgt.shape[0]
+    cout = wgt.shape[1] if wgt.dim() == 3 else wgt.shape[0]
+    ncols = cout // 2 if kw.get("act") == ACT_GEGLU else cout
     if out is None:
         out = torch.empty(*x.shape[:-1], ncols, dtype=torch.float16, device=x.device)
     igemm(x, wgt, out, n=1, h=1, w=m, **kw)
@@ -390,7 +400,8 @@ def silu(x, out):
 
 
 def sched_step(*, eps, n_cond, rows, c, eps_ld, g_text, g_image, x, x0_prev, noise, x_model_in, xin_ld,
-               coef, step_idx):
+               coef, step_idx, guidance=None):
+    """`guidance`: optional device fp32 [2] = (g_text, g_image) read by the kernel instead of the scalars."""
     p = SchedParams()
     p.eps = _ptr(eps)
     p.n_cond, p.rows, p.c, p.eps_ld = n_cond, rows, c, eps_ld
@@ -400,6 +411,7 @@ def sched_step(*, eps, n_cond, rows, c, eps_ld, g_text, g_image, x, x0_prev, noi
     p.xin_ld = xin_ld
     p.coef = _ptr(coef)
     p.step_idx = _ptr(step_idx)
+    p.guidance = _ptr(guidance)
     _check(lib().sw_sched_step(C.byref(p), _stream()), "sw_sched_step")
     _count()
 

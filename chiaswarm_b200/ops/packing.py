@@ -58,3 +58,43 @@ def fold_layernorm(w: torch.Tensor, b: torch.Tensor | None, gamma: torch.Tensor,
     if b is not None:
         b2 = b2 + b.detach().float()
     return w2.contiguous(), b2.to(torch.float16).contiguous(), w2.float().sum(1).contiguous()
+
+
+def pack_kmajor(w: torch.Tensor, taps: int, c1: int, c2: int = 0) -> torch.Tensor:
+    """[cout, taps*(c1+c2)] (the K order of sw_igemm: tap, then the channels of input 1, then of input 2) ->
+    k-block-major [k-blocks, cout, 64]: k-block = (tap, 64-channel slab), slabs zero-padded to 64 channels.
+    Each weight tile the kernel fetches (rows of one N tile, one k-block) is then a single contiguous run of
+    memory, so cold weights stream from HBM in whole-page bursts instead of one 128-byte segment per DRAM page
+    (sw_igemm_params.w_kmajor).  A round trip through `unpack_kmajor` is exact."""
+    cout, k = w.shape
+    ctot = c1 + c2
+    assert k == taps * ctot, (w.shape, taps, c1, c2)
+    nkb1, nkb2 = (c1 + 63) // 64, (c2 + 63) // 64
+    out = torch.zeros(taps * (nkb1 + nkb2), cout, 64, dtype=w.dtype, device=w.device)
+    wt = w.reshape(cout, taps, ctot)
+    for t in range(taps):
+        base = t * (nkb1 + nkb2)
+        for j in range(nkb1):
+            lo, hi = j * 64, min(c1, j * 64 + 64)
+            out[base + j, :, : hi - lo] = wt[:, t, lo:hi]
+        for j in range(nkb2):
+            lo, hi = j * 64, min(c2, j * 64 + 64)
+            out[base + nkb1 + j, :, : hi - lo] = wt[:, t, c1 + lo:c1 + hi]
+    return out.contiguous()
+
+
+def unpack_kmajor(wk: torch.Tensor, taps: int, c1: int, c2: int = 0) -> torch.Tensor:
+    """Inverse of pack_kmajor."""
+    nkb, cout, _ = wk.shape
+    nkb1, nkb2 = (c1 + 63) // 64, (c2 + 63) // 64
+    assert nkb == taps * (nkb1 + nkb2)
+    out = torch.empty(cout, taps, c1 + c2, dtype=wk.dtype, device=wk.device)
+    for t in range(taps):
+        base = t * (nkb1 + nkb2)
+        for j in range(nkb1):
+            lo, hi = j * 64, min(c1, j * 64 + 64)
+            out[:, t, lo:hi] = wk[base + j, :, : hi - lo]
+        for j in range(nkb2):
+            lo, hi = j * 64, min(c2, j * 64 + 64)
+            out[:, t, c1 + lo:c1 + hi] = wk[base + nkb1 + j, :, : hi - lo]
+    return out.reshape(cout, taps * (c1 + c2))

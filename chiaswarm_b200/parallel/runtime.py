@@ -155,3 +155,69 @@ class SymmetricArena:
         """Host-side full barrier of the gang (device-visible writes included)."""
         torch.cuda.synchronize()
         self.gang.barrier()
+
+    def contains(self, t: torch.Tensor) -> bool:
+        base = self.buffer.data_ptr()
+        return base <= t.data_ptr() < base + self.nbytes
+
+    def slices(self, count: int) -> List["ArenaSlice"]:
+        """Cuts what is left of the arena (data and flags) into `count` equal, independently recyclable regions:
+        one per cached plan, so that evicting a plan returns its peer-visible memory instead of leaking a whole
+        arena (every rank must make the same call)."""
+        start = (self._cursor + 4095) // 4096 * 4096
+        per = (self.nbytes - start) // count // 4096 * 4096
+        fper = (FLAG_SLOTS - self._flag_cursor) // count
+        out = [ArenaSlice(self, start + i * per, per, self._flag_cursor + i * fper, fper) for i in range(count)]
+        self._cursor = self.nbytes
+        self._flag_cursor = FLAG_SLOTS
+        return out
+
+
+class ArenaSlice:
+    """A recyclable region of a SymmetricArena with the allocator interface of the arena itself."""
+
+    def __init__(self, parent: SymmetricArena, data_off: int, data_bytes: int, flag_off: int, flag_count: int):
+        self.parent = parent
+        self.gang, self.world, self.rank = parent.gang, parent.world, parent.rank
+        self.peer_bases = parent.peer_bases
+        self.multicast_ptr = parent.multicast_ptr
+        self.buffer = parent.buffer
+        self._lo, self._hi = data_off, data_off + data_bytes
+        self._flag_lo, self._flag_hi = flag_off, flag_off + flag_count
+        self._cursor, self._flag_cursor = self._lo, self._flag_lo
+        self.in_use = False
+
+    def reset(self):
+        """Forget every allocation and clear the flags (their epochs restart from zero with the next plan); a gang
+        barrier makes sure no peer still polls or writes them."""
+        torch.cuda.synchronize()
+        self.gang.barrier()
+        self.parent.buffer[self._flag_lo * 4:self._flag_hi * 4].zero_()
+        self._cursor, self._flag_cursor = self._lo, self._flag_lo
+        torch.cuda.synchronize()
+        self.gang.barrier()
+
+    def alloc(self, *shape, dtype=torch.float16) -> SymTensor:
+        numel = 1
+        for s in shape:
+            numel *= s
+        size = numel * torch.empty((), dtype=dtype).element_size()
+        off = (self._cursor + 255) // 256 * 256
+        if off + size > self._hi:
+            raise MemoryError(f"symmetric arena slice exhausted ({off + size - self._lo} > {self._hi - self._lo})")
+        self._cursor = off + size
+        local = self.buffer[off:off + size].view(dtype).view(*shape)
+        return SymTensor(local=local, offset=off, arena=self)
+
+    def alloc_flags(self, count: Optional[int] = None) -> SymTensor:
+        count = count or self.world
+        if self._flag_cursor + count > self._flag_hi:
+            raise MemoryError("flag area of the arena slice exhausted")
+        off = self._flag_cursor * 4
+        self._flag_cursor += count
+        local = self.buffer[off:off + count * 4].view(torch.int32)
+        return SymTensor(local=local, offset=off, arena=self)
+
+    def contains(self, t: torch.Tensor) -> bool:
+        base = self.buffer.data_ptr()
+        return base + self._lo <= t.data_ptr() < base + self._hi

@@ -41,6 +41,9 @@ struct AttnArgs {
     // v1, short sequences (temporal attention: seq = frames): `pack` batch entries share one 128-row
     // tile (TMA box {64, 1, seq, pack}); the softmax masks everything outside a row's own entry
     int pack;
+    // v2: clocks the second query tile's softmax warpgroup holds back before its first tile, so that the two
+    // warpgroups sit half a period apart (one in the exponentials while the other loads / reduces / waits)
+    int stagger;
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -651,11 +654,36 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
 
         float m_ref = -INFINITY;
         float l = 0.0f;
+        // The exponentials (MUFU: 16 per clock per SM) are the scarce unit and the two warpgroups share it.  Left
+        // alone they run in phase -- tile 1's first scores arrive right after tile 0 copied its own, and the lag
+        // between two identical loops sharing one pipe is neutrally stable -- so both sit in the exponentials at
+        // once and both wait at once (scripts/trace_attn.py: 1920 clocks of exponentials + 1280 of everything
+        // else per KV tile, MUFU idle 40 % of the time).  Holding tile 1 back once by half a period keeps one
+        // warpgroup in the exponentials while the other loads, reduces and waits.
+        if (t == 1 && p.stagger > 0 && nkv > 2) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < p.stagger) {
+            }
+        }
+#ifdef SW_TRACE
+        long long tr_acc[6] = {0, 0, 0, 0, 0, 0};  // wait S, load S, row max, wait PV, exponentials + P store, publish
+        long long tr_t = clock64();
+        const long long tr_begin = tr_t;
+#define ATTN_TR(k)                       \
+    {                                    \
+        const long long now = clock64(); \
+        tr_acc[k] += now - tr_t;         \
+        tr_t = now;                      \
+    }
+#else
+#define ATTN_TR(k)
+#endif
         for (int j = 0; j < nkv; ++j) {
             const int kv_valid = min(BKV, p.seq_kv - j * BKV);
             if (lane == 0) mbar_wait(&s_full[t], uint32_t(j & 1));
             __syncwarp();
             tc_fence_after();
+            ATTN_TR(0)
             // The whole score row moves to registers in one go and the TMEM tile is handed back at once:
             // the MMA warp computes the next S = Q K^T while this row is still in the exponentials.
             uint32_t s0[32], s1[32], s2[32], s3[32];
@@ -666,6 +694,7 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(&s_free[t]);
+            ATTN_TR(1)
             // exact running maximum (online softmax); the reference only moves when the row outgrows
             // it by more than 2^8, so most tiles skip the O rescale
             // (four independent running maxima / sums per thread: with two softmax warps per scheduler a
@@ -688,6 +717,7 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             const float mx = fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3]));
             const float m_new = mx * scale;
             bool need = false;
+            ATTN_TR(2)
             if (j == 0) {
                 m_ref = m_new;
             } else {
@@ -695,6 +725,7 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                 if (lane == 0) mbar_wait(&pv_done[t], uint32_t((j - 1) & 1));  // O stable, P tile free
                 __syncwarp();
                 tc_fence_after();
+                ATTN_TR(3)
                 if (__any_sync(0xffffffffu, need)) {
                     const float alpha = need ? ex2(m_ref - m_new) : 1.0f;
                     if (need) m_ref = m_new;
@@ -744,10 +775,21 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
             chunk(s2, 64);
             chunk(s3, 96);
             l += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+            ATTN_TR(4)
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(&p_full[t]);
+            ATTN_TR(5)
         }
+#ifdef SW_TRACE
+        if ((warp == 2 || warp == 6) && lane == 0) {
+            for (int k = 0; k < 6; ++k) trace_value(t * 6 + k, (unsigned long long)tr_acc[k]);
+            if (t == 0) trace_value(12, (unsigned long long)(clock64() - tr_begin));
+            trace_value(13, trace_smid());
+            trace_value(15, (unsigned long long)gridDim.x | ((unsigned long long)gridDim.y << 20) |
+                                ((unsigned long long)gridDim.z << 40));
+        }
+#endif
         if (lane == 0) mbar_wait(&pv_done[t], uint32_t((nkv - 1) & 1));
         __syncwarp();
         tc_fence_after();
@@ -833,6 +875,14 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
     a.o_stride_s = p->o_stride_s;
     a.idesc_qk = sw::umma_idesc(128, 128, 0, 0, 0);
     a.idesc_pv = sw::umma_idesc(128, a.dpad, 0, 0, 1);
+    {
+        static int env_stagger = -2;  // SW_ATTN_STAGGER: clocks (0 = off); default 1100
+        if (env_stagger == -2) {
+            const char* e = getenv("SW_ATTN_STAGGER");
+            env_stagger = e ? atoi(e) : 1100;
+        }
+        a.stagger = env_stagger;
+    }
 
     // short self-attention sequences (temporal attention over frames): several batch entries per tile
     a.pack = 1;
@@ -913,6 +963,7 @@ extern "C" int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpe
     a.o_stride_s = p->o_stride_s;
     a.idesc_qk = sw::umma_idesc(128, 128, 0, 0, 0);
     a.idesc_pv = sw::umma_idesc(128, a.dpad, 0, 0, 1);
+    a.stagger = 1100;
     a.world = world;
     a.rank = kpeers->rank;
     a.epoch = kpeers->epoch;
@@ -954,3 +1005,6 @@ extern "C" int sw_flash_attn_gather(const sw_attn_params* p, const sw_peers* kpe
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }
+
+// Probe builds (-DSW_TRACE) only: per-CTA softmax phase totals of the last flash-attention launch.
+SW_TRACE_DUMP_FN(sw_trace_dump_attn)

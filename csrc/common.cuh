@@ -290,4 +290,60 @@ __device__ __forceinline__ float2 unpack_h2(uint32_t u) {
     return __half22float2(*reinterpret_cast<__half2*>(&u));
 }
 
+// ---------------------------------------------------------------- phase trace (probe builds only)
+// -DSW_TRACE: every CTA stamps clock64 at its phase boundaries into a per-translation-unit device array that
+// a probe script reads back (SW_TRACE_DUMP_FN defines the extern "C" reader); the shipped library is built
+// without it and the macros vanish.
+#ifdef SW_TRACE
+constexpr int kTraceSlots = 16;
+constexpr int kTraceCtas = 8192;
+static __device__ unsigned long long g_sw_trace[kTraceCtas * kTraceSlots];
+__device__ __forceinline__ unsigned trace_cta() {
+    return (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+}
+__device__ __forceinline__ void trace_stamp(int slot) {
+    const unsigned cta = trace_cta();
+    if (cta < unsigned(kTraceCtas)) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+        g_sw_trace[cta * kTraceSlots + slot] = t;
+    }
+}
+__device__ __forceinline__ void trace_stamp_global(int slot) {
+    const unsigned cta = trace_cta();
+    if (cta < unsigned(kTraceCtas)) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_sw_trace[cta * kTraceSlots + slot] = t;
+    }
+}
+__device__ __forceinline__ void trace_value(int slot, unsigned long long v) {
+    const unsigned cta = trace_cta();
+    if (cta < unsigned(kTraceCtas)) g_sw_trace[cta * kTraceSlots + slot] = v;
+}
+__device__ __forceinline__ unsigned trace_smid() {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    return smid;
+}
+#define TR(slot) sw::trace_stamp(slot)
+#define TRG(slot) sw::trace_stamp_global(slot)
+#define SW_TRACE_DUMP_FN(name)                                                                                   \
+    extern "C" int name(unsigned long long* host, int ctas) {                                                    \
+        if (!host || ctas <= 0 || ctas > sw::kTraceCtas) return -1;                                              \
+        if (cudaDeviceSynchronize() != cudaSuccess) return -2;                                                   \
+        return int(cudaMemcpyFromSymbol(host, sw::g_sw_trace,                                                    \
+                                        size_t(ctas) * sw::kTraceSlots * sizeof(unsigned long long)));           \
+    }
+#else
+#define TR(slot) ((void)0)
+#define TRG(slot) ((void)0)
+#define SW_TRACE_DUMP_FN(name)                                                                                   \
+    extern "C" int name(unsigned long long* host, int ctas) {                                                    \
+        (void)host;                                                                                              \
+        (void)ctas;                                                                                              \
+        return -1; /* library built without SW_TRACE */                                                          \
+    }
+#endif
+
 }  // namespace sw

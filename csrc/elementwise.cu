@@ -158,6 +158,9 @@ __global__ void k_sched_step(const sw_sched_params p) {
     const int step = p.step_idx ? *p.step_idx : 0;
     const float* cf = p.coef + (size_t)step * 8;
     const float e0 = cf[0], e1 = cf[1], c0 = cf[2], c1 = cf[3], c2 = cf[4], c3 = cf[5], s_in = cf[6];
+    // guidance scales: a device slot when given (a captured graph then serves every guidance value), else scalars
+    const float g_text = p.guidance ? p.guidance[0] : p.g_text;
+    const float g_image = p.guidance ? p.guidance[1] : p.g_image;
     const long long total = (long long)p.rows * p.c;
     const __half* eps = static_cast<const __half*>(p.eps);
     __half* xin = static_cast<__half*>(p.x_model_in);
@@ -173,12 +176,12 @@ __global__ void k_sched_step(const sw_sched_params p) {
         } else if (p.n_cond == 2) {
             const float eu = __half2float(eps[ei]);
             const float ec = __half2float(eps[cond_stride + ei]);
-            e = eu + p.g_text * (ec - eu);
+            e = eu + g_text * (ec - eu);
         } else {
             const float et = __half2float(eps[ei]);
             const float em = __half2float(eps[cond_stride + ei]);
             const float eu = __half2float(eps[2 * cond_stride + ei]);
-            e = eu + p.g_text * (et - em) + p.g_image * (em - eu);
+            e = eu + g_text * (et - em) + g_image * (em - eu);
         }
         const float x = p.x[i];
         const float x0 = e0 * x + e1 * e;

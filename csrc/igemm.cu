@@ -23,6 +23,7 @@ using namespace sw;
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kThreads = 192;
+constexpr int kThreadsLean = 320;  // lean kernel: TMA warp, MMA warp, eight epilogue warps
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 
 struct IGemmArgs {
@@ -58,6 +59,7 @@ struct IGemmArgs {
     int ptiles, total_tiles;  // persistent kernel: pixel tiles, pixel tiles x column tiles
     int tma_epi;        // epilogue stages 64-column slabs in shared memory and writes them with TMA stores
     int epi_alias;      // lean kernel: the epilogue boxes overlay the drained operand ring (else dedicated)
+    int w_kmajor;       // weights packed k-block-major [k-blocks][cout][64]: tmB is 3-D {64, cout, k-blocks}
     int cluster_k;      // splits == 2 and the two splits of a tile form a cluster: partials meet in DSMEM
     int splits;         // split-K factor (grid.z)
     int kb_per_split;   // k-blocks per split
@@ -89,36 +91,6 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
         __nanosleep(64);
     }
 }
-
-// ---------------------------------------------------------------- phase trace (probe builds only)
-// -DSW_TRACE: every CTA stamps clock64 at its phase boundaries into a device array that the probe
-// script reads back (sw_trace_dump); the shipped library is built without it.
-#ifdef SW_TRACE
-constexpr int kTraceSlots = 16;
-constexpr int kTraceCtas = 8192;
-__device__ unsigned long long g_sw_trace[kTraceCtas * kTraceSlots];
-__device__ __forceinline__ void trace_stamp(int slot) {
-    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-    if (cta < unsigned(kTraceCtas)) {
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
-        g_sw_trace[cta * kTraceSlots + slot] = t;
-    }
-}
-__device__ __forceinline__ void trace_stamp_global(int slot) {
-    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-    if (cta < unsigned(kTraceCtas)) {
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        g_sw_trace[cta * kTraceSlots + slot] = t;
-    }
-}
-#define TR(slot) trace_stamp(slot)
-#define TRG(slot) trace_stamp_global(slot)
-#else
-#define TR(slot) ((void)0)
-#define TRG(slot) ((void)0)
-#endif
 
 // ---------------------------------------------------------------- raw-address PTX helpers
 // The producer and MMA roles are single threads: every instruction they execute sits on the
@@ -173,6 +145,32 @@ __device__ __forceinline__ void tma2(uint32_t dst, const CUtensorMap* m, uint32_
             "[%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
             "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
             : "memory");
+}
+template <bool PAIR>
+__device__ __forceinline__ void tma3(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2) {
+    if (PAIR)
+        asm volatile(
+            "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2)
+            : "memory");
+    else
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+            "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+            : "memory");
+}
+// weight tile of k-block `kb`: plain [cout][K] layout (columns kcol..kcol+63 of rows bcol0..) or the k-block-major
+// packing [k-blocks][cout][64] in which a tile is one contiguous run of memory (one DRAM page burst per 1 KB
+// instead of a 128-byte segment per page)
+template <bool PAIR>
+__device__ __forceinline__ void tma_b(uint32_t dst, const CUtensorMap* m, uint32_t bar, int kmajor, int kcol, int kb,
+                                      int bcol0) {
+    if (kmajor)
+        tma3<PAIR>(dst, m, bar, 0, bcol0, kb);
+    else
+        tma2<PAIR>(dst, m, bar, kcol, bcol0);
 }
 template <bool PAIR>
 __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
@@ -380,10 +378,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                     if (j < nkb1) {
                         tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                        tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                        tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
                     } else {
                         tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
-                        tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                        tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                     }
                 }
                 if (++j == per_tap) {
@@ -567,9 +565,27 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = 0.0f;
                 const float* src = tile_base + size_t(c8 >> 5) * 4096 + rr * 32 + (c8 & 31);
-                for (int z = 0; z < p.splits; ++z) {
-                    const float4 a0 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * nchunk * 4096));
-                    const float4 a1 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * nchunk * 4096) + 1);
+                const size_t zstride = size_t(nchunk) * 4096;
+                // four splits' partials in flight per thread (the loop was one dependent L2 round trip per split:
+                // ~700 clocks x splits, most of a split-K layer's time -- scripts/trace_igemm.py conv rows); the sums
+                // are still taken in split order, so the result is bit-identical
+                int z = 0;
+                for (; z + 4 <= p.splits; z += 4) {
+                    float4 a0[4], a1[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        a0[u] = __ldcg(reinterpret_cast<const float4*>(src + size_t(z + u) * zstride));
+                        a1[u] = __ldcg(reinterpret_cast<const float4*>(src + size_t(z + u) * zstride) + 1);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        f[0] += a0[u].x, f[1] += a0[u].y, f[2] += a0[u].z, f[3] += a0[u].w;
+                        f[4] += a1[u].x, f[5] += a1[u].y, f[6] += a1[u].z, f[7] += a1[u].w;
+                    }
+                }
+                for (; z < p.splits; ++z) {
+                    const float4 a0 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * zstride));
+                    const float4 a1 = __ldcg(reinterpret_cast<const float4*>(src + size_t(z) * zstride) + 1);
                     f[0] += a0.x, f[1] += a0.y, f[2] += a0.z, f[3] += a0.w;
                     f[4] += a1.x, f[5] += a1.y, f[6] += a1.z, f[7] += a1.w;
                 }
@@ -1166,10 +1182,10 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
                 if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                 if (j < nkb1) {
                     tma4<PAIR>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                    tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                    tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
                 } else {
                     tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
-                    tma2<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                    tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                 }
             }
             if (++j == per_tap) {
@@ -1242,21 +1258,26 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
             if (lane == 0) TR(6);
         }
     } else {
-        // ---------------- epilogue: one thread per accumulator row
+        // ---------------- epilogue: EIGHT warps, two per TMEM lane quadrant.  Warps 2-5 drain the even 64-column
+        // slabs of the accumulator, warps 6-9 the odd ones; each warpgroup has its own staging boxes, named
+        // barrier and TMA store stream, so a 128-column tile leaves in half the time of the four-warp version
+        // (the epilogue is latency-bound: one warp per scheduler walking a serial instruction stream).
+        const int half = (warp - 2) >> 2;
         const int q = warp & 3;
         const int r = q * 32 + lane;
-        const bool lead = threadIdx.x == 64;
+        const bool lead = lane == 0 && ((warp - 2) & 3) == 0;  // threads 64 and 192
+        const uint32_t bar_id = 1u + uint32_t(half);
         const bool tail32 = (cend & 63) == 32;  // last slab is 32 columns wide: staged unswizzled, own tensor map
-        // the residual boxes do not alias the ring: fetch the first two slabs while the main loop runs
-        if (HAS_RES && !p.epi_alias && lead) {
-            for (int sl = 0; sl < 2 && sl < nslab; ++sl) {
-                bar_expect_tx(rfull0 + 8 * sl, a_bytes);
-                tma4<false>(res_stage + sl * 16384, &tmRes, rfull0 + 8 * sl, col0 + sl * 64, x0, y0, n0);
-            }
+        const uint32_t box = uint32_t(half) * 16384u;
+        const uint32_t rfull = rfull0 + 8u * uint32_t(half);
+        // the residual boxes do not alias the ring: fetch this warpgroup's first slab while the main loop runs
+        if (HAS_RES && !p.epi_alias && lead && half < nslab) {
+            bar_expect_tx(rfull, a_bytes);
+            tma4<false>(res_stage + box, &tmRes, rfull, col0 + half * 64, x0, y0, n0);
         }
         // per-column addends (bias, plus the time-embedding row bias: the host only picks this kernel when a
         // tile lies within one image) go to shared memory while the main loop runs
-        for (int i = threadIdx.x - 64; i < BN; i += 128) {
+        for (int i = threadIdx.x - 64; i < BN; i += 256) {
             const int col = col0 + i;
             float b = 0.0f;
             if (col < p.cout) {
@@ -1265,69 +1286,68 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
             }
             s_bias[i] = b;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 3, 256;" ::: "memory");
         if (threadIdx.x == 64) TR(7);
         if (lane == 0) mbar_wait(acc_full, 0);
         __syncwarp();
         tc_fence_after();
         if (threadIdx.x == 64) TR(8);
-        if (HAS_RES && p.epi_alias && lead) {  // the boxes overlay the ring: every MMA has retired by now
-            for (int sl = 0; sl < 2 && sl < nslab; ++sl) {
-                bar_expect_tx(rfull0 + 8 * sl, a_bytes);
-                tma4<false>(res_stage + sl * 16384, &tmRes, rfull0 + 8 * sl, col0 + sl * 64, x0, y0, n0);
-            }
+        if (HAS_RES && p.epi_alias && lead && half < nslab) {  // the boxes overlay the ring: every MMA has retired
+            bar_expect_tx(rfull, a_bytes);
+            tma4<false>(res_stage + box, &tmRes, rfull, col0 + half * 64, x0, y0, n0);
         }
         const uint32_t trow = tmem_acc + (uint32_t(q * 32) << 16);
         const uint32_t row_off = uint32_t(r) * 128u, swz = uint32_t(r) & 7u;
-        uint32_t vn[32];
-        tmem_ld32(trow, vn);
+        int k = 0;  // slabs this warpgroup has handled
 #pragma unroll 1
-        for (int c = 0; c < cend; c += 32) {
-            const int sl = c >> 6;
-            const uint32_t box = uint32_t(sl & 1) * 16384u;
-            if ((c & 63) == 0) {
-                if (sl >= 2) {  // the store issued two slabs ago must have finished reading this box
-                    if (lead) bulk_wait_read<1>();
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                }
-                if (HAS_RES) bar_wait(rfull0 + 8 * (sl & 1), uint32_t(sl >> 1) & 1u);
+        for (int sl = half; sl < nslab; sl += 2, ++k) {
+            const int c0 = sl << 6;
+            const bool two = c0 + 32 < cend;
+            uint32_t v0[32], v1[32];
+            tmem_ld32(trow + c0, v0);
+            if (two) tmem_ld32(trow + c0 + 32, v1);
+            if (k > 0) {  // this warpgroup's previous store must have finished reading the box
+                if (lead) bulk_wait_read<0>();
+                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             }
-            uint32_t v[32];
-            tmem_ld_wait_dep(vn);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = vn[j];
-            if (c + 32 < cend) tmem_ld32(trow + c + 32, vn);
+            if (HAS_RES) bar_wait(rfull, uint32_t(k) & 1u);
             const bool tail_slab = tail32 && sl == nslab - 1;
+            tmem_ld_wait_dep(v0);
+            auto chunk = [&](const uint32_t (&v)[32], int c) {
 #pragma unroll
-            for (int g8 = 0; g8 < 4; ++g8) {
-                const int c8 = c + g8 * 8;
-                const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c8]);
-                const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c8 + 4]);
-                float f0 = __uint_as_float(v[g8 * 8 + 0]) + b0.x, f1 = __uint_as_float(v[g8 * 8 + 1]) + b0.y;
-                float f2 = __uint_as_float(v[g8 * 8 + 2]) + b0.z, f3 = __uint_as_float(v[g8 * 8 + 3]) + b0.w;
-                float f4 = __uint_as_float(v[g8 * 8 + 4]) + b1.x, f5 = __uint_as_float(v[g8 * 8 + 5]) + b1.y;
-                float f6 = __uint_as_float(v[g8 * 8 + 6]) + b1.z, f7 = __uint_as_float(v[g8 * 8 + 7]) + b1.w;
-                const uint32_t off = box + row_off + (((uint32_t(c8 >> 3) & 7u) ^ swz) << 4);
-                if (HAS_RES) {
-                    const uint4 rv = lds128(res_stage + off);
-                    const float2 r0 = unpack_h2(rv.x), r1 = unpack_h2(rv.y), r2 = unpack_h2(rv.z), r3 = unpack_h2(rv.w);
-                    f0 += r0.x, f1 += r0.y, f2 += r1.x, f3 += r1.y;
-                    f4 += r2.x, f5 += r2.y, f6 += r3.x, f7 += r3.y;
-                }
-                const uint32_t dst = tail_slab ? out_stage + box + uint32_t(r) * 64u + ((uint32_t(c8 >> 3) & 3u) << 4)
-                                               : out_stage + off;
-                sts128(dst, make_uint4(pack_h2(f0, f1), pack_h2(f2, f3), pack_h2(f4, f5), pack_h2(f6, f7)));
-            }
-            if ((c & 63) == 32 || c + 32 >= cend) {
-                fence_proxy_async_smem();
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                if (lead) {
-                    tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + sl * 64, x0, y0, n0);
-                    bulk_commit();
-                    if (HAS_RES && sl + 2 < nslab) {
-                        bar_expect_tx(rfull0 + 8 * (sl & 1), a_bytes);
-                        tma4<false>(res_stage + box, &tmRes, rfull0 + 8 * (sl & 1), col0 + (sl + 2) * 64, x0, y0, n0);
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const int c8 = c + g8 * 8;
+                    const float4 b0 = *reinterpret_cast<const float4*>(&s_bias[c8]);
+                    const float4 b1 = *reinterpret_cast<const float4*>(&s_bias[c8 + 4]);
+                    float f0 = __uint_as_float(v[g8 * 8 + 0]) + b0.x, f1 = __uint_as_float(v[g8 * 8 + 1]) + b0.y;
+                    float f2 = __uint_as_float(v[g8 * 8 + 2]) + b0.z, f3 = __uint_as_float(v[g8 * 8 + 3]) + b0.w;
+                    float f4 = __uint_as_float(v[g8 * 8 + 4]) + b1.x, f5 = __uint_as_float(v[g8 * 8 + 5]) + b1.y;
+                    float f6 = __uint_as_float(v[g8 * 8 + 6]) + b1.z, f7 = __uint_as_float(v[g8 * 8 + 7]) + b1.w;
+                    const uint32_t off = box + row_off + (((uint32_t(c8 >> 3) & 7u) ^ swz) << 4);
+                    if (HAS_RES) {
+                        const uint4 rv = lds128(res_stage + off);
+                        const float2 r0 = unpack_h2(rv.x), r1 = unpack_h2(rv.y), r2 = unpack_h2(rv.z), r3 = unpack_h2(rv.w);
+                        f0 += r0.x, f1 += r0.y, f2 += r1.x, f3 += r1.y;
+                        f4 += r2.x, f5 += r2.y, f6 += r3.x, f7 += r3.y;
                     }
+                    const uint32_t dst = tail_slab ? out_stage + box + uint32_t(r) * 64u + ((uint32_t(c8 >> 3) & 3u) << 4)
+                                                   : out_stage + off;
+                    sts128(dst, make_uint4(pack_h2(f0, f1), pack_h2(f2, f3), pack_h2(f4, f5), pack_h2(f6, f7)));
+                }
+            };
+            chunk(v0, c0);
+            if (two) {
+                tmem_ld_wait_dep(v1);  // (both loads were issued together: this is a no-op wait that pins the order)
+                chunk(v1, c0 + 32);
+            }
+            fence_proxy_async_smem();
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            if (lead) {
+                tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + c0, x0, y0, n0);
+                bulk_commit();
+                if (HAS_RES && sl + 2 < nslab) {
+                    bar_expect_tx(rfull, a_bytes);
+                    tma4<false>(res_stage + box, &tmRes, rfull, col0 + c0 + 128, x0, y0, n0);
                 }
             }
         }
@@ -1360,7 +1380,7 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
 }
 
 #define SW_LEAN_KERNEL(NAME, PAIR, RES)                                                                            \
-    __global__ void __launch_bounds__(kThreads)                                                                    \
+    __global__ void __launch_bounds__(kThreadsLean, 2)                                                                \
         NAME(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,                   \
              const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,                   \
              const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut32,               \
@@ -1489,10 +1509,10 @@ __global__ void __launch_bounds__(kThreads)
                         bar_expect_tx(fb, tx_bytes);
                         if (j < nkb1) {
                             tma4<false>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                            tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + j * BK, bcol0);
+                            tma_b<false>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
                         } else {
                             tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
-                            tma2<false>(sa + A_STAGE_BYTES, &tmB, fb, tapbase + p.c1 + (j - nkb1) * BK, bcol0);
+                            tma_b<false>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                         }
                     }
                     if (++j == per_tap) {
@@ -2193,7 +2213,15 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     } else {
         tA2 = tA1;
     }
-    {
+    a.w_kmajor = p->w_kmajor ? 1 : 0;
+    if (a.w_kmajor) {
+        if (p->w_ld > 0) return swh::fail(-1, "sw_igemm: k-block-major weights are dense (w_ld must be 0)");
+        const uint64_t dims[3] = {64, uint64_t(p->cout), uint64_t(kblocks)};
+        const uint64_t str[2] = {128, uint64_t(p->cout) * 128};
+        const uint32_t box[3] = {64, uint32_t(pair ? bn / 2 : bn), 1};
+        int rc = swh::encode_tmap_f16(&tB, p->wgt, 3, dims, str, box);
+        if (rc) return rc;
+    } else {
         const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout)};
         const uint64_t str[1] = {(p->w_ld > 0 ? uint64_t(p->w_ld) : uint64_t(ktotal)) * 2};
         const uint32_t box[2] = {64, uint32_t(pair ? bn / 2 : bn)};
@@ -2273,12 +2301,12 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             cudaStream_t st_ = static_cast<cudaStream_t>(stream);
             if (!pair) {
                 auto kern = p->residual ? k_igemm_lean_r : k_igemm_lean;
-                SW_CUDA_OK(swh::launch_pdl(kern, dim3(grid_x, ntile, 1), dim3(kThreads), size_t(smem), st_, 1, tA1, tA2, tB,
-                                           tOut, tRes, tOut32, a));
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3(grid_x, ntile, 1), dim3(kThreadsLean), size_t(smem), st_, 1, tA1, tA2,
+                                           tB, tOut, tRes, tOut32, a));
             } else {
                 auto kern = p->residual ? k_igemm2_lean_r : k_igemm2_lean;
-                SW_CUDA_OK(swh::launch_pdl(kern, dim3((grid_x + 1) / 2 * 2, ntile, 1), dim3(kThreads), size_t(smem), st_, 2,
-                                           tA1, tA2, tB, tOut, tRes, tOut32, a));
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3((grid_x + 1) / 2 * 2, ntile, 1), dim3(kThreadsLean), size_t(smem), st_,
+                                           2, tA1, tA2, tB, tOut, tRes, tOut32, a));
             }
             return 0;
         }
@@ -2374,15 +2402,4 @@ extern "C" int sw_igemm_rs(const sw_igemm_params* p, const sw_peers* peers, int 
 }
 
 // Probe builds (-DSW_TRACE) only: copies the per-CTA phase stamps of the last launches to the host.
-extern "C" int sw_trace_dump(unsigned long long* host, int ctas) {
-#ifdef SW_TRACE
-    if (!host || ctas <= 0 || ctas > kTraceCtas) return swh::fail(-1, "sw_trace_dump: bad arguments");
-    SW_CUDA_OK(cudaDeviceSynchronize());
-    SW_CUDA_OK(cudaMemcpyFromSymbol(host, g_sw_trace, size_t(ctas) * kTraceSlots * sizeof(unsigned long long)));
-    return 0;
-#else
-    (void)host;
-    (void)ctas;
-    return swh::fail(-1, "sw_trace_dump: library built without SW_TRACE");
-#endif
-}
+SW_TRACE_DUMP_FN(sw_trace_dump)

@@ -293,8 +293,13 @@ __global__ void __launch_bounds__(1024)
                int silu, int rows_per_cta, int rows_per_pass, int c_total) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
+    if (threadIdx.x == 0) {
+        TR(0);
+        TRG(11);
+    }
     pdl_trigger();
     pdl_wait();
+    if (threadIdx.x == 0) TR(1);
     extern __shared__ __align__(16) uint8_t gsm[];
     __shared__ float s_all[16 * 64 * 2];  // [rank][group][2], written by every CTA of the cluster
     __shared__ float s_mean[64], s_rstd[64];
@@ -361,10 +366,30 @@ __global__ void __launch_bounds__(1024)
             dst[2 * i + 1] = ss[i];
         }
     }
+    if (threadIdx.x == 0) TR(2);
     __syncthreads();
-    for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {  // per-channel totals over the row passes (fixed order)
+    if (threadIdx.x == 0) TR(3);
+    // per-channel totals over the row slots, in a fixed order (bit-reproducible) but spread over the whole CTA:
+    // stage 1 folds slots part, part + 8, ... into slot `part`; stage 2 folds those eight
+    constexpr int kParts = 8;
+    for (int i = threadIdx.x; i < c * kParts; i += blockDim.x) {
+        const int ch = i % c, part = i / c;
+        if (part < rows_per_pass) {
+            float a = 0.0f, b = 0.0f;
+            for (int k = part; k < rows_per_pass; k += kParts) {
+                a += sh[(size_t(k) * c + ch) * 2];
+                b += sh[(size_t(k) * c + ch) * 2 + 1];
+            }
+            // (slot `part` is only read by this thread in stage 1: safe to overwrite in place)
+            sh[(size_t(part) * c + ch) * 2] = a;
+            sh[(size_t(part) * c + ch) * 2 + 1] = b;
+        }
+    }
+    __syncthreads();
+    for (int ch = threadIdx.x; ch < c; ch += blockDim.x) {
         float a = 0.0f, b = 0.0f;
-        for (int k = 0; k < rows_per_pass; ++k) {
+        const int np = rows_per_pass < kParts ? rows_per_pass : kParts;
+        for (int k = 0; k < np; ++k) {
             a += sh[(size_t(k) * c + ch) * 2];
             b += sh[(size_t(k) * c + ch) * 2 + 1];
         }
@@ -385,7 +410,9 @@ __global__ void __launch_bounds__(1024)
         remote[(crank * 64 + g) * 2] = a;
         remote[(crank * 64 + g) * 2 + 1] = b;
     }
+    if (threadIdx.x == 0) TR(4);
     cluster.sync();  // release / acquire: every partial of the image is now in this CTA's s_all
+    if (threadIdx.x == 0) TR(5);
     if (threadIdx.x < groups) {
         const int g = threadIdx.x;
         float a = 0.0f, b = 0.0f;
@@ -432,6 +459,17 @@ __global__ void __launch_bounds__(1024)
         }
         *reinterpret_cast<uint4*>(out + size_t(r) * c_total) = make_uint4(o[0], o[1], o[2], o[3]);
     }
+#ifdef SW_TRACE
+    if (threadIdx.x == 0) {
+        TR(6);
+        TRG(12);
+        trace_value(13, trace_smid());
+        trace_value(14, (unsigned long long)blockDim.x | ((unsigned long long)rows_per_cta << 16) |
+                            ((unsigned long long)rows_per_pass << 32));
+        trace_value(15, (unsigned long long)gridDim.x | ((unsigned long long)gridDim.y << 20) |
+                            ((unsigned long long)gridDim.z << 40));
+    }
+#endif
 }
 
 // ---- LayerNorm: one warp per row, row cached in registers (c <= 2048).
@@ -599,17 +637,36 @@ static GnFusedGeom gn_fused_geom(int n, int hw, int c, int groups) {
     for (int sl = 8; sl >= 1; sl >>= 1) {
         if (groups % sl || ((groups / sl) * cgw) % 8) continue;
         const int cs = c / sl, octs = cs / 8;
-        int rpp = 512 / octs;
-        if (rpp < 1) rpp = 1;
-        if (rpp > hw) rpp = hw;
-        // largest cluster (<= 16 CTAs) that still gives every CTA a full pass of rows; more CTAs per image
-        // = more SMs pulling the tensor in (one SM ingests ~40 B/clk)
-        for (int cl = 16; cl >= 1; cl >>= 1) {
-            int rpc = (hw + cl - 1) / cl;
-            rpc = (rpc + rpp - 1) / rpp * rpp;
+        int rpp_max = 512 / octs;
+        if (rpp_max < 1) rpp_max = 1;
+        if (rpp_max > hw) rpp_max = hw;
+        // largest cluster (<= 16 CTAs) whose CTAs all own rows; the rows of a CTA are walked in equal passes
+        // (rows per pass fitted to the CTA's share instead of a fixed 512 threads' worth: with the fixed pass the
+        // 64x64x320 map only qualified for clusters of 4 = 64 CTAs, and the SiLU arithmetic of the apply phase --
+        // ~8 elements per clock per SM -- ran on 64 SMs; scripts/trace_gn.py).  More CTAs per image = more SMs
+        // pulling the tensor in and sharing the arithmetic.
+        // clusters of 4 first, then larger, then smaller: measured (scripts/trace_gn.py sweep, profiles/r2_*) a
+        // cluster of 4 wins whenever an image's slice fits four CTAs' shared memory (the all-to-all exchange of
+        // partial sums and the co-scheduling of 16 CTAs in one GPC cost more than the extra SMs give); bigger
+        // tensors need the bigger clusters anyway
+        static int first_cl = -1;  // SW_GN_MAXCL: cluster size tried first (tuning hook)
+        if (first_cl < 0) {
+            const char* e = getenv("SW_GN_MAXCL");
+            first_cl = e ? atoi(e) : 4;
+            if (first_cl != 1 && first_cl != 2 && first_cl != 4 && first_cl != 8 && first_cl != 16) first_cl = 4;
+        }
+        int order[5], no = 0;
+        for (int cl = first_cl; cl <= 16; cl <<= 1) order[no++] = cl;
+        for (int cl = first_cl >> 1; cl >= 1; cl >>= 1) order[no++] = cl;
+        for (int oi = 0; oi < no; ++oi) {
+            const int cl = order[oi];
+            const int rows = (hw + cl - 1) / cl;
+            const int passes = (rows + rpp_max - 1) / rpp_max;
+            const int rpp = (rows + passes - 1) / passes;
+            const int rpc = rpp * passes;
             if (cl > 1 && rpc * (cl - 1) >= hw) continue;  // trailing CTAs would own no rows
             const size_t smem = size_t(rpc) * cs * 2 + (size_t(rpp) * cs * 2 + size_t(cs) * 2) * sizeof(float);
-            if (smem > 216 * 1024) break;  // smaller clusters only need more
+            if (smem > 216 * 1024) continue;
             if (sl > 1 && long(n) * cl * sl > 2L * sms) break;  // enough CTAs already: use coarser slices
             g.rows_per_pass = rpp;
             g.threads = (octs * rpp + 31) / 32 * 32;
@@ -763,3 +820,6 @@ extern "C" int sw_softmax_rows(const void* x, void* y, int rows, int cols, float
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }
+
+// Probe builds (-DSW_TRACE) only: per-CTA phase stamps of the last GroupNorm launch.
+SW_TRACE_DUMP_FN(sw_trace_dump_gn)

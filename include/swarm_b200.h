@@ -105,6 +105,11 @@ typedef struct {
     float ln_eps;
     int32_t cluster_k;   /* 0 / 1 = off, 2 = split K over a cluster of two CTAs (partials meet in distributed shared memory) when eligible */
     int32_t persist;     /* 0 = auto, 1 = one tile per CTA, 2 = persistent CTAs with double-buffered accumulators when possible */
+    int32_t w_kmajor;    /* 0: wgt is [cout, kh*kw*(c1+c2)] row-major.  1: wgt is packed k-block-major,
+                            [k-blocks][cout][64] fp16, k-block = (filter tap, 64-channel slab of a1, then of a2), slabs
+                            zero-padded to 64 channels: every weight tile the kernel fetches is then one contiguous
+                            run of memory (sequential DRAM bursts instead of one 128-byte segment per row), which is
+                            what weight-streaming layers (few pixels, 1280 channels) are bound by */
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);
@@ -294,6 +299,8 @@ typedef struct {
     int32_t xin_ld;
     const float* coef;      /* fp32 [steps, 8] */
     const int32_t* step_idx;/* device step counter (NULL = row 0) */
+    const float* guidance;  /* optional device fp32 [2] = {g_text, g_image}: overrides the scalars above, so one
+                               captured CUDA graph serves every guidance value (NULL = use the scalars) */
 } sw_sched_params;
 
 int sw_sched_step(const sw_sched_params* p, void* stream);

@@ -30,6 +30,9 @@ shapes = [  # (M, N, K, geglu, residual)
     (512, 1280, 1280, 0, 1), (512, 3840, 1280, 0, 0), (512, 10240, 1280, 1, 0), (512, 1280, 5120, 0, 1),
     (128, 1280, 1280, 0, 1),
 ]
+# conv layers (weight streaming at the deep levels): (n, h, w, cin, cout, ksize) -- traced through the same path
+conv_shapes = [(2, 8, 8, 1280, 1280, 3), (2, 16, 16, 1280, 1280, 3), (2, 8, 8, 2560, 1280, 3), (2, 32, 32, 640, 640, 3),
+               (2, 64, 64, 320, 320, 3)]
 flt = sys.argv[1] if len(sys.argv) > 1 else ""
 lib = nat.lib()
 lib.sw_trace_dump.argtypes = [C.c_void_p, C.c_int]
@@ -60,21 +63,42 @@ def med(x):
     return float(np.median(x)) if len(x) else float("nan")
 
 
-for (m, n, k, geglu, res) in shapes:
-    if flt and flt not in f"{m},{n},{k}":
-        continue
-    x = torch.randn(m, k, device=dev, dtype=torch.float16)
-    w = torch.randn(n, k, device=dev, dtype=torch.float16) * k ** -0.5
-    b = torch.randn(n, device=dev, dtype=torch.float16)
-    nout = n // 2 if geglu else n
-    out = torch.empty(m, nout, device=dev, dtype=torch.float16)
-    r = torch.randn(m, nout, device=dev, dtype=torch.float16) if res else None
-    act = nat.ACT_GEGLU if geglu else nat.ACT_NONE
+from chiaswarm_b200.ops.packing import pack_conv_weight
 
-    def run(**kw):
-        return nat.igemm(x, w, out, n=1, h=1, w=m, bias=b, residual=r, act=act, splitk_scratch=scratch, **kw)
+work = [("lin", sh) for sh in shapes] + [("conv", sh) for sh in conv_shapes]
+for kind, sh in work:
+    if kind == "lin":
+        (m, n, k, geglu, res) = sh
+        if flt and flt not in f"{m},{n},{k}":
+            continue
+        x = torch.randn(m, k, device=dev, dtype=torch.float16)
+        w = torch.randn(n, k, device=dev, dtype=torch.float16) * k ** -0.5
+        b = torch.randn(n, device=dev, dtype=torch.float16)
+        nout = n // 2 if geglu else n
+        out = torch.empty(m, nout, device=dev, dtype=torch.float16)
+        r = torch.randn(m, nout, device=dev, dtype=torch.float16) if res else None
+        act = nat.ACT_GEGLU if geglu else nat.ACT_NONE
 
-    t_cublas = graph_time(lambda: F.linear(x, w, b))
+        def run(**kw):
+            return nat.igemm(x, w, out, n=1, h=1, w=m, bias=b, residual=r, act=act, splitk_scratch=scratch, **kw)
+
+        t_cublas = graph_time(lambda: F.linear(x, w, b))
+    else:
+        (cn, ch, cw, cin, cout, ks) = sh
+        if flt and flt not in f"conv{cn},{ch},{cw},{cin},{cout}":
+            continue
+        m, n, k, geglu, res = cn * ch * cw, cout, cin * ks * ks, 0, 0
+        x = torch.randn(cn, ch, cw, cin, device=dev, dtype=torch.float16)
+        w4 = torch.randn(cout, cin, ks, ks, device=dev, dtype=torch.float16) * k ** -0.5
+        w = pack_conv_weight(w4)
+        b = torch.randn(cout, device=dev, dtype=torch.float16)
+        out = torch.empty(m, cout, device=dev, dtype=torch.float16)
+        xn = x.permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last)
+
+        def run(**kw):
+            return nat.igemm(x, w, out, n=cn, h=ch, w=cw, kh=ks, kw=ks, pad=ks // 2, bias=b, splitk_scratch=scratch, **kw)
+
+        t_cublas = graph_time(lambda: F.conv2d(xn, w4, b, padding=ks // 2))
     for label, kw in (("auto", {}), ("s6", dict(stages=6, cta_pair=1, splitk_min_kb=64, persist=1, tile_n=128))):
         if geglu and label != "auto":
             continue
@@ -104,7 +128,7 @@ for (m, n, k, geglu, res) in shapes:
         d = lambda a, c: tr[:, a] - tr[:, c]
         span = (tr[:, 12].max() - tr[:, 11].min()) / 1e3
         kloop = d(6, 5)
-        print(f"({m},{n},{k}){'g' if geglu else ''}{'+r' if res else ''} {label}: cublas {t_cublas:5.1f} us  ours {t_ours:5.1f} us  "
+        print(f"{kind}({m},{n},{k}){'g' if geglu else ''}{'+r' if res else ''} {label}: cublas {t_cublas:5.1f} us  ours {t_ours:5.1f} us  "
               f"span {span:5.1f} us | grid {gx}x{gy}x{gz} bn {bn} stages {stages} splits {splits} pair {pair} ck {ck} tma_epi {tma_epi} "
               f"persist {pers} sms {len(set(tr[:, 13].tolist()))}\n"
               f"    clk: setup {med(d(1, 0)):6.0f} pdl {med(d(2, 1)):6.0f} tma0 {med(d(3, 2)):6.0f} lat0 {med(d(5, 3)):6.0f} "

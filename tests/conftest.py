@@ -6,6 +6,17 @@ import pytest
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
+@pytest.fixture(autouse=True)
+def _local_job_inputs(tmp_path, monkeypatch):
+    """The suite feeds images as data: / file:// URIs; a worker accepts those only when told to (net.py)."""
+    from chiaswarm_b200 import net
+
+    monkeypatch.setenv("SDAAS_LOCAL_INPUT_ROOT", str(tmp_path))
+    net.allow_local_inputs(True)
+    yield
+    net.allow_local_inputs(None)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (B200); skipped in the CPU tier")
 
