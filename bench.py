@@ -98,6 +98,106 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def torch_baseline(args, dev, prompts, gen, l2_flush, barrier, dist, world, images: int = 3):
+    """img/s of the eager-PyTorch restatement (pipe.backend = "torch") on the same GPU, same clocks, same
+    timed region as the headline (device-timed, L2 flushed, max over ranks).  The denominator of `vs_baseline`."""
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+
+    pipe = StableDiffusionPipeline.from_architecture(args.arch)
+    pipe.backend = "torch"
+    pipe.to(dev, torch.float16)
+    pipe.set_scheduler("dpmpp_2m", True)
+
+    def one(i):
+        return pipe(prompt=prompts[i % len(prompts)], negative_prompt="", height=args.size, width=args.size,
+                    num_inference_steps=args.denoise_steps, guidance_scale=7.5, generator=gen, output_type="device")
+
+    for i in range(3):
+        one(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(images):
+        l2_flush.zero_()
+        one(i)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    del pipe
+    torch.cuda.empty_cache()
+    return {"value": world * images / (float(t.item()) / 1e3), "unit": "images/s", "images": images,
+            "what": "eager PyTorch restatement of the same graph in this process (cuDNN conv, cuBLAS GEMM, SDPA); "
+                    "stands in for the reference, which cannot be installed here"}
+
+
+def sdxl_patch_latency(args, dev, runs: int = 3):
+    """One SDXL-base 1024x1024 image (30 DPM-Solver++ steps, CFG): latency on one GPU and patch-parallel over all
+    N ranks of this job (engine/patch_engine.py), device-timed, max over ranks, median of `runs`."""
+    import statistics
+
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+    from chiaswarm_b200.parallel import runtime
+
+    gang = runtime.init()
+    pipe = StableDiffusionPipeline.from_architecture("sdxl")
+    pipe.backend = "sm100"
+    pipe.to(dev, torch.float16)
+    pipe.set_scheduler("dpmpp_2m", True)
+    steps = args.sdxl_steps
+
+    def call(output_type):
+        g = torch.Generator(device=dev).manual_seed(4321)
+        return pipe(prompt="a single large image for the latency mode", negative_prompt="", height=1024, width=1024,
+                    num_inference_steps=steps, guidance_scale=7.5, generator=g, output_type=output_type)
+
+    def timed():
+        ts = []
+        for i in range(runs + 2):
+            torch.cuda.synchronize()
+            gang.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            call("device")
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                ts.append(gang.all_reduce_max(e0.elapsed_time(e1)))
+        return statistics.median(ts)
+
+    ref = call("latent").latents.float()
+    ms_1gpu = timed()          # every rank runs the same single-GPU job side by side; max over ranks
+    pipe.enable_patch_parallel(gang)
+    out = call("latent").latents.float()
+    err = ((out - ref).abs().max() / ref.abs().max().clamp_min(1e-3)).item()
+    err = gang.all_reduce_max(err if err == err else 1e9)
+    ms = timed()
+    eng = pipe._denoiser()
+    sg = next(v for k, v in eng._graphs.items() if k[0] == "patch")
+    torch.cuda.synchronize()
+    gang.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        sg.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    step_ms = gang.all_reduce_max(e0.elapsed_time(e1) / 10)
+    res = {"n": gang.world, "model": "sdxl-base architecture, 1024x1024, CFG 7.5, DPM-Solver++(2M) karras",
+           "denoise_steps": steps, "ms": ms, "ms_1gpu": ms_1gpu, "speedup": ms_1gpu / ms, "ms_per_step": step_ms,
+           "launches_per_step": sg.launches_per_step, "guidance_groups": sg.ctx.G, "strips": sg.ctx.P,
+           "rel_err_vs_single": err,
+           "timed_region": "text encode + denoise + VAE decode to uint8 (one image), CUDA events, max over ranks"}
+    del pipe
+    torch.cuda.empty_cache()
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -108,6 +208,11 @@ def main():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--denoise-steps", type=int, default=50)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-torch-baseline", action="store_true",
+                    help="skip the same-process eager-PyTorch comparator that fills vs_baseline")
+    ap.add_argument("--no-sdxl-patch", action="store_true",
+                    help="(N > 1) skip the SDXL 1024x1024 patch-parallel latency block")
+    ap.add_argument("--sdxl-steps", type=int, default=30)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -232,11 +337,28 @@ def main():
         e2e = {"value": world * args.steps / float(t.item()), "unit": "images/s", "h2d_bytes_per_step": tok_bytes,
                "d2h_bytes_per_step": img_bytes, "path": "generator.synchronous_do_work_function(job, Device) -> result dict (JPEG, base64, sha256)"}
 
+    # ---------------- same-box comparator: this repo's eager-PyTorch restatement of the same module graph
+    # (cuDNN / cuBLAS / SDPA -- the ops diffusers would issue).  NOT the reference (unavailable).
+    vs_baseline = baseline = None
+    if args.impl == "ours" and not args.no_torch_baseline:
+        baseline = torch_baseline(args, dev, prompts, gen, l2_flush, barrier, dist, world)
+        vs_baseline = value / baseline["value"] if baseline and baseline.get("value") else None
+
+    # ---------------- BASELINE.json's second half: single-image SDXL 1024x1024 latency, patch-parallel over the N ranks
+    sdxl_patch = None
+    if args.impl == "ours" and world > 1 and not args.no_sdxl_patch:
+        del pipe
+        torch.cuda.empty_cache()
+        try:
+            sdxl_patch = sdxl_patch_latency(args, dev)
+        except Exception as e:  # the headline line must still be printed
+            sdxl_patch = {"n": world, "error": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
         out = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "fp16", "data": "synthetic prompts + seeded latents; random-init weights of the named architecture",
+            "vs_baseline": vs_baseline, "dtype": "fp16", "data": "synthetic prompts + seeded latents; random-init weights of the named architecture",
             "impl": args.impl,
             "config": {"model": f"{args.arch} (Stable Diffusion 1.5 architecture)" if args.arch == "sd15" else args.arch,
                        "global_batch": world, "seq_len": (args.size // 8) ** 2, "parallelism": f"dp{world}",
@@ -245,6 +367,10 @@ def main():
                        "timed_region": "text encode + 50 x (UNet, CFG, scheduler) + VAE decode to uint8, per image"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
         }
+        if baseline is not None:
+            out["baseline_torch"] = baseline
+        if sdxl_patch is not None:
+            out["sdxl_patch"] = sdxl_patch
         print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()

@@ -8,7 +8,8 @@ same kwarg handling.  What changes on B200:
   * the reference's low-memory switches (xformers / VAE slicing+tiling / sequential CPU offload,
     triggered by VRAM < 12-16 GB or num_images_per_prompt > 1, lines 76-94) are accepted and
     ignored: 180 GB of HBM3e keeps everything resident (Q4);
-  * `pipeline_config` is a plain dict copy of the model index (Q6).
+  * `pipeline_config` is a plain dict copy of the model index (Q6);
+  * a job may own a gang of 2 / 4 / 8 GPUs (`parallel.context.job_gang()`), see the call below.
 """
 from __future__ import annotations
 
@@ -17,6 +18,7 @@ import logging
 import torch
 
 from ..output_processor import OutputProcessor
+from ..parallel.context import job_gang
 from ..registry import resolve
 from ..utils.weight_cache import pipeline_cache
 from .pipelines import build_pipeline
@@ -74,7 +76,9 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
     pipeline = pipeline_cache().get(key, load)
     pipeline.set_scheduler(scheduler_type, use_karras_sigmas=True)
 
-    p = pipeline(**kwargs)
+    # a job that leased a gang (parallel/gang_worker.py) runs SPMD on every rank of it: one large image goes
+    # patch-parallel, a batch is split across the ranks; without a lease this is the reference's one-GPU call
+    p = pipeline(gang=job_gang(), **kwargs)
 
     pipeline_config = dict(pipeline.config)
     # any flagged image flags the whole result

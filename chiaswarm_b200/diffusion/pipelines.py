@@ -239,7 +239,11 @@ class StableDiffusionPipeline:
     def __call__(self, prompt="", negative_prompt=None, height=None, width=None, num_inference_steps=50,
                  guidance_scale=7.5, num_images_per_prompt=1, generator=None, image=None, mask_image=None,
                  strength=0.8, image_guidance_scale=1.5, controlnet_conditioning_scale=1.0, eta=0.0,
-                 cross_attention_kwargs=None, output_type="pil", latents=None, prompt_embeds=None, **ignored):
+                 cross_attention_kwargs=None, output_type="pil", latents=None, prompt_embeds=None, gang=None,
+                 **ignored):
+        """`gang` (parallel.runtime.Gang, every rank making this same call with the same seed): a single image runs
+        patch-parallel over it (engine/patch_engine.py), a batch is split over it (each rank denoises and decodes
+        batch / world images; the images are all-gathered, so every rank returns the full set)."""
         prompts = [prompt] if isinstance(prompt, str) else list(prompt)
         if negative_prompt is None:
             negative = [""] * len(prompts)
@@ -268,6 +272,12 @@ class StableDiffusionPipeline:
         if mode == "sd_inpaint" and mask_image is None:
             raise ValueError("inpainting needs a mask image")
 
+        image_list = None  # a list of equally sized input images: one per batch element (video frames)
+        if isinstance(image, (list, tuple)):
+            image_list = [_fit_multiple(im, vae_scale) for im in image]
+            if len(image_list) != batch or len({im.size for im in image_list}) != 1:
+                raise ValueError("a list of input images needs one image per prompt, all of the same size")
+            image = image_list[0]
         if image is not None:
             image = _fit_multiple(image, vae_scale)
             width, height = image.size
@@ -318,8 +328,12 @@ class StableDiffusionPipeline:
                     init_latents = (self.vae.encode(img, generator) * self.vae.scaling_factor).float()
                     init_latents = (init_latents, m8.float(), randn().float())
             elif pix2pix:
-                img_lat = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), sample=False)
-                img_lat = img_lat.expand(batch, -1, -1, -1)
+                if image_list is not None:
+                    img_lat = self.vae.encode(torch.cat([pil_to_tensor(im, self.device, self.dtype)
+                                                         for im in image_list]), sample=False)
+                else:
+                    img_lat = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), sample=False)
+                    img_lat = img_lat.expand(batch, -1, -1, -1)
                 zeros = torch.zeros_like(img_lat)
                 extra = torch.cat([img_lat, img_lat, zeros]) if n_cond == 3 else img_lat
             elif mode == "sd_controlnet":
@@ -335,16 +349,43 @@ class StableDiffusionPipeline:
         if plan.needs_noise:
             noise_table = torch.stack([randn().float() for _ in range(plan.num_steps)])
 
-        denoiser = self._denoiser()
+        # ---- gang execution shape: batch split > patch parallel > replicated
+        split = patch = None
+        if gang is not None and gang.world > 1:
+            if batch > 1 and batch % gang.world == 0 and init_latents is None:
+                split = gang
+            elif batch == 1 and control is None and init_latents is None:
+                patch = gang
+        if split is not None:
+            bl = batch // split.world
+            lo, hi = split.rank * bl, (split.rank + 1) * bl
+
+            def cut(t):  # [n_cond * batch, ...] stacked branch-major -> this rank's images of every branch
+                return None if t is None else t.reshape(n_cond, batch, *t.shape[1:])[:, lo:hi].reshape(
+                    n_cond * bl, *t.shape[1:])
+
+            x, embeds, extra, control = x[lo:hi], cut(embeds), cut(extra), cut(control)
+            if added is not None:
+                added = {k: cut(v) for k, v in added.items()}
+            if noise_table is not None:
+                noise_table = noise_table[:, lo:hi]
+
+        denoiser = self._denoiser(patch)
         with timer.stage("denoise"):
             x = denoiser.run(x=x, embeds=embeds, plan=plan, n_cond=n_cond, g_text=float(guidance_scale),
                              g_image=float(image_guidance_scale), extra=extra, control=control,
                              control_scale=float(controlnet_conditioning_scale), added=added, noise=noise_table,
                              inpaint=init_latents)
         if output_type == "latent":
+            if split is not None:
+                x = split.all_gather_cat(x)
             return PipelineOutput(images=[], latents=x, timings=timer.result() if timer.enabled else {})
         with timer.stage("vae_decode"):
             images = denoiser.decode(x / self.vae.scaling_factor)
+        if split is not None:  # every rank ends up with the whole batch, in batch order
+            with timer.stage("gather"):
+                images = split.all_gather_cat(images)
+                x = split.all_gather_cat(x)
         if output_type == "device":  # leave the decoded batch on the GPU (benchmarks, chained stages)
             out = PipelineOutput(images=[], latents=x, timings=timer.result() if timer.enabled else {})
             out.device_images = images
@@ -371,37 +412,58 @@ class StableDiffusionPipeline:
 
     def enable_patch_parallel(self, gang):
         """Single-image jobs run patch-parallel over `gang` (engine/patch_engine.py); every rank of the
-        gang must then issue the same pipeline calls with the same seeds."""
+        gang must then issue the same pipeline calls with the same seeds.  (Per call: `pipe(..., gang=gang)`.)"""
         self.patch_gang = gang if gang is not None and gang.world > 1 else None
-        self._engine = None
 
-    def _denoiser(self):
+    def _denoiser(self, gang=None):
+        """The engine for this call: one per gang identity (a gang's engine owns its symmetric arena and captured
+        patch plans), plus the single-GPU engine; all stay resident with the pipeline."""
+        gang = gang if gang is not None else getattr(self, "patch_gang", None)
+        if gang is not None and gang.world <= 1:
+            gang = None
         if self._engine is None:
+            self._engine = {}
+        key = None if gang is None else (gang.global_ranks or ("world", gang.world))
+        eng = self._engine.get(key)
+        if eng is None:
             if self.backend == "sm100":
                 if self.device.type != "cuda":
                     raise RuntimeError("the sm100 backend needs a CUDA device")
                 from ..engine.denoiser import SM100Denoiser
 
-                if getattr(self, "patch_gang", None) is not None:
+                if gang is not None:
                     from ..engine.patch_engine import PatchDenoiser
 
-                    self._engine = PatchDenoiser(self, self.patch_gang)
+                    eng = PatchDenoiser(self, gang)
                 else:
-                    self._engine = SM100Denoiser(self)
+                    eng = SM100Denoiser(self)
             else:
-                self._engine = TorchDenoiser(self)
-        return self._engine
+                eng = TorchDenoiser(self, gang)
+            self._engine[key] = eng
+        return eng
 
 
 class TorchDenoiser:
     """Eager reference loop: what diffusers would issue (cuDNN / cuBLAS / SDPA on CUDA)."""
 
-    def __init__(self, pipe: StableDiffusionPipeline):
+    def __init__(self, pipe: StableDiffusionPipeline, gang=None):
         self.pipe = pipe
+        self.gang = gang  # patch-parallel over torch.distributed collectives (parallel/patch.py): CPU / baseline
 
     @torch.no_grad()
-    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint):
+    def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint,
+            num_frames: int = 1):
         p = self.pipe
+        unet = p.unet
+        if self.gang is not None and control is None:
+            from ..parallel.patch import PatchParallelUNet
+
+            pp = PatchParallelUNet(p.unet, self.gang)
+            try:
+                pp.split(x)  # raises when the rows do not divide over the gang at every level
+                unet = lambda mi, t, e, down, mid, add: pp(mi, t, e, add)  # noqa: E731
+            except ValueError:
+                pass
         x0_prev = None
         scale = plan.first_scale
         for i in range(plan.num_steps):
@@ -412,7 +474,7 @@ class TorchDenoiser:
             down = mid = None
             if control is not None:
                 down, mid = p.controlnet(model_in, t, embeds, control, control_scale)
-            out = p.unet(model_in, t, embeds, down, mid, added)
+            out = unet(model_in, t, embeds, down, mid, added)
             out = schedulers.guided(out.float(), n_cond, g_text, g_image)
             x, x0_prev, scale = schedulers.apply_step_torch(plan, i, x, out, x0_prev,
                                                             None if noise is None else noise[i])

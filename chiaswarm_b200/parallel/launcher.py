@@ -6,8 +6,13 @@ complete `Worker` bound to its device (resident weights, its own CUDA graphs) th
 on its own.  A child that dies is restarted after a back-off (its in-flight job is simply not
 reported, so the hive re-issues it -- the non-fatal path of the reference's error taxonomy).
 
+With `settings.parallel_mode` = gang / patch / auto and `gang_size` > 1 the launcher instead starts the gang
+server (parallel/gang_worker.py): one hive client, one rank process per GPU in a single torch.distributed world,
+gangs of 1 / 2 / 4 / 8 ranks leased per job.
+
   python -m chiaswarm_b200.parallel.launcher            # all visible GPUs
   python -m chiaswarm_b200.parallel.launcher --gpus 0,1,2,3
+  SDAAS_PARALLEL_MODE=gang SDAAS_GANG_SIZE=8 python -m chiaswarm_b200.parallel.launcher
 """
 from __future__ import annotations
 
@@ -106,6 +111,17 @@ def main(argv=None):
     if not gpus:
         print("CUDA not present. Quitting.")
         return 1
+    from ..settings import load_settings
+    from .gang_worker import GANG_MODES, serve
+
+    settings = load_settings()
+    if str(settings.parallel_mode).lower() in GANG_MODES and int(settings.gang_size) > 1:
+        # gang mode: ONE hive client in this process, one rank process per GPU in one torch.distributed world;
+        # jobs lease 1 / 2 / 4 / 8 ranks from the RankGroup (parallel/gang_worker.py)
+        if args.gpus:
+            os.environ["CUDA_VISIBLE_DEVICES"] = args.gpus
+        serve(settings, len(gpus))
+        return 0
     Supervisor(gpus).run()
     return 0
 

@@ -51,7 +51,8 @@ def init(backend: Optional[str] = None) -> "Gang":
             kw["device_id"] = torch.device("cuda", env_local_rank())
         dist.init_process_group(backend, **kw)
     device = torch.device("cuda", env_local_rank()) if use_cuda else torch.device("cpu")
-    return Gang(rank=env_rank(), world=world, group=dist.group.WORLD if world > 1 else None, device=device)
+    return Gang(rank=env_rank(), world=world, group=dist.group.WORLD if world > 1 else None, device=device,
+                global_ranks=tuple(range(world)))
 
 
 @dataclass
@@ -60,6 +61,7 @@ class Gang:
     world: int
     group: Optional[object]
     device: torch.device
+    global_ranks: tuple = ()   # world ranks of the members (identity of the gang: keys engine caches)
 
     def barrier(self):
         if self.world > 1:
@@ -72,15 +74,43 @@ class Gang:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         return float(t.item())
 
+    def all_gather_cat(self, t: torch.Tensor) -> torch.Tensor:
+        """Concatenates every rank's `t` along dim 0 in rank order; leading dims may differ between ranks (the
+        batch / frame scatter of gang jobs hands the last rank a shorter slice)."""
+        if self.world == 1:
+            return t
+        t = t.contiguous()
+        counts = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+        all_counts = [torch.zeros_like(counts) for _ in range(self.world)]
+        dist.all_gather(all_counts, counts, group=self.group)
+        counts = [int(c.item()) for c in all_counts]
+        cap = max(counts)
+        if t.shape[0] < cap:
+            pad = torch.zeros((cap - t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            t = torch.cat([t, pad])
+        parts = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(parts, t, group=self.group)
+        return torch.cat([p[:c] for p, c in zip(parts, counts)])
+
+    def shard(self, count: int) -> range:
+        """This rank's contiguous share of `count` items (the first ranks take the remainder)."""
+        base, extra = divmod(count, self.world)
+        lo = self.rank * base + min(self.rank, extra)
+        return range(lo, lo + base + (1 if self.rank < extra else 0))
+
     def subgang(self, ranks: Sequence[int]) -> "Gang":
         """Aligned sub-gang (every rank of the parent must call this with the same list)."""
         ranks = list(ranks)
         if len(ranks) == self.world:
             return self
+        if len(ranks) == 1:  # a lone rank needs no process group
+            return Gang(rank=0 if ranks[0] == self.rank else -1, world=1, group=None, device=self.device,
+                        global_ranks=tuple(ranks))
         grp = dist.new_group(ranks)
         if self.rank not in ranks:
-            return Gang(rank=-1, world=len(ranks), group=None, device=self.device)
-        return Gang(rank=ranks.index(self.rank), world=len(ranks), group=grp, device=self.device)
+            return Gang(rank=-1, world=len(ranks), group=None, device=self.device, global_ranks=tuple(ranks))
+        return Gang(rank=ranks.index(self.rank), world=len(ranks), group=grp, device=self.device,
+                    global_ranks=tuple(ranks))
 
 
 @dataclass

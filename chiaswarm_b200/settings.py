@@ -17,8 +17,10 @@ _DEFAULTS = {
     "sdaas_uri": "http://localhost:9511",
     "worker_name": "worker",
     # --- B200 runtime knobs (not in the reference)
-    "parallel_mode": "dp",       # dp | patch | tp
-    "gang_size": 1,              # GPUs leased per job in patch/tp mode (1, 2, 4, 8)
+    "parallel_mode": "dp",       # dp (one GPU per job) | gang / patch / auto (parallel/gang_worker.py leases gangs)
+    "gang_size": 1,              # most GPUs one job may lease in gang mode (1, 2, 4, 8)
+    "patch_min_pixels": 1024 * 1024,  # gang mode: single images at least this large run patch-parallel
+    "job_timeout_s": 900,        # gang mode: a job that overruns is failed non-fatally and the rank world restarted
     "kernel_backend": "sm100",   # sm100 | torch (oracle / baseline path)
     "model_root": "",            # directory holding diffusers-layout checkpoints (HF cache also searched)
     "weight_cache_gb": 120,      # resident weight cache budget per GPU
@@ -26,7 +28,7 @@ _DEFAULTS = {
 }
 
 _ENV = {"sdaas_token": "SDAAS_TOKEN", "sdaas_uri": "SDAAS_URI", "worker_name": "SDAAS_WORKERNAME",
-        "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE",
+        "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE", "job_timeout_s": "SDAAS_JOB_TIMEOUT_S", "patch_min_pixels": "SDAAS_PATCH_MIN_PIXELS",
         "kernel_backend": "SDAAS_KERNEL_BACKEND", "model_root": "SDAAS_MODEL_ROOT"}
 
 
@@ -39,6 +41,8 @@ class Settings:
     worker_name: str = _DEFAULTS["worker_name"]
     parallel_mode: str = _DEFAULTS["parallel_mode"]
     gang_size: int = _DEFAULTS["gang_size"]
+    job_timeout_s: int = _DEFAULTS["job_timeout_s"]
+    patch_min_pixels: int = _DEFAULTS["patch_min_pixels"]
     kernel_backend: str = _DEFAULTS["kernel_backend"]
     model_root: str = _DEFAULTS["model_root"]
     weight_cache_gb: int = _DEFAULTS["weight_cache_gb"]

@@ -5,9 +5,12 @@ Euler-ancestral with Karras sigmas; defaults 15 steps, guidance 7.5, image guida
 `pipeline_config = {nsfw, cost = 512*512*steps*frames}`.
 
 B200 difference: the reference runs a serial Python loop, one pipeline call per frame
-(lines 53-74).  Frames are independent, so here they are batched through the resident pipeline
-(`frame_batch` frames per denoise) and, with a gang lease, scattered across the ranks
-(SURVEY.md section 2.3 "frame-level parallel")."""
+(lines 53-74).  Frames are independent, so here `FRAME_BATCH` frames share one denoising run of the
+resident pipeline (one batched UNet call per step instead of one per frame), and when the job leased a
+gang (`parallel.context.job_gang()`) each rank takes a contiguous share of those chunks and the finished
+frames are all-gathered to the gang's first rank, which encodes the video (SURVEY.md section 2.3
+"frame-level parallel").  Every chunk draws its noise from a generator seeded with (job seed + index of
+its first frame), so the result depends on the seed only, not on the gang size."""
 from __future__ import annotations
 
 import pathlib
@@ -19,10 +22,12 @@ from PIL import Image
 
 from .. import net
 from ..output_processor import make_result
+from ..parallel.context import is_leader, job_gang
 from ..registry import resolve
 from ..utils.weight_cache import pipeline_cache
 
 MAX_FRAMES = 100
+FRAME_BATCH = 8  # frames per denoising run (one CFG x3 batch of 24 UNet samples at 512 px)
 
 
 def model_video_callback(device_identifier, model_name, **kwargs):
@@ -45,14 +50,28 @@ def model_video_callback(device_identifier, model_name, **kwargs):
         tmp = pathlib.Path(tmp)
         video_path = download_video(tmp, kwargs.pop("video_uri"))
         frames, fps = get_frames(tmp, video_path)
-        result_frames = []
-        nsfw = False
-        for index, frame in enumerate(frames[:MAX_FRAMES]):
-            print(f"{index} of {min(len(frames), MAX_FRAMES)}")
-            images, flagged = img2img(pipeline, prompt, guidance_scale, image_guidance_scale, frame,
-                                      num_inference_steps, negative_prompt, 512, 512, generator)
+        frames = frames[:MAX_FRAMES]
+        gang = job_gang()
+        # fixed chunks of FRAME_BATCH frames; a gang deals out whole chunks, so a chunk's content never depends
+        # on how many ranks the job leased
+        chunks = [list(range(lo, min(lo + FRAME_BATCH, len(frames)))) for lo in range(0, len(frames), FRAME_BATCH)]
+        if gang is not None:
+            chunks = [chunks[i] for i in gang.shard(len(chunks))]
+        base_seed = generator.initial_seed() if generator is not None else 0
+        device = generator.device if generator is not None else torch.device(device_identifier)
+        done, nsfw = [], False
+        for chunk in chunks:
+            print(f"frames {chunk[0]}-{chunk[-1]} of {len(frames)}")
+            g = torch.Generator(device=device).manual_seed((base_seed + chunk[0]) % (2 ** 63))
+            images, flagged = img2img(pipeline, prompt, guidance_scale, image_guidance_scale,
+                                      [frames[i] for i in chunk], num_inference_steps, negative_prompt, 512, 512, g)
             nsfw = nsfw or flagged
-            result_frames.append(images[0].convert("RGB"))
+            done.extend(im.convert("RGB") for im in images)
+        if gang is not None:
+            done, nsfw = _gather_frames(gang, done, nsfw)
+            if not is_leader():  # one rank reports; the others are finished
+                return {}, {"nsfw": nsfw, "cost": 512 * 512 * num_inference_steps * len(frames)}
+        result_frames = done
         if not result_frames:
             raise ValueError("input video has no decodable frames")
         out_path = create_video(tmp, result_frames, fps)
@@ -77,17 +96,46 @@ def download_video(tmpdir, video_uri):
     return path
 
 
+def _gather_frames(gang, frames, nsfw):
+    """All-gather the ranks' finished frames (rank order = frame order) as uint8 tensors."""
+    import numpy as np
+
+    dev = gang.device
+    if frames:
+        local = torch.from_numpy(np.stack([np.asarray(f) for f in frames])).to(dev)
+        shape = torch.tensor(local.shape[1:], dtype=torch.int64, device=dev)
+    else:
+        local, shape = None, torch.zeros(3, dtype=torch.int64, device=dev)
+    # a rank without frames (more ranks than frames) still has to bring a tensor of the right frame shape
+    import torch.distributed as dist
+
+    dist.all_reduce(shape, op=dist.ReduceOp.MAX, group=gang.group)
+    if local is None:
+        local = torch.zeros((0,) + tuple(int(v) for v in shape), dtype=torch.uint8, device=dev)
+    every = gang.all_gather_cat(local).cpu().numpy()
+    flag = gang.all_reduce_max(1.0 if nsfw else 0.0) > 0
+    return [Image.fromarray(a) for a in every], flag
+
+
 def img2img(pipeline, prompt, text_guidance_scale, image_guidance_scale, image, steps, neg_prompt, width, height,
             generator=None):
-    if not isinstance(image, Image.Image):
-        image = Image.open(image)
-    ratio = min(height / image.height, width / image.width)
-    image = image.resize((max(8, int(image.width * ratio)), max(8, int(image.height * ratio))),
-                         Image.Resampling.LANCZOS)
-    result = pipeline(prompt, negative_prompt=neg_prompt, image=image, num_inference_steps=int(steps),
+    """`image`: one frame or a list of equally sized frames (batched through one denoising run)."""
+    batch = image if isinstance(image, (list, tuple)) else [image]
+
+    def fit(im):
+        if not isinstance(im, Image.Image):
+            im = Image.open(im)
+        ratio = min(height / im.height, width / im.width)
+        return im.resize((max(8, int(im.width * ratio)), max(8, int(im.height * ratio))), Image.Resampling.LANCZOS)
+
+    batch = [fit(im) for im in batch]
+    many = isinstance(image, (list, tuple))
+    result = pipeline([prompt] * len(batch) if many else prompt,
+                      negative_prompt=[neg_prompt] * len(batch) if many else neg_prompt,
+                      image=batch if many else batch[0], num_inference_steps=int(steps),
                       image_guidance_scale=image_guidance_scale, guidance_scale=text_guidance_scale,
                       generator=generator)
-    return result.images, bool(result.nsfw_content_detected[0])
+    return result.images, any(bool(f) for f in result.nsfw_content_detected)
 
 
 def get_frames(temp_dir, video_in):

@@ -8,8 +8,9 @@ lanes, and the poll itself holds a lane while it is in flight (Q11).
 
 What differs from the reference:
   * settings are read when the worker starts, not at import;
-  * lanes are `Device` objects leased from the rank group, plus one CPU lane for pure-CPU
-    workflows (stitch) so they do not occupy a GPU (Q10);
+  * a lane is a `Device` of this process (one GPU per job) plus one CPU lane for pure-CPU workflows
+    (stitch) so they do not occupy a GPU (Q10); in gang mode (`settings.parallel_mode` != "dp",
+    parallel/gang_worker.py) a lane instead leases 1 / 2 / 4 / 8 rank processes from the RankGroup per job;
   * results that fail to POST are retried a bounded number of times instead of dropped (Q14);
   * `Worker` is an object (testable against a fake hive) -- the module-level functions
     `run_worker/startup/ask_for_work/device_worker/result_worker/submit_result` remain.
@@ -164,6 +165,11 @@ class Worker:
                 return True
 
     # ------------------------------------------------------------------ lanes
+    async def execute(self, job, device):
+        """One job on one lane.  Here: the in-process Device (one GPU per job, as in the reference);
+        parallel.gang_worker.GangWorker overrides it to lease a gang of rank processes instead."""
+        return await do_work(job, device)
+
     async def device_worker(self, device: Device):
         while True:
             job = await self.work_queue.get()
@@ -171,7 +177,7 @@ class Worker:
             try:
                 await self.available_gpus.acquire()
                 acquired = True
-                result = await do_work(job, device)
+                result = await self.execute(job, device)
                 await self.result_queue.put(result)
             except asyncio.CancelledError:
                 raise

@@ -2,6 +2,7 @@
 single-GPU oracle.  Run under torchrun (one process per GPU):
   python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 scripts/dist_check.py
 Device-timed with CUDA events, max over ranks."""
+import argparse
 import json
 import os
 import sys
@@ -15,8 +16,31 @@ from chiaswarm_b200.ops import native as nat
 from chiaswarm_b200.parallel import runtime
 from chiaswarm_b200.parallel.collectives import FusedOps
 
+ap = argparse.ArgumentParser()
+ap.add_argument("--skew-ms", type=float, default=0.0,
+                help="the last rank reaches every checked kernel this many ms late (device-side sleep on its stream)")
+ap.add_argument("--no-timing", action="store_true")
+args = ap.parse_args()
+
 gang = runtime.init()
 dev, W, R = gang.device, gang.world, gang.rank
+
+
+def skewed(fn):
+    """Run fn with the skewed arrival the flag protocol must tolerate (no-op without --skew-ms)."""
+    if args.skew_ms > 0 and R == W - 1:
+        torch.cuda._sleep(int(args.skew_ms * 1e-3 * 1.9e9))
+    fn()
+    if args.skew_ms > 0:  # and the other way round on the next call: the FIRST rank is late
+        torch.cuda.synchronize()
+        gang.barrier()
+        if R == 0:
+            torch.cuda._sleep(int(args.skew_ms * 1e-3 * 1.9e9))
+        fn()
+        torch.cuda.synchronize()
+        gang.barrier()
+
+
 arena = runtime.SymmetricArena(gang, 1 << 30)
 ops = FusedOps(arena)
 results = {}
@@ -28,6 +52,8 @@ def bcast(t):
 
 
 def timed(fn, iters=20):
+    if args.no_timing:
+        return 0.0
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
@@ -66,7 +92,7 @@ xs.local.copy_(x_full[R * m_local:(R + 1) * m_local])
 out_f = torch.empty(W * m_local, n // W, device=dev, dtype=torch.float16)
 out_n = torch.empty_like(out_f)
 arena.barrier()
-ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols)
+skewed(lambda: ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols))
 ops.allgather_gemm_nccl(xs.local, w_cols, out_n, bias=b_cols)
 ref = x_full.float() @ w_cols.float().t() + b_cols.float()
 tf = timed(lambda: ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols))
@@ -90,7 +116,7 @@ staging = arena.alloc(W, m_local, n2)
 o_f = torch.empty(m_local, n2, device=dev, dtype=torch.float16)
 o_n = torch.empty_like(o_f)
 arena.barrier()
-ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc)
+skewed(lambda: ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc))
 ops.gemm_reducescatter_nccl(x_ksh, w_ksh, o_n, bias=b2, residual=res_loc)
 ref2 = (x2.float() @ w2.float().t() + b2.float() + res_full.float())[R * m_local:(R + 1) * m_local]
 tf = timed(lambda: ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc))
@@ -111,7 +137,7 @@ vsym.local.copy_(v_full[:, R * s_loc:(R + 1) * s_loc])
 a_f = torch.empty(b_, s_loc, h_ * d_, device=dev, dtype=torch.float16)
 a_n = torch.empty_like(a_f)
 arena.barrier()
-ops.kv_gather_attention_fused(q_loc, ksym, vsym, a_f, batch=b_, heads=h_, head_dim=d_)
+skewed(lambda: ops.kv_gather_attention_fused(q_loc, ksym, vsym, a_f, batch=b_, heads=h_, head_dim=d_))
 ops.kv_gather_attention_nccl(q_loc, ksym.local, vsym.local, a_n, batch=b_, heads=h_, head_dim=d_)
 ref3 = F.scaled_dot_product_attention(q_loc.float().transpose(1, 2), k_full.float().transpose(1, 2),
                                       v_full.float().transpose(1, 2)).transpose(1, 2).reshape(b_, s_loc, h_ * d_)
@@ -130,7 +156,7 @@ xg_loc = xg[:, R * hw_loc:(R + 1) * hw_loc].contiguous()
 g_f = torch.empty_like(xg_loc)
 g_n = torch.empty_like(xg_loc)
 arena.barrier()
-ops.groupnorm_fused(xg_loc, gam, bet, g_f, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True)
+skewed(lambda: ops.groupnorm_fused(xg_loc, gam, bet, g_f, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True))
 ops.groupnorm_nccl(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True)
 ref4 = F.silu(F.group_norm(xg.float().permute(0, 2, 1), g_, gam.float(), bet.float(), 1e-5)).permute(0, 2, 1)
 ref4 = ref4[:, R * hw_loc:(R + 1) * hw_loc]
@@ -142,7 +168,7 @@ report("groupnorm_allreduce", (g_f.float() - ref4).abs().max().item(), (g_n.floa
 gang.barrier()
 if R == 0:
     os.makedirs("gpurun_out", exist_ok=True)
-    with open(f"gpurun_out/dist_check_w{W}.json", "w") as fh:
+    with open(f"gpurun_out/dist_check_w{W}{'_skew' if args.skew_ms else ''}.json", "w") as fh:
         json.dump(results, fh, indent=1)
     ok = all(v["rel_err_fused"] < 2e-2 for v in results.values())
     print("DIST_CHECK", "PASS" if ok else "FAIL", flush=True)

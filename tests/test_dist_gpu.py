@@ -1,5 +1,6 @@
-"""Fused compute+collective kernels on >= 2 GPUs (torchrun, one process per GPU): each is checked
-against a single-GPU fp32 oracle and the NCCL baseline path."""
+"""Fused compute+collective kernels, the patch-parallel engine and gang serving on 2 / 4 / 8 GPUs (torchrun, one
+process per GPU): each is checked against a single-GPU fp32 oracle and the NCCL baseline path (SURVEY.md section
+4.2 item 5b).  Every case skips itself when the box has fewer GPUs than it needs."""
 import os
 import subprocess
 import sys
@@ -7,26 +8,54 @@ import sys
 import pytest
 import torch
 
-pytestmark = [pytest.mark.gpu, pytest.mark.timeout(900)]
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(1200)]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+N_GPUS = torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-def test_fused_collectives_two_ranks():
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "scripts", "dist_check.py")]
-    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=800)
+def _need(world):
+    if N_GPUS < world:
+        pytest.skip(f"needs >= {world} GPUs, found {N_GPUS}")
+
+
+def _torchrun(world, port, script, *script_args, env=None):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", script), *script_args]
+    return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=1100, env={**os.environ, **(env or {})})
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_collectives(world):
+    _need(world)
+    r = _torchrun(world, 29533, "dist_check.py")
     assert "DIST_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("guidance", [1.0, 7.5])
-def test_patch_parallel_engine_two_ranks(guidance):
-    """SD1.5-shaped UNet, one image over 2 GPUs: guidance 1.0 -> two strips (halo push, GroupNorm all-reduce,
-    K/V-gather attention, K/V push for the short mid-block sequence), 7.5 -> one CFG branch per GPU (epsilon
-    exchange only); latents must match the single-GPU engine."""
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "scripts", "patch_check.py"), "--arch", "sd15",
-           "--size", "512", "--steps", "3", "--guidance", str(guidance)]
-    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=800)
+@pytest.mark.parametrize("world", [2, 4])
+def test_fused_collectives_skewed_arrival(world):
+    """One rank reaches every kernel 50 ms late (SW_DIST_SKEW_MS): the flag protocol has to hold the early ranks
+    back without a timeout trap, and results must not change."""
+    _need(world)
+    r = _torchrun(world, 29535, "dist_check.py", "--skew-ms", "50", "--no-timing")
+    assert "DIST_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world,guidance", [(2, 1.0), (2, 7.5), (4, 7.5), (8, 7.5)])
+def test_patch_parallel_engine(world, guidance):
+    """SD1.5-shaped UNet, one image over the gang: guidance 1.0 -> every rank a strip (halo push, GroupNorm
+    all-reduce, K/V-gather attention, K/V push for the short mid-block sequence), 7.5 -> two CFG branches on disjoint
+    halves (epsilon exchange between them); latents must match the single-GPU engine."""
+    _need(world)
+    r = _torchrun(world, 29537, "patch_check.py", "--arch", "sd15", "--size", "512", "--steps", "3", "--guidance",
+                  str(guidance))
     assert "PATCH_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world,gang", [(2, 2), (4, 2)])
+def test_gang_serving(world, gang):
+    """Jobs through the GangScheduler on NCCL rank processes: patch-parallel single image, split batch, and (4 GPUs)
+    two gangs of two side by side -- the images must match the single-rank run of the same job."""
+    _need(world)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "gang_check.py"), "--world", str(world), "--gang",
+                        str(gang)], cwd=ROOT, capture_output=True, text=True, timeout=1100)
+    assert "GANG_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -1,0 +1,176 @@
+"""Gang jobs through the job API (SURVEY.md sections 2.3, 5.3, 5.8): the hive client leases
+1 / 2 / 4 / 8 ranks per job from the RankGroup, the ranks run the job SPMD, the gang's first rank answers.
+CPU tier: two real rank processes over gloo with the eager back end; the GPU tier repeats it on NCCL with the
+sm_100a patch engine (tests/test_dist_gpu.py)."""
+import asyncio
+import multiprocessing as mp
+import os
+import time
+
+import numpy as np
+import pytest
+
+from tests.helpers import decode_artifact_image
+from tests.test_worker_hive import FakeHive
+
+
+def _settings(**kw):
+    from chiaswarm_b200.settings import Settings
+
+    s = Settings()
+    s.sdaas_uri, s.sdaas_token, s.worker_name = "http://127.0.0.1:9", "secret", "gangrig"
+    for k, v in kw.items():
+        setattr(s, k, v)
+    return s
+
+
+def test_plan_gang_size_policy():
+    from chiaswarm_b200.parallel.gang_worker import aligned_subsets, plan_gang_size
+
+    dp = _settings(parallel_mode="dp", gang_size=8)
+    gang = _settings(parallel_mode="gang", gang_size=8)
+    sdxl = {"model_name": "stabilityai/stable-diffusion-xl-base-1.0", "height": 1024, "width": 1024}
+    assert plan_gang_size(sdxl, dp, 8) == 1                    # reference behaviour: one GPU per job
+    assert plan_gang_size(sdxl, gang, 8) == 8                  # one large image: patch-parallel over the gang
+    assert plan_gang_size(sdxl, gang, 4) == 4
+    assert plan_gang_size(dict(sdxl, height=512, width=512), gang, 8) == 1   # small image: launch-bound, stays DP
+    assert plan_gang_size(dict(sdxl, num_images_per_prompt=8, height=768, width=768), gang, 8) == 8
+    assert plan_gang_size(dict(sdxl, num_images_per_prompt=6), gang, 8) == 2  # largest power of two dividing 6
+    assert plan_gang_size(dict(sdxl, num_images_per_prompt=3), gang, 8) == 1
+    assert plan_gang_size({"workflow": "vid2vid", "model_name": "timbrooks/instruct-pix2pix"}, gang, 8) == 8
+    assert plan_gang_size({"workflow": "txt2vid", "model_name": "m"}, _settings(parallel_mode="gang", gang_size=4), 8) == 4
+    assert plan_gang_size({"workflow": "stitch", "model_name": "m"}, gang, 8) == 1
+    assert plan_gang_size(dict(sdxl, start_image_uri="x"), gang, 8) == 1
+    assert plan_gang_size(sdxl, _settings(parallel_mode="gang", gang_size=3), 8) == 2  # rounded down to a buddy size
+    assert aligned_subsets(4) == [(0, 1), (2, 3), (0, 1, 2, 3)]
+    assert len(aligned_subsets(8)) == 4 + 2 + 1
+
+
+def _job(job_id, **kw):
+    job = {"id": job_id, "model_name": "tiny-sd", "prompt": "a gang job", "height": 64, "width": 64,
+           "num_inference_steps": 2, "seed": 11, "content_type": "image/png"}
+    job.update(kw)
+    return job
+
+
+@pytest.fixture
+def gang_env(tmp_path, monkeypatch):
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    return {"SDAAS_ROOT": str(tmp_path), "SDAAS_RANDOM_INIT": "1", "SDAAS_KERNEL_BACKEND": "torch"}
+
+
+def test_gang_jobs_match_single_rank(gang_env, monkeypatch):
+    """A patch-parallel single image and a split batch on a 2-rank gang give the images one rank gives."""
+    from chiaswarm_b200.generator import synchronous_do_work_function
+    from chiaswarm_b200.gpu.device import Device
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    for k, v in gang_env.items():
+        monkeypatch.setenv(k, v)
+    single = _job("one")
+    batch = _job("four", num_images_per_prompt=4, seed=5)
+    ref_single = synchronous_do_work_function(dict(single), Device("cpu"))
+    ref_batch = synchronous_do_work_function(dict(batch), Device("cpu"))
+    assert "error" not in ref_single["pipeline_config"], ref_single["pipeline_config"]
+
+    sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2, patch_min_pixels=64 * 64), use_cuda=False,
+                          env=gang_env, job_timeout_s=300)
+    sched.start()
+    try:
+        got_single = sched.submit(single)
+        got_batch = sched.submit(batch)
+        assert sched.leases_by_size == {2: 2}
+        assert sched.pool.free_count() == 2
+    finally:
+        sched.stop()
+    for ref, got in ((ref_single, got_single), (ref_batch, got_batch)):
+        assert "error" not in got["pipeline_config"], got["pipeline_config"]
+        assert got["pipeline_config"]["seed"] == ref["pipeline_config"]["seed"]
+        a = np.asarray(decode_artifact_image(ref["artifacts"]["primary"]), dtype=np.float32)
+        b = np.asarray(decode_artifact_image(got["artifacts"]["primary"]), dtype=np.float32)
+        assert a.shape == b.shape
+        assert np.abs(a - b).max() <= 2.0  # same latents up to fp32 reduction order -> same 8-bit image +- 1-2 levels
+
+
+def test_gang_worker_serves_a_fake_hive(gang_env):
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler, GangWorker
+
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        hive.jobs = [_job("patch"), _job("dp", height=32, width=32), {"id": "bad", "model_name": "tiny-sd", "height": 5000, "width": 64}]
+        s = _settings(parallel_mode="gang", gang_size=2, patch_min_pixels=64 * 64, sdaas_uri=uri)
+        sched = GangScheduler(2, s, use_cuda=False, env=gang_env, job_timeout_s=300)
+        try:
+            w = GangWorker(s, scheduler=sched, cpu_lane=False)
+
+            async def fast_sleep(_):
+                await asyncio.sleep(0)
+
+            await w.run(max_polls=2, sleep=fast_sleep)
+            by_id = {r["id"]: r for r in hive.results}
+            assert sorted(by_id) == ["bad", "dp", "patch"]
+            assert by_id["bad"]["fatal_error"] is True
+            assert "error" not in by_id["patch"]["pipeline_config"]
+            # "patch" and the oversized "bad" job are large enough for a gang of 2, "dp" (32x32) keeps one rank
+            assert sched.leases_by_size.get(2) == 2 and sched.leases_by_size.get(1) == 1
+        finally:
+            sched.stop()
+            await hive.stop()
+
+    asyncio.run(main())
+
+
+def _dying_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
+    """Stand-in rank body: rank 1 exits in the middle of its first job (no torch needed)."""
+    result_q.put(("ready", rank, None))
+    first = not os.path.exists(os.path.join(env["MARK"], f"restarted{rank}"))
+    open(os.path.join(env["MARK"], f"restarted{rank}"), "w").close()
+    while True:
+        msg = job_q.get()
+        if msg is None:
+            return
+        lease_id, ranks, job = msg
+        if rank == 1 and first:
+            os._exit(7)
+        result_q.put(("result" if ranks[0] == rank else "done", lease_id, {"id": job["id"], "ok": True}))
+
+
+def _stuck_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
+    result_q.put(("ready", rank, None))
+    while True:
+        msg = job_q.get()
+        if msg is None:
+            return
+        time.sleep(3600)
+
+
+def test_dead_rank_fails_the_job_and_restarts_the_world(tmp_path):
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    s = _settings(parallel_mode="gang", gang_size=2)
+    sched = GangScheduler(2, s, use_cuda=False, env={"MARK": str(tmp_path)}, job_timeout_s=60, target=_dying_rank)
+    sched.start()
+    try:
+        r = sched.submit({"id": "j1", "model_name": "m", "workflow": "vid2vid"})
+        assert "died" in r["pipeline_config"]["error"] and "fatal_error" not in r  # non-fatal: the hive re-issues it
+        assert sched.restarts == 1 and sched.pool.free_count() == 2
+        r2 = sched.submit({"id": "j2", "model_name": "m", "workflow": "vid2vid"})  # the new world serves
+        assert r2 == {"id": "j2", "ok": True}
+    finally:
+        sched.stop()
+
+
+def test_watchdog_times_a_wedged_gang_out(tmp_path):
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2), use_cuda=False, env={},
+                          job_timeout_s=1.0, target=_stuck_rank)
+    sched.start()
+    try:
+        t0 = time.time()
+        r = sched.submit({"id": "j", "model_name": "m", "workflow": "txt2vid"})
+        assert "exceeded" in r["pipeline_config"]["error"] and time.time() - t0 < 30
+        assert sched.restarts == 1
+    finally:
+        sched.stop()
