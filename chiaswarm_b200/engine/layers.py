@@ -135,7 +135,7 @@ class Conv:
     def __call__(self, rec: Recorder, x: FM, x2: Optional[FM] = None, row_bias=None, residual: Optional[FM] = None,
                  act=nat.ACT_NONE, out_scale=1.0, out: Optional[FM] = None) -> FM:
         a, halo = x.t, {}
-        if rec.patch is not None and self.k == 3:  # rows above / below this strip live on the neighbours
+        if rec.patch is not None and rec.patch.rows and self.k == 3:  # rows above / below this strip live on the neighbours
             assert x2 is None and self.pad == 1 and not self.asym
             a, halo = rec.patch.conv_input(rec, x)
         if self.stride == 1:
@@ -284,10 +284,15 @@ class GroupNorm:
         self.gamma = gn.weight.detach().to(torch.float16).contiguous()
         self.beta = gn.bias.detach().to(torch.float16).contiguous()
 
-    def __call__(self, rec: Recorder, x: FM, silu: bool, x2: Optional[FM] = None) -> FM:
+    def __call__(self, rec: Recorder, x: FM, silu: bool, x2: Optional[FM] = None, out: Optional[FM] = None,
+                 dist: Optional[bool] = None) -> FM:
+        """`dist`: the statistics span rows held by the other ranks of the strip group (default: every GroupNorm
+        of a row-split plan; frame-split video plans say so for their temporal layers only)."""
         c = x.c + (x2.c if x2 is not None else 0)
-        o = rec.fm(x.n, x.h, x.w, c)
-        if rec.patch is not None and rec.patch.P > 1:  # statistics span the whole image: in-kernel all-reduce
+        o = out or rec.fm(x.n, x.h, x.w, c)
+        if dist is None:
+            dist = rec.patch is not None and rec.patch.rows
+        if dist and rec.patch is not None and rec.patch.P > 1:  # in-kernel all-reduce of the partial sums
             rec.add(nat.groupnorm_dist, x.t, self.gamma, self.beta, o.t, rec.patch.gn_peers(self.groups), n=x.n,
                     hw=x.h * x.w, groups=self.groups, eps=self.eps, silu=silu, stats=rec.gn_stats,
                     x2=None if x2 is None else x2.t)
@@ -416,7 +421,7 @@ class TransformerBlock:
         """x: input of the fused QKV projection (LayerNorm output, or the raw stream + its statistics)."""
         attn = rec.buf(n, s, self.c)
         lin = qkv_lin or self.qkv
-        if rec.patch is not None and rec.patch.P > 1:
+        if rec.patch is not None and rec.patch.rows and rec.patch.P > 1:
             # sequence-parallel self-attention: K/V of the other strips are read from their owners inside the
             # kernel (TMA over the NVLink mappings), never gathered
             if s % 128 == 0 and self.dh <= 128:

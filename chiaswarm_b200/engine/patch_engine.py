@@ -44,9 +44,13 @@ class _Channel:
 
 
 class PatchContext:
-    def __init__(self, gang: Gang, n_cond: int, arena):
+    def __init__(self, gang: Gang, n_cond: int, arena, rows: bool = True):
         """`arena`: a SymmetricArena or one recyclable ArenaSlice of the gang's arena (PatchDenoiser hands every
-        cached plan its own slice, so the peer-visible memory of an evicted plan is reused)."""
+        cached plan its own slice, so the peer-visible memory of an evicted plan is reused).
+        `rows`: True = every feature map is cut into horizontal strips (images); False = a video clip is cut
+        along the FRAME axis -- spatial layers are then local to a rank and only the temporal layers
+        (engine/unet3d_sm100.py) talk to the strip group."""
+        self.rows = rows
         if gang.world % n_cond:
             raise ValueError(f"{gang.world} ranks cannot be split into {n_cond} guidance groups")
         self.gang = gang
@@ -57,8 +61,7 @@ class PatchContext:
         self.arena = SymmetricArena(gang, arena) if isinstance(arena, int) else arena
         self.tick = torch.zeros(1, dtype=torch.int32, device=gang.device)
         self._channels: Dict[str, _Channel] = {}
-        self._gn_stats: Optional[SymTensor] = None
-        self._gn_groups = 0
+        self._gn_stats: Dict[int, SymTensor] = {}
 
     # ---- addressing
     def global_rank(self, d: int) -> int:
@@ -113,12 +116,10 @@ class PatchContext:
         return st.local.view(1, h + 2, x.w, x.c), dict(a_h_total=h + 2, a_y_off=1)
 
     def gn_peers(self, groups: int) -> nat.Peers:
-        if self._gn_stats is None:
-            self._gn_groups = groups
-            self._gn_stats = self.arena.alloc(2 * self.P * groups * 2, dtype=torch.float32)
-        if groups != self._gn_groups:
-            raise ValueError("patch-parallel GroupNorm expects one group count per model")
-        return self._peers("gn", [self._gn_stats.peer_ptr(self.global_rank(d)) for d in range(self.P)])
+        st = self._gn_stats.get(groups)  # one double-buffered slot set per group count (32 spatial, 8 temporal conv)
+        if st is None:
+            st = self._gn_stats[groups] = self.arena.alloc(2 * self.P * groups * 2, dtype=torch.float32)
+        return self._peers("gn", [st.peer_ptr(self.global_rank(d)) for d in range(self.P)])
 
     def kv_peers(self, qkv: SymTensor, c: int):
         ranks = [self.global_rank(d) for d in range(self.P)]
@@ -163,6 +164,30 @@ class PatchRecorder(Recorder):
         super().release(t)
 
 
+class FrameRecorder(Recorder):
+    """Recorder of a frame-split video plan: feature maps are ordinary local buffers (whole frames live on one
+    rank); only what the temporal layers exchange is carved from the symmetric arena."""
+
+    def __init__(self, device, ctx: PatchContext):
+        super().__init__(device)
+        self.patch = ctx
+
+    def halo_fm(self, nf: int, hw: int, c: int) -> FM:
+        """[nf + 2, hw, c] peer-visible buffer viewed as the (1, nf, hw, c) map a (3,1,1) conv reads: frames -1 and
+        nf are filled by the neighbouring ranks (zero at the ends of the clip = the conv's padding)."""
+        st = self.patch.arena.alloc(nf + 2, hw, c)
+        return FM(st.local[1:nf + 1].view(1, nf, hw, c), 1, nf, hw, c, sym=st)
+
+    def release(self, t):
+        if isinstance(t, FM):
+            if t.sym is not None:
+                return
+            t = t.t
+        if self.patch.owns(t):
+            return
+        super().release(t)
+
+
 class _PatchStepGraph(_StepGraph):
     def __init__(self, eng: "PatchDenoiser", h, w, n_cond, extra_ch, has_noise, aug, arena):
         super().__init__(eng, 1, h, w, n_cond, extra_ch, False, has_noise, aug)
@@ -203,11 +228,55 @@ class _PatchStepGraph(_StepGraph):
         return self
 
 
+class _FrameStepGraph(_StepGraph):
+    """Text-to-video over a gang (BASELINE config 5; reference call site swarm/video/tx2vid.py:55): guidance branch
+    g on ranks [g*P, (g+1)*P), and inside a branch rank p owns frames [p*F/P, (p+1)*F/P) of the clip.  Spatial
+    convs / GroupNorms / attention see whole frames and never communicate; the temporal layers do:
+      temporal conv (3,1,1)   one halo FRAME from each neighbour (the same push + flag as an image strip's halo row)
+      its GroupNorm, and the temporal transformer's: statistics over the whole clip -> sw_groupnorm_nhwc_dist
+      temporal attention      K/V of this rank's frames pushed into every peer's full-clip K/V buffer
+    followed by the same epsilon exchange + redundant scheduler step as the image plan."""
+
+    def __init__(self, eng: "PatchDenoiser", frames, h, w, n_cond, has_noise, arena):
+        super().__init__(eng, frames, h, w, n_cond, 0, False, has_noise, False)
+        self.arena_slice = arena
+        self.ctx = PatchContext(eng.gang, n_cond, arena, rows=False)
+
+    def build(self, max_noise_steps: int):
+        eng, up, ctx = self.eng, self.eng.unet_plan, self.ctx
+        F, H, W = self.batch, self.h, self.w
+        if F % ctx.P:
+            raise ValueError(f"{F} frames do not split over {ctx.P} ranks")
+        fl = F // ctx.P
+        if self.has_noise:
+            self.noise = torch.zeros(max_noise_steps, self.rows, self.lat_c, dtype=torch.float32, device=eng.device)
+        rec = FrameRecorder(eng.device, ctx)
+        up.num_frames, up.total_frames = fl, F
+        lo = ctx.g * F + ctx.p * fl
+        x_in = FM(self.model_in[lo:lo + fl], fl, H, W, up.in_pad)
+        temb = up.record_time_embedding(rec, fl, self.t_table, self.step, None)
+        mid, skips = up.record_encoder(rec, x_in, temb)
+        cpad = _r8(up.out_ch)
+        self.eps_all = ctx.arena.alloc(self.n_cond, F, H, W, cpad)
+        mine = self.eps_all.local[ctx.g, ctx.p * fl:(ctx.p + 1) * fl]
+        up.record_decoder(rec, mid, skips, temb, out=FM(mine, fl, H, W, cpad))
+        if ctx.world > 1:
+            ctx.all_exchange(rec, None, None, 0)
+            off = ((ctx.g * F + ctx.p * fl) * H * W * cpad) * 2
+            ctx.all_exchange(rec, mine, self.eps_all, off)
+        rec.add(self._sched, FM(self.eps_all.local.view(self.n_cond * F, H, W, cpad), self.n_cond * F, H, W, cpad))
+        rec.add(nat.advance_counter, self.step)
+        rec.add(nat.advance_counter, ctx.tick)
+        ctx.finalize()
+        self.rec = rec
+        return self
+
+
 class PatchDenoiser(SM100Denoiser):
     """SM100Denoiser whose single-image jobs run patch-parallel over `gang`; every rank of the gang
     must make the same calls with the same seeds (SPMD).  Other jobs fall back to the local engine."""
 
-    def __init__(self, pipe, gang: Gang, arena_bytes: int = 6 << 30, max_patch_graphs: int = 2):
+    def __init__(self, pipe, gang: Gang, arena_bytes: int = 16 << 30, max_patch_graphs: int = 2):
         super().__init__(pipe)
         self.gang = gang
         self.arena_bytes = arena_bytes
@@ -242,6 +311,8 @@ class PatchDenoiser(SM100Denoiser):
     @torch.no_grad()
     def run(self, x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise, inpaint,
             num_frames: int = 1):
+        if num_frames > 1 and self.supports_frames(x, n_cond, num_frames, extra, control, added, inpaint):
+            return self._run_frames(x, embeds, plan, n_cond, g_text, noise, num_frames)
         if not self.supports(x, n_cond, control, inpaint) or num_frames != 1:
             return super().run(x, embeds, plan, n_cond, g_text, g_image, extra, control, control_scale, added, noise,
                                inpaint, num_frames)
@@ -268,6 +339,39 @@ class PatchDenoiser(SM100Denoiser):
             sg.replay()
         self.last_launches = sg.launches_per_step * steps
         return sg.x.view(batch, h, w, c).permute(0, 3, 1, 2).contiguous()
+
+    def supports_frames(self, x, n_cond, num_frames, extra, control, added, inpaint) -> bool:
+        w = self.gang.world
+        return (w > 1 and hasattr(self.unet_plan, "num_frames") and x.shape[0] == num_frames and w % n_cond == 0
+                and num_frames % (w // n_cond) == 0 and extra is None and control is None and added is None
+                and inpaint is None)
+
+    @torch.no_grad()
+    def _run_frames(self, x, embeds, plan, n_cond, g_text, noise, num_frames):
+        """One clip ([F, c, h, w] latents, `embeds` one row per frame, branch-major) frame-split over the gang."""
+        F, c, h, w = x.shape
+        steps = plan.num_steps
+        if steps > MAX_STEPS:
+            raise ValueError(f"at most {MAX_STEPS} denoising steps are supported")
+        key = ("patch", "frames", F, h, w, n_cond, noise is not None)
+        sg = self._graphs.pop(key, None)
+        fresh = sg is None
+        if fresh:
+            sg = _FrameStepGraph(self, F, h, w, n_cond, noise is not None, self._take_slice())
+        self._graphs[key] = sg
+        ctx = sg.ctx
+        fl = F // ctx.P
+        lo = ctx.g * F + ctx.p * fl
+        self.unet_plan.set_context(embeds[lo:lo + fl].to(torch.float16))  # this rank's frames of its branch
+        if fresh:
+            sg.build(steps if noise is not None else 0)
+            self._load_job(sg, x, plan, None, None, None, noise, g_text, 0.0)
+            sg.capture()
+        self._load_job(sg, x, plan, None, None, None, noise, g_text, 0.0)
+        for _ in range(steps):
+            sg.replay()
+        self.last_launches = sg.launches_per_step * steps
+        return sg.x.view(F, h, w, c).permute(0, 3, 1, 2).contiguous()
 
     def _load_patch_job(self, sg: _PatchStepGraph, x, plan, extra, added, noise, g_text=7.5, g_image=1.5):
         local_aug = sg.aug_emb

@@ -23,6 +23,11 @@ from .layers import FM, GroupNorm, LayerNorm, Linear, Recorder
 from .unet_sm100 import UNetPlan
 
 
+def _frame_split(rec: Recorder) -> bool:
+    """Is this plan one rank's share of a clip that is split along the frame axis (engine/patch_engine.py)?"""
+    return rec.patch is not None and not rec.patch.rows and rec.patch.P > 1
+
+
 class TemporalConv:
     def __init__(self, m):
         seqs = [m.conv1, m.conv2, m.conv3, m.conv4]
@@ -37,11 +42,21 @@ class TemporalConv:
     def __call__(self, rec: Recorder, x: FM, nf: int) -> FM:
         b, hw = x.n // nf, x.h * x.w
         cur = FM(x.t, b, nf, hw, x.c)
+        split = _frame_split(rec)
         for i in range(4):
-            g = self.norms[i](rec, cur, True)
+            halo = {}
+            if split:
+                # frame-split clip: the GroupNorm spans every rank's frames, and the conv's taps f-1 / f+1 of the
+                # first / last local frame live on the neighbours (halo frames pushed into the padded buffer)
+                g = rec.halo_fm(nf, hw, x.c)
+                self.norms[i](rec, cur, True, out=g, dist=True)
+                a, halo = rec.patch.conv_input(rec, g)
+            else:
+                g = self.norms[i](rec, cur, True)
+                a = g.t
             out = rec.fm(b, nf, hw, x.c)
-            rec.add(nat.igemm, g.t, self.wgts[i], out.tokens(), n=b, h=nf, w=hw, kh=3, kw=1, pad=1, pad_w=0,
-                    bias=self.biases[i], residual=x.tokens() if i == 3 else None, splitk_scratch=rec.splitk)
+            rec.add(nat.igemm, a, self.wgts[i], out.tokens(), n=b, h=nf, w=hw, kh=3, kw=1, pad=1, pad_w=0,
+                    bias=self.biases[i], residual=x.tokens() if i == 3 else None, splitk_scratch=rec.splitk, **halo)
             rec.release(g)
             if i > 0:
                 rec.release(cur)
@@ -67,6 +82,30 @@ class TemporalBlock:
         rows = b * nf * hw
         for k in range(2):
             xn = self.lns[k](rec, y)
+            if _frame_split(rec):
+                # this rank holds nf of the clip's P * nf frames: queries stay local, its K/V rows go into the
+                # full-clip K/V buffer of every rank of the strip group (frame-major, so a rank's share is one
+                # contiguous block), and attention runs over all frames for the local query frames
+                ctx = rec.patch
+                c, tot = self.c, ctx.P * nf
+                q = rec.buf(rows, c)
+                self.qkv[k].call_rows(rec, xn, 0, c, q)
+                kvf = ctx.sym_buf(tot * hw, 2 * c)
+                mine = kvf.local[ctx.p * rows:(ctx.p + 1) * rows]
+                self.qkv[k].call_rows(rec, xn, c, 3 * c, mine)
+                rec.release(xn)
+                ctx.group_exchange(rec, mine, kvf, ctx.p * rows * 2 * c * 2)
+                attn = rec.buf(rows, c)
+                q4 = q.view(nf, hw, self.heads, self.dh).permute(1, 0, 2, 3)
+                kv5 = kvf.local.view(tot, hw, 2, self.heads, self.dh).permute(1, 0, 2, 3, 4)
+                rec.add(nat.flash_attn, q4, kv5[:, :, 0], kv5[:, :, 1], attn.view(nf, hw, c).permute(1, 0, 2), batch=hw,
+                        heads=self.heads, seq_q=nf, seq_kv=tot, head_dim=self.dh)
+                rec.release(q)
+                y2 = self.out[k](rec, attn, residual=y)
+                rec.release(attn)
+                rec.release(y)
+                y = y2
+                continue
             qkv = self.qkv[k](rec, xn)
             rec.release(xn)
             attn = rec.buf(rows, self.c)
@@ -99,7 +138,7 @@ class TemporalTransformer:
 
     def __call__(self, rec: Recorder, x: FM, nf: int) -> FM:
         b, hw = x.n // nf, x.h * x.w
-        g = self.norm(rec, FM(x.t, b, nf, hw, x.c), False)
+        g = self.norm(rec, FM(x.t, b, nf, hw, x.c), False, dist=_frame_split(rec))  # statistics over the clip
         y = self.proj_in(rec, g.tokens())
         rec.release(g)
         for blk in self.blocks:
@@ -157,7 +196,7 @@ class UNet3DPlan(UNetPlan):
         x = self._res(rec, self.mid, 1, x, None, temb_all, release_in=True)
         return x, skips
 
-    def record_decoder(self, rec: Recorder, x: FM, skips: List[FM], temb_all) -> FM:
+    def record_decoder(self, rec: Recorder, x: FM, skips: List[FM], temb_all, out: Optional[FM] = None) -> FM:
         skips = list(skips)
         for d in self.up:
             for i in range(len(d["resnets"])):
@@ -168,6 +207,6 @@ class UNet3DPlan(UNetPlan):
                 x = x2
         g = self.norm_out(rec, x, True)
         rec.release(x)
-        out = self.conv_out(rec, g)
+        out = self.conv_out(rec, g, out=out)
         rec.release(g)
         return out

@@ -137,7 +137,7 @@ def lib() -> C.CDLL:
                 "sw_igemm", "sw_flash_attn", "sw_groupnorm_nhwc", "sw_layernorm", "sw_upsample2x_nhwc",
                 "sw_im2col_nhwc", "sw_nchw_to_nhwc", "sw_nhwc_to_nchw", "sw_timestep_embedding",
                 "sw_advance_counter", "sw_add", "sw_silu", "sw_sched_step", "sw_image_to_u8", "sw_softmax_rows",
-                "sw_igemm_ag", "sw_igemm_rs", "sw_rs_reduce", "sw_peer_signal", "sw_peer_wait",
+                "sw_igemm_ag", "sw_igemm_rs", "sw_igemm_allgather", "sw_igemm_reducescatter", "sw_gn_partial_sums", "sw_gn_apply_sums", "sw_rs_reduce", "sw_peer_signal", "sw_peer_wait",
                 "sw_flash_attn_gather", "sw_groupnorm_nhwc_dist", "sw_peer_exchange", "sw_groupnorm_nhwc_zeroed",
             ):
                 getattr(l, name).restype = C.c_int
@@ -145,6 +145,12 @@ def lib() -> C.CDLL:
             l.sw_flash_attn.argtypes = [C.POINTER(AttnParams), C.c_void_p]
             l.sw_igemm_ag.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p]
             l.sw_igemm_rs.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p, C.c_void_p]
+            l.sw_igemm_allgather.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p]
+            l.sw_igemm_reducescatter.argtypes = [C.POINTER(IGemmParams), C.POINTER(Peers), C.c_int, C.c_void_p, C.c_int,
+                                                 C.c_void_p]
+            l.sw_gn_partial_sums.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+            l.sw_gn_apply_sums.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                           C.c_int, C.c_int, C.c_longlong, C.c_float, C.c_int, C.c_void_p]
             l.sw_rs_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.POINTER(Peers), C.c_void_p]
             l.sw_peer_signal.argtypes = [C.POINTER(Peers), C.c_void_p]
@@ -449,6 +455,29 @@ def igemm_ag(wgt, out, peers: Peers, *, m_local, k, bias=None, residual=None, ac
     return out
 
 
+def igemm_allgather(wgt, out, peers: Peers, *, m_local, k, a_ld=0, bias=None, tile_n=0):
+    """out[world*m_local, N] = gathered @ wgt^T (+ bias); peers.peer[d] = rank d's gathered buffer, whose rows of
+    this rank are pushed to the peers by the kernel's copy role (include/swarm_b200.h: sw_igemm_allgather)."""
+    p = _gemm_params(wgt, out.data_ptr(), out.stride(-2), m_local * peers.world, k, bias)
+    p.a_ld, p.tile_n = a_ld, tile_n
+    _check(lib().sw_igemm_allgather(C.byref(p), C.byref(peers), m_local, _stream()), "sw_igemm_allgather")
+    _count()
+    return out
+
+
+def igemm_reducescatter(x, wgt, peers: Peers, out, *, m_local, ldc, bias=None, residual=None, tile_n=0):
+    """out[m_local, N] = this rank's rows of sum_r (x_r @ wgt_r^T) (+ bias, + residual): partial tiles TMA-stored
+    into the owners' staging slots, reduced by the kernel's own reduce role (sw_igemm_reducescatter)."""
+    p = _gemm_params(wgt, None, ldc, m_local * peers.world, x.shape[-1], bias, residual)
+    p.a1 = x.data_ptr()
+    p.a_ld = x.stride(-2)
+    p.tile_n = tile_n
+    _check(lib().sw_igemm_reducescatter(C.byref(p), C.byref(peers), m_local, out.data_ptr(), out.stride(-2), _stream()),
+           "sw_igemm_reducescatter")
+    _count()
+    return out
+
+
 def igemm_rs(x, wgt, peers: Peers, ticket, *, m_local, ldc):
     """Partial GEMM over this rank's K shard, rows pushed to their owners' staging slots."""
     p = _gemm_params(wgt, None, ldc, m_local * peers.world, x.shape[-1])
@@ -462,6 +491,20 @@ def rs_reduce(staging, out, peers: Peers, *, m_local, ncols, bias=None, residual
                               staging.stride(-2), out.stride(-2), 0 if residual is None else residual.stride(-2),
                               C.byref(peers), _stream()), "sw_rs_reduce")
     _count()
+    return out
+
+
+def gn_partial_sums(x, *, n, hw, groups):
+    sums = torch.empty(n, groups, 2, dtype=torch.float32, device=x.device)
+    _check(lib().sw_gn_partial_sums(_ptr(x), _ptr(sums), n, hw, x.shape[-1], groups, _stream()), "sw_gn_partial_sums")
+    _count(1)
+    return sums
+
+
+def gn_apply_sums(x, sums, gamma, beta, out, *, n, hw, groups, count, eps, silu):
+    _check(lib().sw_gn_apply_sums(_ptr(x), _ptr(sums), _ptr(gamma), _ptr(beta), _ptr(out), n, hw, x.shape[-1], groups,
+                                  int(count), float(eps), int(silu), _stream()), "sw_gn_apply_sums")
+    _count(1)
     return out
 
 

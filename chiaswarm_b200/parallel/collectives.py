@@ -31,6 +31,10 @@ class FusedOps:
         self.gang = arena.gang
         self.world, self.rank = arena.world, arena.rank
         self.flags = {name: arena.alloc_flags() for name in ("ag", "rs", "kv", "gn")}
+        self._tile_flags = {}   # (kind, count) -> per-tile flag arrays of the second-generation GEMM collectives
+        self._gather = {}       # (m_local, k) -> two gathered buffers, alternated by call parity
+        self._stage = {}        # (m_local, n) -> two staging buffers, alternated by call parity
+        self._calls = {"ag": 0, "rs": 0}
         self.ticket = torch.zeros(4, dtype=torch.int32, device=self.gang.device)
         self.gn_scratch = torch.zeros(1 << 20, dtype=torch.float32, device=self.gang.device)
         self._gn_slots = {}
@@ -39,7 +43,51 @@ class FusedOps:
         return nat.make_peers(self.world, self.rank, epoch, None if buf is None else buf.peer_ptrs(),
                               flags.peer_ptrs())
 
-    # ------------------------------------------------------------------ W11
+    def _flags_for(self, kind: str, count: int) -> SymTensor:
+        fl = self._tile_flags.get((kind, count))
+        if fl is None:
+            fl = self._tile_flags[(kind, count)] = self.arena.alloc_flags(count)
+        return fl
+
+    # ------------------------------------------------------------------ W11, second generation
+    def gather_buffer(self, m_local: int, k: int) -> SymTensor:
+        """The gathered activation [world*m_local, k] the NEXT allgather_gemm call will use.  The producer of the
+        shard writes rows [rank*m_local, (rank+1)*m_local) of `.local` directly (no staging copy); two buffers
+        alternate so a peer still reading call n cannot be overwritten by a fast rank's call n+1."""
+        pair = self._gather.get((m_local, k))
+        if pair is None:
+            pair = self._gather[(m_local, k)] = [self.arena.alloc(self.world * m_local, k) for _ in range(2)]
+        return pair[self._calls["ag"] & 1]
+
+    def allgather_gemm(self, gathered: SymTensor, wgt, out, bias=None, tile_n=0):
+        """ONE kernel: copy role pushes this rank's rows of `gathered` to every peer, compute blocks wait per tile."""
+        rows, k = gathered.local.shape
+        m_local = rows // self.world
+        tiles = m_local // 128
+        fl = self._flags_for("ag", self.world * tiles)
+        self._calls["ag"] += 1
+        pf = self.peers(gathered, fl, self.arena.next_epoch())
+        nat.igemm_allgather(wgt, out, pf, m_local=m_local, k=k, a_ld=gathered.local.stride(0), bias=bias, tile_n=tile_n)
+        return out
+
+    # ------------------------------------------------------------------ W12, second generation
+    def gemm_reducescatter(self, x_kshard, wgt_kshard, out, bias=None, residual=None, tile_n=0):
+        """ONE kernel: partial tiles TMA-stored to their owners, reduce role folds them tile by tile."""
+        m_local, n = out.shape
+        pair = self._stage.get((m_local, n))
+        if pair is None:
+            pair = self._stage[(m_local, n)] = [self.arena.alloc(self.world, m_local, n) for _ in range(2)]
+        staging = pair[self._calls["rs"] & 1]
+        self._calls["rs"] += 1
+        bn = tile_n or 128
+        ntile = (n + bn - 1) // bn
+        fl = self._flags_for("rs", self.world * (m_local // 128) * ntile)
+        pf = self.peers(staging, fl, self.arena.next_epoch())
+        nat.igemm_reducescatter(x_kshard, wgt_kshard, pf, out, m_local=m_local, ldc=n, bias=bias, residual=residual,
+                                tile_n=tile_n)
+        return out
+
+    # ------------------------------------------------------------------ W11 (first generation: pull through peer TMA)
     def allgather_gemm_fused(self, x: SymTensor, wgt, out, bias=None, act=nat.ACT_NONE):
         """x: this rank's [m_local, K] shard (symmetric). out: [world*m_local, N]."""
         m_local, k = x.local.shape
@@ -109,6 +157,15 @@ class FusedOps:
         pf = self.peers(slot, self.flags["gn"], e)
         nat.groupnorm_dist(x, gamma, beta, out, pf, n=n, hw=hw_local, groups=groups, eps=eps, silu=silu,
                            stats=self.gn_scratch, x2=x2)
+        return out
+
+    def groupnorm_nccl_native(self, x, gamma, beta, out, *, n, hw_local, groups, eps, silu):
+        """Like-for-like baseline: native partial-sum kernel, NCCL all-reduce of the sums, native apply kernel."""
+        c = x.shape[-1]
+        sums = nat.gn_partial_sums(x, n=n, hw=hw_local, groups=groups)        # fp32 [n, groups, 2]
+        dist.all_reduce(sums, group=self.gang.group)
+        nat.gn_apply_sums(x, sums, gamma, beta, out, n=n, hw=hw_local, groups=groups, count=hw_local * self.world * (c // groups),
+                          eps=eps, silu=silu)
         return out
 
     def groupnorm_nccl(self, x, gamma, beta, out, *, n, hw_local, groups, eps, silu):

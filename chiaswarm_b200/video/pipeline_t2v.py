@@ -103,14 +103,28 @@ class TextToVideoPipeline:
         img = self.vae.decode(z.to(self.dtype)).float()
         return ((img / 2 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8).permute(0, 2, 3, 1)
 
-    def _sm100(self):
+    def _sm100(self, gang=None):
+        """Engine per gang identity (None = this GPU alone); a gang's engine frame-splits the clip
+        (engine/patch_engine.py::_FrameStepGraph)."""
+        if gang is not None and gang.world <= 1:
+            gang = None
         if self._engine is None:
+            self._engine = {}
+        key = None if gang is None else (gang.global_ranks or ("world", gang.world))
+        eng = self._engine.get(key)
+        if eng is None:
             from ..engine.denoiser import SM100Denoiser
 
-            self._engine = SM100Denoiser(self)
-        return self._engine
+            if gang is None:
+                eng = SM100Denoiser(self)
+            else:
+                from ..engine.patch_engine import PatchDenoiser
 
-    def _denoise_sm100(self, x, embeds, plan, n_cond, guidance_scale, generator):
+                eng = PatchDenoiser(self, gang)
+            self._engine[key] = eng
+        return eng
+
+    def _denoise_sm100(self, x, embeds, plan, n_cond, guidance_scale, generator, gang=None):
         """Whole denoising loop on the engine: frames ride in the batch dimension of the captured plan."""
         nf = x.shape[2]
         frames = x[0].permute(1, 0, 2, 3).contiguous()                     # (F, 4, h, w)
@@ -119,13 +133,15 @@ class TextToVideoPipeline:
         if plan.needs_noise:
             noise = torch.randn((plan.num_steps,) + tuple(frames.shape), generator=generator, device=self.device,
                                 dtype=self.dtype)
-        out = self._sm100().run(frames, per_frame, plan, n_cond, float(guidance_scale), 0.0, None, None, 1.0, None,
-                                noise, None, num_frames=nf)
+        out = self._sm100(gang).run(frames, per_frame, plan, n_cond, float(guidance_scale), 0.0, None, None, 1.0, None,
+                                    noise, None, num_frames=nf)
         return out.permute(1, 0, 2, 3).unsqueeze(0)
 
     @torch.no_grad()
     def __call__(self, prompt="", negative_prompt=None, height=None, width=None, num_frames=16,
-                 num_inference_steps=50, guidance_scale=9.0, generator=None, output_type="np", **ignored):
+                 num_inference_steps=50, guidance_scale=9.0, generator=None, output_type="np", gang=None, **ignored):
+        """`gang` (parallel.runtime.Gang; every rank makes this call with the same seed): the clip is denoised
+        frame-split over the gang and its frames are decoded by the VAE in per-rank shares, then all-gathered."""
         vae_scale = 2 ** (len(self.vae.config["block_out_channels"]) - 1)
         sample = self.unet.config.get("sample_size", 32)
         height = int(height or sample * vae_scale)
@@ -148,7 +164,7 @@ class TextToVideoPipeline:
         n_cond = 2 if do_cfg else 1
         engine = self.backend == "sm100" and self.device.type == "cuda"
         if engine:
-            x = self._denoise_sm100(x, embeds, plan, n_cond, guidance_scale, generator)
+            x = self._denoise_sm100(x, embeds, plan, n_cond, guidance_scale, generator, gang)
         for i in range(0 if engine else plan.num_steps):
             t = torch.tensor(float(plan.timesteps[i]), device=self.device)
             model_in = torch.cat([x] * n_cond).to(self.dtype) * scale
@@ -162,6 +178,11 @@ class TextToVideoPipeline:
             return VideoOutput(frames=[], latents=x)
         z = (x[0].permute(1, 0, 2, 3) / self.vae.scaling_factor).contiguous()  # (F, 4, h, w)
         frames = []
+        if gang is not None and gang.world > 1:  # frames are independent for the VAE: every rank decodes its share
+            mine = gang.shard(z.shape[0])
+            part = self._decode(z[mine.start:mine.stop]) if len(mine) else \
+                torch.zeros((0, height, width, 3), dtype=torch.uint8, device=self.device)
+            return VideoOutput(frames=list(gang.all_gather_cat(part.contiguous()).cpu().numpy()), latents=x)
         for chunk in z.split(8 if not engine else 24):
             frames.extend(list(self._decode(chunk).cpu().numpy()))
         return VideoOutput(frames=frames, latents=x)

@@ -1,7 +1,8 @@
 """Text-to-video job callback (reference: swarm/video/tx2vid.py:17-88).  Defaults kept: 25 frames,
 mp4 (h264 -> falls back to mp4v when the OpenCV build lacks an h264 encoder) or webm (VP90),
 8 fps (Q12), thumbnail = frame 0.  The reference always enables model-CPU-offload; on B200 the
-3-D UNet stays resident and, with a gang lease, runs row-split across ranks."""
+3-D UNet stays resident and, when the job leased a gang (parallel/gang_worker.py), the clip is split along
+the frame axis across the ranks (engine/patch_engine.py::_FrameStepGraph)."""
 from __future__ import annotations
 
 import pathlib
@@ -11,6 +12,7 @@ from io import BytesIO
 import torch
 
 from ..output_processor import make_result
+from ..parallel.context import job_gang
 from ..registry import resolve
 from ..toolbox.video_helpers import frames_to_video, get_frame
 from ..utils.weight_cache import pipeline_cache
@@ -32,7 +34,7 @@ def txt2vid_diffusion_callback(device_identifier, model_name, **kwargs):
         lambda: TextToVideoPipeline.from_pretrained(model_name, revision=revision, variant=variant,
                                                     torch_dtype=torch.float16, device=device_identifier))
     pipeline.set_scheduler(scheduler_type, use_karras_sigmas=True)
-    p = pipeline(**kwargs)
+    p = pipeline(gang=job_gang(), **kwargs)  # with a gang lease: frame-split denoising + scattered VAE decode
     video_frames = p.frames
 
     container, codecs = ("mp4", ("h264", "avc1", "mp4v")) if content_type == "video/mp4" else ("webm", ("VP90", "VP80"))

@@ -886,8 +886,11 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
 
     // short self-attention sequences (temporal attention over frames): several batch entries per tile
     a.pack = 1;
-    if (p->seq_q == p->seq_kv && p->seq_q <= 64 && p->batch > 1) {
-        a.pack = 128 / p->seq_q;
+    // (queries and keys may differ in length: a frame-split clip attends from its own frames to all of them; row r of a
+    // tile belongs to entry r / seq_q and sees columns [entry * seq_kv, (entry + 1) * seq_kv))
+    const int seq_max = p->seq_q > p->seq_kv ? p->seq_q : p->seq_kv;
+    if (seq_max <= 64 && p->batch > 1) {
+        a.pack = 128 / seq_max;
         if (a.pack > p->batch) a.pack = p->batch;
         if (a.pack > 128) a.pack = 128;
         static int no_pack = -1;  // SW_ATTN_PACK=0: one batch entry per tile (A/B runs)

@@ -38,7 +38,8 @@ __device__ __forceinline__ int resolve_epoch(const PeerFlags& f) {
 // Everything this rank wrote before (on this stream) becomes visible to the peers, then its flag
 // slot on every peer is raised to `epoch`.
 __global__ void k_peer_signal(const PeerFlags f) {
-    __threadfence_system();
+    // (earlier kernels of this stream have completed; the release store below orders their writes before the flag.
+    // A system-scope fence here cost ~10 us per kernel on an NVLink-connected box for nothing.)
     if (threadIdx.x < f.world) st_release_sys(f.flags[threadIdx.x] + f.rank, resolve_epoch(f));
 }
 
@@ -53,24 +54,53 @@ __global__ void k_peer_wait(const PeerFlags f) {
 // rank runs the same kernel at the same point of its stream, so the waits cannot cycle.
 struct Xfers {
     int count;
+    int slices;             // CTAs per transfer
+    unsigned int* tickets;  // [8] arrival counters of this launch's transfers (zero between launches)
     int dst[8];
     const uint4* src[8];
     uint4* dst_ptr[8];
     long long n16[8];
 };
 
+// Arrival counters for the sliced transfers.  Launches of one process are stream-ordered per gang, and the last CTA
+// of a transfer re-arms its counter, so a small rotating pool is enough (slot = launch sequence number % 64).
+__device__ unsigned int g_xfer_tickets[64 * 8];
+
+// blockIdx.x = transfer * slices + slice.  A large transfer (the K/V of a video clip's frames is tens of MB) is
+// cut into `slices` contiguous pieces so that it is carried by many SMs' store pipes instead of one; the slice
+// that finishes last publishes the whole transfer and waits for the partner's.
 __global__ void __launch_bounds__(1024) k_peer_exchange(const PeerFlags f, const Xfers x) {
-    const int t = blockIdx.x;
+    const int t = blockIdx.x / x.slices, sl = blockIdx.x - t * x.slices;
     if (t >= x.count) return;
     const uint4* __restrict__ src = x.src[t];
     uint4* __restrict__ dst = x.dst_ptr[t];
-    for (long long i = threadIdx.x; i < x.n16[t]; i += blockDim.x) dst[i] = src[i];
-    __threadfence_system();
+    const long long per = (x.n16[t] + x.slices - 1) / x.slices;
+    const long long lo = per * sl, hi = lo + per < x.n16[t] ? lo + per : x.n16[t];
+    long long i = lo + threadIdx.x;
+    for (; i + 3 * 1024 < hi; i += 4 * 1024) {  // four independent 16-byte loads in flight per thread
+        const uint4 a = src[i], b = src[i + 1024], c = src[i + 2048], d = src[i + 3072];
+        dst[i] = a, dst[i + 1024] = b, dst[i + 2048] = c, dst[i + 3072] = d;
+    }
+    for (; i < hi; i += 1024) dst[i] = src[i];
+    // ordering: every thread's stores -> CTA barrier -> (sliced: device-scope fence + ticket) -> ONE st.release.sys,
+    // which is cumulative over everything that happened before it.  No system-scope fence per CTA: on a box with
+    // peer mappings each one stalls for microseconds.
+    if (x.slices > 1) __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        const int epoch = resolve_epoch(f);
-        st_release_sys(f.flags[x.dst[t]] + f.rank, epoch);
-        wait_flag_ge(f.flags[f.rank] + x.dst[t], epoch);
+        bool last = true;
+        if (x.slices > 1) {
+            last = atomicAdd(&x.tickets[t], 1u) == unsigned(x.slices) - 1u;
+            if (last) {
+                x.tickets[t] = 0u;
+                __threadfence();  // (the other slices' stores, observed through the ticket, precede the flag)
+            }
+        }
+        if (last) {
+            const int epoch = resolve_epoch(f);
+            st_release_sys(f.flags[x.dst[t]] + f.rank, epoch);
+            wait_flag_ge(f.flags[f.rank] + x.dst[t], epoch);
+        }
     }
 }
 
@@ -180,7 +210,23 @@ extern "C" int sw_peer_exchange(const sw_peers* peers, const sw_xfer* xfers, int
         x.dst_ptr[i] = static_cast<uint4*>(t.dst_ptr);
         x.n16[i] = t.nbytes / 16;
     }
-    k_peer_exchange<<<count, 1024, 0, static_cast<cudaStream_t>(stream)>>>(f, x);
+    long long biggest = 0;
+    for (int i = 0; i < count; ++i) biggest = x.n16[i] > biggest ? x.n16[i] : biggest;
+    // one slice per 256 KB, at most 16 per transfer and ~one wave of the chip in total
+    int slices = int((biggest * 16 + (256 << 10) - 1) / (256 << 10));
+    if (slices > 16) slices = 16;
+    if (slices * count > 128) slices = 128 / count;
+    if (slices < 1) slices = 1;
+    x.slices = slices;
+    static unsigned int* ticket_base[64] = {nullptr};  // per device: the symbol has one instance on each
+    static unsigned int seq = 0;
+    int dev = 0;
+    SW_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return swh::fail(-1, "sw_peer_exchange: device index %d out of range", dev);
+    if (!ticket_base[dev])  // (first call on a device: resolve the address outside any stream capture)
+        SW_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ticket_base[dev]), g_xfer_tickets));
+    x.tickets = ticket_base[dev] + (seq++ % 64) * 8;
+    k_peer_exchange<<<count * slices, 1024, 0, static_cast<cudaStream_t>(stream)>>>(f, x);
     SW_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -73,6 +73,16 @@ struct IGemmArgs {
     __half* rs_out[8];      // mode 2: rank d's staging buffer [world][m_local][ldc]
     int* flags[8];          // rank d's int32[world] epoch flags
     unsigned int* rs_ticket;
+    // ---- lean fused collectives (igemm_lean_body<.., MODE>): copy / reduce roles inside the GEMM grid, per-tile flags
+    __half* gathered[8];    // MODE 1: rank d's gathered activation [world * m_local][a_ld] (symmetric)
+    int a_ld;               // MODE 1: row pitch of the gathered buffer (elements)
+    int shard_tiles;        // 128-row tiles per rank shard (m_local / 128)
+    const int* epoch_base;  // optional device counter (CUDA-graph replays): epoch += *epoch_base * epoch_mul
+    int epoch_mul;
+    const __half* rs_stage; // MODE 2: this rank's staging [world][m_local][ldc] (what the peers push into)
+    __half* rs_final;       // MODE 2: this rank's reduced rows [m_local][ld_final]
+    int ld_final;
+    int dbg;                // SW_FUSED_DBG bit mask (timing bisection only): 1 no completion wait / flag, 2 no reduce role
 };
 
 struct AgMaps {
@@ -90,6 +100,25 @@ __device__ __forceinline__ void wait_flag_ge(const int* p, int v) {
         if (i > (1u << 27)) __trap();
         __nanosleep(64);
     }
+}
+// timing probe variants of the wait (SW_FUSED_DBG bits 16 / 32 / 64)
+__device__ __forceinline__ void wait_flag_ge_dbg(const int* p, int v, int dbg) {
+    if (!(dbg & (16 | 32 | 64))) {
+        wait_flag_ge(p, v);
+        return;
+    }
+    int cur;
+    for (unsigned i = 0;; ++i) {
+        if (dbg & 64)
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(cur) : "l"(p) : "memory");
+        else
+            asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(cur) : "l"(p) : "memory");
+        if (cur >= v) break;
+        if (i > (1u << 27)) __trap();
+        __nanosleep(64);
+    }
+    if (dbg & 32) asm volatile("fence.acq_rel.sys;" ::: "memory");
+    if (dbg & 16) asm volatile("fence.acq_rel.gpu;" ::: "memory");
 }
 
 // ---------------------------------------------------------------- raw-address PTX helpers
@@ -994,13 +1023,13 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     if (p.mode == 2) {
         // every CTA publishes its pushes system-wide; the CTA that finishes last raises this
         // rank's epoch flag on every peer (their reduce kernels poll it)
-        __threadfence_system();
+        __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) {
             const unsigned int total = gridDim.x * gridDim.y;
             if (atomicAdd(p.rs_ticket, 1u) == total - 1u) {
                 *p.rs_ticket = 0u;
-                __threadfence_system();
+                __threadfence();
                 for (int d = 0; d < p.world; ++d) st_release_sys(p.flags[d] + p.rank, p.epoch);
             }
         }
@@ -1072,11 +1101,125 @@ __global__ void __launch_bounds__(kThreads)
 // choices are template parameters or gone, everything that does not touch global memory is computed before the
 // dependency wait, and (when the grid is a single wave anyway) the residual tile gets its own staging boxes so
 // its TMA loads are issued before the main loop instead of after it.
-template <bool PAIR, bool HAS_RES>
+//
+// MODE 1 / 2 are the fused collectives of a tensor-parallel block (plain GEMMs, single-CTA tiles).  Both keep the
+// math path above untouched and add a second ROLE to the same grid, tied to it by per-tile epoch flags:
+//   MODE 1, all-gather -> GEMM: blocks with blockIdx.y == 0 (the first the hardware dispatches) copy this rank's
+//     activation shard, tile by tile, into every peer's gathered buffer with 16-byte stores over NVLink and raise
+//     flag [rank][tile] on the peer; a compute block whose 128 rows came from rank s waits for flag [s][tile] before
+//     its first A load, and then reads LOCAL memory only -- a remote tile crosses NVLink exactly once, and the tile
+//     order is rotated so every rank starts on rows it already holds.
+//   MODE 2, GEMM -> reduce-scatter: a compute block hands its fp16 partial tile to the TMA store unit with the tensor
+//     map of the rows' OWNER (its staging slot for this rank, over NVLink) and raises flag [rank][tile_m][tile_n]
+//     there once the stores have completed; blocks with blockIdx.y == gridDim.y - 1 (the last dispatched) each own
+//     some tiles of this rank's rows: they wait for the `world` flags of a tile and add the slots in rank order in
+//     fp32 (+ bias, + residual) -- deterministic, and a tile is reduced as soon as its last partial lands instead
+//     of after the whole GEMM and a kernel boundary.
+// Neither role ever waits for a block with a higher dispatch index of its own grid, so the waits cannot cycle.
+struct PeerMaps {
+    CUtensorMap m[8];
+};
+
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ int lean_epoch(const IGemmArgs& p) {
+    return p.epoch + (p.epoch_base ? __ldcg(p.epoch_base) * p.epoch_mul : 0);
+}
+
+__device__ __forceinline__ void lean_push_role(const IGemmArgs& p) {
+    // MODE 1 copy role: tile blockIdx.x of this rank's shard -> the same rows of every peer's gathered buffer
+    const int tile = blockIdx.x;
+    pdl_trigger();
+    pdl_wait();  // the shard is the previous kernel's output
+    if (tile >= p.shard_tiles) return;
+    const int cpr = p.c1 >> 3;                       // 16-byte chunks per row
+    const int ld16 = p.a_ld >> 3;
+    const size_t row0 = size_t(p.rank) * p.m_local + size_t(tile) * BM;
+    const uint4* __restrict__ src = reinterpret_cast<const uint4*>(p.gathered[p.rank]) + row0 * ld16;
+    const int total = BM * cpr;
+    for (int i = threadIdx.x; i < total; i += 4 * int(blockDim.x)) {
+        uint4 v[4];
+        int off[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int ii = i + u * int(blockDim.x);
+            const int r = ii / cpr;
+            off[u] = ii < total ? r * ld16 + (ii - r * cpr) : -1;
+            if (off[u] >= 0) v[u] = src[off[u]];
+        }
+        for (int d = 0; d < p.world; ++d) {
+            if (d == p.rank) continue;
+            uint4* __restrict__ dst = reinterpret_cast<uint4*>(p.gathered[d]) + row0 * ld16;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (off[u] >= 0) dst[off[u]] = v[u];
+        }
+    }
+    __syncthreads();  // (every thread's stores happen before the release stores below; no system fence needed)
+    if (int(threadIdx.x) < p.world && int(threadIdx.x) != p.rank)
+        st_release_sys(p.flags[threadIdx.x] + p.rank * p.shard_tiles + tile, lean_epoch(p));
+}
+
+__device__ __forceinline__ void lean_reduce_role(const IGemmArgs& p, int b) {
+    // MODE 2 reduce role: block b of shard_tiles * ntile owns ONE tile of this rank's rows, in the order the
+    // partials arrive; out = sum over src (rank order) of staging[src] (+ bias) (+ residual)
+    const int ntile = (p.cout + p.bn - 1) / p.bn;
+    const int tm = b / ntile;
+    const int r0 = tm * BM;
+    pdl_trigger();
+    pdl_wait();  // (residual / out belong to earlier kernels until here)
+    for (int tn = b % ntile; tn < ntile; tn += ntile) {
+        if (int(threadIdx.x) < p.world && !(p.dbg & 4))
+            wait_flag_ge_dbg(p.flags[p.rank] + (int(threadIdx.x) * p.shard_tiles + tm) * ntile + tn, lean_epoch(p), p.dbg);
+        __syncthreads();
+        const int c0 = tn * p.bn;
+        const int ncol = min(p.bn, p.cout - c0);
+        const int octs = ncol >> 3;
+        for (int i = threadIdx.x; i < BM * octs; i += blockDim.x) {
+            const int r = r0 + i / octs, c = c0 + ((i % octs) << 3);
+            float acc[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+            auto add8 = [&](const __half* ptr) {
+                const uint4 v = __ldcg(reinterpret_cast<const uint4*>(ptr));
+                const float2 a = unpack_h2(v.x), b = unpack_h2(v.y), cc = unpack_h2(v.z), d = unpack_h2(v.w);
+                acc[0] += a.x, acc[1] += a.y, acc[2] += b.x, acc[3] += b.y;
+                acc[4] += cc.x, acc[5] += cc.y, acc[6] += d.x, acc[7] += d.y;
+            };
+            for (int src = 0; src < p.world; ++src) add8(p.rs_stage + (size_t(src) * p.m_local + r) * p.ldc + c);
+            if (p.bias) add8(p.bias + c);
+            if (p.residual) add8(p.residual + size_t(r) * p.ldr + c);
+            *reinterpret_cast<uint4*>(p.rs_final + size_t(r) * p.ld_final + c) =
+                make_uint4(pack_h2(acc[0], acc[1]), pack_h2(acc[2], acc[3]), pack_h2(acc[4], acc[5]),
+                           pack_h2(acc[6], acc[7]));
+        }
+        __syncthreads();
+    }
+}
+
+template <bool PAIR, bool HAS_RES, int MODE = 0>
 __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const CUtensorMap& tmA2,
                                                 const CUtensorMap& tmB, const CUtensorMap& tmOut,
                                                 const CUtensorMap& tmRes, const CUtensorMap& tmOut32,
-                                                const IGemmArgs& p) {
+                                                const IGemmArgs& p, const PeerMaps* pm = nullptr) {
+    // fused modes run on a 1-D grid so that the dispatch order is exactly: [copy blocks] -> compute blocks, row tile
+    // major in rank-rotated order (every column tile of the rows this rank already holds before any row that has to
+    // arrive; rows this rank owns last) -> [reduce blocks]
+    const int ntile_f = MODE != 0 ? (p.cout + p.bn - 1) / p.bn : 1;
+    int cblock = int(blockIdx.x);        // compute block index
+    if (MODE == 1) {
+        if (cblock < p.shard_tiles) {
+            lean_push_role(p);
+            return;
+        }
+        cblock -= p.shard_tiles;
+    }
+    if (MODE == 2 && cblock >= p.tiles_x * ntile_f) {
+        if (!(p.dbg & 2)) lean_reduce_role(p, cblock - p.tiles_x * ntile_f);
+        return;
+    }
+    const int ctile_f = MODE != 0 ? cblock % ntile_f : int(blockIdx.y);
     const int BN = p.bn;
     const int B_STAGE_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
     const int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -1136,13 +1279,17 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
 
     // ---- everything that needs no global memory comes before the dependency wait
     int t = blockIdx.x;
+    if (MODE != 0)  // rank-rotated tile order: (all-gather) own rows first, (reduce-scatter) own rows last
+        t = (cblock / ntile_f + (p.rank + (MODE == 2 ? 1 : 0)) * p.shard_tiles) % p.tiles_x;
     const int tx = t % p.tiles_x;
     t /= p.tiles_x;
     const int ty = t % p.tiles_y;
     const int tn = t / p.tiles_y;
     const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
-    const int col0 = blockIdx.y * BN;
+    const int col0 = ctile_f * BN;
     const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
+    const int peer_of_tile = MODE != 0 ? x0 / p.m_local : 0;                 // who produced (1) / owns (2) these rows
+    const int tile_in_shard = MODE != 0 ? (x0 - peer_of_tile * p.m_local) / BM : 0;
     const int nkb1 = (p.c1 + BK - 1) / BK;
     const int nkb2 = (p.c2 + BK - 1) / BK;
     const int per_tap = nkb1 + nkb2;
@@ -1175,6 +1322,12 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
         uint32_t sa = smem0, fb = full0, eb = empty0;
         int s = 0;
         uint32_t ph = 1;
+        if (MODE == 1 && peer_of_tile != p.rank) {
+            // these rows are another rank's: its copy role raises the flag once they have landed in OUR buffer.
+            // The data arrived through generic-proxy stores and is about to be read by the async proxy (TMA).
+            wait_flag_ge(p.flags[p.rank] + peer_of_tile * p.shard_tiles + tile_in_shard, lean_epoch(p));
+            fence_proxy_async_all();
+        }
         if (lane == 0) TR(3);
         for (int it = 0; it < total_kb; ++it) {
             bar_wait(eb, ph);
@@ -1280,7 +1433,7 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
         for (int i = threadIdx.x - 64; i < BN; i += 256) {
             const int col = col0 + i;
             float b = 0.0f;
-            if (col < p.cout) {
+            if (col < p.cout && MODE != 2) {  // (reduce-scatter: bias and residual are added once, by the reduce role)
                 if (p.bias) b = __half2float(p.bias[col]);
                 if (p.row_bias && n0 < p.n) b += __half2float(p.row_bias[size_t(n0) * p.row_bias_ld + col]);
             }
@@ -1343,7 +1496,10 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
             fence_proxy_async_smem();
             asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             if (lead) {
-                tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + c0, x0, y0, n0);
+                if (MODE == 2)  // the owner's staging slot for this rank (peer memory), rows relative to its shard
+                    tma_store_4d(&pm->m[peer_of_tile], out_stage + box, col0 + c0, x0 - peer_of_tile * p.m_local, 0, 0);
+                else
+                    tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + c0, x0, y0, n0);
                 bulk_commit();
                 if (HAS_RES && sl + 2 < nslab) {
                     bar_expect_tx(rfull, a_bytes);
@@ -1351,7 +1507,24 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
                 }
             }
         }
-        if (lead) bulk_wait_read<0>();
+        if (MODE == 2 && (p.dbg & 1)) {
+            if (lead) bulk_wait_read<0>();
+        } else if (MODE == 2) {
+            // both warpgroups' stores must have COMPLETED (not merely been read out of shared memory) before the
+            // owner is told; async-proxy writes are ordered before the generic-proxy flag store by the fence
+            if (lead) {
+                bulk_wait_all();
+                fence_proxy_async_all();
+            }
+            asm volatile("bar.sync 3, 256;" ::: "memory");
+            if (threadIdx.x == 64 && !(p.dbg & 8)) {
+                const int ntile = (p.cout + BN - 1) / BN;
+                st_release_sys(p.flags[peer_of_tile] + (p.rank * p.shard_tiles + tile_in_shard) * ntile + ctile_f,
+                               lean_epoch(p));
+            }
+        } else if (lead) {
+            bulk_wait_read<0>();
+        }
     }
     if (threadIdx.x == 64) TR(9);
     tc_fence_before();
@@ -1392,6 +1565,18 @@ SW_LEAN_KERNEL(k_igemm_lean_r, false, true)
 SW_LEAN_KERNEL(k_igemm2_lean, true, false)
 SW_LEAN_KERNEL(k_igemm2_lean_r, true, true)
 #undef SW_LEAN_KERNEL
+
+__global__ void __launch_bounds__(kThreadsLean, 2)
+    k_igemm_lean_ag(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmOut32,
+                    const IGemmArgs p) {
+    igemm_lean_body<false, false, 1>(tmA1, tmA1, tmB, tmOut, tmOut, tmOut32, p);
+}
+__global__ void __launch_bounds__(kThreadsLean, 2)
+    k_igemm_lean_rs(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ PeerMaps pm, const IGemmArgs p) {
+    igemm_lean_body<false, false, 2>(tmA1, tmA1, tmB, pm.m[0], pm.m[0], pm.m[0], p, &pm);
+}
 
 // =================================================================================================
 // Persistent variant (mode 0, single-CTA tiles, no split-K): each CTA walks tiles
@@ -2386,6 +2571,142 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         return 0;
     }
     return launch(a, tA1, tA2, tB, tOut, tRes, tOut32, grid_x, pair, static_cast<cudaStream_t>(stream));
+}
+
+// ---- fused collectives on the lean kernel (copy / reduce roles inside the GEMM grid, per-tile flags)
+static int igemm_fused_lean(const sw_igemm_params* p, const sw_peers* peers, int mode, int m_local, void* final_out,
+                            int ld_final, void* stream) {
+    if (!p || !p->wgt || !peers || peers->world < 1 || peers->world > 8 || peers->rank < 0 || peers->rank >= peers->world)
+        return swh::fail(-1, "sw_igemm fused: null argument or bad peer description");
+    const int W = peers->world, R = peers->rank;
+    if (p->kh != 1 || p->kw != 1 || p->n != 1 || p->h != 1 || p->c2 != 0 || p->act != SW_ACT_NONE || p->row_bias ||
+        p->row_stats_in || p->row_stats_out || p->bf16 || p->w_kmajor)
+        return swh::fail(-1, "sw_igemm fused: defined for plain fp16 GEMMs (no activation, no row bias)");
+    if (m_local <= 0 || m_local % BM || p->w != m_local * W)
+        return swh::fail(-1, "sw_igemm fused: m_local=%d must be a multiple of 128 and w == world*m_local", m_local);
+    if (p->c1 <= 0 || p->c1 % 8 || p->cout <= 0 || p->cout % 8 || p->ldc % 8 || (p->a_ld && (p->a_ld % 8 || p->a_ld < p->c1)))
+        return swh::fail(-1, "sw_igemm fused: channel counts / leading dimensions must be multiples of 8");
+    if (mode == 1 && (!p->out || p->residual)) return swh::fail(-1, "sw_igemm_allgather: needs out, takes no residual");
+    if (mode == 2 && (!p->a1 || !final_out || p->cout % 64 || ld_final % 8 || (p->residual && p->ldr % 8)))
+        return swh::fail(-1, "sw_igemm_reducescatter: needs a1 and out, cout %% 64 == 0");
+    for (int d = 0; d < W; ++d)
+        if (!peers->peer[d] || !peers->flags[d]) return swh::fail(-1, "sw_igemm fused: peer %d has no buffer / flags", d);
+
+    IGemmArgs a;
+    memset(&a, 0, sizeof(a));
+    a.c1 = p->c1;
+    a.n = a.h = 1;
+    a.w = p->w;
+    a.kh = a.kw = 1;
+    a.cout = p->cout;
+    a.bw = BM;
+    a.bh = a.bi = 1;
+    a.tiles_x = p->w / BM;
+    a.tiles_y = 1;
+    a.bias = static_cast<const __half*>(p->bias);
+    a.residual = static_cast<const __half*>(p->residual);
+    a.ldr = p->ldr;
+    a.out = static_cast<__half*>(p->out);
+    a.ldc = p->ldc;
+    a.out_scale = 1.0f;
+    a.mode = mode;
+    a.world = W;
+    a.rank = R;
+    a.epoch = peers->epoch;
+    a.epoch_base = peers->epoch_base;
+    a.epoch_mul = peers->epoch_mul;
+    a.m_local = m_local;
+    a.shard_tiles = m_local / BM;
+    const int lda = p->a_ld > 0 ? p->a_ld : p->c1;
+    a.a_ld = lda;
+    for (int d = 0; d < W; ++d) {
+        a.flags[d] = peers->flags[d];
+        if (mode == 1) a.gathered[d] = static_cast<__half*>(peers->peer[d]);
+    }
+    if (mode == 2) {
+        a.rs_stage = static_cast<const __half*>(peers->peer[R]);
+        a.rs_final = static_cast<__half*>(final_out);
+        a.ld_final = ld_final;
+    }
+    int bn = p->tile_n > 0 ? p->tile_n : 128;
+    if (bn > p->cout) bn = (p->cout + 31) / 32 * 32;
+    if (bn < 32 || bn > 256 || bn % 32 || (mode == 2 && bn % 64))
+        return swh::fail(-1, "sw_igemm fused: tile_n=%d must be a multiple of 32 (64 for reduce-scatter) in [32,256]", bn);
+    a.bn = bn;
+    a.tmem_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;
+    const int ntile = (p->cout + bn - 1) / bn;
+    const int kblocks = (p->c1 + 63) / 64;
+    const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+    int stages = (3 * stage_bytes <= 110 * 1024) ? 3 : 4;
+    if (stage_bytes <= 24 * 1024) stages = 4;
+    if (p->stages > 0) stages = p->stages;
+    while (stages > 2 && stages * stage_bytes > 200 * 1024) --stages;
+    if (kblocks < stages) stages = kblocks;
+    a.stages = stages;
+    a.idesc = sw::umma_idesc(128, bn, 0, 0, 0);
+    a.tma_epi = 1;
+    a.epi_alias = 1;
+    {
+        const char* e = getenv("SW_FUSED_DBG");
+        a.dbg = e ? atoi(e) : 0;
+    }
+    const int ring = stages * stage_bytes < 65536 ? 65536 : stages * stage_bytes;
+    const int smem = ring + 1024 + 512;
+
+    CUtensorMap tA, tB;
+    {
+        const void* abase = mode == 1 ? peers->peer[R] : p->a1;   // (all-gather: A is this rank's OWN gathered buffer)
+        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), 1, 1};
+        const uint64_t str[3] = {uint64_t(lda) * 2, uint64_t(p->w) * lda * 2, uint64_t(p->w) * lda * 2};
+        const uint32_t box[4] = {64, BM, 1, 1};
+        if (int rc = swh::encode_tmap_f16(&tA, abase, 4, dims, str, box)) return rc;
+        const uint64_t bd[2] = {uint64_t(p->c1), uint64_t(p->cout)};
+        const uint64_t bs[1] = {(p->w_ld > 0 ? uint64_t(p->w_ld) : uint64_t(p->c1)) * 2};
+        const uint32_t bb[2] = {64, uint32_t(bn)};
+        if (int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, bd, bs, bb)) return rc;
+    }
+    static bool configured[64] = {false};
+    int dev = 0;
+    SW_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 64 && !configured[dev]) {
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_lean_ag, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SW_CUDA_OK(cudaFuncSetAttribute(k_igemm_lean_rs, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        configured[dev] = true;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // 1-D grid: [copy blocks |] compute blocks (row tile major) [| one reduce block per tile of this rank's rows]
+    const dim3 grid(a.tiles_x * ntile + a.shard_tiles * (mode == 1 ? 1 : ntile), 1, 1);
+    if (mode == 1) {
+        CUtensorMap tOut, tOut32;
+        const uint64_t dims[4] = {uint64_t(p->cout), uint64_t(p->w), 1, 1};
+        const uint64_t so[3] = {uint64_t(p->ldc) * 2, uint64_t(p->w) * p->ldc * 2, uint64_t(p->w) * p->ldc * 2};
+        const uint32_t box[4] = {64, BM, 1, 1}, box32[4] = {32, BM, 1, 1};
+        if (int rc = swh::encode_tmap_f16(&tOut, p->out, 4, dims, so, box)) return rc;
+        if (int rc = swh::encode_tmap_f16_ex(&tOut32, p->out, 4, dims, so, box32, false)) return rc;
+        SW_CUDA_OK(swh::launch_pdl(k_igemm_lean_ag, grid, dim3(kThreadsLean), size_t(smem), st, 1, tA, tB, tOut, tOut32, a));
+    } else {
+        PeerMaps pm;
+        for (int d = 0; d < W; ++d) {  // rank d's staging slot [R]: rows of d's shard, as this rank's partial
+            __half* base = static_cast<__half*>(peers->peer[d]) + size_t(R) * m_local * p->ldc;
+            const uint64_t dims[4] = {uint64_t(p->cout), uint64_t(m_local), 1, 1};
+            const uint64_t so[3] = {uint64_t(p->ldc) * 2, uint64_t(m_local) * p->ldc * 2, uint64_t(m_local) * p->ldc * 2};
+            const uint32_t box[4] = {64, BM, 1, 1};
+            if (int rc = swh::encode_tmap_f16(&pm.m[d], base, 4, dims, so, box)) return rc;
+        }
+        for (int d = W; d < 8; ++d) pm.m[d] = pm.m[0];
+        SW_CUDA_OK(swh::launch_pdl(k_igemm_lean_rs, grid, dim3(kThreadsLean), size_t(smem), st, 1, tA, tB, pm, a));
+    }
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_igemm_allgather(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* stream) {
+    return igemm_fused_lean(p, peers, 1, m_local, nullptr, 0, stream);
+}
+
+extern "C" int sw_igemm_reducescatter(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* out,
+                                      int ldo, void* stream) {
+    return igemm_fused_lean(p, peers, 2, m_local, out, ldo, stream);
 }
 
 extern "C" int sw_igemm(const sw_igemm_params* p, void* stream) {

@@ -180,7 +180,7 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
     }
     if (threadIdx.x == 0) tickets[n] = 0u;  // leave the scratch ready for the next call
     if (dist.world > 1) {
-        __threadfence_system();
+        __threadfence();  // device scope is enough ahead of the ticket; the flag store below is the sys-scope release
         __syncthreads();
         if (threadIdx.x == 0) {
             // the image that finishes last raises this rank's flag on every peer
@@ -788,6 +788,91 @@ extern "C" int sw_groupnorm_nhwc_dist(const void* x, const void* x2, void* y, co
     if (!x || !y || !stats_scratch || !peers) return swh::fail(-1, "sw_groupnorm_nhwc_dist: null argument");
     return sw_groupnorm_launch(x, x2, y, gamma, beta, n, hw, c1, c2, groups, eps, silu,
                                stats_scratch, static_cast<cudaStream_t>(stream), peers);
+}
+
+// ---- the two halves of a GroupNorm as separate kernels: what a framework has to run when the statistics
+// all-reduce in between is a library call (NCCL).  They exist as the like-for-like baseline of
+// sw_groupnorm_nhwc_dist (parallel/collectives.py::groupnorm_nccl_native), not as a product path.
+namespace {
+__global__ void __launch_bounds__(256) k_gn_sums(const __half* __restrict__ x, float* __restrict__ sums, int hw, int c,
+                                                 int groups, int rows_per_cta) {
+    // grid (row chunks, n): per-channel-pair partial sums over this CTA's rows, folded per group, one atomicAdd
+    // per (CTA, group, moment)
+    extern __shared__ float sh[];  // [2][groups]
+    const int n = blockIdx.y, cpg = c / groups;
+    for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) sh[i] = 0.0f;
+    __syncthreads();
+    const int r0 = blockIdx.x * rows_per_cta, r1 = min(hw, r0 + rows_per_cta);
+    const int pairs = c >> 1;
+    for (int pc = threadIdx.x; pc < pairs; pc += blockDim.x) {
+        float su = 0.0f, sq = 0.0f;
+        const __half2* col = reinterpret_cast<const __half2*>(x + (size_t(n) * hw + r0) * c) + pc;
+        for (int r = r0; r < r1; ++r, col += pairs) {
+            const float2 v = __half22float2(*col);
+            su += v.x + v.y;
+            sq += v.x * v.x + v.y * v.y;
+        }
+        const int g = (2 * pc) / cpg;
+        atomicAdd(&sh[g], su);
+        atomicAdd(&sh[groups + g], sq);
+    }
+    __syncthreads();
+    for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+        atomicAdd(&sums[(size_t(n) * groups + g) * 2], sh[g]);
+        atomicAdd(&sums[(size_t(n) * groups + g) * 2 + 1], sh[groups + g]);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_gn_apply_sums(const __half* __restrict__ x, const float* __restrict__ sums,
+                                                       const __half* __restrict__ gamma, const __half* __restrict__ beta,
+                                                       __half* __restrict__ y, int hw, int c, int groups, float inv_count,
+                                                       float eps, int silu, long long total_pairs) {
+    const int cpg = c / groups, pairs = c >> 1;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_pairs;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int pc = int(i % pairs);
+        const long long row = i / pairs;
+        const int n = int(row / hw), g = (2 * pc) / cpg;
+        const float mean = sums[(size_t(n) * groups + g) * 2] * inv_count;
+        const float var = fmaxf(sums[(size_t(n) * groups + g) * 2 + 1] * inv_count - mean * mean, 0.0f);
+        const float rstd = rsqrtf(var + eps);
+        const float2 v = __half22float2(reinterpret_cast<const __half2*>(x)[i]);
+        const float2 ga = __half22float2(reinterpret_cast<const __half2*>(gamma)[pc]);
+        const float2 be = __half22float2(reinterpret_cast<const __half2*>(beta)[pc]);
+        float u0 = (v.x - mean) * rstd * ga.x + be.x, u1 = (v.y - mean) * rstd * ga.y + be.y;
+        if (silu) {
+            u0 = silu_f(u0);
+            u1 = silu_f(u1);
+        }
+        reinterpret_cast<__half2*>(y)[i] = __floats2half2_rn(u0, u1);
+    }
+}
+}  // namespace
+
+extern "C" int sw_gn_partial_sums(const void* x, float* sums, int n, int hw, int c, int groups, void* stream) {
+    if (!x || !sums || c % 2 || groups <= 0 || c % groups || (c / groups) % 2)
+        return swh::fail(-1, "sw_gn_partial_sums: bad arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SW_CUDA_OK(cudaMemsetAsync(sums, 0, size_t(n) * groups * 2 * sizeof(float), st));
+    const int rows_per_cta = 64;
+    k_gn_sums<<<dim3((hw + rows_per_cta - 1) / rows_per_cta, n), 256, 2 * groups * sizeof(float), st>>>(
+        static_cast<const __half*>(x), sums, hw, c, groups, rows_per_cta);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sw_gn_apply_sums(const void* x, const float* sums, const void* gamma, const void* beta, void* y, int n,
+                                int hw, int c, int groups, long long count, float eps, int silu, void* stream) {
+    if (!x || !sums || !gamma || !beta || !y || c % 2 || c % groups || (c / groups) % 2 || count <= 0)
+        return swh::fail(-1, "sw_gn_apply_sums: bad arguments");
+    const long long total = (long long)n * hw * (c / 2);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_gn_apply_sums<<<int(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __half*>(x), sums, static_cast<const __half*>(gamma), static_cast<const __half*>(beta),
+        static_cast<__half*>(y), hw, c, groups, 1.0f / float(count), eps, silu, total);
+    SW_CUDA_OK(cudaGetLastError());
+    return 0;
 }
 
 extern "C" int sw_layernorm(const void* x, void* y, const void* gamma, const void* beta, int rows,

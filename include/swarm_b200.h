@@ -132,6 +132,37 @@ int sw_igemm_rs(const sw_igemm_params* p, const sw_peers* peers, int m_local, ui
 int sw_rs_reduce(const void* staging_local, void* out, const void* bias, const void* residual, int m_local,
                  int ncols, int ld_stage, int ldo, int ldr, const sw_peers* peers, void* stream);
 
+/* The two halves of a GroupNorm as separate kernels (per-(image, group) sum / sum of squares into fp32
+ * sums[n][groups][2]; apply given such sums over `count` elements per group): the like-for-like baseline of
+ * sw_groupnorm_nhwc_dist with a library all-reduce in between.  Not used by any product path. */
+int sw_gn_partial_sums(const void* x, float* sums, int n, int hw, int c, int groups, void* stream);
+int sw_gn_apply_sums(const void* x, const float* sums, const void* gamma, const void* beta, void* y, int n, int hw,
+                     int c, int groups, long long count, float eps, int silu, void* stream);
+
+/* Second generation of the two fused GEMM collectives (what parallel/collectives.py and the tensor-parallel block use;
+ * the first generation above is kept for A/B runs).  Both add a second role to the GEMM's own grid, tied to the
+ * compute blocks by PER-TILE epoch flags, so data crosses NVLink once and reduction starts tile by tile:
+ *
+ * sw_igemm_allgather: peers->peer[d] = rank d's GATHERED activation [world*m_local, a_ld] (symmetric memory); this
+ *   rank's shard already sits in rows [rank*m_local, (rank+1)*m_local) of its own buffer (the producing kernel wrote
+ *   it there).  Copy blocks (dispatched first) push the shard tile by tile into the same rows of every peer's
+ *   buffer and raise flag [rank*T + tile] there (T = m_local/128); a compute block whose rows came from rank s waits
+ *   for flag [s*T + tile] and then TMA-loads LOCAL memory only.  p->a1 is ignored, p->a_ld is the pitch of the
+ *   gathered buffer, p->w == world*m_local.  peers->flags[d]: int32 [world*T] on rank d.
+ *   Reuse rule: a peer may still read its gathered buffer while this rank starts the next call -- alternate two
+ *   gathered buffers (epoch parity) or put a collective of the opposite direction in between.
+ *
+ * sw_igemm_reducescatter: partial = a1 . wgt^T over this rank's K shard for all world*m_local rows; a compute block
+ *   TMA-stores its fp16 tile into the staging slot [rank] of the rows' owner (peers->peer[d]: fp16
+ *   [world][m_local][ldc] on rank d) and raises flag [(rank*T + tile_m)*NT + tile_n] there once the stores have
+ *   completed (NT = column tiles); reduce blocks (dispatched last) wait for the `world` flags of a tile of this
+ *   rank's rows and write out[m_local, ldo] = sum over ranks in rank order, fp32 (+ p->bias, + p->residual).
+ *   p->out is ignored; p->cout % 64 == 0.  peers->flags[d]: int32 [world*T*NT].  Same reuse rule for `staging`.
+ * Plain fp16 GEMMs only (no activation); m_local % 128 == 0; p->tile_n (default 128) names the column tile. */
+int sw_igemm_allgather(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* stream);
+int sw_igemm_reducescatter(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* out, int ldo,
+                           void* stream);
+
 /* Epoch-flag signal / wait between the ranks of a gang (st.release.sys / ld.acquire.sys on peer
  * mappings; bounded spin).  Used to publish a tensor to the peers and as the NCCL-free barrier. */
 int sw_peer_signal(const sw_peers* peers, void* stream);

@@ -95,12 +95,60 @@ arena.barrier()
 skewed(lambda: ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols))
 ops.allgather_gemm_nccl(xs.local, w_cols, out_n, bias=b_cols)
 ref = x_full.float() @ w_cols.float().t() + b_cols.float()
-tf = timed(lambda: ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols))
+tf1 = timed(lambda: ops.allgather_gemm_fused(xs, w_cols, out_f, bias=b_cols))
 tn = timed(lambda: ops.allgather_gemm_nccl(xs.local, w_cols, out_n, bias=b_cols))
 flops = 2.0 * W * m_local * k * (n // W)
 link_bytes = (W - 1) * m_local * k * 2
-report("allgather_gemm", relerr(out_f, ref), relerr(out_n, ref), tf, tn,
-       dict(gflop=flops / 1e9, link_mb=link_bytes / 1e6))
+err_v1 = relerr(out_f, ref)
+# second generation: copy role inside the GEMM grid pushes the shard once, compute blocks read local memory.
+# Inputs change on every call (the shard is rewritten, scaled by the call index) and the LAST result is checked, so a
+# racing overwrite of a buffer a peer still reads cannot hide behind identical values.
+out_f.zero_()
+calls = [0]
+
+
+def ag2():
+    calls[0] += 1
+    g = ops.gather_buffer(m_local, k)
+    torch.mul(x_full[R * m_local:(R + 1) * m_local], float(calls[0] % 3 + 1), out=g.local[R * m_local:(R + 1) * m_local])
+    ops.allgather_gemm(g, w_cols, out_f, bias=b_cols)
+
+
+skewed(ag2)
+for _ in range(5):  # back-to-back calls on changing inputs (parity buffers, no host sync in between)
+    ag2()
+torch.cuda.synchronize()
+gang.barrier()
+for pair_buf in ops._gather[(m_local, k)]:  # timing runs on fixed inputs: both parity buffers hold the shard
+    pair_buf.local[R * m_local:(R + 1) * m_local].copy_(x_full[R * m_local:(R + 1) * m_local])
+scratch_ag = torch.empty_like(out_f)
+tf = timed(lambda: ops.allgather_gemm(ops.gather_buffer(m_local, k), w_cols, scratch_ag, bias=b_cols))
+ref_last = (x_full.float() * float(calls[0] % 3 + 1)) @ w_cols.float().t() + b_cols.float()
+# diagnostics: (a) the same kernel with every "peer" pointing at this rank's own memory and epoch 0 (no NVLink traffic,
+# no waiting): what the two-role kernel costs by itself; (b) a bare push exchange of the same bytes
+g_loc = ops.gather_buffer(m_local, k)
+g_loc.local.copy_(x_full)
+fl_loc = ops._flags_for("ag", W * (m_local // 128))
+pf_loc = nat.make_peers(W, R, 0, [g_loc.peer_ptr(R)] * W, [fl_loc.peer_ptr(R)] * W)
+t_ag_local = timed(lambda: nat.igemm_allgather(w_cols, out_n, pf_loc, m_local=m_local, k=k, bias=b_cols, tile_n=256))
+xch = arena.alloc(W, m_local, k)
+xfl = arena.alloc_flags(8)
+xcalls = [0]
+
+
+def push_only():
+    xcalls[0] += 1
+    pf = nat.make_peers(W, R, xcalls[0], None, xfl.peer_ptrs())
+    nat.peer_exchange(pf, [(d, xs.local, xch.peer_ptr(d) + R * m_local * k * 2) for d in range(W) if d != R])
+
+
+t_push = timed(push_only)
+x_all = x_full.clone()
+t_gemm = timed(lambda: nat.linear(x_all, w_cols, out=out_n, bias=b_cols))  # the math alone (no communication at all)
+tf256 = timed(lambda: ops.allgather_gemm(ops.gather_buffer(m_local, k), w_cols, out_n, bias=b_cols, tile_n=256))
+report("allgather_gemm", relerr(out_f, ref_last), relerr(out_n, ref) if args.no_timing else 0.0, tf, tn,
+       dict(gflop=flops / 1e9, link_mb=link_bytes / 1e6, us_fused_gen1=tf1, rel_err_gen1=err_v1, us_local_gemm_only=t_gemm,
+            us_fused_tile256=tf256, us_fused_tile256_local_only=t_ag_local, us_push_exchange_only=t_push))
 
 # ---------------------------------------------------------------- W12 GEMM -> reduce-scatter (FF-out shape)
 kk, n2 = 2560, 640
@@ -119,10 +167,38 @@ arena.barrier()
 skewed(lambda: ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc))
 ops.gemm_reducescatter_nccl(x_ksh, w_ksh, o_n, bias=b2, residual=res_loc)
 ref2 = (x2.float() @ w2.float().t() + b2.float() + res_full.float())[R * m_local:(R + 1) * m_local]
-tf = timed(lambda: ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc))
+tf1 = timed(lambda: ops.gemm_reducescatter_fused(x_ksh, w_ksh, staging, o_f, bias=b2, residual=res_loc))
 tn = timed(lambda: ops.gemm_reducescatter_nccl(x_ksh, w_ksh, o_n, bias=b2, residual=res_loc))
-report("gemm_reducescatter", relerr(o_f, ref2), relerr(o_n, ref2), tf, tn,
-       dict(gflop=2.0 * W * m_local * ks * n2 / 1e9, link_mb=(W - 1) * m_local * n2 * 2 / 1e6))
+err_v1 = relerr(o_f, ref2)
+o_f.zero_()
+x_var = x_ksh.clone()
+rcalls = [0]
+
+
+def rs2():
+    rcalls[0] += 1
+    torch.mul(x_ksh, float(rcalls[0] % 3 + 1), out=x_var)  # inputs differ call to call, the last result is checked
+    ops.gemm_reducescatter(x_var, w_ksh, o_f, bias=b2, residual=res_loc)
+
+
+skewed(rs2)
+for _ in range(5):
+    rs2()
+torch.cuda.synchronize()
+gang.barrier()
+ref2_last = (x2.float() * float(rcalls[0] % 3 + 1) @ w2.float().t() + b2.float() + res_full.float())[R * m_local:(R + 1) * m_local]
+st_loc = ops._stage[(m_local, n2)][0]
+fl_rs = ops._flags_for("rs", W * (m_local // 128) * ((n2 + 127) // 128))
+pf_rs = nat.make_peers(W, R, 0, [st_loc.peer_ptr(R)] * W, [fl_rs.peer_ptr(R)] * W)
+scratch_out = torch.empty_like(o_f)
+t_rs_local = timed(lambda: nat.igemm_reducescatter(x_ksh, w_ksh, pf_rs, scratch_out, m_local=m_local, ldc=n2, bias=b2,
+                                                   residual=res_loc))
+tf = timed(lambda: ops.gemm_reducescatter(x_ksh, w_ksh, scratch_out, bias=b2, residual=res_loc))
+part = torch.empty(W * m_local, n2, device=dev, dtype=torch.float16)
+t_gemm = timed(lambda: nat.linear(x_ksh, w_ksh, out=part))
+report("gemm_reducescatter", relerr(o_f, ref2_last), relerr(o_n, ref2), tf, tn,
+       dict(gflop=2.0 * W * m_local * ks * n2 / 1e9, link_mb=(W - 1) * m_local * n2 * 2 / 1e6, us_fused_gen1=tf1,
+            rel_err_gen1=err_v1, us_local_gemm_only=t_gemm, us_fused_local_only=t_rs_local))
 
 # ---------------------------------------------------------------- W9 attention with K/V gather (SDXL L1: S=4096, 10 heads, d=64)
 b_, h_, d_, s_tot = 2, 10, 64, 4096
@@ -161,9 +237,13 @@ ops.groupnorm_nccl(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=
 ref4 = F.silu(F.group_norm(xg.float().permute(0, 2, 1), g_, gam.float(), bet.float(), 1e-5)).permute(0, 2, 1)
 ref4 = ref4[:, R * hw_loc:(R + 1) * hw_loc]
 tf = timed(lambda: ops.groupnorm_fused(xg_loc, gam, bet, g_f, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True))
-tn = timed(lambda: ops.groupnorm_nccl(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True))
+tn_eager = timed(lambda: ops.groupnorm_nccl(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True))
+g_n.zero_()
+ops.groupnorm_nccl_native(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True)
+tn = timed(lambda: ops.groupnorm_nccl_native(xg_loc, gam, bet, g_n, n=n_, hw_local=hw_loc, groups=g_, eps=1e-5, silu=True))
 report("groupnorm_allreduce", (g_f.float() - ref4).abs().max().item(), (g_n.float() - ref4).abs().max().item(), tf, tn,
-       dict(mbytes=3 * xg_loc.numel() * 2 / 1e6, link_bytes=(W - 1) * n_ * g_ * 8))
+       dict(mbytes=3 * xg_loc.numel() * 2 / 1e6, link_bytes=(W - 1) * n_ * g_ * 8, us_nccl_eager_torch=tn_eager,
+            note="us_nccl = native partial-sum kernel + NCCL all-reduce + native apply kernel"))
 
 gang.barrier()
 if R == 0:

@@ -345,6 +345,24 @@ def test_flash_attn_over_frames(nat, f, hw, heads, d):
     assert _rel_err(out, ref) < 5e-3
 
 
+@pytest.mark.parametrize("fq,fkv,hw,heads,d", [(6, 24, 180, 8, 40), (3, 24, 37, 4, 80), (12, 24, 64, 8, 64)])
+def test_flash_attn_frames_local_queries(nat, fq, fkv, hw, heads, d):
+    """Frame-split clip: queries are this rank's frames, keys / values all frames (packed block-diagonal tiles with
+    seq_q != seq_kv)."""
+    torch.manual_seed(9)
+    c = heads * d
+    q = torch.randn(fq, hw, heads, d, device="cuda", dtype=torch.float16)
+    kv = torch.randn(fkv, hw, 2, heads, d, device="cuda", dtype=torch.float16)
+    out = torch.zeros(fq, hw, c, device="cuda", dtype=torch.float16)
+    kv5 = kv.permute(1, 0, 2, 3, 4)
+    nat.flash_attn(q.permute(1, 0, 2, 3), kv5[:, :, 0], kv5[:, :, 1], out.permute(1, 0, 2), batch=hw, heads=heads,
+                   seq_q=fq, seq_kv=fkv, head_dim=d)
+    qq = q.float().permute(1, 2, 0, 3)                     # [hw, heads, fq, d]
+    kk, vv = (kv5[:, :, i].float().permute(0, 2, 1, 3) for i in range(2))
+    ref = F.scaled_dot_product_attention(qq, kk, vv).permute(2, 0, 1, 3).reshape(fq, hw, c)
+    assert _rel_err(out, ref) < 5e-3
+
+
 @pytest.mark.parametrize("rows,c,nout,geglu", [(512, 1280, 3840, False), (2048, 640, 640, False), (8192, 320, 2560, True),
                                                (300, 320, 960, False), (1024, 1280, 10240, True)])
 def test_layernorm_folded_into_gemm(nat, rows, c, nout, geglu):
