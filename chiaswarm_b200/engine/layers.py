@@ -21,7 +21,7 @@ import torch
 
 from ..ops import native as nat
 from ..ops import tuning
-from ..ops.packing import fold_layernorm, interleave_geglu, pack_conv_weight, pad_vector
+from ..ops.packing import fold_layernorm, fold_upsample2x, interleave_geglu, pack_conv_weight, pad_vector
 
 
 def _r8(c: int) -> int:
@@ -118,7 +118,7 @@ class Recorder:
 
 # ------------------------------------------------------------------------------------------ layers
 class Conv:
-    """3x3 / 1x1 stride-1 conv (implicit GEMM) or stride-2 conv (im2col + GEMM)."""
+    """3x3 / 1x1 conv as implicit GEMM, stride 1 or 2 (no im2col, no materialised padding)."""
 
     def __init__(self, conv: torch.nn.Conv2d, cin_pad: Optional[int] = None, asym_pad: bool = False):
         w = conv.weight.detach().to(torch.float16)
@@ -146,33 +146,27 @@ class Conv:
                     splitk_scratch=rec.splitk, **halo)
             return o
         assert x2 is None and self.stride == 2
-        if halo:  # stride 2 over the halo-padded strip: the top halo row is the padding row
+        # stride 2 as implicit GEMM: the TMA box skips every other pixel (sw_igemm `stride`), no im2col buffer.
+        # UNet downsamplers pad 1 symmetrically; the VAE encoder pads (0,1,0,1) = no leading pad, and the trailing
+        # pad row / column is the TMA unit's out-of-bounds zero fill either way.
+        if halo:  # over the halo-padded strip: its top halo row is input row -1
             assert halo["a_y_off"] == 1 and x.h % 2 == 0
-            oh, ow = x.h // 2, (x.w + 2 * self.pad - self.k) // 2 + 1
-            cols = rec.buf(x.n, oh, ow, self.k * self.k * x.c)
-            rec.add(nat.im2col, a, cols, n=x.n, h=x.h + 2, w=x.w, kh=self.k, kw=self.k, stride=2, pad_top=0,
-                    pad_left=self.pad, oh=oh, ow=ow)
-            o = out or rec.fm(x.n, oh, ow, self.cout)
-            rec.add(nat.igemm, cols.view(-1, cols.shape[-1]), self.wgt, o.t.view(-1, o.c), n=1, h=1, w=x.n * oh * ow,
-                    bias=self.bias, residual=None if residual is None else residual.tokens(), act=act,
-                    out_scale=out_scale, splitk_scratch=rec.splitk)
-            rec.release(cols)
-            return o
-        if self.asym:  # VAE encoder: pad (0,1,0,1) then valid conv
-            oh, ow = (x.h + 1 - self.k) // 2 + 1, (x.w + 1 - self.k) // 2 + 1
-            pt = pl = 0
+        if self.asym:
+            oh, ow, pad = (x.h + 1 - self.k) // 2 + 1, (x.w + 1 - self.k) // 2 + 1, 0
         else:
-            oh, ow = (x.h + 2 * self.pad - self.k) // 2 + 1, (x.w + 2 * self.pad - self.k) // 2 + 1
-            pt = pl = self.pad
-        cols = rec.buf(x.n, oh, ow, self.k * self.k * x.c)
-        rec.add(nat.im2col, x.t, cols, n=x.n, h=x.h, w=x.w, kh=self.k, kw=self.k, stride=2, pad_top=pt, pad_left=pl,
-                oh=oh, ow=ow)
+            oh, ow, pad = (x.h + 2 * self.pad - self.k) // 2 + 1, (x.w + 2 * self.pad - self.k) // 2 + 1, self.pad
         o = out or rec.fm(x.n, oh, ow, self.cout)
-        rec.add(nat.igemm, cols.view(-1, cols.shape[-1]), self.wgt, o.t.view(-1, o.c), n=1, h=1, w=x.n * oh * ow,
-                bias=self.bias, row_bias=None, residual=None if residual is None else residual.tokens(), act=act,
-                out_scale=out_scale, splitk_scratch=rec.splitk)
-        rec.release(cols)
+        rec.add(nat.igemm, a, self.wgt, o.t.view(-1, o.c), n=x.n, h=oh, w=ow, kh=self.k, kw=self.k, pad=pad, stride=2,
+                in_h=x.h, in_w=x.w, bias=self.bias, residual=None if residual is None else residual.tokens(), act=act,
+                out_scale=out_scale, splitk_scratch=rec.splitk, **halo)
         return o
+
+
+def patch_attention_mode() -> str:
+    """How a row-split plan runs self-attention: "kv" = K/V of the other strips read inside the attention kernel
+    (sw_flash_attn_gather, sequence parallel), "tp" = head parallel through the two fused GEMM collectives
+    (TransformerBlock._self_attention_tp) where the shapes allow.  SW_PATCH_ATTN selects; default "kv"."""
+    return os.environ.get("SW_PATCH_ATTN", "kv").lower()
 
 
 STATS_TILE = 128  # column tile of GEMMs that emit row statistics (fixes the number of partial slots)
@@ -308,8 +302,8 @@ class LayerNorm:
         self.gamma = ln.weight.detach().to(torch.float16).contiguous()
         self.beta = ln.bias.detach().to(torch.float16).contiguous()
 
-    def __call__(self, rec: Recorder, x: torch.Tensor) -> torch.Tensor:
-        o = rec.buf(*x.shape)
+    def __call__(self, rec: Recorder, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        o = out if out is not None else rec.buf(*x.shape)
         rec.add(nat.layernorm, x, self.gamma, self.beta, o, self.eps)
         return o
 
@@ -378,6 +372,7 @@ class TransformerBlock:
         self.c = c
         a1, a2 = m.attn1, m.attn2
         self.self_is_cross = m.only_cross_attention
+        self._tp = {}
         self.can_fuse = fuse_layernorm(c) and not self.self_is_cross
         self.ln1, self.ln2, self.ln3 = LayerNorm(m.norm1), LayerNorm(m.norm2), LayerNorm(m.norm3)
         if not self.self_is_cross:
@@ -396,6 +391,53 @@ class TransformerBlock:
         self.o2 = Linear(a2.to_out[0].weight, a2.to_out[0].bias)
         self.ff1 = Linear(m.ff.net[0].proj.weight, m.ff.net[0].proj.bias, geglu=True)
         self.ff2 = Linear(m.ff.net[2].weight, m.ff.net[2].bias)
+
+    # ---- head-parallel (tensor-parallel) self-attention for row-split plans: the north star's "all-gather fused into
+    # the QKV GEMM, out-projection GEMM fused with its reduce-scatter"  inside a model
+    def tp_eligible(self, rec: Recorder, s: int) -> bool:
+        ctx = rec.patch
+        return (ctx is not None and ctx.rows and ctx.P > 1 and not self.self_is_cross and patch_attention_mode() == "tp"
+                and self.heads % ctx.P == 0 and s % 128 == 0 and self.dh <= 128)
+
+    def _tp_weights(self, P: int, p: int):
+        key = (P, p)
+        tw = self._tp.get(key)
+        if tw is None:
+            hp, c = self.heads // P, self.c
+            lo, hi = p * hp * self.dh, (p + 1) * hp * self.dh
+            w = self.qkv.wgt  # [3c, c]: q rows, k rows, v rows
+            wqkv = torch.cat([w[lo:hi], w[c + lo:c + hi], w[2 * c + lo:2 * c + hi]], 0).contiguous()
+            wo = self.o1.wgt[:, lo:hi].contiguous()  # this rank's K shard of the output projection
+            tw = self._tp[key] = (wqkv, wo)
+        return tw
+
+    def _self_attention_tp(self, rec: Recorder, y: torch.Tensor, s: int) -> torch.Tensor:
+        """y: this strip's rows [s, c] of the residual stream (not released here).  Returns y + out_proj(attention):
+          LayerNorm(y) is written straight into this rank's rows of a peer-visible gathered buffer;
+          sw_igemm_allgather pushes those rows to the group and computes Q/K/V of THIS rank's heads for ALL rows;
+          flash attention runs locally (heads / P heads, the whole sequence);
+          sw_igemm_reducescatter multiplies by this rank's K shard of W_o, pushes partial tiles to the rows' owners
+          and reduces its own rows (+ bias + residual) -- no K/V gather, no separate collective."""
+        ctx = rec.patch
+        P, p, c = ctx.P, ctx.p, self.c
+        hp = self.heads // P
+        wqkv, wo = self._tp_weights(P, p)
+        gathered = ctx.sym_buf(P * s, c)
+        self.ln1(rec, y, out=gathered.local[p * s:(p + 1) * s])
+        qkv = rec.buf(P * s, 3 * hp * self.dh)
+        rec.add(nat.igemm_allgather, wqkv, qkv, ctx.tile_peers(gathered, P * (s // 128)), m_local=s, k=c, a_ld=c)
+        v5 = qkv.view(1, P * s, 3, hp, self.dh)
+        attn = rec.buf(P * s, hp * self.dh)
+        rec.add(nat.flash_attn, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn.view(1, P * s, hp * self.dh), batch=1, heads=hp,
+                seq_q=P * s, seq_kv=P * s, head_dim=self.dh)
+        rec.release(qkv)
+        staging = ctx.sym_buf(P * s, c)  # [P][s][c]: slot [src] holds rank src's partial of this rank's rows
+        ntile = (c + 127) // 128
+        y1 = rec.buf(s, c)
+        rec.add(nat.igemm_reducescatter, attn, wo, ctx.tile_peers(staging, P * (s // 128) * ntile), y1, m_local=s, ldc=c,
+                bias=self.o1.bias, residual=y)
+        rec.release(attn)
+        return y1
 
     def use_fused(self, rows: int) -> bool:
         """Fold the LayerNorms for this call?  Big token counts keep the separate kernel: their GEMMs want CTA
@@ -472,6 +514,20 @@ class TransformerBlock:
             rec.release(ff)
             rec.release(y2)
             return y3
+        if n == 1 and self.tp_eligible(rec, s):
+            y1 = self._self_attention_tp(rec, y, s)
+            rec.release(y)
+            x2 = self.ln2(rec, y1)
+            y2 = self._cross(rec, self.q2(rec, x2), self.kv2, n, s, self.o2, y1, False)
+            rec.release(x2)
+            rec.release(y1)
+            x3 = self.ln3(rec, y2)
+            ff = self.ff1(rec, x3)
+            rec.release(x3)
+            y3 = self.ff2(rec, ff, residual=y2)
+            rec.release(ff)
+            rec.release(y2)
+            return y3
         x1 = self.ln1(rec, y)
         if not self.self_is_cross:
             attn = self._self_attention(rec, x1, None, n, s)
@@ -531,12 +587,27 @@ class Transformer2D:
 
 
 class Upsample:
+    """Nearest 2x + conv3x3, folded: four 2x2 convs on the small map write the four output phases directly
+    (ops/packing.fold_upsample2x) -- no upsampled buffer, 2.25x fewer multiply-adds."""
+
     def __init__(self, m):
         self.conv = Conv(m.conv)
+        w = m.conv.weight.detach().to(torch.float16)
+        self.phases = fold_upsample2x(w, self.conv.cin, self.conv.cout)
+        # all four phases in one launch (grid z = phase) when the kernel's phase mode applies
+        self.stacked = torch.cat([self.phases[(a, b)] for a in (0, 1) for b in (0, 1)], 0).contiguous() \
+            if self.conv.cout % 64 == 0 else None
 
     def __call__(self, rec: Recorder, x: FM) -> FM:
-        up = rec.fm(x.n, 2 * x.h, 2 * x.w, x.c)
-        rec.add(nat.upsample2x, x.t, up.t, n=x.n, h=x.h, w=x.w)
-        o = self.conv(rec, up)
-        rec.release(up)
+        a, halo = x.t, {}
+        if rec.patch is not None and rec.patch.rows:  # rows y-1 / y+1 of a strip's edge live on the neighbours
+            a, halo = rec.patch.conv_input(rec, x)
+        o = rec.fm(x.n, 2 * x.h, 2 * x.w, self.conv.cout)
+        if self.stacked is not None:
+            rec.add(nat.igemm, a, self.stacked, o.t, n=x.n, h=x.h, w=x.w, kh=2, kw=2, pad=1, bias=self.conv.bias,
+                    out_sx=2, out_sy=2, out_phases=1, ldc=o.c, **halo)
+            return o
+        for (pa, pb), wgt in self.phases.items():
+            rec.add(nat.igemm, a, wgt, o.t[:, pa::2, pb::2, :], n=x.n, h=x.h, w=x.w, kh=2, kw=2, pad=1 - pa, pad_w=1 - pb,
+                    bias=self.conv.bias, out_sx=2, out_sy=2, ldc=o.c, **halo)
         return o

@@ -62,6 +62,7 @@ class PatchContext:
         self.tick = torch.zeros(1, dtype=torch.int32, device=gang.device)
         self._channels: Dict[str, _Channel] = {}
         self._gn_stats: Dict[int, SymTensor] = {}
+        self._tile_syncs = 0
 
     # ---- addressing
     def global_rank(self, d: int) -> int:
@@ -89,6 +90,9 @@ class PatchContext:
         for ch in self._channels.values():
             for ps in ch.structs:
                 ps.epoch_mul = len(ch.structs)
+        if self._tile_syncs:  # freshly zeroed per-tile flag arrays: nobody may push into one that is not cleared yet
+            torch.cuda.synchronize()
+            self.gang.barrier()
 
     # ---- buffers
     def sym_buf(self, rows: int, c: int) -> SymTensor:
@@ -120,6 +124,17 @@ class PatchContext:
         if st is None:
             st = self._gn_stats[groups] = self.arena.alloc(2 * self.P * groups * 2, dtype=torch.float32)
         return self._peers("gn", [st.peer_ptr(self.global_rank(d)) for d in range(self.P)])
+
+    def tile_peers(self, buf: SymTensor, flag_count: int) -> nat.Peers:
+        """Peers of one fused GEMM collective (sw_igemm_allgather / sw_igemm_reducescatter): `buf` on every rank of
+        the strip group plus a per-tile flag array of its own, epoch = step counter + 1 (one use per step)."""
+        flags = self.arena.alloc(flag_count, dtype=torch.int32)
+        flags.local.zero_()  # (an evicted plan may have left large epochs here; finalize() barriers before any use)
+        ranks = [self.global_rank(d) for d in range(self.P)]
+        ps = nat.make_peers(self.P, self.p, 1, [buf.peer_ptr(r) for r in ranks], [flags.peer_ptr(r) for r in ranks],
+                            epoch_base=self.tick, epoch_mul=1)
+        self._tile_syncs += 1
+        return ps
 
     def kv_peers(self, qkv: SymTensor, c: int):
         ranks = [self.global_rank(d) for d in range(self.P)]

@@ -65,6 +65,8 @@ class IGemmParams(C.Structure):
         ("cluster_k", C.c_int32),
         ("persist", C.c_int32),
         ("w_kmajor", C.c_int32),
+        ("stride", C.c_int32), ("in_h", C.c_int32), ("in_w", C.c_int32),
+        ("out_sx", C.c_int32), ("out_sy", C.c_int32), ("out_phases", C.c_int32),
     ]
 
 
@@ -219,7 +221,7 @@ def _f16(t: torch.Tensor, name: str) -> torch.Tensor:
 def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_bias=None,
           residual=None, act=ACT_NONE, out_scale=1.0, tile_n=0, splitk_scratch=None, cta_pair=0, splitk_min_kb=0, stages=0, pad_w=None,
           a_h_total=0, a_y_off=0, persist=0, row_stats_out=None, row_stats_in=None, col_sums=None, stats_tiles=0,
-          ln_width=0, ln_eps=0.0, cluster_k=0):
+          ln_width=0, ln_eps=0.0, cluster_k=0, stride=1, in_h=0, in_w=0, out_sx=1, out_sy=1, ldc=None, out_phases=0):
     """Implicit-GEMM conv / linear (see sw_igemm in swarm_b200.h). `a1`/`a2` are channels-last
     [n,h,w,c] (any view with that memory layout), `wgt` is [cout, kh*kw*(c1+c2)]."""
     for t, nm in ((a1, "a1"), (wgt, "wgt"), (out, "out")):
@@ -233,16 +235,16 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
         assert wgt.is_contiguous() and wgt.shape[2] == 64
         assert wgt.shape[0] == kh * kw * ((c1 + 63) // 64 + (c2 + 63) // 64), (wgt.shape, kh, kw, c1, c2)
     else:
-        cout = wgt.shape[0]
+        cout = wgt.shape[0] // (4 if out_phases else 1)
         assert wgt.shape[1] == kh * kw * (c1 + c2), (wgt.shape, kh, kw, c1, c2)
-    assert a1.numel() == n * (a_h_total or h) * w * c1
+    assert a1.numel() == n * (a_h_total or in_h or h) * (in_w or w) * c1
     # strided 2-D views (a column block of a wider matrix) are passed through leading dimensions
     a_ld = 0 if a1.is_contiguous() else a1.stride(-2)
     w_ld = 0 if (kmajor or wgt.is_contiguous()) else wgt.stride(0)
     if a_ld and (a1.dim() != 2 or kh != 1 or a2 is not None):
         raise ValueError("strided a1 is only supported for plain GEMMs")
     if (tile_n == 0 and cta_pair == 0 and splitk_min_kb == 0 and stages == 0 and persist == 0 and cluster_k == 0
-            and row_stats_out is None and row_stats_in is None):
+            and row_stats_out is None and row_stats_in is None and stride == 1 and out_sx == 1 and out_sy == 1):
         tuned = tuning.lookup(n, h, w, kh, kw, c1, c2, cout, act, residual is not None)
         if tuned is not None:
             tile_n, cta_pair, splitk_min_kb, persist, cluster_k = tuned
@@ -259,7 +261,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.residual = _ptr(residual)
     p.ldr = 0 if residual is None else residual.stride(-2)
     p.out = _ptr(out)
-    p.ldc = out.stride(-2) if out.dim() > 1 else out.shape[-1]
+    p.ldc = ldc if ldc is not None else (out.stride(-2) if out.dim() > 1 else out.shape[-1])
     p.act = act
     p.out_scale = out_scale
     p.bf16 = 0
@@ -276,6 +278,7 @@ def igemm(a1, wgt, out, *, n, h, w, kh=1, kw=1, pad=0, a2=None, bias=None, row_b
     p.persist = persist
     p.cluster_k = cluster_k
     p.w_kmajor = 1 if kmajor else 0
+    p.stride, p.in_h, p.in_w, p.out_sx, p.out_sy, p.out_phases = stride, in_h, in_w, out_sx, out_sy, out_phases
     p.row_stats_out, p.row_stats_in, p.col_sums = _ptr(row_stats_out), _ptr(row_stats_in), _ptr(col_sums)
     p.stats_tiles, p.ln_width, p.ln_eps = stats_tiles, ln_width, ln_eps
     if splitk_scratch is not None:

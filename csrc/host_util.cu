@@ -44,8 +44,21 @@ int encode_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t
     return encode_tmap_f16_ex(out, base, rank, dims, strides_bytes, box, true);
 }
 
+static int encode_impl(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                       const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128, const uint32_t* elem_strides);
+
 int encode_tmap_f16_ex(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                        const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
+    return encode_impl(out, base, rank, dims, strides_bytes, box, swizzle128, nullptr);
+}
+
+int encode_tmap_f16_strided(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                            const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides) {
+    return encode_impl(out, base, rank, dims, strides_bytes, box, true, elem_strides);
+}
+
+static int encode_impl(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                       const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128, const uint32_t* elem_strides) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return fail(-2, "cuTensorMapEncodeTiled entry point unavailable");
     cuuint64_t gd[5];
@@ -55,7 +68,7 @@ int encode_tmap_f16_ex(CUtensorMap* out, const void* base, int rank, const uint6
     for (int i = 0; i < rank; ++i) {
         gd[i] = dims[i];
         bx[i] = box[i];
-        es[i] = 1;
+        es[i] = elem_strides ? elem_strides[i] : 1;
         if (i + 1 < rank) gs[i] = strides_bytes[i];
     }
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0)

@@ -24,6 +24,10 @@ int fail(int code, const char* fmt, ...);
 int encode_tmap_f16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box);
 // Same, with an explicit swizzle choice (false = CU_TENSOR_MAP_SWIZZLE_NONE: rows of the box are dense).
+// `elem_strides` (may be NULL = all 1): traversal stride per dimension; a box of `box[i]` traversed elements then
+// delivers ceil(box[i] / elem_strides[i]) elements (stride-2 convolutions read every other pixel this way).
+int encode_tmap_f16_strided(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                            const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides);
 int encode_tmap_f16_ex(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128);
 

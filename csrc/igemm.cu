@@ -30,6 +30,8 @@ struct IGemmArgs {
     int c1, c2;
     int n, h, w;
     int kh, kw, pad, pad_w, pad_y1;
+    int sx;  // convolution stride (1 or 2): tile origin in input pixels = output origin * sx
+    int phases;  // lean kernel: blockIdx.z = output phase (a, b) of a folded nearest-2x upsample + conv3x3
     int cout;
     int bw, bh, bi;  // tile box: bw*bh*bi <= 128 pixels
     int tiles_x, tiles_y;
@@ -327,6 +329,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
     const int ty = t % p.tiles_y;
     const int tn = t / p.tiles_y;
     const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+    const int xs0 = x0 * p.sx, ys0 = y0 * p.sx;  // tile origin in input pixels
     const int col0 = blockIdx.y * BN;
     const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
     // mode 1 (all-gather fused): this tile's rows live on rank `ag_src`; they are fetched straight
@@ -406,10 +409,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
                     // both CTAs' loads complete on the leader's barrier; only the leader arms it
                     if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                     if (j < nkb1) {
-                        tma4<PAIR>(sa, pA1, fb, j * BK, ax0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                        tma4<PAIR>(sa, pA1, fb, j * BK, ax0 * p.sx + kx - p.pad_w, y0 * p.sx + ky - p.pad_y1, n0);
                         tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
                     } else {
-                        tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                        tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, xs0 + kx - p.pad_w, ys0 + ky - p.pad, n0);
                         tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                     }
                 }
@@ -1286,8 +1289,17 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
     const int ty = t % p.tiles_y;
     const int tn = t / p.tiles_y;
     const int x0 = tx * p.bw, y0 = ty * p.bh, n0 = tn * p.bi;
+    const int xs0 = x0 * p.sx, ys0 = y0 * p.sx;  // tile origin in input pixels
     const int col0 = ctile_f * BN;
     const int bcol0 = col0 + (PAIR ? int(cta_rank) * (BN / 2) : 0);
+    // folded upsample (p.phases): the four output phases (a, b) of out[2y+a, 2x+b] are the z slices of ONE grid; a
+    // phase has its own taps (rows a-1.., columns b-1..), its own block of weight rows and its own output map
+    // (the kernel arguments tmOut, tmRes, tmOut32, tmA2 carry the maps of phases 0..3: none of them has its usual
+    // role in a bias-only, single-input, cout % 64 == 0 convolution)
+    const int phase = (MODE == 0 && p.phases) ? int(blockIdx.z) : 0;
+    const int pad_yp = p.pad_y1 - (phase >> 1), pad_xp = p.pad_w - (phase & 1);
+    const int brow0 = bcol0 + phase * p.cout;
+    const CUtensorMap* const out_map = phase == 0 ? &tmOut : phase == 1 ? &tmRes : phase == 2 ? &tmOut32 : &tmA2;
     const int peer_of_tile = MODE != 0 ? x0 / p.m_local : 0;                 // who produced (1) / owns (2) these rows
     const int tile_in_shard = MODE != 0 ? (x0 - peer_of_tile * p.m_local) / BM : 0;
     const int nkb1 = (p.c1 + BK - 1) / BK;
@@ -1334,10 +1346,10 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
             if (elect_one()) {
                 if (!PAIR || leader) bar_expect_tx(fb, tx_bytes);
                 if (j < nkb1) {
-                    tma4<PAIR>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
-                    tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
+                    tma4<PAIR>(sa, &tmA1, fb, j * BK, xs0 + kx - pad_xp, ys0 + ky - pad_yp, n0);
+                    tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, brow0);
                 } else {
-                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                    tma4<PAIR>(sa, &tmA2, fb, (j - nkb1) * BK, xs0 + kx - p.pad_w, ys0 + ky - p.pad, n0);
                     tma_b<PAIR>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                 }
             }
@@ -1498,6 +1510,8 @@ __device__ __forceinline__ void igemm_lean_body(const CUtensorMap& tmA1, const C
             if (lead) {
                 if (MODE == 2)  // the owner's staging slot for this rank (peer memory), rows relative to its shard
                     tma_store_4d(&pm->m[peer_of_tile], out_stage + box, col0 + c0, x0 - peer_of_tile * p.m_local, 0, 0);
+                else if (MODE == 0 && p.phases)
+                    tma_store_4d(out_map, out_stage + box, col0 + c0, x0, y0, n0);
                 else
                     tma_store_4d(tail_slab ? &tmOut32 : &tmOut, out_stage + box, col0 + c0, x0, y0, n0);
                 bulk_commit();
@@ -1693,10 +1707,10 @@ __global__ void __launch_bounds__(kThreads)
                     if (elect_one()) {
                         bar_expect_tx(fb, tx_bytes);
                         if (j < nkb1) {
-                            tma4<false>(sa, &tmA1, fb, j * BK, x0 + kx - p.pad_w, y0 + ky - p.pad_y1, n0);
+                            tma4<false>(sa, &tmA1, fb, j * BK, x0 * p.sx + kx - p.pad_w, y0 * p.sx + ky - p.pad_y1, n0);
                             tma_b<false>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + j * BK, it, bcol0);
                         } else {
-                            tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 + kx - p.pad_w, y0 + ky - p.pad, n0);
+                            tma4<false>(sa, &tmA2, fb, (j - nkb1) * BK, x0 * p.sx + kx - p.pad_w, y0 * p.sx + ky - p.pad, n0);
                             tma_b<false>(sa + A_STAGE_BYTES, &tmB, fb, p.w_kmajor, tapbase + p.c1 + (j - nkb1) * BK, it, bcol0);
                         }
                     }
@@ -2188,7 +2202,8 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     if (p->cout <= 0 || p->cout % 8) return swh::fail(-1, "sw_igemm: cout=%d not a multiple of 8", p->cout);
     if (p->n <= 0 || p->h <= 0 || p->w <= 0 || p->kh <= 0 || p->kw <= 0)
         return swh::fail(-1, "sw_igemm: bad shape");
-    if (p->a_h_total < 0 || (p->a_h_total > 0 && (mode != 0 || p->a_y_off < 0 || p->a_y_off + p->h > p->a_h_total)))
+    if (p->a_h_total < 0 || (p->a_h_total > 0 && (mode != 0 || p->a_y_off < 0 ||
+                                                  p->a_y_off + (p->in_h > 0 ? p->in_h : p->h) > p->a_h_total)))
         return swh::fail(-1, "sw_igemm: a_h_total=%d / a_y_off=%d do not contain the %d output rows", p->a_h_total,
                          p->a_y_off, p->h);
     const bool ln_fused = p->row_stats_out != nullptr || p->row_stats_in != nullptr;
@@ -2206,8 +2221,25 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     if (p->ldc % 8 || (p->residual && p->ldr % 8) || (p->row_bias && p->row_bias_ld % 8))
         return swh::fail(-1, "sw_igemm: leading dimensions must be multiples of 8");
 
+    const int cstride = p->stride > 1 ? p->stride : 1;
+    const int in_h = p->in_h > 0 ? p->in_h : p->h, in_w = p->in_w > 0 ? p->in_w : p->w;
+    const int osx = p->out_sx > 1 ? p->out_sx : 1, osy = p->out_sy > 1 ? p->out_sy : 1;
+    const bool out_strided = osx > 1 || osy > 1;
+    if (cstride > 2 || (cstride == 1 && (in_h != p->h || in_w != p->w) && p->a_h_total == 0))
+        return swh::fail(-1, "sw_igemm: stride must be 1 or 2 (in_h / in_w only with stride 2)");
+    if ((cstride > 1 || out_strided) && (mode != 0 || ln_fused || p->a_ld))
+        return swh::fail(-1, "sw_igemm: strided convolutions / strided outputs are plain local convolutions");
+    if (out_strided && (p->residual || p->act == SW_ACT_GEGLU))
+        return swh::fail(-1, "sw_igemm: a strided output takes no residual and no GEGLU");
+    const bool phases = p->out_phases != 0;
+    if (phases && (p->kh != 2 || p->kw != 2 || p->pad != 1 || p->pad_w1 != 0 || osx != 2 || osy != 2 || p->c2 != 0 ||
+                   p->cout % 64 || p->act != SW_ACT_NONE || p->row_bias || cstride != 1 || p->w_kmajor || p->w_ld ||
+                   (p->out_scale != 0.0f && p->out_scale != 1.0f)))
+        return swh::fail(-1, "sw_igemm: out_phases is the folded 2x upsample: 2x2 taps, pad 1, out strides 2, bias only, cout %% 64 == 0");
     IGemmArgs a;
     memset(&a, 0, sizeof(a));
+    a.sx = cstride;
+    a.phases = phases ? 1 : 0;
     a.c1 = p->c1;
     a.c2 = p->c2;
     a.n = p->n;
@@ -2271,7 +2303,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         // percent of the best everywhere except (a) layers big enough to fill the chip several times over
         // with 128-wide tiles, which want the widest tile (least operand re-fetch per flop), and (b) grids
         // so small that even split-K cannot spread them, which want many narrow tiles
-        const long ctas128 = long(grid_x) * ((p->cout + 127) / 128);
+        const long ctas128 = long(grid_x) * ((p->cout + 127) / 128) * (p->out_phases ? 4 : 1);
         if (2 * ctas128 >= 5L * sms) {
             const int ntiles = (p->cout + 255) / 256;
             bn = ((p->cout + ntiles - 1) / ntiles + 31) / 32 * 32;
@@ -2325,7 +2357,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
     // CTAs share each tile's K range (deterministic reduction by the last arrival).
     a.splits = 1;
     a.kb_per_split = kblocks;
-    const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol;
+    const long ctas = long(pair ? (grid_x + 1) / 2 * 2 : grid_x) * tiles_ncol * (phases ? 4 : 1);
     // ---- split-K over a cluster of two (DSMEM exchange, see the epilogue): small GEMMs whose tiles do not fill
     // the chip, so that every SM streams half of its activation slab
     {
@@ -2334,7 +2366,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             const char* e = getenv("SW_IGEMM_CLUSTERK");
             env_ck = e ? atoi(e) : 1;
         }
-        const bool eligible = mode == 0 && !pair && !ln_fused && p->act != SW_ACT_GEGLU && bn % 64 == 0 && kblocks >= 4 &&
+        const bool eligible = mode == 0 && !pair && !ln_fused && !out_strided && p->act != SW_ACT_GEGLU && bn % 64 == 0 && kblocks >= 4 &&
                               2 * ctas <= 2L * sms;
         const bool want = env_ck == 2 || (env_ck == 1 && p->cluster_k == 2);
         if (eligible && want && p->cluster_k != 1) {
@@ -2346,7 +2378,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         }
     }
     const int min_kb = p->splitk_min_kb > 0 ? p->splitk_min_kb : 16;
-    if (mode == 0 && !a.cluster_k && !ln_fused && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
+    if (mode == 0 && !a.cluster_k && !ln_fused && !out_strided && p->splitk_scratch && p->act != SW_ACT_GEGLU && 2 * ctas <= 3L * sms / 2 && kblocks >= 2 * min_kb &&
         ctas <= kMaxSplitTiles) {
         const int slots = (2 * (stages * stage_bytes + 2048) <= 226 * 1024) ? 2 * sms : sms;
         int want = int(slots / ctas);
@@ -2381,19 +2413,22 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         tA1 = ag.m[0];
     } else {
         const uint64_t lda = p->a_ld > 0 ? uint64_t(p->a_ld) : uint64_t(p->c1);
-        const uint64_t ah = p->a_h_total > 0 ? uint64_t(p->a_h_total) : uint64_t(p->h);
-        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(p->w), ah, uint64_t(p->n)};
-        const uint64_t str[3] = {lda * 2, uint64_t(p->w) * lda * 2, ah * p->w * lda * 2};
-        const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
-        int rc = swh::encode_tmap_f16(&tA1, p->a1, 4, dims, str, box);
+        const uint64_t ah = p->a_h_total > 0 ? uint64_t(p->a_h_total) : uint64_t(in_h);
+        const uint64_t dims[4] = {uint64_t(p->c1), uint64_t(in_w), ah, uint64_t(p->n)};
+        const uint64_t str[3] = {lda * 2, uint64_t(in_w) * lda * 2, ah * in_w * lda * 2};
+        // stride 2: the box spans 2x the pixels and the TMA unit keeps every other one
+        const uint32_t box[4] = {64, uint32_t(a.bw * cstride), uint32_t(a.bh * cstride), uint32_t(a.bi)};
+        const uint32_t es[4] = {1, uint32_t(cstride), uint32_t(cstride), 1};
+        int rc = swh::encode_tmap_f16_strided(&tA1, p->a1, 4, dims, str, box, es);
         if (rc) return rc;
     }
     if (p->c2 > 0) {
-        const uint64_t dims[4] = {uint64_t(p->c2), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
-        const uint64_t str[3] = {uint64_t(p->c2) * 2, uint64_t(p->w) * p->c2 * 2,
-                                 uint64_t(p->h) * p->w * p->c2 * 2};
-        const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
-        int rc = swh::encode_tmap_f16(&tA2, p->a2, 4, dims, str, box);
+        const uint64_t dims[4] = {uint64_t(p->c2), uint64_t(in_w), uint64_t(in_h), uint64_t(p->n)};
+        const uint64_t str[3] = {uint64_t(p->c2) * 2, uint64_t(in_w) * p->c2 * 2,
+                                 uint64_t(in_h) * in_w * p->c2 * 2};
+        const uint32_t box[4] = {64, uint32_t(a.bw * cstride), uint32_t(a.bh * cstride), uint32_t(a.bi)};
+        const uint32_t es[4] = {1, uint32_t(cstride), uint32_t(cstride), 1};
+        int rc = swh::encode_tmap_f16_strided(&tA2, p->a2, 4, dims, str, box, es);
         if (rc) return rc;
     } else {
         tA2 = tA1;
@@ -2407,7 +2442,7 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 3, dims, str, box);
         if (rc) return rc;
     } else {
-        const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout)};
+        const uint64_t dims[2] = {uint64_t(ktotal), uint64_t(p->cout) * (phases ? 4 : 1)};
         const uint64_t str[1] = {(p->w_ld > 0 ? uint64_t(p->w_ld) : uint64_t(ktotal)) * 2};
         const uint32_t box[2] = {64, uint32_t(pair ? bn / 2 : bn)};
         int rc = swh::encode_tmap_f16(&tB, p->wgt, 2, dims, str, box);
@@ -2424,12 +2459,15 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             const char* e = getenv("SW_IGEMM_TMA_EPI");
             env_epi = e ? atoi(e) : 1;
         }
-        if (!env_epi && !ln_fused) a.tma_epi = 0;
+        if (!env_epi && !ln_fused && !out_strided) a.tma_epi = 0;
     }
+    if (out_strided && !a.tma_epi) return swh::fail(-1, "sw_igemm: a strided output needs the TMA-store epilogue");
     if (a.tma_epi) {
         const uint64_t nc = p->act == SW_ACT_GEGLU ? uint64_t(p->cout / 2) : uint64_t(p->cout);
         const uint64_t dims[4] = {nc, uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
-        const uint64_t so[3] = {uint64_t(p->ldc) * 2, uint64_t(p->w) * p->ldc * 2, uint64_t(p->h) * p->w * p->ldc * 2};
+        // (strided output: pixel (y, x) lands in row y*osy, column x*osx of a [h*osy, w*osx] image)
+        const uint64_t so[3] = {uint64_t(p->ldc) * 2 * osx, uint64_t(p->w) * osx * p->ldc * 2 * osy,
+                                uint64_t(p->h) * osy * p->w * osx * p->ldc * 2};
         const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
         const uint32_t box32[4] = {32, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
         int rc = swh::encode_tmap_f16(&tOut, p->out, 4, dims, so, box);
@@ -2445,6 +2483,18 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         }
     } else {
         tOut = tRes = tOut32 = tB;
+    }
+    if (phases) {
+        // the maps of phases 1..3 ride in the slots of tmRes, tmOut32 and tmA2 (unused by such a convolution)
+        if (!a.tma_epi) return swh::fail(-1, "sw_igemm: out_phases needs the TMA-store epilogue");
+        CUtensorMap* slot[4] = {&tOut, &tRes, &tOut32, &tA2};
+        const uint64_t dims[4] = {uint64_t(p->cout), uint64_t(p->w), uint64_t(p->h), uint64_t(p->n)};
+        const uint64_t so[3] = {uint64_t(p->ldc) * 4, uint64_t(p->w) * p->ldc * 8, uint64_t(p->h) * p->w * p->ldc * 8};
+        const uint32_t box[4] = {64, uint32_t(a.bw), uint32_t(a.bh), uint32_t(a.bi)};
+        for (int ph = 0; ph < 4; ++ph) {
+            __half* base = static_cast<__half*>(p->out) + (size_t(ph >> 1) * 2 * p->w + (ph & 1)) * p->ldc;
+            if (int rc = swh::encode_tmap_f16(slot[ph], base, 4, dims, so, box)) return rc;
+        }
     }
     // ---- lean kernel (see igemm_lean_body): plain bias / row bias / residual epilogue, no split, no folded
     // LayerNorm -- most layers of a step
@@ -2486,18 +2536,19 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
             cudaStream_t st_ = static_cast<cudaStream_t>(stream);
             if (!pair) {
                 auto kern = p->residual ? k_igemm_lean_r : k_igemm_lean;
-                SW_CUDA_OK(swh::launch_pdl(kern, dim3(grid_x, ntile, 1), dim3(kThreadsLean), size_t(smem), st_, 1, tA1, tA2,
-                                           tB, tOut, tRes, tOut32, a));
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3(grid_x, ntile, phases ? 4 : 1), dim3(kThreadsLean), size_t(smem), st_, 1,
+                                           tA1, tA2, tB, tOut, tRes, tOut32, a));
             } else {
                 auto kern = p->residual ? k_igemm2_lean_r : k_igemm2_lean;
-                SW_CUDA_OK(swh::launch_pdl(kern, dim3((grid_x + 1) / 2 * 2, ntile, 1), dim3(kThreadsLean), size_t(smem), st_,
-                                           2, tA1, tA2, tB, tOut, tRes, tOut32, a));
+                SW_CUDA_OK(swh::launch_pdl(kern, dim3((grid_x + 1) / 2 * 2, ntile, phases ? 4 : 1), dim3(kThreadsLean),
+                                           size_t(smem), st_, 2, tA1, tA2, tB, tOut, tRes, tOut32, a));
             }
             return 0;
         }
     }
+    if (phases) return swh::fail(-1, "sw_igemm: out_phases runs on the lean kernel only (SW_IGEMM_LEAN=0?)");
     // ---- persistent kernel (see k_igemm_p): worth it once a CTA would get more than one tile
-    if (mode == 0 && !pair && a.splits == 1 && (!ln_fused || (p->act == SW_ACT_GEGLU && !p->row_stats_out))) {
+    if (mode == 0 && !pair && !out_strided && a.splits == 1 && (!ln_fused || (p->act == SW_ACT_GEGLU && !p->row_stats_out))) {
         static int env_persist = -1;  // SW_IGEMM_PERSIST: 0 never, 1 auto (default), 2 whenever possible
         if (env_persist < 0) {
             const char* e = getenv("SW_IGEMM_PERSIST");

@@ -50,7 +50,7 @@ enum { SW_ACT_NONE = 0, SW_ACT_SILU = 1, SW_ACT_GELU = 2, SW_ACT_GEGLU = 3 };
  *
  * `in` is the channel-concatenation of a1 (c1 channels) and a2 (c2 channels, may be NULL): the
  * UNet skip-concat is consumed as two K-slabs, never materialised.  A plain linear layer is the
- * case n=h=1, w=M, kh=kw=1, pad=0.  Stride is always 1.
+ * case n=h=1, w=M, kh=kw=1, pad=0.  Stride 1 unless `stride` says 2 (see the end of the struct).
  * With act == SW_ACT_GEGLU the weight rows must be pre-interleaved in blocks of 64 value rows
  * followed by their 64 gate rows; `cout` counts weight rows and the output has cout/2 columns.
  */
@@ -110,6 +110,22 @@ typedef struct {
                             zero-padded to 64 channels: every weight tile the kernel fetches is then one contiguous
                             run of memory (sequential DRAM bursts instead of one 128-byte segment per row), which is
                             what weight-streaming layers (few pixels, 1280 channels) are bound by */
+    /* Strided convolution as implicit GEMM (no im2col buffer): output pixel (y, x) reads input pixels
+     * (y*stride + ky - pad, x*stride + kx - pad) of an input of in_h x in_w pixels (h, w stay the OUTPUT size); the
+     * TMA box simply skips every other pixel.  0 / 1 = stride 1 with in_h = h, in_w = w. */
+    int32_t stride;
+    int32_t in_h, in_w;
+    /* Output pixel strides (0 = 1): pixel (n, y, x) is stored at out + ((n*h*out_sy + y*out_sy) * w*out_sx +
+     * x*out_sx) * ldc, i.e. into every out_sy-th row / out_sx-th column of a [n, h*out_sy, w*out_sx, ldc] tensor whose
+     * first written pixel `out` points at.  A nearest-2x upsample followed by a 3x3 conv is four such 2x2 convs on the
+     * small map, one per output phase, with the filter taps pre-summed (ops/packing.py::fold_upsample2x).  Needs the
+     * TMA-store epilogue: no residual, no split-K, no GEGLU. */
+    int32_t out_sx, out_sy;
+    /* 1: all four phases of such a folded upsample in ONE launch (grid z = phase a*2+b).  kh = kw = 2, pad = 1 (the
+     * kernel takes 1-a / 1-b per phase), out_sx = out_sy = 2, `out` = the first pixel of the [n, 2h, 2w, ldc] tensor,
+     * wgt = the four phase matrices stacked, [4*cout, 4*c1]; bias only (no residual / activation / second input),
+     * cout % 64 == 0. */
+    int32_t out_phases;
 } sw_igemm_params;
 
 int sw_igemm(const sw_igemm_params* p, void* stream);

@@ -1,7 +1,8 @@
 """Per-op DEVICE time of one recorded UNet step: the plan runs once eagerly under CUPTI (torch.profiler,
 SW_PDL=0 so kernels do not overlap), kernel records are matched to plan ops by launch order, then grouped
 by op + shape with achieved TFLOP/s.  Caches are in their real per-step state (weights stream from HBM).
-  SW_PDL=0 python scripts/profile_kernels_plan.py sdxl 1024 7.5"""
+  SW_PDL=0 python scripts/profile_kernels_plan.py sdxl 1024 7.5
+  SW_PDL=0 python scripts/profile_kernels_plan.py sd15 512 7.5 vae     (the VAE decode plan instead of the UNet step)"""
 import os
 import sys
 from collections import defaultdict
@@ -18,16 +19,20 @@ from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
 arch = sys.argv[1] if len(sys.argv) > 1 else "sd15"
 size = int(sys.argv[2]) if len(sys.argv) > 2 else 512
 guidance = float(sys.argv[3]) if len(sys.argv) > 3 else 7.5
+which = sys.argv[4] if len(sys.argv) > 4 else "unet"
 pipe = StableDiffusionPipeline.from_architecture(arch)
 pipe.backend = "sm100"
 pipe.to("cuda:0", torch.float16)
 pipe.set_scheduler("dpmpp_2m", True)
 g = torch.Generator(device="cuda:0").manual_seed(0)
-pipe(prompt="p", height=size, width=size, num_inference_steps=2, generator=g, output_type="latent",
-     guidance_scale=guidance)
+pipe(prompt="p", height=size, width=size, num_inference_steps=2, generator=g,
+     output_type="device" if which == "vae" else "latent", guidance_scale=guidance)
 eng = pipe._denoiser()
-sg = next(iter(eng._graphs.values()))
-rec = sg.rec
+if which == "vae":
+    rec = next(iter(eng._vae_graphs.values()))[2]
+else:
+    sg = next(iter(eng._graphs.values()))
+    rec = sg.rec
 rec.run()
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA]) as prof:

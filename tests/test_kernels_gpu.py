@@ -116,6 +116,56 @@ def test_conv3x3(nat, n, h, w, cin, cout):
     assert _rel_err(out, ref) < 4e-3
 
 
+@pytest.mark.parametrize("n,h,w,cin,cout,asym", [(2, 64, 64, 320, 320, False), (2, 32, 32, 640, 640, False),
+                                                 (2, 16, 16, 1280, 1280, False), (1, 128, 128, 128, 128, True),
+                                                 (1, 10, 18, 64, 96, False), (3, 9, 7, 32, 32, True), (2, 96, 96, 320, 320, False)])
+def test_conv3x3_stride2_implicit(nat, n, h, w, cin, cout, asym):
+    """Stride-2 3x3 conv straight from the NHWC tensor (TMA element strides), UNet (pad 1) and VAE-encoder
+    ((0,1,0,1) pad, then valid) flavours, odd sizes included, against F.conv2d(stride=2)."""
+    from chiaswarm_b200.ops.packing import pack_conv_weight
+
+    torch.manual_seed(31)
+    x = torch.randn(n, cin, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=torch.float16) * ((9 * cin) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    if asym:
+        ref = F.conv2d(F.pad(x.float(), (0, 1, 0, 1)), wt.float(), b.float(), stride=2)
+    else:
+        ref = F.conv2d(x.float(), wt.float(), b.float(), stride=2, padding=1)
+    oh, ow = ref.shape[2], ref.shape[3]
+    out = torch.empty(n, oh, ow, cout, device="cuda", dtype=torch.float16)
+    scratch = torch.zeros((64 << 20) + 16384, dtype=torch.uint8, device="cuda")
+    nat.igemm(x.permute(0, 2, 3, 1).contiguous(), pack_conv_weight(wt), out, n=n, h=oh, w=ow, kh=3, kw=3,
+              pad=0 if asym else 1, stride=2, in_h=h, in_w=w, bias=b, splitk_scratch=scratch)
+    assert _rel_err(out, ref.permute(0, 2, 3, 1)) < 4e-3
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout", [(2, 16, 16, 1280, 1280), (2, 32, 32, 640, 640), (1, 64, 64, 512, 512),
+                                            (1, 5, 9, 32, 64), (1, 128, 128, 256, 256)])
+def test_upsample2x_folded_into_conv(nat, n, h, w, cin, cout):
+    """conv3x3(nearest2x(x)) as four phase convs (2x2 taps, pre-summed weights) writing every other output pixel,
+    against F.interpolate + F.conv2d."""
+    from chiaswarm_b200.ops.packing import fold_upsample2x
+
+    torch.manual_seed(32)
+    x = torch.randn(n, cin, h, w, device="cuda", dtype=torch.float16)
+    wt = torch.randn(cout, cin, 3, 3, device="cuda", dtype=torch.float16) * ((9 * cin) ** -0.5)
+    b = torch.randn(cout, device="cuda", dtype=torch.float16)
+    x_nhwc = x.permute(0, 2, 3, 1).contiguous()
+    out = torch.zeros(n, 2 * h, 2 * w, cout, device="cuda", dtype=torch.float16)
+    for (pa, pb), pw in fold_upsample2x(wt).items():
+        nat.igemm(x_nhwc, pw, out[:, pa::2, pb::2, :], n=n, h=h, w=w, kh=2, kw=2, pad=1 - pa, pad_w=1 - pb, bias=b,
+                  out_sx=2, out_sy=2, ldc=cout)
+    ref = F.conv2d(F.interpolate(x.float(), scale_factor=2, mode="nearest"), wt.float(), b.float(), padding=1)
+    assert _rel_err(out, ref.permute(0, 2, 3, 1)) < 6e-3
+    # the same four phases as the z slices of one launch
+    ph = fold_upsample2x(wt)
+    stacked = torch.cat([ph[(a, bb)] for a in (0, 1) for bb in (0, 1)], 0).contiguous()
+    out1 = torch.zeros_like(out)
+    nat.igemm(x_nhwc, stacked, out1, n=n, h=h, w=w, kh=2, kw=2, pad=1, bias=b, out_sx=2, out_sy=2, out_phases=1, ldc=cout)
+    assert _rel_err(out1, ref.permute(0, 2, 3, 1)) < 6e-3
+
+
 @pytest.mark.parametrize("n,h,w,cin,cout,tile_n", [(2, 64, 64, 320, 320, 0), (2, 32, 32, 640, 640, 256), (2, 16, 16, 128, 192, 64),
                                                    (1, 96, 96, 64, 128, 128), (3, 40, 72, 64, 320, 160), (1, 24, 24, 64, 64, 64)])
 def test_conv3x3_cta_pair(nat, n, h, w, cin, cout, tile_n):
