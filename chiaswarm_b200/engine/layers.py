@@ -437,6 +437,7 @@ class TransformerBlock:
         rec.add(nat.igemm_reducescatter, attn, wo, ctx.tile_peers(staging, P * (s // 128) * ntile), y1, m_local=s, ldc=c,
                 bias=self.o1.bias, residual=y)
         rec.release(attn)
+        self._tp_debug = (gathered, qkv, attn, y1, wqkv, wo)  # (scripts/tp_block_check.py inspects the stages)
         return y1
 
     def use_fused(self, rows: int) -> bool:

@@ -2646,6 +2646,7 @@ static int igemm_fused_lean(const sw_igemm_params* p, const sw_peers* peers, int
     IGemmArgs a;
     memset(&a, 0, sizeof(a));
     a.c1 = p->c1;
+    a.sx = 1;
     a.n = a.h = 1;
     a.w = p->w;
     a.kh = a.kw = 1;

@@ -59,3 +59,13 @@ def test_gang_serving(world, gang):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "gang_check.py"), "--world", str(world), "--gang",
                         str(gang)], cwd=ROOT, capture_output=True, text=True, timeout=1100)
     assert "GANG_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_tensor_parallel_transformer_block(world):
+    """A transformer block of a row-split plan with head-parallel self-attention (LayerNorm -> all-gather fused into
+    the QKV GEMM -> local attention over this rank's heads -> out-projection GEMM fused with its reduce-scatter):
+    every stage and the block output against the single-GPU plan, replayed with changing inputs."""
+    _need(world)
+    r = _torchrun(world, 29539, "tp_block_check.py")
+    assert "TP_BLOCK_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
