@@ -191,6 +191,7 @@ class StableDiffusionPipeline:
         if self.safety_checker is not None and hasattr(self.safety_checker, "to"):
             self.safety_checker.to(self.device, self.dtype)
         self._engine = None
+        self.__dict__.pop("_text_engines", None)
         return self
 
     # ------------------------------------------------------------------ scheduler selection
@@ -203,6 +204,21 @@ class StableDiffusionPipeline:
         self.scheduler_kind = kind
         self.use_karras_sigmas = bool(use_karras_sigmas)
 
+    def _text_encoder_fn(self, module):
+        """The callable that runs a CLIP text encoder: the recorded sm_100a plan (engine/clip_sm100.py) on the sm100
+        back end, the eager module otherwise (SW_TEXT_ENCODER=torch forces the module)."""
+        if module is None:
+            return None
+        if self.backend != "sm100" or self.device.type != "cuda" or os.environ.get("SW_TEXT_ENCODER", "sm100") == "torch":
+            return module
+        engines = self.__dict__.setdefault("_text_engines", {})
+        eng = engines.get(id(module))
+        if eng is None:
+            from ..engine.clip_sm100 import ClipTextEngine
+
+            eng = engines[id(module)] = ClipTextEngine(module, self.device)
+        return eng
+
     # ------------------------------------------------------------------ text conditioning
     @torch.no_grad()
     def encode_prompt(self, prompts: List[str], negative: List[str], n_cond: int):
@@ -213,13 +229,15 @@ class StableDiffusionPipeline:
                 return ids.pin_memory().to(self.device, non_blocking=True)
             return ids
 
+        te1, te2 = self._text_encoder_fn(self.text_encoder), self._text_encoder_fn(self.text_encoder_2)
+
         def enc(texts):
             ids = to_dev(self.tokenizer(texts))
             if self.text_encoder_2 is None:
-                return self.text_encoder(ids)[0], None
-            h1, _ = self.text_encoder(ids, output_hidden_state=-2)
+                return te1(ids)[0], None
+            h1, _ = te1(ids, output_hidden_state=-2)
             ids2 = to_dev(self.tokenizer_2(texts))
-            h2, pooled = self.text_encoder_2(ids2, output_hidden_state=-2)
+            h2, pooled = te2(ids2, output_hidden_state=-2)
             return torch.cat([h1, h2], dim=-1), pooled
 
         cond, pooled_c = enc(prompts)
@@ -233,6 +251,19 @@ class StableDiffusionPipeline:
             embeds = torch.cat([cond, unc, unc])
             pooled = None if pooled_c is None else torch.cat([pooled_c, pooled_u, pooled_u])
         return embeds, pooled
+
+    # ------------------------------------------------------------------ VAE encode
+    def _vae_encode(self, x, generator=None, sample=True):
+        """AutoencoderKL.encode: on the sm_100a engine when that is the back end (engine/unet_sm100.VaeEncoderPlan),
+        else the eager module; the reparameterisation noise is drawn the same way either way."""
+        if self.backend != "sm100" or self.device.type != "cuda" or os.environ.get("SW_VAE_ENCODE", "1") in ("0", "torch"):
+            return self.vae.encode(x, generator, sample)
+        mean, logvar = self._denoiser().encode_moments(x)
+        if not sample:
+            return mean
+        std = torch.exp(0.5 * logvar.float().clamp(-30.0, 20.0)).to(mean.dtype)
+        noise = torch.randn(mean.shape, generator=generator, device=mean.device, dtype=mean.dtype)
+        return mean + std * noise
 
     # ------------------------------------------------------------------ main entry
     @torch.no_grad()
@@ -307,7 +338,7 @@ class StableDiffusionPipeline:
         control = None        # control image [n_cond*B, 3, H, W] in [0,1]
         init_latents = None
         if mode == "sd_img2img":
-            init = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), generator) * self.vae.scaling_factor
+            init = self._vae_encode(pil_to_tensor(image, self.device, self.dtype), generator) * self.vae.scaling_factor
             init = init.expand(batch, -1, -1, -1)
             t_start = max(int(num_inference_steps) - min(int(int(num_inference_steps) * strength), int(num_inference_steps)), 0)
             plan = plan.slice_from(t_start)
@@ -320,19 +351,19 @@ class StableDiffusionPipeline:
                 img = pil_to_tensor(image, self.device, self.dtype)
                 m = torch.from_numpy(np.asarray(mask_image.convert("L").resize((width, height)), dtype=np.float32) / 255.0)
                 m = (m >= 0.5).to(self.device, self.dtype)[None, None]
-                masked = self.vae.encode(img * (1 - m), generator) * self.vae.scaling_factor
+                masked = self._vae_encode(img * (1 - m), generator) * self.vae.scaling_factor
                 m8 = torch.nn.functional.interpolate(m, size=(h8, w8))
                 if unet_in == 9:
                     extra = torch.cat([m8, masked], dim=1).expand(batch, -1, -1, -1).repeat(n_cond, 1, 1, 1)
                 else:  # legacy 4-channel inpainting: re-impose the known region every step
-                    init_latents = (self.vae.encode(img, generator) * self.vae.scaling_factor).float()
+                    init_latents = (self._vae_encode(img, generator) * self.vae.scaling_factor).float()
                     init_latents = (init_latents, m8.float(), randn().float())
             elif pix2pix:
                 if image_list is not None:
-                    img_lat = self.vae.encode(torch.cat([pil_to_tensor(im, self.device, self.dtype)
-                                                         for im in image_list]), sample=False)
+                    img_lat = self._vae_encode(torch.cat([pil_to_tensor(im, self.device, self.dtype)
+                                                          for im in image_list]), sample=False)
                 else:
-                    img_lat = self.vae.encode(pil_to_tensor(image, self.device, self.dtype), sample=False)
+                    img_lat = self._vae_encode(pil_to_tensor(image, self.device, self.dtype), sample=False)
                     img_lat = img_lat.expand(batch, -1, -1, -1)
                 zeros = torch.zeros_like(img_lat)
                 extra = torch.cat([img_lat, img_lat, zeros]) if n_cond == 3 else img_lat

@@ -1,0 +1,123 @@
+"""CLIP text encoder on the sm_100a kernels (the reference runs it through transformers /
+cuBLAS inside `pipeline(**kwargs)`, swarm/diffusion/diffusion_func.py:96).
+
+Same recorded-plan design as the UNet (engine/layers.py): per (batch, tokens) one static list of launches --
+LayerNorm, fused QKV GEMM, causal flash attention (sw_flash_attn `causal`), output projection with the residual in
+its epilogue, LayerNorm, fc1 with the activation in its epilogue, fc2 with the residual -- captured in a CUDA graph.
+quick_gelu(x) = x * sigmoid(1.702 x) is SiLU(1.702 x) / 1.702, so fc1 carries the 1.702 in its weights and the
+epilogue's output scale carries the 1 / 1.702: no extra kernel.  Only the token / position embedding gather and the
+EOS-row pick stay in torch (two tiny indexing kernels, no GEMM).
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict
+
+import torch
+
+from ..ops import native as nat
+from .layers import LayerNorm, Linear, Recorder
+
+
+class _Layer:
+    def __init__(self, m, act: str):
+        a = m.self_attn
+        self.heads = a.heads
+        self.ln1, self.ln2 = LayerNorm(m.layer_norm1), LayerNorm(m.layer_norm2)
+        self.qkv = Linear(torch.cat([a.q_proj.weight, a.k_proj.weight, a.v_proj.weight], 0),
+                          torch.cat([a.q_proj.bias, a.k_proj.bias, a.v_proj.bias], 0))
+        self.out = Linear(a.out_proj.weight, a.out_proj.bias)
+        if act == "quick_gelu":
+            self.fc1 = Linear(m.mlp.fc1.weight.detach().float() * 1.702, m.mlp.fc1.bias.detach().float() * 1.702)
+            self.fc1_act, self.fc1_scale = nat.ACT_SILU, 1.0 / 1.702
+        elif act in ("gelu", "gelu_new"):
+            self.fc1 = Linear(m.mlp.fc1.weight, m.mlp.fc1.bias)
+            self.fc1_act, self.fc1_scale = nat.ACT_GELU, 1.0
+        else:
+            raise ValueError(f"unsupported CLIP activation {act}")
+        self.fc2 = Linear(m.mlp.fc2.weight, m.mlp.fc2.bias)
+
+    def __call__(self, rec: Recorder, x: torch.Tensor, b: int, s: int, keep_input: bool) -> torch.Tensor:
+        d = x.shape[-1]
+        dh = d // self.heads
+        h = self.ln1(rec, x)
+        qkv = self.qkv(rec, h)
+        rec.release(h)
+        v5 = qkv.view(b, s, 3, self.heads, dh)
+        attn = rec.buf(b, s, d)
+        rec.add(nat.flash_attn, v5[:, :, 0], v5[:, :, 1], v5[:, :, 2], attn, batch=b, heads=self.heads, seq_q=s, seq_kv=s,
+                head_dim=dh, causal=True)
+        rec.release(qkv)
+        x1 = self.out(rec, attn.view(b * s, d), residual=x)
+        rec.release(attn)
+        if not keep_input:
+            rec.release(x)
+        h = self.ln2(rec, x1)
+        f = self.fc1(rec, h, act=self.fc1_act, out_scale=self.fc1_scale)
+        rec.release(h)
+        x2 = self.fc2(rec, f, residual=x1)
+        rec.release(f)
+        rec.release(x1)
+        return x2
+
+
+class ClipTextEngine:
+    """Drop-in for `CLIPTextModel.__call__`: (ids, output_hidden_state=-1, eos_token_id=None) -> (hidden, pooled)."""
+
+    def __init__(self, model, device):
+        nat.lib()
+        self.model = model
+        self.device = torch.device(device)
+        cfg = model.config
+        self.d = cfg["hidden_size"]
+        self.layers = [_Layer(m, cfg["hidden_act"]) for m in model.text_model.encoder.layers]
+        self.final_ln = LayerNorm(model.text_model.final_layer_norm)
+        self.proj = Linear(model.text_projection.weight) if model.text_projection is not None else None
+        self._plans: Dict[tuple, tuple] = {}
+        self.last_launches = 0
+
+    def _plan(self, b: int, s: int):
+        entry = self._plans.get((b, s))
+        if entry is not None:
+            return entry
+        rec = Recorder(self.device)
+        x_in = torch.zeros(b * s, self.d, dtype=torch.float16, device=self.device)
+        x = x_in
+        penult = None
+        n = len(self.layers)
+        for i, layer in enumerate(self.layers):
+            if i == n - 1:
+                penult = x  # hidden[-2]: what the last layer consumes; it must survive the last layer
+            x = layer(rec, x, b, s, keep_input=(i == 0 or i == n - 1))
+        last = self.final_ln(rec, x)
+        rec.run()  # eager pass: kernel attributes, validation
+        torch.cuda.synchronize()
+        graph = None
+        if os.environ.get("SDAAS_CUDA_GRAPH", "1") not in ("0", "false", ""):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                rec.run()
+        entry = self._plans[(b, s)] = (x_in, penult if penult is not None else x_in, last, rec, graph)
+        if len(self._plans) > 8:
+            self._plans.pop(next(iter(self._plans)))
+        return entry
+
+    @torch.no_grad()
+    def __call__(self, input_ids, output_hidden_state: int = -1, eos_token_id=None):
+        if output_hidden_state not in (-1, -2):
+            return self.model(input_ids, output_hidden_state, eos_token_id)  # (other layers: the eager module)
+        b, s = input_ids.shape
+        x_in, penult, last, rec, graph = self._plan(b, s)
+        x_in.copy_(self.model.text_model.embeddings(input_ids).reshape(b * s, self.d))
+        if graph is not None:
+            graph.replay()
+        else:
+            rec.run()
+        self.last_launches = len(rec)
+        lastv = last.view(b, s, self.d)
+        eos = input_ids.argmax(dim=-1) if eos_token_id is None else (input_ids == eos_token_id).int().argmax(dim=-1)
+        pooled = lastv[torch.arange(b, device=lastv.device), eos]
+        if self.proj is not None:
+            pooled = nat.linear(pooled.contiguous(), self.proj.wgt)
+        out = lastv if output_hidden_state == -1 else penult.view(b, s, self.d)
+        return out.clone(), pooled.clone()  # (the plan's buffers are reused by the next call)

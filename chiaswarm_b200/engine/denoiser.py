@@ -224,6 +224,32 @@ class SM100Denoiser:
         rec.run()
         sg.control_feat.t.copy_(feat.t)
 
+    # ------------------------------------------------------------------ VAE encode
+    @torch.no_grad()
+    def encode_moments(self, x):
+        """x: images in [-1, 1], NCHW. Returns (mean, logvar) NCHW like AutoencoderKL.encode_moments, computed by the
+        recorded sm_100a plan (one plan per input shape, kept with the engine)."""
+        from .unet_sm100 import VaeEncoderPlan
+
+        if getattr(self, "vae_enc_plan", None) is None:
+            self.vae_enc_plan = VaeEncoderPlan(self.pipe.vae, self.device)
+            self._vae_enc = {}
+        vp = self.vae_enc_plan
+        n, c, h, w = x.shape
+        entry = self._vae_enc.get((n, h, w))
+        if entry is None:
+            xin = torch.zeros(n, h, w, vp.in_pad, dtype=torch.float16, device=self.device)
+            rec = Recorder(self.device)
+            out = vp.record(rec, FM(xin, n, h, w, vp.in_pad))
+            entry = self._vae_enc[(n, h, w)] = (xin, out, rec)
+            if len(self._vae_enc) > 4:
+                self._vae_enc.pop(next(iter(self._vae_enc)))
+        xin, out, rec = entry
+        nat.nchw_to_nhwc(x.to(torch.float16).contiguous(), xin, vp.in_pad)
+        rec.run()
+        m = out.t[..., :vp.moments].permute(0, 3, 1, 2).to(x.dtype)
+        return m.chunk(2, dim=1)
+
     # ------------------------------------------------------------------ VAE decode
     @torch.no_grad()
     def decode(self, z):

@@ -603,8 +603,15 @@ class Upsample:
         a, halo = x.t, {}
         if rec.patch is not None and rec.patch.rows:  # rows y-1 / y+1 of a strip's edge live on the neighbours
             a, halo = rec.patch.conv_input(rec, x)
+        mode = os.environ.get("SW_UPSAMPLE", "fold")  # fold (default) | phases4 (one launch per phase) | materialise
+        if mode == "materialise":  # A/B path: the nearest-2x copy in memory, then the 3x3 conv on it
+            up = rec.fm(x.n, 2 * x.h, 2 * x.w, x.c)
+            rec.add(nat.upsample2x, x.t, up.t, n=x.n, h=x.h, w=x.w)
+            o = self.conv(rec, up)
+            rec.release(up)
+            return o
         o = rec.fm(x.n, 2 * x.h, 2 * x.w, self.conv.cout)
-        if self.stacked is not None:
+        if self.stacked is not None and mode != "phases4":
             rec.add(nat.igemm, a, self.stacked, o.t, n=x.n, h=x.h, w=x.w, kh=2, kw=2, pad=1, bias=self.conv.bias,
                     out_sx=2, out_sy=2, out_phases=1, ldc=o.c, **halo)
             return o

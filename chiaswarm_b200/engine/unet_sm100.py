@@ -202,6 +202,93 @@ class ControlNetPlan(UNetPlan):
                 bias=self.zero_mid.bias, residual=unet_mid.tokens())
 
 
+SCORE_BYTES = 16 << 20  # largest score block of the VAE's single-head attention (the 128x128x512 map itself is 16 MiB)
+
+
+def vae_attention(rec: Recorder, x: FM, norm: GroupNorm, qkv_lin: Linear, out_lin: Linear, c: int) -> FM:
+    """AutoencoderKL mid-block attention: ONE head of width c = 512, sequence = every pixel.  The head is too wide for
+    the flash kernel's TMEM budget (S + O accumulators), so it runs as GEMM -> row softmax -> GEMM on blocks of
+    query rows sized so that a score block never exceeds SCORE_BYTES: 1024x1024 images (S = 16384) take 32 blocks
+    of 512 rows instead of one 512 MiB S x S matrix."""
+    s = x.h * x.w
+    g = norm(rec, x, False)
+    qkv = qkv_lin(rec, g.tokens())  # [n*s, 3c]
+    rec.release(g)
+    out = rec.fm(x.n, x.h, x.w, c)
+    attn = rec.buf(x.n * s, c)
+    qc = s if s * s * 2 <= SCORE_BYTES else max(128, (SCORE_BYTES // (2 * s)) // 128 * 128)
+    scores = rec.buf(qc, s)
+    vt = rec.buf(c, s)
+    for b in range(x.n):
+        blk = qkv[b * s:(b + 1) * s]
+        # q, k are column blocks of the fused projection (strided operands); V^T via the channels-last -> planar
+        # transpose kernel, once per image
+        rec.add(nat.nhwc_to_nchw, blk[:, 2 * c:], vt.view(1, c, 1, s), 3 * c)
+        for q0 in range(0, s, qc):
+            rows = min(qc, s - q0)
+            sc = scores[:rows]
+            rec.add(nat.igemm, blk[q0:q0 + rows, :c], blk[:, c:2 * c], sc, n=1, h=1, w=rows, out_scale=c ** -0.5)
+            rec.add(nat.softmax_rows, sc, sc, 1.0)
+            rec.add(nat.igemm, sc, vt, attn[b * s + q0:b * s + q0 + rows], n=1, h=1, w=rows)
+    out_lin(rec, attn, residual=x.tokens(), out=out.tokens())
+    for t in (attn, scores, vt, qkv):
+        rec.release(t)
+    return out
+
+
+class VaeEncoderPlan:
+    """AutoencoderKL.encode on sm_100a kernels (img2img / inpaint / pix2pix inputs; the reference reaches it inside
+    `pipeline(**kwargs)`, swarm/diffusion/diffusion_func.py:96): conv_in -> down blocks (stride-2 convs as implicit
+    GEMM with the (0,1,0,1) padding as TMA out-of-bounds fill) -> mid block -> GN+SiLU -> conv_out -> quant_conv.
+    Output: the moments [n, h/8, w/8, 2*latent] channels-last."""
+
+    def __init__(self, vae, device):
+        enc = vae.encoder
+        self.in_pad = _r8(vae.config["in_channels"])
+        self.conv_in = Conv(enc.conv_in, cin_pad=self.in_pad)
+        self.downs = []
+        for blk in enc.down_blocks:
+            self.downs.append(dict(resnets=[Resnet(r) for r in blk.resnets],
+                                   down=Conv(blk.downsamplers[0].conv, asym_pad=True) if blk.downsamplers is not None else None))
+        self.mid_res = [Resnet(r) for r in enc.mid_block.resnets]
+        at = enc.mid_block.attentions[0]
+        self.attn_norm = GroupNorm(at.group_norm)
+        self.attn_qkv = Linear(torch.cat([at.to_q.weight, at.to_k.weight, at.to_v.weight], 0),
+                               torch.cat([at.to_q.bias, at.to_k.bias, at.to_v.bias], 0))
+        self.attn_out = Linear(at.to_out[0].weight, at.to_out[0].bias)
+        self.attn_c = at.to_q.weight.shape[0]
+        self.norm_out = GroupNorm(enc.conv_norm_out)
+        self.conv_out = Conv(enc.conv_out)
+        self.quant = Linear(vae.quant_conv.weight, vae.quant_conv.bias)
+        self.moments = 2 * vae.config["latent_channels"]
+
+    def record(self, rec: Recorder, img: FM) -> FM:
+        x = self.conv_in(rec, img)
+        for blk in self.downs:
+            for r in blk["resnets"]:
+                x2 = r(rec, x)
+                rec.release(x)
+                x = x2
+            if blk["down"] is not None:
+                x2 = blk["down"](rec, x)
+                rec.release(x)
+                x = x2
+        x2 = self.mid_res[0](rec, x)
+        rec.release(x)
+        x = vae_attention(rec, x2, self.attn_norm, self.attn_qkv, self.attn_out, self.attn_c)
+        rec.release(x2)
+        x2 = self.mid_res[1](rec, x)
+        rec.release(x)
+        g = self.norm_out(rec, x2, True)
+        rec.release(x2)
+        h = self.conv_out(rec, g)
+        rec.release(g)
+        out = rec.fm(h.n, h.h, h.w, self.quant.nout)
+        self.quant(rec, h.tokens(), out=out.tokens())
+        rec.release(h)
+        return out
+
+
 class VaeDecoderPlan:
     """AutoencoderKL.decode on sm_100a kernels, ending in a uint8 HWC image (row W8)."""
 
@@ -227,28 +314,7 @@ class VaeDecoderPlan:
         self.conv_out = Conv(dec.conv_out)
 
     def _attention(self, rec: Recorder, x: FM) -> FM:
-        c = self.attn_c
-        s = x.h * x.w
-        g = self.attn_norm(rec, x, False)
-        qkv = self.attn_qkv(rec, g.tokens())  # [n*s, 3c]
-        rec.release(g)
-        out = rec.fm(x.n, x.h, x.w, c)
-        o_tok = out.tokens()
-        attn = rec.buf(x.n * s, c)
-        scores = rec.buf(s, s)
-        vt = rec.buf(c, s)
-        for b in range(x.n):
-            blk = qkv[b * s:(b + 1) * s]
-            # q, k are column blocks of the fused projection (strided operands); V^T via the
-            # channels-last -> planar transpose kernel
-            rec.add(nat.igemm, blk[:, :c], blk[:, c:2 * c], scores, n=1, h=1, w=s, out_scale=c ** -0.5)
-            rec.add(nat.softmax_rows, scores, scores, 1.0)
-            rec.add(nat.nhwc_to_nchw, blk[:, 2 * c:], vt.view(1, c, 1, s), 3 * c)
-            rec.add(nat.igemm, scores, vt, attn[b * s:(b + 1) * s], n=1, h=1, w=s)
-        self.attn_out(rec, attn, residual=x.tokens(), out=o_tok)
-        for t in (attn, scores, vt, qkv):
-            rec.release(t)
-        return out
+        return vae_attention(rec, x, self.attn_norm, self.attn_qkv, self.attn_out, self.attn_c)
 
     def record(self, rec: Recorder, z: FM):
         """z: latents / scaling_factor (+ post-quant bias), channels-last, padded to 8 channels.

@@ -80,6 +80,7 @@ class AttnParams(C.Structure):
         ("batch", C.c_int32), ("heads", C.c_int32), ("seq_q", C.c_int32), ("seq_kv", C.c_int32),
         ("head_dim", C.c_int32),
         ("scale", C.c_float),
+        ("causal", C.c_int32),
     ]
 
 
@@ -301,7 +302,7 @@ def linear(x, wgt, out=None, **kw):
     return out
 
 
-def flash_attn(q, k, v, out, *, batch, heads, seq_q, seq_kv, head_dim, scale=None):
+def flash_attn(q, k, v, out, *, batch, heads, seq_q, seq_kv, head_dim, scale=None, causal=False):
     """q/k/v: fp16 tensors viewed as [batch, seq, heads, head_dim] (strides taken from the views);
     out: [batch, seq_q, heads*head_dim]."""
     for t, nm in ((q, "q"), (k, "k"), (v, "v")):
@@ -316,6 +317,7 @@ def flash_attn(q, k, v, out, *, batch, heads, seq_q, seq_kv, head_dim, scale=Non
     p.o_stride_b, p.o_stride_s = out.stride(0), out.stride(1)
     p.batch, p.heads, p.seq_q, p.seq_kv, p.head_dim = batch, heads, seq_q, seq_kv, head_dim
     p.scale = float(scale if scale is not None else head_dim ** -0.5)
+    p.causal = int(bool(causal))
     _check(lib().sw_flash_attn(C.byref(p), _stream()), "sw_flash_attn")
     _count()
     return out

@@ -41,6 +41,7 @@ struct AttnArgs {
     // v1, short sequences (temporal attention: seq = frames): `pack` batch entries share one 128-row
     // tile (TMA box {64, 1, seq, pack}); the softmax masks everything outside a row's own entry
     int pack;
+    int causal;  // v1: row q0 + r sees columns <= its own index
     // v2: clocks the second query tile's softmax warpgroup holds back before its first tile, so that the two
     // warpgroups sit half a period apart (one in the exponentials while the other loads / reduces / waits)
     int stagger;
@@ -266,7 +267,8 @@ __global__ void __launch_bounds__(kThreads)
         float l = 0.0f;
         for (int j = 0; j < nkv; ++j) {
             const int kv_valid = pack > 1 ? pack * p.seq_kv : min(BKV, p.seq_kv - j * BKV);
-            const int col_hi = pack > 1 ? col_lo + p.seq_kv : kv_valid;
+            int col_hi = pack > 1 ? col_lo + p.seq_kv : kv_valid;
+            if (p.causal) col_hi = min(col_hi, q0 + r - j * BKV + 1);  // (an empty range leaves m_ref and l untouched)
             if (lane == 0) mbar_wait(s_full, uint32_t(j & 1));
             __syncwarp();
             tc_fence_after();
@@ -884,12 +886,15 @@ extern "C" int sw_flash_attn(const sw_attn_params* p, void* stream) {
         a.stagger = env_stagger;
     }
 
+    a.causal = p->causal ? 1 : 0;
+    if (a.causal && (p->seq_q > BQ || p->seq_q != p->seq_kv))
+        return swh::fail(-1, "sw_flash_attn: causal attention is defined for self-attention with seq <= %d", BQ);
     // short self-attention sequences (temporal attention over frames): several batch entries per tile
     a.pack = 1;
     // (queries and keys may differ in length: a frame-split clip attends from its own frames to all of them; row r of a
     // tile belongs to entry r / seq_q and sees columns [entry * seq_kv, (entry + 1) * seq_kv))
     const int seq_max = p->seq_q > p->seq_kv ? p->seq_q : p->seq_kv;
-    if (seq_max <= 64 && p->batch > 1) {
+    if (seq_max <= 64 && p->batch > 1 && !a.causal) {
         a.pack = 128 / seq_max;
         if (a.pack > p->batch) a.pack = p->batch;
         if (a.pack > 128) a.pack = 128;

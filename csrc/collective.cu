@@ -5,6 +5,8 @@
 #include "common.cuh"
 #include "host_util.h"
 
+#include <stdlib.h>
+
 namespace {
 
 using namespace sw;
@@ -29,6 +31,7 @@ struct PeerFlags {
     int* flags[8];
     const int* epoch_base;  // optional device counter: epoch += *epoch_base * epoch_mul
     int epoch_mul;
+    int sysfence;           // SW_PEER_SYSFENCE=1: every thread runs a system-scope fence before the flag (A/B switch)
 };
 
 __device__ __forceinline__ int resolve_epoch(const PeerFlags& f) {
@@ -38,8 +41,9 @@ __device__ __forceinline__ int resolve_epoch(const PeerFlags& f) {
 // Everything this rank wrote before (on this stream) becomes visible to the peers, then its flag
 // slot on every peer is raised to `epoch`.
 __global__ void k_peer_signal(const PeerFlags f) {
-    // (earlier kernels of this stream have completed; the release store below orders their writes before the flag.
-    // A system-scope fence here cost ~10 us per kernel on an NVLink-connected box for nothing.)
+    // Everything earlier kernels of this stream wrote (TMA stores included) must be visible to the peers before the
+    // flag: one system-scope fence per signalling thread, then the release store.
+    __threadfence_system();
     if (threadIdx.x < f.world) st_release_sys(f.flags[threadIdx.x] + f.rank, resolve_epoch(f));
 }
 
@@ -85,7 +89,10 @@ __global__ void __launch_bounds__(1024) k_peer_exchange(const PeerFlags f, const
     // ordering: every thread's stores -> CTA barrier -> (sliced: device-scope fence + ticket) -> ONE st.release.sys,
     // which is cumulative over everything that happened before it.  No system-scope fence per CTA: on a box with
     // peer mappings each one stalls for microseconds.
-    if (x.slices > 1) __threadfence();
+    if (f.sysfence)
+        __threadfence_system();
+    else if (x.slices > 1)
+        __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
         bool last = true;
@@ -167,6 +174,12 @@ int fill(PeerFlags* f, const sw_peers* p) {
     f->epoch_base = p->epoch_base;
     f->epoch_mul = p->epoch_mul;
     for (int d = 0; d < p->world; ++d) f->flags[d] = p->flags[d];
+    static int env = -1;
+    if (env < 0) {
+        const char* e = getenv("SW_PEER_SYSFENCE");
+        env = e ? atoi(e) : 0;
+    }
+    f->sysfence = env;
     return 0;
 }
 
@@ -217,6 +230,14 @@ extern "C" int sw_peer_exchange(const sw_peers* peers, const sw_xfer* xfers, int
     if (slices > 16) slices = 16;
     if (slices * count > 128) slices = 128 / count;
     if (slices < 1) slices = 1;
+    {
+        static int env = -1;  // SW_XFER_SLICES=n caps the CTAs per transfer (A/B switch; 1 = the single-CTA copy)
+        if (env < 0) {
+            const char* e = getenv("SW_XFER_SLICES");
+            env = e ? atoi(e) : 0;
+        }
+        if (env > 0 && slices > env) slices = env;
+    }
     x.slices = slices;
     static unsigned int* ticket_base[64] = {nullptr};  // per device: the symbol has one instance on each
     static unsigned int seq = 0;

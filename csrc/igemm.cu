@@ -2316,6 +2316,8 @@ static int igemm_impl(const sw_igemm_params* p, const sw_peers* peers, int mode,
         }
     }
     if (bn < 32 || bn > 256 || bn % 32) return swh::fail(-1, "sw_igemm: tile_n=%d must be a multiple of 32 in [32,256]", bn);
+    // phase mode has no 32-column tail map (its slot carries a phase's output map): whole 64-column slabs only
+    if (phases && bn % 64) bn = (bn + 63) / 64 * 64;
     const int tiles_ncol = (p->cout + bn - 1) / bn;
     a.bn = bn;
     a.tmem_cols = bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256;

@@ -25,6 +25,7 @@ struct GnDist {
     int* peer_flags[8];    // rank d: int [world], slot [src] written by rank src
     const int* epoch_base;  // optional device counter: epoch += *epoch_base * epoch_mul (graph replays)
     int epoch_mul;
+    int sysfence;           // SW_PEER_SYSFENCE=1: system-scope fence by every thread before the flag (A/B switch)
 };
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
@@ -180,7 +181,10 @@ __global__ void k_gn_stats(const __half* __restrict__ x1, const __half* __restri
     }
     if (threadIdx.x == 0) tickets[n] = 0u;  // leave the scratch ready for the next call
     if (dist.world > 1) {
-        __threadfence();  // device scope is enough ahead of the ticket; the flag store below is the sys-scope release
+        if (dist.sysfence)
+            __threadfence_system();
+        else
+            __threadfence();  // device scope ahead of the ticket; the flag store below is the sys-scope release
         __syncthreads();
         if (threadIdx.x == 0) {
             // the image that finishes last raises this rank's flag on every peer
@@ -714,6 +718,14 @@ static int gn_launch(const void* x, const void* x2, void* y, const void* gamma, 
         dist.epoch = peers->epoch;
         dist.epoch_base = peers->epoch_base;
         dist.epoch_mul = peers->epoch_mul;
+        {
+            static int env = -1;
+            if (env < 0) {
+                const char* e = getenv("SW_PEER_SYSFENCE");
+                env = e ? atoi(e) : 0;
+            }
+            dist.sysfence = env;
+        }
         for (int d = 0; d < peers->world; ++d) {
             dist.peer_stats[d] = static_cast<float*>(peers->peer[d]);
             dist.peer_flags[d] = peers->flags[d];

@@ -199,7 +199,7 @@ typedef struct {
 } sw_xfer;
 int sw_peer_exchange(const sw_peers* peers, const sw_xfer* xfers, int count, void* stream);
 
-/* Flash attention (non-causal, no mask) on tcgen05: S=QK^T and O+=PV accumulate in TMEM, online
+/* Flash attention (no mask, or causal for short sequences) on tcgen05: S=QK^T and O+=PV accumulate in TMEM, online
  * softmax in registers.  Replaces SDPA / xformers memory_efficient_attention (K1, K2), reference
  * call sites swarm/diffusion/diffusion_func.py:86-87,96.
  * q/k/v are fp16 with layout [batch, seq, heads, head_dim] expressed through element strides
@@ -214,6 +214,8 @@ typedef struct {
     void* out; int64_t o_stride_b, o_stride_s;  /* elements; head h starts at column h*head_dim */
     int32_t batch, heads, seq_q, seq_kv, head_dim;
     float scale;                                 /* softmax scale, usually head_dim^-0.5 */
+    int32_t causal;                              /* 1: query i attends to keys 0..i only (CLIP text encoder); needs
+                                                    seq_q <= 128 (one query tile), sw_flash_attn only */
 } sw_attn_params;
 
 int sw_flash_attn(const sw_attn_params* p, void* stream);

@@ -133,3 +133,61 @@ def test_layernorm_fusion_matches_torch(monkeypatch):
     _compare(ref, eng, 2, 5e-2, height=256, width=256)
     rec = next(iter(eng._denoiser()._graphs.values())).rec
     assert not any(getattr(fn, "__name__", "") == "layernorm" for fn, _, _ in rec.ops)
+
+
+@pytest.mark.parametrize("size", [(256, 256), (320, 192)])
+def test_vae_encode_engine_matches_torch(size):
+    """AutoencoderKL.encode on the recorded sm_100a plan (stride-2 implicit-GEMM downsamplers, chunk-free mid-block
+    attention at this size) against the eager module: moments of a structured test image."""
+    ref, eng = _pipes("sd15")
+    h, w = size
+    g = torch.Generator(device="cuda:0").manual_seed(9)
+    x = (torch.rand(2, 3, h, w, generator=g, device="cuda:0") * 2 - 1).to(torch.float16)
+    want = ref.vae.encode(x, sample=False).float()
+    got = eng._vae_encode(x, sample=False).float()
+    assert got.shape == want.shape
+    assert ((got - want).abs().max() / want.abs().max().clamp_min(1e-3)).item() < 3e-2
+
+
+def test_vae_attention_in_query_blocks(monkeypatch):
+    """The VAE's single-head attention with the score matrix cut into blocks of query rows (what a 1024x1024 decode
+    does) gives what the one-block form gives."""
+    from chiaswarm_b200.engine import unet_sm100
+
+    ref, eng = _pipes("sd15")
+    g = torch.Generator(device="cuda:0").manual_seed(4)
+    lat = torch.randn(1, 4, 48, 48, generator=g, device="cuda:0", dtype=torch.float16)
+    whole = eng._denoiser().decode(lat).float()
+    monkeypatch.setattr(unet_sm100, "SCORE_BYTES", 48 * 48 * 2 * 256)  # 256 query rows per block -> 9 blocks
+    eng._engine = None
+    blocks = eng._denoiser().decode(lat).float()
+    assert (whole - blocks).abs().max().item() <= 1.0  # uint8 levels
+
+
+@pytest.mark.parametrize("cfg", [dict(), dict(hidden_size=1280, intermediate_size=5120, num_hidden_layers=4,
+                                              num_attention_heads=20, hidden_act="gelu", projection_dim=1280)])
+def test_clip_text_engine_matches_module(cfg):
+    """CLIP text encoder as a recorded sm_100a plan (causal flash attention, quick_gelu folded into fc1) against the
+    eager module: last hidden state, penultimate hidden state (SDXL / clip-skip) and pooled output."""
+    from chiaswarm_b200.diffusion.pipelines import _init_module
+    from chiaswarm_b200.engine.clip_sm100 import ClipTextEngine
+    from chiaswarm_b200.models.clip_text import CLIPTextModel
+
+    te = _init_module(CLIPTextModel(**cfg), 21).to("cuda:0", torch.float16).eval()
+    with torch.no_grad():
+        for prm in te.parameters():  # biases / LayerNorm offsets away from their init values
+            if prm.dim() == 1:
+                prm.add_(torch.randn_like(prm) * 0.05)
+    eng = ClipTextEngine(te, "cuda:0")
+    g = torch.Generator(device="cuda:0").manual_seed(2)
+    ids = torch.randint(1, 40000, (2, 77), generator=g, device="cuda:0")
+    ids[0, 9:] = 49407
+    ids[1, 30:] = 49407
+    for which in (-1, -2):
+        with torch.no_grad():
+            want_h, want_p = te.float()(ids, output_hidden_state=which)
+        te.half()
+        got_h, got_p = eng(ids, output_hidden_state=which)
+        assert ((got_h.float() - want_h).abs().max() / want_h.abs().max()).item() < 2e-2
+        assert ((got_p.float() - want_p).abs().max() / want_p.abs().max()).item() < 2e-2
+    assert eng.last_launches > 0

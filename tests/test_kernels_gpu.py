@@ -141,7 +141,8 @@ def test_conv3x3_stride2_implicit(nat, n, h, w, cin, cout, asym):
 
 
 @pytest.mark.parametrize("n,h,w,cin,cout", [(2, 16, 16, 1280, 1280), (2, 32, 32, 640, 640), (1, 64, 64, 512, 512),
-                                            (1, 5, 9, 32, 64), (1, 128, 128, 256, 256)])
+                                            (1, 5, 9, 32, 64), (1, 128, 128, 256, 256), (6, 20, 36, 640, 640),
+                                            (12, 20, 36, 640, 640), (6, 10, 18, 1280, 1280), (3, 40, 24, 320, 320)])
 def test_upsample2x_folded_into_conv(nat, n, h, w, cin, cout):
     """conv3x3(nearest2x(x)) as four phase convs (2x2 taps, pre-summed weights) writing every other output pixel,
     against F.interpolate + F.conv2d."""
@@ -237,6 +238,19 @@ def test_flash_attn(nat, b, heads, sq, skv, d):
     s = (qf @ kf.transpose(-1, -2)) * (d ** -0.5)
     ref = (s.softmax(-1) @ vf).permute(0, 2, 1, 3).reshape(b, sq, heads * d)
     assert _rel_err(out, ref) < 6e-3
+
+
+@pytest.mark.parametrize("b,heads,s,d", [(2, 12, 77, 64), (1, 20, 77, 64), (3, 8, 128, 40), (2, 4, 45, 80)])
+def test_flash_attn_causal(nat, b, heads, s, d):
+    """Causal self-attention of the CLIP text encoder (one query tile) against SDPA(is_causal=True)."""
+    torch.manual_seed(17)
+    qkv = torch.randn(b, s, 3, heads, d, device="cuda", dtype=torch.float16)
+    out = torch.zeros(b, s, heads * d, device="cuda", dtype=torch.float16)
+    nat.flash_attn(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], out, batch=b, heads=heads, seq_q=s, seq_kv=s, head_dim=d,
+                   causal=True)
+    q, k, v = (qkv[:, :, i].float().transpose(1, 2) for i in range(3))
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(b, s, heads * d)
+    assert _rel_err(out, ref) < 5e-3
 
 
 def test_flash_attn_fused_qkv_layout(nat):
