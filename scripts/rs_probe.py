@@ -44,6 +44,15 @@ def timed(fn, iters=30):
     return e0.elapsed_time(e1) / iters * 1e3
 
 
+# all-gather GEMM, same local-only arrangement (every "peer" is this GPU's gathered buffer, epoch 0)
+k_ag, n_ag = 640, 2560
+gathered = torch.randn(W * m_local, k_ag, device=dev, dtype=torch.float16)
+w_ag = torch.randn(n_ag, k_ag, device=dev, dtype=torch.float16) * k_ag ** -0.5
+out_ag = torch.empty(W * m_local, n_ag, device=dev, dtype=torch.float16)
+flags_ag = torch.zeros(4096, dtype=torch.int32, device=dev)
+pf_ag = nat.make_peers(W, 0, 0, [gathered.data_ptr()] * W, [flags_ag.data_ptr()] * W)
+t_ag = timed(lambda: nat.igemm_allgather(w_ag, out_ag, pf_ag, m_local=m_local, k=k_ag))
+print("fused_ag_local %.1f us" % t_ag, "| plain gemm %.1f us" % timed(lambda: nat.linear(gathered, w_ag, out=out_ag)))
 print("SYMM", mode, "SW_FUSED_DBG", os.environ.get("SW_FUSED_DBG", "0"), "SW_PDL", os.environ.get("SW_PDL", "1"),
       "fused_rs_local %.1f us" % timed(lambda: nat.igemm_reducescatter(x, w, pf, out, m_local=m_local, ldc=n2)),
       "| plain gemm %.1f us" % timed(lambda: nat.linear(x, w, out=part)),
