@@ -191,3 +191,18 @@ def test_clip_text_engine_matches_module(cfg):
         assert ((got_h.float() - want_h).abs().max() / want_h.abs().max()).item() < 2e-2
         assert ((got_p.float() - want_p).abs().max() / want_p.abs().max()).item() < 2e-2
     assert eng.last_launches > 0
+
+
+def test_controlnet_768_batch2_engine_matches_torch():
+    """BASELINE config 4 at its real width (SD1.5 UNet + ControlNet, 768x768) with a batch of 2: the engine plan
+    (ControlNet encoder, residual adds fused into the zero convs, UNet) against the eager modules."""
+    from PIL import Image
+
+    from chiaswarm_b200.diffusion.pipelines import _init_module
+    from chiaswarm_b200.models import configs
+    from chiaswarm_b200.models.controlnet import ControlNetModel
+
+    cn = _init_module(ControlNetModel(**configs.get_controlnet("controlnet-sd15")), 9)
+    ref, eng = _pipes("sd15", controlnet=cn, family="sd_controlnet")
+    img = Image.radial_gradient("L").resize((768, 768)).convert("RGB")
+    _compare(ref, eng, 2, 5e-2, image=img, num_images_per_prompt=2)

@@ -64,6 +64,45 @@ def test_linear_split_k(nat, m, n, k):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("m,n,k,act,res", [(8192, 2560, 320, "geglu", False), (2048, 640, 640, "none", True), (512, 1280, 1280, "silu", False),
+                                           (300, 960, 320, "none", False), (8192, 320, 1280, "none", True)])
+def test_linear_persistent_kernel(nat, m, n, k, act, res):
+    """persist=2: persistent CTAs with two TMEM accumulators (the producer runs into the next tile while the epilogue
+    drains the previous one), asked for directly instead of through the tuning table."""
+    from chiaswarm_b200.ops.packing import interleave_geglu
+
+    torch.manual_seed(21)
+    x = torch.randn(m, k, device="cuda", dtype=torch.float16)
+    w = torch.randn(n, k, device="cuda", dtype=torch.float16) * (k ** -0.5)
+    b = torch.randn(n, device="cuda", dtype=torch.float16)
+    r = torch.randn(m, n, device="cuda", dtype=torch.float16) if res else None
+    y = x.float() @ w.float().t() + b.float()
+    if act == "geglu":
+        wi, bi = interleave_geglu(w, b, 64)
+        out = nat.linear(x, wi, bias=bi, act=nat.ACT_GEGLU, tile_n=128, persist=2)
+        ref = y[:, :n // 2] * F.gelu(y[:, n // 2:])
+    else:
+        out = nat.linear(x, w, bias=b, residual=r, act=nat.ACT_SILU if act == "silu" else nat.ACT_NONE, tile_n=128, cta_pair=1,
+                         persist=2)
+        ref = (F.silu(y) if act == "silu" else y) + (r.float() if res else 0)
+    assert _rel_err(out, ref) < 5e-3
+
+
+@pytest.mark.parametrize("m,n,k", [(512, 1280, 1280), (128, 1280, 1280), (2048, 640, 2560), (300, 320, 1280)])
+def test_linear_cluster_split_k(nat, m, n, k):
+    """cluster_k=2: K split over a cluster of two CTAs, the halves of the accumulator exchanged through distributed
+    shared memory behind one cluster barrier (no scratch, no global round trip)."""
+    torch.manual_seed(22)
+    x = torch.randn(m, k, device="cuda", dtype=torch.float16)
+    w = torch.randn(n, k, device="cuda", dtype=torch.float16) * (k ** -0.5)
+    b = torch.randn(n, device="cuda", dtype=torch.float16)
+    r = torch.randn(m, n, device="cuda", dtype=torch.float16)
+    out = nat.linear(x, w, bias=b, residual=r, tile_n=128, cta_pair=1, cluster_k=2)
+    ref = x.float() @ w.float().t() + b.float() + r.float()
+    assert _rel_err(out, ref) < 4e-3
+    assert torch.equal(out, nat.linear(x, w, bias=b, residual=r, tile_n=128, cta_pair=1, cluster_k=2))  # deterministic
+
+
 def test_conv_split_k(nat):
     from chiaswarm_b200.ops.packing import pack_conv_weight
 
