@@ -303,15 +303,21 @@ class StableDiffusionPipeline:
         if mode == "sd_inpaint" and mask_image is None:
             raise ValueError("inpainting needs a mask image")
 
+        # input images are fitted to a size every UNet level can halve (the reference forwards odd sizes to
+        # diffusers, which carries an explicit upsample size through the up path; a 910-wide video frame would
+        # otherwise break the skip concatenation)
+        fit = vae_scale * 2 ** (len(self.unet.config["block_out_channels"]) - 1)
         image_list = None  # a list of equally sized input images: one per batch element (video frames)
         if isinstance(image, (list, tuple)):
-            image_list = [_fit_multiple(im, vae_scale) for im in image]
+            image_list = [_fit_multiple(im, fit) for im in image]
             if len(image_list) != batch or len({im.size for im in image_list}) != 1:
                 raise ValueError("a list of input images needs one image per prompt, all of the same size")
             image = image_list[0]
         if image is not None:
-            image = _fit_multiple(image, vae_scale)
+            image = _fit_multiple(image, fit)
             width, height = image.size
+            if mask_image is not None and mask_image.size != image.size:
+                mask_image = mask_image.resize(image.size)
         sample = self.unet.config.get("sample_size", 64)
         height = int(height or sample * vae_scale)
         width = int(width or sample * vae_scale)

@@ -74,6 +74,7 @@ def _pipe(cls, unet, vae, text, sched=None, **extra):
 
 ARCHITECTURES = {
     "tiny-sd": _pipe("StableDiffusionPipeline", _TINY_UNET, _TINY_VAE, _TINY_CLIP),
+    "tiny-pix2pix": _pipe("StableDiffusionInstructPix2PixPipeline", dict(_TINY_UNET, in_channels=8), _TINY_VAE, _TINY_CLIP),
     "sd15": _pipe("StableDiffusionPipeline", _SD15_UNET, _SD_VAE, _CLIP_L),
     "sd15-inpaint": _pipe("StableDiffusionInpaintPipeline", dict(_SD15_UNET, in_channels=9), _SD_VAE, _CLIP_L),
     "instruct-pix2pix": _pipe("StableDiffusionInstructPix2PixPipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
@@ -96,6 +97,7 @@ _NAME_RULES = [
     ("tiny-t2v", "tiny-t2v"), ("tiny-text-to-video", "tiny-t2v"),
     ("tiny-stable-diffusion", "tiny-sd"), ("tiny-sd", "tiny-sd"),
     ("controlnet-tiny", "tiny-sd"),
+    ("tiny-pix2pix", "tiny-pix2pix"),
     ("instruct-pix2pix", "instruct-pix2pix"),
     ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
     ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),

@@ -26,8 +26,10 @@ from ..parallel.context import is_leader, job_gang
 from ..registry import resolve
 from ..utils.weight_cache import pipeline_cache
 
+import os
+
 MAX_FRAMES = 100
-FRAME_BATCH = 8  # frames per denoising run (one CFG x3 batch of 24 UNet samples at 512 px)
+FRAME_BATCH = int(os.environ.get("SDAAS_FRAME_BATCH", "8"))  # frames per denoising run (CFG x3 -> 24 UNet samples at 512 px)
 
 
 def model_video_callback(device_identifier, model_name, **kwargs):

@@ -121,6 +121,51 @@ def test_gang_worker_serves_a_fake_hive(gang_env):
     asyncio.run(main())
 
 
+def test_vid2vid_frames_scatter_over_a_gang(gang_env, tmp_path, monkeypatch):
+    """Frame-level parallelism: the chunks of a video-to-video job are dealt out over the
+    ranks of the leased gang and gathered in order; the video equals the single-rank one frame for frame."""
+    import base64
+
+    import cv2
+
+    from chiaswarm_b200.generator import synchronous_do_work_function
+    from chiaswarm_b200.gpu.device import Device
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+    from tests.test_workflows_cpu import _tiny_video
+
+    env = dict(gang_env, SDAAS_FRAME_BATCH="1", SDAAS_LOCAL_INPUTS="1", SDAAS_LOCAL_INPUT_ROOT=str(tmp_path))
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    from chiaswarm_b200.video import pix2pix
+
+    monkeypatch.setattr(pix2pix, "FRAME_BATCH", 1)
+    job = {"id": "v2v", "workflow": "vid2vid", "model_name": "tiny-pix2pix", "prompt": "night", "num_inference_steps": 1,
+           "video_uri": _tiny_video(tmp_path / "in.mp4", frames=3), "seed": 8}
+
+    def frames_of(result, name):
+        assert "error" not in result["pipeline_config"], result["pipeline_config"]
+        path = tmp_path / name
+        path.write_bytes(base64.b64decode(result["artifacts"]["primary"]["blob"]))
+        cap, out = cv2.VideoCapture(str(path)), []
+        while True:
+            ok, f = cap.read()
+            if not ok:
+                break
+            out.append(f.astype(np.float32))
+        return out
+
+    ref = frames_of(synchronous_do_work_function(dict(job), Device("cpu")), "ref.mp4")
+    sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2), use_cuda=False, env=env, job_timeout_s=600)
+    sched.start()
+    try:
+        got = frames_of(sched.submit(job), "gang.mp4")
+        assert sched.leases_by_size == {2: 1}
+    finally:
+        sched.stop()
+    assert len(ref) == len(got) == 3
+    assert max(float(np.abs(a - b).max()) for a, b in zip(ref, got)) <= 2.0
+
+
 def _dying_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
     """Stand-in rank body: rank 1 exits in the middle of its first job (no torch needed)."""
     result_q.put(("ready", rank, None))

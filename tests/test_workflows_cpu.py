@@ -122,3 +122,64 @@ def test_controlnet_preprocessors_all_types_produce_rgb():
     assert preprocess_image(img, {"type": "canny", "preprocess": False}) is img
     with pytest.raises(Exception, match="Unknown controlnet type"):
         preprocess_image(img, {"type": "nope", "preprocess": True})
+
+
+def _tiny_video(path, frames=11, size=(64, 48), fps=8.0):
+    import cv2
+
+    w = cv2.VideoWriter(str(path), cv2.VideoWriter_fourcc(*"mp4v"), fps, size)
+    assert w.isOpened()
+    for i in range(frames):
+        img = np.zeros((size[1], size[0], 3), np.uint8)
+        img[:, : 4 + 5 * i] = (40 + 15 * i, 200 - 10 * i, 90)
+        w.write(img)
+    w.release()
+    return "file://" + str(path)
+
+
+def _video_frames(artifact, tmp_path):
+    import cv2
+
+    out = tmp_path / "result.mp4"
+    out.write_bytes(base64.b64decode(artifact["blob"]))
+    cap = cv2.VideoCapture(str(out))
+    frames = []
+    while True:
+        ok, f = cap.read()
+        if not ok:
+            break
+        frames.append(f)
+    cap.release()
+    return frames
+
+
+def test_vid2vid_job_batches_frames_and_returns_a_video(tmp_path, monkeypatch):
+    """Video-to-video (instruct-pix2pix per frame, swarm/video/pix2pix.py): 5 frames go through the pipeline in
+    chunks of FRAME_BATCH instead of one call per frame, and every frame comes back (fitted into 512 x 512)."""
+    from chiaswarm_b200.video import pix2pix
+
+    calls = []
+    real = pix2pix.img2img
+
+    def spy(pipeline, prompt, tg, ig, image, *a, **k):
+        calls.append(len(image) if isinstance(image, (list, tuple)) else 1)
+        return real(pipeline, prompt, tg, ig, image, *a, **k)
+
+    monkeypatch.setattr(pix2pix, "img2img", spy)
+    monkeypatch.setattr(pix2pix, "FRAME_BATCH", 3)
+    uri = _tiny_video(tmp_path / "in.mp4", frames=5)
+    r = _run({"id": "vv", "workflow": "vid2vid", "model_name": "tiny-pix2pix", "prompt": "make it night", "video_uri": uri,
+              "num_inference_steps": 2, "seed": 4})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert calls == [3, 2]  # five frames in two denoising runs, not five
+    art = r["artifacts"]["primary"]
+    assert art["content_type"] == "video/mp4"
+    frames = _video_frames(art, tmp_path)
+    assert len(frames) == 5 and max(frames[0].shape[:2]) <= 512 and min(frames[0].shape[:2]) >= 256
+    assert r["pipeline_config"]["cost"] == 512 * 512 * 2 * 5
+
+
+def test_vid2vid_guards(tmp_path):
+    r = _run({"id": "vg", "workflow": "vid2vid", "model_name": "tiny-pix2pix", "prompt": "x",
+              "video_uri": png_data_uri((32, 32))})
+    assert "does not appear to be an video" in r["pipeline_config"]["error"]
