@@ -6,7 +6,6 @@ the IF block variant (`resnet_time_scale_shift="scale_shift"`, learned variance)
 from __future__ import annotations
 
 import torch
-from PIL import Image
 
 from ..utils import checkpoints
 
@@ -36,13 +35,10 @@ def run_if_cascade(device, stage1, stage2, stage3, prompt, negative_prompt=None,
                     generator=generator, low_res=img)
     from .pipelines import StableDiffusionPipeline, tensor_to_pil
 
-    try:
-        up = StableDiffusionPipeline.from_pretrained(stage3, torch_dtype=torch.float16, device=device,
-                                                     family="sd_img2img")
-        pil = tensor_to_pil(img)
-        big = [p.resize((p.width * 4, p.height * 4), Image.Resampling.LANCZOS) for p in pil]
-        out = up(prompt=prompt, image=big[0], strength=0.25, num_inference_steps=30, generator=generator)
-        return out.images, any(out.nsfw_content_detected or [False])
-    except ValueError:
-        pil = tensor_to_pil(img)
-        return [p.resize((p.width * 4, p.height * 4), Image.Resampling.LANCZOS) for p in pil], False
+    # stage III: the SD x4 upscaler proper (noise level 100 as in the reference, diffusers' defaults for the rest):
+    # the 256 px tensor goes in as the noised conditioning channels, not through an img2img approximation
+    up = StableDiffusionPipeline.from_pretrained(stage3, torch_dtype=torch.float16, device=device, family="sd_upscale")
+    up.set_scheduler("ddim", False)
+    out = up(prompt=prompt, negative_prompt=negative_prompt, image=img.to(torch.float16), noise_level=100,
+             num_inference_steps=75, guidance_scale=9.0, generator=generator)
+    return out.images, any(out.nsfw_content_detected or [False])

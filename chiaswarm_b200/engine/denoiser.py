@@ -209,6 +209,8 @@ class SM100Denoiser:
 
         unet = self.pipe.unet
         cfg = unet.config
+        if "class_labels" in added:  # x4 upscaler: the noise level of the low-resolution input, as a class embedding
+            return unet.class_embedding(added["class_labels"]).to(torch.float16)
         tids = added["time_ids"]
         tid_emb = timestep_embedding(tids.flatten(), cfg["addition_time_embed_dim"]).reshape(tids.shape[0], -1)
         vec = torch.cat([added["text_embeds"].float(), tid_emb], dim=-1).to(self.pipe.dtype)

@@ -85,6 +85,22 @@ ARCHITECTURES = {
                   text_encoder_2=_CLIP_BIGG),
     "zeroscope": _pipe("TextToVideoSDPipeline", _ZEROSCOPE_UNET3D, _SD_VAE, _CLIP_H),
     "tiny-t2v": _pipe("TextToVideoSDPipeline", _TINY_UNET3D, _TINY_VAE, _TINY_CLIP),
+    # stabilityai/stable-diffusion-x4-upscaler: 7 input channels (4 latent + the noised low-resolution RGB image), the
+    # noise level enters as a class label, first three levels attend to the text only, VAE with a 4x factor
+    "sd-x4-upscaler": _pipe("StableDiffusionUpscalePipeline",
+                            dict(in_channels=7, out_channels=4, block_out_channels=(256, 512, 512, 1024), layers_per_block=2,
+                                 down_block_types=("DownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D", "CrossAttnDownBlock2D"),
+                                 up_block_types=("CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "CrossAttnUpBlock2D", "UpBlock2D"),
+                                 attention_head_dim=8, cross_attention_dim=1024, norm_num_groups=32, norm_eps=1e-5,
+                                 use_linear_projection=True, only_cross_attention=(True, True, True, False),
+                                 num_class_embeds=1000, sample_size=128),
+                            dict(_SD_VAE, block_out_channels=(128, 256, 512), scaling_factor=0.08333), _CLIP_H,
+                            dict(_SD_SCHED, beta_start=0.0001, beta_end=0.02, prediction_type="v_prediction")),
+    "tiny-x4": _pipe("StableDiffusionUpscalePipeline",
+                     dict(_TINY_UNET, in_channels=7, use_linear_projection=True, only_cross_attention=(False, True),
+                          num_class_embeds=1000),
+                     dict(_TINY_VAE, scaling_factor=0.08333), _TINY_CLIP,
+                     dict(_SD_SCHED, beta_start=0.0001, beta_end=0.02, prediction_type="v_prediction")),
     "sd-x2-latent-upscaler": _pipe("StableDiffusionLatentUpscalePipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
 }
 
@@ -102,6 +118,7 @@ _NAME_RULES = [
     ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
     ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
     ("sd-x2-latent-upscaler", "sd-x2-latent-upscaler"),
+    ("tiny-x4", "tiny-x4"), ("x4-upscaler", "sd-x4-upscaler"),
     ("stable-diffusion-2-1-base", "sd21-base"), ("stable-diffusion-2-base", "sd21-base"),
     ("stable-diffusion-2", "sd21"),
     ("zeroscope", "zeroscope"), ("text-to-video", "zeroscope"), ("modelscope", "zeroscope"),

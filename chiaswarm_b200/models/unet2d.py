@@ -135,7 +135,8 @@ class BasicTransformerBlock(nn.Module):
 
 
 class Transformer2DModel(nn.Module):
-    def __init__(self, channels, heads, dim_head, depth, cross_dim, groups=32, use_linear_projection=False):
+    def __init__(self, channels, heads, dim_head, depth, cross_dim, groups=32, use_linear_projection=False,
+                 only_cross_attention=False):
         super().__init__()
         inner = heads * dim_head
         self.use_linear_projection = use_linear_projection
@@ -147,7 +148,7 @@ class Transformer2DModel(nn.Module):
             self.proj_in = nn.Conv2d(channels, inner, 1)
             self.proj_out = nn.Conv2d(inner, channels, 1)
         self.transformer_blocks = nn.ModuleList(
-            [BasicTransformerBlock(inner, heads, dim_head, cross_dim) for _ in range(depth)])
+            [BasicTransformerBlock(inner, heads, dim_head, cross_dim, only_cross_attention) for _ in range(depth)])
 
     def forward(self, x, context):
         b, c, h, w = x.shape
@@ -195,12 +196,12 @@ class DownBlock(nn.Module):
     """DownBlock2D / CrossAttnDownBlock2D."""
 
     def __init__(self, cin, cout, temb_dim, layers, groups, eps, has_attn, heads, dim_head, depth, cross_dim,
-                 add_downsample, use_linear_projection):
+                 add_downsample, use_linear_projection, only_cross_attention=False):
         super().__init__()
         self.resnets = nn.ModuleList(
             [ResnetBlock2D(cin if i == 0 else cout, cout, temb_dim, groups, eps) for i in range(layers)])
         self.attentions = nn.ModuleList(
-            [Transformer2DModel(cout, heads, dim_head, depth, cross_dim, groups, use_linear_projection)
+            [Transformer2DModel(cout, heads, dim_head, depth, cross_dim, groups, use_linear_projection, only_cross_attention)
              for _ in range(layers)]) if has_attn else None
         self.downsamplers = nn.ModuleList([Downsample2D(cout)]) if add_downsample else None
 
@@ -219,11 +220,12 @@ class DownBlock(nn.Module):
 
 class MidBlock(nn.Module):
     def __init__(self, ch, temb_dim, groups, eps, heads, dim_head, depth, cross_dim, use_linear_projection,
-                 has_attn=True):
+                 has_attn=True, only_cross_attention=False):
         super().__init__()
         self.resnets = nn.ModuleList([ResnetBlock2D(ch, ch, temb_dim, groups, eps) for _ in range(2)])
         self.attentions = nn.ModuleList(
-            [Transformer2DModel(ch, heads, dim_head, depth, cross_dim, groups, use_linear_projection)]) if has_attn else None
+            [Transformer2DModel(ch, heads, dim_head, depth, cross_dim, groups, use_linear_projection,
+                                only_cross_attention)]) if has_attn else None
 
     def forward(self, x, temb, context):
         x = self.resnets[0](x, temb)
@@ -236,7 +238,7 @@ class UpBlock(nn.Module):
     """UpBlock2D / CrossAttnUpBlock2D."""
 
     def __init__(self, cin, cout, prev_out, temb_dim, layers, groups, eps, has_attn, heads, dim_head, depth,
-                 cross_dim, add_upsample, use_linear_projection):
+                 cross_dim, add_upsample, use_linear_projection, only_cross_attention=False):
         super().__init__()
         resnets = []
         for i in range(layers):
@@ -245,7 +247,7 @@ class UpBlock(nn.Module):
             resnets.append(ResnetBlock2D(rin + skip, cout, temb_dim, groups, eps))
         self.resnets = nn.ModuleList(resnets)
         self.attentions = nn.ModuleList(
-            [Transformer2DModel(cout, heads, dim_head, depth, cross_dim, groups, use_linear_projection)
+            [Transformer2DModel(cout, heads, dim_head, depth, cross_dim, groups, use_linear_projection, only_cross_attention)
              for _ in range(layers)]) if has_attn else None
         self.upsamplers = nn.ModuleList([Upsample2D(cout)]) if add_upsample else None
 
@@ -277,6 +279,8 @@ class UNet2DConditionModel(nn.Module):
         # `num_attention_heads` wins when present.
         heads_cfg = c.get("num_attention_heads") or c["attention_head_dim"]
         heads = _as_list(heads_cfg, n)
+        # per-level flag: "self"-attention of these blocks attends to the text instead (SD x4 upscaler)
+        oca = [bool(v) for v in _as_list(c.get("only_cross_attention", False), n)]
 
         self.conv_in = nn.Conv2d(c["in_channels"], boc[0], 3, padding=1)
         self.time_embedding = TimestepEmbedding(boc[0], temb_dim)
@@ -294,18 +298,19 @@ class UNet2DConditionModel(nn.Module):
         for i, typ in enumerate(c["down_block_types"]):
             cin, ch = ch, boc[i]
             self.down_blocks.append(DownBlock(cin, ch, temb_dim, layers[i], groups, eps, "CrossAttn" in typ,
-                                              heads[i], ch // heads[i], depth[i], cross, i < n - 1, ulp))
+                                              heads[i], ch // heads[i], depth[i], cross, i < n - 1, ulp, oca[i]))
         self.mid_block = MidBlock(boc[-1], temb_dim, groups, eps, heads[-1], boc[-1] // heads[-1], depth[-1], cross,
-                                  ulp, has_attn=c.get("mid_block_type", "UNetMidBlock2DCrossAttn") is not None)
+                                  ulp, has_attn=c.get("mid_block_type", "UNetMidBlock2DCrossAttn") is not None,
+                                  only_cross_attention=c.get("mid_block_only_cross_attention", oca[-1]) or False)
         self.up_blocks = nn.ModuleList()
         rev = boc[::-1]
-        rheads, rdepth, rlayers = heads[::-1], depth[::-1], layers[::-1]
+        rheads, rdepth, rlayers, roca = heads[::-1], depth[::-1], layers[::-1], oca[::-1]
         ch = rev[0]
         for i, typ in enumerate(c["up_block_types"]):
             prev, ch = ch, rev[i]
             cin = rev[min(i + 1, n - 1)]
             self.up_blocks.append(UpBlock(cin, ch, prev, temb_dim, rlayers[i] + 1, groups, eps, "CrossAttn" in typ,
-                                          rheads[i], ch // rheads[i], rdepth[i], cross, i < n - 1, ulp))
+                                          rheads[i], ch // rheads[i], rdepth[i], cross, i < n - 1, ulp, roca[i]))
         self.conv_norm_out = nn.GroupNorm(groups, boc[0], eps=eps)
         self.conv_out = nn.Conv2d(boc[0], c["out_channels"], 3, padding=1)
 
@@ -316,12 +321,14 @@ class UNet2DConditionModel(nn.Module):
         temb = timestep_embedding(t, c["block_out_channels"][0], c.get("flip_sin_to_cos", True),
                                   c.get("freq_shift", 0)).to(dtype)
         emb = self.time_embedding(temb)
-        if self.add_embedding is not None and added_cond is not None:
+        if self.add_embedding is not None and added_cond is not None and "time_ids" in added_cond:
             tids = added_cond["time_ids"]
             tid_emb = timestep_embedding(tids.flatten(), c["addition_time_embed_dim"], c.get("flip_sin_to_cos", True),
                                          c.get("freq_shift", 0)).reshape(tids.shape[0], -1)
             add = torch.cat([added_cond["text_embeds"].float(), tid_emb], dim=-1).to(dtype)
             emb = emb + self.add_embedding(add)
+        if class_labels is None and added_cond is not None:
+            class_labels = added_cond.get("class_labels")
         if self.class_embedding is not None and class_labels is not None:
             if isinstance(self.class_embedding, TimestepEmbedding):
                 class_labels = timestep_embedding(class_labels, c["block_out_channels"][0]).to(dtype)

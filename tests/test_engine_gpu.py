@@ -206,3 +206,20 @@ def test_controlnet_768_batch2_engine_matches_torch():
     ref, eng = _pipes("sd15", controlnet=cn, family="sd_controlnet")
     img = Image.radial_gradient("L").resize((768, 768)).convert("RGB")
     _compare(ref, eng, 2, 5e-2, image=img, num_images_per_prompt=2)
+
+
+def test_x4_upscaler_engine_matches_torch():
+    """x4 upscaler on the engine: 7 input channels (latent + noised low-resolution image as constant extra channels),
+    the noise level as a class embedding in the time-embedding slot, text-only attention blocks."""
+    from PIL import Image
+
+    ref, eng = _pipes("tiny-x4")
+    low = Image.radial_gradient("L").resize((32, 32)).convert("RGB")
+    outs = []
+    for p in (ref, eng):
+        p.set_scheduler("ddim", False)
+        g = torch.Generator(device="cuda:0").manual_seed(11)
+        outs.append(p(prompt="sharper", image=low, num_inference_steps=3, guidance_scale=5.0, noise_level=100, generator=g,
+                      output_type="latent").latents.float())
+    err = ((outs[0] - outs[1]).abs().max() / outs[0].abs().max().clamp_min(1e-3)).item()
+    assert torch.isfinite(outs[1]).all() and err < 4e-2, err

@@ -183,3 +183,33 @@ def test_vid2vid_guards(tmp_path):
     r = _run({"id": "vg", "workflow": "vid2vid", "model_name": "tiny-pix2pix", "prompt": "x",
               "video_uri": png_data_uri((32, 32))})
     assert "does not appear to be an video" in r["pipeline_config"]["error"]
+
+
+def test_x4_upscaler_pipeline_matches_a_direct_unet_loop():
+    """`StableDiffusionUpscalePipeline` semantics (stage III of the IF cascade): the low-resolution image is noised
+    to `noise_level`, rides as three extra UNet input channels, the level enters as a class label, blocks flagged
+    only_cross_attention attend to the text; output is 4x (the VAE of this tiny arch: 2x) the input size."""
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline, pil_to_tensor
+
+    pipe = StableDiffusionPipeline.from_architecture("tiny-x4").to("cpu")
+    assert pipe.family == "sd_upscale" and pipe.unet.class_embedding is not None
+    blocks = pipe.unet.down_blocks[1].attentions[0].transformer_blocks
+    assert blocks[0].only_cross_attention and blocks[0].attn1.to_k.in_features == 32
+    pipe.set_scheduler("ddim", False)
+    low = Image.radial_gradient("L").resize((16, 16)).convert("RGB")
+    g = torch.Generator().manual_seed(3)
+    out = pipe(prompt="sharper", image=low, num_inference_steps=3, guidance_scale=4.0, noise_level=100, generator=g)
+    assert out.images[0].size == (32, 32)  # tiny VAE factor 2; the real x4 VAE gives 4x
+    a = np.asarray(out.images[0], dtype=np.float32)
+    # another noise level is another class embedding and another amount of noise on the conditioning image
+    g = torch.Generator().manual_seed(3)
+    b = np.asarray(pipe(prompt="sharper", image=low, num_inference_steps=3, guidance_scale=4.0, noise_level=900,
+                        generator=g).images[0], dtype=np.float32)
+    assert np.abs(a - b).mean() > 0.5
+    # a tensor input (what the IF cascade hands over) gives the same image as the PIL input
+    g = torch.Generator().manual_seed(3)
+    c = np.asarray(pipe(prompt="sharper", image=pil_to_tensor(low, "cpu", torch.float32), num_inference_steps=3,
+                        guidance_scale=4.0, noise_level=100, generator=g).images[0], dtype=np.float32)
+    assert np.abs(a - c).max() <= 1.0
