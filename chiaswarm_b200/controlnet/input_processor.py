@@ -3,8 +3,9 @@
 Dispatch on `controlnet["type"]` exactly as the reference.  canny / tile / pix2pix / shuffle are
 self-contained (OpenCV / PIL / numpy).  The learned annotators (mlsd, depth, normalbae, seg,
 lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers hub models in the
-reference; they are used when importable and locally cached, otherwise a classical CPU
-approximation keeps the job serviceable (documented per type), so no type raises for a missing
+reference; they are used when importable and locally cached; soft edges / scribbles additionally have this
+tree's own HED network (controlnet/annotators.py, loads `lllyasviel/Annotators/ControlNetHED.pth`); otherwise a
+classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
 dependency.  Unknown types raise, as in the reference."""
 from __future__ import annotations
 
@@ -165,6 +166,11 @@ def image_to_softedge(image, scribble=False):
     det = _aux("HEDdetector" if scribble else "PidiNetDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image, scribble=True) if scribble else det(image)
+    from .annotators import load_hed  # this tree's own HED network, when its checkpoint is present locally
+
+    hed = load_hed()
+    if hed is not None:
+        return hed.edges(image, next(hed.parameters()).device, scribble=scribble)
     _, _, mag = _sobel_mag(image)
     if scribble:
         edge = (mag > 0.25).astype(np.uint8) * 255

@@ -213,3 +213,29 @@ def test_x4_upscaler_pipeline_matches_a_direct_unet_loop():
     c = np.asarray(pipe(prompt="sharper", image=pil_to_tensor(low, "cpu", torch.float32), num_inference_steps=3,
                         guidance_scale=4.0, noise_level=100, generator=g).images[0], dtype=np.float32)
     assert np.abs(a - c).max() <= 1.0
+
+
+def test_hed_annotator_loads_the_reference_checkpoint_layout(tmp_path, monkeypatch):
+    """The in-tree HED network has the parameter names of `lllyasviel/Annotators/ControlNetHED.pth`, is picked up from
+    the local model root by the soft-edge / scribble pre-processors, and returns an RGB edge map of the input size."""
+    import torch
+
+    from chiaswarm_b200.controlnet import annotators, input_processor
+
+    net = annotators.HEDNet()
+    names = set(net.state_dict())
+    assert {"norm", "block1.convs.0.weight", "block1.convs.1.bias", "block3.convs.2.weight", "block5.projection.weight"} <= names
+    assert len(names) == 1 + 2 * (2 + 2 + 3 + 3 + 3) + 2 * 5
+    torch.manual_seed(0)
+    root = tmp_path / "models" / "lllyasviel" / "Annotators"
+    root.mkdir(parents=True)
+    torch.save(net.state_dict(), root / "ControlNetHED.pth")
+    monkeypatch.setenv("SDAAS_MODEL_ROOT", str(tmp_path / "models"))
+    annotators._cache.clear()
+    img = Image.radial_gradient("L").resize((96, 64)).convert("RGB")
+    soft = input_processor.preprocess_image(img, {"preprocess": True, "type": "softedge"})
+    scr = input_processor.preprocess_image(img, {"preprocess": True, "type": "scribble"})
+    assert annotators._cache["hed"] is not None  # the learned detector ran, not the Sobel stand-in
+    assert soft.size == img.size and soft.mode == "RGB" and scr.size == img.size
+    assert set(np.unique(np.asarray(scr))) <= {0, 255}
+    annotators._cache.clear()
