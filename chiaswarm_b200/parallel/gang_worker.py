@@ -13,7 +13,7 @@ what leases them.
                              aligned sub-gang {0-1, 2-3, .., 0-3, 4-7, 0-7} created at start-up.  A rank runs
                              `synchronous_do_work_function(job, Device)` with `parallel.context.job_gang()` set; the
                              callbacks then go patch-parallel (one large image), split the batch (ControlNet batch 8),
-                             scatter frames (vid2vid) or row-split the 3-D UNet (txt2vid).  The gang's first rank
+                             scatter frames (vid2vid) or split the clip along the frame axis (txt2vid).  The gang's first rank
                              returns the result.
 
 Failure handling: a job that overruns `job_timeout_s` (utils.tracing.Watchdog) or loses a
@@ -63,7 +63,7 @@ def plan_gang_size(job: dict, settings: Settings, world: int) -> int:
     if workflow in ("stitch", "img2txt", "txt2audio"):
         return 1
     if workflow == "txt2vid":
-        return cap          # rows of every frame split over the gang (engine/patch_engine.py)
+        return cap          # the clip is split along the frame axis over the gang (engine/patch_engine.py)
     if workflow == "vid2vid":
         return cap          # frames are independent: scattered over the gang (video/pix2pix.py)
     if str(job.get("model_name", "")).startswith("DeepFloyd/"):
