@@ -217,12 +217,21 @@ class SM100Denoiser:
         return unet.add_embedding(vec).to(torch.float16)
 
     def _embed_control(self, sg: _StepGraph, control):
+        """ControlNet conditioning embedder (step invariant): one recorded plan per input shape, kept with the engine
+        and re-run per job -- not re-recorded, and no scratch of its own."""
         cp = self.control_plan
         n, _, H, W = control.shape
-        cond = torch.zeros(n, H, W, cp.cond_in_pad, dtype=torch.float16, device=self.device)
+        plans = self.__dict__.setdefault("_cond_plans", {})
+        entry = plans.get((n, H, W))
+        if entry is None:
+            cond = torch.zeros(n, H, W, cp.cond_in_pad, dtype=torch.float16, device=self.device)
+            rec = Recorder(self.device)
+            feat = cp.record_cond_embedding(rec, FM(cond, n, H, W, cp.cond_in_pad))
+            entry = plans[(n, H, W)] = (cond, rec, feat)
+            if len(plans) > 4:
+                plans.pop(next(iter(plans)))
+        cond, rec, feat = entry
         nat.nchw_to_nhwc(control.contiguous(), cond, cp.cond_in_pad)
-        rec = Recorder(self.device)
-        feat = cp.record_cond_embedding(rec, FM(cond, n, H, W, cp.cond_in_pad))
         rec.run()
         sg.control_feat.t.copy_(feat.t)
 

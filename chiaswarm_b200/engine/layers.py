@@ -56,14 +56,23 @@ class Recorder:
 
     patch = None  # PatchContext when the plan runs patch-parallel (engine/patch_engine.py)
 
+    _scratch = {}  # device -> (GroupNorm scratch, split-K scratch): ONE pair per device, shared by every plan
+
     def __init__(self, device):
         self.device = torch.device(device)
         self.ops = []
         self._free = {}
         self.bytes_allocated = 0
-        self.gn_stats = torch.zeros(1 << 20, dtype=torch.float32, device=self.device)  # GroupNorm scratch
-        # split-K scratch (tickets + fp32 partial tiles), zeroed once; shared by every GEMM of the plan
-        self.splitk = torch.zeros((64 << 20) + 16384, dtype=torch.uint8, device=self.device)
+        # GroupNorm scratch and split-K scratch (tickets + fp32 partial tiles, zeroed once, left reusable by the
+        # kernels).  Plans of a device run one after the other on one stream, so they share a single pair instead of
+        # each cached graph (and each ControlNet job's embedder plan) allocating and clearing 68 MiB of its own.
+        key = (self.device.type, self.device.index if self.device.index is not None else torch.cuda.current_device())
+        pair = Recorder._scratch.get(key)
+        if pair is None:
+            pair = Recorder._scratch[key] = (
+                torch.zeros(1 << 20, dtype=torch.float32, device=self.device),
+                torch.zeros((64 << 20) + 16384, dtype=torch.uint8, device=self.device))
+        self.gn_stats, self.splitk = pair
 
     # ---- buffers (explicit liveness: release() makes a buffer reusable by later ops)
     def buf(self, *shape, dtype=torch.float16):

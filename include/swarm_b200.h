@@ -135,7 +135,11 @@ int sw_igemm(const sw_igemm_params* p, void* stream);
  * out[world*m_local, cout] = concat_d(X_d) . wgt^T by TMA-loading every A tile straight from the
  * rank that owns it (NVLink peer mapping) -- no gathered copy exists.  The loader of a remote
  * tile first waits for that rank's epoch flag (raised by sw_peer_signal or a producer kernel).
- * p->a1 is ignored; p->w must equal world*m_local; m_local % 128 == 0. */
+ * p->a1 is ignored; p->w must equal world*m_local; m_local % 128 == 0.
+ * Reuse rule for all peer-visible operands of the fused kernels (activation shards, K / V, staging, gathered
+ * buffers): there is no consumer-done handshake, so a buffer a peer may still be reading must not be rewritten until
+ * a sw_peer_exchange barrier or a flag round trip in the opposite direction has passed -- or alternate two buffers by
+ * epoch parity (what parallel/collectives.py::FusedOps and the GroupNorm slots do). */
 int sw_igemm_ag(const sw_igemm_params* p, const sw_peers* peers, int m_local, void* stream);
 
 /* GEMM fused with reduce-scatter (collective call site 3): every rank multiplies
