@@ -4,9 +4,9 @@ IF stage I (64 px, T5-XXL text) -> IF-II-L (256 px) -> stable-diffusion-x4-upsca
 prompt), nothing is written to the working directory, steps / guidance are honoured, and the NSFW
 flag comes from the pipeline output.
 
-The pixel-space IF UNets use the same ResNet/attention building blocks as the latent UNet
-(`models/unet2d.py`) with class/timestep `resnet_time_scale_shift="scale_shift"` blocks; they and
-T5-XXL (~20 GB) are only runnable from local checkpoints."""
+The pixel-space IF UNets are `models/unet_if.py` (the IF block family, checkpoint-compatible names, strict
+loading); they and T5-XXL (~20 GB) are only runnable from local checkpoints.  `SDAAS_IF_SIZES` ("64,256") sets the
+stage resolutions (tests run the cascade at toy sizes)."""
 from __future__ import annotations
 
 from ..output_processor import OutputProcessor
@@ -20,9 +20,12 @@ def diffusion_if_callback(device_identifier, model_name, **kwargs):
     missing = [m for m in (model_name, STAGE_2, STAGE_3) if checkpoints.locate_checkpoint(m) is None]
     if missing:
         raise ValueError(f"DeepFloyd IF needs local checkpoints; missing: {', '.join(missing)}")
+    import os
+
     from .pipeline_if import run_if_cascade
 
-    images, nsfw = run_if_cascade(device_identifier, model_name, STAGE_2, STAGE_3,
+    sizes = tuple(int(v) for v in os.environ.get("SDAAS_IF_SIZES", "64,256").split(","))
+    images, nsfw = run_if_cascade(device_identifier, model_name, STAGE_2, STAGE_3, sizes=sizes,
                                   prompt=kwargs.get("prompt", ""), negative_prompt=kwargs.get("negative_prompt"),
                                   num_inference_steps=kwargs.get("num_inference_steps"),
                                   guidance_scale=kwargs.get("guidance_scale", 7.0), generator=kwargs.get("generator"))

@@ -1,8 +1,7 @@
 """DeepFloyd-IF cascade (reference: swarm/diffusion/diffusion_func_if.py:16-65).  Stage I and II are
-pixel-space UNets conditioned on T5-XXL, stage III is the SD x4 upscaler.  The stage checkpoints
-(and T5-XXL, ~20 GB) must be present locally; the callback has already verified that.  The T5
-encoder comes from transformers; the denoisers run on this framework's UNet / scheduler code with
-the IF block variant (`resnet_time_scale_shift="scale_shift"`, learned variance) handled here."""
+pixel-space UNets conditioned on T5-XXL (`models/unet_if.py`, sampled by `if_unet.IFStage`), stage III is the
+SD x4 upscaler (`pipelines.py`, mode sd_upscale).  The stage checkpoints (and T5-XXL, ~20 GB) must be present
+locally; the callback has already verified that.  The T5 encoder and its tokenizer come from transformers."""
 from __future__ import annotations
 
 import torch
@@ -11,28 +10,32 @@ from ..utils import checkpoints
 
 
 def run_if_cascade(device, stage1, stage2, stage3, prompt, negative_prompt=None, num_inference_steps=None,
-                   guidance_scale=7.0, generator=None):
-    from transformers import T5EncoderModel, T5Tokenizer
+                   guidance_scale=7.0, generator=None, sizes=(64, 256)):
+    from transformers import AutoTokenizer, T5EncoderModel
 
     root1 = checkpoints.locate_checkpoint(stage1)
-    tok = T5Tokenizer.from_pretrained(str(root1 / "tokenizer"))
-    enc = T5EncoderModel.from_pretrained(str(root1 / "text_encoder"), torch_dtype=torch.float16).to(device)
+    tok = AutoTokenizer.from_pretrained(str(root1 / "tokenizer"))
+    on_gpu = str(device).startswith("cuda")
+    enc = T5EncoderModel.from_pretrained(str(root1 / "text_encoder"), torch_dtype=torch.float16 if on_gpu else torch.float32)
+    enc = enc.to(device).eval()
 
     def embed(text):
         ids = tok(text, max_length=77, padding="max_length", truncation=True, return_tensors="pt").to(device)
         with torch.no_grad():
-            return enc(**ids).last_hidden_state
+            return enc(input_ids=ids["input_ids"], attention_mask=ids["attention_mask"]).last_hidden_state
 
     cond, unc = embed(prompt), embed(negative_prompt or "")
     del enc
     from .if_unet import IFStage
 
     s1 = IFStage.from_checkpoint(checkpoints.locate_checkpoint(stage1), device)
-    img = s1.sample(cond, unc, size=64, steps=num_inference_steps or 100, guidance_scale=guidance_scale,
+    img = s1.sample(cond, unc, size=sizes[0], steps=num_inference_steps or 100, guidance_scale=guidance_scale,
                     generator=generator)
+    del s1
     s2 = IFStage.from_checkpoint(checkpoints.locate_checkpoint(stage2), device)
-    img = s2.sample(cond, unc, size=256, steps=num_inference_steps or 50, guidance_scale=min(guidance_scale, 4.0),
-                    generator=generator, low_res=img)
+    img = s2.sample(cond, unc, size=sizes[1], steps=num_inference_steps or 50, guidance_scale=min(guidance_scale, 4.0),
+                    generator=generator, low_res=img, noise_level=250)
+    del s2
     from .pipelines import StableDiffusionPipeline, tensor_to_pil
 
     # stage III: the SD x4 upscaler proper (noise level 100 as in the reference, diffusers' defaults for the rest):
@@ -40,5 +43,5 @@ def run_if_cascade(device, stage1, stage2, stage3, prompt, negative_prompt=None,
     up = StableDiffusionPipeline.from_pretrained(stage3, torch_dtype=torch.float16, device=device, family="sd_upscale")
     up.set_scheduler("ddim", False)
     out = up(prompt=prompt, negative_prompt=negative_prompt, image=img.to(torch.float16), noise_level=100,
-             num_inference_steps=75, guidance_scale=9.0, generator=generator)
+             num_inference_steps=num_inference_steps or 75, guidance_scale=9.0, generator=generator)
     return out.images, any(out.nsfw_content_detected or [False])
