@@ -166,6 +166,66 @@ def test_vid2vid_frames_scatter_over_a_gang(gang_env, tmp_path, monkeypatch):
     assert max(float(np.abs(a - b).max()) for a, b in zip(ref, got)) <= 2.0
 
 
+def test_txt2vid_on_a_gang_scatters_the_decode(gang_env):
+    """Text-to-video on a leased gang (eager back end here: denoising is replicated, the VAE decode of the frames is
+    dealt out over the ranks and all-gathered; on GPUs the engine also splits the denoising along the frame axis):
+    the clip equals the single-rank one."""
+    import base64
+
+    from chiaswarm_b200.generator import synchronous_do_work_function
+    from chiaswarm_b200.gpu.device import Device
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    job = {"id": "t2v", "workflow": "txt2vid", "model_name": "tiny-t2v", "prompt": "waves", "num_frames": 5, "height": 32,
+           "width": 32, "num_inference_steps": 2, "seed": 9}
+    import os
+
+    os.environ.update(gang_env)
+    ref = synchronous_do_work_function(dict(job), Device("cpu"))
+    sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2), use_cuda=False, env=gang_env, job_timeout_s=300)
+    sched.start()
+    try:
+        got = sched.submit(job)
+        assert sched.leases_by_size == {2: 1}
+    finally:
+        sched.stop()
+    import cv2
+
+    def frames_of(r, name, tmp=os.environ["SDAAS_ROOT"]):
+        assert "error" not in r["pipeline_config"], r["pipeline_config"]
+        path = os.path.join(tmp, name)
+        with open(path, "wb") as fh:
+            fh.write(base64.b64decode(r["artifacts"]["primary"]["blob"]))
+        cap, out = cv2.VideoCapture(path), []
+        while True:
+            ok, f = cap.read()
+            if not ok:
+                break
+            out.append(f.astype(np.float32))
+        return out
+
+    a, b = frames_of(ref, "ref.mp4"), frames_of(got, "gang.mp4")
+    assert len(a) == len(b) == 5
+    # (decode batches of 3 + 2 frames instead of 5: fp rounding, amplified a little by the lossy video codec)
+    assert max(float(np.abs(x - y).mean()) for x, y in zip(a, b)) <= 1.0
+    assert max(float(np.abs(x - y).max()) for x, y in zip(a, b)) <= 16.0
+
+
+def test_launcher_picks_the_gang_server(monkeypatch):
+    """`settings.parallel_mode` / `gang_size` decide between the per-GPU supervisor and the gang server."""
+    from chiaswarm_b200.parallel import gang_worker, launcher
+
+    calls = []
+    monkeypatch.setattr(gang_worker, "serve", lambda settings, world: calls.append(("gang", world, settings.gang_size)))
+    monkeypatch.setattr(launcher.Supervisor, "run", lambda self, max_seconds=None: calls.append(("dp", len(self.gpus))))
+    monkeypatch.setenv("SDAAS_PARALLEL_MODE", "gang")
+    monkeypatch.setenv("SDAAS_GANG_SIZE", "4")
+    assert launcher.main(["--gpus", "0,1,2,3"]) == 0
+    monkeypatch.setenv("SDAAS_PARALLEL_MODE", "dp")
+    assert launcher.main(["--gpus", "0,1"]) == 0
+    assert calls == [("gang", 4, 4), ("dp", 2)]
+
+
 def _dying_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
     """Stand-in rank body: rank 1 exits in the middle of its first job (no torch needed)."""
     result_q.put(("ready", rank, None))
