@@ -509,6 +509,9 @@ __device__ __forceinline__ void attn2_body(const CUtensorMap& tmQ, const CUtenso
                     row = (jj - src * per_rank) * BKV;
                     if (src != last_src) {  // first touch of a peer's shard: wait until it is published
                         attn_wait_flag_ge(p.flags_local + src, epoch);
+                        // the flag was read through the generic proxy, the shard is about to be read by TMA (async
+                        // proxy): order the two
+                        asm volatile("fence.proxy.async;" ::: "memory");
                         last_src = src;
                     }
                 }

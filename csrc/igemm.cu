@@ -401,7 +401,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tmA1, const CUtens
             uint32_t sa = smem0, fb = full0, eb = empty0;
             int s = 0;
             uint32_t ph = 1;
-            if (p.mode == 1 && ag_src != p.rank) wait_flag_ge(p.flags[p.rank] + ag_src, p.epoch);
+            if (p.mode == 1 && ag_src != p.rank) {
+                wait_flag_ge(p.flags[p.rank] + ag_src, p.epoch);
+                asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy flag read -> async-proxy (TMA) loads
+            }
             if (lane == 0) TR(3);
             for (int it = it_begin; it < it_end; ++it) {
                 bar_wait(eb, ph);
