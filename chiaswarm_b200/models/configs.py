@@ -63,7 +63,18 @@ _TINY_UNET3D = dict(
 
 _CONTROLNET_SD15 = dict(_SD15_UNET, conditioning_channels=3, conditioning_embedding_out_channels=(16, 32, 96, 256))
 
-_LATENT_UPSCALER_NOTE = "sd-x2-latent-upscaler uses a K-diffusion UNet; served by the SD UNet driver at 2x latent size"
+# stabilityai/sd-x2-latent-upscaler: the K-diffusion UNet of models/unet_k.py.  8 input channels (4 noisy latents + the
+# nearest-2x low-resolution latents), 5 outputs (4 + a variance channel the sampler drops), time embedding conditioned on
+# [128 noise-level features ; 768 CLIP pooled]; Euler sampler over a linear-beta schedule that predicts the sample
+_K_UNET = dict(
+    in_channels=8, out_channels=5, block_out_channels=(384, 384, 768, 768), layers_per_block=(2, 2, 4, 4),
+    down_block_types=("KDownBlock2D", "KCrossAttnDownBlock2D", "KCrossAttnDownBlock2D", "KCrossAttnDownBlock2D"),
+    up_block_types=("KCrossAttnUpBlock2D", "KCrossAttnUpBlock2D", "KCrossAttnUpBlock2D", "KUpBlock2D"),
+    mid_block_type=None, attention_head_dim=64, cross_attention_dim=768, only_cross_attention=(True, True, True, False),
+    act_fn="gelu", norm_num_groups=None, norm_eps=1e-5, resnet_time_scale_shift="scale_shift",
+    time_embedding_type="fourier", timestep_post_act="gelu", time_cond_proj_dim=896, conv_in_kernel=1, conv_out_kernel=1)
+_K_SCHED = dict(num_train_timesteps=1000, beta_start=0.0001, beta_end=0.02, beta_schedule="linear",
+                prediction_type="sample", steps_offset=0)
 
 
 def _pipe(cls, unet, vae, text, sched=None, **extra):
@@ -101,7 +112,11 @@ ARCHITECTURES = {
                           num_class_embeds=1000),
                      dict(_TINY_VAE, scaling_factor=0.08333), _TINY_CLIP,
                      dict(_SD_SCHED, beta_start=0.0001, beta_end=0.02, prediction_type="v_prediction")),
-    "sd-x2-latent-upscaler": _pipe("StableDiffusionLatentUpscalePipeline", dict(_SD15_UNET, in_channels=8), _SD_VAE, _CLIP_L),
+    "sd-x2-latent-upscaler": _pipe("StableDiffusionLatentUpscalePipeline", _K_UNET, _SD_VAE, _CLIP_L, _K_SCHED),
+    "tiny-x2-latent": _pipe("StableDiffusionLatentUpscalePipeline",
+                            dict(_K_UNET, block_out_channels=(32, 32, 64, 64), layers_per_block=(1, 1, 2, 2),
+                                 attention_head_dim=16, cross_attention_dim=32, time_cond_proj_dim=48),
+                            _TINY_VAE, _TINY_CLIP, _K_SCHED),
 }
 
 _CONTROLNET_TINY = dict(_TINY_UNET, conditioning_channels=3, conditioning_embedding_out_channels=(16, 32))
@@ -117,7 +132,7 @@ _NAME_RULES = [
     ("instruct-pix2pix", "instruct-pix2pix"),
     ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
     ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
-    ("sd-x2-latent-upscaler", "sd-x2-latent-upscaler"),
+    ("tiny-x2-latent", "tiny-x2-latent"), ("sd-x2-latent-upscaler", "sd-x2-latent-upscaler"),
     ("tiny-x4", "tiny-x4"), ("x4-upscaler", "sd-x4-upscaler"),
     ("stable-diffusion-2-1-base", "sd21-base"), ("stable-diffusion-2-base", "sd21-base"),
     ("stable-diffusion-2", "sd21"),
