@@ -53,6 +53,7 @@ class RankGroup:
         self._cv = threading.Condition()
         self._s = _State(world=world, free=[True] * world)
         self._leases = {}
+        self._dead = set()
 
     @property
     def world(self) -> int:
@@ -111,7 +112,7 @@ class RankGroup:
             if self._leases.pop(gang.lease_id, None) is None:
                 raise ValueError("gang is not leased (double release?)")
             for r in gang.ranks:
-                self._s.free[r] = True
+                self._s.free[r] = r not in self._dead  # (a rank that died while leased does not come back)
             self._cv.notify_all()
 
     def mark_dead(self, rank: int) -> List[Gang]:
@@ -120,7 +121,12 @@ class RankGroup:
         with self._cv:
             hit = [g for g in self._leases.values() if rank in g.ranks]
             self._s.free[rank] = False
+            self._dead.add(rank)
             return hit
+
+    def dead_ranks(self) -> List[int]:
+        with self._cv:
+            return sorted(self._dead)
 
 
 # ---- single-device view with the reference's function names --------------------------------
