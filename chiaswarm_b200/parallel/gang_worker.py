@@ -137,7 +137,9 @@ def rank_main(rank: int, world: int, port: int, job_q, result_q, use_cuda: bool,
                 result = synchronous_do_work_function(dict(job), device)
         except BaseException as e:  # synchronous_do_work_function already folds job errors into results
             result = {"id": job.get("id"), "rank_error": f"{type(e).__name__}: {e}"}
-        result_q.put(("result" if leader else "done", lease_id, result if leader else None))
+        # a follower hands back only whether it failed: a rank that errors out alone leaves its peers inside a collective
+        error = result.get("rank_error") or (result.get("pipeline_config") or {}).get("error")
+        result_q.put(("result" if leader else "done", lease_id, result if leader else ({"error": error} if error else None)))
     try:
         import torch.distributed as dist
 
@@ -225,6 +227,10 @@ class GangScheduler:
         self.pool = RankGroup(world)
         self.ranks = RankWorld(world, use_cuda, env, target)
         self.job_timeout_s = float(job_timeout_s or getattr(self.settings, "job_timeout_s", 900))
+        # a job error is symmetric (every rank of the gang refuses the same arguments) and then all ranks return at once;
+        # a rank that fails ALONE (out of memory, a device fault) leaves the others waiting in a collective: give them
+        # this long before the world is declared wedged, instead of the whole job timeout
+        self.straggler_grace_s = 30.0
         self._lock = threading.Lock()
         self.generation = 0
         self.restarts = 0
@@ -261,34 +267,47 @@ class GangScheduler:
         size = plan_gang_size(job, self.settings, self.world)
         if "seed" not in job or job["seed"] is None:
             job["seed"] = random.getrandbits(63)  # every rank of a gang must draw the same noise
-        generation, pool, ranks = self.generation, self.pool, self.ranks
+        with self._lock:  # one consistent view: a restart swaps the pool, the processes and their queues together
+            generation, pool, ranks = self.generation, self.pool, self.ranks
+            job_qs, result_qs, procs = ranks.job_qs, ranks.result_qs, ranks.procs
         gang = pool.lease(size)
-        self.leases_by_size[size] = self.leases_by_size.get(size, 0) + 1
+        with self._lock:
+            self.leases_by_size[size] = self.leases_by_size.get(size, 0) + 1
         failure = None
         result = None
+        lone_error = None  # (rank, message, time) of the first rank that came back with an error
         try:
             for r in gang.ranks:
-                ranks.job_qs[r].put((gang.lease_id, gang.ranks, job))
+                job_qs[r].put((gang.lease_id, gang.ranks, job))
             pending = set(gang.ranks)
             try:
                 with Watchdog(self.job_timeout_s, f"job {job.get('id')} on ranks {gang.ranks}") as dog:
                     while pending and failure is None:
                         dog.check()  # TimeoutError once the job has overrun
+                        if lone_error is not None and time.time() - lone_error[2] > self.straggler_grace_s:
+                            failure = (f"rank {lone_error[0]} failed ({lone_error[1]}) and ranks {sorted(pending)} did not "
+                                       f"return within {self.straggler_grace_s:g} s")
+                            break
                         for r in list(pending):
                             try:
-                                kind, lease_id, payload = ranks.result_qs[r].get(timeout=0.05)
+                                kind, lease_id, payload = result_qs[r].get(timeout=0.05)
                             except queue.Empty:
                                 if generation != self.generation:
                                     failure = "the rank world was restarted under this job"
-                                elif not ranks.alive(r):
+                                    break
+                                if not procs[r].is_alive():
                                     pool.mark_dead(r)
                                     failure = f"rank {r} died while running the job"
+                                    break
                                 continue
                             if lease_id != gang.lease_id:
                                 continue  # stale message of an abandoned lease
                             pending.discard(r)
                             if kind == "result":
                                 result = payload
+                                payload = {"error": payload.get("rank_error") or (payload.get("pipeline_config") or {}).get("error")}
+                            if lone_error is None and payload and payload.get("error"):
+                                lone_error = (r, str(payload["error"])[:200], time.time())
             except TimeoutError as e:
                 failure = str(e)
         finally:

@@ -279,3 +279,40 @@ def test_watchdog_times_a_wedged_gang_out(tmp_path):
         assert sched.restarts == 1
     finally:
         sched.stop()
+
+
+def _lone_failure_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
+    """Rank 1 comes back with an error of its own; the leader never returns (it waits in a collective for rank 1)."""
+    result_q.put(("ready", rank, None))
+    first = not os.path.exists(os.path.join(env["MARK"], f"up{rank}"))
+    open(os.path.join(env["MARK"], f"up{rank}"), "w").close()
+    while True:
+        msg = job_q.get()
+        if msg is None:
+            return
+        lease_id, ranks, job = msg
+        if first and rank == 1:
+            result_q.put(("done", lease_id, {"error": "CUDA out of memory"}))
+        elif first:
+            time.sleep(3600)
+        else:
+            result_q.put(("result" if ranks[0] == rank else "done", lease_id, {"id": job["id"], "ok": True}))
+
+
+def test_a_rank_that_fails_alone_does_not_cost_the_whole_job_timeout(tmp_path):
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2), use_cuda=False, env={"MARK": str(tmp_path)},
+                          job_timeout_s=600, target=_lone_failure_rank)
+    sched.straggler_grace_s = 0.5
+    sched.start()
+    try:
+        t0 = time.time()
+        r = sched.submit({"id": "j1", "model_name": "m", "workflow": "txt2vid"})
+        assert time.time() - t0 < 60
+        err = r["pipeline_config"]["error"]
+        assert "rank 1 failed (CUDA out of memory)" in err and "ranks [0] did not return" in err
+        assert sched.restarts == 1
+        assert sched.submit({"id": "j2", "model_name": "m", "workflow": "txt2vid"}) == {"id": "j2", "ok": True}
+    finally:
+        sched.stop()
