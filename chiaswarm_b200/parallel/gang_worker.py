@@ -19,6 +19,8 @@ what leases them.
 Failure handling: a job that overruns `job_timeout_s` (utils.tracing.Watchdog) or loses a
 rank process is answered with a non-fatal error (the hive re-issues it), the rank is withdrawn
 (`RankGroup.mark_dead`), and the rank world is restarted as a whole -- a torch.distributed world cannot lose a member.
+A rank that fails ALONE (out of memory, a device fault) says so when it returns; its peers, left waiting in a collective,
+then get `straggler_grace_s` (30 s) rather than the whole job timeout before the same restart happens.
 
 `settings.parallel_mode`: "dp" = every job one rank (the reference's behaviour, N independent lanes);
 "gang" / "patch" / "auto" = jobs that profit lease up to `settings.gang_size` ranks, the rest one.
