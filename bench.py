@@ -341,7 +341,10 @@ def main():
     # (cuDNN / cuBLAS / SDPA -- the ops diffusers would issue).  NOT the reference (unavailable).
     vs_baseline = baseline = None
     if args.impl == "ours" and not args.no_torch_baseline:
-        baseline = torch_baseline(args, dev, prompts, gen, l2_flush, barrier, dist, world)
+        try:
+            baseline = torch_baseline(args, dev, prompts, gen, l2_flush, barrier, dist, world)
+        except Exception as e:  # the headline line must still be printed
+            baseline = {"error": f"{type(e).__name__}: {e}"[:300]}
         vs_baseline = value / baseline["value"] if baseline and baseline.get("value") else None
 
     # ---------------- BASELINE.json's second half: single-image SDXL 1024x1024 latency, patch-parallel over the N ranks
