@@ -44,10 +44,15 @@ def image_from_text(text, size=(512, 512), color=0) -> Image.Image:
 
 
 def make_thumbnail(buffer) -> BytesIO:
-    if not isinstance(buffer, BytesIO):
-        buffer = BytesIO(buffer)
-    buffer.seek(0)
-    image = Image.open(buffer).convert("RGB")
+    """`buffer`: encoded image bytes / BytesIO (the reference's form, swarm/output_processor.py:73-80), or the PIL image
+    itself -- the packer below hands over the image it just encoded, which saves decoding a progressive JPEG again."""
+    if isinstance(buffer, Image.Image):
+        image = buffer.convert("RGB")  # (a copy: thumbnail() works in place)
+    else:
+        if not isinstance(buffer, BytesIO):
+            buffer = BytesIO(buffer)
+        buffer.seek(0)
+        image = Image.open(buffer).convert("RGB")
     image.thumbnail(THUMB_BOX, Image.Resampling.LANCZOS)
     return image_to_buffer(image, "image/jpeg", "web_low")
 
@@ -116,8 +121,8 @@ class OutputProcessor:
         self.other_outputs[name] = images
 
     def _pack(self, images):
-        buf = image_to_buffer(post_process(images), self.main_content_type)
-        return make_result(buf, buf, self.main_content_type)
+        sheet = post_process(images)
+        return make_result(image_to_buffer(sheet, self.main_content_type), sheet, self.main_content_type)
 
     def get_results(self):
         results = {}
