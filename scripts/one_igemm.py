@@ -1,3 +1,4 @@
+"""One launch of the igemm kernel at an SD1.5 shape: the target of `ncu --set full` captures (profiles/)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
