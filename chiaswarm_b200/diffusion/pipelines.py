@@ -558,7 +558,12 @@ class TorchDenoiser:
 
     @torch.no_grad()
     def decode(self, z):
-        return self.pipe.vae.decode(z.to(self.pipe.dtype))
+        z = z.to(self.pipe.dtype)
+        if self.gang is not None and z.shape[2] % self.gang.world == 0:
+            from ..parallel.patch import PatchParallelVAEDecoder
+
+            return PatchParallelVAEDecoder(self.pipe.vae, self.gang)(z)  # each rank decodes its strip of the image
+        return self.pipe.vae.decode(z)
 
 
 def _family_of_class(name: str) -> str:

@@ -9,6 +9,10 @@ nearest upsample, time embedding) is local.  This module expresses exactly that 
 torch ops + torch.distributed collectives (NCCL on GPUs, gloo in the CPU tests); the fused
 sm_100a kernels in `collectives.py` replace the three communication sites one by one.  It is the
 correctness reference for the partitioning and the "baseline, not the product" timing.
+
+`PatchParallelVAEDecoder` is the same algebra for the image decoder (collective call site 6): conv halos,
+GroupNorm statistics, and the single-head mid-block attention with local query rows against gathered K / V; every rank
+decodes its strip of the image and the strips are gathered once, as pixels.
 """
 from __future__ import annotations
 
@@ -187,3 +191,51 @@ class PatchParallelUNet:
     def __call__(self, sample, timestep, context, added_cond=None):
         """Full-tensor convenience wrapper: split, run, gather."""
         return self.ops.gather_rows(self.forward_local(self.split(sample), timestep, context, added_cond))
+
+
+class PatchParallelVAEDecoder:
+    """`AutoencoderKL.decode` with row-sharded activations: [n, 4, h, w] latents -> this rank's strip of the image."""
+
+    def __init__(self, vae, gang: Gang):
+        self.vae, self.ops = vae, PatchOps(gang)
+
+    def split(self, z):
+        h, w = z.shape[2], self.ops.world
+        if h % w:
+            raise ValueError(f"latent height {h} cannot be split over {w} ranks")
+        hl = h // w
+        return z[:, :, self.ops.rank * hl:(self.ops.rank + 1) * hl].contiguous()
+
+    def _resnet(self, m, x):
+        o = self.ops
+        h = o.conv(m.conv1, F.silu(o.group_norm(m.norm1, x)))
+        h = o.conv(m.conv2, F.silu(o.group_norm(m.norm2, h)))
+        if m.conv_shortcut is not None:
+            x = m.conv_shortcut(x)
+        return (x + h) / m.output_scale_factor
+
+    def _attention(self, a, x):
+        b, c, h, w = x.shape
+        y = self.ops.group_norm(a.group_norm, x).reshape(b, c, h * w).transpose(1, 2)
+        q = a.to_q(y)
+        k, v = self.ops.gather_tokens(a.to_k(y)), self.ops.gather_tokens(a.to_v(y))
+        o = F.scaled_dot_product_attention(q[:, None], k[:, None], v[:, None])[:, 0]
+        return x + a.to_out[0](o).transpose(1, 2).reshape(b, c, h, w)
+
+    @torch.no_grad()
+    def decode_local(self, z_local):
+        d, o = self.vae.decoder, self.ops
+        x = o.conv(d.conv_in, self.vae.post_quant_conv(z_local))
+        x = self._resnet(d.mid_block.resnets[0], x)
+        x = self._attention(d.mid_block.attentions[0], x)
+        x = self._resnet(d.mid_block.resnets[1], x)
+        for blk in d.up_blocks:
+            for r in blk.resnets:
+                x = self._resnet(r, x)
+            if blk.upsamplers is not None:
+                x = o.conv(blk.upsamplers[0].conv, F.interpolate(x, scale_factor=2.0, mode="nearest"))
+        return o.conv(d.conv_out, F.silu(o.group_norm(d.conv_norm_out, x)))
+
+    @torch.no_grad()
+    def __call__(self, z):
+        return self.ops.gather_rows(self.decode_local(self.split(z)))

@@ -15,7 +15,8 @@ def main(rank, world, port, out_path):
     from chiaswarm_b200.models import configs
     from chiaswarm_b200.models.unet2d import UNet2DConditionModel
     from chiaswarm_b200.parallel import runtime
-    from chiaswarm_b200.parallel.patch import PatchOps, PatchParallelUNet
+    from chiaswarm_b200.models.vae import AutoencoderKL
+    from chiaswarm_b200.parallel.patch import PatchOps, PatchParallelUNet, PatchParallelVAEDecoder
 
     gang = runtime.init("gloo")
     torch.manual_seed(0)
@@ -35,6 +36,13 @@ def main(rank, world, port, out_path):
         full = conv(x)
         mine = ops.gather_rows(ops.conv(conv, pp.split(x)))
     err2 = (full - mine).abs().max().item()
+    # the image decoder, row-split: halos through the up-sampling convs, distributed GroupNorm, mid-block attention
+    vae = _init_module(AutoencoderKL(**configs.get_architecture("tiny-sd")["vae"]), 5).eval()
+    z = torch.randn(2, 4, 8, 6, generator=g)
+    with torch.no_grad():
+        img = vae.decode(z)
+        img_pp = PatchParallelVAEDecoder(vae, gang)(z)
+    err3 = (img - img_pp).abs().max().item() / img.abs().max().item()
     # same seed -> same initial latents on every rank
     lat = torch.randn(1, 4, 8, 8, generator=torch.Generator().manual_seed(77))
     parts = [torch.empty_like(lat) for _ in range(world)]
@@ -42,7 +50,7 @@ def main(rank, world, port, out_path):
     same = all(torch.equal(p, lat) for p in parts)
     if rank == 0:
         with open(out_path, "w") as fh:
-            fh.write(f"{err} {err2} {int(same)}")
+            fh.write(f"{err} {err2} {int(same)} {err3}")
     dist.barrier()
     dist.destroy_process_group()
 

@@ -1,5 +1,6 @@
 """Patch-parallel algebra on CPU with real processes (gloo, world_size 2 and 4): the row-sharded
-UNet (halo exchange, GroupNorm all-reduce, K/V all-gather) must reproduce the unsplit model."""
+UNet (halo exchange, GroupNorm all-reduce, K/V all-gather) and the row-sharded VAE decoder must reproduce the unsplit
+models."""
 import os
 import socket
 import subprocess
@@ -24,5 +25,6 @@ def test_patch_parallel_unet_matches_unsplit(tmp_path, world):
              for r in range(world)]
     logs = [p.communicate(timeout=600)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), "\n".join(logs)[-4000:]
-    err, err2, same = out.read_text().split()
+    err, err2, same, err_vae = out.read_text().split()
     assert float(err) < 1e-4 and float(err2) < 1e-5 and same == "1"
+    assert float(err_vae) < 1e-4  # row-split VAE decode == whole decode
