@@ -237,6 +237,7 @@ class GangScheduler:
         self.generation = 0
         self.restarts = 0
         self.leases_by_size: Dict[int, int] = {}
+        self.metrics = None  # utils.metrics.Metrics of the hive client that owns this scheduler (GangWorker sets it)
 
     def start(self):
         self.ranks.start()
@@ -251,6 +252,8 @@ class GangScheduler:
                 return
             self.generation += 1
             self.restarts += 1
+            if self.metrics is not None:
+                self.metrics.inc("swarm_rank_world_restarts_total")
             logging.error("gang scheduler: restarting the rank world (generation %d)", self.generation)
             self.ranks.stop()
             self.pool = RankGroup(self.world)
@@ -275,6 +278,8 @@ class GangScheduler:
         gang = pool.lease(size)
         with self._lock:
             self.leases_by_size[size] = self.leases_by_size.get(size, 0) + 1
+        if self.metrics is not None:
+            self.metrics.inc("swarm_gang_leases_total", {"size": size})
         failure = None
         result = None
         lone_error = None  # (rank, message, time) of the first rank that came back with an error
@@ -348,6 +353,7 @@ class GangWorker(Worker):
             scheduler = GangScheduler(world, settings)
         self.scheduler = scheduler
         super().__init__(settings=settings, devices=[_Lane(i) for i in range(scheduler.world)], cpu_lane=cpu_lane)
+        scheduler.metrics = self.metrics
 
     async def startup(self):
         await super().startup()

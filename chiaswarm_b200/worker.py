@@ -12,6 +12,8 @@ What differs from the reference:
     (stitch) so they do not occupy a GPU (Q10); in gang mode (`settings.parallel_mode` != "dp",
     parallel/gang_worker.py) a lane instead leases 1 / 2 / 4 / 8 rank processes from the RankGroup per job;
   * results that fail to POST are retried a bounded number of times instead of dropped (Q14);
+  * polls, jobs, job times, uploads and queue depths are counted (utils/metrics.py) and served as Prometheus text at
+    `/metrics` when `settings.metrics_port` is set (the reference has no metrics at all);
   * `Worker` is an object (testable against a fake hive) -- the module-level functions
     `run_worker/startup/ask_for_work/device_worker/result_worker/submit_result` remain.
 """
@@ -20,6 +22,7 @@ from __future__ import annotations
 import asyncio
 import json
 import logging
+import time
 from datetime import datetime
 from typing import List, Optional
 
@@ -30,6 +33,7 @@ from .generator import do_work
 from .gpu.device import Device
 from .log_setup import setup_logging
 from .settings import Settings, load_settings, resolve_path
+from .utils import metrics as metrics_mod
 
 POLL_FOUND_S = 1
 POLL_IDLE_S = 11
@@ -52,6 +56,9 @@ class Worker:
         self.result_queue: asyncio.Queue = asyncio.Queue()
         self._tasks: list = []
         self.polls = 0
+        self.metrics = metrics_mod.new_registry()
+        self._busy = 0
+        self._metrics_server = None
 
     # ------------------------------------------------------------------ lifecycle
     def _headers(self):
@@ -84,6 +91,13 @@ class Worker:
         self.work_queue = asyncio.Queue(maxsize=lanes)
         self.cpu_queue = asyncio.Queue()
         self.available_gpus = asyncio.Semaphore(lanes)
+        self.metrics.set("swarm_queue_depth", lambda: self.work_queue.qsize(), {"queue": "gpu"})
+        self.metrics.set("swarm_queue_depth", lambda: self.cpu_queue.qsize(), {"queue": "cpu"})
+        self.metrics.set("swarm_queue_depth", lambda: self.result_queue.qsize(), {"queue": "results"})
+        self.metrics.set("swarm_lanes_busy", lambda: self._busy)
+        port = int(getattr(self.settings, "metrics_port", 0) or 0)
+        if port > 0 and self._metrics_server is None:
+            self._metrics_server = await metrics_mod.serve(self.metrics, port, getattr(self.settings, "metrics_host", "127.0.0.1"))
 
     async def run(self, max_polls: Optional[int] = None, sleep=asyncio.sleep):
         """The serve loop. `max_polls` bounds it for tests."""
@@ -113,6 +127,9 @@ class Worker:
             t.cancel()
         await asyncio.gather(*self._tasks, return_exceptions=True)
         self._tasks.clear()
+        if self._metrics_server is not None:
+            await self._metrics_server.cleanup()
+            self._metrics_server = None
 
     # ------------------------------------------------------------------ hive I/O
     async def ask_for_work(self) -> int:
@@ -137,6 +154,7 @@ class Worker:
                                 await self.cpu_queue.put(job)
                             else:
                                 await self.work_queue.put(job)
+                        self.metrics.inc("swarm_polls_total", {"outcome": "jobs" if found else "idle"})
                         return POLL_FOUND_S if found else POLL_IDLE_S
                     if response.status == 400:
                         body = await response.json()
@@ -147,6 +165,7 @@ class Worker:
         except Exception as e:
             logging.exception(e)
             print(e)
+            self.metrics.inc("swarm_polls_total", {"outcome": "error"})
             return POLL_ERROR_S
         finally:
             self.available_gpus.release()
@@ -160,8 +179,10 @@ class Worker:
                                     headers=self._headers()) as response:
                 if response.status == 500:
                     print(f"The hive returned an error: {response.reason}")
+                    self.metrics.inc("swarm_results_posted_total", {"outcome": "rejected"})
                     return False
                 print(f"Result {await response.json()}")
+                self.metrics.inc("swarm_results_posted_total", {"outcome": "ok"})
                 return True
 
     # ------------------------------------------------------------------ lanes
@@ -170,6 +191,22 @@ class Worker:
         parallel.gang_worker.GangWorker overrides it to lease a gang of rank processes instead."""
         return await do_work(job, device)
 
+    async def _counted(self, job, run):
+        """Runs one job and accounts for it (count by workflow / outcome, wall time, busy lanes)."""
+        workflow = str(job.get("workflow") or "image")
+        t0 = time.monotonic()
+        self._busy += 1
+        try:
+            result = await run()
+        except BaseException:
+            self.metrics.inc("swarm_jobs_total", {"workflow": workflow, "outcome": "crashed"})
+            raise
+        finally:
+            self._busy -= 1
+            self.metrics.observe("swarm_job_seconds", time.monotonic() - t0, {"workflow": workflow})
+        self.metrics.inc("swarm_jobs_total", {"workflow": workflow, "outcome": metrics_mod.job_outcome(result)})
+        return result
+
     async def device_worker(self, device: Device):
         while True:
             job = await self.work_queue.get()
@@ -177,7 +214,7 @@ class Worker:
             try:
                 await self.available_gpus.acquire()
                 acquired = True
-                result = await self.execute(job, device)
+                result = await self._counted(job, lambda: self.execute(job, device))
                 await self.result_queue.put(result)
             except asyncio.CancelledError:
                 raise
@@ -194,7 +231,7 @@ class Worker:
         while True:
             job = await self.cpu_queue.get()
             try:
-                await self.result_queue.put(await do_work(job, cpu))
+                await self.result_queue.put(await self._counted(job, lambda: do_work(job, cpu)))
             except asyncio.CancelledError:
                 raise
             except Exception as e:
@@ -217,6 +254,7 @@ class Worker:
                     except Exception as e:
                         logging.exception(e)
                         print(f"result_worker {e}")
+                        self.metrics.inc("swarm_results_posted_total", {"outcome": "failed"})
                     if attempt + 1 < attempts:
                         await backoff(min(2 ** attempt, 30))
             finally:

@@ -129,3 +129,84 @@ def test_full_loop_generates_and_posts_results():
             await hive.stop()
 
     asyncio.run(main())
+
+
+def test_metrics_are_counted_and_served():
+    """utils/metrics.py: the same loop as above, then GET /metrics of the worker's own endpoint."""
+    import socket
+
+    import aiohttp
+
+    from chiaswarm_b200.utils import metrics as M
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        hive.jobs = [
+            {"id": "img", "model_name": "tiny-sd", "prompt": "p", "height": 64, "width": 64, "num_inference_steps": 1, "seed": 3},
+            {"id": "bad", "model_name": "tiny-sd", "height": 5000, "width": 64},
+            {"id": "st", "workflow": "stitch", "model_name": "x", "jobs": []},
+        ]
+        hive.fail_results = 1
+        try:
+            w = _worker(uri)
+            w.settings.metrics_port = port
+
+            async def fast_sleep(s):
+                await asyncio.sleep(0)
+
+            w.result_worker.__func__.__defaults__ = (fast_sleep,)
+            page = {}
+
+            async def scrape_then_sleep(s):  # scrape while the worker is up (drain() closes the endpoint)
+                if w.polls == 2 and not page:
+                    await w.work_queue.join()
+                    await w.cpu_queue.join()
+                    await w.result_queue.join()
+                    async with aiohttp.ClientSession() as session:
+                        async with session.get(f"http://127.0.0.1:{port}/metrics") as r:
+                            assert r.status == 200 and r.headers["Content-Type"].startswith("text/plain")
+                            page["text"] = await r.text()
+                        async with session.get(f"http://127.0.0.1:{port}/healthz") as r:
+                            page["health"] = await r.json()
+                await asyncio.sleep(0)
+
+            await w.run(max_polls=2, sleep=scrape_then_sleep)
+            m = w.metrics
+            assert m.value("swarm_polls_total", {"outcome": "jobs"}) == 1 and m.value("swarm_polls_total", {"outcome": "idle"}) == 1
+            assert m.value("swarm_jobs_total", {"workflow": "image", "outcome": "ok"}) == 1
+            assert m.value("swarm_jobs_total", {"workflow": "image", "outcome": "fatal"}) == 1
+            assert m.value("swarm_jobs_total", {"workflow": "stitch", "outcome": "ok"}) \
+                + m.value("swarm_jobs_total", {"workflow": "stitch", "outcome": "error"}) \
+                + m.value("swarm_jobs_total", {"workflow": "stitch", "outcome": "fatal"}) == 1
+            assert m.value("swarm_job_seconds", {"workflow": "image"}) == 2
+            assert m.value("swarm_results_posted_total", {"outcome": "ok"}) == 3
+            assert m.value("swarm_results_posted_total", {"outcome": "rejected"}) == 1
+            assert w._busy == 0 and w._metrics_server is None
+            text = page["text"]
+            assert page["health"] == {"status": "ok"}
+            assert "# TYPE swarm_jobs_total counter" in text and 'swarm_jobs_total{outcome="ok",workflow="image"} 1' in text
+            assert 'swarm_job_seconds_bucket{workflow="image",le="+Inf"} 2' in text and "swarm_job_seconds_sum" in text
+            assert 'swarm_queue_depth{queue="gpu"} 0' in text and "swarm_lanes_busy 0" in text
+            # every line is `name{labels} value` or a comment: the exposition format Prometheus parses
+            import re
+
+            for line in text.strip().splitlines():
+                assert line.startswith("# ") or re.fullmatch(r'[a-z_]+(\{[^}]*\})? [-+0-9.eE]+(inf)?', line), line
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
+    # the registry on its own: labels are escaped, histograms are cumulative
+    m = M.new_registry()
+    m.inc("swarm_jobs_total", {"workflow": 'we"ird\n', "outcome": "ok"})
+    for v in (0.05, 0.3, 400.0, 5000.0):
+        m.observe("swarm_job_seconds", v)
+    text = m.render()
+    assert 'workflow="we\\"ird\\n"' in text
+    assert 'swarm_job_seconds_bucket{le="0.1"} 1' in text and 'swarm_job_seconds_bucket{le="0.5"} 2' in text
+    assert 'swarm_job_seconds_bucket{le="900"} 3' in text and 'swarm_job_seconds_bucket{le="+Inf"} 4' in text
