@@ -2,6 +2,7 @@
 reference call sites swarm/diffusion/diffusion_func.py:29-34,48-68)."""
 from __future__ import annotations
 
+import math
 import os
 import re
 from pathlib import Path
@@ -42,41 +43,96 @@ def _find_file(ref, names):
     for n in names:
         if (root / n).is_file():
             return root / n
+    if root.is_dir():  # a folder holding one weight file under another name (Kohya exports)
+        files = [p for p in sorted(root.iterdir()) if p.suffix in (".safetensors", ".bin", ".pt")]
+        if len(files) == 1:
+            return files[0]
     return None
 
 
-_LORA_KEY = re.compile(r"(.*)\.processor\.(to_q|to_k|to_v|to_out)_lora\.(down|up)\.weight$")
+# ---- LoRA file formats.  Every format boils down to (component, target module, {down, up, alpha}); they differ in how the
+# target is spelled.  `unet.load_attn_procs(lora)` of the reference (swarm/diffusion/diffusion_func.py:58-60) accepts all of
+# these through the diffusers releases its unpinned installer may pull.
+_DOWN = ("lora.down.weight", "lora_linear_layer.down.weight", "lora_A.weight", "lora_down.weight")
+_UP = ("lora.up.weight", "lora_linear_layer.up.weight", "lora_B.weight", "lora_up.weight")
+_PROCESSOR = re.compile(r"(.*)\.processor\.(to_q|to_k|to_v|to_out)_lora\.(down|up)\.weight$")
+_COMPONENTS = (("unet.", "unet"), ("text_encoder_2.", "te2"), ("text_encoder.", "te"),
+               ("lora_unet_", "unet"), ("lora_te2_", "te2"), ("lora_te1_", "te"), ("lora_te_", "te"))
+
+
+def _parse_lora_key(key: str):
+    """-> (component, target, flat, role) or None.  `flat`: the target is a Kohya name (dots written as underscores)."""
+    comp, rest, flat = "unet", key, False
+    for prefix, c in _COMPONENTS:
+        if key.startswith(prefix):
+            comp, rest, flat = c, key[len(prefix):], prefix.startswith("lora_")
+            break
+    m = _PROCESSOR.match(rest)
+    if m:  # diffusers <= 0.16 attention processors
+        return comp, f"{m.group(1)}.{'to_out.0' if m.group(2) == 'to_out' else m.group(2)}", False, m.group(3)
+    if rest.endswith(".alpha"):
+        return comp, rest[:-len(".alpha")], flat, "alpha"
+    for role, suffixes in (("down", _DOWN), ("up", _UP)):
+        for suffix in suffixes:
+            if rest.endswith("." + suffix):
+                return comp, rest[:-len(suffix) - 1], flat, role
+    return None
+
+
+def _lora_delta(w: dict, shape, scale: float) -> torch.Tensor:
+    down, up = w["down"].float(), w["up"].float()
+    rank = down.shape[0]
+    if "alpha" in w:  # Kohya: the update is scaled by alpha / rank
+        scale = scale * float(w["alpha"]) / rank
+    delta = up.flatten(1) @ down.flatten(1)                     # linear, or conv with a 1x1 `up`
+    if delta.numel() != math.prod(shape):
+        raise ValueError(f"update of shape {tuple(up.shape)} x {tuple(down.shape)} does not fit a weight of {tuple(shape)}")
+    return delta.reshape(shape) * scale
 
 
 def load_lora(pipe, lora, scale=1.0):
-    """Merges attention-processor LoRA weights (`pytorch_lora_weights.*`, keys
-    `...attn{1,2}.processor.to_{q,k,v,out}_lora.{down,up}.weight`) into the UNet projections:
-    W += scale * up @ down.  Merging (instead of a runtime side path) keeps the fused QKV GEMM."""
+    """Merges LoRA weights into the model: W += scale * (alpha / rank) * up @ down.  Merging (instead of a runtime side path)
+    keeps the fused QKV GEMM and the packed weights of the engine.  Formats: attention-processor files of diffusers <= 0.16
+    (`...attn1.processor.to_q_lora.down.weight`), the per-layer diffusers layout (`unet.<module>.lora.down.weight`,
+    `text_encoder.<module>.lora_linear_layer.up.weight`), PEFT (`lora_A` / `lora_B`) and Kohya `.safetensors`
+    (`lora_unet_<module with underscores>.lora_down.weight` + `.alpha`, `lora_te_...` for the text encoder) as long as the
+    module names are the diffusers ones.  Targets may be attention projections, feed-forward layers, proj_in / proj_out and
+    convolutions.  A key that names no module of this model is an error, not a silent skip."""
     path = _find_file(lora, ("pytorch_lora_weights.safetensors", "pytorch_lora_weights.bin"))
     if path is None:
         raise ValueError(f"LoRA weights {lora} not found locally")
     sd = checkpoints.load_state_dict(path)
-    pairs = {}
+    groups = {}
     for k, v in sd.items():
-        m = _LORA_KEY.match(k.replace("unet.", "", 1) if k.startswith("unet.") else k)
-        if not m:
-            continue
-        pairs.setdefault((m.group(1), m.group(2)), {})[m.group(3)] = v
-    if not pairs:
-        raise ValueError("no attention-processor LoRA keys found")
-    modules = dict(pipe.unet.named_modules())
+        parsed = _parse_lora_key(k)
+        if parsed is not None:
+            comp, target, flat, role = parsed
+            groups.setdefault((comp, target, flat), {})[role] = v
+    if not groups:
+        raise ValueError("no LoRA keys found (expected attention-processor, diffusers, PEFT or Kohya names)")
+    roots = {"unet": pipe.unet, "te": pipe.text_encoder, "te2": getattr(pipe, "text_encoder_2", None)}
+    tables = {}
     merged = 0
-    for (attn_path, proj), w in pairs.items():
-        attn = modules.get(attn_path)
-        if attn is None or "down" not in w or "up" not in w:
-            raise ValueError(f"LoRA target {attn_path} does not exist in this UNet")
-        lin = attn.to_out[0] if proj == "to_out" else getattr(attn, proj)
-        delta = (w["up"].float() @ w["down"].float()) * float(scale)
-        if delta.shape != lin.weight.shape:
-            raise ValueError(f"LoRA shape {tuple(delta.shape)} does not match {attn_path}.{proj} {tuple(lin.weight.shape)}")
-        lin.weight.data += delta.to(lin.weight.device, lin.weight.dtype)
+    for (comp, target, flat), w in sorted(groups.items(), key=lambda kv: kv[0][:2]):
+        root = roots.get(comp)
+        if root is None:
+            raise ValueError(f"LoRA targets {comp} but this pipeline has no such component")
+        if comp not in tables:
+            mods = {n: m for n, m in root.named_modules() if isinstance(m, (torch.nn.Linear, torch.nn.Conv2d))}
+            tables[comp] = (mods, {n.replace(".", "_"): m for n, m in mods.items()})
+        mod = tables[comp][1 if flat else 0].get(target)
+        if mod is None:
+            raise ValueError(f"LoRA target {target} does not exist in this {comp}")
+        if "down" not in w or "up" not in w:
+            raise ValueError(f"LoRA target {target} has only one of its two factors")
+        try:
+            delta = _lora_delta(w, mod.weight.shape, float(scale))
+        except ValueError as e:
+            raise ValueError(f"LoRA for {target}: {e}") from e
+        mod.weight.data += delta.to(mod.weight.device, mod.weight.dtype)
         merged += 1
     pipe._engine = None  # packed weights are stale
+    pipe.__dict__.pop("_text_engines", None)
     return merged
 
 

@@ -129,6 +129,72 @@ def test_lora_merge_and_textual_inversion(tmp_path):
     assert torch.equal(pipe.text_encoder.text_model.embeddings.token_embedding.weight[row], torch.ones(dim))
 
 
+def test_lora_file_formats_merge_to_the_same_weights(tmp_path):
+    """One LoRA (attention, feed-forward, proj_in conv, text encoder) written in the diffusers, PEFT and Kohya spellings."""
+    from safetensors.torch import save_file
+
+    from chiaswarm_b200.diffusion.loaders import load_lora
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+
+    base = StableDiffusionPipeline.from_architecture("tiny-sd")
+    blk = "down_blocks.1.attentions.0"
+    unet_targets = [f"{blk}.transformer_blocks.0.attn2.to_k", f"{blk}.transformer_blocks.0.attn1.to_out.0",
+                    f"{blk}.transformer_blocks.0.ff.net.0.proj", f"{blk}.transformer_blocks.0.ff.net.2", f"{blk}.proj_in"]
+    te_targets = ["text_model.encoder.layers.1.self_attn.q_proj", "text_model.encoder.layers.0.mlp.fc1"]
+    g = torch.Generator().manual_seed(0)
+    rank, alpha = 4, 2.0
+    factors, expected = {}, {}
+    for comp, root, names in (("unet", base.unet, unet_targets), ("te", base.text_encoder, te_targets)):
+        mods = dict(root.named_modules())
+        for n in names:
+            w = mods[n].weight
+            conv = w.dim() == 4
+            down = torch.randn((rank, w.shape[1], 1, 1) if conv else (rank, w.shape[1]), generator=g)
+            up = torch.randn((w.shape[0], rank, 1, 1) if conv else (w.shape[0], rank), generator=g)
+            factors[(comp, n)] = (down, up)
+            expected[(comp, n)] = w.detach().clone() + 0.5 * (up.flatten(1) @ down.flatten(1)).reshape(w.shape)
+    assert base.unet.get_submodule(f"{blk}.proj_in").weight.dim() == 4  # SD1.x: proj_in is a 1x1 conv
+
+    def write(folder, spell, with_alpha=False):
+        folder.mkdir()
+        sd = {}
+        for (comp, n), (down, up) in factors.items():
+            for role, t in (("down", down), ("up", up)):
+                sd[spell(comp, n, role)] = t.contiguous()
+            if with_alpha:  # Kohya scales by alpha / rank: pre-divide so that the merged result is the same
+                sd[spell(comp, n, "alpha")] = torch.tensor(alpha)
+                sd[spell(comp, n, "up")] = (up * (rank / alpha)).contiguous()
+        save_file(sd, str(folder / ("pytorch_lora_weights.safetensors" if not with_alpha else "my_style_v2.safetensors")))
+        return str(folder)
+
+    prefix = {"unet": "unet.", "te": "text_encoder."}
+    spellings = {
+        "diffusers": lambda c, n, r: f"{prefix[c]}{n}.{'lora' if c == 'unet' else 'lora_linear_layer'}.{r}.weight",
+        "peft": lambda c, n, r: f"{prefix[c]}{n}.lora_{'A' if r == 'down' else 'B'}.weight",
+        "kohya": lambda c, n, r: (f"lora_{'unet' if c == 'unet' else 'te'}_{n.replace('.', '_')}."
+                                  + {"down": "lora_down.weight", "up": "lora_up.weight", "alpha": "alpha"}[r]),
+    }
+    for name, spell in spellings.items():
+        pipe = StableDiffusionPipeline.from_architecture("tiny-sd")
+        assert load_lora(pipe, write(tmp_path / name, spell, with_alpha=(name == "kohya")), scale=0.5) == len(factors)
+        for (comp, n), want in expected.items():
+            got = (pipe.unet if comp == "unet" else pipe.text_encoder).get_submodule(n).weight
+            assert torch.allclose(got, want, atol=1e-5), (name, comp, n)
+    # a key that names no module of this model is refused, and so is a factor pair that does not fit its weight
+    bad = tmp_path / "bad"
+    bad.mkdir()
+    save_file({"unet.mid_block.attentions.7.to_q.lora.down.weight": torch.zeros(4, 8),
+               "unet.mid_block.attentions.7.to_q.lora.up.weight": torch.zeros(8, 4)}, str(bad / "pytorch_lora_weights.safetensors"))
+    with pytest.raises(ValueError, match="does not exist"):
+        load_lora(StableDiffusionPipeline.from_architecture("tiny-sd"), str(bad))
+    wrong = tmp_path / "wrong"
+    wrong.mkdir()
+    save_file({f"unet.{unet_targets[0]}.lora.down.weight": torch.zeros(4, 3),
+               f"unet.{unet_targets[0]}.lora.up.weight": torch.zeros(5, 4)}, str(wrong / "pytorch_lora_weights.safetensors"))
+    with pytest.raises(ValueError, match="does not fit"):
+        load_lora(StableDiffusionPipeline.from_architecture("tiny-sd"), str(wrong))
+
+
 def test_initialize_first_run_prompts_and_reports(tmp_path, monkeypatch):
     monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
     from chiaswarm_b200 import initialize, settings
