@@ -136,26 +136,68 @@ def load_lora(pipe, lora, scale=1.0):
     return merged
 
 
+def _grow_embedding(text_encoder, rows: int):
+    """`resize_token_embeddings`: the table gains rows for the placeholder ids; existing rows are kept."""
+    emb_mod = text_encoder.text_model.embeddings
+    old = emb_mod.token_embedding
+    if rows <= old.weight.shape[0]:
+        return old
+    new = torch.nn.Embedding(rows, old.weight.shape[1], device=old.weight.device, dtype=old.weight.dtype)
+    with torch.no_grad():
+        new.weight.zero_()
+        new.weight[: old.weight.shape[0]] = old.weight
+    new.weight.requires_grad_(False)
+    emb_mod.token_embedding = new
+    if isinstance(getattr(text_encoder, "config", None), dict):
+        text_encoder.config["vocab_size"] = rows
+    return new
+
+
+def _textual_inversion_entries(sd, default_token: str):
+    """-> [(component, token, vectors [n, dim])].  Formats: diffusers `learned_embeds` ({token: [dim] or [n, dim]}),
+    AUTOMATIC1111 `.pt` ({"string_to_param": {"*": [n, dim]}, "name": token}), SDXL pairs ({"clip_l": .., "clip_g": ..})."""
+    if "string_to_param" in sd:
+        vec = next(iter(sd["string_to_param"].values()))
+        return [("te", str(sd.get("name") or default_token), torch.as_tensor(vec))]
+    if "clip_l" in sd or "clip_g" in sd:
+        out = []
+        if "clip_l" in sd:
+            out.append(("te", default_token, torch.as_tensor(sd["clip_l"])))
+        if "clip_g" in sd:
+            out.append(("te2", default_token, torch.as_tensor(sd["clip_g"])))
+        return out
+    return [("te", str(token), torch.as_tensor(vec)) for token, vec in sd.items() if torch.is_tensor(vec)]
+
+
 def load_textual_inversion(pipe, ref):
-    """Adds learned token embeddings (`learned_embeds.bin|safetensors`: {token: vector}) by
-    overwriting unused rows at the end of the embedding table and teaching the tokenizer the
-    token when it supports it."""
+    """`pipeline.load_textual_inversion(ref)` of the reference (swarm/diffusion/diffusion_func.py:48-50): the learned
+    vectors become new rows of the token-embedding table, the placeholder becomes a token of the tokenizer (a placeholder
+    that stands for n vectors is written as n tokens at prompt time), so a prompt that names the placeholder conditions on
+    the learned vectors.  Returns {placeholder: first token id}."""
     path = _find_file(ref, ("learned_embeds.safetensors", "learned_embeds.bin"))
     if path is None:
         raise ValueError(f"textual inversion {ref} not found locally")
-    sd = checkpoints.load_state_dict(path)
-    if "string_to_param" in sd:  # A1111 .pt
-        sd = {k: v for k, v in zip(sd.get("string_to_token", {"*": 0}).keys(), sd["string_to_param"].values())}
-    emb = pipe.text_encoder.text_model.embeddings.token_embedding
-    dim = emb.weight.shape[1]
-    slot = emb.weight.shape[0] - 3
+    sd = checkpoints.load_state_dict(path)  # (pickles are read with weights_only=True: tensors and plain containers only)
+    entries = _textual_inversion_entries(sd, f"<{path.stem}>")
+    if not entries:
+        raise ValueError("no embeddings found in the textual-inversion file")
+    parts = {"te": (pipe.text_encoder, pipe.tokenizer),
+             "te2": (getattr(pipe, "text_encoder_2", None), getattr(pipe, "tokenizer_2", None))}
     added = {}
-    for token, vec in sd.items():
-        vec = torch.as_tensor(vec).reshape(-1, vec.shape[-1])
+    for comp, token, vec in entries:
+        encoder, tokenizer = parts[comp]
+        if encoder is None:
+            raise ValueError("the file carries embeddings for a second text encoder this pipeline does not have")
+        vec = vec.reshape(-1, vec.shape[-1])
+        dim = encoder.text_model.embeddings.token_embedding.weight.shape[1]
         if vec.shape[-1] != dim:
             raise ValueError(f"embedding dim {vec.shape[-1]} does not match the text encoder ({dim})")
-        emb.weight.data[slot] = vec[0].to(emb.weight.device, emb.weight.dtype)
-        added[token] = slot
-        slot -= 1
+        ids = tokenizer.register_placeholder(token, vec.shape[0])
+        emb = _grow_embedding(encoder, max(max(ids) + 1, len(tokenizer)))
+        with torch.no_grad():
+            for row, v in zip(ids, vec):
+                emb.weight[row] = v.to(emb.weight.device, emb.weight.dtype)
+        added.setdefault(token, ids[0])
     pipe.textual_inversion_tokens = added
+    pipe.__dict__.pop("_text_engines", None)  # (the recorded text-encoder plans keep no copy of the table, but start clean)
     return added

@@ -124,9 +124,38 @@ def test_lora_merge_and_textual_inversion(tmp_path):
     ti_dir.mkdir()
     dim = pipe.text_encoder.config["hidden_size"]
     save_file({"<cat-toy>": torch.ones(dim)}, str(ti_dir / "learned_embeds.safetensors"))
+    vocab = pipe.text_encoder.text_model.embeddings.token_embedding.weight.shape[0]
+    table_before = pipe.text_encoder.text_model.embeddings.token_embedding.weight.clone()
+    plain, _ = pipe.encode_prompt(["a photo of <cat-toy>"], [""], 1)
     added = load_textual_inversion(pipe, str(ti_dir))
     row = added["<cat-toy>"]
-    assert torch.equal(pipe.text_encoder.text_model.embeddings.token_embedding.weight[row], torch.ones(dim))
+    table = pipe.text_encoder.text_model.embeddings.token_embedding.weight
+    assert row == vocab and table.shape[0] == vocab + 1       # a NEW row: no existing token is overwritten
+    assert torch.equal(table[row], torch.ones(dim)) and torch.equal(table[:vocab], table_before)
+    # the placeholder is now one token of the prompt, and the prompt conditions on the learned vector
+    ids = pipe.tokenizer(["a photo of <cat-toy>"])[0].tolist()
+    assert ids.count(row) == 1 and ids.index(row) == 4
+    learned, _ = pipe.encode_prompt(["a photo of <cat-toy>"], [""], 1)
+    assert not torch.allclose(learned, plain)
+    same_a, _ = pipe.encode_prompt(["a photo of a dog"], [""], 1)
+    assert same_a.shape == learned.shape
+    with pytest.raises(ValueError, match="already in the tokenizer"):
+        load_textual_inversion(pipe, str(ti_dir))
+    # a multi-vector embedding (AUTOMATIC1111 layout) becomes n tokens at prompt time
+    multi = tmp_path / "multi"
+    multi.mkdir()
+    torch.save({"string_to_param": {"*": torch.arange(3 * dim, dtype=torch.float32).reshape(3, dim)}, "name": "<style>"},
+               str(multi / "style.pt"))
+    first = load_textual_inversion(pipe, str(multi))["<style>"]
+    ids = pipe.tokenizer(["in <style> please"])[0].tolist()
+    assert ids[2:5] == [first, first + 1, first + 2]
+    table = pipe.text_encoder.text_model.embeddings.token_embedding.weight
+    assert torch.equal(table[first + 2], torch.arange(2 * dim, 3 * dim, dtype=torch.float32))
+    wrong = tmp_path / "wrong_dim"
+    wrong.mkdir()
+    save_file({"<x>": torch.ones(dim + 1)}, str(wrong / "learned_embeds.safetensors"))
+    with pytest.raises(ValueError, match="does not match the text encoder"):
+        load_textual_inversion(pipe, str(wrong))
 
 
 def test_lora_file_formats_merge_to_the_same_weights(tmp_path):
