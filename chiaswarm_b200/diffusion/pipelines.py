@@ -13,6 +13,7 @@ family of the requested pipeline type plus which inputs are present.  Two execut
 """
 from __future__ import annotations
 
+import logging
 import os
 from dataclasses import dataclass, field
 from pathlib import Path
@@ -278,7 +279,11 @@ class StableDiffusionPipeline:
         """`gang` (parallel.runtime.Gang, every rank making this same call with the same seed): a single image runs
         patch-parallel over it (engine/patch_engine.py), a batch is split over it (each rank denoises and decodes
         batch / world images; the images are all-gathered, so every rank returns the full set)."""
+        if ignored:  # (diffusers raises on these; the hive's `unsupported_pipeline_arguments` exists to strip them)
+            logging.warning("pipeline arguments without effect here: %s", sorted(ignored))
         prompts = [prompt] if isinstance(prompt, str) else list(prompt)
+        if prompt_embeds is not None and len(prompts) == 1 and prompt_embeds.shape[0] > 1:
+            prompts = prompts * prompt_embeds.shape[0]
         if negative_prompt is None:
             negative = [""] * len(prompts)
         else:
@@ -357,9 +362,17 @@ class StableDiffusionPipeline:
         with timer.stage("encode_prompt"):
             embeds, pooled = self.encode_prompt(prompts, negative, n_cond)
         embeds = embeds.to(self.dtype)
+        if prompt_embeds is not None:  # precomputed text states replace the conditional branch
+            pe = prompt_embeds.to(self.device, self.dtype)
+            if pe.shape[0] * num_images_per_prompt == batch and num_images_per_prompt > 1:
+                pe = pe.repeat_interleave(num_images_per_prompt, dim=0)
+            if pe.shape != embeds[:batch].shape:
+                raise ValueError(f"`prompt_embeds` of shape {tuple(pe.shape)} do not fit {tuple(embeds[:batch].shape)}")
+            embeds = pe if n_cond == 1 else (torch.cat([embeds[:batch], pe]) if n_cond == 2
+                                             else torch.cat([pe, embeds[batch:]]))
 
-        plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), self.scheduler_config,
-                                    self.use_karras_sigmas)
+        sched_cfg = self.scheduler_config if not eta else {**self.scheduler_config, "eta": float(eta)}  # (DDIM only)
+        plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), sched_cfg, self.use_karras_sigmas)
         shape = (batch, lat_ch, h8, w8)
 
         def randn():

@@ -152,16 +152,20 @@ def make_plan(kind: str, num_steps: int, config: Optional[dict] = None, use_karr
         ts = (np.arange(num_steps) * ratio).round()[::-1].astype(np.int64) + cfg.get("steps_offset", 0)
         ts = ts.clip(max=n_train - 1)
         coef = []
+        eta = float(cfg.get("eta", 0.0) or 0.0)  # DDIM's stochasticity knob: 0 = deterministic, 1 = DDPM-like variance
         for t in ts:
             prev = t - ratio
             a_t = acp[t]
             a_p = acp[prev] if prev >= 0 else (1.0 if cfg.get("set_alpha_to_one", False) else acp[0])
             sig = math.sqrt((1 - a_t) / a_t)
             e0, e1 = _x0_coefs(sig, prediction, sigma_space=False)
-            c0 = math.sqrt(1 - a_p) / math.sqrt(1 - a_t)
-            coef.append([e0, e1, c0, math.sqrt(a_p) - c0 * math.sqrt(a_t), 0.0, 0.0, 1.0, 0.0])
+            # x_prev = sqrt(a_p) x0 + sqrt(1 - a_p - s^2) eps + s z, eps = (x - sqrt(a_t) x0) / sqrt(1 - a_t),
+            # s = eta sqrt((1 - a_p) / (1 - a_t)) sqrt(1 - a_t / a_p)
+            s_noise = eta * math.sqrt(max((1 - a_p) / (1 - a_t) * (1 - a_t / a_p), 0.0))
+            c0 = math.sqrt(max(1 - a_p - s_noise * s_noise, 0.0)) / math.sqrt(1 - a_t)
+            coef.append([e0, e1, c0, math.sqrt(a_p) - c0 * math.sqrt(a_t), 0.0, s_noise, 1.0, 0.0])
         sig = np.concatenate([table[ts], [0.0]])
-        return StepPlan(kind, ts.astype(np.float64), sig, np.asarray(coef, np.float32), 1.0, 1.0, False, prediction, acp)
+        return StepPlan(kind, ts.astype(np.float64), sig, np.asarray(coef, np.float32), 1.0, 1.0, eta > 0.0, prediction, acp)
 
     if use_karras_sigmas:
         sig = karras_sigmas(float(table[0]), float(table[-1]), num_steps)

@@ -102,3 +102,33 @@ def test_img2img_slice_restarts_first_order():
     s = plan.sigmas[8]
     a = 1 / math.sqrt(s * s + 1)
     assert torch.allclose(sl.add_noise(x0, nz, 0), a * x0 + s * a * nz)
+
+
+def test_ddim_eta_adds_the_ddpm_variance():
+    """eta > 0: x_prev = sqrt(a_p) x0 + sqrt(1 - a_p - s^2) eps + s z with s = eta sqrt((1-a_p)/(1-a_t)) sqrt(1 - a_t/a_p)."""
+    import math
+
+    det = S.make_plan("ddim", 10, None, False)
+    sto = S.make_plan("ddim", 10, {"eta": 1.0}, False)
+    assert not det.needs_noise and sto.needs_noise and np.all(det.coef[:, 5] == 0)
+    acp = det.alphas_cumprod
+    ratio = 1000 // 10
+    for i, t in enumerate(det.timesteps.astype(int)):
+        a_t, a_p = acp[t], (acp[t - ratio] if t - ratio >= 0 else acp[0])
+        s = math.sqrt((1 - a_p) / (1 - a_t) * (1 - a_t / a_p))
+        assert sto.coef[i, 5] == pytest.approx(s, rel=1e-5, abs=1e-7)
+        # the deterministic and the noise parts together keep the marginal variance 1 - a_p
+        k = sto.coef[i, 2] * math.sqrt(1 - a_t)
+        assert k * k + s * s == pytest.approx(1 - a_p, rel=1e-4)
+    # with a perfect epsilon model the x0 estimate stays exact whatever the noise
+    g = torch.Generator().manual_seed(0)
+    x0 = torch.randn(1, 4, 4, 4, generator=g, dtype=torch.float64)
+    eps = torch.randn(1, 4, 4, 4, generator=g, dtype=torch.float64)
+    x = sto.add_noise(x0, eps, 0)
+    for i in range(sto.num_steps):
+        s_i = float(sto.sigmas[i])
+        a = 1 / math.sqrt(s_i * s_i + 1)
+        pred = (x - a * x0) / (s_i * a)
+        x, x0_hat, _ = S.apply_step_torch(sto, i, x, pred, None, torch.randn(x.shape, generator=g, dtype=torch.float64))
+        x = x.double()
+        assert torch.allclose(x0_hat.double(), x0, atol=1e-3)

@@ -239,3 +239,32 @@ def test_hed_annotator_loads_the_reference_checkpoint_layout(tmp_path, monkeypat
     assert soft.size == img.size and soft.mode == "RGB" and scr.size == img.size
     assert set(np.unique(np.asarray(scr))) <= {0, 255}
     annotators._cache.clear()
+
+
+def test_eta_and_prompt_embeds_are_honoured():
+    """Two pipeline arguments that used to be accepted and dropped: DDIM `eta` and precomputed `prompt_embeds`."""
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+    from chiaswarm_b200.registry import resolve
+
+    pipe = StableDiffusionPipeline.from_architecture("tiny-sd")
+    kw = dict(prompt="a red cube", height=32, width=32, num_inference_steps=3, output_type="latent")
+    gen = lambda: torch.Generator().manual_seed(11)  # noqa: E731
+    pipe.set_scheduler(resolve("DDIMScheduler"), use_karras_sigmas=False)
+    det = pipe(generator=gen(), **kw).latents
+    sto = pipe(generator=gen(), eta=1.0, **kw).latents
+    assert torch.equal(det, pipe(generator=gen(), **kw).latents)
+    assert torch.equal(sto, pipe(generator=gen(), eta=1.0, **kw).latents) and not torch.allclose(det, sto)
+    pipe.set_scheduler(resolve("DPMSolverMultistepScheduler"))
+    base = pipe(generator=gen(), **kw).latents
+    assert torch.equal(base, pipe(generator=gen(), eta=1.0, **kw).latents)  # eta is DDIM's knob only
+    cond, _ = pipe.encode_prompt(["a red cube"], [""], 1)
+    via_embeds = pipe(generator=gen(), prompt_embeds=cond, **dict(kw, prompt="")).latents
+    assert torch.allclose(via_embeds, base, atol=1e-6)
+    other, _ = pipe.encode_prompt(["a blue sphere"], [""], 1)
+    assert not torch.allclose(pipe(generator=gen(), prompt_embeds=other, **dict(kw, prompt="")).latents, base)
+    import pytest as _pytest
+
+    with _pytest.raises(ValueError, match="do not fit"):
+        pipe(generator=gen(), prompt_embeds=cond[:, :5], **kw)
