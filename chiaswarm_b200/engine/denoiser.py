@@ -23,6 +23,8 @@ from .layers import FM, Recorder, _r8
 from .unet_sm100 import ControlNetPlan, UNetPlan, VaeDecoderPlan
 
 MAX_STEPS = 1024
+NOISE_STEPS_MIN = 64  # rows of a captured per-step noise table (ancestral samplers, DDIM eta): a graph built for a 15-step job
+#                       also serves a 50-step job of the same shape; longer jobs re-record (single GPU) or are refused (gangs)
 
 
 def _use_graphs() -> bool:
@@ -142,6 +144,9 @@ class SM100Denoiser:
         # refreshed per job, so a new guidance value never re-records or re-captures a plan
         key = (batch, h, w, n_cond, extra_ch, control is not None, noise is not None, added is not None, num_frames)
         sg = self._graphs.pop(key, None)
+        if sg is not None and noise is not None and sg.noise.shape[0] < steps:
+            sg.graph = sg.rec = None  # the captured noise table is too short for this job: re-record with a longer one
+            sg = None
         if sg is not None:
             self._graphs[key] = sg  # most recently used goes last
         up = self.unet_plan
@@ -155,7 +160,7 @@ class SM100Denoiser:
         if sg is None:
             sg = _StepGraph(self, batch, h, w, n_cond, extra_ch, control is not None, noise is not None,
                             added is not None)
-            sg.build(steps if noise is not None else 0)
+            sg.build(max(steps, NOISE_STEPS_MIN) if noise is not None else 0)
             self._load_job(sg, x, plan, extra, control, added, noise, g_text, g_image, control_scale)
             sg.capture()
             self._graphs[key] = sg
@@ -188,7 +193,8 @@ class SM100Denoiser:
         sg.coef[:steps].copy_(torch.from_numpy(plan.coef))
         if noise is not None:
             if sg.noise.shape[0] < steps:
-                raise ValueError("noise table shorter than the step count")
+                raise ValueError(f"this plan was captured with a {sg.noise.shape[0]}-step noise table; {steps} steps of a "
+                                 "noise-driven sampler do not fit it")
             sg.noise[:steps].copy_(noise.float().permute(0, 1, 3, 4, 2).reshape(steps, sg.rows, c))
         first = (x_nhwc * plan.first_scale).to(torch.float16).view(batch, h, w, c)
         mi = sg.model_in.view(sg.n_cond, batch, h, w, -1)

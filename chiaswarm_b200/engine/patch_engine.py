@@ -33,7 +33,7 @@ import torch
 
 from ..ops import native as nat
 from ..parallel.runtime import Gang, SymmetricArena, SymTensor
-from .denoiser import MAX_STEPS, SM100Denoiser, _StepGraph
+from .denoiser import MAX_STEPS, NOISE_STEPS_MIN, SM100Denoiser, _StepGraph
 from .layers import FM, Recorder, _r8
 
 
@@ -346,7 +346,7 @@ class PatchDenoiser(SM100Denoiser):
         g = sg.ctx.g
         self.unet_plan.set_context(embeds[g:g + 1].to(torch.float16))
         if fresh:
-            sg.build(steps if noise is not None else 0)
+            sg.build(max(steps, NOISE_STEPS_MIN) if noise is not None else 0)
             self._load_patch_job(sg, x, plan, extra, added, noise, g_text, g_image)
             sg.capture()
         self._load_patch_job(sg, x, plan, extra, added, noise, g_text, g_image)
@@ -379,7 +379,7 @@ class PatchDenoiser(SM100Denoiser):
         lo = ctx.g * F + ctx.p * fl
         self.unet_plan.set_context(embeds[lo:lo + fl].to(torch.float16))  # this rank's frames of its branch
         if fresh:
-            sg.build(steps if noise is not None else 0)
+            sg.build(max(steps, NOISE_STEPS_MIN) if noise is not None else 0)
             self._load_job(sg, x, plan, None, None, None, noise, g_text, 0.0)
             sg.capture()
         self._load_job(sg, x, plan, None, None, None, noise, g_text, 0.0)
