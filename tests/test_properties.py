@@ -12,7 +12,7 @@ from hypothesis import HealthCheck, assume, given, settings
 from hypothesis import strategies as st
 from PIL import Image
 
-FAST = settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+FAST = settings(max_examples=40, deadline=None, derandomize=True, database=None, suppress_health_check=[HealthCheck.too_slow])  # same examples every run
 
 
 # ---------------------------------------------------------------- gang allocator
