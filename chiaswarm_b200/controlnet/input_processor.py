@@ -9,8 +9,19 @@ classical CPU approximation keeps the job serviceable (documented per type), so 
 dependency.  Unknown types raise, as in the reference."""
 from __future__ import annotations
 
+import logging
+
 import numpy as np
 from PIL import Image, ImageFilter
+
+_reported = set()
+
+
+def _stand_in(kind: str, what: str):
+    """The learned annotator of `kind` is not on this worker: say so (once per type) instead of degrading silently."""
+    if kind not in _reported:
+        _reported.add(kind)
+        logging.warning("controlnet pre-processor %s: learned annotator not available locally, using %s", kind, what)
 
 
 def preprocess_image(image, controlnet):
@@ -83,6 +94,8 @@ def image_to_mlsd(image):
         return det(image)
     import cv2  # fallback: probabilistic Hough line segments on Canny edges
 
+    _stand_in("mlsd", "Hough line segments on Canny edges")
+
     arr = np.array(image.convert("RGB"))
     edges = cv2.Canny(arr, 60, 180)
     canvas = np.zeros(edges.shape, np.uint8)
@@ -101,6 +114,7 @@ def image_to_depth(image):
         return _gray3(np.array(depth))
     except Exception:
         # fallback: defocus heuristic (sharp = near) so the control image has the right modality
+        _stand_in("depth", "a defocus heuristic")
         _, _, mag = _sobel_mag(image)
         import cv2
 
@@ -112,6 +126,7 @@ def image_to_normal(image):
     det = _aux("NormalBaeDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image)
+    _stand_in("normalbae", "normals from Sobel gradients")
     gx, gy, _ = _sobel_mag(image)
     n = np.stack([-gx, -gy, np.full_like(gx, 255.0 / 4)], axis=2)
     n /= np.linalg.norm(n, axis=2, keepdims=True) + 1e-6
@@ -130,6 +145,8 @@ def image_to_segmentation(image):
         seg = proc.post_process_semantic_segmentation(out, target_sizes=[image.size[::-1]])[0].numpy()
     except Exception:
         import cv2  # fallback: k-means colour clustering into palette classes
+
+        _stand_in("seg", "k-means colour clustering")
 
         arr = np.array(image.convert("RGB"))
         small = cv2.resize(arr, (max(8, arr.shape[1] // 4), max(8, arr.shape[0] // 4)))
@@ -150,6 +167,7 @@ def image_to_lineart(image):
     det = _aux("LineartDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image)
+    _stand_in("lineart", "Sobel edge magnitude")
     _, _, mag = _sobel_mag(image)
     return _gray3(255 * np.clip(mag * 3.0, 0, 1))
 
@@ -159,6 +177,7 @@ def image_to_openpose(image):
     if det is not None:
         return det(image)
     # no classical stand-in for a pose estimator: an empty skeleton canvas means "no pose constraint"
+    _stand_in("openpose", "an empty skeleton canvas (no pose constraint)")
     return Image.new("RGB", image.size, 0)
 
 
@@ -171,6 +190,7 @@ def image_to_softedge(image, scribble=False):
     hed = load_hed()
     if hed is not None:
         return hed.edges(image, next(hed.parameters()).device, scribble=scribble)
+    _stand_in("scribble" if scribble else "softedge", "Sobel edge magnitude")
     _, _, mag = _sobel_mag(image)
     if scribble:
         edge = (mag > 0.25).astype(np.uint8) * 255
