@@ -3,8 +3,9 @@
 Dispatch on `controlnet["type"]` exactly as the reference.  canny / tile / pix2pix / shuffle are
 self-contained (OpenCV / PIL / numpy).  The learned annotators (mlsd, depth, normalbae, seg,
 lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers hub models in the
-reference; they are used when importable and locally cached; soft edges / scribbles additionally have this
-tree's own HED network (controlnet/annotators.py, loads `lllyasviel/Annotators/ControlNetHED.pth`); otherwise a
+reference; they are used when importable and locally cached; soft edges / scribbles and lineart additionally have this
+tree's own networks (controlnet/annotators.py: HED from `lllyasviel/Annotators/ControlNetHED.pth`, the lineart generator
+from `sk_model.pth`); otherwise a
 classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
 dependency.  Unknown types raise, as in the reference."""
 from __future__ import annotations
@@ -167,6 +168,11 @@ def image_to_lineart(image):
     det = _aux("LineartDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image)
+    from .annotators import load_lineart  # this tree's own lineart generator, when its checkpoint is present locally
+
+    net = load_lineart()
+    if net is not None:
+        return net.lines(image, next(net.parameters()).device)
     _stand_in("lineart", "Sobel edge magnitude")
     _, _, mag = _sobel_mag(image)
     return _gray3(255 * np.clip(mag * 3.0, 0, 1))

@@ -241,6 +241,39 @@ def test_hed_annotator_loads_the_reference_checkpoint_layout(tmp_path, monkeypat
     annotators._cache.clear()
 
 
+def test_lineart_annotator_loads_the_reference_checkpoint_layout(tmp_path, monkeypatch):
+    """The in-tree lineart generator has the parameter names of `lllyasviel/Annotators/sk_model.pth` (informative-drawings
+    Generator(3, 1, 3)), is picked up from the local model root, and returns white-on-black lines of the input size."""
+    import torch
+
+    from chiaswarm_b200.controlnet import annotators, input_processor
+
+    net = annotators.LineartNet()
+    sd = net.state_dict()
+    expect = {"model0.1.weight": (64, 3, 7, 7), "model1.0.weight": (128, 64, 3, 3), "model1.3.weight": (256, 128, 3, 3),
+              "model2.0.conv_block.1.weight": (256, 256, 3, 3), "model2.2.conv_block.5.bias": (256,),
+              "model3.0.weight": (256, 128, 3, 3), "model3.3.weight": (128, 64, 3, 3), "model4.1.weight": (1, 64, 7, 7)}
+    for k, shape in expect.items():
+        assert tuple(sd[k].shape) == shape, k
+    assert len(sd) == 2 * (1 + 2 + 2 * 3 + 2 + 1)  # instance norms carry no parameters
+    torch.manual_seed(0)
+    root = tmp_path / "models" / "lllyasviel" / "Annotators"
+    root.mkdir(parents=True)
+    torch.save(sd, root / "sk_model.pth")
+    monkeypatch.setenv("SDAAS_MODEL_ROOT", str(tmp_path / "models"))
+    annotators._cache.clear()
+    img = Image.radial_gradient("L").resize((98, 63)).convert("RGB")  # not a multiple of 4: fitted, then restored
+    out = input_processor.preprocess_image(img, {"preprocess": True, "type": "lineart"})
+    assert annotators._cache["lineart"] is not None  # the learned generator ran, not the Sobel stand-in
+    assert out.size == img.size and out.mode == "RGB"
+    # a file that is not this network is refused, not half-loaded
+    annotators._cache.clear()
+    torch.save({"model0.1.weight": torch.zeros(64, 3, 7, 7)}, root / "sk_model.pth")
+    with pytest.raises(RuntimeError):
+        annotators.load_lineart()
+    annotators._cache.clear()
+
+
 def test_eta_and_prompt_embeds_are_honoured():
     """Two pipeline arguments that used to be accepted and dropped: DDIM `eta` and precomputed `prompt_embeds`."""
     import torch
