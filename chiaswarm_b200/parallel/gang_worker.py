@@ -23,7 +23,9 @@ A rank that fails ALONE (out of memory, a device fault) says so when it returns;
 then get `straggler_grace_s` (30 s) rather than the whole job timeout before the same restart happens.
 
 `settings.parallel_mode`: "dp" = every job one rank (the reference's behaviour, N independent lanes);
-"gang" / "patch" / "auto" = jobs that profit lease up to `settings.gang_size` ranks, the rest one.
+"gang" / "patch" / "auto" = jobs that profit lease up to `settings.gang_size` ranks, the rest one; "tp" = the same, with the
+self-attention of row-split plans head-parallel over the gang (fused all-gather GEMM + GEMM reduce-scatter; faster than the
+K/V gather on SD1.5-sized levels, slower on SDXL's: DESIGN.md).
 """
 from __future__ import annotations
 
@@ -227,6 +229,11 @@ class GangScheduler:
             use_cuda = torch.cuda.is_available()
         self.world = world
         self.pool = RankGroup(world)
+        env = dict(env or {})
+        if str(getattr(self.settings, "parallel_mode", "dp")).lower() == "tp":
+            # row-split plans run self-attention head-parallel through the fused all-gather GEMM / GEMM reduce-scatter
+            # (engine/layers.py::TransformerBlock._self_attention_tp) instead of gathering K / V inside the attention kernel
+            env.setdefault("SW_PATCH_ATTN", "tp")
         self.ranks = RankWorld(world, use_cuda, env, target)
         self.job_timeout_s = float(job_timeout_s or getattr(self.settings, "job_timeout_s", 900))
         # a job error is symmetric (every rank of the gang refuses the same arguments) and then all ranks return at once;

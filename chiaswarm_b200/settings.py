@@ -17,7 +17,7 @@ _DEFAULTS = {
     "sdaas_uri": "http://localhost:9511",
     "worker_name": "worker",
     # --- B200 runtime knobs (not in the reference)
-    "parallel_mode": "dp",       # dp (one GPU per job) | gang / patch / auto (parallel/gang_worker.py leases gangs)
+    "parallel_mode": "dp",       # dp (one GPU per job) | gang / patch / auto (parallel/gang_worker.py leases gangs) | tp (+ head-parallel attention)
     "gang_size": 1,              # most GPUs one job may lease in gang mode (1, 2, 4, 8)
     "patch_min_pixels": 1024 * 1024,  # gang mode: single images at least this large run patch-parallel
     "job_timeout_s": 900,        # gang mode: a job that overruns is failed non-fatally and the rank world restarted

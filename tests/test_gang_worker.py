@@ -316,3 +316,27 @@ def test_a_rank_that_fails_alone_does_not_cost_the_whole_job_timeout(tmp_path):
         assert sched.submit({"id": "j2", "model_name": "m", "workflow": "txt2vid"}) == {"id": "j2", "ok": True}
     finally:
         sched.stop()
+
+
+def _env_echo_rank(rank, world, port, job_q, result_q, use_cuda, env=None):
+    os.environ.update(env or {})
+    result_q.put(("ready", rank, None))
+    while True:
+        msg = job_q.get()
+        if msg is None:
+            return
+        lease_id, ranks, job = msg
+        result_q.put(("result" if ranks[0] == rank else "done", lease_id,
+                      {"id": job["id"], "attn": os.environ.get("SW_PATCH_ATTN", "kv")}))
+
+
+def test_tp_mode_selects_head_parallel_attention_in_the_ranks():
+    from chiaswarm_b200.parallel.gang_worker import GangScheduler
+
+    for mode, want in (("tp", "tp"), ("gang", "kv")):
+        sched = GangScheduler(2, _settings(parallel_mode=mode, gang_size=2), use_cuda=False, env={}, target=_env_echo_rank)
+        sched.start()
+        try:
+            assert sched.submit({"id": "j", "model_name": "m", "workflow": "txt2vid"})["attn"] == want
+        finally:
+            sched.stop()
