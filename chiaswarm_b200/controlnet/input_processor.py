@@ -5,7 +5,8 @@ self-contained (OpenCV / PIL / numpy).  The learned annotators (mlsd, depth, nor
 lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers hub models in the
 reference; they are used when importable and locally cached; soft edges / scribbles and lineart additionally have this
 tree's own networks (controlnet/annotators.py: HED from `lllyasviel/Annotators/ControlNetHED.pth`, the lineart generator
-from `sk_model.pth`); otherwise a
+from `sk_model.pth`), and openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`);
+otherwise a
 classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
 dependency.  Unknown types raise, as in the reference."""
 from __future__ import annotations
@@ -182,6 +183,11 @@ def image_to_openpose(image):
     det = _aux("OpenposeDetector", "lllyasviel/ControlNet")
     if det is not None:
         return det(image)
+    from .openpose import load_body_pose  # this tree's own body-pose detector, when its checkpoint is present locally
+
+    body = load_body_pose()
+    if body is not None:
+        return body(image)
     # no classical stand-in for a pose estimator: an empty skeleton canvas means "no pose constraint"
     _stand_in("openpose", "an empty skeleton canvas (no pose constraint)")
     return Image.new("RGB", image.size, 0)
