@@ -5,7 +5,8 @@ self-contained (OpenCV / PIL / numpy).  The learned annotators (mlsd, depth, nor
 lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers hub models in the
 reference; they are used when importable and locally cached; soft edges / scribbles and lineart additionally have this
 tree's own networks (controlnet/annotators.py: HED from `lllyasviel/Annotators/ControlNetHED.pth`, the lineart generator
-from `sk_model.pth`), and openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`);
+from `sk_model.pth`), openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`) and mlsd this
+tree's M-LSD network (controlnet/mlsd.py, `mlsd_large_512_fp32.pth`);
 otherwise a
 classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
 dependency.  Unknown types raise, as in the reference."""
@@ -94,6 +95,11 @@ def image_to_mlsd(image):
     det = _aux("MLSDdetector", "lllyasviel/ControlNet")
     if det is not None:
         return det(image)
+    from .mlsd import load_mlsd  # this tree's own M-LSD network, when its checkpoint is present locally
+
+    own = load_mlsd()
+    if own is not None:
+        return own(image)
     import cv2  # fallback: probabilistic Hough line segments on Canny edges
 
     _stand_in("mlsd", "Hough line segments on Canny edges")
