@@ -362,6 +362,12 @@ class StableDiffusionPipeline:
         with timer.stage("encode_prompt"):
             embeds, pooled = self.encode_prompt(prompts, negative, n_cond)
         embeds = embeds.to(self.dtype)
+        if n_cond == 2 and negative_prompt is None and self.config.get("force_zeros_for_empty_prompt", False):
+            # SDXL checkpoints (model_index.json): without a negative prompt the unconditional branch is conditioned on
+            # ZERO text states and a zero pooled vector, not on the encoding of the empty string
+            embeds = torch.cat([torch.zeros_like(embeds[:batch]), embeds[batch:]])
+            if pooled is not None:
+                pooled = torch.cat([torch.zeros_like(pooled[:batch]), pooled[batch:]])
         if prompt_embeds is not None:  # precomputed text states replace the conditional branch
             pe = prompt_embeds.to(self.device, self.dtype)
             if pe.shape[0] * num_images_per_prompt == batch and num_images_per_prompt > 1:

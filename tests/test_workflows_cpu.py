@@ -301,3 +301,32 @@ def test_eta_and_prompt_embeds_are_honoured():
 
     with _pytest.raises(ValueError, match="do not fit"):
         pipe(generator=gen(), prompt_embeds=cond[:, :5], **kw)
+
+
+def test_force_zeros_for_empty_prompt_is_honoured():
+    """SDXL's model_index flag: no negative prompt -> zero unconditional text states (not the encoding of "")."""
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+
+    pipe = StableDiffusionPipeline.from_architecture("tiny-sd")
+    kw = dict(prompt="a red cube", height=32, width=32, num_inference_steps=2, output_type="latent")
+    gen = lambda: torch.Generator().manual_seed(5)  # noqa: E731
+    plain = pipe(generator=gen(), **kw).latents
+    seen = {}
+    real_run = None
+
+    pipe.config["force_zeros_for_empty_prompt"] = True
+    den = pipe._denoiser()
+    real_run = den.run
+
+    def spy(**k):
+        seen["embeds"] = k["embeds"].clone()
+        return real_run(**k)
+
+    den.run = spy
+    zeroed = pipe(generator=gen(), **kw).latents
+    assert not seen["embeds"][:1].any() and seen["embeds"][1:].any()      # [uncond = 0, cond]
+    assert not torch.allclose(zeroed, plain)
+    with_negative = pipe(generator=gen(), negative_prompt="", **kw).latents  # an explicit negative prompt is encoded
+    assert seen["embeds"][:1].any() and torch.allclose(with_negative, plain, atol=1e-6)
