@@ -89,6 +89,22 @@ def _fit_multiple(image: Image.Image, multiple=8) -> Image.Image:
     return image if (w2, h2) == (w, h) else image.resize((w2, h2), Image.Resampling.LANCZOS)
 
 
+def vae_needs_fp32(pipe) -> bool:
+    """`force_upcast` in vae/config.json (the original SDXL VAE): its activations overflow fp16, so diffusers runs that VAE
+    in fp32; so does this worker (eager, off the engine).  fp16-safe VAEs (sdxl-vae-fp16-fix, SD 1.x / 2.x) do not set it."""
+    return bool(pipe.vae.config.get("force_upcast", False)) and pipe.dtype == torch.float16
+
+
+def vae_fp32(pipe):
+    """An fp32 copy of the pipeline's VAE, made on first use and dropped by `pipe.to()`."""
+    vae = pipe.__dict__.get("_vae_fp32")
+    if vae is None:
+        import copy
+
+        vae = pipe.__dict__["_vae_fp32"] = copy.deepcopy(pipe.vae).float().eval()
+    return vae
+
+
 class StableDiffusionPipeline:
     """SD 1.x / 2.x / XL family driver."""
 
@@ -196,6 +212,7 @@ class StableDiffusionPipeline:
             self.safety_checker.to(self.device, self.dtype)
         self._engine = None
         self.__dict__.pop("_text_engines", None)
+        self.__dict__.pop("_vae_fp32", None)
         return self
 
     # ------------------------------------------------------------------ scheduler selection
@@ -260,6 +277,8 @@ class StableDiffusionPipeline:
     def _vae_encode(self, x, generator=None, sample=True):
         """AutoencoderKL.encode: on the sm_100a engine when that is the back end (engine/unet_sm100.VaeEncoderPlan),
         else the eager module; the reparameterisation noise is drawn the same way either way."""
+        if vae_needs_fp32(self):
+            return vae_fp32(self).encode(x.float(), generator, sample).to(self.dtype)
         if self.backend != "sm100" or self.device.type != "cuda" or os.environ.get("SW_VAE_ENCODE", "1") in ("0", "torch"):
             return self.vae.encode(x, generator, sample)
         mean, logvar = self._denoiser().encode_moments(x)
@@ -577,6 +596,8 @@ class TorchDenoiser:
 
     @torch.no_grad()
     def decode(self, z):
+        if vae_needs_fp32(self.pipe):
+            return vae_fp32(self.pipe).decode(z.float())
         z = z.to(self.pipe.dtype)
         if self.gang is not None and z.shape[2] % self.gang.world == 0:
             from ..parallel.patch import PatchParallelVAEDecoder

@@ -270,7 +270,12 @@ class SM100Denoiser:
     # ------------------------------------------------------------------ VAE decode
     @torch.no_grad()
     def decode(self, z):
-        """z: latents already divided by the scaling factor, NCHW. Returns uint8 [n, H, W, 3]."""
+        """z: latents already divided by the scaling factor, NCHW. Returns uint8 [n, H, W, 3] -- or, for a VAE whose config
+        asks for fp32 (`force_upcast`: the original SDXL VAE overflows fp16), float NCHW from the eager fp32 module."""
+        from ..diffusion.pipelines import vae_fp32, vae_needs_fp32
+
+        if vae_needs_fp32(self.pipe):
+            return vae_fp32(self.pipe).decode(z.float())
         if self.vae_plan is None:
             self.vae_plan = VaeDecoderPlan(self.pipe.vae, self.device)
         n, c, h, w = z.shape

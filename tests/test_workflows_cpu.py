@@ -330,3 +330,29 @@ def test_force_zeros_for_empty_prompt_is_honoured():
     assert not torch.allclose(zeroed, plain)
     with_negative = pipe(generator=gen(), negative_prompt="", **kw).latents  # an explicit negative prompt is encoded
     assert seen["embeds"][:1].any() and torch.allclose(with_negative, plain, atol=1e-6)
+
+
+def test_vae_force_upcast_runs_the_vae_in_fp32():
+    """`force_upcast` (vae/config.json of the original SDXL VAE): an fp16 pipeline decodes / encodes through an fp32 copy."""
+    import torch
+
+    from chiaswarm_b200.diffusion import pipelines as P
+
+    pipe = P.StableDiffusionPipeline.from_architecture("tiny-sd")
+    assert not P.vae_needs_fp32(pipe)
+    pipe.vae.config["force_upcast"] = True
+    assert not P.vae_needs_fp32(pipe)          # an fp32 pipeline (CPU) needs no second copy
+    pipe.dtype = torch.float16                 # what a CUDA pipeline runs at
+    assert P.vae_needs_fp32(pipe)
+    z = torch.randn(1, 4, 8, 8, generator=torch.Generator().manual_seed(0))
+    want = pipe.vae.decode(z)
+    got = P.TorchDenoiser(pipe).decode(z.half())
+    assert got.dtype == torch.float32 and torch.allclose(got, pipe.vae.decode(z.half().float()), atol=1e-6)
+    assert torch.allclose(got, want, atol=5e-2)
+    copy = pipe.__dict__["_vae_fp32"]
+    assert copy is not pipe.vae and next(copy.parameters()).dtype == torch.float32
+    img = torch.rand(1, 3, 16, 16) * 2 - 1
+    enc = pipe._vae_encode(img.half(), sample=False)
+    assert enc.dtype == torch.float16 and torch.allclose(enc.float(), pipe.vae.encode(img.half().float(), None, False), atol=2e-3)
+    pipe.to("cpu", torch.float32)
+    assert "_vae_fp32" not in pipe.__dict__
