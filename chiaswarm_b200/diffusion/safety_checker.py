@@ -41,8 +41,9 @@ class ClipImageProcessor:
         for im in images:
             im = im.convert("RGB")
             w, h = im.size
-            s = self.size / min(w, h)
-            im = im.resize((max(self.crop, round(w * s)), max(self.crop, round(h * s))), Image.Resampling.BICUBIC)
+            # short side to `size`, long side truncated (transformers' get_resize_output_image_size)
+            w2, h2 = (self.size, int(self.size * h / w)) if w <= h else (int(self.size * w / h), self.size)
+            im = im.resize((max(self.crop, w2), max(self.crop, h2)), Image.Resampling.BICUBIC)
             w, h = im.size
             l, t = (w - self.crop) // 2, (h - self.crop) // 2
             im = im.crop((l, t, l + self.crop, t + self.crop))

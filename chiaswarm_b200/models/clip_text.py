@@ -96,9 +96,12 @@ class CLIPTextModel(nn.Module):
         c.update(cfg)
         self.config = c
         self.text_model = _TextModel(c)
-        self.text_projection = None
-        if c.get("projection_dim"):
-            self.text_projection = nn.Linear(c["hidden_size"], c["projection_dim"], bias=False)
+        # `projection_dim` is in EVERY transformers CLIP text config (SD 1.x's plain CLIPTextModel says 768); only a
+        # CLIPTextModelWithProjection (SDXL's second encoder) has the matrix.  A checkpoint config names its class in
+        # `architectures`; this tree's own architecture tables set `projection_dim` only where the matrix exists.
+        arch = c.get("architectures")
+        with_projection = bool(c.get("projection_dim")) and (not arch or any("WithProjection" in a for a in arch))
+        self.text_projection = nn.Linear(c["hidden_size"], c["projection_dim"], bias=False) if with_projection else None
 
     def forward(self, input_ids, output_hidden_state: int = -1, eos_token_id=None):
         """Returns (hidden [b,s,d], pooled [b,d or proj]). `output_hidden_state=-2` gives the

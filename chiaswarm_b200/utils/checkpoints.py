@@ -123,6 +123,16 @@ def load_into(module: torch.nn.Module, sd: Dict[str, torch.Tensor], strict: bool
     unexpected = [k for k in unexpected if not k.endswith("position_ids")]
     if strict and (missing or unexpected):
         raise ValueError(f"checkpoint mismatch: missing={missing[:8]} unexpected={unexpected[:8]}")
+    # strict=False tolerates tensors this tree does not model (logged: they may be a feature that is being ignored), never
+    # parameters the checkpoint does not provide -- those would run with whatever the constructor left in them
+    if missing:
+        raise ValueError(f"{type(module).__name__}: the checkpoint has no weights for {len(missing)} parameter(s), e.g. "
+                         f"{missing[:6]}")
+    if unexpected:
+        import logging
+
+        logging.warning("%s: %d checkpoint tensor(s) are not part of this model and were ignored, e.g. %s",
+                        type(module).__name__, len(unexpected), unexpected[:6])
     return missing, unexpected
 
 
