@@ -106,15 +106,23 @@ class BodyPoseNet(nn.Module):
 
 
 # ------------------------------------------------------------------------------------------ maps -> people
+def _symmetric_pad(x: torch.Tensor, r: int, dim: int) -> torch.Tensor:
+    """scipy's default border ("reflect": d c b a | a b c d -- the edge sample repeats), r may exceed the size."""
+    n = x.shape[dim]
+    idx = torch.arange(-r, n + r, device=x.device)
+    idx = idx % (2 * n)
+    idx = torch.where(idx >= n, 2 * n - 1 - idx, idx)
+    return x.index_select(dim, idx)
+
+
 def _gaussian_blur(maps: torch.Tensor, sigma: float = 3.0) -> torch.Tensor:
-    """[c, h, w] -> smoothed (separable kernel truncated at 4 sigma, reflect borders: scipy.ndimage.gaussian_filter)."""
+    """[c, h, w] -> smoothed exactly as scipy.ndimage.gaussian_filter does (kernel truncated at 4 sigma, its borders)."""
     r = int(4 * sigma + 0.5)
     k = torch.exp(-0.5 * (torch.arange(-r, r + 1, dtype=maps.dtype, device=maps.device) / sigma) ** 2)
     k = k / k.sum()
     x = maps[:, None]
-    pad = lambda t, p: F.pad(t, p, mode="reflect") if min(t.shape[-2:]) > r else F.pad(t, p, mode="replicate")  # noqa: E731
-    x = F.conv2d(pad(x, (r, r, 0, 0)), k.view(1, 1, 1, -1))
-    x = F.conv2d(pad(x, (0, 0, r, r)), k.view(1, 1, -1, 1))
+    x = F.conv2d(_symmetric_pad(x, r, 3), k.view(1, 1, 1, -1))
+    x = F.conv2d(_symmetric_pad(x, r, 2), k.view(1, 1, -1, 1))
     return x[:, 0]
 
 

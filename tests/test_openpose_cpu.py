@@ -114,3 +114,14 @@ def test_rendering_uses_the_training_colours():
     assert mid.tolist() == [int(c * 0.6) for c in op.COLORS[2]]
     empty = op.draw_poses((64, 48), np.zeros((0, 4)), np.zeros((0, 20)))
     assert not np.asarray(empty).any()
+
+
+def test_heat_map_smoothing_is_scipy_gaussian_filter():
+    """The original smooths every heat map with scipy.ndimage.gaussian_filter(sigma=3) before looking for peaks."""
+    from scipy.ndimage import gaussian_filter
+
+    rng = np.random.default_rng(0)
+    for shape in ((2, 40, 50), (1, 5, 7), (1, 30, 9)):  # maps smaller than the 25-tap kernel included
+        m = rng.random(shape).astype(np.float32)
+        want = np.stack([gaussian_filter(x, sigma=3) for x in m])
+        assert np.abs(op._gaussian_blur(torch.from_numpy(m)).numpy() - want).max() < 1e-6
