@@ -1,6 +1,7 @@
 """AudioLDM driver (reference: `AudioLDMPipeline`, swarm/audio/audioldm.py:19-24).  CLAP text
-embedding -> class-conditioned UNet2DCondition over mel-spectrogram latents (this framework's UNet
-with `class_embed_type="simple_projection"` semantics handled as an added embedding) -> VAE decode
+embedding -> class-conditioned UNet2DCondition over mel-spectrogram latents (this framework's UNet:
+`class_embed_type="simple_projection"`, `class_embeddings_concat`, no cross-attention width -- every attn2 is a second
+self-attention, as `encoder_hidden_states=None` makes it in diffusers) -> VAE decode
 to a mel spectrogram -> HiFi-GAN vocoder.  CLAP and the vocoder are transformers models
 (ClapTextModelWithProjection, SpeechT5HifiGan) loaded from the local checkpoint; without a local
 checkpoint the job fails as a fatal (non-resubmittable) error, exactly like any other missing model."""
@@ -41,12 +42,8 @@ class AudioLDMPipeline:
         self.tokenizer = RobertaTokenizerFast.from_pretrained(str(root / "tokenizer"))
         self.text_encoder = ClapTextModelWithProjection.from_pretrained(str(root / "text_encoder")).to(self.device, self.dtype)
         self.vocoder = SpeechT5HifiGan.from_pretrained(str(root / "vocoder")).to(self.device, self.dtype)
-        # AudioLDM conditions through a projected class embedding of the CLAP vector
-        cdim = self.unet.config.get("projection_class_embeddings_input_dim") or self.text_encoder.config.projection_dim
-        self.class_proj = torch.nn.Linear(cdim, self.unet.config["block_out_channels"][0] * 4).to(self.device, self.dtype)
-        sd = checkpoints.load_state_dict(checkpoints.find_weights(root / "unet"))
-        if "class_embedding.weight" in sd:
-            self.class_proj.load_state_dict({"weight": sd["class_embedding.weight"], "bias": sd["class_embedding.bias"]})
+        if self.unet.class_embedding is None:
+            raise ValueError("not an AudioLDM UNet: it has no class embedding for the CLAP text vector")
         self.scheduler_config = checkpoints.component_config(root, "scheduler") or schedulers.SD_SCHEDULER_CONFIG
         self.scheduler_kind = "dpmpp_2m"
 
@@ -77,32 +74,19 @@ class AudioLDMPipeline:
         do_cfg = guidance_scale > 1.0
         cond = clap(prompt)
         emb = torch.cat([clap(negative_prompt or ""), cond]) if do_cfg else cond
-        class_emb = self.class_proj(emb)
         plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), self.scheduler_config, False)
         shape = (1, self.unet.config["in_channels"], height // vae_scale, n_mel // vae_scale)
         x = torch.randn(shape, generator=generator, device=self.device, dtype=self.dtype).float() * plan.init_noise_sigma
         x0_prev, scale, n_cond = None, plan.first_scale, (2 if do_cfg else 1)
-        ctx = torch.zeros(n_cond, 1, self.unet.config["cross_attention_dim"] or 8, device=self.device, dtype=self.dtype)
         for i in range(plan.num_steps):
             t = torch.tensor(float(plan.timesteps[i]), device=self.device)
             model_in = torch.cat([x] * n_cond).to(self.dtype) * scale
-            temb = self.unet.time_embed(t, model_in.shape[0], self.dtype) + class_emb
-            out = self._unet_with_emb(model_in, temb, ctx)
+            # no text sequence: the CLAP vector is the class label (added or concatenated to the time embedding, as the
+            # checkpoint's config says) and every attn2 is a second self-attention (encoder_hidden_states=None)
+            out = self.unet(model_in, t, None, class_labels=emb)
             out = schedulers.guided(out.float(), n_cond, float(guidance_scale))
             x, x0_prev, scale = schedulers.apply_step_torch(plan, i, x, out, x0_prev, None)
         mel = self.vae.decode((x / self.vae.scaling_factor).to(self.dtype))
         wave = self.vocoder(mel.squeeze(1) if mel.dim() == 4 else mel).float().cpu().numpy()
         n = int(audio_length_in_s * self.vocoder.config.sampling_rate)
         return AudioOutput(audios=wave[:, :n])
-
-    def _unet_with_emb(self, sample, emb, ctx):
-        u = self.unet
-        x = u.conv_in(sample)
-        skips = [x]
-        for blk in u.down_blocks:
-            x, outs = blk(x, emb, ctx)
-            skips.extend(outs)
-        x = u.mid_block(x, emb, ctx)
-        for blk in u.up_blocks:
-            x = blk(x, skips, emb, ctx)
-        return u.conv_out(torch.nn.functional.silu(u.conv_norm_out(x)))

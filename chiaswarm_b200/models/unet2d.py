@@ -273,6 +273,10 @@ class UNet2DConditionModel(nn.Module):
         temb_dim = boc[0] * 4
         layers = _as_list(c["layers_per_block"], n)
         cross = c["cross_attention_dim"]
+        if isinstance(cross, (list, tuple)):  # (per-block lists appear in some configs; this UNet takes one width)
+            if len({x for x in cross}) > 1:
+                raise ValueError(f"per-block cross_attention_dim {cross} is not supported")
+            cross = cross[0]
         depth = _as_list(c.get("transformer_layers_per_block", 1), n)
         ulp = c.get("use_linear_projection", False)
         # `attention_head_dim` is the number of heads for SD1.x/2.x checkpoints (appendix A.7);
@@ -292,6 +296,14 @@ class UNet2DConditionModel(nn.Module):
             self.class_embedding = nn.Embedding(c["num_class_embeds"], temb_dim)
         elif c.get("class_embed_type") == "timestep":
             self.class_embedding = TimestepEmbedding(boc[0], temb_dim)
+        elif c.get("class_embed_type") == "simple_projection":  # AudioLDM: a Linear of the CLAP text embedding
+            self.class_embedding = nn.Linear(c["projection_class_embeddings_input_dim"], temb_dim)
+        elif c.get("class_embed_type") is not None:
+            raise ValueError(f"class_embed_type {c['class_embed_type']} is not supported")
+        # AudioLDM concatenates the class embedding to the time embedding instead of adding it: every resnet then
+        # projects a vector twice as wide
+        self.class_embeddings_concat = bool(c.get("class_embeddings_concat", False))
+        temb_dim = temb_dim * 2 if self.class_embeddings_concat else temb_dim
 
         self.down_blocks = nn.ModuleList()
         ch = boc[0]
@@ -332,7 +344,10 @@ class UNet2DConditionModel(nn.Module):
         if self.class_embedding is not None and class_labels is not None:
             if isinstance(self.class_embedding, TimestepEmbedding):
                 class_labels = timestep_embedding(class_labels, c["block_out_channels"][0]).to(dtype)
-            emb = emb + self.class_embedding(class_labels)
+            class_emb = self.class_embedding(class_labels.to(dtype) if class_labels.is_floating_point() else class_labels)
+            emb = torch.cat([emb, class_emb], dim=-1) if self.class_embeddings_concat else emb + class_emb
+        elif self.class_embeddings_concat:
+            raise ValueError("this UNet concatenates a class embedding to the time embedding: class_labels are required")
         return emb
 
     def forward(self, sample, timestep, encoder_hidden_states, down_residuals: Optional[Sequence] = None,

@@ -37,24 +37,24 @@ def _tiny_audioldm(root):
     from chiaswarm_b200.models.vae import AutoencoderKL
     from chiaswarm_b200.utils import checkpoints
 
+    # the layout of cvssp/audioldm*/unet: the CLAP vector enters as a "simple_projection" class embedding CONCATENATED to the
+    # time embedding, there is no cross-attention width (every attn2 is a second self-attention)
     unet = _init_module(UNet2DConditionModel(in_channels=4, out_channels=4, block_out_channels=(32, 64), layers_per_block=1,
                                              down_block_types=("DownBlock2D", "CrossAttnDownBlock2D"),
                                              up_block_types=("CrossAttnUpBlock2D", "UpBlock2D"), attention_head_dim=4,
-                                             cross_attention_dim=8, norm_num_groups=32, sample_size=8,
+                                             cross_attention_dim=None, norm_num_groups=32, sample_size=8,
+                                             class_embed_type="simple_projection", class_embeddings_concat=True,
                                              projection_class_embeddings_input_dim=16), 1)
+    assert unet.class_embedding.weight.shape == (128, 16)
+    assert unet.down_blocks[0].resnets[0].time_emb_proj.weight.shape == (32, 256)      # twice the time-embedding width
+    assert unet.down_blocks[1].attentions[0].transformer_blocks[0].attn2.to_k.weight.shape == (64, 64)
+    with torch.no_grad():
+        unet.class_embedding.weight.copy_(torch.randn(128, 16, generator=torch.Generator().manual_seed(5)) * 0.2)
     vae = _init_module(AutoencoderKL(in_channels=1, out_channels=1, latent_channels=4, block_out_channels=(32, 64),
                                      layers_per_block=1, norm_num_groups=32, scaling_factor=0.9), 2)
     checkpoints.save_diffusers_layout(root, {"unet": unet, "vae": vae}, {"_class_name": "AudioLDMPipeline"},
                                       {"num_train_timesteps": 1000, "beta_start": 0.0015, "beta_end": 0.0195,
                                        "beta_schedule": "scaled_linear", "prediction_type": "epsilon"})
-    # the CLAP class projection lives in the UNet checkpoint as class_embedding.{weight,bias}
-    from safetensors.torch import load_file, save_file
-
-    w = load_file(str(root / "unet" / "diffusion_pytorch_model.safetensors"))
-    g = torch.Generator().manual_seed(5)
-    w["class_embedding.weight"] = torch.randn(128, 16, generator=g) * 0.2
-    w["class_embedding.bias"] = torch.zeros(128)
-    save_file(w, str(root / "unet" / "diffusion_pytorch_model.safetensors"))
 
     tok = Tokenizer(models.BPE(unk_token="<unk>"))
     tok.pre_tokenizer = pre_tokenizers.ByteLevel(add_prefix_space=False)
