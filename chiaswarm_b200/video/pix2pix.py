@@ -29,6 +29,12 @@ from ..utils.weight_cache import pipeline_cache
 import os
 
 MAX_FRAMES = 100
+def frame_height() -> int:
+    """Working height of the frames: 512 as in the reference (swarm/video/pix2pix.py:163); SDAAS_VIDEO_HEIGHT overrides it
+    (smaller for CPU tests, larger for a B200 that has the memory for it)."""
+    return max(8, int(os.environ.get("SDAAS_VIDEO_HEIGHT", "512")))
+
+
 FRAME_BATCH = int(os.environ.get("SDAAS_FRAME_BATCH", "8"))  # frames per denoising run (CFG x3 -> 24 UNet samples at 512 px)
 
 
@@ -66,7 +72,8 @@ def model_video_callback(device_identifier, model_name, **kwargs):
             print(f"frames {chunk[0]}-{chunk[-1]} of {len(frames)}")
             g = torch.Generator(device=device).manual_seed((base_seed + chunk[0]) % (2 ** 63))
             images, flagged = img2img(pipeline, prompt, guidance_scale, image_guidance_scale,
-                                      [frames[i] for i in chunk], num_inference_steps, negative_prompt, 512, 512, g)
+                                      [frames[i] for i in chunk], num_inference_steps, negative_prompt, frame_height(),
+                                      frame_height(), g)
             nsfw = nsfw or flagged
             done.extend(im.convert("RGB") for im in images)
         if gang is not None:
@@ -160,8 +167,8 @@ def get_frames(temp_dir, video_in):
             if i >= next_keep:
                 next_keep += keep_every
                 h, w = frame.shape[:2]
-                scale = 512.0 / h
-                frame = cv2.resize(frame, (max(8, int(round(w * scale))), 512), interpolation=cv2.INTER_AREA)
+                target = frame_height()
+                frame = cv2.resize(frame, (max(8, int(round(w * target / h))), target), interpolation=cv2.INTER_AREA)
                 frames.append(Image.fromarray(cv2.cvtColor(frame, cv2.COLOR_BGR2RGB)))
             i += 1
     finally:

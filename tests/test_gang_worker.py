@@ -133,7 +133,8 @@ def test_vid2vid_frames_scatter_over_a_gang(gang_env, tmp_path, monkeypatch):
     from chiaswarm_b200.parallel.gang_worker import GangScheduler
     from tests.test_workflows_cpu import _tiny_video
 
-    env = dict(gang_env, SDAAS_FRAME_BATCH="1", SDAAS_LOCAL_INPUTS="1", SDAAS_LOCAL_INPUT_ROOT=str(tmp_path))
+    env = dict(gang_env, SDAAS_FRAME_BATCH="1", SDAAS_LOCAL_INPUTS="1", SDAAS_LOCAL_INPUT_ROOT=str(tmp_path),
+               SDAAS_VIDEO_HEIGHT="96")
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     from chiaswarm_b200.video import pix2pix
@@ -163,7 +164,9 @@ def test_vid2vid_frames_scatter_over_a_gang(gang_env, tmp_path, monkeypatch):
     finally:
         sched.stop()
     assert len(ref) == len(got) == 3
-    assert max(float(np.abs(a - b).max()) for a, b in zip(ref, got)) <= 2.0
+    # same frames up to fp32 reduction order (the ranks run with fewer threads) seen through a lossy codec
+    assert max(float(np.abs(a - b).mean()) for a, b in zip(ref, got)) <= 0.5
+    assert max(float(np.abs(a - b).max()) for a, b in zip(ref, got)) <= 6.0
 
 
 def test_txt2vid_on_a_gang_scatters_the_decode(gang_env):

@@ -155,8 +155,11 @@ def _video_frames(artifact, tmp_path):
 
 def test_vid2vid_job_batches_frames_and_returns_a_video(tmp_path, monkeypatch):
     """Video-to-video (instruct-pix2pix per frame, swarm/video/pix2pix.py): 5 frames go through the pipeline in
-    chunks of FRAME_BATCH instead of one call per frame, and every frame comes back (fitted into 512 x 512)."""
+    chunks of FRAME_BATCH instead of one call per frame, and every frame comes back at the working height (512 in
+    production; 96 here to keep the CPU run short)."""
     from chiaswarm_b200.video import pix2pix
+
+    monkeypatch.setenv("SDAAS_VIDEO_HEIGHT", "96")
 
     calls = []
     real = pix2pix.img2img
@@ -175,7 +178,7 @@ def test_vid2vid_job_batches_frames_and_returns_a_video(tmp_path, monkeypatch):
     art = r["artifacts"]["primary"]
     assert art["content_type"] == "video/mp4"
     frames = _video_frames(art, tmp_path)
-    assert len(frames) == 5 and max(frames[0].shape[:2]) <= 512 and min(frames[0].shape[:2]) >= 256
+    assert len(frames) == 5 and frames[0].shape[:2] == (72, 96)  # 4:3 frames fitted into the height x height box
     assert r["pipeline_config"]["cost"] == 512 * 512 * 2 * 5
 
 
