@@ -25,6 +25,7 @@ _DEFAULTS = {
     "model_root": "",            # directory holding diffusers-layout checkpoints (HF cache also searched)
     "weight_cache_gb": 120,      # resident weight cache budget per GPU
     "result_retries": 3,         # bounded retry for POST /api/results (reference drops on failure)
+    "result_spool": "spool",     # results the hive did not take are kept here (under SDAAS_ROOT) and re-sent later; "" = drop
     "metrics_port": 0,           # > 0: serve Prometheus text at http://<metrics_host>:<port>/metrics (utils/metrics.py)
     "metrics_host": "127.0.0.1",
 }
@@ -32,7 +33,7 @@ _DEFAULTS = {
 _ENV = {"sdaas_token": "SDAAS_TOKEN", "sdaas_uri": "SDAAS_URI", "worker_name": "SDAAS_WORKERNAME",
         "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE", "job_timeout_s": "SDAAS_JOB_TIMEOUT_S", "patch_min_pixels": "SDAAS_PATCH_MIN_PIXELS",
         "kernel_backend": "SDAAS_KERNEL_BACKEND", "model_root": "SDAAS_MODEL_ROOT",
-        "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
+        "result_spool": "SDAAS_RESULT_SPOOL", "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
 
 
 class Settings:
@@ -50,6 +51,7 @@ class Settings:
     model_root: str = _DEFAULTS["model_root"]
     weight_cache_gb: int = _DEFAULTS["weight_cache_gb"]
     result_retries: int = _DEFAULTS["result_retries"]
+    result_spool: str = _DEFAULTS["result_spool"]
     metrics_port: int = _DEFAULTS["metrics_port"]
     metrics_host: str = _DEFAULTS["metrics_host"]
 

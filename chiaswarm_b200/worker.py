@@ -11,7 +11,8 @@ What differs from the reference:
   * a lane is a `Device` of this process (one GPU per job) plus one CPU lane for pure-CPU workflows
     (stitch) so they do not occupy a GPU (Q10); in gang mode (`settings.parallel_mode` != "dp",
     parallel/gang_worker.py) a lane instead leases 1 / 2 / 4 / 8 rank processes from the RankGroup per job;
-  * results that fail to POST are retried a bounded number of times instead of dropped (Q14);
+  * results that fail to POST are retried a bounded number of times instead of dropped (Q14), then spooled to disk
+    (`settings.result_spool`) and re-sent once the hive takes results again, also after a worker restart;
   * polls, jobs, job times, uploads and queue depths are counted (utils/metrics.py) and served as Prometheus text at
     `/metrics` when `settings.metrics_port` is set (the reference has no metrics at all);
   * `Worker` is an object (testable against a fake hive) -- the module-level functions
@@ -109,6 +110,8 @@ class Worker:
         if self.cpu_lane:
             self._tasks.append(asyncio.create_task(self.cpu_worker()))
         self._tasks.append(asyncio.create_task(self.result_worker()))
+        if self._spool_dir() is not None and any(self._spool_dir().glob("*.json")):
+            self._flush_task = asyncio.create_task(self.flush_spool())  # results a previous run could not deliver
         try:
             while max_polls is None or self.polls < max_polls:
                 while self.work_queue.full():
@@ -123,6 +126,10 @@ class Worker:
         await self.work_queue.join()
         await self.cpu_queue.join()
         await self.result_queue.join()
+        flush = getattr(self, "_flush_task", None)
+        if flush is not None:  # let a start-up re-send finish: cancelling it between POST and unlink would send twice
+            await asyncio.gather(flush, return_exceptions=True)
+            self._flush_task = None
         for t in self._tasks:
             t.cancel()
         await asyncio.gather(*self._tasks, return_exceptions=True)
@@ -245,9 +252,11 @@ class Worker:
             result = await self.result_queue.get()
             try:
                 attempts = max(1, int(getattr(self.settings, "result_retries", 1)))
+                delivered = False
                 for attempt in range(attempts):
                     try:
                         if await self.submit_result(result):
+                            delivered = True
                             break
                     except asyncio.CancelledError:
                         raise
@@ -257,8 +266,62 @@ class Worker:
                         self.metrics.inc("swarm_results_posted_total", {"outcome": "failed"})
                     if attempt + 1 < attempts:
                         await backoff(min(2 ** attempt, 30))
+                if delivered:
+                    await self.flush_spool()  # the hive is taking results again: hand over what it missed
+                else:
+                    self.spool_result(result)
             finally:
                 self.result_queue.task_done()
+
+    # ------------------------------------------------------------------ undelivered results
+    SPOOL_LIMIT = 256  # files; beyond it the oldest are dropped (a result is a few hundred KB of base64)
+
+    def _spool_dir(self):
+        name = getattr(self.settings, "result_spool", "") or ""
+        return resolve_path(f"{name}/.keep").parent if name else None
+
+    def spool_result(self, result) -> bool:
+        """A result the hive did not take (outage, 500s) is written under `settings.result_spool` instead of being
+        dropped as in the reference (swarm/worker.py:131-142); `flush_spool` re-sends it."""
+        folder = self._spool_dir()
+        if folder is None:
+            return False
+        try:
+            safe = "".join(ch if ch.isalnum() or ch in "-_" else "_" for ch in str(result.get("id", "job")))[:64]
+            path = folder / f"{time.time_ns()}-{safe}.json"
+            path.write_text(json.dumps(result))
+            files = sorted(folder.glob("*.json"))
+            for old in files[:-self.SPOOL_LIMIT]:
+                old.unlink(missing_ok=True)
+            self.metrics.inc("swarm_results_posted_total", {"outcome": "spooled"})
+            return True
+        except Exception as e:  # a full disk must not take the result loop down
+            logging.exception(e)
+            return False
+
+    async def flush_spool(self) -> int:
+        """Re-sends spooled results, oldest first; stops at the first one the hive does not take."""
+        folder = self._spool_dir()
+        if folder is None:
+            return 0
+        sent = 0
+        for path in sorted(folder.glob("*.json")):
+            try:
+                result = json.loads(path.read_text())
+            except Exception:
+                path.unlink(missing_ok=True)  # unreadable: nothing to deliver
+                continue
+            try:
+                if not await self.submit_result(result):
+                    break
+            except asyncio.CancelledError:
+                raise
+            except Exception as e:
+                logging.exception(e)
+                break
+            path.unlink(missing_ok=True)
+            sent += 1
+        return sent
 
 
 # ---------------------------------------------------------------- module-level surface

@@ -210,3 +210,43 @@ def test_metrics_are_counted_and_served():
     assert 'workflow="we\\"ird\\n"' in text
     assert 'swarm_job_seconds_bucket{le="0.1"} 1' in text and 'swarm_job_seconds_bucket{le="0.5"} 2' in text
     assert 'swarm_job_seconds_bucket{le="900"} 3' in text and 'swarm_job_seconds_bucket{le="+Inf"} 4' in text
+
+
+def test_undelivered_results_are_spooled_and_resent(tmp_path):
+    """The reference drops a result whose POST fails (swarm/worker.py:131-142); here it survives a hive outage and a
+    worker restart."""
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        try:
+            async def fast_sleep(s):
+                await asyncio.sleep(0)
+
+            w = _worker(uri, retries=2)
+            w.result_worker.__func__.__defaults__ = (fast_sleep,)
+            hive.jobs = [{"id": "lost/../one", "workflow": "stitch", "model_name": "x", "jobs": []}]
+            hive.fail_results = 99                                   # the hive takes no results at all
+            await w.run(max_polls=1, sleep=fast_sleep)
+            spool = tmp_path / "spool"
+            files = list(spool.glob("*.json"))
+            assert hive.results == [] and len(files) == 1 and "/" not in files[0].name[len(str(spool)):]
+            assert json.loads(files[0].read_text())["id"] == "lost/../one"
+            assert w.metrics.value("swarm_results_posted_total", {"outcome": "spooled"}) == 1
+
+            hive.fail_results = 0                                    # the hive is back; a NEW worker process starts
+            w2 = _worker(uri)
+            w2.result_worker.__func__.__defaults__ = (fast_sleep,)
+            await w2.run(max_polls=1, sleep=fast_sleep)
+            for _ in range(50):
+                if hive.results:
+                    break
+                await asyncio.sleep(0.05)
+            assert [r["id"] for r in hive.results] == ["lost/../one"] and not list(spool.glob("*.json"))
+            # spooling can be switched off: then the result is dropped as in the reference
+            w3 = _worker(uri, retries=1)
+            w3.settings.result_spool = ""
+            assert w3.spool_result({"id": "x"}) is False and await w3.flush_spool() == 0
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
