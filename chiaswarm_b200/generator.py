@@ -12,12 +12,13 @@ import logging
 
 from . import __version__
 from .job_arguments import format_args
-from .output_processor import image_from_text, image_to_buffer, make_result, make_text_result
+from .output_processor import (DeferredArtifact, deferring_packaging, image_from_text, image_to_buffer, make_result,
+                               make_text_result)
 
 
-async def do_work(job, device):
+async def do_work(job, device, defer_packaging: bool = False):
     loop = asyncio.get_running_loop()
-    return await loop.run_in_executor(None, synchronous_do_work_function, job, device)
+    return await loop.run_in_executor(None, synchronous_do_work_function, job, device, defer_packaging)
 
 
 def _error_result(job_id, job, exc, fatal):
@@ -39,7 +40,9 @@ def _error_result(job_id, job, exc, fatal):
     return result
 
 
-def synchronous_do_work_function(job, device):
+def synchronous_do_work_function(job, device, defer_packaging: bool = False):
+    """`defer_packaging`: image artifacts come back as `DeferredArtifact`s (encoding not done yet); the caller finishes
+    them with `materialize_result` -- the serve loop does that on its result thread, off the GPU lane."""
     job_id = job.pop("id")
     print(f"Processing {job_id} on {device.descriptor()}")
 
@@ -49,20 +52,41 @@ def synchronous_do_work_function(job, device):
         return _error_result(job_id, job, e, fatal=True)
 
     try:
-        artifacts, pipeline_config = device(worker_function, **kwargs)
+        with deferring_packaging(defer_packaging):
+            artifacts, pipeline_config = device(worker_function, **kwargs)
     except ValueError as e:  # generation says the request itself is unsatisfiable
         return _error_result(job_id, job, e, fatal=True)
     except Exception as e:
         logging.exception(e)
         return _error_result(job_id, job, e, fatal=False)
 
-    return {
+    result = {
         "id": job_id,
         "artifacts": artifacts,
         "nsfw": pipeline_config.get("nsfw", False),
         "worker_version": __version__,
         "pipeline_config": pipeline_config,
     }
+    if defer_packaging:
+        result["_job"] = {"content_type": job.get("content_type", "image/jpeg")}  # for an error raised while encoding
+    return result
+
+
+def materialize_result(result: dict) -> dict:
+    """Runs the encoding a deferred result still owes.  An encoding failure becomes the error result the synchronous path
+    would have produced (ValueError: fatal, e.g. more images than the grid holds; anything else: retryable)."""
+    job = result.pop("_job", None) or {}
+    artifacts = result.get("artifacts") or {}
+    try:
+        for name, value in list(artifacts.items()):
+            if isinstance(value, DeferredArtifact):
+                artifacts[name] = value.resolve()
+    except ValueError as e:
+        return _error_result(result.get("id"), job, e, fatal=True)
+    except Exception as e:
+        logging.exception(e)
+        return _error_result(result.get("id"), job, e, fatal=False)
+    return result
 
 
 def _message(e):

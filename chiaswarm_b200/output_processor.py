@@ -9,6 +9,7 @@ import base64
 import hashlib
 import io
 import json
+import threading
 from io import BytesIO
 
 from PIL import Image, ImageDraw
@@ -17,6 +18,44 @@ from PIL import Image, ImageDraw
 _GRID_FOR_COUNT = {2: (1, 2), 3: (2, 2), 4: (2, 2), 5: (2, 3), 6: (2, 3), 7: (3, 3), 8: (3, 3), 9: (3, 3)}
 MAX_GRID_IMAGES = 9
 THUMB_BOX = (100, 100)
+
+
+_tls = threading.local()
+
+
+class DeferredArtifact:
+    """An artifact whose encoding (grid, JPEG / PNG, thumbnail, base64, sha256) has not run yet.  The serve loop asks for
+    these (`generator.synchronous_do_work_function(..., defer_packaging=True)`) so that a GPU lane starts its next job
+    while a result thread encodes the previous one; `resolve()` gives the wire dictionary."""
+
+    def __init__(self, pack):
+        self._pack, self._value = pack, None
+
+    def resolve(self) -> dict:
+        if self._value is None:
+            self._value = self._pack()
+            self._pack = None
+        return self._value
+
+
+def packaging_deferred() -> bool:
+    return bool(getattr(_tls, "defer", False))
+
+
+class deferring_packaging:
+    """`with deferring_packaging(flag):` -- OutputProcessors of this thread hand out DeferredArtifacts."""
+
+    def __init__(self, flag: bool = True):
+        self.flag = bool(flag)
+
+    def __enter__(self):
+        self.prev = packaging_deferred()
+        _tls.defer = self.flag
+        return self
+
+    def __exit__(self, *exc):
+        _tls.defer = self.prev
+        return False
 
 
 def _b64(data: bytes) -> str:
@@ -125,9 +164,15 @@ class OutputProcessor:
         return make_result(image_to_buffer(sheet, self.main_content_type), sheet, self.main_content_type)
 
     def get_results(self):
+        defer = packaging_deferred()
+
+        def pack(images):
+            images = list(images)
+            return DeferredArtifact(lambda: self._pack(images)) if defer else self._pack(images)
+
         results = {}
         if "primary" in self.output_list:
-            results["primary"] = self._pack(self.outputs)
+            results["primary"] = pack(self.outputs)
         for name, images in self.other_outputs.items():
-            results[name] = self._pack(images)
+            results[name] = pack(images)
         return results

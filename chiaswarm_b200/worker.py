@@ -30,7 +30,7 @@ from typing import List, Optional
 import aiohttp
 
 from . import __version__
-from .generator import do_work
+from .generator import do_work, materialize_result
 from .gpu.device import Device
 from .log_setup import setup_logging
 from .settings import Settings, load_settings, resolve_path
@@ -196,7 +196,7 @@ class Worker:
     async def execute(self, job, device):
         """One job on one lane.  Here: the in-process Device (one GPU per job, as in the reference);
         parallel.gang_worker.GangWorker overrides it to lease a gang of rank processes instead."""
-        return await do_work(job, device)
+        return await do_work(job, device, defer_packaging=True)  # encoded by the result worker, off this lane
 
     async def _counted(self, job, run):
         """Runs one job and accounts for it (count by workflow / outcome, wall time, busy lanes)."""
@@ -238,7 +238,7 @@ class Worker:
         while True:
             job = await self.cpu_queue.get()
             try:
-                await self.result_queue.put(await self._counted(job, lambda: do_work(job, cpu)))
+                await self.result_queue.put(await self._counted(job, lambda: do_work(job, cpu, defer_packaging=True)))
             except asyncio.CancelledError:
                 raise
             except Exception as e:
@@ -251,6 +251,9 @@ class Worker:
         while True:
             result = await self.result_queue.get()
             try:
+                # image encoding (grid, JPEG, thumbnail, base64, hash) runs here, on an executor thread, while the lane
+                # that produced the result is already denoising its next job
+                result = await asyncio.get_running_loop().run_in_executor(None, materialize_result, result)
                 attempts = max(1, int(getattr(self.settings, "result_retries", 1)))
                 delivered = False
                 for attempt in range(attempts):

@@ -251,3 +251,28 @@ def test_device_is_exclusive_and_seeds():
     assert out["r"][1] == {"generator_seed": 7, "seed": 7}
     _, cfg = d(lambda i, m, **kw: ({}, {}), model_name="m")
     assert isinstance(cfg["seed"], int)
+
+
+def test_deferred_packaging_gives_the_same_result_off_the_lane():
+    """The serve loop takes results with their image encoding still owed and finishes them on the result thread."""
+    from chiaswarm_b200.generator import materialize_result, synchronous_do_work_function
+    from chiaswarm_b200.gpu.device import Device
+    from chiaswarm_b200.output_processor import DeferredArtifact, packaging_deferred
+
+    job = {"id": "d1", "model_name": "tiny-sd", "prompt": "p", "height": 64, "width": 64, "num_inference_steps": 1, "seed": 9,
+           "content_type": "image/png"}
+    dev = Device("cpu")
+    plain = synchronous_do_work_function(dict(job), dev)
+    lazy = synchronous_do_work_function(dict(job), dev, defer_packaging=True)
+    assert isinstance(lazy["artifacts"]["primary"], DeferredArtifact) and not packaging_deferred()
+    assert lazy["pipeline_config"]["seed"] == 9 and lazy["id"] == "d1"
+    done = materialize_result(lazy)
+    assert "_job" not in done and done == plain                       # same PNG, thumbnail and hash
+    assert materialize_result(dict(plain)) == plain                   # results that owe nothing pass through
+    # an error that only shows while encoding (more images than the contact grid holds) becomes the same fatal result
+    many = dict(job, id="d2", num_images_per_prompt=10)
+    want = synchronous_do_work_function(dict(many), dev)
+    got = materialize_result(synchronous_do_work_function(dict(many), dev, defer_packaging=True))
+    assert want["fatal_error"] is True and "Too many images" in want["pipeline_config"]["error"]
+    assert got["fatal_error"] is True and got["pipeline_config"] == want["pipeline_config"] and got["id"] == "d2"
+    assert got["artifacts"]["primary"]["content_type"] == "image/png"
