@@ -13,6 +13,9 @@ What differs from the reference:
     parallel/gang_worker.py) a lane instead leases 1 / 2 / 4 / 8 rank processes from the RankGroup per job;
   * results that fail to POST are retried a bounded number of times instead of dropped (Q14), then spooled to disk
     (`settings.result_spool`) and re-sent once the hive takes results again, also after a worker restart;
+  * a lane does not encode its own results: `do_work(..., defer_packaging=True)` returns with the image encoding owed and
+    the result worker finishes it (`generator.materialize_result`) on an executor thread while the lane is already
+    denoising its next job (10-40 ms of JPEG / thumbnail / base64 / hash work per image off the GPU's critical path);
   * polls, jobs, job times, uploads and queue depths are counted (utils/metrics.py) and served as Prometheus text at
     `/metrics` when `settings.metrics_port` is set (the reference has no metrics at all);
   * `Worker` is an object (testable against a fake hive) -- the module-level functions
