@@ -20,9 +20,13 @@ def generate_audio(prompt, device, model_name="suno/bark"):
         raise ValueError(f"Model {model_name} is not available locally")
     from transformers import AutoProcessor, BarkModel
 
-    processor = AutoProcessor.from_pretrained(str(root))
-    model = BarkModel.from_pretrained(str(root), torch_dtype=torch.float16 if str(device).startswith("cuda") else torch.float32)
-    model = model.to(device)
+    from ..utils.weight_cache import pipeline_cache
+
+    dtype = torch.float16 if str(device).startswith("cuda") else torch.float32
+    # resident between jobs (the reference's `preload_models()` re-reads them for every job)
+    processor, model = pipeline_cache().get(
+        ("bark", str(root), str(device)),
+        lambda: (AutoProcessor.from_pretrained(str(root)), BarkModel.from_pretrained(str(root), torch_dtype=dtype).to(device).eval()))
     inputs = processor(prompt).to(device)
     with torch.no_grad():
         audio = model.generate(**inputs)

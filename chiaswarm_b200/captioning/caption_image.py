@@ -8,6 +8,7 @@ import torch
 from ..output_processor import make_text_result
 from ..type_helpers import get_type
 from ..utils import checkpoints
+from ..utils.weight_cache import pipeline_cache
 
 
 def caption_callback(device_identifier, model_name, **kwargs):
@@ -22,8 +23,11 @@ def caption_callback(device_identifier, model_name, **kwargs):
         source = str(root) if root is not None else model_name
         on_gpu = str(device_identifier).startswith("cuda")
         dtype = torch.float16 if on_gpu else torch.float32
-        processor = processor_type.from_pretrained(source)
-        model = model_type.from_pretrained(source, torch_dtype=dtype).to(device_identifier)
+        # resident between jobs (the reference reloads processor and model from disk for every caption)
+        processor, model = pipeline_cache().get(
+            ("caption", source, params["processor_type"], params["model_type"], str(device_identifier)),
+            lambda: (processor_type.from_pretrained(source),
+                     model_type.from_pretrained(source, torch_dtype=dtype).to(device_identifier).eval()))
         image = kwargs["image"]
         if kwargs.get("prompt"):
             inputs = processor(image, kwargs["prompt"], return_tensors="pt")

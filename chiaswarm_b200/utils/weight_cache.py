@@ -10,16 +10,32 @@ from typing import Callable, Hashable
 
 
 def _nbytes(obj) -> int:
-    total = 0
-    seen = set()
-    for attr in ("unet", "vae", "text_encoder", "text_encoder_2", "controlnet"):
-        m = getattr(obj, attr, None)
-        if m is None or not hasattr(m, "parameters"):
-            continue
-        for p in m.parameters():
-            if id(p) not in seen:
-                seen.add(id(p))
-                total += p.numel() * p.element_size()
+    """Bytes of the parameters and buffers an entry keeps resident: the entry itself when it is a module, the modules in
+    a tuple / list / dict, or the modules held one attribute deep by a pipeline object (unet, vae, text encoders, vocoder,
+    ...).  Shared tensors count once."""
+    seen, total = set(), 0
+
+    def add(module):
+        nonlocal total
+        for t in list(module.parameters()) + list(module.buffers()):
+            if id(t) not in seen:
+                seen.add(id(t))
+                total += t.numel() * t.element_size()
+
+    def visit(x, depth):
+        if hasattr(x, "parameters") and hasattr(x, "buffers") and callable(x.parameters):
+            add(x)
+        elif isinstance(x, (tuple, list)):
+            for v in x:
+                visit(v, depth)
+        elif isinstance(x, dict):
+            for v in x.values():
+                visit(v, depth)
+        elif depth > 0 and hasattr(x, "__dict__"):
+            for v in vars(x).values():
+                visit(v, depth - 1)
+
+    visit(obj, 1)
     return total
 
 
