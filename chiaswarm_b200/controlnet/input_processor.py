@@ -114,12 +114,32 @@ def image_to_mlsd(image):
     return _gray3(canvas)
 
 
+_learned_cache = {}
+
+
+def _learned(kind: str, loader):
+    """A transformers-backed annotator, built once per process; a failed attempt (not cached locally, no network) is
+    remembered too, so later jobs go straight to the stand-in instead of retrying the hub."""
+    if kind not in _learned_cache:
+        try:
+            _learned_cache[kind] = loader()
+        except Exception as e:
+            logging.info("controlnet pre-processor %s: %s", kind, e)
+            _learned_cache[kind] = None
+    return _learned_cache[kind]
+
+
 def image_to_depth(image):
     try:
-        from transformers import pipeline
+        def load():
+            from transformers import pipeline
 
-        depth = pipeline("depth-estimation")(image)["depth"]
-        return _gray3(np.array(depth))
+            return pipeline("depth-estimation")
+
+        estimator = _learned("depth", load)
+        if estimator is None:
+            raise RuntimeError("no depth estimator")
+        return _gray3(np.array(estimator(image)["depth"]))
     except Exception:
         # fallback: defocus heuristic (sharp = near) so the control image has the right modality
         _stand_in("depth", "a defocus heuristic")
@@ -146,8 +166,11 @@ def image_to_segmentation(image):
         import torch
         from transformers import AutoImageProcessor, UperNetForSemanticSegmentation
 
-        proc = AutoImageProcessor.from_pretrained("openmmlab/upernet-convnext-small")
-        seg_model = UperNetForSemanticSegmentation.from_pretrained("openmmlab/upernet-convnext-small")
+        loaded = _learned("seg", lambda: (AutoImageProcessor.from_pretrained("openmmlab/upernet-convnext-small"),
+                                          UperNetForSemanticSegmentation.from_pretrained("openmmlab/upernet-convnext-small").eval()))
+        if loaded is None:
+            raise RuntimeError("no segmentation model")
+        proc, seg_model = loaded
         with torch.no_grad():
             out = seg_model(proc(image, return_tensors="pt").pixel_values)
         seg = proc.post_process_semantic_segmentation(out, target_sizes=[image.size[::-1]])[0].numpy()
