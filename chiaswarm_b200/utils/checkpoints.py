@@ -85,10 +85,20 @@ def find_weights(folder: Path, variant: Optional[str] = None) -> Optional[Path]:
                 p = folder / (f"{stem}.{v}{ext}" if v else f"{stem}{ext}")
                 if p.is_file():
                     return p
+                # sharded: <stem>.safetensors.index.json (variant: <stem>.safetensors.index.fp16.json) names the shards
+                idx = folder / (f"{stem}{ext}.index.{v}.json" if v else f"{stem}{ext}.index.json")
+                if idx.is_file():
+                    return idx
     return None
 
 
 def load_state_dict(path: Path) -> Dict[str, torch.Tensor]:
+    if path.suffix == ".json":  # a shard index: {"weight_map": {tensor name: shard file}}
+        shards = sorted(set(read_json(path)["weight_map"].values()))
+        out: Dict[str, torch.Tensor] = {}
+        for shard in shards:
+            out.update(load_state_dict(path.parent / shard))
+        return out
     if path.suffix == ".safetensors":
         from safetensors.torch import load_file
 

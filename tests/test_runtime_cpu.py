@@ -285,3 +285,30 @@ def test_stage_timer_and_watchdog():
             time.sleep(0.2)
     with Watchdog(5):
         pass
+
+
+def test_sharded_checkpoints_load_through_their_index(tmp_path):
+    """transformers / diffusers split large weight files: `<stem>.safetensors.index.json` maps tensors to shards."""
+    import json
+
+    from safetensors.torch import save_file
+
+    from chiaswarm_b200.utils import checkpoints
+
+    folder = tmp_path / "unet"
+    folder.mkdir()
+    a, b = {"x.weight": torch.ones(2, 2), "x.bias": torch.zeros(2)}, {"y.weight": torch.full((3,), 2.0)}
+    save_file(a, str(folder / "diffusion_pytorch_model-00001-of-00002.safetensors"))
+    save_file(b, str(folder / "diffusion_pytorch_model-00002-of-00002.safetensors"))
+    index = {"metadata": {}, "weight_map": {**{k: "diffusion_pytorch_model-00001-of-00002.safetensors" for k in a},
+                                            **{k: "diffusion_pytorch_model-00002-of-00002.safetensors" for k in b}}}
+    (folder / "diffusion_pytorch_model.safetensors.index.json").write_text(json.dumps(index))
+    found = checkpoints.find_weights(folder)
+    assert found is not None and found.name.endswith(".index.json")
+    sd = checkpoints.load_state_dict(found)
+    assert set(sd) == {"x.weight", "x.bias", "y.weight"} and torch.equal(sd["y.weight"], b["y.weight"])
+    # a single file wins over an index of the same stem; a variant index is found by its variant
+    (folder / "diffusion_pytorch_model.safetensors.index.json").rename(folder / "diffusion_pytorch_model.safetensors.index.fp16.json")
+    assert checkpoints.find_weights(folder, "fp16").name == "diffusion_pytorch_model.safetensors.index.fp16.json"
+    save_file(b, str(folder / "diffusion_pytorch_model.safetensors"))
+    assert checkpoints.find_weights(folder).name == "diffusion_pytorch_model.safetensors"
