@@ -2,9 +2,10 @@
 
 `python -m chiaswarm_b200.initialize [--reset] [--silent]` prompts for the hive URI and token,
 stores them, fetches `GET {uri}/api/models`, saves `models.json` and warms every pre-loadable
-model.  The reference warms the HuggingFace cache by downloading; this worker cannot assume a
-network, so warming means: locate the diffusers-layout checkpoint locally and load + pack it into
-the resident weight cache format, reporting what is missing.  The first-run prompt really is
+model.  The reference warms the HuggingFace cache by downloading; this worker does not assume a
+network: by default it locates the diffusers-layout checkpoints locally and reports what is missing,
+with `--download` it pulls the missing repositories into the HuggingFace cache first (configs, tokenizers
+and safetensors weights only).  The first-run prompt really is
 shown on first run here (the reference's `settings_exist` test is always true, Q8)."""
 from __future__ import annotations
 
@@ -22,6 +23,8 @@ async def init(argv=None, input_fn=input):
     parser = argparse.ArgumentParser()
     parser.add_argument("--reset", action="store_true", help="overwrite existing settings")
     parser.add_argument("--silent", action="store_true", help="do not prompt for input")
+    parser.add_argument("--download", action="store_true",
+                        help="fetch models that are not present locally from the HuggingFace hub (needs a network)")
     args = parser.parse_args(argv)
 
     exists = settings_exist()
@@ -43,13 +46,15 @@ async def init(argv=None, input_fn=input):
     print(f"Version {__version__}")
     print(f"Torch version {torch.__version__}")
     print("App initialization complete")
-    report = await download_diffusers(settings)
+    report = await download_diffusers(settings, fetch=args.download)
     print("To be the swarm type 'python -m chiaswarm_b200.worker'")
     return report
 
 
-async def download_diffusers(settings):
-    """Warm every model the hive knows. Returns {model_name: "ok" | "missing: ..."}."""
+async def download_diffusers(settings, fetch: bool = False):
+    """Warm every model the hive knows. Returns {model_name: "ok" | "downloaded" | "missing: ..."}.  `fetch`: models that
+    are not on the box are pulled into the HuggingFace cache first (the reference's only mode, swarm/initialize.py:62-94:
+    it downloads by instantiating every pipeline); without it nothing leaves the machine."""
     print("Downloading models...")
     from .utils.checkpoints import locate_checkpoint
 
@@ -61,13 +66,37 @@ async def download_diffusers(settings):
         parameters = model.pop("parameters", {})
         if not parameters.get("can_preload", True):
             continue
-        path = locate_checkpoint(model_name, revision=revision, variant=model.get("variant"),
-                                 model_root=getattr(settings, "model_root", ""))
-        report[model_name] = "ok" if path is not None else "missing: no local diffusers-layout checkpoint"
-        if path is None:
-            print(f"  {model_name}: not present locally (no network fetch on this worker)")
+        where = dict(revision=revision, variant=model.get("variant"), model_root=getattr(settings, "model_root", ""))
+        path = locate_checkpoint(model_name, **where)
+        state = "ok"
+        if path is None and fetch:
+            error = fetch_from_hub(model_name, revision, getattr(settings, "huggingface_token", None))
+            path = locate_checkpoint(model_name, **where)
+            state = "downloaded" if path is not None else f"missing: download failed ({error})"
+        elif path is None:
+            state = "missing: no local diffusers-layout checkpoint"
+            print(f"  {model_name}: not present locally (run with --download to fetch it)")
+        report[model_name] = state
     print("Model download complete")
     return report
+
+
+# what a worker reads from a model repository: configs, tokenizers, and the safetensors weights (fp16 variant preferred by
+# the loaders); the multi-GB .ckpt / .bin duplicates most repositories also carry are left on the hub
+HUB_PATTERNS = ["*.json", "*.txt", "*.model", "*.safetensors", "*.pth"]
+
+
+def fetch_from_hub(model_name: str, revision: str = "main", token=None):
+    """Pulls one repository into the HuggingFace cache.  Returns None on success, the reason otherwise (never raises)."""
+    try:
+        from huggingface_hub import snapshot_download
+
+        snapshot_download(model_name, revision=revision, allow_patterns=HUB_PATTERNS,
+                          token=token if isinstance(token, str) and token else None)
+        return None
+    except Exception as e:
+        print(f"  {model_name}: download failed: {e}")
+        return f"{type(e).__name__}: {e}"[:200]
 
 
 def get_models_from_hive(hive_uri):

@@ -240,6 +240,38 @@ def test_initialize_first_run_prompts_and_reports(tmp_path, monkeypatch):
     assert json.loads(settings.get_settings_full_path().read_text())["sdaas_token"] == "tok123"
 
 
+def test_initialize_download_fetches_what_is_missing(tmp_path, monkeypatch):
+    """`--download`: repositories that are not on the box are pulled into the HF cache (hub call stubbed: no network)."""
+    import huggingface_hub
+
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    monkeypatch.setenv("SDAAS_MODEL_ROOT", str(tmp_path / "models"))
+    from chiaswarm_b200 import initialize
+
+    monkeypatch.setattr(initialize, "get_models_from_hive", lambda uri: [
+        {"model_name": "org/fetchable", "revision": "main", "parameters": {}},
+        {"model_name": "org/unreachable", "revision": "main", "parameters": {}}])
+    calls = []
+
+    def fake_snapshot(repo, revision="main", allow_patterns=None, token=None):
+        calls.append((repo, revision, tuple(allow_patterns), token))
+        if repo == "org/unreachable":
+            raise OSError("no route to host")
+        root = tmp_path / "models" / "org" / "fetchable"
+        root.mkdir(parents=True)
+        (root / "model_index.json").write_text("{}")
+
+    monkeypatch.setattr(huggingface_hub, "snapshot_download", fake_snapshot)
+    report = asyncio.run(initialize.init(["--silent", "--download"]))
+    assert report["org/fetchable"] == "downloaded"
+    assert report["org/unreachable"].startswith("missing: download failed (OSError: no route to host")
+    assert [c[0] for c in calls] == ["org/fetchable", "org/unreachable"] and "*.safetensors" in calls[0][2]
+    assert all("*.ckpt" not in c[2] and "*.bin" not in c[2] for c in calls)
+    calls.clear()
+    report = asyncio.run(initialize.init(["--silent"]))                  # without the flag nothing leaves the machine
+    assert calls == [] and report["org/fetchable"] == "ok" and report["org/unreachable"].startswith("missing: no local")
+
+
 def test_type_helpers_and_registry():
     from chiaswarm_b200.registry import pipeline_names, scheduler_names
     from chiaswarm_b200.type_helpers import get_type, has_method
