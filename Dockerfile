@@ -21,9 +21,9 @@ ENV SDAAS_ROOT=/sdaas/ \
     SDAAS_TOKEN= \
     SDAAS_URI=https://chiaswarm.ai \
     SDAAS_WORKERNAME=b200_worker \
-    SWARM_PARALLEL_MODE=dp \
-    SWARM_GANG_SIZE=1
-# one process per visible GPU; SWARM_PARALLEL_MODE=patch + SWARM_GANG_SIZE=2|4|8 leases gangs for single-image jobs
+    SDAAS_PARALLEL_MODE=dp \
+    SDAAS_GANG_SIZE=1
+# one process per visible GPU; SDAAS_PARALLEL_MODE=patch + SDAAS_GANG_SIZE=2|4|8 leases gangs for single-image jobs
 CMD ["python", "-m", "chiaswarm_b200.parallel.launcher"]
 
 # docker build -t chiaswarm-b200 .
