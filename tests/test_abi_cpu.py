@@ -56,3 +56,46 @@ def test_every_header_struct_has_a_binding_and_every_entry_point_exists_in_the_l
     assert used, "binding calls not found"
     missing = sorted(n for n in used if n not in declared)
     assert not missing, f"bound but not declared in the header: {missing}"
+
+
+def test_argtypes_match_the_header_prototypes():
+    """Every function the binding declares `argtypes` for: same number of parameters as the header's prototype and the
+    same class per parameter (pointer / 32-bit int / 64-bit int / float).  A missing declaration truncates 64-bit
+    pointers to int -- the illegal-address failure this guards against."""
+    import re
+
+    from chiaswarm_b200.ops import native
+
+    if not native.LIB_PATH.exists():
+        pytest.skip("native library not built")
+    lib = native.lib()
+    header = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", "swarm_b200.h")).read(), flags=re.S)
+    protos = {m.group(1): m.group(2) for m in re.finditer(r"\b(sw_\w+)\s*\(([^()]*)\)\s*;", header)}
+
+    def c_class(param):
+        p = param.strip()
+        if "*" in p or "[" in p:
+            return "ptr"
+        if "float" in p:
+            return "f32"
+        if "int64_t" in p or "long long" in p or "size_t" in p:
+            return "i64"
+        return "i32"
+
+    def py_class(t):
+        if t in (ctypes.c_void_p, ctypes.c_char_p) or hasattr(t, "_type_") and not isinstance(t._type_, str):
+            return "ptr"
+        return {ctypes.c_float: "f32", ctypes.c_int64: "i64", ctypes.c_longlong: "i64", ctypes.c_int: "i32",
+                ctypes.c_int32: "i32"}[t]
+
+    src = open(native.__file__).read()
+    bound = sorted(set(re.findall(r"\bl\.(sw_\w+)\.argtypes", src)))
+    assert len(bound) > 25
+    called = set(re.findall(r"\bL\.(sw_\w+)\(", src)) | set(re.findall(r"lib\(\)\.(sw_\w+)\(", src))
+    assert not sorted(n for n in called if n not in bound and n != "sw_last_error"), "called without argtypes"
+    for name in bound:
+        assert name in protos, f"{name} has argtypes but no prototype in the header"
+        params = [p for p in protos[name].split(",") if p.strip() and p.strip() != "void"]
+        want = [c_class(p) for p in params]
+        got = [py_class(t) for t in getattr(lib, name).argtypes]
+        assert got == want, f"{name}: header {want}, binding {got}"
