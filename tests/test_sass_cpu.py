@@ -60,3 +60,30 @@ def test_peer_traffic_uses_system_scope(kernels):
         assert hits, needle
         for k in hits:
             assert any(re.search(r"\.SYS\b", line) for line in kernels[k]), f"{k}: no .SYS access"
+
+
+def test_hot_kernels_keep_their_arguments_out_of_the_stack():
+    """`cuobjdump -res-usage`: the single-thread TMA / MMA issue loops of the GEMM and attention kernels must not run off a
+    stack copy of the argument struct (a `__noinline__` helper taking it by reference once cost 512 bytes of stack and a
+    2-3x slower kernel), and nothing spills to local memory."""
+    from chiaswarm_b200.ops import native
+
+    if shutil.which("cuobjdump") is None or not native.LIB_PATH.exists():
+        pytest.skip("needs cuobjdump and the built library")
+    out = subprocess.run(["cuobjdump", "-res-usage", str(native.LIB_PATH)], capture_output=True, text=True, check=True).stdout
+    usage, name = {}, None
+    for line in out.splitlines():
+        m = re.search(r"Function (\S+):", line)
+        if m:
+            name = m.group(1)
+            continue
+        m = re.search(r"REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", line)
+        if m and name:
+            usage[name] = tuple(int(v) for v in m.groups())
+            name = None
+    hot = {k: v for k, v in usage.items() if re.search(r"k_igemm|k_flash_attn|k_gn_fused|k_layernorm", k)}
+    assert len(hot) >= 12
+    for k, (reg, stack, shared, local) in hot.items():
+        assert stack <= 16 and local == 0, f"{k}: STACK {stack} LOCAL {local}"
+        assert reg <= 168, f"{k}: {reg} registers (two CTAs of the attention kernel per SM need <= 168)"
+    assert all(v[3] == 0 for v in usage.values()), "a kernel spills to local memory"
