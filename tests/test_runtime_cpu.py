@@ -344,3 +344,40 @@ def test_sharded_checkpoints_load_through_their_index(tmp_path):
     assert checkpoints.find_weights(folder, "fp16").name == "diffusion_pytorch_model.safetensors.index.fp16.json"
     save_file(b, str(folder / "diffusion_pytorch_model.safetensors"))
     assert checkpoints.find_weights(folder).name == "diffusion_pytorch_model.safetensors"
+
+
+def test_doctor_reports_what_is_wrong_with_a_box(tmp_path, monkeypatch, capsys):
+    """`python -m chiaswarm_b200.doctor`: independent checks that never raise, a fix per failure, exit 1 when a required
+    check failed (here: no GPU), JSON for tooling."""
+    import torch
+
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    monkeypatch.setenv("SDAAS_MODEL_ROOT", str(tmp_path / "models"))
+    from chiaswarm_b200 import doctor
+
+    (tmp_path / "models.json").write_text(json.dumps({"language_models": [], "models": [
+        {"model_name": "org/here"}, {"model_name": "org/absent"}]}))
+    (tmp_path / "models" / "org" / "here").mkdir(parents=True)
+    (tmp_path / "models" / "org" / "here" / "model_index.json").write_text("{}")
+    rc = doctor.main(["--json", "--no-hive"])
+    report = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    by = {c["check"]: c for c in report["checks"]}
+    assert by["torch"]["status"] == "ok" and "models" in by and "hive" not in by
+    assert by["models"]["detail"].startswith("1 of the hive's 2 models") and "--download" in by["models"]["fix"]
+    if not torch.cuda.is_available():
+        assert rc == 1 and report["ready"] is False and by["gpus"]["status"] == "fail" and by["gpus"]["fix"]
+    # a check that blows up is a finding, not a crash; a GPU of another architecture is refused with the way out
+    assert doctor._guard("x", lambda: 1 / 0).status == "fail"
+
+    class Props:
+        name, major, minor, total_memory, multi_processor_count = "H100", 9, 0, 80 << 30, 132
+
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(torch.cuda, "device_count", lambda: 1)
+    monkeypatch.setattr(torch.cuda, "get_device_properties", lambda i: Props)
+    c = doctor.check_gpus()
+    assert c.status == "fail" and "sm_90" in c.detail and "SDAAS_KERNEL_BACKEND=torch" in c.fix
+    Props.major, Props.minor, Props.name = 10, 0, "B200"
+    assert doctor.check_gpus().status == "ok"
+    # the hive check: no token -> warn, with the command that fixes it
+    assert doctor.check_settings_and_hive().status == "warn"
