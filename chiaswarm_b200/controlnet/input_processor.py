@@ -5,7 +5,7 @@ self-contained (OpenCV / PIL / numpy).  The learned annotators (mlsd, depth, nor
 lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers hub models in the
 reference; they are used when importable and locally cached; soft edges / scribbles and lineart additionally have this
 tree's own networks (controlnet/annotators.py: HED from `lllyasviel/Annotators/ControlNetHED.pth`, the lineart generator
-from `sk_model.pth`), openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`) and mlsd this
+from `sk_model.pth`, PiDiNet from `table5_pidinet.pth` in controlnet/pidinet.py), openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`) and mlsd this
 tree's M-LSD network (controlnet/mlsd.py, `mlsd_large_512_fp32.pth`);
 otherwise a
 classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
@@ -226,6 +226,12 @@ def image_to_softedge(image, scribble=False):
     det = _aux("HEDdetector" if scribble else "PidiNetDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image, scribble=True) if scribble else det(image)
+    if not scribble:  # the reference's softedge detector is PiDiNet (HED draws the scribbles)
+        from .pidinet import load_pidinet
+
+        pidi = load_pidinet()
+        if pidi is not None:
+            return pidi.edges(image, next(pidi.parameters()).device)
     from .annotators import load_hed  # this tree's own HED network, when its checkpoint is present locally
 
     hed = load_hed()
