@@ -67,11 +67,9 @@ class HEDNet(nn.Module):
         hh, ww = x.shape[-2:]
         sides = [F.interpolate(s.float(), size=(hh, ww), mode="bilinear", align_corners=False) for s in self(x)]
         edge = torch.sigmoid(torch.stack(sides).mean(0))[0, 0]
-        if scribble:  # thin the soft map to strokes: local maxima above a threshold, then a small dilation
-            e = edge[None, None]
-            peak = (e >= F.max_pool2d(e, 3, 1, 1) - 1e-6) & (e > 0.25)
-            edge = F.max_pool2d(peak.float(), 3, 1, 1)[0, 0]
-        out = (edge.clamp(0, 1) * 255).round().to(torch.uint8).cpu().numpy()
+        out = (edge.clamp(0, 1) * 255).to(torch.uint8).cpu().numpy()
+        if scribble:
+            out = scribble_strokes(out)
         return Image.fromarray(np.stack([out] * 3, axis=2))
 
 
@@ -112,6 +110,24 @@ class LineartNet(nn.Module):
         out = (255 - (line * 255).round()).to(torch.uint8).cpu().numpy()
         img = Image.fromarray(np.stack([out] * 3, axis=2))
         return img if (w4, h4) == (w, h) else img.resize((w, h), Image.Resampling.BILINEAR)
+
+
+def scribble_strokes(edge_map: np.ndarray) -> np.ndarray:
+    """Soft edge map (uint8) -> binary strokes, the way the reference's `HEDdetector(..., scribble=True)` does it:
+    blur, keep pixels that are the maximum along one of the four line directions through them and above 127, blur again,
+    binarise at 4."""
+    import cv2
+
+    x = cv2.GaussianBlur(edge_map.astype(np.float32), (0, 0), 3.0)
+    lines = [np.array(k, dtype=np.uint8) for k in ([[0, 0, 0], [1, 1, 1], [0, 0, 0]], [[0, 1, 0], [0, 1, 0], [0, 1, 0]],
+                                                    [[1, 0, 0], [0, 1, 0], [0, 0, 1]], [[0, 0, 1], [0, 1, 0], [1, 0, 0]])]
+    y = np.zeros_like(x)
+    for k in lines:
+        np.putmask(y, cv2.dilate(x, kernel=k) == x, x)
+    z = np.zeros_like(y, dtype=np.uint8)
+    z[y > 127] = 255
+    z = cv2.GaussianBlur(z.astype(np.float32), (0, 0), 3.0)
+    return np.where(z > 4, 255, 0).astype(np.uint8)
 
 
 _cache = {}

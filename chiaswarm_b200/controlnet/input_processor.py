@@ -15,7 +15,7 @@ from __future__ import annotations
 import logging
 
 import numpy as np
-from PIL import Image, ImageFilter
+from PIL import Image
 
 _reported = set()
 
@@ -239,10 +239,12 @@ def image_to_softedge(image, scribble=False):
         return hed.edges(image, next(hed.parameters()).device, scribble=scribble)
     _stand_in("scribble" if scribble else "softedge", "Sobel edge magnitude")
     _, _, mag = _sobel_mag(image)
-    if scribble:
-        edge = (mag > 0.25).astype(np.uint8) * 255
-        return _gray3(np.array(Image.fromarray(edge).filter(ImageFilter.MaxFilter(3))))
-    return _gray3(255 * np.clip(mag * 2.0, 0, 1))
+    soft = (255 * np.clip(mag * 2.0, 0, 1)).astype(np.uint8)
+    if scribble:  # the same thinning / binarisation the learned detector's map gets
+        from .annotators import scribble_strokes
+
+        return _gray3(scribble_strokes(soft))
+    return _gray3(soft)
 
 
 def image_to_shuffle(image, seed=None):
