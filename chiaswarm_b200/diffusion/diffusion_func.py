@@ -89,7 +89,7 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
     images = p.images
     if upscale:
         images = upscale_image(images, device_identifier, kwargs.get("prompt", ""), num_images_per_prompt,
-                               kwargs.get("generator"))
+                               kwargs.get("generator"), info=pipeline_config)
     output_processor.add_outputs(images)
     logging.debug("diffusion_callback done: %d image(s)", len(images))
     return output_processor.get_results(), pipeline_config

@@ -200,8 +200,12 @@ class LatentUpscalePipeline:
         return PipelineOutput(images=tensor_to_pil(pixels))
 
 
-def upscale_image(images, device_identifier, prompt, num_images_per_prompt, generator) -> List[Image.Image]:
+def upscale_image(images, device_identifier, prompt, num_images_per_prompt, generator, info: dict = None) -> List[Image.Image]:
+    """`info` (optional dict) receives `{"upscaler": "sd-x2-latent-upscaler" | "lanczos"}`: which of the two ran goes into
+    the job's `pipeline_config`, so a resize standing in for the network is visible on the wire, not only in the log."""
     print("Upscaling...")
+    info = {} if info is None else info
+    info["upscaler"] = "sd-x2-latent-upscaler"
     try:
         pipe = pipeline_cache().get((UPSCALER, device_identifier),
                                     lambda: LatentUpscalePipeline.from_pretrained(UPSCALER, torch.float16, device_identifier))
@@ -209,5 +213,6 @@ def upscale_image(images, device_identifier, prompt, num_images_per_prompt, gene
         if "not available locally" not in str(e):
             raise
         logging.warning("%s is not on this worker: 2x LANCZOS resize instead of the latent upscaler", UPSCALER)
+        info["upscaler"] = "lanczos"
         return [im.resize((im.width * 2, im.height * 2), Image.Resampling.LANCZOS) for im in images]
     return list(pipe(prompt=prompt, image=list(images), num_inference_steps=20, guidance_scale=0, generator=generator).images)

@@ -225,7 +225,7 @@ def test_upscale_flag_through_the_job_api_with_a_local_checkpoint(tmp_path, monk
     r = _run(dict(job))
     assert "error" not in r["pipeline_config"], r["pipeline_config"]
     big = decode_artifact_image(r["artifacts"]["primary"])
-    assert big.size == (64, 64)
+    assert big.size == (64, 64) and r["pipeline_config"]["upscaler"] == "sd-x2-latent-upscaler"
     # the checkpoint on disk is the one that ran: same weights as the pipeline that wrote it
     from chiaswarm_b200.utils.weight_cache import pipeline_cache
 
@@ -252,5 +252,6 @@ def test_without_a_checkpoint_the_stage_resizes(tmp_path, monkeypatch):
     from chiaswarm_b200.diffusion.upscale import upscale_image
 
     im = Image.new("RGB", (24, 16), (10, 200, 30))
-    out = upscale_image([im, im], "cpu", "x", 2, None)
-    assert [o.size for o in out] == [(48, 32), (48, 32)]
+    info = {}
+    out = upscale_image([im, im], "cpu", "x", 2, None, info=info)
+    assert [o.size for o in out] == [(48, 32), (48, 32)] and info == {"upscaler": "lanczos"}   # visible in pipeline_config
