@@ -13,15 +13,19 @@ dependency.  Unknown types raise, as in the reference."""
 from __future__ import annotations
 
 import logging
+import threading
 
 import numpy as np
 from PIL import Image
 
 _reported = set()
+_tls = threading.local()
 
 
 def _stand_in(kind: str, what: str):
-    """The learned annotator of `kind` is not on this worker: say so (once per type) instead of degrading silently."""
+    """The learned annotator of `kind` is not on this worker: say so (in the log once per type, and on the image the
+    pre-processor returns, from where the job callback copies it into `pipeline_config`) instead of degrading silently."""
+    _tls.stand_in = what
     if kind not in _reported:
         _reported.add(kind)
         logging.warning("controlnet pre-processor %s: learned annotator not available locally, using %s", kind, what)
@@ -47,7 +51,11 @@ def preprocess_image(image, controlnet):
     }
     if kind not in handlers:
         raise Exception("Unknown controlnet type")
-    return handlers[kind](image)
+    _tls.stand_in = None
+    out = handlers[kind](image)
+    if getattr(_tls, "stand_in", None) and hasattr(out, "info"):
+        out.info["controlnet_annotator"] = f"stand-in for {kind}: {_tls.stand_in}"
+    return out
 
 
 def _gray3(arr) -> Image.Image:

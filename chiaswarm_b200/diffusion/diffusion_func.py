@@ -86,6 +86,9 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
     if flagged is not None and ((isinstance(flagged, bool) and flagged) or (isinstance(flagged, list) and any(flagged))):
         pipeline_config["nsfw"] = True
 
+    note = getattr(kwargs.get("image"), "info", {}).get("controlnet_annotator")
+    if note:  # the control image came from a classical stand-in, not from the learned annotator (controlnet/input_processor.py)
+        pipeline_config["controlnet_annotator"] = note
     images = p.images
     if upscale:
         images = upscale_image(images, device_identifier, kwargs.get("prompt", ""), num_images_per_prompt,

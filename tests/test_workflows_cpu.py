@@ -47,6 +47,14 @@ def test_controlnet_canny_job_emits_preprocessed_input():
     edges = np.asarray(decode_artifact_image(r["artifacts"]["preprocessed_input"]).convert("L"))
     assert edges.max() > 200 and edges.mean() < 60  # thin white edges on black
     assert decode_artifact_image(r["artifacts"]["primary"]).size == (64, 64)
+    assert "controlnet_annotator" not in r["pipeline_config"]          # canny is exact: nothing stood in
+    # a learned annotator that is not on this worker: the stand-in is named in the result, not only in the log
+    r = _run({"id": "c1b", "model_name": "tiny-sd", "prompt": "pose", "start_image_uri": _checker(), "seed": 2,
+              "num_inference_steps": 1,
+              "parameters": {"controlnet": {"type": "openpose", "preprocess": True,
+                                            "controlnet_model_name": "lllyasviel/controlnet-tiny"}}})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert r["pipeline_config"]["controlnet_annotator"].startswith("stand-in for openpose: an empty skeleton")
 
 
 def test_controlnet_changes_the_image():
