@@ -302,9 +302,12 @@ class GangScheduler:
                             failure = (f"rank {lone_error[0]} failed ({lone_error[1]}) and ranks {sorted(pending)} did not "
                                        f"return within {self.straggler_grace_s:g} s")
                             break
+                        # every pending rank is looked at without blocking and the loop naps 2 ms when none had news:
+                        # a blocking wait per rank would add up to (ranks x its timeout) to the latency of every job
+                        progressed = False
                         for r in list(pending):
                             try:
-                                kind, lease_id, payload = result_qs[r].get(timeout=0.05)
+                                kind, lease_id, payload = result_qs[r].get_nowait()
                             except queue.Empty:
                                 if generation != self.generation:
                                     failure = "the rank world was restarted under this job"
@@ -314,6 +317,7 @@ class GangScheduler:
                                     failure = f"rank {r} died while running the job"
                                     break
                                 continue
+                            progressed = True
                             if lease_id != gang.lease_id:
                                 continue  # stale message of an abandoned lease
                             pending.discard(r)
@@ -322,6 +326,8 @@ class GangScheduler:
                                 payload = {"error": payload.get("rank_error") or (payload.get("pipeline_config") or {}).get("error")}
                             if lone_error is None and payload and payload.get("error"):
                                 lone_error = (r, str(payload["error"])[:200], time.time())
+                        if not progressed and failure is None:
+                            time.sleep(0.002)
             except TimeoutError as e:
                 failure = str(e)
         finally:
