@@ -54,6 +54,8 @@ class RankGroup:
         self._s = _State(world=world, free=[True] * world)
         self._leases = {}
         self._dead = set()
+        self._waiting: List[int] = []   # tickets of lease() calls in arrival order: leases are granted first come, first
+        self._next_ticket = 0           # served, so a stream of one-rank jobs cannot starve a job that waits for a gang
 
     @property
     def world(self) -> int:
@@ -89,20 +91,27 @@ class RankGroup:
         return gang
 
     def lease(self, size: int = 1, timeout: Optional[float] = None) -> Gang:
-        """Blocks until an aligned gang of `size` ranks is free. Raises Exception("busy") on timeout
-        (the reference's pool raises the same when empty, swarm/gpu/device_pool.py:30-32)."""
+        """Blocks until an aligned gang of `size` ranks is free AND every earlier caller has been served (first come, first
+        served: while an 8-rank job waits for the box to drain, later one-rank jobs queue up behind it instead of keeping
+        ranks busy forever).  Raises Exception("busy") on timeout (the reference's pool raises the same when empty,
+        swarm/gpu/device_pool.py:30-32)."""
         if size > self._s.world:
             raise ValueError(f"gang of {size} does not fit a world of {self._s.world}")
         with self._cv:
-            gang = self._try_lease(size)
-            if gang is None and timeout == 0:
-                raise Exception("busy")
-            if gang is None:
-                ok = self._cv.wait_for(lambda: self._peek(size), timeout)
-                if not ok:
-                    raise Exception("busy")
-                gang = self._try_lease(size)
-            return gang
+            ticket = self._next_ticket
+            self._next_ticket += 1
+            self._waiting.append(ticket)
+            try:
+                def ready():
+                    return self._waiting[0] == ticket and self._peek(size)
+
+                if not ready():
+                    if timeout == 0 or not self._cv.wait_for(ready, timeout):
+                        raise Exception("busy")
+                return self._try_lease(size)
+            finally:
+                self._waiting.remove(ticket)
+                self._cv.notify_all()  # the next caller in line may be servable now
 
     def _peek(self, size: int) -> bool:
         return any(all(self._s.free[r] for r in s) for s in self.aligned_subsets(size))

@@ -381,3 +381,37 @@ def test_doctor_reports_what_is_wrong_with_a_box(tmp_path, monkeypatch, capsys):
     assert doctor.check_gpus().status == "ok"
     # the hive check: no token -> warn, with the command that fixes it
     assert doctor.check_settings_and_hive().status == "warn"
+
+
+def test_gang_leases_are_first_come_first_served():
+    """A job waiting for a whole gang is not starved by later one-rank jobs that would fit the free ranks."""
+    import threading
+    import time
+
+    from chiaswarm_b200.gpu.device_pool import RankGroup
+
+    pool = RankGroup(2)
+    first = pool.lease(1)                       # rank 0 busy, rank 1 free
+    order, got = [], {}
+
+    def want(name, size):
+        got[name] = pool.lease(size, timeout=20)
+        order.append(name)
+
+    big = threading.Thread(target=want, args=("big", 2))
+    big.start()
+    time.sleep(0.2)                             # the gang-of-2 request is waiting for rank 0
+    small = threading.Thread(target=want, args=("small", 1))
+    small.start()
+    time.sleep(0.3)
+    assert order == [] and pool.free_count() == 1   # the later small job did NOT take the free rank past the big one
+    with pytest.raises(Exception, match="busy"):
+        pool.lease(1, timeout=0)                # non-blocking callers do not jump the line either
+    pool.release(first)
+    big.join(10)
+    assert order == ["big"] and got["big"].ranks == (0, 1)
+    pool.release(got["big"])
+    small.join(10)
+    assert order == ["big", "small"]
+    pool.release(got["small"])
+    assert pool.free_count() == 2
