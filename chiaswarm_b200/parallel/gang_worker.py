@@ -117,6 +117,15 @@ def rank_main(rank: int, world: int, port: int, job_q, result_q, use_cuda: bool,
 
     if not use_cuda:
         torch.set_num_threads(max(1, (os.cpu_count() or 2) // max(world, 1)))
+    try:  # each rank logs to its own rotating file next to the hive client's (log/generator.rank3.log)
+        from ..log_setup import setup_logging
+        from ..settings import load_settings, resolve_path
+
+        s = load_settings()
+        base, ext = os.path.splitext(s.log_filename)
+        setup_logging(resolve_path(f"{base}.rank{rank}{ext or '.log'}"), s.log_level)
+    except Exception:
+        pass  # logging must never keep a rank from coming up
     try:
         gang_world = runtime.init(None if use_cuda else "gloo")
         gangs: Dict[tuple, object] = {}
