@@ -202,8 +202,11 @@ def make_plan(kind: str, num_steps: int, config: Optional[dict] = None, use_karr
             down = math.sqrt(max(sn * sn - up * up, 0.0))
             r = down / s
             coef.append([e0, e1, r, 1 - r, 0.0, up, s_in_next, 0.0])
-    init_sigma = float(sig[0])
-    first = 1.0 / math.sqrt(init_sigma ** 2 + 1)
+    first = 1.0 / math.sqrt(float(sig[0]) ** 2 + 1)
+    # diffusers' Euler schedulers start from randn * sigma_max, except with "leading" timestep spacing (what the SDXL
+    # checkpoints configure), where it is randn * sqrt(sigma_max^2 + 1)
+    leading = cfg.get("timestep_spacing", "linspace") == "leading"
+    init_sigma = math.sqrt(float(sig[0]) ** 2 + 1) if leading else float(sig[0])
     return StepPlan(kind, ts, sig, np.asarray(coef, np.float32), init_sigma, first, kind == "euler_a", prediction, acp)
 
 

@@ -132,3 +132,13 @@ def test_ddim_eta_adds_the_ddpm_variance():
         x, x0_hat, _ = S.apply_step_torch(sto, i, x, pred, None, torch.randn(x.shape, generator=g, dtype=torch.float64))
         x = x.double()
         assert torch.allclose(x0_hat.double(), x0, atol=1e-3)
+
+
+def test_euler_initial_noise_scale_follows_the_timestep_spacing():
+    """diffusers: init_noise_sigma = sigma_max for linspace / trailing spacing, sqrt(sigma_max^2 + 1) for leading (SDXL)."""
+    plain = S.make_plan("euler", 20, None, True)
+    lead = S.make_plan("euler", 20, {"timestep_spacing": "leading"}, True)
+    assert plain.init_noise_sigma == pytest.approx(plain.sigmas[0])
+    assert lead.init_noise_sigma == pytest.approx(math.sqrt(lead.sigmas[0] ** 2 + 1))
+    assert np.array_equal(plain.sigmas, lead.sigmas) and np.array_equal(plain.coef, lead.coef)
+    assert S.make_plan("dpmpp_2m", 20, {"timestep_spacing": "leading"}, True).init_noise_sigma == 1.0
