@@ -134,6 +134,35 @@ def new_registry() -> Metrics:
     return m
 
 
+def register_gpu_gauges(metrics: Metrics, nvml=None) -> int:
+    """Per-GPU gauges read from NVML when the page is rendered: memory in use, utilisation, SM clock, throttle reasons
+    (the same fields `bench.py` samples while timing).  Returns the number of GPUs registered; 0 when NVML is not usable
+    (no driver: the page then simply has no GPU section)."""
+    try:
+        if nvml is None:
+            import pynvml as nvml
+        nvml.nvmlInit()
+        count = int(nvml.nvmlDeviceGetCount())
+    except Exception:
+        return 0
+    for name, text in (("swarm_gpu_memory_used_bytes", "Device memory in use."),
+                       ("swarm_gpu_utilization_ratio", "Fraction of the last sample period a kernel was running."),
+                       ("swarm_gpu_sm_clock_mhz", "Current SM clock."),
+                       ("swarm_gpu_throttle_reasons", "NVML clocks-event reason bit mask (0 = none).")):
+        metrics.describe(name, "gauge", text)
+    for i in range(count):
+        handle = nvml.nvmlDeviceGetHandleByIndex(i)
+        labels = {"gpu": i}
+        metrics.set("swarm_gpu_memory_used_bytes", lambda h=handle: nvml.nvmlDeviceGetMemoryInfo(h).used, labels)
+        metrics.set("swarm_gpu_utilization_ratio", lambda h=handle: nvml.nvmlDeviceGetUtilizationRates(h).gpu / 100.0, labels)
+        metrics.set("swarm_gpu_sm_clock_mhz", lambda h=handle: nvml.nvmlDeviceGetClockInfo(h, nvml.NVML_CLOCK_SM), labels)
+        metrics.set("swarm_gpu_throttle_reasons",
+                    lambda h=handle: nvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    if hasattr(nvml, "nvmlDeviceGetCurrentClocksEventReasons")
+                    else nvml.nvmlDeviceGetCurrentClocksThrottleReasons(h), labels)
+    return count
+
+
 def job_outcome(result: dict) -> str:
     if result.get("fatal_error"):
         return "fatal"

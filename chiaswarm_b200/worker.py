@@ -101,6 +101,7 @@ class Worker:
         self.metrics.set("swarm_lanes_busy", lambda: self._busy)
         port = int(getattr(self.settings, "metrics_port", 0) or 0)
         if port > 0 and self._metrics_server is None:
+            metrics_mod.register_gpu_gauges(self.metrics)
             self._metrics_server = await metrics_mod.serve(self.metrics, port, getattr(self.settings, "metrics_host", "127.0.0.1"))
 
     async def run(self, max_polls: Optional[int] = None, sleep=asyncio.sleep):

@@ -250,3 +250,61 @@ def test_undelivered_results_are_spooled_and_resent(tmp_path):
             await hive.stop()
 
     asyncio.run(main())
+
+
+def test_gpu_gauges_come_from_nvml_and_survive_its_absence():
+    from chiaswarm_b200.utils import metrics as M
+
+    class Mem:
+        used = 5 << 30
+
+    class Util:
+        gpu = 87
+
+    class FakeNvml:
+        NVML_CLOCK_SM = 1
+        calls = 0
+
+        @staticmethod
+        def nvmlInit():
+            pass
+
+        @staticmethod
+        def nvmlDeviceGetCount():
+            return 2
+
+        @staticmethod
+        def nvmlDeviceGetHandleByIndex(i):
+            return f"h{i}"
+
+        @staticmethod
+        def nvmlDeviceGetMemoryInfo(h):
+            return Mem
+
+        @staticmethod
+        def nvmlDeviceGetUtilizationRates(h):
+            return Util
+
+        @staticmethod
+        def nvmlDeviceGetClockInfo(h, which):
+            if h == "h1":
+                raise RuntimeError("GPU is lost")             # one broken gauge must not take the page down
+            return 1965
+
+        @staticmethod
+        def nvmlDeviceGetCurrentClocksThrottleReasons(h):
+            return 0
+
+    m = M.new_registry()
+    assert M.register_gpu_gauges(m, FakeNvml) == 2
+    text = m.render()
+    assert 'swarm_gpu_memory_used_bytes{gpu="1"} 5.36871e+09' in text and 'swarm_gpu_utilization_ratio{gpu="0"} 0.87' in text
+    assert 'swarm_gpu_sm_clock_mhz{gpu="0"} 1965' in text and 'swarm_gpu_sm_clock_mhz{gpu="1"}' not in text
+    assert 'swarm_gpu_throttle_reasons{gpu="0"} 0' in text
+
+    class NoDriver:
+        @staticmethod
+        def nvmlInit():
+            raise OSError("libnvidia-ml.so.1: cannot open shared object file")
+
+    assert M.register_gpu_gauges(M.new_registry(), NoDriver) == 0
