@@ -134,3 +134,58 @@ def test_if_without_checkpoints_is_a_fatal_job_error():
 
     r = asyncio.run(do_work({"id": "if2", "model_name": "DeepFloyd/IF-I-XL-v1.0", "prompt": "x"}, Device("cpu")))
     assert r["fatal_error"] is True and "needs local checkpoints" in r["pipeline_config"]["error"]
+
+
+def test_ddpm_step_is_the_learned_range_posterior():
+    """`ddpm_step` against the DDPM posterior q(x_{t'} | x_t, x0) written out, with the variance interpolated in log space
+    between the posterior variance (v = -1) and beta_t (v = +1), and with Imagen's dynamic thresholding."""
+    import math
+
+    from chiaswarm_b200.diffusion.if_unet import IF_SCHEDULER, ddpm_step, dynamic_threshold
+    from chiaswarm_b200.ops import schedulers
+
+    acp = np.cumprod(1.0 - schedulers._betas(IF_SCHEDULER))
+    g = torch.Generator().manual_seed(0)
+    x0 = torch.rand(2, 3, 8, 8, generator=g, dtype=torch.float64) * 1.6 - 0.8          # inside [-1, 1]: thresholding is a no-op
+    eps = torch.randn(2, 3, 8, 8, generator=g, dtype=torch.float64)
+    noise = torch.randn(2, 3, 8, 8, generator=g, dtype=torch.float64)
+    t, prev = 600, 590
+    a_t, a_p = acp[t], acp[prev]
+    x_t = math.sqrt(a_t) * x0 + math.sqrt(1 - a_t) * eps
+    beta = 1 - a_t / a_p                                                                # the step's effective beta
+    mean = (math.sqrt(a_p) * beta / (1 - a_t)) * x0 + (math.sqrt(a_t / a_p) * (1 - a_p) / (1 - a_t)) * x_t
+    post_var = (1 - a_p) / (1 - a_t) * beta
+    for v, want_var in ((-1.0, post_var), (1.0, beta), (0.0, math.sqrt(post_var * beta))):   # log-space interpolation
+        got = ddpm_step(x_t, eps, torch.full_like(x_t, v), t, prev, acp, noise)
+        assert torch.allclose(got, mean + math.sqrt(want_var) * noise, atol=1e-9), v
+    assert torch.allclose(ddpm_step(x_t, eps, None, t, prev, acp, noise), mean + math.sqrt(post_var) * noise, atol=1e-9)
+    # the last step (prev < 0) lands on the predicted image exactly, and adds no noise
+    t0 = 3
+    x_last = math.sqrt(acp[t0]) * x0 + math.sqrt(1 - acp[t0]) * eps
+    assert torch.allclose(ddpm_step(x_last, eps, torch.zeros_like(x0), t0, t0 - 10, acp, None), x0, atol=1e-9)
+    # dynamic thresholding: the 95th percentile of |x| (clamped to [1, 1.5]) becomes the new unit
+    big = torch.linspace(-3, 3, 601, dtype=torch.float64).view(1, 1, 1, -1)
+    th = dynamic_threshold(big)
+    assert float(th.max()) == pytest.approx(1.0) and float(th.min()) == pytest.approx(-1.0)
+    assert float(th[0, 0, 0, 300 + 50]) == pytest.approx(0.5 / 1.5)                     # s hit the 1.5 cap; inner values / s
+    small = big / 10
+    assert torch.allclose(dynamic_threshold(small), small)                              # s floors at 1: untouched
+
+
+def test_if_stage_samplers(tmp_path):
+    from chiaswarm_b200.diffusion.if_unet import IFStage
+
+    root = tmp_path / "models" / "DeepFloyd" / "IF-I-tiny"
+    _save_if_stage(root, 1)
+    stage = IFStage.from_checkpoint(root, "cpu")
+    g = torch.Generator().manual_seed(3)
+    cond, unc = torch.randn(1, 5, 24, generator=g), torch.zeros(1, 5, 24)
+    kw = dict(size=16, steps=4, guidance_scale=3.0)
+    a = stage.sample(cond, unc, generator=torch.Generator().manual_seed(1), **kw)
+    b = stage.sample(cond, unc, generator=torch.Generator().manual_seed(1), **kw)
+    c = stage.sample(cond, unc, generator=torch.Generator().manual_seed(2), **kw)
+    d = stage.sample(cond, unc, generator=torch.Generator().manual_seed(1), sampler="ddim", **kw)
+    assert a.shape == (1, 3, 16, 16) and torch.isfinite(a).all() and float(a.abs().max()) <= 1.0
+    assert torch.equal(a, b) and not torch.allclose(a, c) and not torch.allclose(a, d)   # ancestral: the seed drives the path
+    with pytest.raises(ValueError, match="unknown IF sampler"):
+        stage.sample(cond, unc, sampler="euler", **kw)
