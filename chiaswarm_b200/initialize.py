@@ -77,21 +77,36 @@ async def download_diffusers(settings, fetch: bool = False):
             state = "missing: no local diffusers-layout checkpoint"
             print(f"  {model_name}: not present locally (run with --download to fetch it)")
         report[model_name] = state
+    if fetch:  # the ControlNet pre-processors' own checkpoints (controlnet/{annotators,pidinet,mlsd,openpose}.py)
+        for repo, files in ANNOTATOR_FILES.items():
+            have = locate_checkpoint(repo, model_root=getattr(settings, "model_root", ""))
+            if have is not None and all((have / f).is_file() for f in files):
+                report[repo] = "ok"
+                continue
+            error = fetch_from_hub(repo, "main", getattr(settings, "huggingface_token", None), patterns=files)
+            report[repo] = "downloaded" if error is None else f"missing: download failed ({error})"
     print("Model download complete")
     return report
 
+
+# the learned ControlNet annotators this tree implements, by repository (file names as published)
+ANNOTATOR_FILES = {
+    "lllyasviel/Annotators": ["ControlNetHED.pth", "sk_model.pth", "table5_pidinet.pth", "body_pose_model.pth",
+                              "mlsd_large_512_fp32.pth"],
+}
 
 # what a worker reads from a model repository: configs, tokenizers, and the safetensors weights (fp16 variant preferred by
 # the loaders); the multi-GB .ckpt / .bin duplicates most repositories also carry are left on the hub
 HUB_PATTERNS = ["*.json", "*.txt", "*.model", "*.safetensors", "*.pth"]
 
 
-def fetch_from_hub(model_name: str, revision: str = "main", token=None):
-    """Pulls one repository into the HuggingFace cache.  Returns None on success, the reason otherwise (never raises)."""
+def fetch_from_hub(model_name: str, revision: str = "main", token=None, patterns=None):
+    """Pulls one repository (or the named files of it) into the HuggingFace cache.  Returns None on success, the reason
+    otherwise (never raises)."""
     try:
         from huggingface_hub import snapshot_download
 
-        snapshot_download(model_name, revision=revision, allow_patterns=HUB_PATTERNS,
+        snapshot_download(model_name, revision=revision, allow_patterns=list(patterns or HUB_PATTERNS),
                           token=token if isinstance(token, str) and token else None)
         return None
     except Exception as e:

@@ -257,16 +257,19 @@ def test_initialize_download_fetches_what_is_missing(tmp_path, monkeypatch):
         calls.append((repo, revision, tuple(allow_patterns), token))
         if repo == "org/unreachable":
             raise OSError("no route to host")
-        root = tmp_path / "models" / "org" / "fetchable"
-        root.mkdir(parents=True)
-        (root / "model_index.json").write_text("{}")
+        if repo == "org/fetchable":
+            root = tmp_path / "models" / "org" / "fetchable"
+            root.mkdir(parents=True)
+            (root / "model_index.json").write_text("{}")
 
     monkeypatch.setattr(huggingface_hub, "snapshot_download", fake_snapshot)
     report = asyncio.run(initialize.init(["--silent", "--download"]))
     assert report["org/fetchable"] == "downloaded"
     assert report["org/unreachable"].startswith("missing: download failed (OSError: no route to host")
-    assert [c[0] for c in calls] == ["org/fetchable", "org/unreachable"] and "*.safetensors" in calls[0][2]
-    assert all("*.ckpt" not in c[2] and "*.bin" not in c[2] for c in calls)
+    assert [c[0] for c in calls] == ["org/fetchable", "org/unreachable", "lllyasviel/Annotators"]
+    assert "*.safetensors" in calls[0][2] and all("*.ckpt" not in c[2] and "*.bin" not in c[2] for c in calls)
+    assert "table5_pidinet.pth" in calls[2][2] and "body_pose_model.pth" in calls[2][2]   # the annotators' own files only
+    assert report["lllyasviel/Annotators"] == "downloaded"
     calls.clear()
     report = asyncio.run(initialize.init(["--silent"]))                  # without the flag nothing leaves the machine
     assert calls == [] and report["org/fetchable"] == "ok" and report["org/unreachable"].startswith("missing: no local")
