@@ -130,5 +130,11 @@ def get_models_from_hive(hive_uri):
         return []
 
 
-if __name__ == "__main__":
+def main() -> int:
+    """Console entry point (`chiaswarm-init`, `python -m chiaswarm_b200.initialize`)."""
     asyncio.run(init())
+    return 0
+
+
+if __name__ == "__main__":
+    main()

@@ -366,5 +366,11 @@ async def run_worker():
     await _get().run()
 
 
-if __name__ == "__main__":
+def main() -> int:
+    """Console entry point (`chiaswarm-worker`, `python -m chiaswarm_b200.worker`)."""
     asyncio.run(run_worker())
+    return 0
+
+
+if __name__ == "__main__":
+    main()

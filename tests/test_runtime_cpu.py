@@ -418,3 +418,22 @@ def test_gang_leases_are_first_come_first_served():
     assert order == ["big", "small"]
     pool.release(got["small"])
     assert pool.free_count() == 2
+
+
+def test_console_scripts_point_at_real_functions():
+    """[project.scripts] of pyproject.toml: every entry resolves to a callable (a missing `main` only shows after
+    `pip install`, as an ImportError of the generated launcher)."""
+    import importlib
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "pyproject.toml")).read()
+    block = text[text.index("[project.scripts]"):].split("\n[", 1)[0]
+    entries = re.findall(r'^([\w-]+)\s*=\s*"([\w.]+):(\w+)"', block, re.M)
+    assert len(entries) >= 4
+    for name, module, func in entries:
+        assert callable(getattr(importlib.import_module(module), func, None)), f"{name} -> {module}:{func}"
+    # the alias package keeps the reference's module paths alive
+    for mod in ("swarm.worker", "swarm.initialize"):
+        assert importlib.import_module(mod) is not None
