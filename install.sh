@@ -48,6 +48,7 @@ cat <<MSG
 chiaswarm_b200 is installed.
   . ./activate
   python -m swarm.initialize          # hive URI + token, model report (add --download to fetch missing models)
+  python -m chiaswarm_b200.doctor     # pre-flight: GPU architecture, kernel library, peer access, hive, models
   python -m swarm.worker              # one process, one job lane per GPU
   python -m chiaswarm_b200.parallel.launcher   # one rank process per GPU (+ gang jobs: SDAAS_PARALLEL_MODE=patch)
 MSG
