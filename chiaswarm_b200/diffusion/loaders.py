@@ -3,7 +3,6 @@ reference call sites swarm/diffusion/diffusion_func.py:29-34,48-68)."""
 from __future__ import annotations
 
 import math
-import os
 import re
 from pathlib import Path
 

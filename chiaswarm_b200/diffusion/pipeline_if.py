@@ -36,7 +36,7 @@ def run_if_cascade(device, stage1, stage2, stage3, prompt, negative_prompt=None,
     img = s2.sample(cond, unc, size=sizes[1], steps=num_inference_steps or 50, guidance_scale=min(guidance_scale, 4.0),
                     generator=generator, low_res=img, noise_level=250)
     del s2
-    from .pipelines import StableDiffusionPipeline, tensor_to_pil
+    from .pipelines import StableDiffusionPipeline
 
     # stage III: the SD x4 upscaler proper (noise level 100 as in the reference, diffusers' defaults for the rest):
     # the 256 px tensor goes in as the noised conditioning channels, not through an img2img approximation

@@ -38,7 +38,7 @@ import random
 import socket
 import threading
 import time
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Optional
 
 from ..gpu.device_pool import VALID_GANG_SIZES, RankGroup
 from ..settings import Settings, load_settings

@@ -16,13 +16,10 @@ decodes its strip of the image and the strips are gathered once, as pixels.
 """
 from __future__ import annotations
 
-from typing import List, Optional
-
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 
-from ..models.unet2d import timestep_embedding
 from .runtime import Gang
 
 
