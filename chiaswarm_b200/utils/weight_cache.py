@@ -39,13 +39,33 @@ def _nbytes(obj) -> int:
     return total
 
 
+def _device_free_fraction():
+    """Free / total memory of the current CUDA device; None without one."""
+    try:
+        import torch
+
+        if not torch.cuda.is_available():
+            return None
+        free, total = torch.cuda.mem_get_info()
+        return free / max(total, 1)
+    except Exception:
+        return None
+
+
 class LRUByBytes:
-    def __init__(self, budget_bytes: int):
+    """`budget_bytes` bounds what the entries' modules occupy; `min_free` (fraction of device memory) bounds what this
+    accounting cannot see -- the engines' packed weight copies, captured graphs and work buffers, other processes: after
+    an insertion, least-recently-used entries are dropped (and the allocator's cache released) until that much of the
+    device is free again."""
+
+    def __init__(self, budget_bytes: int, min_free: float = 0.08, free_fraction: Callable = _device_free_fraction):
         self.budget = budget_bytes
+        self.min_free, self._free_fraction = min_free, free_fraction
         self._items: "OrderedDict[Hashable, tuple]" = OrderedDict()
         self._lock = threading.Lock()
         self.hits = 0
         self.misses = 0
+        self.evictions = 0
 
     def get(self, key: Hashable, loader: Callable):
         with self._lock:
@@ -61,7 +81,31 @@ class LRUByBytes:
             self._items.move_to_end(key)
             while len(self._items) > 1 and sum(s for _, s in self._items.values()) > self.budget:
                 self._items.popitem(last=False)
+                self.evictions += 1
+            self._relieve_pressure()
         return value
+
+    def _relieve_pressure(self):
+        """Called with the lock held, after an insertion."""
+        frac = self._free_fraction()
+        while frac is not None and frac < self.min_free and len(self._items) > 1:
+            self._items.popitem(last=False)
+            self.evictions += 1
+            self._release_device_memory()
+            frac = self._free_fraction()
+
+    @staticmethod
+    def _release_device_memory():
+        import gc
+
+        gc.collect()
+        try:
+            import torch
+
+            if torch.cuda.is_available():
+                torch.cuda.empty_cache()
+        except Exception:
+            pass
 
     def clear(self):
         with self._lock:

@@ -437,3 +437,32 @@ def test_console_scripts_point_at_real_functions():
     # the alias package keeps the reference's module paths alive
     for mod in ("swarm.worker", "swarm.initialize"):
         assert importlib.import_module(mod) is not None
+
+
+def test_weight_cache_sheds_entries_under_device_memory_pressure():
+    """What the byte accounting cannot see (engine copies, graphs, other processes) is bounded by the free fraction of the
+    device: least-recently-used entries go until enough is free again; the newest entry always stays."""
+    from chiaswarm_b200.utils.weight_cache import LRUByBytes
+
+    free = {"value": 0.5}
+    cache = LRUByBytes(1 << 40, min_free=0.10, free_fraction=lambda: free["value"])
+    mk = lambda: torch.nn.Linear(4, 4)  # noqa: E731
+    cache.get("a", mk)
+    cache.get("b", mk)
+    cache.get("c", mk)
+    assert len(cache) == 3 and cache.evictions == 0
+    free["value"] = 0.02                         # the device is nearly full and stays so: everything but the newcomer goes
+    cache.get("d", mk)
+    assert len(cache) == 1 and cache.evictions == 3 and cache.get("d", lambda: pytest.fail("d was evicted")) is not None
+    # pressure that one eviction relieves costs one entry only
+    steps = iter([0.05, 0.30])
+    cache2 = LRUByBytes(1 << 40, min_free=0.10, free_fraction=lambda: next(steps, 0.30))
+    cache2.get("x", mk)                          # a single entry is never evicted (first reading 0.05 is ignored: len == 1)
+    cache2._free_fraction = iter([0.05, 0.30]).__next__
+    cache2.get("y", mk)
+    assert len(cache2) == 1 and cache2.evictions == 1
+    # no device (CPU box): the free fraction is unknown and plays no part
+    cache3 = LRUByBytes(1 << 40, free_fraction=lambda: None)
+    for k in "pqr":
+        cache3.get(k, mk)
+    assert len(cache3) == 3
