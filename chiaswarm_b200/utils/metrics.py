@@ -12,6 +12,7 @@ A process-local registry of counters, gauges and histograms -- no dependency: th
     swarm_lanes_busy                           gauge
     swarm_gang_leases_total{size}              gang mode: jobs by number of ranks leased
     swarm_rank_world_restarts_total            gang mode: restarts after a dead rank / wedged gang
+    swarm_weight_cache_{bytes,entries,hits,misses,evictions}   resident models of this process (utils/weight_cache.py)
     swarm_gpu_{memory_used_bytes,utilization_ratio,sm_clock_mhz,throttle_reasons}{gpu}   gauges read from NVML per scrape
 
 Gauges may be callables, read when the page is rendered."""

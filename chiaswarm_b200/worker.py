@@ -99,6 +99,14 @@ class Worker:
         self.metrics.set("swarm_queue_depth", lambda: self.cpu_queue.qsize(), {"queue": "cpu"})
         self.metrics.set("swarm_queue_depth", lambda: self.result_queue.qsize(), {"queue": "results"})
         self.metrics.set("swarm_lanes_busy", lambda: self._busy)
+        from .utils.weight_cache import pipeline_cache
+
+        for name, read in (("swarm_weight_cache_bytes", lambda: pipeline_cache().bytes_resident()),
+                           ("swarm_weight_cache_entries", lambda: len(pipeline_cache())),
+                           ("swarm_weight_cache_hits", lambda: pipeline_cache().hits),
+                           ("swarm_weight_cache_misses", lambda: pipeline_cache().misses),
+                           ("swarm_weight_cache_evictions", lambda: pipeline_cache().evictions)):
+            self.metrics.set(name, read)
         port = int(getattr(self.settings, "metrics_port", 0) or 0)
         if port > 0 and self._metrics_server is None:
             metrics_mod.register_gpu_gauges(self.metrics)
