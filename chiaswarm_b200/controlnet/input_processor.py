@@ -6,7 +6,7 @@ lineart, openpose, scribble, softedge) come from `controlnet_aux` / transformers
 reference; they are used when importable and locally cached; soft edges / scribbles and lineart additionally have this
 tree's own networks (controlnet/annotators.py: HED from `lllyasviel/Annotators/ControlNetHED.pth`, the lineart generator
 from `sk_model.pth`, PiDiNet from `table5_pidinet.pth` in controlnet/pidinet.py), openpose this tree's body-pose detector (controlnet/openpose.py, `body_pose_model.pth`) and mlsd this
-tree's M-LSD network (controlnet/mlsd.py, `mlsd_large_512_fp32.pth`);
+tree's M-LSD network (controlnet/mlsd.py, `mlsd_large_512_fp32.pth`) and normalbae this tree's NNET (controlnet/normalbae.py, `scannet.pt`);
 otherwise a
 classical CPU approximation keeps the job serviceable (documented per type), so no type raises for a missing
 dependency.  Unknown types raise, as in the reference."""
@@ -162,6 +162,11 @@ def image_to_normal(image):
     det = _aux("NormalBaeDetector", "lllyasviel/Annotators")
     if det is not None:
         return det(image)
+    from .normalbae import load_normalbae  # this tree's own NNET, when its checkpoint is present locally
+
+    nnet = load_normalbae()
+    if nnet is not None:
+        return nnet.normals(image, next(nnet.parameters()).device)
     _stand_in("normalbae", "normals from Sobel gradients")
     gx, gy, _ = _sobel_mag(image)
     n = np.stack([-gx, -gy, np.full_like(gx, 255.0 / 4)], axis=2)

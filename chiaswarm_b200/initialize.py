@@ -92,7 +92,7 @@ async def download_diffusers(settings, fetch: bool = False):
 # the learned ControlNet annotators this tree implements, by repository (file names as published)
 ANNOTATOR_FILES = {
     "lllyasviel/Annotators": ["ControlNetHED.pth", "sk_model.pth", "table5_pidinet.pth", "body_pose_model.pth",
-                              "mlsd_large_512_fp32.pth"],
+                              "mlsd_large_512_fp32.pth", "scannet.pt"],
 }
 
 # what a worker reads from a model repository: configs, tokenizers, and the safetensors weights (fp16 variant preferred by
