@@ -80,7 +80,7 @@ async def download_diffusers(settings, fetch: bool = False):
     if fetch:  # the ControlNet pre-processors' own checkpoints (controlnet/{annotators,pidinet,mlsd,openpose}.py)
         for repo, files in ANNOTATOR_FILES.items():
             have = locate_checkpoint(repo, model_root=getattr(settings, "model_root", ""))
-            if have is not None and all((have / f).is_file() for f in files):
+            if have is not None and all((have / f).is_file() for f in (files or ["config.json"])):
                 report[repo] = "ok"
                 continue
             error = fetch_from_hub(repo, "main", getattr(settings, "huggingface_token", None), patterns=files)
@@ -93,6 +93,9 @@ async def download_diffusers(settings, fetch: bool = False):
 ANNOTATOR_FILES = {
     "lllyasviel/Annotators": ["ControlNetHED.pth", "sk_model.pth", "table5_pidinet.pth", "body_pose_model.pth",
                               "mlsd_large_512_fp32.pth", "scannet.pt"],
+    # the two annotators that run through transformers (controlnet/input_processor.py: depth, seg): whole repositories
+    "Intel/dpt-large": None,
+    "openmmlab/upernet-convnext-small": None,
 }
 
 # what a worker reads from a model repository: configs, tokenizers, and the safetensors weights (fp16 variant preferred by

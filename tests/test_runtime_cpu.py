@@ -266,7 +266,8 @@ def test_initialize_download_fetches_what_is_missing(tmp_path, monkeypatch):
     report = asyncio.run(initialize.init(["--silent", "--download"]))
     assert report["org/fetchable"] == "downloaded"
     assert report["org/unreachable"].startswith("missing: download failed (OSError: no route to host")
-    assert [c[0] for c in calls] == ["org/fetchable", "org/unreachable", "lllyasviel/Annotators"]
+    assert [c[0] for c in calls] == ["org/fetchable", "org/unreachable", "lllyasviel/Annotators", "Intel/dpt-large",
+                                     "openmmlab/upernet-convnext-small"]
     assert "*.safetensors" in calls[0][2] and all("*.ckpt" not in c[2] and "*.bin" not in c[2] for c in calls)
     assert "table5_pidinet.pth" in calls[2][2] and "body_pose_model.pth" in calls[2][2]   # the annotators' own files only
     assert report["lllyasviel/Annotators"] == "downloaded"
