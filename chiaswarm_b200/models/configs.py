@@ -94,6 +94,14 @@ ARCHITECTURES = {
     "sd21-base": _pipe("StableDiffusionPipeline", dict(_SD21_UNET, sample_size=64), _SD_VAE, _CLIP_H),
     "sdxl": _pipe("StableDiffusionXLPipeline", _SDXL_UNET, dict(_SD_VAE, scaling_factor=0.13025), _CLIP_L,
                   text_encoder_2=_CLIP_BIGG),
+    # the SDXL wiring at toy size: two text encoders (the second with a projection), hidden states concatenated
+    # (32 + 48 = cross-attention width 80), pooled vector + six size numbers as the added time embedding (48 + 6 * 8 = 96)
+    "tiny-sdxl": _pipe("StableDiffusionXLPipeline",
+                       dict(_TINY_UNET, cross_attention_dim=80, use_linear_projection=True, transformer_layers_per_block=(1, 2),
+                            addition_embed_type="text_time", addition_time_embed_dim=8, projection_class_embeddings_input_dim=96),
+                       dict(_TINY_VAE, scaling_factor=0.13025), _TINY_CLIP,
+                       text_encoder_2=dict(_TINY_CLIP, hidden_size=48, num_attention_heads=4, intermediate_size=64,
+                                           projection_dim=48, hidden_act="gelu")),
     "zeroscope": _pipe("TextToVideoSDPipeline", _ZEROSCOPE_UNET3D, _SD_VAE, _CLIP_H),
     "tiny-t2v": _pipe("TextToVideoSDPipeline", _TINY_UNET3D, _TINY_VAE, _TINY_CLIP),
     # stabilityai/stable-diffusion-x4-upscaler: 7 input channels (4 latent + the noised low-resolution RGB image), the
@@ -131,7 +139,7 @@ _NAME_RULES = [
     ("tiny-pix2pix", "tiny-pix2pix"),
     ("instruct-pix2pix", "instruct-pix2pix"),
     ("inpainting", "sd15-inpaint"), ("-inpaint", "sd15-inpaint"),
-    ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
+    ("tiny-sdxl", "tiny-sdxl"), ("stable-diffusion-xl", "sdxl"), ("sdxl", "sdxl"),
     ("tiny-x2-latent", "tiny-x2-latent"), ("sd-x2-latent-upscaler", "sd-x2-latent-upscaler"),
     ("tiny-x4", "tiny-x4"), ("x4-upscaler", "sd-x4-upscaler"),
     ("stable-diffusion-2-1-base", "sd21-base"), ("stable-diffusion-2-base", "sd21-base"),

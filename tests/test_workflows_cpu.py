@@ -367,3 +367,55 @@ def test_vae_force_upcast_runs_the_vae_in_fp32():
     assert enc.dtype == torch.float16 and torch.allclose(enc.float(), pipe.vae.encode(img.half().float(), None, False), atol=2e-3)
     pipe.to("cpu", torch.float32)
     assert "_vae_fp32" not in pipe.__dict__
+
+
+def test_sdxl_wiring_at_toy_size():
+    """`tiny-sdxl`: two text encoders (penultimate states concatenated, pooled vector from the projecting second one) and
+    the size micro-conditioning reach the UNet; SDXL's force_zeros_for_empty_prompt zeroes states AND pooled vector."""
+    import torch
+
+    from chiaswarm_b200.diffusion.pipelines import StableDiffusionPipeline
+
+    r = _run({"id": "xl", "model_name": "tiny-sdxl", "prompt": "a lighthouse", "height": 64, "width": 32, "seed": 5,
+              "num_inference_steps": 2})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert decode_artifact_image(r["artifacts"]["primary"]).size == (32, 64)
+    assert r["pipeline_config"]["_class_name"] == "StableDiffusionXLPipeline"
+
+    pipe = StableDiffusionPipeline.from_architecture("tiny-sdxl")
+    seen = {}
+    den = pipe._denoiser()
+    real = den.run
+
+    def spy(**k):
+        seen.update(embeds=k["embeds"].clone(), added={n: v.clone() for n, v in k["added"].items()})
+        return real(**k)
+
+    den.run = spy
+    kw = dict(prompt="a lighthouse", num_inference_steps=1, output_type="latent")
+    gen = lambda: torch.Generator().manual_seed(2)  # noqa: E731
+    a = pipe(height=64, width=32, generator=gen(), **kw).latents
+    assert seen["embeds"].shape == (2, 77, 80)                                     # [uncond, cond] x (32 + 48)
+    assert seen["added"]["text_embeds"].shape == (2, 48)
+    assert seen["added"]["time_ids"].tolist() == [[64.0, 32.0, 0.0, 0.0, 64.0, 32.0]] * 2
+    h1, _ = pipe.text_encoder(pipe.tokenizer(["a lighthouse"]), output_hidden_state=-2)
+    h2, pooled = pipe.text_encoder_2(pipe.tokenizer_2(["a lighthouse"]), output_hidden_state=-2)
+    assert torch.allclose(seen["embeds"][1], torch.cat([h1, h2], -1)[0], atol=1e-6)
+    assert torch.allclose(seen["added"]["text_embeds"][1], pooled[0], atol=1e-6)
+    # the size numbers condition the UNet: same latent shape, other micro-conditioning, other result
+    pipe.unet.add_embedding.linear_2.weight.data.normal_(0, 0.5)                   # (random init leaves this path faint)
+    a = pipe(height=64, width=32, generator=gen(), **kw).latents
+    ids = seen["added"]["time_ids"].clone()
+    real_embed = pipe.unet.time_embed
+
+    def other_size(t, batch, dtype, added_cond=None, class_labels=None):
+        return real_embed(t, batch, dtype, dict(added_cond, time_ids=ids * 2), class_labels)
+
+    pipe.unet.time_embed = other_size
+    b = pipe(height=64, width=32, generator=gen(), **kw).latents
+    pipe.unet.time_embed = real_embed
+    assert a.shape == b.shape and not torch.allclose(a, b)
+    pipe.config["force_zeros_for_empty_prompt"] = True
+    pipe(height=64, width=32, generator=gen(), **kw)
+    assert not seen["embeds"][0].any() and not seen["added"]["text_embeds"][0].any()
+    assert seen["embeds"][1].any() and seen["added"]["text_embeds"][1].any()
