@@ -69,8 +69,10 @@ def test_gang_jobs_match_single_rank(gang_env, monkeypatch):
         monkeypatch.setenv(k, v)
     single = _job("one")
     batch = _job("four", num_images_per_prompt=4, seed=5)
+    xl = _job("xl", model_name="tiny-sdxl", seed=11)    # the SDXL path: pooled text + size conditioning under a row split
     ref_single = synchronous_do_work_function(dict(single), Device("cpu"))
     ref_batch = synchronous_do_work_function(dict(batch), Device("cpu"))
+    ref_xl = synchronous_do_work_function(dict(xl), Device("cpu"))
     assert "error" not in ref_single["pipeline_config"], ref_single["pipeline_config"]
 
     sched = GangScheduler(2, _settings(parallel_mode="gang", gang_size=2, patch_min_pixels=64 * 64), use_cuda=False,
@@ -79,11 +81,12 @@ def test_gang_jobs_match_single_rank(gang_env, monkeypatch):
     try:
         got_single = sched.submit(single)
         got_batch = sched.submit(batch)
-        assert sched.leases_by_size == {2: 2}
+        got_xl = sched.submit(xl)
+        assert sched.leases_by_size == {2: 3}
         assert sched.pool.free_count() == 2
     finally:
         sched.stop()
-    for ref, got in ((ref_single, got_single), (ref_batch, got_batch)):
+    for ref, got in ((ref_single, got_single), (ref_batch, got_batch), (ref_xl, got_xl)):
         assert "error" not in got["pipeline_config"], got["pipeline_config"]
         assert got["pipeline_config"]["seed"] == ref["pipeline_config"]["seed"]
         a = np.asarray(decode_artifact_image(ref["artifacts"]["primary"]), dtype=np.float32)
