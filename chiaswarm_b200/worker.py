@@ -16,6 +16,8 @@ What differs from the reference:
   * a lane does not encode its own results: `do_work(..., defer_packaging=True)` returns with the image encoding owed and
     the result worker finishes it (`generator.materialize_result`) on an executor thread while the lane is already
     denoising its next job (10-40 ms of JPEG / thumbnail / base64 / hash work per image off the GPU's critical path);
+  * SIGTERM / SIGINT stop the polling, the jobs already taken are finished and their results delivered (or spooled)
+    before the process leaves (`request_stop`); the reference dies with its jobs;
   * polls, jobs, job times, uploads and queue depths are counted (utils/metrics.py) and served as Prometheus text at
     `/metrics` when `settings.metrics_port` is set (the reference has no metrics at all);
   * `Worker` is an object (testable against a fake hive) -- the module-level functions
@@ -124,15 +126,51 @@ class Worker:
         self._tasks.append(asyncio.create_task(self.result_worker()))
         if self._spool_dir() is not None and any(self._spool_dir().glob("*.json")):
             self._flush_task = asyncio.create_task(self.flush_spool())  # results a previous run could not deliver
+        self._stop = asyncio.Event()
+        self._install_signal_handlers()
         try:
-            while max_polls is None or self.polls < max_polls:
-                while self.work_queue.full():
-                    await sleep(1)
+            while (max_polls is None or self.polls < max_polls) and not self._stop.is_set():
+                while self.work_queue.full() and not self._stop.is_set():
+                    await self._nap(1, sleep)
+                if self._stop.is_set():
+                    break
                 delay = await self.ask_for_work()
-                await sleep(delay)
+                await self._nap(delay, sleep)
         finally:
-            if max_polls is not None:
+            if max_polls is not None or self._stop.is_set():
+                # bounded runs (tests) and a requested stop (SIGTERM / SIGINT: `docker stop`, a service manager) finish the
+                # jobs already taken from the hive and deliver -- or spool -- their results before leaving
                 await self.drain()
+
+    def request_stop(self):
+        """Stop asking the hive for work; `run()` returns once the jobs in flight are finished and their results sent."""
+        stop = getattr(self, "_stop", None)
+        if stop is not None and not stop.is_set():
+            print("stop requested: finishing the jobs in flight")
+            stop.set()
+
+    def _install_signal_handlers(self):
+        import signal
+        import threading
+
+        if threading.current_thread() is not threading.main_thread():
+            return
+        loop = asyncio.get_running_loop()
+        for sig in (signal.SIGTERM, signal.SIGINT):
+            try:
+                loop.add_signal_handler(sig, self.request_stop)
+            except (NotImplementedError, RuntimeError, ValueError):  # platforms / loops without signal support
+                pass
+
+    async def _nap(self, seconds, sleep):
+        """`sleep(seconds)` that a stop request cuts short (the idle / error back-off is up to 121 s)."""
+        if sleep is not asyncio.sleep:      # tests inject their own clock
+            await sleep(seconds)
+            return
+        try:
+            await asyncio.wait_for(self._stop.wait(), timeout=seconds)
+        except asyncio.TimeoutError:
+            pass
 
     async def drain(self):
         await self.work_queue.join()

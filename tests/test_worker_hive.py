@@ -308,3 +308,41 @@ def test_gpu_gauges_come_from_nvml_and_survive_its_absence():
             raise OSError("libnvidia-ml.so.1: cannot open shared object file")
 
     assert M.register_gpu_gauges(M.new_registry(), NoDriver) == 0
+
+
+def test_a_stop_request_finishes_the_jobs_in_flight():
+    """SIGTERM (here: `request_stop`, and a real signal to this process) ends the polling at once -- even inside the 11 s
+    idle back-off -- while the job already taken is finished and its result delivered."""
+    import os
+    import signal
+    import time
+
+    async def main(use_signal):
+        hive = FakeHive()
+        uri = await hive.start()
+        hive.jobs = [{"id": "last", "model_name": "tiny-sd", "prompt": "p", "height": 64, "width": 64,
+                      "num_inference_steps": 1, "seed": 1}]
+        try:
+            w = _worker(uri)
+
+            async def stopper():
+                while not hive.work_requests:
+                    await asyncio.sleep(0.01)
+                await asyncio.sleep(0.05)
+                if use_signal:
+                    os.kill(os.getpid(), signal.SIGTERM)
+                else:
+                    w.request_stop()
+
+            t0 = time.time()
+            task = asyncio.create_task(stopper())
+            await w.run()                                   # unbounded serve loop: only the stop request ends it
+            await task
+            assert time.time() - t0 < 60
+            assert [r["id"] for r in hive.results] == ["last"] and len(hive.work_requests) <= 2
+            assert w._tasks == []
+        finally:
+            await hive.stop()
+
+    asyncio.run(main(False))
+    asyncio.run(main(True))
