@@ -89,13 +89,20 @@ class Supervisor:
         finally:
             self.stop()
 
-    def stop(self):
+    def stop(self, grace_s: float = 60.0):
+        """SIGTERM to every worker: each stops polling, finishes the job it holds and delivers the result
+        (worker.py::request_stop); a worker still alive after `grace_s` is killed."""
         self._stop = True
         for p in self.procs.values():
             if p.is_alive():
                 p.terminate()
+        deadline = time.time() + grace_s
         for p in self.procs.values():
-            p.join(timeout=10)
+            p.join(timeout=max(0.0, deadline - time.time()))
+        for p in self.procs.values():  # exactly the processes this supervisor started
+            if p.is_alive():
+                p.kill()
+                p.join(timeout=5)
 
 
 def main(argv=None):
