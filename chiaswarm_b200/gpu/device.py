@@ -8,6 +8,7 @@ start without CUDA, swarm/worker.py:167-168), and the returned config is a plain
 than a mutated frozen mapping (Q6)."""
 from __future__ import annotations
 
+import contextlib
 import logging
 from threading import Lock
 
@@ -49,7 +50,10 @@ class Device:
             if seed is None:
                 seed = torch.seed()
             kwargs["generator"] = torch.Generator(device=self.idenitifier()).manual_seed(seed)
-            artifacts, pipeline_config = func(self.idenitifier(), model_name, **kwargs)
+            # the callback runs on an executor thread whose current CUDA device is 0: make this lane's GPU current for it
+            # (the native kernels launch on the current device's stream; one process serving several GPUs needs this)
+            with (contextlib.nullcontext() if self.is_cpu else torch.cuda.device(self.device_id)):
+                artifacts, pipeline_config = func(self.idenitifier(), model_name, **kwargs)
             pipeline_config = dict(pipeline_config)
             pipeline_config["seed"] = seed
             return artifacts, pipeline_config

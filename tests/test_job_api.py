@@ -276,3 +276,43 @@ def test_deferred_packaging_gives_the_same_result_off_the_lane():
     assert want["fatal_error"] is True and "Too many images" in want["pipeline_config"]["error"]
     assert got["fatal_error"] is True and got["pipeline_config"] == want["pipeline_config"] and got["id"] == "d2"
     assert got["artifacts"]["primary"]["content_type"] == "image/png"
+
+
+def test_device_makes_its_gpu_current_for_the_callback(monkeypatch):
+    """One process serving several GPUs (`python -m swarm.worker`): the callback of lane k runs with cuda:k current, so
+    the native kernels launch on that GPU's stream, not on device 0's."""
+    import contextlib
+
+    import torch
+
+    from chiaswarm_b200.gpu import device as dev_mod
+
+    entered = []
+
+    @contextlib.contextmanager
+    def fake_device(idx):
+        entered.append(("enter", idx))
+        yield
+        entered.append(("exit", idx))
+
+    class FakeGen:
+        def __init__(self, device=None):
+            self.device = device
+
+        def manual_seed(self, s):
+            return self
+
+    monkeypatch.setattr(torch.cuda, "mem_get_info", lambda i=None: (1 << 34, 180 << 30))
+    monkeypatch.setattr(torch.cuda, "device", fake_device)
+    monkeypatch.setattr(torch, "Generator", FakeGen)
+    d = dev_mod.Device(3)
+
+    def cb(identifier, model_name, **kw):
+        assert entered == [("enter", 3)] and identifier == "cuda:3" and kw["generator"].device == "cuda:3"
+        return {}, {}
+
+    d(cb, model_name="m", seed=1)
+    assert entered == [("enter", 3), ("exit", 3)]
+    entered.clear()
+    dev_mod.Device("cpu")(lambda identifier, model_name, **kw: ({}, {}), model_name="m", seed=1)
+    assert entered == []
