@@ -304,6 +304,7 @@ def test_device_makes_its_gpu_current_for_the_callback(monkeypatch):
 
     monkeypatch.setattr(torch.cuda, "mem_get_info", lambda i=None: (1 << 34, 180 << 30))
     monkeypatch.setattr(torch.cuda, "device", fake_device)
+    monkeypatch.setattr(torch.cuda, "get_device_name", lambda i=None: "B200")
     monkeypatch.setattr(torch, "Generator", FakeGen)
     d = dev_mod.Device(3)
 
