@@ -94,8 +94,10 @@ class ClipTextEngine:
         torch.cuda.synchronize()
         graph = None
         if os.environ.get("SDAAS_CUDA_GRAPH", "1") not in ("0", "false", ""):
+            from .denoiser import capture_mode
+
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            with torch.cuda.graph(graph, capture_error_mode=capture_mode()):
                 rec.run()
         entry = self._plans[(b, s)] = (x_in, penult if penult is not None else x_in, last, rec, graph)
         if len(self._plans) > 8:

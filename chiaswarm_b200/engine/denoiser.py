@@ -31,6 +31,15 @@ def _use_graphs() -> bool:
     return os.environ.get("SDAAS_CUDA_GRAPH", "1") not in ("0", "false", "")
 
 
+def capture_mode() -> str:
+    """cudaStreamCaptureMode of the plan captures.  "global" (the default, one lane per process: launcher, gang ranks,
+    bench) makes an allocation on ANY thread during a capture an error; a process that serves several GPUs from lane
+    threads (`python -m swarm.worker`, worker.py sets SW_GRAPH_CAPTURE_MODE) needs "thread_local", or lane A's capture
+    fails whenever lane B allocates."""
+    mode = os.environ.get("SW_GRAPH_CAPTURE_MODE", "global")
+    return mode if mode in ("global", "thread_local", "relaxed") else "global"
+
+
 class _StepGraph:
     """Static buffers + recorded plan (+ CUDA graph) for one problem shape."""
 
@@ -93,7 +102,7 @@ class _StepGraph:
         torch.cuda.synchronize()
         if _use_graphs():
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, capture_error_mode=capture_mode()):
                 self.rec.run()
             self.graph = g
         self.launches_per_step = len(self.rec)
@@ -294,7 +303,7 @@ class SM100Denoiser:
             graph = None
             if _use_graphs():
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
+                with torch.cuda.graph(graph, capture_error_mode=capture_mode()):
                     rec.run()
             entry = (zin, out, rec, graph)
             self._vae_graphs[key] = entry

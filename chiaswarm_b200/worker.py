@@ -94,6 +94,11 @@ class Worker:
 
         lanes = max(1, len(self.devices))
         print(f"Found {len(self.devices)} GPUs")
+        if sum(1 for d in self.devices if not getattr(d, "is_cpu", True)) > 1:
+            import os
+
+            # several GPU lanes in ONE process: plan captures must not trip over the other lanes' allocations
+            os.environ.setdefault("SW_GRAPH_CAPTURE_MODE", "thread_local")
         self.work_queue = asyncio.Queue(maxsize=lanes)
         self.cpu_queue = asyncio.Queue()
         self.available_gpus = asyncio.Semaphore(lanes)
