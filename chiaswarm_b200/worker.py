@@ -328,6 +328,11 @@ class Worker:
                     await self.flush_spool()  # the hive is taking results again: hand over what it missed
                 else:
                     self.spool_result(result)
+            except asyncio.CancelledError:
+                raise
+            except Exception as e:  # the result loop must outlive any one result (reference: swarm/worker.py:137-142)
+                logging.exception(e)
+                print(f"result_worker {e}")
             finally:
                 self.result_queue.task_done()
 

@@ -347,3 +347,23 @@ def test_a_stop_request_finishes_the_jobs_in_flight():
 
     asyncio.run(main(False))
     asyncio.run(main(True))
+
+
+def test_the_result_loop_outlives_a_result_it_cannot_handle(monkeypatch):
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        try:
+            w = _worker(uri)
+            await w.startup()
+            task = asyncio.create_task(w.result_worker())
+            await w.result_queue.put(object())                       # not a result at all: materialising it blows up
+            await w.result_queue.put({"id": "fine", "artifacts": {}, "pipeline_config": {}})
+            await asyncio.wait_for(w.result_queue.join(), timeout=20)
+            assert not task.done() and [r["id"] for r in hive.results] == ["fine"]
+            task.cancel()
+            await asyncio.gather(task, return_exceptions=True)
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
