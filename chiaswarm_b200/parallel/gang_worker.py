@@ -383,7 +383,13 @@ class GangWorker(Worker):
             await asyncio.get_running_loop().run_in_executor(None, self.scheduler.start)
 
     async def execute(self, job, lane):
-        return await asyncio.get_running_loop().run_in_executor(None, self.scheduler.submit, job)
+        try:
+            return await asyncio.get_running_loop().run_in_executor(None, self.scheduler.submit, job)
+        except asyncio.CancelledError:
+            raise
+        except Exception as e:  # a scheduler fault is answered like any other transient failure: the hive re-issues the job
+            logging.exception(e)
+            return GangScheduler._error_result(job, f"gang scheduler: {type(e).__name__}: {e}")
 
     async def drain(self):
         await super().drain()
