@@ -25,6 +25,11 @@ _DEFAULTS = {
     "model_root": "",            # directory holding diffusers-layout checkpoints (HF cache also searched)
     "weight_cache_gb": 120,      # resident weight cache budget per GPU
     "result_retries": 3,         # bounded retry for POST /api/results (reference drops on failure)
+    # the reference's cadence (poll holds a lane; 1 s pause after a poll that returned jobs) caps a lane at one poll's worth
+    # of jobs per (1 s + their run time) -- fine for a 10 s job, idle time for a 0.25 s one.  Both knobs default to the
+    # reference's behaviour; raise / lower them when the hive allows
+    "prefetch_jobs": 0,          # > 0: keep up to this many extra jobs queued locally and poll while the lanes are busy
+    "poll_found_s": 1.0,         # pause after a poll that returned jobs
     "result_spool": "spool",     # results the hive did not take are kept here (under SDAAS_ROOT) and re-sent later; "" = drop
     "metrics_port": 0,           # > 0: serve Prometheus text at http://<metrics_host>:<port>/metrics (utils/metrics.py)
     "metrics_host": "127.0.0.1",
@@ -33,7 +38,7 @@ _DEFAULTS = {
 _ENV = {"sdaas_token": "SDAAS_TOKEN", "sdaas_uri": "SDAAS_URI", "worker_name": "SDAAS_WORKERNAME",
         "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE", "job_timeout_s": "SDAAS_JOB_TIMEOUT_S", "patch_min_pixels": "SDAAS_PATCH_MIN_PIXELS",
         "kernel_backend": "SDAAS_KERNEL_BACKEND", "model_root": "SDAAS_MODEL_ROOT",
-        "result_spool": "SDAAS_RESULT_SPOOL", "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
+        "prefetch_jobs": "SDAAS_PREFETCH_JOBS", "poll_found_s": "SDAAS_POLL_FOUND_S", "result_spool": "SDAAS_RESULT_SPOOL", "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
 
 
 class Settings:
@@ -51,6 +56,8 @@ class Settings:
     model_root: str = _DEFAULTS["model_root"]
     weight_cache_gb: int = _DEFAULTS["weight_cache_gb"]
     result_retries: int = _DEFAULTS["result_retries"]
+    prefetch_jobs: int = _DEFAULTS["prefetch_jobs"]
+    poll_found_s: float = _DEFAULTS["poll_found_s"]
     result_spool: str = _DEFAULTS["result_spool"]
     metrics_port: int = _DEFAULTS["metrics_port"]
     metrics_host: str = _DEFAULTS["metrics_host"]

@@ -99,7 +99,8 @@ class Worker:
 
             # several GPU lanes in ONE process: plan captures must not trip over the other lanes' allocations
             os.environ.setdefault("SW_GRAPH_CAPTURE_MODE", "thread_local")
-        self.work_queue = asyncio.Queue(maxsize=lanes)
+        self.prefetch = max(0, int(getattr(self.settings, "prefetch_jobs", 0) or 0))
+        self.work_queue = asyncio.Queue(maxsize=lanes + self.prefetch)
         self.cpu_queue = asyncio.Queue()
         self.available_gpus = asyncio.Semaphore(lanes)
         self.metrics.set("swarm_queue_depth", lambda: self.work_queue.qsize(), {"queue": "gpu"})
@@ -195,7 +196,11 @@ class Worker:
 
     # ------------------------------------------------------------------ hive I/O
     async def ask_for_work(self) -> int:
-        await self.available_gpus.acquire()  # no polling while every lane is busy
+        # reference behaviour (Q11): the poll holds a lane, so there is no polling while every lane is busy.  With
+        # `settings.prefetch_jobs` the local queue is deeper than the lanes and polling goes on while they work
+        holds_lane = getattr(self, "prefetch", 0) == 0
+        if holds_lane:
+            await self.available_gpus.acquire()
         self.polls += 1
         print(f"{datetime.now()}: Asking for work from the hive at {self.hive_uri}...")
         try:
@@ -217,7 +222,7 @@ class Worker:
                             else:
                                 await self.work_queue.put(job)
                         self.metrics.inc("swarm_polls_total", {"outcome": "jobs" if found else "idle"})
-                        return POLL_FOUND_S if found else POLL_IDLE_S
+                        return float(getattr(self.settings, "poll_found_s", POLL_FOUND_S)) if found else POLL_IDLE_S
                     if response.status == 400:
                         body = await response.json()
                         print(f"{self.hive_uri} says {body.pop('message', 'bad worker')}")
@@ -230,7 +235,8 @@ class Worker:
             self.metrics.inc("swarm_polls_total", {"outcome": "error"})
             return POLL_ERROR_S
         finally:
-            self.available_gpus.release()
+            if holds_lane:
+                self.available_gpus.release()
         return POLL_IDLE_S
 
     async def submit_result(self, result) -> bool:

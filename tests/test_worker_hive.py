@@ -367,3 +367,48 @@ def test_the_result_loop_outlives_a_result_it_cannot_handle(monkeypatch):
             await hive.stop()
 
     asyncio.run(main())
+
+
+def test_prefetch_polls_while_the_lane_is_busy():
+    """Reference cadence (default): the poll holds a lane, so a busy single-lane worker does not poll.  With
+    `settings.prefetch_jobs` the local queue is deeper than the lanes and the hive is asked while the lane works."""
+    import threading
+
+    async def main(prefetch):
+        hive = FakeHive()
+        uri = await hive.start()
+        try:
+            w = _worker(uri)
+            w.settings.prefetch_jobs = prefetch
+            gate = threading.Event()
+
+            async def slow(job, device):
+                await asyncio.get_running_loop().run_in_executor(None, gate.wait, 10)
+                return {"id": job["id"], "artifacts": {}, "pipeline_config": {}}
+
+            w.execute = slow
+            await w.startup()
+            assert w.work_queue.maxsize == 1 + prefetch
+            lane = asyncio.create_task(w.device_worker(w.devices[0]))
+            hive.jobs = [{"id": "a", "model_name": "m"}]
+            assert await w.ask_for_work() == 1.0
+            await asyncio.sleep(0.1)                                  # the lane now holds job "a" (and the only semaphore slot)
+            hive.jobs = [{"id": "b", "model_name": "m"}]
+            poll = asyncio.create_task(w.ask_for_work())
+            await asyncio.sleep(0.3)
+            polled_while_busy = poll.done()
+            gate.set()
+            await asyncio.wait_for(poll, 10)
+            await asyncio.wait_for(w.work_queue.join(), 10)
+            lane.cancel()
+            await asyncio.gather(lane, return_exceptions=True)
+            return polled_while_busy, len(hive.work_requests)
+        finally:
+            await hive.stop()
+
+    assert asyncio.run(main(0)) == (False, 2)       # the second poll waited for the lane
+    assert asyncio.run(main(2)) == (True, 2)        # the second poll went out while the lane was working
+    # the pause after a productive poll is a setting (default: the reference's 1 s)
+    from chiaswarm_b200.settings import Settings
+
+    assert Settings().poll_found_s == 1.0 and Settings().prefetch_jobs == 0
