@@ -412,3 +412,15 @@ def test_prefetch_polls_while_the_lane_is_busy():
     from chiaswarm_b200.settings import Settings
 
     assert Settings().poll_found_s == 1.0 and Settings().prefetch_jobs == 0
+
+
+def test_host_loop_benchmark_script_runs():
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "scripts", "bench_host_loop.py"), "--jobs", "6", "--gpu-ms", "5",
+                          "--size", "64", "--prefetch", "2"], capture_output=True, text=True, timeout=240, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "encoding on the result worker" in out.stdout and "jobs/s" in out.stdout
