@@ -392,11 +392,15 @@ def test_prefetch_polls_while_the_lane_is_busy():
             lane = asyncio.create_task(w.device_worker(w.devices[0]))
             hive.jobs = [{"id": "a", "model_name": "m"}]
             assert await w.ask_for_work() == 1.0
-            await asyncio.sleep(0.1)                                  # the lane now holds job "a" (and the only semaphore slot)
+            for _ in range(500):                                      # until the lane holds job "a" (and the only semaphore slot)
+                if w._busy == 1:
+                    break
+                await asyncio.sleep(0.01)
+            assert w._busy == 1
             hive.jobs = [{"id": "b", "model_name": "m"}]
             poll = asyncio.create_task(w.ask_for_work())
-            await asyncio.sleep(0.3)
-            polled_while_busy = poll.done()
+            done, _ = await asyncio.wait({poll}, timeout=(10 if prefetch else 0.5))
+            polled_while_busy = bool(done)
             gate.set()
             await asyncio.wait_for(poll, 10)
             await asyncio.wait_for(w.work_queue.join(), 10)
