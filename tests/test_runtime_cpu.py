@@ -402,12 +402,20 @@ def test_gang_leases_are_first_come_first_served():
         got[name] = pool.lease(size, timeout=20)
         order.append(name)
 
+    def until(cond):
+        for _ in range(1000):
+            if cond():
+                return
+            time.sleep(0.01)
+        pytest.fail("timed out")
+
     big = threading.Thread(target=want, args=("big", 2))
     big.start()
-    time.sleep(0.2)                             # the gang-of-2 request is waiting for rank 0
+    until(lambda: len(pool._waiting) == 1)      # the gang-of-2 request is waiting for rank 0
     small = threading.Thread(target=want, args=("small", 1))
     small.start()
-    time.sleep(0.3)
+    until(lambda: len(pool._waiting) == 2)
+    time.sleep(0.2)
     assert order == [] and pool.free_count() == 1   # the later small job did NOT take the free rank past the big one
     with pytest.raises(Exception, match="busy"):
         pool.lease(1, timeout=0)                # non-blocking callers do not jump the line either
