@@ -129,7 +129,10 @@ class Worker:
             print(f"Started device {device.descriptor()}")
         if self.cpu_lane:
             self._tasks.append(asyncio.create_task(self.cpu_worker()))
-        self._tasks.append(asyncio.create_task(self.result_worker()))
+        # one result worker keeps up with ~40 images/s of encoding (scripts/bench_host_loop.py); a process that serves many
+        # lanes gets one per two lanes, at most four
+        for _ in range(max(1, min(4, len(self.devices) // 2))):
+            self._tasks.append(asyncio.create_task(self.result_worker()))
         if self._spool_dir() is not None and any(self._spool_dir().glob("*.json")):
             self._flush_task = asyncio.create_task(self.flush_spool())  # results a previous run could not deliver
         self._stop = asyncio.Event()
