@@ -17,7 +17,7 @@ import logging
 
 import torch
 
-from ..output_processor import OutputProcessor
+from ..output_processor import BatchArtifacts, OutputProcessor
 from ..parallel.context import job_gang
 from ..registry import resolve
 from ..utils.weight_cache import pipeline_cache
@@ -34,6 +34,7 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
     lora = kwargs.pop("lora", None)
     kwargs.pop("supports_xformers", True)  # no xformers here: attention is our own kernel
     cross_attention_scale = kwargs.pop("cross_attention_scale", 1.0)
+    batch_seeds = kwargs.pop("batch_seeds", None)  # several hive jobs in one denoising run: one seed and one result per job
 
     output_processor = OutputProcessor(kwargs.pop("outputs", ["primary"]), kwargs.pop("content_type", "image/jpeg"))
 
@@ -78,6 +79,8 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
 
     # a job that leased a gang (parallel/gang_worker.py) runs SPMD on every rank of it: one large image goes
     # patch-parallel, a batch is split across the ranks; without a lease this is the reference's one-GPU call
+    if batch_seeds is not None:
+        kwargs["seeds"] = batch_seeds
     p = pipeline(gang=job_gang(), **kwargs)
 
     pipeline_config = dict(pipeline.config)
@@ -89,6 +92,15 @@ def diffusion_callback(device_identifier, model_name, **kwargs):
     note = getattr(kwargs.get("image"), "info", {}).get("controlnet_annotator")
     if note:  # the control image came from a classical stand-in, not from the learned annotator (controlnet/input_processor.py)
         pipeline_config["controlnet_annotator"] = note
+    if batch_seeds is not None:
+        flags = p.nsfw_content_detected if isinstance(p.nsfw_content_detected, list) else [False] * len(p.images)
+        pipeline_config.pop("nsfw", None)
+        per_job = []
+        for image in p.images:
+            one = OutputProcessor(output_processor.output_list, output_processor.main_content_type)
+            one.add_outputs([image])
+            per_job.append(one.get_results())
+        return BatchArtifacts(per_job, flags), pipeline_config
     images = p.images
     if upscale:
         images = upscale_image(images, device_identifier, kwargs.get("prompt", ""), num_images_per_prompt,

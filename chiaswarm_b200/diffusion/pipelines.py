@@ -294,7 +294,7 @@ class StableDiffusionPipeline:
                  guidance_scale=7.5, num_images_per_prompt=1, generator=None, image=None, mask_image=None,
                  strength=0.8, image_guidance_scale=1.5, controlnet_conditioning_scale=1.0, eta=0.0,
                  cross_attention_kwargs=None, output_type="pil", latents=None, prompt_embeds=None, gang=None,
-                 noise_level=20, **ignored):
+                 noise_level=20, seeds=None, **ignored):
         """`gang` (parallel.runtime.Gang, every rank making this same call with the same seed): a single image runs
         patch-parallel over it (engine/patch_engine.py), a batch is split over it (each rank denoises and decodes
         batch / world images; the images are all-gathered, so every rank returns the full set)."""
@@ -400,8 +400,18 @@ class StableDiffusionPipeline:
         plan = schedulers.make_plan(self.scheduler_kind, int(num_inference_steps), sched_cfg, self.use_karras_sigmas)
         shape = (batch, lat_ch, h8, w8)
 
+        # `seeds` (one per image): every image draws its noise from its own generator, exactly what it would draw as a
+        # job of its own -- several hive jobs merged into one batch (generator.synchronous_do_work_batch) stay reproducible
+        row_gens = None
+        if seeds is not None:
+            if len(seeds) != batch:
+                raise ValueError(f"`seeds` has {len(seeds)} entries for a batch of {batch}")
+            row_gens = [torch.Generator(device=self.device).manual_seed(int(sd)) for sd in seeds]
+
         def randn():
-            return torch.randn(shape, generator=generator, device=self.device, dtype=self.dtype)
+            if row_gens is None:
+                return torch.randn(shape, generator=generator, device=self.device, dtype=self.dtype)
+            return torch.cat([torch.randn((1,) + shape[1:], generator=g, device=self.device, dtype=self.dtype) for g in row_gens])
 
         extra = None          # constant extra UNet input channels [n_cond*B, C_extra, h8, w8]
         control = None        # control image [n_cond*B, 3, H, W] in [0,1]

@@ -38,6 +38,15 @@ class DeferredArtifact:
         return self._value
 
 
+class BatchArtifacts(list):
+    """What the image callback answers when several jobs shared one denoising run (generator.synchronous_do_work_batch):
+    one artifacts dict per job, in job order, plus the per-image NSFW flags."""
+
+    def __init__(self, per_job, nsfw=None):
+        super().__init__(per_job)
+        self.nsfw = list(nsfw) if nsfw is not None else [False] * len(per_job)
+
+
 def packaging_deferred() -> bool:
     return bool(getattr(_tls, "defer", False))
 

@@ -30,6 +30,8 @@ _DEFAULTS = {
     # reference's behaviour; raise / lower them when the hive allows
     "prefetch_jobs": 0,          # > 0: keep up to this many extra jobs queued locally and poll while the lanes are busy
     "poll_found_s": 1.0,         # pause after a poll that returned jobs
+    "max_batch": 1,              # > 1: a lane takes up to this many WAITING jobs at once; those that differ only in prompt /
+                                 # seed share one denoising run (generator.synchronous_do_work_batch).  Needs prefetch_jobs
     "result_spool": "spool",     # results the hive did not take are kept here (under SDAAS_ROOT) and re-sent later; "" = drop
     "metrics_port": 0,           # > 0: serve Prometheus text at http://<metrics_host>:<port>/metrics (utils/metrics.py)
     "metrics_host": "127.0.0.1",
@@ -38,7 +40,7 @@ _DEFAULTS = {
 _ENV = {"sdaas_token": "SDAAS_TOKEN", "sdaas_uri": "SDAAS_URI", "worker_name": "SDAAS_WORKERNAME",
         "parallel_mode": "SDAAS_PARALLEL_MODE", "gang_size": "SDAAS_GANG_SIZE", "job_timeout_s": "SDAAS_JOB_TIMEOUT_S", "patch_min_pixels": "SDAAS_PATCH_MIN_PIXELS",
         "kernel_backend": "SDAAS_KERNEL_BACKEND", "model_root": "SDAAS_MODEL_ROOT",
-        "prefetch_jobs": "SDAAS_PREFETCH_JOBS", "poll_found_s": "SDAAS_POLL_FOUND_S", "result_spool": "SDAAS_RESULT_SPOOL", "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
+        "prefetch_jobs": "SDAAS_PREFETCH_JOBS", "poll_found_s": "SDAAS_POLL_FOUND_S", "max_batch": "SDAAS_MAX_BATCH", "result_spool": "SDAAS_RESULT_SPOOL", "metrics_port": "SDAAS_METRICS_PORT", "metrics_host": "SDAAS_METRICS_HOST"}
 
 
 class Settings:
@@ -58,6 +60,7 @@ class Settings:
     result_retries: int = _DEFAULTS["result_retries"]
     prefetch_jobs: int = _DEFAULTS["prefetch_jobs"]
     poll_found_s: float = _DEFAULTS["poll_found_s"]
+    max_batch: int = _DEFAULTS["max_batch"]
     result_spool: str = _DEFAULTS["result_spool"]
     metrics_port: int = _DEFAULTS["metrics_port"]
     metrics_host: str = _DEFAULTS["metrics_host"]

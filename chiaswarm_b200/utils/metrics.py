@@ -122,6 +122,7 @@ _HELP = {
     "swarm_jobs_total": ("counter", "Finished jobs by workflow and outcome (ok, error, fatal)."),
     "swarm_job_seconds": ("histogram", "Wall time per job in seconds."),
     "swarm_results_posted_total": ("counter", "Result uploads by outcome (ok, rejected, failed)."),
+    "swarm_batches_total": ("counter", "Lane calls that took several waiting jobs at once, by number of jobs."),
     "swarm_queue_depth": ("gauge", "Jobs waiting for an execution lane."),
     "swarm_lanes_busy": ("gauge", "Execution lanes running a job."),
     "swarm_gang_leases_total": ("counter", "Gang mode: jobs by number of ranks leased."),

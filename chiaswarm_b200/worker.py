@@ -278,15 +278,42 @@ class Worker:
         self.metrics.inc("swarm_jobs_total", {"workflow": workflow, "outcome": metrics_mod.job_outcome(result)})
         return result
 
+    async def execute_batch(self, jobs, device):
+        """Several queued jobs on one lane in one call (`settings.max_batch` > 1): compatible ones share a denoising run
+        (generator.synchronous_do_work_batch).  Results in job order."""
+        from .generator import synchronous_do_work_batch
+
+        return await asyncio.get_running_loop().run_in_executor(None, synchronous_do_work_batch, jobs, device, True)
+
     async def device_worker(self, device: Device):
+        max_batch = max(1, int(getattr(self.settings, "max_batch", 1) or 1))
         while True:
-            job = await self.work_queue.get()
+            jobs = [await self.work_queue.get()]
+            while len(jobs) < max_batch:  # what is ALREADY waiting (settings.prefetch_jobs fills the queue): never waits for more
+                try:
+                    jobs.append(self.work_queue.get_nowait())
+                except asyncio.QueueEmpty:
+                    break
             acquired = False
             try:
                 await self.available_gpus.acquire()
                 acquired = True
-                result = await self._counted(job, lambda: self.execute(job, device))
-                await self.result_queue.put(result)
+                if len(jobs) == 1:
+                    results = [await self._counted(jobs[0], lambda: self.execute(jobs[0], device))]
+                else:
+                    t0 = time.monotonic()
+                    self._busy += 1
+                    try:
+                        results = await self.execute_batch(jobs, device)
+                    finally:
+                        self._busy -= 1
+                    for job, result in zip(jobs, results):
+                        workflow = str(job.get("workflow") or "image")
+                        self.metrics.observe("swarm_job_seconds", time.monotonic() - t0, {"workflow": workflow})
+                        self.metrics.inc("swarm_jobs_total", {"workflow": workflow, "outcome": metrics_mod.job_outcome(result)})
+                    self.metrics.inc("swarm_batches_total", {"jobs": len(jobs)})
+                for result in results:
+                    await self.result_queue.put(result)
             except asyncio.CancelledError:
                 raise
             except Exception as e:
@@ -295,7 +322,8 @@ class Worker:
             finally:
                 if acquired:
                     self.available_gpus.release()
-                self.work_queue.task_done()
+                for _ in jobs:
+                    self.work_queue.task_done()
 
     async def cpu_worker(self):
         cpu = Device("cpu")

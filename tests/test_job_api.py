@@ -317,3 +317,54 @@ def test_device_makes_its_gpu_current_for_the_callback(monkeypatch):
     entered.clear()
     dev_mod.Device("cpu")(lambda identifier, model_name, **kw: ({}, {}), model_name="m", seed=1)
     assert entered == []
+
+
+def test_jobs_that_differ_only_in_prompt_and_seed_share_one_denoising_run(monkeypatch):
+    """generator.synchronous_do_work_batch: compatible jobs run as one batch, each image from its own seed (so each result
+    is what the job gives alone); incompatible and malformed jobs in the same call keep their own path and verdict."""
+    import numpy as np
+
+    from chiaswarm_b200.diffusion import pipelines
+    from chiaswarm_b200.generator import synchronous_do_work_batch, synchronous_do_work_function
+    from chiaswarm_b200.gpu.device import Device
+
+    base = {"model_name": "tiny-sd", "height": 64, "width": 64, "num_inference_steps": 2, "content_type": "image/png"}
+    jobs = [dict(base, id="a", prompt="a cat", seed=3),
+            dict(base, id="wide", prompt="a fox", seed=4, width=32),                      # other shape: runs alone
+            dict(base, id="b", prompt="a dog", negative_prompt="", seed=5),               # negative "" vs None: own group
+            dict(base, id="bad", prompt="x", height=5000),                                 # malformed: fatal, others unaffected
+            dict(base, id="c", prompt="a bird", seed=6),
+            dict(base, id="d", prompt="a fish", seed=7, num_images_per_prompt=2)]          # a grid of its own: runs alone
+    calls = []
+    real = pipelines.StableDiffusionPipeline.__call__
+
+    def spy(self, *a, **k):
+        calls.append(k.get("prompt"))
+        return real(self, *a, **k)
+
+    monkeypatch.setattr(pipelines.StableDiffusionPipeline, "__call__", spy)
+    dev = Device("cpu")
+    got = synchronous_do_work_batch([dict(j) for j in jobs], dev)
+    assert [r["id"] for r in got] == ["a", "wide", "b", "bad", "c", "d"]
+    assert calls.count(["a cat", "a bird"]) == 1 and len(calls) == 4                       # a + c shared one run
+    assert got[3]["fatal_error"] is True and "max image size" in got[3]["pipeline_config"]["error"]
+    assert [got[i]["pipeline_config"]["seed"] for i in (0, 1, 2, 4, 5)] == [3, 4, 5, 6, 7]
+    calls.clear()
+    for j, r in zip(jobs, got):
+        if j["id"] == "bad":
+            continue
+        alone = synchronous_do_work_function(dict(j), dev)
+        a = np.asarray(decode_artifact_image(alone["artifacts"]["primary"]), dtype=np.int16)
+        b = np.asarray(decode_artifact_image(r["artifacts"]["primary"]), dtype=np.int16)
+        assert a.shape == b.shape and int(np.abs(a - b).max()) <= 1, j["id"]
+        assert set(r["artifacts"]["primary"]) == {"blob", "content_type", "thumbnail", "sha256_hash"}
+
+    # a batch that fails as a whole is re-run job by job: each job still gets its own verdict
+    def broken(self, *a, **k):
+        if isinstance(k.get("prompt"), list):
+            raise RuntimeError("out of memory at this batch size")
+        return real(self, *a, **k)
+
+    monkeypatch.setattr(pipelines.StableDiffusionPipeline, "__call__", broken)
+    again = synchronous_do_work_batch([dict(jobs[0]), dict(jobs[4])], dev)
+    assert [r["id"] for r in again] == ["a", "c"] and all("error" not in r["pipeline_config"] for r in again)

@@ -428,3 +428,47 @@ def test_host_loop_benchmark_script_runs():
                           "--size", "64", "--prefetch", "2"], capture_output=True, text=True, timeout=240, cwd=root)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "encoding on the result worker" in out.stdout and "jobs/s" in out.stdout
+
+
+def test_max_batch_merges_waiting_jobs_through_the_hive_loop(monkeypatch):
+    """settings.max_batch + prefetch_jobs: jobs waiting in the local queue are taken together; those that differ only in
+    prompt / seed are denoised in one pipeline call and every job still gets its own result, under its own id and seed."""
+    from chiaswarm_b200.diffusion import pipelines
+
+    calls = []
+    real = pipelines.StableDiffusionPipeline.__call__
+
+    def spy(self, *a, **k):
+        calls.append(k.get("prompt"))
+        return real(self, *a, **k)
+
+    monkeypatch.setattr(pipelines.StableDiffusionPipeline, "__call__", spy)
+
+    async def main():
+        hive = FakeHive()
+        uri = await hive.start()
+        base = {"model_name": "tiny-sd", "height": 64, "width": 64, "num_inference_steps": 1}
+        hive.jobs = [dict(base, id=f"j{i}", prompt=f"prompt {i}", seed=10 + i) for i in range(4)]
+        try:
+            w = _worker(uri)
+            w.settings.prefetch_jobs, w.settings.max_batch = 4, 4
+
+            async def fast_sleep(s):
+                await asyncio.sleep(0)
+
+            w.result_worker.__func__.__defaults__ = (fast_sleep,)
+            await w.run(max_polls=2, sleep=fast_sleep)
+            by_id = {r["id"]: r for r in hive.results}
+            assert sorted(by_id) == ["j0", "j1", "j2", "j3"]
+            assert [by_id[f"j{i}"]["pipeline_config"]["seed"] for i in range(4)] == [10, 11, 12, 13]
+            assert all("blob" in r["artifacts"]["primary"] for r in hive.results)
+            blobs = {r["artifacts"]["primary"]["sha256_hash"] for r in hive.results}
+            assert len(blobs) == 4                                              # four different images
+            merged = [c for c in calls if isinstance(c, list)]
+            assert merged and sum(len(c) for c in merged) + sum(1 for c in calls if isinstance(c, str)) == 4
+            assert len(calls) < 4                                               # fewer pipeline calls than jobs
+            assert w.metrics.value("swarm_jobs_total", {"workflow": "image", "outcome": "ok"}) == 4
+        finally:
+            await hive.stop()
+
+    asyncio.run(main())
