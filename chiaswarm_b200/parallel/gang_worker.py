@@ -391,6 +391,10 @@ class GangWorker(Worker):
             logging.exception(e)
             return GangScheduler._error_result(job, f"gang scheduler: {type(e).__name__}: {e}")
 
+    async def execute_batch(self, jobs, lane):
+        """Gang jobs are not merged (a lease is per job): `settings.max_batch` only lets one lane take several at once."""
+        return [await self.execute(job, lane) for job in jobs]
+
     async def drain(self):
         await super().drain()
         self.scheduler.stop()
