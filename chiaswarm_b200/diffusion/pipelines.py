@@ -300,6 +300,7 @@ class StableDiffusionPipeline:
         batch / world images; the images are all-gathered, so every rank returns the full set)."""
         if ignored:  # (diffusers raises on these; the hive's `unsupported_pipeline_arguments` exists to strip them)
             logging.warning("pipeline arguments without effect here: %s", sorted(ignored))
+        prompt = "" if prompt is None else prompt
         prompts = [prompt] if isinstance(prompt, str) else list(prompt)
         if prompt_embeds is not None and len(prompts) == 1 and prompt_embeds.shape[0] > 1:
             prompts = prompts * prompt_embeds.shape[0]
@@ -370,8 +371,17 @@ class StableDiffusionPipeline:
         sample = self.unet.config.get("sample_size", 64)
         height = int(height or sample * vae_scale)
         width = int(width or sample * vae_scale)
+        if height <= 0 or width <= 0 or int(num_inference_steps) < 1:
+            raise ValueError(f"height, width and num_inference_steps must be positive (got {height}, {width}, {num_inference_steps})")
         if height % vae_scale or width % vae_scale:
             raise ValueError(f"`height` and `width` have to be divisible by {vae_scale} but are {height} and {width}.")
+        # a size the UNet cannot halve at every level (600 x 800: latent 75 x 100): diffusers carries an explicit
+        # up-sample size through the up path; here the image is generated at the next size that halves cleanly and
+        # centre-cropped to what was asked for, so the result has the requested geometry
+        crop_to = None
+        if image is None and low_res is None and (height % fit or width % fit):
+            crop_to = (width, height)
+            height, width = -(-height // fit) * fit, -(-width // fit) * fit
         h8, w8 = height // vae_scale, width // vae_scale
 
         pix2pix = mode == "sd_pix2pix"
@@ -512,6 +522,9 @@ class StableDiffusionPipeline:
             return out
         pil = tensor_to_pil(images) if isinstance(images, torch.Tensor) and images.dtype != torch.uint8 else \
             [Image.fromarray(a) for a in images.cpu().numpy()]
+        if crop_to is not None:
+            left, top = (width - crop_to[0]) // 2, (height - crop_to[1]) // 2
+            pil = [im.crop((left, top, left + crop_to[0], top + crop_to[1])) for im in pil]
         with timer.stage("safety_checker"):
             pil, flags = self.run_safety_checker(pil)
         return PipelineOutput(images=pil, nsfw_content_detected=flags, latents=x,

@@ -174,7 +174,12 @@ def _message(e):
 
 def exception_image(e, content_type):
     message = _message(e)
-    buffer = image_to_buffer(image_from_text(message), content_type)
+    image = image_from_text(message)
+    try:
+        buffer = image_to_buffer(image, content_type)
+    except ValueError:  # an image type the packer does not write (the very reason the job failed, perhaps): still answer
+        content_type = "image/jpeg"
+        buffer = image_to_buffer(image, content_type)
     return {"primary": make_result(buffer, buffer, content_type)}, {"error": message}
 
 

@@ -368,3 +368,21 @@ def test_jobs_that_differ_only_in_prompt_and_seed_share_one_denoising_run(monkey
     monkeypatch.setattr(pipelines.StableDiffusionPipeline, "__call__", broken)
     again = synchronous_do_work_batch([dict(jobs[0]), dict(jobs[4])], dev)
     assert [r["id"] for r in again] == ["a", "c"] and all("error" not in r["pipeline_config"] for r in again)
+
+
+def test_awkward_but_legal_requests_are_answered():
+    """Sizes the UNet cannot halve at every level come back at the requested geometry; a missing prompt is the empty
+    prompt; an image type the packer cannot write and non-positive sizes are fatal errors WITH an artifact (the error image
+    falls back to JPEG) instead of an exception that loses the job."""
+    r = _run({"id": "s", "model_name": "tiny-sd", "prompt": "p", "height": 70, "width": 42, "num_inference_steps": 1, "seed": 1})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    assert decode_artifact_image(r["artifacts"]["primary"]).size == (42, 70)
+    r = _run({"id": "n", "model_name": "tiny-sd", "prompt": None, "height": 32, "width": 32, "num_inference_steps": 1})
+    assert "error" not in r["pipeline_config"], r["pipeline_config"]
+    r = _run({"id": "w", "model_name": "tiny-sd", "prompt": "p", "height": 32, "width": 32, "num_inference_steps": 1,
+              "content_type": "image/webp"})
+    assert r["fatal_error"] is True and "Invalid image format" in r["pipeline_config"]["error"]
+    assert r["artifacts"]["primary"]["content_type"] == "image/jpeg"
+    for bad in ({"height": -32, "width": 32}, {"height": 32, "width": 32, "num_inference_steps": 0}):
+        r = _run({"id": "b", "model_name": "tiny-sd", "prompt": "p", "num_inference_steps": 1, **bad})
+        assert r["fatal_error"] is True and "must be positive" in r["pipeline_config"]["error"]
