@@ -142,6 +142,8 @@ class TextToVideoPipeline:
                  num_inference_steps=50, guidance_scale=9.0, generator=None, output_type="np", gang=None, **ignored):
         """`gang` (parallel.runtime.Gang; every rank makes this call with the same seed): the clip is denoised
         frame-split over the gang and its frames are decoded by the VAE in per-rank shares, then all-gathered."""
+        if int(num_frames) < 1 or int(num_inference_steps) < 1:
+            raise ValueError(f"num_frames and num_inference_steps must be positive (got {num_frames}, {num_inference_steps})")
         vae_scale = 2 ** (len(self.vae.config["block_out_channels"]) - 1)
         sample = self.unet.config.get("sample_size", 32)
         height = int(height or sample * vae_scale)

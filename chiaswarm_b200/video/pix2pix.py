@@ -56,6 +56,8 @@ def model_video_callback(device_identifier, model_name, **kwargs):
 
     with tempfile.TemporaryDirectory() as tmp:
         tmp = pathlib.Path(tmp)
+        if not kwargs.get("video_uri"):
+            raise ValueError("vid2vid needs a video_uri")  # (ValueError: the hive must not re-issue what cannot succeed)
         video_path = download_video(tmp, kwargs.pop("video_uri"))
         frames, fps = get_frames(tmp, video_path)
         frames = frames[:MAX_FRAMES]
@@ -96,9 +98,9 @@ def model_video_callback(device_identifier, model_name, **kwargs):
 def download_video(tmpdir, video_uri):
     content_type, content_length = net.probe(video_uri)
     if not content_type.startswith("video"):
-        raise Exception(f"Input does not appear to be an video.\nContent type was {content_type}.")
+        raise ValueError(f"Input does not appear to be an video.\nContent type was {content_type}.")
     if int(content_length) > net.MAX_VIDEO_BYTES:
-        raise Exception(
+        raise ValueError(
             f"Input video too large.\nMax size is {net.MAX_VIDEO_BYTES} bytes.\nImage was {content_length}.")
     path = str(pathlib.Path(tmpdir).joinpath("input.mp4"))
     net.fetch_to_file(video_uri, path)
