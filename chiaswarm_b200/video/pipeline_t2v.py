@@ -150,6 +150,10 @@ class TextToVideoPipeline:
         width = int(width or sample * vae_scale)
         if height % vae_scale or width % vae_scale:
             raise ValueError(f"`height` and `width` have to be divisible by {vae_scale}")
+        fit = vae_scale * 2 ** (len(self.unet.config["block_out_channels"]) - 1)
+        if height <= 0 or width <= 0 or height % fit or width % fit:
+            # (a frame size the 3-D UNet cannot halve at every level would only fail later, inside the skip concatenation)
+            raise ValueError(f"`height` and `width` have to be positive multiples of {fit} for this model (got {height} x {width})")
         do_cfg = guidance_scale > 1.0
         ids = self.tokenizer([prompt]).to(self.device)
         cond = self.text_encoder(ids)[0]
