@@ -475,3 +475,20 @@ def test_weight_cache_sheds_entries_under_device_memory_pressure():
     for k in "pqr":
         cache3.get(k, mk)
     assert len(cache3) == 3
+
+
+def test_smoke_script_runs_every_workflow(tmp_path, monkeypatch, capsys):
+    """`python -m swarm.test` (reference: swarm/test.py): one job per workflow through the executor, a verdict per line,
+    the exit status counts real failures (a model that is not on the box is not one)."""
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path))
+    monkeypatch.setenv("SDAAS_KERNEL_BACKEND", "torch")
+    monkeypatch.delenv("SDAAS_TEST_VIDEO_URI", raising=False)
+    import importlib
+
+    smoke = importlib.import_module("swarm.test")
+    assert smoke.main(["--tiny", "txt2img", "txt2vid", "txt2audio", "vid2vid"]) == 0
+    out = capsys.readouterr().out
+    assert "txt2img    ok (image/jpeg" in out and "txt2vid    ok (video/mp4" in out
+    assert "txt2audio  error: Model cvssp/audioldm is not available locally" in out and "vid2vid    skipped" in out
+    with pytest.raises(SystemExit):
+        smoke.main(["nonsense"])
