@@ -513,3 +513,29 @@ def test_every_module_path_of_the_reference_resolves():
     assert last is images[-1] and len(video.getvalue()) > 100
     with pytest.raises(ValueError):
         make_video([], 1.0)
+
+
+def test_every_top_level_name_of_the_reference_exists_here():
+    """API surface: each function / class a reference module defines at top level is defined by the module of the same path
+    here (skipped where the reference tree is not mounted)."""
+    import ast
+    import glob
+    import importlib
+    import os
+
+    ref_root = "/root/reference/swarm"
+    if not os.path.isdir(ref_root):
+        pytest.skip("reference tree not present")
+    missing, checked = {}, 0
+    for f in sorted(glob.glob(ref_root + "/**/*.py", recursive=True)):
+        rel = os.path.relpath(f, ref_root)[:-3].replace("/", ".")
+        if rel.endswith("__init__"):
+            continue
+        names = [n.name for n in ast.parse(open(f).read()).body
+                 if isinstance(n, (ast.FunctionDef, ast.AsyncFunctionDef, ast.ClassDef))]
+        module = importlib.import_module("chiaswarm_b200." + rel)
+        checked += len(names)
+        lost = [n for n in names if not hasattr(module, n)]
+        if lost:
+            missing[rel] = lost
+    assert checked > 60 and not missing, missing
