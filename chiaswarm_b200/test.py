@@ -34,9 +34,15 @@ def jobs(tiny: bool):
     }
 
 
-async def run_test(name, job, device) -> str:
+async def run_test(job, device=None, name="job") -> str:
+    """One job through the executor; returns the verdict line (the reference's `run_test(job)` prints it)."""
     from .generator import do_work
+    from .gpu.device import Device
 
+    if device is None:
+        import torch
+
+        device = Device(0) if torch.cuda.is_available() else Device("cpu")
     result = await do_work(dict(job, id=f"__test_{name}__", outputs=["primary"]), device)
     error = result["pipeline_config"].get("error")
     kind = result["artifacts"]["primary"]["content_type"]
@@ -64,7 +70,7 @@ def main(argv=None) -> int:
         if name == "vid2vid" and not table[name]["video_uri"]:
             print(f"{name:10} skipped (set SDAAS_TEST_VIDEO_URI to a video)")
             continue
-        verdict = asyncio.run(run_test(name, table[name], device))
+        verdict = asyncio.run(run_test(table[name], device, name))
         print(f"{name:10} {verdict}")
         if verdict.startswith("error") and "not available locally" not in verdict and "local checkpoints" not in verdict:
             failed += 1
