@@ -34,6 +34,12 @@ def jobs(tiny: bool):
     }
 
 
+# the reference's literal job dictionaries, by their names there (swarm/test.py:7-59)
+_full = jobs(False)
+test_job, txt2audio_job, vid2vid_job = _full["txt2img"], _full["txt2audio"], _full["vid2vid"]
+txt2vidJob, bark_job, if_job = _full["txt2vid"], _full["bark"], _full["if"]
+
+
 async def run_test(job, device=None, name="job") -> str:
     """One job through the executor; returns the verdict line (the reference's `run_test(job)` prints it)."""
     from .generator import do_work

@@ -459,6 +459,14 @@ async def run_worker():
     await _get().run()
 
 
+def __getattr__(name):
+    """The reference's module-level state (`swarm.worker.settings`, `.hive_uri`, `.result_queue`, read at import there,
+    swarm/worker.py:30-33): served from the process-wide Worker on first use, so importing this module has no side effects."""
+    if name in ("settings", "hive_uri", "result_queue"):
+        return getattr(_get(), name)
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+
+
 def main() -> int:
     """Console entry point (`chiaswarm-worker`, `python -m chiaswarm_b200.worker`)."""
     asyncio.run(run_worker())

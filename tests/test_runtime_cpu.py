@@ -534,6 +534,8 @@ def test_every_top_level_name_of_the_reference_exists_here():
         names = [n.name for n in ast.parse(open(f).read()).body
                  if isinstance(n, (ast.FunctionDef, ast.AsyncFunctionDef, ast.ClassDef))]
         module = importlib.import_module("chiaswarm_b200." + rel)
+        names += [t.id for n in ast.parse(open(f).read()).body if isinstance(n, ast.Assign)
+                  for t in n.targets if isinstance(t, ast.Name)]                       # module-level variables too
         checked += len(names)
         lost = [n for n in names if not hasattr(module, n)]
         if lost:
