@@ -8,9 +8,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 @pytest.fixture(autouse=True)
 def _local_job_inputs(tmp_path, monkeypatch):
-    """The suite feeds images as data: / file:// URIs; a worker accepts those only when told to (net.py)."""
+    """The suite feeds images as data: / file:// URIs; a worker accepts those only when told to (net.py).  Settings, logs,
+    the result spool and models.json live under SDAAS_ROOT: every test gets its own, so nothing is written to ~/.sdaas
+    (tests that set SDAAS_ROOT themselves override this)."""
     from chiaswarm_b200 import net
 
+    monkeypatch.setenv("SDAAS_ROOT", str(tmp_path / "sdaas_root"))
     monkeypatch.setenv("SDAAS_LOCAL_INPUT_ROOT", str(tmp_path))
     net.allow_local_inputs(True)
     yield
