@@ -140,7 +140,9 @@ class Worker:
         try:
             while (max_polls is None or self.polls < max_polls) and not self._stop.is_set():
                 while self.work_queue.full() and not self._stop.is_set():
-                    await self._nap(1, sleep)
+                    # (a local check, no hive traffic: with a prefetch queue it is looked at often enough that a fast lane
+                    # does not drain the queue and idle before the next poll goes out)
+                    await self._nap(0.05 if getattr(self, "prefetch", 0) else 1, sleep)
                 if self._stop.is_set():
                     break
                 delay = await self.ask_for_work()
