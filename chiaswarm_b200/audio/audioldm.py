@@ -25,7 +25,12 @@ def txt2audio_diffusion_callback(device_identifier, model_name, **kwargs):
 
     from .pipeline_audioldm import AudioLDMPipeline
 
-    pipeline = AudioLDMPipeline.from_pretrained(model_name, torch_dtype=torch.float16, device=device_identifier)
+    from ..utils.weight_cache import pipeline_cache
+
+    # resident between jobs (the reference reloads the pipeline from disk for every clip)
+    pipeline = pipeline_cache().get(
+        ("audioldm", model_name, str(device_identifier)),
+        lambda: AudioLDMPipeline.from_pretrained(model_name, torch_dtype=torch.float16, device=device_identifier))
     pipeline.set_scheduler(scheduler_type)
     audio = pipeline(**kwargs).audios[0]
     buffer, ctype = encode_audio(np.asarray(audio), SAMPLE_RATE, content_type)
