@@ -55,6 +55,7 @@ def test_caption_job_with_a_local_checkpoint(tmp_path):
     _tiny_blip(tmp_path / "models" / "Salesforce" / "blip-tiny")
     job = {"id": "c1", "workflow": "img2txt", "model_name": "Salesforce/blip-tiny", "start_image_uri": png_data_uri((40, 30)),
            "parameters": {"processor_type": "BlipProcessor", "model_type": "BlipForConditionalGeneration"}}
+    hits0, misses0 = pipeline_cache().hits, pipeline_cache().misses          # (process-wide counters: other tests count too)
     r = _run(dict(job, parameters=dict(job["parameters"])))
     assert "error" not in r["pipeline_config"], r["pipeline_config"]
     caption = r["pipeline_config"]["caption"]
@@ -63,12 +64,12 @@ def test_caption_job_with_a_local_checkpoint(tmp_path):
     assert json.loads(base64.b64decode(art["blob"])) == {"caption": caption}
     assert art["sha256_hash"] == hashlib.sha256(caption.encode()).hexdigest()     # the raw string is hashed (reference quirk)
     cache = pipeline_cache()
-    assert len(cache) == 1 and cache.bytes_resident() > 10_000 and cache.misses == 1
+    assert len(cache) == 1 and cache.bytes_resident() > 10_000 and cache.misses == misses0 + 1
     # the second job (prompted captioning this time) finds processor and model resident and is deterministic
     r2 = _run(dict(job, id="c2", prompt="a picture of", parameters=dict(job["parameters"])))
     r3 = _run(dict(job, id="c3", prompt="a picture of", parameters=dict(job["parameters"])))
     assert "error" not in r2["pipeline_config"] and r2["pipeline_config"]["caption"] == r3["pipeline_config"]["caption"]
-    assert cache.misses == 1 and cache.hits == 2
+    assert cache.misses == misses0 + 1 and cache.hits == hits0 + 2
     # a class name transformers does not have is a caption-shaped error, not an exception
     r4 = _run(dict(job, id="c4", parameters={"processor_type": "NoSuchProcessor", "model_type": "BlipForConditionalGeneration"}))
     assert "NoSuchProcessor" in r4["pipeline_config"]["error"]
