@@ -24,8 +24,9 @@ ENV SDAAS_ROOT=/sdaas/ \
     SDAAS_PARALLEL_MODE=dp \
     SDAAS_GANG_SIZE=1
 # one process per visible GPU; SDAAS_PARALLEL_MODE=patch + SDAAS_GANG_SIZE=2|4|8 leases gangs for single-image jobs
-# Prometheus text at :9100/metrics when SDAAS_METRICS_PORT=9100 (and SDAAS_METRICS_HOST=0.0.0.0) is set
-EXPOSE 9100
+# Prometheus text at :9100+<gpu>/metrics when SDAAS_METRICS_PORT=9100 (and SDAAS_METRICS_HOST=0.0.0.0) is set: one endpoint per
+# worker process in data-parallel mode, one (the hive client's) in gang mode
+EXPOSE 9100-9107
 # pre-flight as the container's health: GPUs are sm_100, the kernel library loads, peers can map each other
 HEALTHCHECK --interval=5m --timeout=90s --start-period=2m CMD python -m chiaswarm_b200.doctor --no-hive --json || exit 1
 CMD ["python", "-m", "chiaswarm_b200.parallel.launcher"]

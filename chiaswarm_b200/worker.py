@@ -118,7 +118,10 @@ class Worker:
         port = int(getattr(self.settings, "metrics_port", 0) or 0)
         if port > 0 and self._metrics_server is None:
             metrics_mod.register_gpu_gauges(self.metrics)
-            self._metrics_server = await metrics_mod.serve(self.metrics, port, getattr(self.settings, "metrics_host", "127.0.0.1"))
+            try:
+                self._metrics_server = await metrics_mod.serve(self.metrics, port, getattr(self.settings, "metrics_host", "127.0.0.1"))
+            except OSError as e:  # (port taken: serving jobs matters more than serving metrics)
+                logging.error("metrics endpoint on port %d not started: %s", port, e)
 
     async def run(self, max_polls: Optional[int] = None, sleep=asyncio.sleep):
         """The serve loop. `max_polls` bounds it for tests."""

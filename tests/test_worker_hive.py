@@ -472,3 +472,18 @@ def test_max_batch_merges_waiting_jobs_through_the_hive_loop(monkeypatch):
             await hive.stop()
 
     asyncio.run(main())
+
+
+def test_a_taken_metrics_port_does_not_stop_the_worker():
+    import socket
+
+    async def main():
+        with socket.socket() as taken:
+            taken.bind(("127.0.0.1", 0))
+            taken.listen(1)
+            w = _worker("http://127.0.0.1:9")
+            w.settings.metrics_port = taken.getsockname()[1]
+            await w.startup()                       # logs the failure, keeps going
+            assert w._metrics_server is None and w.work_queue.maxsize == 1
+
+    asyncio.run(main())
