@@ -39,6 +39,8 @@ def _child(gpu: int, worker_name_suffix: bool):
     settings = load_settings()
     if worker_name_suffix:
         settings.worker_name = f"{settings.worker_name}-gpu{gpu}"
+    base, ext = os.path.splitext(settings.log_filename)
+    settings.log_filename = f"{base}.gpu{gpu}{ext or '.log'}"  # one rotating log per process (the handler is not multi-process safe)
     if int(getattr(settings, "metrics_port", 0) or 0) > 0:
         settings.metrics_port = int(settings.metrics_port) + gpu  # one /metrics endpoint per worker process: base port + GPU index
     worker = Worker(settings=settings, devices=[Device(gpu)], cpu_lane=(gpu == 0))
