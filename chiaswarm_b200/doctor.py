@@ -136,13 +136,26 @@ def check_models() -> Check:
                  "" if len(have) == len(names) else "python -m chiaswarm_b200.initialize --download")
 
 
-REQUIRED = ("torch", "gpus", "native library")
+def check_environment() -> Check:
+    """Probe-only switches that must not be set on a serving worker."""
+    import os
+
+    if os.environ.get("SW_FUSED_DBG", "0") not in ("", "0"):
+        return Check("environment", "fail", f"SW_FUSED_DBG={os.environ['SW_FUSED_DBG']} switches synchronisation steps of the "
+                     "fused GEMM collectives off (a timing probe): results are wrong while it is set", "unset SW_FUSED_DBG")
+    if os.environ.get("SDAAS_KERNEL_BACKEND", "sm100") == "torch":
+        return Check("environment", "warn", "SDAAS_KERNEL_BACKEND=torch: jobs run on the eager oracle path, not on the sm_100a kernels")
+    return Check("environment", "ok", "no probe switches set")
+
+
+REQUIRED = ("torch", "gpus", "native library", "environment")
 
 
 def run(gpu_test: bool = False, hive: bool = True) -> List[Check]:
     checks = [_guard("torch", check_torch), _guard("gpus", check_gpus), _guard("native library", check_native_library)]
     if gpu_test and checks[1].status == "ok" and checks[2].status == "ok":
         checks.append(_guard("kernels", check_kernels_run))
+    checks.append(_guard("environment", check_environment))
     checks.append(_guard("peer access", check_peer_access))
     if hive:
         checks.append(_guard("hive", check_settings_and_hive))
