@@ -163,6 +163,16 @@ class Worker:
             print("stop requested: finishing the jobs in flight")
             stop.set()
 
+    def _on_signal(self):
+        """SIGTERM / SIGINT: the first one drains (`request_stop`), a second one leaves at once."""
+        if getattr(self, "_signalled", False):
+            import os
+
+            print("second signal: leaving without draining")
+            os._exit(130)
+        self._signalled = True
+        self.request_stop()
+
     def _install_signal_handlers(self):
         import signal
         import threading
@@ -172,7 +182,7 @@ class Worker:
         loop = asyncio.get_running_loop()
         for sig in (signal.SIGTERM, signal.SIGINT):
             try:
-                loop.add_signal_handler(sig, self.request_stop)
+                loop.add_signal_handler(sig, self._on_signal)
             except (NotImplementedError, RuntimeError, ValueError):  # platforms / loops without signal support
                 pass
 
