@@ -448,6 +448,23 @@ def test_console_scripts_point_at_real_functions():
         assert importlib.import_module(mod) is not None
 
 
+def test_editor_launch_configs_name_real_modules_and_settings():
+    """.vscode/launch.json (reference: .vscode/launch.json:14-37): every module a configuration launches exists and every
+    SDAAS_* variable it sets is one the settings loader reads."""
+    import importlib.util
+    import json
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    launch = json.load(open(os.path.join(root, ".vscode", "launch.json")))
+    known_env = open(os.path.join(root, "chiaswarm_b200", "settings.py")).read()
+    assert len(launch["configurations"]) >= 4
+    for cfg in launch["configurations"]:
+        assert importlib.util.find_spec(cfg["module"]) is not None, cfg["name"]
+        for var in cfg.get("env", {}):
+            assert f'"{var}"' in known_env, f"{cfg['name']}: {var} is not a settings variable"
+
+
 def test_weight_cache_sheds_entries_under_device_memory_pressure():
     """What the byte accounting cannot see (engine copies, graphs, other processes) is bounded by the free fraction of the
     device: least-recently-used entries go until enough is free again; the newest entry always stays."""
