@@ -483,9 +483,26 @@ def __getattr__(name):
 
 
 def main() -> int:
-    """Console entry point (`chiaswarm-worker`, `python -m chiaswarm_b200.worker`)."""
+    """Console entry point (`chiaswarm-worker`, `python -m chiaswarm_b200.worker`, `python -m swarm.worker`).
+
+    With gangs configured (`parallel_mode` gang / patch / auto / tp and `gang_size` > 1) the reference's start command must
+    not quietly serve one job per GPU: it hands over to the launcher, which owns the rank processes."""
+    if _wants_gangs(load_settings()):
+        from .parallel import launcher
+
+        print("gang mode is configured: starting the launcher (one hive client, one rank process per GPU)")
+        return int(launcher.main([]) or 0)
     asyncio.run(run_worker())
     return 0
+
+
+def _wants_gangs(settings) -> bool:
+    from .parallel.gang_worker import GANG_MODES
+
+    try:
+        return str(settings.parallel_mode).lower() in GANG_MODES and int(settings.gang_size) > 1
+    except (TypeError, ValueError):
+        return False
 
 
 if __name__ == "__main__":

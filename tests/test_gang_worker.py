@@ -346,3 +346,23 @@ def test_tp_mode_selects_head_parallel_attention_in_the_ranks():
             assert sched.submit({"id": "j", "model_name": "m", "workflow": "txt2vid"})["attn"] == want
         finally:
             sched.stop()
+
+
+def test_the_reference_start_command_hands_over_to_the_launcher_in_gang_mode(monkeypatch):
+    """`python -m swarm.worker` with gangs configured must not quietly serve one job per GPU (reference start command:
+    Dockerfile:37)."""
+    from chiaswarm_b200 import worker
+    from chiaswarm_b200.parallel import launcher
+    from chiaswarm_b200.settings import Settings
+
+    s = Settings()
+    s.parallel_mode, s.gang_size = "patch", 4
+    calls = []
+    monkeypatch.setattr(worker, "load_settings", lambda: s)
+    monkeypatch.setattr(launcher, "main", lambda argv=None: calls.append(argv) or 0)
+    monkeypatch.setattr(worker, "run_worker", lambda: (_ for _ in ()).throw(AssertionError("served dp")))
+    assert worker.main() == 0 and calls == [[]]
+    s.gang_size = 1  # gangs of one = the plain worker
+    assert not worker._wants_gangs(s)
+    s.parallel_mode, s.gang_size = "dp", 8
+    assert not worker._wants_gangs(s)
